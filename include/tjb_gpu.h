@@ -1,0 +1,127 @@
+/* libtjb_gpu — C ABI of the B200-native (sm_100a) replacement for tatajuba's hot path.
+ *
+ * tatajuba has no plugin/FFI interface; the seam is its internal C API (reference src/hopo_counter.h:61-81)
+ * as used by the per-sample OpenMP loop body (src/genome_set.c:69-78 and 84-93).  One call here stands in for
+ *
+ *     hc = new_or_append_hopo_counter_from_file (NULL, R1, opt);          src/hopo_counter.c:135-157
+ *     hc = new_or_append_hopo_counter_from_file (hc,   R2, opt);          (paired end only)
+ *     finalise_hopo_counter (hc);   -- steps 0-4 + coverage,              src/hopo_counter.c:339-415
+ *                                      i.e. everything BEFORE the mapper call at :416
+ *
+ * and returns the counter state exactly as the reference holds it when it calls BWA (src/hopo_counter.c:523):
+ * elem[] (reference-layout 40-byte hopo_element, reference order), n_elem, idx_initial[], idx_final[], n_idx,
+ * coverage.  INTEGRATION.md shows the ~30-line patch that makes the reference call this.
+ *
+ * Plain pointers and sizes only; no torch / CUDA types in any signature (streams and device pointers travel
+ * as void* / integers).  There is NO CPU fallback: every compute entry point returns TJB_ERR_CUDA when no
+ * sm_100-class device is usable.
+ */
+#ifndef TJB_GPU_H
+#define TJB_GPU_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* status of a counted sample; 1..3 mirror the reference's three "sample will be excluded" paths */
+enum {
+  TJB_OK = 0,
+  TJB_NO_HT = 1,                 /* hopo_counter.c:345-349  no tract at all                              */
+  TJB_NO_HT_AFTER_QC = 2,        /* hopo_counter.c:376-381  none left after strand-bias / singleton QC   */
+  TJB_NO_CTX_ABOVE_COVERAGE = 3, /* hopo_counter.c:406-411  no context reaches min_coverage              */
+  /* errors (negative): the reference would biomcmc_error() -> exit(EXIT_FAILURE) (lowlevel.c:39-53) */
+  TJB_ERR_CUDA = -1,
+  TJB_ERR_ARG = -2,
+  TJB_ERR_IO = -3,
+  TJB_ERR_NOMEM = -4,
+  TJB_ERR_TOO_LARGE = -5         /* more than INT32_MAX tract observations (the reference's int n_elem) */
+};
+
+/* the four tatajuba_options_t fields the path reads (src/hopo_counter.h:20-32); clamps as src/main.c:184-192 */
+typedef struct {
+  int32_t kmer_size;      /* -k, 2..32  flank length in bases                        */
+  int32_t min_tract_size; /* -m, 1..32  (effective minimum is max(m,2), hopo_counter.c:227-229) */
+  int32_t min_coverage;   /* -i, 0..65535                                            */
+  int32_t remove_biased;  /* 1 = default (keep canon_flag==3), 0 = "-b" (keep count>1) */
+  int32_t paired_end;     /* only echoed in warnings by the reference; not used by the arithmetic */
+} tjb_opts;
+
+/* counter state at the BWA boundary; replaces the fields of struct hopo_counter_struct (src/hopo_counter.h:51-59).
+ * elem/idx_initial/idx_final/name are malloc()'ed host memory owned by the caller (the reference free()s them,
+ * hopo_counter.c:180-183, 568-571); release with tjb_counter_out_free() or plain free(). */
+typedef struct {
+  int32_t status;            /* TJB_OK or one of the three drop codes; then n_elem = n_idx = 0 like the reference */
+  int32_t n_elem, n_idx, coverage;
+  void    *elem;             /* n_elem x 40-byte hopo_element (hopo_counter.h:34-49); mapping fields as initialised
+                                at hopo_counter.c:296-302 and read_offset = -1 as after :511 */
+  int32_t *idx_initial, *idx_final;
+  char    *name;             /* copy of the first file name (hopo_counter.c:145-149), NULL for buffer inputs */
+  /* diagnostics (not part of the reference state) */
+  int64_t n_reads, n_bases;  /* sequences / sequence bytes consumed (0 for device buffers: not counted there) */
+  int64_t n_raw;             /* tract observations before the reduce (hc->n_elem before finalise)       */
+  int64_t n_distinct;        /* distinct (base, contexts, length) before the QC filter                   */
+  int64_t n_skipped_nonacgt; /* qualifying runs of a non-ACGTU byte (undefined behaviour in the reference,
+                                hopo_counter.c:233-248): counted and skipped, see DESIGN.md                 */
+  double  ms_decode, ms_device; /* host FASTQ decode wall time; device time (CUDA events) for scan+reduce */
+} tjb_counter_out;
+
+typedef struct tjb_ctx tjb_ctx; /* one per (host thread, device): stream, pinned double buffers, device workspace */
+
+/* per-kernel timing, filled when profiling is on (CUDA events on the context's stream) */
+typedef struct {
+  char    name[48];
+  int64_t launches;
+  double  ms_total;
+  int64_t bytes_algorithmic; /* algorithmic bytes summed over those launches (DESIGN.md states the per-unit figure) */
+} tjb_kernel_stat;
+
+const char *tjb_version (void);
+const char *tjb_strerror (int code);
+/* last error message of this context (CUDA error string, file name, ...) */
+const char *tjb_ctx_last_error (const tjb_ctx *ctx);
+
+/* device = CUDA ordinal.  Fails with TJB_ERR_CUDA when there is no usable GPU (no CPU fallback exists). */
+int  tjb_ctx_create (int device, tjb_ctx **ctx);
+void tjb_ctx_destroy (tjb_ctx *ctx);
+/* the context's stream as a cudaStream_t cast to void* (for callers that time with their own events) */
+void *tjb_ctx_stream (tjb_ctx *ctx);
+int  tjb_ctx_set_profiling (tjb_ctx *ctx, int on);
+/* returns the number of kernels with at least one launch since the last reset; fills up to max_stats entries */
+int  tjb_ctx_kernel_stats (tjb_ctx *ctx, tjb_kernel_stat *stats, int max_stats);
+void tjb_ctx_reset_kernel_stats (tjb_ctx *ctx);
+/* kernels launched by this context since creation (or since reset_kernel_stats) */
+int64_t tjb_ctx_launch_count (const tjb_ctx *ctx);
+
+/* Whole replaced span from FASTQ/FASTA(.gz) files: n_files = 1 (single end) or 2 (R1 then R2 into one counter,
+ * genome_set.c:72-73).  Host C decode (kseq semantics, src/kseq.h:172-212) into pinned double-buffered chunks,
+ * scan per chunk overlapped with the next chunk's decode + H2D, then sort + reduce. */
+int tjb_count_sample_files (tjb_ctx *ctx, const char *const *files, int n_files, const tjb_opts *opt,
+                            tjb_counter_out *out);
+/* Same from sequences already decoded on the host: reads separated by '\n' (pageable or pinned memory). */
+int tjb_count_sample_host (tjb_ctx *ctx, const uint8_t *seqs, size_t n_bytes, const tjb_opts *opt,
+                           tjb_counter_out *out);
+/* Same from sequences resident in device memory (16-byte aligned, reads separated by '\n'). */
+int tjb_count_sample_device (tjb_ctx *ctx, const void *d_seqs, size_t n_bytes, const tjb_opts *opt,
+                             tjb_counter_out *out);
+
+/* One-shot, re-entrant form of tjb_count_sample_files for the reference's OpenMP loop body: uses a context
+ * cached per (calling thread, device). */
+int tjb_count_sample (const char *const *files, int n_files, const tjb_opts *opt, int device,
+                      tjb_counter_out *out);
+
+void tjb_counter_out_free (tjb_counter_out *out);
+
+/* host FASTQ/FASTA(.gz) decoder on its own (kseq semantics): appends "SEQ\n" per record to dst (capacity cap);
+ * returns bytes written (0 = end of file), <0 on error.  Exposed for tests and for callers that feed
+ * tjb_count_sample_host themselves. */
+typedef struct tjb_reader tjb_reader;
+tjb_reader *tjb_reader_open (const char *path);
+int64_t tjb_reader_fill (tjb_reader *r, uint8_t *dst, size_t cap, int64_t *n_reads, int64_t *n_bases);
+void tjb_reader_close (tjb_reader *r);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,185 @@
+"""ctypes bindings of the two CPU checkers (TEST INFRASTRUCTURE ONLY).
+
+* ``Restatement``  -> oracle/_build/libtjb_oracle.so (our plain-C restatement, oracle/tjb_oracle.c)
+* ``Reference``    -> oracle/_ref/libref_hotpath.so  (the unmodified reference sources, oracle/Makefile)
+
+Only tests/, ``__graft_entry__.smoke()`` and ``bench.py``'s cpu_baseline / ``--impl reference`` legs may import
+this module; nothing under ``tatajuba_b200/`` does.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ORACLE_SO = os.path.join(HERE, "_build", "libtjb_oracle.so")
+REF_SO = os.path.join(HERE, "_ref", "libref_hotpath.so")
+
+# numpy view of the reference's 40-byte hopo_element (src/hopo_counter.h:34-49)
+HOPO_DTYPE = np.dtype([("ctx0", "<u8"), ("ctx1", "<u8"), ("bits", "<u8"), ("read_offset", "<i4"),
+                       ("loc_ref_id", "<i4"), ("loc_pos", "<i4"), ("loc_last", "<i4")])
+assert HOPO_DTYPE.itemsize == 40
+BITS_MASK = np.uint64((1 << 52) - 1)  # bits 52..63 of the bit-field word are padding (uninitialised in the reference)
+
+
+def build(ref: bool = True) -> None:
+    """make the restatement, and the compiled reference when /root/reference is present"""
+    subprocess.run(["make", "-s", "-C", HERE, "oracle"] + (["ref"] if ref else []), check=True)
+
+
+def unpack_bits(bits):
+    """bit-field word -> dict of signed field values (base, length, count, mismatches, multi, neg_strand, canon_flag)"""
+    bits = np.asarray(bits, dtype=np.uint64)
+
+    def field(lo, width, signed=True):
+        v = ((bits >> np.uint64(lo)) & np.uint64((1 << width) - 1)).astype(np.int64)
+        if signed:
+            v = (v ^ (1 << (width - 1))) - (1 << (width - 1))
+        return v
+    return dict(base=field(0, 2), length=field(2, 10), count=field(12, 20), mismatches=field(32, 12),
+                multi=field(44, 3), neg_strand=field(47, 2), canon_flag=field(49, 3))
+
+
+class _RefDump(C.Structure):
+    _fields_ = [("status", C.c_int), ("n_raw", C.c_int), ("n_elem", C.c_int), ("n_idx", C.c_int),
+                ("coverage", C.c_int), ("elem", C.c_void_p), ("idx_initial", C.POINTER(C.c_int)),
+                ("idx_final", C.POINTER(C.c_int)), ("secs_scan", C.c_double), ("secs_finalise", C.c_double)]
+
+
+class _Rec(C.Structure):
+    _fields_ = [("ctx", C.c_uint64 * 2), ("base", C.c_int32), ("length", C.c_int32), ("count", C.c_int32),
+                ("flag", C.c_int32)]
+
+
+REC_DTYPE = np.dtype([("ctx0", "<u8"), ("ctx1", "<u8"), ("base", "<i4"), ("length", "<i4"), ("count", "<i4"),
+                      ("flag", "<i4")])
+assert REC_DTYPE.itemsize == C.sizeof(_Rec)
+
+
+class _Result(C.Structure):
+    _fields_ = [("status", C.c_int), ("n_raw", C.c_int64), ("n_skipped_nonacgt", C.c_int64),
+                ("n_distinct", C.c_int64), ("n_elem", C.c_int32), ("n_idx", C.c_int32), ("coverage", C.c_int32),
+                ("elem", C.POINTER(_Rec)), ("idx_initial", C.POINTER(C.c_int32)),
+                ("idx_final", C.POINTER(C.c_int32))]
+
+
+class Boundary:
+    """State at the BWA boundary, in comparable form."""
+
+    def __init__(self, status, n_raw, elem40, idx_initial, idx_final, coverage, n_skipped=0, secs=(0.0, 0.0)):
+        self.status = int(status)
+        self.n_raw = int(n_raw)
+        self.elem = elem40  # structured array, HOPO_DTYPE
+        self.idx_initial = idx_initial
+        self.idx_final = idx_final
+        self.coverage = int(coverage)
+        self.n_skipped_nonacgt = int(n_skipped)
+        self.secs_scan, self.secs_finalise = secs
+
+    @property
+    def n_elem(self):
+        return len(self.elem)
+
+    @property
+    def n_idx(self):
+        return len(self.idx_initial)
+
+    def canonical(self):
+        """tuple of plain arrays with padding bits masked (what "bit-exact" means for this struct)"""
+        e = self.elem
+        return (self.status, self.n_raw, self.coverage, e["ctx0"].tolist(), e["ctx1"].tolist(),
+                (e["bits"] & BITS_MASK).tolist(), e["read_offset"].tolist(), e["loc_ref_id"].tolist(),
+                e["loc_pos"].tolist(), e["loc_last"].tolist(), self.idx_initial.tolist(), self.idx_final.tolist())
+
+
+def assert_same_boundary(a: "Boundary", b: "Boundary", what=""):
+    assert a.status == b.status, f"{what}: status {a.status} != {b.status}"
+    assert a.n_raw == b.n_raw, f"{what}: n_raw {a.n_raw} != {b.n_raw}"
+    if a.status != 0:
+        return
+    assert a.n_elem == b.n_elem, f"{what}: n_elem {a.n_elem} != {b.n_elem}"
+    for f in ("ctx0", "ctx1", "read_offset", "loc_ref_id", "loc_pos", "loc_last"):
+        assert np.array_equal(a.elem[f], b.elem[f]), f"{what}: field {f} differs"
+    assert np.array_equal(a.elem["bits"] & BITS_MASK, b.elem["bits"] & BITS_MASK), f"{what}: bit-fields differ"
+    assert np.array_equal(a.idx_initial, b.idx_initial), f"{what}: idx_initial differs"
+    assert np.array_equal(a.idx_final, b.idx_final), f"{what}: idx_final differs"
+    assert a.coverage == b.coverage, f"{what}: coverage {a.coverage} != {b.coverage}"
+
+
+class Reference:
+    """the compiled, unmodified reference"""
+
+    def __init__(self):
+        if not os.path.exists(REF_SO):
+            raise FileNotFoundError(REF_SO)
+        self.lib = C.CDLL(REF_SO)
+        self.lib.ref_sizeof_hopo_element.restype = C.c_size_t
+        assert self.lib.ref_sizeof_hopo_element() == 40
+
+    @staticmethod
+    def available():
+        return os.path.exists(REF_SO)
+
+    def _collect(self, d):
+        n, g = (d.n_elem, d.n_idx) if d.status == 0 else (0, 0)
+        elem = np.zeros(n, dtype=HOPO_DTYPE)
+        if n:
+            C.memmove(elem.ctypes.data, d.elem, 40 * n)
+        ii = np.array(d.idx_initial[:g], dtype=np.int32) if g else np.zeros(0, np.int32)
+        jj = np.array(d.idx_final[:g], dtype=np.int32) if g else np.zeros(0, np.int32)
+        out = Boundary(d.status, d.n_raw, elem, ii, jj, d.coverage if d.status == 0 else 0,
+                       secs=(d.secs_scan, d.secs_finalise))
+        self.lib.ref_dump_free(C.byref(d))
+        return out
+
+    def run_files(self, files, k=25, m=4, min_coverage=5, remove_biased=True):
+        arr = (C.c_char_p * len(files))(*[os.fsencode(f) for f in files])
+        d = _RefDump()
+        self.lib.ref_hotpath_run_files(arr, len(files), k, m, min_coverage, int(remove_biased), C.byref(d))
+        return self._collect(d)
+
+    def run_buffer(self, buf: bytes, k=25, m=4, min_coverage=5, remove_biased=True):
+        d = _RefDump()
+        b = (C.c_char * len(buf)).from_buffer_copy(buf) if len(buf) else (C.c_char * 1)()
+        self.lib.ref_hotpath_run_buffer(b, C.c_size_t(len(buf)), k, m, min_coverage, int(remove_biased), C.byref(d))
+        return self._collect(d)
+
+
+class Restatement:
+    """our plain-C restatement"""
+
+    def __init__(self):
+        if not os.path.exists(ORACLE_SO):
+            build(ref=False)
+        self.lib = C.CDLL(ORACLE_SO)
+        self.lib.tjbo_scan_buffer.restype = C.c_int64
+
+    def run_buffer(self, buf, k=25, m=4, min_coverage=5, remove_biased=True):
+        buf = np.frombuffer(buf, dtype=np.uint8) if not isinstance(buf, np.ndarray) else buf
+        r = _Result()
+        self.lib.tjbo_count_buffer(C.c_void_p(buf.ctypes.data), C.c_size_t(buf.size), k, m, min_coverage,
+                                   int(remove_biased), C.byref(r))
+        n, g = (r.n_elem, r.n_idx) if r.status == 0 else (0, 0)
+        elem = np.zeros(n, dtype=HOPO_DTYPE)
+        if n:
+            self.lib.tjbo_pack_hopo_elements(r.elem, C.c_int64(n), C.c_void_p(elem.ctypes.data))
+        ii = np.array(r.idx_initial[:g], dtype=np.int32) if g else np.zeros(0, np.int32)
+        jj = np.array(r.idx_final[:g], dtype=np.int32) if g else np.zeros(0, np.int32)
+        out = Boundary(r.status, r.n_raw, elem, ii, jj, r.coverage if r.status == 0 else 0, r.n_skipped_nonacgt)
+        out.n_distinct = int(r.n_distinct)
+        self.lib.tjbo_free_result(C.byref(r))
+        return out
+
+    def scan_buffer(self, buf, k=25, m=4):
+        """raw scan records in emission order -> (structured array REC_DTYPE, n_skipped)"""
+        buf = np.frombuffer(buf, dtype=np.uint8) if not isinstance(buf, np.ndarray) else buf
+        p = C.POINTER(_Rec)()
+        skipped = C.c_int64(0)
+        n = self.lib.tjbo_scan_buffer(C.c_void_p(buf.ctypes.data), C.c_size_t(buf.size), k, m, C.byref(p),
+                                      C.byref(skipped))
+        out = np.zeros(n, dtype=REC_DTYPE)
+        if n:
+            C.memmove(out.ctypes.data, p, n * REC_DTYPE.itemsize)
+        self.lib.tjbo_free(p)
+        return out, int(skipped.value)

@@ -1,0 +1,594 @@
+// libtjb_gpu: context, workspace, stream orchestration and the C ABI declared in include/tjb_gpu.h.
+// Device work only — there is no host fallback for any compute step in this file.
+#include <chrono>
+#include <climits>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <string>
+#include <vector>
+
+#include "tjb_gpu.h"
+#include "tjb_common.cuh"
+#include "tjb_scan.cuh"
+#include "tjb_sort.cuh"
+#include "tjb_reduce.cuh"
+
+#define TJB_VERSION_STR "tatajuba_b200 0.1 (sm_100a)"
+#define TJB_CHUNK_BYTES (64u << 20) // host->device chunk of decoded reads
+
+enum KernelId { K_SCAN = 0, K_SORT_HIST, K_SORT_SCATTER, K_PSCAN, K_RLE, K_GROUP, K_COVERAGE, K_PACK, K_COUNT };
+static const char *kKernelNames[K_COUNT] = {"tjb_scan_kernel", "rsort_hist_kernel", "rsort_scatter_kernel", "pscan_kernels",
+                                            "rle_kernels", "group_kernels", "coverage_kernels", "pack_hopo_kernel"};
+
+struct DevBuf {
+  void *p = nullptr;
+  size_t cap = 0;
+};
+
+struct PendingEvent { int kid; cudaEvent_t a, b; };
+
+struct tjb_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  std::string err;
+  int profiling = 0; // 0 off, 1 scan kernel only, 2 every kernel
+  int64_t launches = 0;
+  tjb_kernel_stat stats[K_COUNT];
+  std::vector<PendingEvent> pending;
+  std::vector<cudaEvent_t> free_events;
+  int sm_count = 148;
+
+  uint8_t *h_pinned[2] = {nullptr, nullptr};
+  cudaEvent_t h_free[2] = {nullptr, nullptr}; // pinned buffer i may be overwritten once this has fired
+  DevBuf d_chunk[2];
+
+  DevBuf rec_a, rec_b; // raw tract observations + sort ping-pong
+  size_t rec_capacity = 0; // records rec_a can hold
+  int rec_words = 0;
+  unsigned long long n_raw_known = 0, n_skip_known = 0;
+  const uint8_t *pend_ptr = nullptr; size_t pend_len = 0; bool pend = false; // scan launched, overflow not checked yet
+  unsigned long long *d_counters = nullptr; // [0] = n_raw, [1] = skipped non-ACGTU runs
+  u32 *d_totals = nullptr;                  // small device scalars
+  int *d_cov = nullptr;
+  DevBuf hist, ptmp, heads, pos, seg, drec, dcount, keep, kpos, krec, kcount, cw, csum, gkeep, gkpos, pairs_a, pairs_b, out40,
+      idx_i, idx_f;
+
+  cudaEvent_t ev_t0 = nullptr, ev_t1 = nullptr;
+};
+
+// ------------------------------------------------------------------------------------------- helpers ----
+#define CU(call)                                                                                        \
+  do {                                                                                                  \
+    cudaError_t e_ = (call);                                                                            \
+    if (e_ != cudaSuccess) {                                                                            \
+      ctx->err = std::string (#call) + ": " + cudaGetErrorString (e_);                                  \
+      return TJB_ERR_CUDA;                                                                              \
+    }                                                                                                   \
+  } while (0)
+#define TRY(call)                \
+  do {                           \
+    int rc_ = (call);            \
+    if (rc_ < 0) return rc_;     \
+  } while (0)
+
+static int ensure (tjb_ctx *ctx, DevBuf &b, size_t bytes)
+{
+  if (bytes <= b.cap) return 0;
+  size_t want = bytes + bytes / 4 + 256;
+  if (b.p) { CU (cudaStreamSynchronize (ctx->stream)); CU (cudaFree (b.p)); b.p = nullptr; b.cap = 0; }
+  CU (cudaMalloc (&b.p, want));
+  b.cap = want;
+  return 0;
+}
+
+static cudaEvent_t get_event (tjb_ctx *ctx)
+{
+  if (!ctx->free_events.empty ()) { cudaEvent_t e = ctx->free_events.back (); ctx->free_events.pop_back (); return e; }
+  cudaEvent_t e = nullptr;
+  cudaEventCreate (&e);
+  return e;
+}
+
+struct LaunchScope { // counts a launch and, when profiling, brackets it with events on the context's stream
+  tjb_ctx *ctx; int kid; bool timed; cudaEvent_t a = nullptr, b = nullptr;
+  LaunchScope (tjb_ctx *c, int k, int64_t alg_bytes) : ctx (c), kid (k)
+  {
+    timed = ctx->profiling >= 2 || (ctx->profiling == 1 && kid == K_SCAN);
+    ctx->launches++;
+    ctx->stats[kid].launches++;
+    ctx->stats[kid].bytes_algorithmic += alg_bytes;
+    if (timed) { a = get_event (ctx); b = get_event (ctx); cudaEventRecord (a, ctx->stream); }
+  }
+  ~LaunchScope ()
+  {
+    if (timed) { cudaEventRecord (b, ctx->stream); ctx->pending.push_back ({kid, a, b}); }
+  }
+};
+#define LAUNCH(kid, alg_bytes, ...) do { LaunchScope ls_ (ctx, kid, (int64_t) (alg_bytes)); __VA_ARGS__; } while (0)
+
+static void resolve_events (tjb_ctx *ctx) // call only after the stream has been synchronised
+{
+  for (auto &p : ctx->pending) {
+    float ms = 0.f;
+    if (cudaEventElapsedTime (&ms, p.a, p.b) == cudaSuccess) ctx->stats[p.kid].ms_total += ms;
+    ctx->free_events.push_back (p.a);
+    ctx->free_events.push_back (p.b);
+  }
+  ctx->pending.clear ();
+}
+
+static inline u32 nblk (size_t n, u32 per) { return (u32) ((n + per - 1) / per); }
+
+// ------------------------------------------------------------------------------------ scan + sort -------
+static int exclusive_scan (tjb_ctx *ctx, const u32 *in, u32 *out, size_t n, u32 *tmp, u32 *total_out)
+{
+  if (n <= PSCAN_TILE) {
+    LAUNCH (K_PSCAN, 8 * n, (pscan_scan_kernel<<<1, PSCAN_THREADS, 0, ctx->stream>>> (in, out, nullptr, n, total_out)));
+    return 0;
+  }
+  u32 nb = nblk (n, PSCAN_TILE);
+  LAUNCH (K_PSCAN, 4 * n, (pscan_reduce_kernel<<<nb, PSCAN_THREADS, 0, ctx->stream>>> (in, tmp, n)));
+  TRY (exclusive_scan (ctx, tmp, tmp, nb, tmp + nb, nullptr));
+  LAUNCH (K_PSCAN, 8 * n, (pscan_scan_kernel<<<nb, PSCAN_THREADS, 0, ctx->stream>>> (in, out, tmp, n, total_out)));
+  return 0;
+}
+
+static void add_digits (std::vector<DigitDesc> &v, int word, int lo, int nbits)
+{
+  for (int done = 0; done < nbits; done += RSORT_RADIX_BITS) {
+    int nb = nbits - done < RSORT_RADIX_BITS ? nbits - done : RSORT_RADIX_BITS;
+    v.push_back ({word, lo + done, nb});
+  }
+}
+// least significant digit first: flag < length < ctx1 < ctx0 < base (see tjb_common.cuh)
+static std::vector<DigitDesc> tract_digits (int W, int k)
+{
+  std::vector<DigitDesc> v;
+  if (W == 2) { add_digits (v, 0, 0, 12 + 2 * k); add_digits (v, 1, 0, 2 * k + 1); }
+  else { add_digits (v, 0, 0, 12); add_digits (v, 1, 0, 2 * k); add_digits (v, 2, 0, 2 * k); add_digits (v, 0, 12, 1); }
+  return v;
+}
+
+template <int W>
+static int radix_sort (tjb_ctx *ctx, u64 *a, u64 *b, size_t n, const std::vector<DigitDesc> &digits, u64 **sorted)
+{
+  u32 n_tiles = nblk (n, RSORT_TILE);
+  size_t hn = (size_t) RSORT_RADIX * n_tiles;
+  TRY (ensure (ctx, ctx->hist, hn * sizeof (u32)));
+  TRY (ensure (ctx, ctx->ptmp, pscan_tmp_elems (hn > n ? hn : n) * sizeof (u32) + 64));
+  u32 *hist = (u32*) ctx->hist.p;
+  for (const DigitDesc &dd : digits) {
+    LAUNCH (K_SORT_HIST, 8 * W * n, (rsort_hist_kernel<W><<<n_tiles, RSORT_THREADS, 0, ctx->stream>>> (a, n, dd, hist, n_tiles)));
+    TRY (exclusive_scan (ctx, hist, hist, hn, (u32*) ctx->ptmp.p, nullptr));
+    LAUNCH (K_SORT_SCATTER, 16 * W * n, (rsort_scatter_kernel<W><<<n_tiles, RSORT_THREADS, 0, ctx->stream>>> (a, b, n, dd, hist, n_tiles)));
+    u64 *t = a; a = b; b = t;
+  }
+  *sorted = a;
+  return 0;
+}
+
+static int grow_records (tjb_ctx *ctx, size_t want_records)
+{
+  if (want_records <= ctx->rec_capacity) return 0;
+  size_t bytes = want_records * ctx->rec_words * sizeof (u64);
+  void *np = nullptr;
+  CU (cudaMalloc (&np, bytes));
+  if (ctx->rec_a.p && ctx->n_raw_known)
+    CU (cudaMemcpyAsync (np, ctx->rec_a.p, (size_t) ctx->n_raw_known * ctx->rec_words * sizeof (u64), cudaMemcpyDeviceToDevice, ctx->stream));
+  CU (cudaStreamSynchronize (ctx->stream));
+  if (ctx->rec_a.p) CU (cudaFree (ctx->rec_a.p));
+  ctx->rec_a.p = np; ctx->rec_a.cap = bytes;
+  ctx->rec_capacity = want_records;
+  return 0;
+}
+
+static int begin_sample (tjb_ctx *ctx, const tjb_opts *opt)
+{
+  if (!opt || opt->kmer_size < 2 || opt->kmer_size > 32 || opt->min_tract_size < 1 || opt->min_coverage < 0) {
+    ctx->err = "options out of range (kmer_size 2..32, min_tract_size >= 1, min_coverage >= 0)";
+    return TJB_ERR_ARG;
+  }
+  CU (cudaSetDevice (ctx->device));
+  int W = tjb_rec_words (opt->kmer_size);
+  if (W != ctx->rec_words) { ctx->rec_words = W; ctx->rec_capacity = ctx->rec_a.cap / (W * sizeof (u64)); }
+  ctx->n_raw_known = ctx->n_skip_known = 0;
+  ctx->pend = false;
+  CU (cudaMemsetAsync (ctx->d_counters, 0, 2 * sizeof (unsigned long long), ctx->stream));
+  return 0;
+}
+
+static int launch_scan (tjb_ctx *ctx, const uint8_t *d_seqs, size_t n, const tjb_opts *opt)
+{
+  long long n_tiles = (long long) ((n + SCAN_TILE - 1) / SCAN_TILE);
+  if (!n_tiles) return 0;
+  int min_len = opt->min_tract_size < 2 ? 2 : opt->min_tract_size;
+  long long grid = n_tiles < (long long) ctx->sm_count * 4 ? n_tiles : (long long) ctx->sm_count * 4;
+  // algorithmic bytes of this launch: every sequence byte read once (+ 8W bytes per emitted record, added by the caller)
+  if (ctx->rec_words == 2)
+    LAUNCH (K_SCAN, n, (tjb_scan_kernel<2><<<(u32) grid, SCAN_THREADS, 0, ctx->stream>>> (d_seqs, (long long) n, opt->kmer_size, min_len, (u64*) ctx->rec_a.p, ctx->rec_capacity, ctx->d_counters, n_tiles)));
+  else
+    LAUNCH (K_SCAN, n, (tjb_scan_kernel<3><<<(u32) grid, SCAN_THREADS, 0, ctx->stream>>> (d_seqs, (long long) n, opt->kmer_size, min_len, (u64*) ctx->rec_a.p, ctx->rec_capacity, ctx->d_counters, n_tiles)));
+  CU (cudaGetLastError ());
+  return 0;
+}
+
+// Launches the scan of one device-resident chunk (asynchronous).  The record array is grown beforehand to an estimate;
+// scan_resolve() then synchronises and, if the chunk overflowed the array (overflowing records are counted but never
+// written), grows it to the exact size and re-runs the chunk from the pre-chunk counter values.
+static int scan_launch (tjb_ctx *ctx, const uint8_t *d_seqs, size_t n, const tjb_opts *opt)
+{
+  size_t guess = (size_t) ctx->n_raw_known + n / 16 + 65536;
+  TRY (grow_records (ctx, guess));
+  TRY (launch_scan (ctx, d_seqs, n, opt));
+  ctx->pend_ptr = d_seqs; ctx->pend_len = n; ctx->pend = true;
+  return 0;
+}
+static int scan_resolve (tjb_ctx *ctx, const tjb_opts *opt)
+{
+  if (!ctx->pend) return 0;
+  ctx->pend = false;
+  unsigned long long cnt[2];
+  CU (cudaMemcpyAsync (cnt, ctx->d_counters, sizeof (cnt), cudaMemcpyDeviceToHost, ctx->stream));
+  CU (cudaStreamSynchronize (ctx->stream));
+  if (cnt[0] > ctx->rec_capacity) {
+    unsigned long long back[2] = {ctx->n_raw_known, ctx->n_skip_known};
+    TRY (grow_records (ctx, (size_t) cnt[0] + 1024));
+    CU (cudaMemcpyAsync (ctx->d_counters, back, sizeof (back), cudaMemcpyHostToDevice, ctx->stream));
+    TRY (launch_scan (ctx, ctx->pend_ptr, ctx->pend_len, opt));
+    CU (cudaMemcpyAsync (cnt, ctx->d_counters, sizeof (cnt), cudaMemcpyDeviceToHost, ctx->stream));
+    CU (cudaStreamSynchronize (ctx->stream));
+  }
+  ctx->n_raw_known = cnt[0];
+  ctx->n_skip_known = cnt[1];
+  return 0;
+}
+static int scan_chunk (tjb_ctx *ctx, const uint8_t *d_seqs, size_t n, const tjb_opts *opt)
+{
+  TRY (scan_launch (ctx, d_seqs, n, opt));
+  return scan_resolve (ctx, opt);
+}
+
+// --------------------------------------------------------------------------------------- finalise -------
+template <int W>
+static int finalise_t (tjb_ctx *ctx, const tjb_opts *opt, tjb_counter_out *out)
+{
+  const int k = opt->kmer_size;
+  cudaStream_t st = ctx->stream;
+  unsigned long long cnt[2];
+  CU (cudaMemcpyAsync (cnt, ctx->d_counters, sizeof (cnt), cudaMemcpyDeviceToHost, st));
+  CU (cudaStreamSynchronize (st));
+  out->n_raw = (int64_t) cnt[0];
+  out->n_skipped_nonacgt = (int64_t) cnt[1];
+  if (cnt[0] == 0) { out->status = TJB_NO_HT; return 0; }
+  if (cnt[0] > (unsigned long long) INT32_MAX) { ctx->err = "more than INT32_MAX tract observations"; return TJB_ERR_TOO_LARGE; }
+  const u32 n = (u32) cnt[0];
+
+  // 1. sort (hopo_counter.c:351)
+  TRY (ensure (ctx, ctx->rec_b, (size_t) n * W * sizeof (u64)));
+  u64 *sorted = nullptr;
+  TRY ((radix_sort<W> (ctx, (u64*) ctx->rec_a.p, (u64*) ctx->rec_b.p, n, tract_digits (W, k), &sorted)));
+
+  // 2. run-length count (:352-365) + QC filter (:367-374)
+  TRY (ensure (ctx, ctx->heads, (size_t) n * 4)); TRY (ensure (ctx, ctx->pos, (size_t) n * 4)); TRY (ensure (ctx, ctx->seg, (size_t) n * 4));
+  TRY (ensure (ctx, ctx->ptmp, pscan_tmp_elems (n) * 4 + 64));
+  u32 *heads = (u32*) ctx->heads.p, *pos = (u32*) ctx->pos.p, *seg = (u32*) ctx->seg.p, *ptmp = (u32*) ctx->ptmp.p;
+  u32 h_tot[4];
+  LAUNCH (K_RLE, 16 * W * n, (head_kernel<W, 0><<<nblk (n, RED_THREADS), RED_THREADS, 0, st>>> (sorted, n, heads)));
+  TRY (exclusive_scan (ctx, heads, pos, n, ptmp, ctx->d_totals + 0));
+  CU (cudaMemcpyAsync (h_tot, ctx->d_totals, 4, cudaMemcpyDeviceToHost, st));
+  LAUNCH (K_RLE, 12 * n, (seg_start_kernel<<<nblk (n, RED_THREADS), RED_THREADS, 0, st>>> (heads, pos, n, seg)));
+  CU (cudaStreamSynchronize (st));
+  const u32 n_dist = h_tot[0];
+  out->n_distinct = n_dist;
+  TRY (ensure (ctx, ctx->drec, (size_t) n_dist * W * 8)); TRY (ensure (ctx, ctx->dcount, (size_t) n_dist * 4));
+  TRY (ensure (ctx, ctx->keep, (size_t) n_dist * 4)); TRY (ensure (ctx, ctx->kpos, (size_t) n_dist * 4));
+  LAUNCH (K_RLE, (16 * W + 12) * (size_t) n_dist, (rle_emit_kernel<W><<<nblk (n_dist, RED_THREADS), RED_THREADS, 0, st>>> (sorted, n, seg, n_dist, opt->remove_biased, (u64*) ctx->drec.p, (int*) ctx->dcount.p, (u32*) ctx->keep.p)));
+  TRY (exclusive_scan (ctx, (u32*) ctx->keep.p, (u32*) ctx->kpos.p, n_dist, ptmp, ctx->d_totals + 1));
+  CU (cudaMemcpyAsync (h_tot, ctx->d_totals + 1, 4, cudaMemcpyDeviceToHost, st));
+  CU (cudaStreamSynchronize (st));
+  const u32 n_keep = h_tot[0];
+  if (!n_keep) { out->status = TJB_NO_HT_AFTER_QC; return 0; }
+  TRY (ensure (ctx, ctx->krec, (size_t) n_keep * W * 8)); TRY (ensure (ctx, ctx->kcount, (size_t) n_keep * 4));
+  u64 *krec = (u64*) ctx->krec.p; int *kcount = (int*) ctx->kcount.p;
+  LAUNCH (K_RLE, (16 * W + 8) * (size_t) n_keep, (compact_kernel<W><<<nblk (n_dist, RED_THREADS), RED_THREADS, 0, st>>> ((u64*) ctx->drec.p, (int*) ctx->dcount.p, (u32*) ctx->keep.p, (u32*) ctx->kpos.p, n_dist, krec, kcount)));
+
+  // 3. context groups above min coverage (:388-413); heads/pos/seg are free again (n_keep <= n)
+  TRY (ensure (ctx, ctx->cw, (size_t) n_keep * 4)); TRY (ensure (ctx, ctx->csum, (size_t) n_keep * 4));
+  TRY (ensure (ctx, ctx->gkeep, (size_t) n_keep * 4)); TRY (ensure (ctx, ctx->gkpos, (size_t) n_keep * 4));
+  LAUNCH (K_GROUP, 16 * W * (size_t) n_keep, (head_kernel<W, 1><<<nblk (n_keep, RED_THREADS), RED_THREADS, 0, st>>> (krec, n_keep, heads)));
+  TRY (exclusive_scan (ctx, heads, pos, n_keep, ptmp, ctx->d_totals + 0));
+  LAUNCH (K_GROUP, 12 * (size_t) n_keep, (seg_start_kernel<<<nblk (n_keep, RED_THREADS), RED_THREADS, 0, st>>> (heads, pos, n_keep, seg)));
+  LAUNCH (K_GROUP, 8 * (size_t) n_keep, (icopy_kernel<<<nblk (n_keep, RED_THREADS), RED_THREADS, 0, st>>> (kcount, n_keep, (u32*) ctx->cw.p)));
+  TRY (exclusive_scan (ctx, (u32*) ctx->cw.p, (u32*) ctx->csum.p, n_keep, ptmp, ctx->d_totals + 2));
+  CU (cudaMemcpyAsync (h_tot, ctx->d_totals, 4, cudaMemcpyDeviceToHost, st));
+  CU (cudaStreamSynchronize (st));
+  const u32 n_groups = h_tot[0];
+  LAUNCH (K_GROUP, 12 * (size_t) n_groups, (group_keep_kernel<<<nblk (n_groups, RED_THREADS), RED_THREADS, 0, st>>> (seg, n_groups, n_keep, (u32*) ctx->csum.p, ctx->d_totals + 2, opt->min_coverage, (u32*) ctx->gkeep.p)));
+  TRY (exclusive_scan (ctx, (u32*) ctx->gkeep.p, (u32*) ctx->gkpos.p, n_groups, ptmp, ctx->d_totals + 3));
+  CU (cudaMemcpyAsync (h_tot, ctx->d_totals + 3, 4, cudaMemcpyDeviceToHost, st));
+  CU (cudaStreamSynchronize (st));
+  const u32 n_idx = h_tot[0];
+  if (!n_idx) { out->status = TJB_NO_CTX_ABOVE_COVERAGE; return 0; }
+  TRY (ensure (ctx, ctx->idx_i, (size_t) n_idx * 4)); TRY (ensure (ctx, ctx->idx_f, (size_t) n_idx * 4));
+  LAUNCH (K_GROUP, 16 * (size_t) n_groups, (group_emit_kernel<<<nblk (n_groups, RED_THREADS), RED_THREADS, 0, st>>> (seg, (u32*) ctx->gkeep.p, (u32*) ctx->gkpos.p, n_groups, n_keep, (int*) ctx->idx_i.p, (int*) ctx->idx_f.p)));
+
+  // 4. coverage (:420-438)
+  const u32 n2 = 2 * n_keep;
+  TRY (ensure (ctx, ctx->pairs_a, (size_t) n2 * 8)); TRY (ensure (ctx, ctx->pairs_b, (size_t) n2 * 8));
+  TRY (ensure (ctx, ctx->heads, (size_t) n2 * 4)); TRY (ensure (ctx, ctx->pos, (size_t) n2 * 4)); TRY (ensure (ctx, ctx->seg, (size_t) n2 * 4));
+  TRY (ensure (ctx, ctx->cw, (size_t) n2 * 4)); TRY (ensure (ctx, ctx->csum, (size_t) n2 * 4));
+  heads = (u32*) ctx->heads.p; pos = (u32*) ctx->pos.p; seg = (u32*) ctx->seg.p;
+  LAUNCH (K_COVERAGE, (8 * W + 4 + 16) * (size_t) n_keep, (cov_pairs_kernel<W><<<nblk (n_keep, RED_THREADS), RED_THREADS, 0, st>>> (krec, kcount, n_keep, k, (u64*) ctx->pairs_a.p)));
+  std::vector<DigitDesc> cdig;
+  add_digits (cdig, 0, 32, 31);
+  u64 *psorted = nullptr;
+  TRY ((radix_sort<1> (ctx, (u64*) ctx->pairs_a.p, (u64*) ctx->pairs_b.p, n2, cdig, &psorted)));
+  ptmp = (u32*) ctx->ptmp.p;
+  LAUNCH (K_COVERAGE, 20 * (size_t) n2, (head_kernel<1, 2><<<nblk (n2, RED_THREADS), RED_THREADS, 0, st>>> (psorted, n2, heads)));
+  TRY (exclusive_scan (ctx, heads, pos, n2, ptmp, ctx->d_totals + 0));
+  LAUNCH (K_COVERAGE, 12 * (size_t) n2, (seg_start_kernel<<<nblk (n2, RED_THREADS), RED_THREADS, 0, st>>> (heads, pos, n2, seg)));
+  LAUNCH (K_COVERAGE, 12 * (size_t) n2, (lo32_kernel<<<nblk (n2, RED_THREADS), RED_THREADS, 0, st>>> (psorted, n2, (u32*) ctx->cw.p)));
+  TRY (exclusive_scan (ctx, (u32*) ctx->cw.p, (u32*) ctx->csum.p, n2, ptmp, ctx->d_totals + 2));
+  int cov_init = INT_MIN;
+  CU (cudaMemcpyAsync (ctx->d_cov, &cov_init, 4, cudaMemcpyHostToDevice, st));
+  CU (cudaMemcpyAsync (h_tot, ctx->d_totals, 4, cudaMemcpyDeviceToHost, st));
+  CU (cudaStreamSynchronize (st));
+  const u32 n_cseg = h_tot[0];
+  LAUNCH (K_COVERAGE, 12 * (size_t) n_cseg, (cov_max_kernel<<<nblk (n_cseg, RED_THREADS), RED_THREADS, 0, st>>> (seg, n_cseg, n2, (u32*) ctx->csum.p, ctx->d_totals + 2, ctx->d_cov)));
+
+  // 5. reference-layout elements + copy out into malloc'ed host memory (the reference free()s these)
+  TRY (ensure (ctx, ctx->out40, (size_t) n_keep * 40));
+  LAUNCH (K_PACK, (8 * W + 4 + 40) * (size_t) n_keep, (pack_hopo_kernel<W><<<nblk (n_keep, RED_THREADS), RED_THREADS, 0, st>>> (krec, kcount, n_keep, k, (u64*) ctx->out40.p)));
+  out->elem = malloc ((size_t) n_keep * 40);
+  out->idx_initial = (int32_t*) malloc ((size_t) n_idx * 4);
+  out->idx_final = (int32_t*) malloc ((size_t) n_idx * 4);
+  if (!out->elem || !out->idx_initial || !out->idx_final) { ctx->err = "malloc failed"; return TJB_ERR_NOMEM; }
+  int cov = 0;
+  CU (cudaMemcpyAsync (out->elem, ctx->out40.p, (size_t) n_keep * 40, cudaMemcpyDeviceToHost, st));
+  CU (cudaMemcpyAsync (out->idx_initial, ctx->idx_i.p, (size_t) n_idx * 4, cudaMemcpyDeviceToHost, st));
+  CU (cudaMemcpyAsync (out->idx_final, ctx->idx_f.p, (size_t) n_idx * 4, cudaMemcpyDeviceToHost, st));
+  CU (cudaMemcpyAsync (&cov, ctx->d_cov, 4, cudaMemcpyDeviceToHost, st));
+  CU (cudaStreamSynchronize (st));
+  out->n_elem = (int32_t) n_keep;
+  out->n_idx = (int32_t) n_idx;
+  out->coverage = cov;
+  out->status = TJB_OK;
+  return 0;
+}
+
+static int finalise (tjb_ctx *ctx, const tjb_opts *opt, tjb_counter_out *out)
+{
+  int rc = ctx->rec_words == 2 ? finalise_t<2> (ctx, opt, out) : finalise_t<3> (ctx, opt, out);
+  if (rc == 0) {
+    // scan wrote 8W bytes per record on top of the sequence bytes it read
+    ctx->stats[K_SCAN].bytes_algorithmic += (int64_t) out->n_raw * 8 * ctx->rec_words;
+  }
+  cudaStreamSynchronize (ctx->stream);
+  resolve_events (ctx);
+  if (rc < 0 || out->status != TJB_OK) { // the reference leaves an "empty counter" (n_elem = 0)
+    free (out->elem); free (out->idx_initial); free (out->idx_final);
+    out->elem = nullptr; out->idx_initial = out->idx_final = nullptr;
+    out->n_elem = out->n_idx = 0; out->coverage = 0;
+  }
+  return rc;
+}
+
+static void out_reset (tjb_counter_out *out) { memset (out, 0, sizeof (*out)); }
+
+// ------------------------------------------------------------------------------------------- C ABI ------
+extern "C" {
+
+const char *tjb_version (void) { return TJB_VERSION_STR; }
+
+const char *tjb_strerror (int code)
+{
+  switch (code) {
+    case TJB_OK: return "ok";
+    case TJB_NO_HT: return "no homopolymer tract found (sample excluded)";
+    case TJB_NO_HT_AFTER_QC: return "no tract left after strand-bias / singleton filter (sample excluded)";
+    case TJB_NO_CTX_ABOVE_COVERAGE: return "no context reaches the minimum coverage (sample excluded)";
+    case TJB_ERR_CUDA: return "CUDA error (no usable sm_100 device? there is no CPU fallback)";
+    case TJB_ERR_ARG: return "invalid argument";
+    case TJB_ERR_IO: return "I/O error";
+    case TJB_ERR_NOMEM: return "out of memory";
+    case TJB_ERR_TOO_LARGE: return "input too large";
+    default: return "unknown code";
+  }
+}
+
+const char *tjb_ctx_last_error (const tjb_ctx *ctx) { return ctx ? ctx->err.c_str () : "null context"; }
+
+int tjb_ctx_create (int device, tjb_ctx **pctx)
+{
+  if (!pctx) return TJB_ERR_ARG;
+  *pctx = nullptr;
+  int n_dev = 0;
+  if (cudaGetDeviceCount (&n_dev) != cudaSuccess || device < 0 || device >= n_dev) return TJB_ERR_CUDA;
+  tjb_ctx *ctx = new tjb_ctx ();
+  ctx->device = device;
+  for (int i = 0; i < K_COUNT; i++) { memset (&ctx->stats[i], 0, sizeof (tjb_kernel_stat)); strncpy (ctx->stats[i].name, kKernelNames[i], 47); }
+  auto fail = [&] (cudaError_t e) { (void) e; delete ctx; return TJB_ERR_CUDA; };
+  cudaError_t e;
+  if ((e = cudaSetDevice (device)) != cudaSuccess) return fail (e);
+  cudaDeviceProp prop;
+  if ((e = cudaGetDeviceProperties (&prop, device)) != cudaSuccess) return fail (e);
+  if (prop.major < 10) { delete ctx; return TJB_ERR_CUDA; } // kernels are built for sm_100a only
+  ctx->sm_count = prop.multiProcessorCount;
+  if ((e = cudaStreamCreateWithFlags (&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) return fail (e);
+  if ((e = cudaMalloc (&ctx->d_counters, 2 * sizeof (unsigned long long))) != cudaSuccess) return fail (e);
+  if ((e = cudaMalloc (&ctx->d_totals, 16 * sizeof (u32))) != cudaSuccess) return fail (e);
+  if ((e = cudaMalloc (&ctx->d_cov, sizeof (int))) != cudaSuccess) return fail (e);
+  cudaEventCreate (&ctx->ev_t0); cudaEventCreate (&ctx->ev_t1);
+  *pctx = ctx;
+  return 0;
+}
+
+void tjb_ctx_destroy (tjb_ctx *ctx)
+{
+  if (!ctx) return;
+  cudaSetDevice (ctx->device);
+  if (ctx->stream) cudaStreamSynchronize (ctx->stream);
+  resolve_events (ctx);
+  for (cudaEvent_t e : ctx->free_events) cudaEventDestroy (e);
+  DevBuf *bufs[] = {&ctx->d_chunk[0], &ctx->d_chunk[1], &ctx->rec_a, &ctx->rec_b, &ctx->hist, &ctx->ptmp, &ctx->heads, &ctx->pos, &ctx->seg,
+                    &ctx->drec, &ctx->dcount, &ctx->keep, &ctx->kpos, &ctx->krec, &ctx->kcount, &ctx->cw, &ctx->csum, &ctx->gkeep,
+                    &ctx->gkpos, &ctx->pairs_a, &ctx->pairs_b, &ctx->out40, &ctx->idx_i, &ctx->idx_f};
+  for (DevBuf *b : bufs) if (b->p) cudaFree (b->p);
+  for (int i = 0; i < 2; i++) { if (ctx->h_pinned[i]) cudaFreeHost (ctx->h_pinned[i]); if (ctx->h_free[i]) cudaEventDestroy (ctx->h_free[i]); }
+  if (ctx->d_counters) cudaFree (ctx->d_counters);
+  if (ctx->d_totals) cudaFree (ctx->d_totals);
+  if (ctx->d_cov) cudaFree (ctx->d_cov);
+  if (ctx->ev_t0) cudaEventDestroy (ctx->ev_t0);
+  if (ctx->ev_t1) cudaEventDestroy (ctx->ev_t1);
+  if (ctx->stream) cudaStreamDestroy (ctx->stream);
+  delete ctx;
+}
+
+void *tjb_ctx_stream (tjb_ctx *ctx) { return ctx ? (void*) ctx->stream : nullptr; }
+
+int tjb_ctx_set_profiling (tjb_ctx *ctx, int on) { if (!ctx) return TJB_ERR_ARG; ctx->profiling = on; return 0; }
+
+int tjb_ctx_kernel_stats (tjb_ctx *ctx, tjb_kernel_stat *stats, int max_stats)
+{
+  if (!ctx) return TJB_ERR_ARG;
+  int n = 0;
+  for (int i = 0; i < K_COUNT; i++) if (ctx->stats[i].launches) { if (stats && n < max_stats) stats[n] = ctx->stats[i]; n++; }
+  return n;
+}
+
+void tjb_ctx_reset_kernel_stats (tjb_ctx *ctx)
+{
+  if (!ctx) return;
+  for (int i = 0; i < K_COUNT; i++) { ctx->stats[i].launches = 0; ctx->stats[i].ms_total = 0; ctx->stats[i].bytes_algorithmic = 0; }
+  ctx->launches = 0;
+}
+
+int64_t tjb_ctx_launch_count (const tjb_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+int tjb_count_sample_device (tjb_ctx *ctx, const void *d_seqs, size_t n_bytes, const tjb_opts *opt, tjb_counter_out *out)
+{
+  if (!ctx || !out || (n_bytes && !d_seqs)) return TJB_ERR_ARG;
+  if (((uintptr_t) d_seqs) & 15) { ctx->err = "device buffer must be 16-byte aligned"; return TJB_ERR_ARG; }
+  out_reset (out);
+  TRY (begin_sample (ctx, opt));
+  CU (cudaEventRecord (ctx->ev_t0, ctx->stream));
+  TRY (scan_chunk (ctx, (const uint8_t*) d_seqs, n_bytes, opt));
+  int rc = finalise (ctx, opt, out);
+  if (rc < 0) return rc;
+  CU (cudaEventRecord (ctx->ev_t1, ctx->stream));
+  CU (cudaEventSynchronize (ctx->ev_t1));
+  float ms = 0.f;
+  cudaEventElapsedTime (&ms, ctx->ev_t0, ctx->ev_t1);
+  out->ms_device = ms;
+  return out->status;
+}
+
+// cut [p, p+len) at the last '\n' so that a chunk always holds whole reads
+static size_t whole_reads_prefix (const uint8_t *p, size_t len, size_t remaining)
+{
+  if (len >= remaining) return remaining;
+  const void *nl = memrchr (p, '\n', len);
+  return nl ? (size_t) ((const uint8_t*) nl - p) + 1 : 0;
+}
+
+int tjb_count_sample_host (tjb_ctx *ctx, const uint8_t *seqs, size_t n_bytes, const tjb_opts *opt, tjb_counter_out *out)
+{
+  if (!ctx || !out || (n_bytes && !seqs)) return TJB_ERR_ARG;
+  out_reset (out);
+  TRY (begin_sample (ctx, opt));
+  CU (cudaEventRecord (ctx->ev_t0, ctx->stream));
+  const size_t max_chunk = 512u << 20;
+  size_t off = 0;
+  int which = 0;
+  while (off < n_bytes) {
+    size_t len = whole_reads_prefix (seqs + off, max_chunk < n_bytes - off ? max_chunk : n_bytes - off, n_bytes - off);
+    if (!len) { ctx->err = "a single read exceeds the chunk size"; return TJB_ERR_TOO_LARGE; }
+    TRY (ensure (ctx, ctx->d_chunk[which], (len + 15) & ~(size_t) 15));
+    CU (cudaMemcpyAsync (ctx->d_chunk[which].p, seqs + off, len, cudaMemcpyHostToDevice, ctx->stream));
+    TRY (scan_chunk (ctx, (const uint8_t*) ctx->d_chunk[which].p, len, opt));
+    off += len;
+    which ^= 1;
+  }
+  int rc = finalise (ctx, opt, out);
+  if (rc < 0) return rc;
+  CU (cudaEventRecord (ctx->ev_t1, ctx->stream));
+  CU (cudaEventSynchronize (ctx->ev_t1));
+  float ms = 0.f;
+  cudaEventElapsedTime (&ms, ctx->ev_t0, ctx->ev_t1);
+  out->ms_device = ms;
+  return out->status;
+}
+
+int tjb_count_sample_files (tjb_ctx *ctx, const char *const *files, int n_files, const tjb_opts *opt, tjb_counter_out *out)
+{
+  if (!ctx || !out || !files || n_files < 1 || n_files > 2) return TJB_ERR_ARG;
+  out_reset (out);
+  TRY (begin_sample (ctx, opt));
+  for (int i = 0; i < 2; i++) {
+    if (!ctx->h_pinned[i]) CU (cudaMallocHost ((void**) &ctx->h_pinned[i], TJB_CHUNK_BYTES));
+    if (!ctx->h_free[i]) CU (cudaEventCreateWithFlags (&ctx->h_free[i], cudaEventDisableTiming));
+    TRY (ensure (ctx, ctx->d_chunk[i], TJB_CHUNK_BYTES));
+  }
+  CU (cudaEventRecord (ctx->ev_t0, ctx->stream));
+  double ms_decode = 0.;
+  int which = 0;
+  for (int f = 0; f < n_files; f++) {
+    tjb_reader *rd = tjb_reader_open (files[f]);
+    if (!rd) { ctx->err = std::string ("cannot open ") + files[f]; return TJB_ERR_IO; }
+    for (;;) {
+      // pinned buffer `which` was handed to the copy engine two chunks ago; wait until that copy has drained it
+      cudaEventSynchronize (ctx->h_free[which]);
+      // host decode of this chunk overlaps with the H2D copy + scan of the previous one (still in flight)
+      auto t0 = std::chrono::steady_clock::now ();
+      int64_t got = tjb_reader_fill (rd, ctx->h_pinned[which], TJB_CHUNK_BYTES, &out->n_reads, &out->n_bases);
+      ms_decode += std::chrono::duration<double, std::milli> (std::chrono::steady_clock::now () - t0).count ();
+      if (got < 0) { tjb_reader_close (rd); ctx->err = std::string ("decode failed: ") + files[f]; return (int) got; }
+      if (got == 0) break;
+      int rc = scan_resolve (ctx, opt); // previous chunk: record count known, overflow handled
+      if (rc < 0) { tjb_reader_close (rd); return rc; }
+      CU (cudaMemcpyAsync (ctx->d_chunk[which].p, ctx->h_pinned[which], (size_t) got, cudaMemcpyHostToDevice, ctx->stream));
+      CU (cudaEventRecord (ctx->h_free[which], ctx->stream));
+      rc = scan_launch (ctx, (const uint8_t*) ctx->d_chunk[which].p, (size_t) got, opt);
+      if (rc < 0) { tjb_reader_close (rd); return rc; }
+      which ^= 1;
+    }
+    tjb_reader_close (rd);
+  }
+  TRY (scan_resolve (ctx, opt));
+  out->ms_decode = ms_decode;
+  int rc = finalise (ctx, opt, out);
+  if (rc < 0) return rc;
+  CU (cudaEventRecord (ctx->ev_t1, ctx->stream));
+  CU (cudaEventSynchronize (ctx->ev_t1));
+  size_t nl = strlen (files[0]);
+  out->name = (char*) malloc (nl + 1);
+  if (out->name) memcpy (out->name, files[0], nl + 1);
+  return out->status;
+}
+
+int tjb_count_sample (const char *const *files, int n_files, const tjb_opts *opt, int device, tjb_counter_out *out)
+{
+  struct Cache {
+    std::map<int, tjb_ctx*> m;
+    ~Cache () { for (auto &kv : m) tjb_ctx_destroy (kv.second); }
+  };
+  static thread_local Cache cache;
+  tjb_ctx *ctx = nullptr;
+  auto it = cache.m.find (device);
+  if (it == cache.m.end ()) {
+    int rc = tjb_ctx_create (device, &ctx);
+    if (rc < 0) return rc;
+    cache.m[device] = ctx;
+  } else ctx = it->second;
+  return tjb_count_sample_files (ctx, files, n_files, opt, out);
+}
+
+void tjb_counter_out_free (tjb_counter_out *out)
+{
+  if (!out) return;
+  free (out->elem); free (out->idx_initial); free (out->idx_final); free (out->name);
+  out->elem = nullptr; out->idx_initial = out->idx_final = nullptr; out->name = nullptr;
+}
+
+} // extern "C"
