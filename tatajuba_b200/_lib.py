@@ -1,0 +1,89 @@
+"""ctypes binding of tatajuba_b200/lib/libtjb_gpu.so (C ABI: include/tjb_gpu.h).
+
+The library is the product; this module only loads it.  There is no Python or CPU fallback: if the shared
+library is missing, loading raises, and every compute entry point fails loudly without a B200-class GPU.
+"""
+import ctypes as C
+import os
+import subprocess
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "lib", "libtjb_gpu.so")
+CSRC = os.path.join(HERE, "csrc")
+
+# every symbol include/tjb_gpu.h declares (checked by tests/test_abi.py)
+EXPORTS = [
+    "tjb_version", "tjb_strerror", "tjb_ctx_last_error", "tjb_ctx_create", "tjb_ctx_destroy", "tjb_ctx_stream",
+    "tjb_ctx_set_profiling", "tjb_ctx_kernel_stats", "tjb_ctx_reset_kernel_stats", "tjb_ctx_launch_count",
+    "tjb_count_sample_files", "tjb_count_sample_host", "tjb_count_sample_device", "tjb_count_sample",
+    "tjb_counter_out_free", "tjb_reader_open", "tjb_reader_fill", "tjb_reader_close",
+]
+
+
+class TjbOpts(C.Structure):
+    _fields_ = [("kmer_size", C.c_int32), ("min_tract_size", C.c_int32), ("min_coverage", C.c_int32),
+                ("remove_biased", C.c_int32), ("paired_end", C.c_int32)]
+
+
+class TjbCounterOut(C.Structure):
+    _fields_ = [("status", C.c_int32), ("n_elem", C.c_int32), ("n_idx", C.c_int32), ("coverage", C.c_int32),
+                ("elem", C.c_void_p), ("idx_initial", C.POINTER(C.c_int32)), ("idx_final", C.POINTER(C.c_int32)),
+                ("name", C.c_char_p), ("n_reads", C.c_int64), ("n_bases", C.c_int64), ("n_raw", C.c_int64),
+                ("n_distinct", C.c_int64), ("n_skipped_nonacgt", C.c_int64), ("ms_decode", C.c_double),
+                ("ms_device", C.c_double)]
+
+
+class TjbKernelStat(C.Structure):
+    _fields_ = [("name", C.c_char * 48), ("launches", C.c_int64), ("ms_total", C.c_double),
+                ("bytes_algorithmic", C.c_int64)]
+
+
+def build(verbose: bool = False) -> str:
+    """compile the CUDA extension in-tree for sm_100a (nvcc cross-compiles without a GPU)"""
+    subprocess.run(["make", "-C", CSRC] + ([] if verbose else ["-s"]), check=True)
+    return LIB_PATH
+
+
+_lib = None
+
+
+def load():
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise RuntimeError(f"{LIB_PATH} is missing: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                           "(there is no CPU fallback for the tatajuba_b200 hot path)")
+    lib = C.CDLL(LIB_PATH)
+    vp, cp, i32, i64, sz = C.c_void_p, C.c_char_p, C.c_int, C.c_int64, C.c_size_t
+    lib.tjb_version.restype = cp
+    lib.tjb_strerror.restype = cp
+    lib.tjb_strerror.argtypes = [i32]
+    lib.tjb_ctx_last_error.restype = cp
+    lib.tjb_ctx_last_error.argtypes = [vp]
+    lib.tjb_ctx_create.argtypes = [i32, C.POINTER(vp)]
+    lib.tjb_ctx_destroy.argtypes = [vp]
+    lib.tjb_ctx_destroy.restype = None
+    lib.tjb_ctx_stream.restype = vp
+    lib.tjb_ctx_stream.argtypes = [vp]
+    lib.tjb_ctx_set_profiling.argtypes = [vp, i32]
+    lib.tjb_ctx_kernel_stats.argtypes = [vp, C.POINTER(TjbKernelStat), i32]
+    lib.tjb_ctx_reset_kernel_stats.argtypes = [vp]
+    lib.tjb_ctx_reset_kernel_stats.restype = None
+    lib.tjb_ctx_launch_count.restype = i64
+    lib.tjb_ctx_launch_count.argtypes = [vp]
+    po, pout = C.POINTER(TjbOpts), C.POINTER(TjbCounterOut)
+    lib.tjb_count_sample_files.argtypes = [vp, C.POINTER(cp), i32, po, pout]
+    lib.tjb_count_sample_host.argtypes = [vp, vp, sz, po, pout]
+    lib.tjb_count_sample_device.argtypes = [vp, vp, sz, po, pout]
+    lib.tjb_count_sample.argtypes = [C.POINTER(cp), i32, po, i32, pout]
+    lib.tjb_counter_out_free.argtypes = [pout]
+    lib.tjb_counter_out_free.restype = None
+    lib.tjb_reader_open.restype = vp
+    lib.tjb_reader_open.argtypes = [cp]
+    lib.tjb_reader_fill.restype = i64
+    lib.tjb_reader_fill.argtypes = [vp, vp, sz, C.POINTER(i64), C.POINTER(i64)]
+    lib.tjb_reader_close.argtypes = [vp]
+    lib.tjb_reader_close.restype = None
+    _lib = lib
+    return lib

@@ -1,0 +1,197 @@
+"""Host-side mirror of the reference's hopo_counter interface (src/hopo_counter.h:51-81) over libtjb_gpu.
+
+    hc = new_or_append_hopo_counter_from_file(None, "s1_R1.fastq.gz", opt)   # src/hopo_counter.c:135
+    hc = new_or_append_hopo_counter_from_file(hc,   "s1_R2.fastq.gz", opt)   # paired end: same counter
+    finalise_hopo_counter(hc)                                                # src/hopo_counter.c:339 (up to :415)
+    hc.elem, hc.n_elem, hc.idx_initial, hc.idx_final, hc.n_idx, hc.coverage  # state at the BWA boundary (:523)
+
+Everything is computed by the CUDA library; nothing here touches oracle/ and there is no CPU fallback.
+"""
+import ctypes as C
+import os
+import warnings
+
+import numpy as np
+
+from . import _lib
+from ._lib import TjbCounterOut, TjbKernelStat, TjbOpts
+
+# numpy view of the reference's 40-byte hopo_element (src/hopo_counter.h:34-49)
+HOPO_DTYPE = np.dtype([("ctx0", "<u8"), ("ctx1", "<u8"), ("bits", "<u8"), ("read_offset", "<i4"),
+                       ("loc_ref_id", "<i4"), ("loc_pos", "<i4"), ("loc_last", "<i4")])
+
+TJB_OK, TJB_NO_HT, TJB_NO_HT_AFTER_QC, TJB_NO_CTX_ABOVE_COVERAGE = 0, 1, 2, 3
+
+
+class TatajubaOptions:
+    """the fields of tatajuba_options_t the path reads (src/hopo_counter.h:20-32); defaults as src/main.c:56-60"""
+
+    def __init__(self, kmer_size=25, min_tract_size=4, min_coverage=5, remove_biased=True, paired_end=False):
+        self.kmer_size, self.min_tract_size, self.min_coverage = kmer_size, min_tract_size, min_coverage
+        self.remove_biased, self.paired_end = remove_biased, paired_end
+
+    def c_struct(self):
+        return TjbOpts(self.kmer_size, self.min_tract_size, self.min_coverage, int(self.remove_biased),
+                       int(self.paired_end))
+
+
+class TjbError(RuntimeError):
+    pass
+
+
+class Context:
+    """one tjb_ctx: a (host thread, device) pair with its stream, pinned double buffers and device workspace"""
+
+    def __init__(self, device=0):
+        self.lib = _lib.load()
+        h = C.c_void_p()
+        rc = self.lib.tjb_ctx_create(int(device), C.byref(h))
+        if rc < 0:
+            raise TjbError(f"tjb_ctx_create(device={device}) failed: {self.lib.tjb_strerror(rc).decode()}")
+        self.h = h
+        self.device = device
+
+    def close(self):
+        if getattr(self, "h", None):
+            self.lib.tjb_ctx_destroy(self.h)
+            self.h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def _check(self, rc):
+        if rc < 0:
+            raise TjbError(f"{self.lib.tjb_strerror(rc).decode()}: {self.lib.tjb_ctx_last_error(self.h).decode()}")
+        return rc
+
+    def set_profiling(self, level):
+        self.lib.tjb_ctx_set_profiling(self.h, int(level))
+
+    def reset_kernel_stats(self):
+        self.lib.tjb_ctx_reset_kernel_stats(self.h)
+
+    def launch_count(self):
+        return int(self.lib.tjb_ctx_launch_count(self.h))
+
+    def stream(self):
+        return self.lib.tjb_ctx_stream(self.h)
+
+    def kernel_stats(self):
+        arr = (TjbKernelStat * 16)()
+        n = self.lib.tjb_ctx_kernel_stats(self.h, arr, 16)
+        return [dict(name=arr[i].name.decode(), launches=arr[i].launches, ms_total=arr[i].ms_total,
+                     bytes_algorithmic=arr[i].bytes_algorithmic) for i in range(min(n, 16))]
+
+    # the three entry points -------------------------------------------------------------------------
+    def count_files(self, files, opt):
+        arr = (C.c_char_p * len(files))(*[os.fsencode(f) for f in files])
+        out = TjbCounterOut()
+        o = opt.c_struct()
+        self._check(self.lib.tjb_count_sample_files(self.h, arr, len(files), C.byref(o), C.byref(out)))
+        return HopoCounter._from_out(self.lib, out, opt)
+
+    def count_host(self, seqs, opt):
+        """seqs: bytes / numpy uint8 / pinned torch uint8 tensor of reads separated by '\\n'"""
+        ptr, n = _host_ptr(seqs)
+        out = TjbCounterOut()
+        o = opt.c_struct()
+        self._check(self.lib.tjb_count_sample_host(self.h, ptr, n, C.byref(o), C.byref(out)))
+        return HopoCounter._from_out(self.lib, out, opt)
+
+    def count_device(self, d_ptr, n_bytes, opt):
+        """d_ptr: integer device address (e.g. tensor.data_ptr()), 16-byte aligned"""
+        out = TjbCounterOut()
+        o = opt.c_struct()
+        self._check(self.lib.tjb_count_sample_device(self.h, C.c_void_p(int(d_ptr)), int(n_bytes), C.byref(o),
+                                                     C.byref(out)))
+        return HopoCounter._from_out(self.lib, out, opt)
+
+
+def _host_ptr(seqs):
+    if isinstance(seqs, (bytes, bytearray)):
+        a = np.frombuffer(seqs, dtype=np.uint8)
+        _host_ptr.keep = a
+        return C.c_void_p(a.ctypes.data), a.size
+    if isinstance(seqs, np.ndarray):
+        assert seqs.dtype == np.uint8 and seqs.flags["C_CONTIGUOUS"]
+        return C.c_void_p(seqs.ctypes.data), seqs.size
+    # torch tensor (CPU, possibly pinned)
+    assert not seqs.is_cuda and seqs.is_contiguous()
+    return C.c_void_p(seqs.data_ptr()), seqs.numel()
+
+
+class HopoCounter:
+    """struct hopo_counter_struct at the BWA boundary (src/hopo_counter.h:51-59)"""
+
+    def __init__(self, opt):
+        self.opt = opt
+        self.files = []
+        self.name = None
+        self.status = None
+        self.elem = np.zeros(0, dtype=HOPO_DTYPE)
+        self.idx_initial = np.zeros(0, np.int32)
+        self.idx_final = np.zeros(0, np.int32)
+        self.n_elem = self.n_idx = self.coverage = 0
+        self.ref_start = 0
+        self.finalised = False
+
+    @classmethod
+    def _from_out(cls, lib, out, opt):
+        hc = cls(opt)
+        hc.status = out.status
+        hc.n_elem, hc.n_idx, hc.coverage = out.n_elem, out.n_idx, out.coverage
+        if out.n_elem:
+            hc.elem = np.zeros(out.n_elem, dtype=HOPO_DTYPE)
+            C.memmove(hc.elem.ctypes.data, out.elem, 40 * out.n_elem)
+        if out.n_idx:
+            hc.idx_initial = np.ctypeslib.as_array(out.idx_initial, (out.n_idx,)).copy()
+            hc.idx_final = np.ctypeslib.as_array(out.idx_final, (out.n_idx,)).copy()
+        hc.name = out.name.decode() if out.name else None
+        for f in ("n_reads", "n_bases", "n_raw", "n_distinct", "n_skipped_nonacgt", "ms_decode", "ms_device"):
+            setattr(hc, f, getattr(out, f))
+        hc.finalised = True
+        lib.tjb_counter_out_free(C.byref(out))
+        return hc
+
+
+_default_ctx = {}
+
+
+def _ctx(device=0):
+    if device not in _default_ctx:
+        _default_ctx[device] = Context(device)
+    return _default_ctx[device]
+
+
+def new_or_append_hopo_counter_from_file(hc, filename, opt):
+    """src/hopo_counter.c:135-157: the first file names the sample; appending after finalise is an error (:152)"""
+    if hc is None:
+        hc = HopoCounter(opt)
+        hc.name = filename
+    if hc.finalised:
+        raise TjbError("This counter has been compared to another; cannot add more reads to it")
+    if len(hc.files) >= 2:
+        raise TjbError("at most two files (R1, R2) per sample")
+    hc.files.append(filename)
+    return hc
+
+
+def finalise_hopo_counter(hc, device=0):
+    """src/hopo_counter.c:339-415 (everything before the mapper call): fills hc in place and warns like the
+    reference on the three "sample will be excluded" paths"""
+    res = _ctx(device).count_files(hc.files, hc.opt)
+    name, files = hc.name, hc.files
+    hc.__dict__.update(res.__dict__)
+    hc.name, hc.files = name, files
+    pair = " together with its pair." if hc.opt.paired_end else "."
+    if hc.status == TJB_NO_HT:
+        warnings.warn(f"No HTs were found in sample {name}{pair[:-1]}, not even before QC. This sample will be excluded.")
+    elif hc.status == TJB_NO_HT_AFTER_QC:
+        warnings.warn(f"No HTs found in sample {name} after QC. This sample will be excluded.")
+    elif hc.status == TJB_NO_CTX_ABOVE_COVERAGE:
+        warnings.warn(f"From the HTs found in sample {name}, not a single one has coverage higher than "
+                      f"{hc.opt.min_coverage}. This sample will be excluded.")
+    return hc
