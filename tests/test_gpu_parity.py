@@ -1,0 +1,146 @@
+"""GPU parity tests proper (-m gpu): the CUDA path through the C ABI vs the oracle, bit-exact.
+Nothing here reads /root/reference (absent on the GPU box): the checkers are the plain-C restatement, the committed
+golden vectors (made from the compiled reference) and the prebuilt oracle/_ref library when it travelled."""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+from oracle import pyoracle
+from tatajuba_b200 import Context, TatajubaOptions, synth
+
+pytestmark = pytest.mark.gpu
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+
+
+@pytest.fixture(scope="module")
+def ctx(built):
+    import torch
+    assert torch.cuda.is_available()
+    c = Context(0)
+    yield c
+    c.close()
+
+
+def as_boundary(hc):
+    return pyoracle.Boundary(hc.status, hc.n_raw, hc.elem, hc.idx_initial, hc.idx_final, hc.coverage, hc.n_skipped_nonacgt)
+
+
+def check(ctx, restatement, buf, k, m, cov, rb, what, device_too=True):
+    import torch
+    opt = TatajubaOptions(k, m, cov, rb)
+    want = restatement.run_buffer(buf, k, m, cov, rb)
+    got = as_boundary(ctx.count_host(buf, opt))
+    pyoracle.assert_same_boundary(got, want, what + " [host]")
+    assert got.n_skipped_nonacgt == want.n_skipped_nonacgt
+    if device_too and len(buf):
+        d = torch.frombuffer(bytearray(buf), dtype=torch.uint8).cuda()
+        got = as_boundary(ctx.count_device(d.data_ptr(), d.numel(), opt))
+        pyoracle.assert_same_boundary(got, want, what + " [device]")
+    return want
+
+
+from test_golden_and_abi import GOLDENS, golden_input, load_golden  # noqa: E402
+
+
+@pytest.mark.parametrize("name", GOLDENS)
+def test_gpu_matches_reference_goldens(ctx, name):
+    want, k, m, cov, rb = load_golden(os.path.join(GOLD, name))
+    got = as_boundary(ctx.count_host(golden_input(name), TatajubaOptions(k, m, cov, rb)))
+    pyoracle.assert_same_boundary(got, want, name)
+
+
+@pytest.mark.parametrize("k,m,cov,rb,err", [(25, 4, 5, True, 0.0), (25, 4, 5, False, 0.003), (32, 3, 5, True, 0.001),
+                                            (26, 2, 3, True, 0.0), (27, 4, 5, True, 0.0), (2, 1, 5, True, 0.0),
+                                            (13, 2, 10, False, 0.01), (8, 32, 0, False, 0.0)])
+def test_gpu_matches_oracle_on_synthetic(ctx, restatement, k, m, cov, rb, err):
+    buf = synth.sample_buffer(400_000, 30, seed=9, sample=2, error_rate=err).tobytes()
+    want = check(ctx, restatement, buf, k, m, cov, rb, f"synthetic k={k} m={m}")
+    if m <= 4:
+        assert want.n_raw > 1000
+
+
+@pytest.mark.parametrize("k", [2, 3, 7, 16, 25, 26, 27, 31, 32])
+def test_gpu_matches_oracle_on_adversarial(ctx, restatement, k):
+    reads = synth.adversarial_reads(k, wrap_lengths=True)
+    buf = b"\n".join(reads * 3) + b"\n"
+    for m, cov, rb in [(1, 1, False), (4, 2, False), (3, 0, True), (2, 1, True)]:
+        check(ctx, restatement, buf, k, m, cov, rb, f"adversarial k={k} m={m}")
+
+
+def test_gpu_nonacgt_runs_and_separators(ctx, restatement):
+    fl = b"GATC" * 8
+    reads = [fl + b"NNNNN" + fl, fl + b"AAAA" + fl, fl + b"nnnn" + fl + b"TTTTT" + fl, b"", b"", b"", fl + b"AAAA" + fl,
+             b"N" * 200, fl + b"----" + fl, fl + b"AAAA" + fl[:-1] + b"N"]
+    buf = b"\n".join(reads * 4) + b"\n"
+    want = check(ctx, restatement, buf, 25, 4, 1, False, "non-ACGT")
+    assert want.n_skipped_nonacgt == 4 * 3
+    check(ctx, restatement, buf[:-1], 25, 4, 1, False, "no trailing newline")
+
+
+def test_gpu_drop_paths(ctx, restatement):
+    one = b"GATC" * 8 + b"AAAAA" + b"CTAG" * 8 + b"\n"
+    for buf, rb, cov, status in [(b"ACGTACGTAC\nACGT\n\n", True, 5, 1), (b"", True, 5, 1), (one, False, 5, 2),
+                                 (one, True, 5, 2), (one * 2, False, 50, 3)]:
+        want = check(ctx, restatement, buf, 25, 4, cov, rb, f"drop {status}")
+        assert want.status == status
+
+
+def test_gpu_tile_boundaries(ctx, restatement):
+    """tracts, flanks and long runs straddling the 8192-byte scan tiles and the staged halo"""
+    rng = np.random.default_rng(4)
+    fl = (b"GATC" * 8)
+    for pad in list(range(8100, 8260, 7)) + [16300, 16384, 16385]:
+        pre = bytes(rng.choice(np.frombuffer(b"ACGT", np.uint8), size=pad - 40).tobytes())
+        buf = pre + b"\n" + fl + b"A" * 9 + fl + b"\n" + fl + b"T" * 300 + fl + b"\n" + fl + b"C" * 5 + fl
+        check(ctx, restatement, buf, 25, 4, 1, False, f"pad {pad}", device_too=False)
+        check(ctx, restatement, buf, 32, 2, 1, False, f"pad {pad} k32", device_too=False)
+    long_run = fl + b"G" * 20000 + fl + b"\n"
+    check(ctx, restatement, long_run * 2, 25, 4, 1, False, "20k run")
+
+
+def test_gpu_files_path_matches_oracle(ctx, restatement, tmp_path):
+    rows = synth.paired_reads(synth.inject_tract_polymorphism(synth.random_genome(300_000, 5)), 30, seed=8)
+    r1, r2 = str(tmp_path / "s_R1.fastq.gz"), str(tmp_path / "s_R2.fastq")
+    synth.write_fastq(r1, rows[0::2]); synth.write_fastq(r2, rows[1::2])
+    opt = TatajubaOptions(paired_end=True)
+    hc = ctx.count_files([r1, r2], opt)
+    want = restatement.run_buffer(rows[0::2].tobytes() + rows[1::2].tobytes(), 25, 4, 5, True)
+    pyoracle.assert_same_boundary(as_boundary(hc), want, "files")
+    assert hc.name == r1 and hc.n_reads == rows.shape[0] and hc.n_bases == rows.shape[0] * 150
+
+
+def test_gpu_matches_compiled_reference_when_it_travelled(ctx):
+    if not pyoracle.Reference.available():
+        pytest.skip("oracle/_ref not present")
+    ref = pyoracle.Reference()
+    buf = synth.sample_buffer(300_000, 40, seed=13, error_rate=0.002).tobytes()
+    for k, m, rb in [(25, 4, True), (32, 3, True), (25, 4, False)]:
+        want = ref.run_buffer(buf, k, m, 5, rb)
+        got = as_boundary(ctx.count_host(buf, TatajubaOptions(k, m, 5, rb)))
+        pyoracle.assert_same_boundary(got, want, f"reference k={k}")
+
+
+def test_gpu_full_size_properties(ctx):
+    """BASELINE config 2 size (5 Mbp, 100x): oracle too slow to be the checker at every run, so size-independent
+    properties: order strictly descending, counts sum to n_raw minus filtered, groups partition correctly, and the
+    result is invariant under shuffling the reads."""
+    import torch
+    buf = synth.sample_buffer(5_000_000, 100, seed=1)
+    opt = TatajubaOptions()
+    d = torch.from_numpy(buf).cuda()
+    a = ctx.count_device(d.data_ptr(), d.numel(), opt)
+    assert a.status == 0 and a.n_raw > 3_000_000
+    e = a.elem
+    f = pyoracle.unpack_bits(e["bits"])
+    key = np.stack([f["base"].astype(np.uint64), e["ctx0"], e["ctx1"], (f["length"] + 512).astype(np.uint64)], 1)
+    order = np.lexsort(key.T[::-1])
+    assert np.array_equal(order[::-1], np.arange(len(e)))  # strictly descending = sorted ascending reversed, no ties
+    assert np.all(f["canon_flag"] == 3) and np.all(f["count"] >= 2)
+    assert np.all(a.idx_final > a.idx_initial) and np.all(a.idx_initial[1:] >= a.idx_final[:-1])
+    rows = buf.reshape(-1, 151)
+    perm = np.random.default_rng(0).permutation(rows.shape[0])
+    d2 = torch.from_numpy(np.ascontiguousarray(rows[perm]).reshape(-1)).cuda()
+    b = ctx.count_device(d2.data_ptr(), d2.numel(), opt)
+    pyoracle.assert_same_boundary(as_boundary(a), as_boundary(b), "shuffle invariance")
