@@ -1,0 +1,484 @@
+// Bucketed sort + segmented run-length reduction of tract observations (the main reduce path).
+//
+// Replaces qsort + the sequential loops of finalise_hopo_counter() and estimate_coverage_hopo_counter()
+// (reference src/hopo_counter.c:351-413, 420-438).  Instead of ~14 full-array LSD passes over the 112..138-bit
+// keys, the records are moved ONCE (an MSD partition on the top F bits of (base, ctx0), F <= 16, with splitters
+// chosen from the histogram the scan kernel accumulates), and every bucket (<= BK_CAP records, sized to stay in
+// shared memory) is then sorted on chip by an LSD radix sort over the remaining digits and reduced in the same
+// CTA: run-length count (:352-365), strand-bias / singleton QC (:367-374) and the context groups above the
+// minimum coverage (:388-404).  A context (base, ctx0, ctx1) never straddles two buckets because the partition
+// looks at context bits only.  Everything is produced in the reference's DESCENDING order.
+//
+//   plan_kernel          1 CTA     bin histogram -> splitters (buckets of < BK_CAP records), bin -> bucket LUT
+//   partition_kernel     grid      rec_a -> rec_b, bucket-contiguous (order inside a bucket is irrelevant)
+//   bucket_reduce_kernel grid      per bucket: smem LSD sort + RLE + QC + groups; compact output at the bucket start
+//   totals_kernel        1 CTA     exclusive scans of the per-bucket kept / group counts
+//   pack_kernel          grid      reference-layout 40-byte hopo_element + idx arrays + coverage hash inserts
+//   cov_max_kernel       grid      coverage = max over the hash table
+//
+// Buckets with more than BK_CAP records (one bin holding > BK_CAP/2 observations: very short k or a pathological
+// sample) are flagged and reduced by the multi-pass global path in tjb_sort.cuh / tjb_reduce.cuh instead.
+#pragma once
+#include "tjb_common.cuh"
+
+#define BK_THREADS 256
+#define BK_WARPS (BK_THREADS / 32)
+#define BK_IPT 8
+#define BK_CAP (BK_THREADS * BK_IPT) // records per on-chip bucket
+#define BK_CAPH (BK_CAP / 2)
+#define PLAN_THREADS 1024
+#define TJB_MAX_BIN_BITS 16
+#define TJB_MAX_BINS (1 << TJB_MAX_BIN_BITS)
+
+// meta[] slots (device u32)
+enum { META_NBUCKETS = 0, META_NOVERSIZE = 1, META_TICKET = 2, META_N = 3, META_NDIST = 4, META_NKEEP = 5, META_NIDX = 6, META_WORDS = 8 };
+
+struct DigitList { int n; unsigned char word[28], shift[28], nbits[28]; };
+
+// bin = top F bits of the context (base, ctx0[, ctx1]); F <= 16
+template <int W> __device__ __forceinline__ u32 rec_bin (const Rec<W> &r, int k, int F);
+template <> __device__ __forceinline__ u32 rec_bin<2> (const Rec<2> &r, int k, int F)
+{
+  const int top = 2 * k + 1; // significant bits of w1 = base:ctx0
+  if (F <= top) return (u32) (r.w[1] >> (top - F));
+  const int extra = F - top; // spill into the top bits of ctx1 (w0 bits 12 .. 12+2k)
+  return ((u32) r.w[1] << extra) | (u32) ((r.w[0] >> (12 + 2 * k - extra)) & ((1u << extra) - 1));
+}
+template <> __device__ __forceinline__ u32 rec_bin<3> (const Rec<3> &r, int k, int F)
+{
+  return ((u32) ((r.w[0] >> 12) & 1) << (F - 1)) | (u32) (r.w[2] >> (2 * k - (F - 1)));
+}
+
+// ------------------------------------------------------------------------------- block scan helpers ------
+// exclusive scan of one value per thread over a block of NT threads; *total = block sum.  Two barriers.
+template <int NT>
+__device__ __forceinline__ u32 blk_excl_scan (u32 v, u32 *s_warp /*[NT/32 + 1]*/, u32 *total)
+{
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  u32 inc = v;
+#pragma unroll
+  for (int d = 1; d < 32; d <<= 1) { u32 t = __shfl_up_sync (0xffffffffu, inc, d); if (lane >= d) inc += t; }
+  if (lane == 31) s_warp[wid] = inc;
+  __syncthreads ();
+  if (wid == 0) {
+    u32 w = lane < NT / 32 ? s_warp[lane] : 0, winc = w;
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { u32 t = __shfl_up_sync (0xffffffffu, winc, d); if (lane >= d) winc += t; }
+    if (lane < NT / 32) s_warp[lane] = winc - w;
+    if (lane == 31) s_warp[NT / 32] = winc;
+  }
+  __syncthreads ();
+  u32 r = s_warp[wid] + inc - v;
+  *total = s_warp[NT / 32];
+  __syncthreads (); // s_warp may be reused immediately
+  return r;
+}
+
+// ------------------------------------------------------------------------------- histogram (fallback) ----
+// the scan kernel accumulates the bin histogram itself; this kernel rebuilds it from the records after a
+// record-array overflow forced a chunk to be re-scanned
+template <int W>
+__global__ void __launch_bounds__ (256)
+rec_hist_kernel (const u64 *__restrict__ recs, const unsigned long long *__restrict__ counters, unsigned long long capacity, int k, int F,
+                 u32 *__restrict__ bin_hist)
+{
+  unsigned long long n = counters[0] < capacity ? counters[0] : capacity;
+  for (size_t i = (size_t) blockIdx.x * 256 + threadIdx.x; i < n; i += (size_t) gridDim.x * 256)
+    atomicAdd (&bin_hist[rec_bin<W> (load_rec<W> (recs, i), k, F)], 1u);
+}
+
+// ------------------------------------------------------------------------------------------- plan --------
+// Bins are walked from the highest to the lowest (descending key order).  P[j] = number of records in bins before
+// j in that order; bins whose P falls into the same window of BK_CAPH records form one bucket, so a bucket holds
+// fewer than BK_CAPH + (its last bin) records: at most BK_CAP unless a single bin exceeds BK_CAPH.
+__global__ void __launch_bounds__ (PLAN_THREADS)
+plan_kernel (const u32 *__restrict__ bin_hist, int F, const unsigned long long *__restrict__ counters, unsigned long long capacity,
+             u32 *__restrict__ bkt_start, unsigned short *__restrict__ lut, u32 *__restrict__ cursor, u32 *__restrict__ meta)
+{
+  __shared__ u32 s_a[PLAN_THREADS / 32], s_base[PLAN_THREADS / 32 + 1];
+  const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  const u32 NB = 1u << F;
+  const u32 chunk = NB / 32 > 32 ? NB / 32 : 32; // bins per warp (a multiple of 32): coalesced rows of 32 bins
+  const u32 j0 = wid * chunk, j1 = (j0 + chunk < NB) ? j0 + chunk : NB;
+  auto warp_incl = [&] (u32 v) {
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { u32 t = __shfl_up_sync (0xffffffffu, v, d); if (lane >= d) v += t; }
+    return v;
+  };
+  auto scan_warps = [&] (u32 v) { // exclusive scan of one value per warp -> s_base[0..32], s_base[32] = total
+    if (lane == 0) s_a[wid] = v;
+    __syncthreads ();
+    if (wid == 0) { u32 x = s_a[lane], inc = warp_incl (x); s_base[lane] = inc - x; if (lane == 31) s_base[32] = inc; }
+    __syncthreads ();
+  };
+  // pass 1: records per warp chunk
+  u32 sum = 0;
+  for (u32 j = j0 + lane; j < j1 && j0 < NB; j += 32) sum += bin_hist[NB - 1 - j];
+#pragma unroll
+  for (int d = 16; d; d >>= 1) sum += __shfl_xor_sync (0xffffffffu, sum, d);
+  scan_warps (sum);
+  const u32 base = s_base[wid], total = s_base[32];
+  __syncthreads ();
+  // pass 2 counts the bucket heads of the chunk, pass 3 assigns bucket indices
+  u32 hbase = 0;
+  for (int pass = 2; pass <= 3; pass++) {
+    u32 carry = base, nheads = 0;
+    u32 hprev_last = (j0 > 0 && j0 < NB) ? bin_hist[NB - j0] : 0; // records of bin j0 - 1
+    for (u32 row = j0; row < j1 && j0 < NB; row += 32) {
+      const u32 j = row + lane;
+      const u32 h = j < j1 ? bin_hist[NB - 1 - j] : 0;
+      const u32 inc = warp_incl (h);
+      const u32 P = carry + inc - h;
+      u32 hp = __shfl_up_sync (0xffffffffu, h, 1);
+      if (lane == 0) hp = hprev_last;
+      const bool head = j < j1 && (j == 0 || P / BK_CAPH != (P - hp) / BK_CAPH);
+      const u32 hm = __ballot_sync (0xffffffffu, head);
+      if (pass == 3 && j < j1) {
+        const u32 idx = hbase + nheads + __popc (hm & (0xffffffffu >> (31 - lane))) - 1;
+        if (head) { bkt_start[idx] = P; cursor[idx] = P; }
+        lut[NB - 1 - j] = (unsigned short) idx;
+      }
+      nheads += __popc (hm);
+      carry += __shfl_sync (0xffffffffu, inc, 31);
+      hprev_last = __shfl_sync (0xffffffffu, h, 31);
+    }
+    if (pass == 2) { scan_warps (nheads); hbase = s_base[wid]; }
+  }
+  if (threadIdx.x == 0) {
+    const u32 nb_total = s_base[32];
+    bkt_start[nb_total] = total;
+    meta[META_NBUCKETS] = nb_total;
+    meta[META_NOVERSIZE] = 0;
+    meta[META_TICKET] = 0;
+    unsigned long long n = counters[0] < capacity ? counters[0] : capacity;
+    meta[META_N] = (u32) n;
+  }
+}
+
+// --------------------------------------------------------------------------------------- partition -------
+template <int W>
+__global__ void __launch_bounds__ (256)
+partition_kernel (const u64 *__restrict__ in, u64 *__restrict__ out, const unsigned long long *__restrict__ counters,
+                  unsigned long long capacity, int k, int F, const unsigned short *__restrict__ lut, u32 *__restrict__ cursor)
+{
+  const unsigned long long n = counters[0] < capacity ? counters[0] : capacity;
+  const size_t stride = (size_t) gridDim.x * 256;
+  for (size_t i0 = (size_t) blockIdx.x * 256 + threadIdx.x; i0 < n; i0 += 4 * stride) {
+    Rec<W> r[4];
+    u32 pos[4];
+#pragma unroll
+    for (int u = 0; u < 4; u++) { size_t i = i0 + u * stride; if (i < n) r[u] = load_rec<W> (in, i); }
+#pragma unroll
+    for (int u = 0; u < 4; u++) { size_t i = i0 + u * stride; if (i < n) pos[u] = atomicAdd (&cursor[lut[rec_bin<W> (r[u], k, F)]], 1u); }
+#pragma unroll
+    for (int u = 0; u < 4; u++) { size_t i = i0 + u * stride; if (i < n && pos[u] < capacity) store_rec<W> (out, pos[u], r[u]); }
+  }
+}
+
+// ---------------------------------------------------------------------------------- bucket reduce --------
+template <int W> constexpr size_t bucket_smem_bytes ()
+{
+  return (size_t) W * BK_CAP * 8 /* s_w */ + 2 * BK_CAP * 2 /* perm */ + BK_WARPS * 256 * 2 /* counts */ + BK_CAP * 2 /* aux */ +
+         BK_CAP * 4 /* val */ + BK_CAP * 4 /* sum */;
+}
+
+template <int W>
+__global__ void __launch_bounds__ (BK_THREADS)
+bucket_reduce_kernel (const u64 *__restrict__ recs, const u32 *__restrict__ bkt_start, u32 *__restrict__ meta, unsigned long long capacity,
+                      DigitList dl, int remove_biased, int min_coverage, u64 *__restrict__ out_rec, u32 *__restrict__ out_cnt,
+                      u32 *__restrict__ out_idx_i, u32 *__restrict__ out_idx_f, uint4 *__restrict__ bstat)
+{
+  extern __shared__ __align__ (16) unsigned char smem[];
+  u64 *s_w = reinterpret_cast<u64*> (smem);                                  // [W][BK_CAP]
+  const u32 *s_w32 = reinterpret_cast<const u32*> (smem);
+  unsigned short *s_perm0 = reinterpret_cast<unsigned short*> (s_w + W * BK_CAP);
+  unsigned short *s_perm1 = s_perm0 + BK_CAP;
+  unsigned short *s_cnt = s_perm1 + BK_CAP;                                  // [BK_WARPS][256]
+  unsigned short *s_aux = s_cnt + BK_WARPS * 256;                            // [BK_CAP]
+  u32 *s_val = reinterpret_cast<u32*> (s_aux + BK_CAP);                      // [BK_CAP]
+  u32 *s_sum = s_val + BK_CAP;                                               // [BK_CAP]
+  __shared__ u32 s_warp[BK_WARPS + 1];
+  __shared__ u32 s_bucket;
+  __shared__ u32 s_diff[2 * W];
+
+  const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
+  const u32 lt_mask = (1u << lane) - 1;
+
+  for (;;) {
+    if (tid == 0) s_bucket = atomicAdd (&meta[META_TICKET], 1u);
+    if (tid < 2 * W) s_diff[tid] = 0;
+    __syncthreads ();
+    const u32 b = s_bucket;
+    if (b >= meta[META_NBUCKETS]) break;
+    unsigned long long st = bkt_start[b], en = bkt_start[b + 1];
+    if (st > capacity) st = capacity;
+    if (en > capacity) en = capacity;
+    const u32 start = (u32) st, n = (u32) (en - st);
+    if (n > BK_CAP) { // reduced by the global multi-pass path (host reads the flag after the first sync)
+      if (tid == 0) { bstat[b] = make_uint4 (0, 0, 0, 1); atomicAdd (&meta[META_NOVERSIZE], 1u); }
+      __syncthreads ();
+      continue;
+    }
+    // ---- load the bucket; remember which key bits differ at all ------------------------------------------
+    {
+      u64 d[W];
+#pragma unroll
+      for (int j = 0; j < W; j++) d[j] = 0;
+      Rec<W> f;
+      if (n) f = load_rec<W> (recs, start);
+      for (u32 i = tid; i < n; i += BK_THREADS) {
+        Rec<W> r = load_rec<W> (recs, (size_t) start + i);
+#pragma unroll
+        for (int j = 0; j < W; j++) { s_w[j * BK_CAP + i] = r.w[j]; d[j] |= r.w[j] ^ f.w[j]; }
+        s_perm0[i] = (unsigned short) i;
+      }
+#pragma unroll
+      for (int j = 0; j < W; j++) {
+        u32 lo = __reduce_or_sync (0xffffffffu, (u32) d[j]), hi = __reduce_or_sync (0xffffffffu, (u32) (d[j] >> 32));
+        if (lane == 0) { if (lo) atomicOr (&s_diff[2 * j], lo); if (hi) atomicOr (&s_diff[2 * j + 1], hi); }
+      }
+    }
+    __syncthreads ();
+    // ---- LSD radix sort of the index permutation, ascending; digits on which the whole bucket agrees are skipped
+    unsigned short *cur = s_perm0, *nxt = s_perm1;
+    for (int q = 0; q < dl.n; q++) {
+      const int word = dl.word[q], shift = dl.shift[q];
+      const u32 mask = (1u << dl.nbits[q]) - 1;
+      const int half = shift >> 5, sh = shift & 31;
+      if (((s_diff[2 * word + half] >> sh) & mask) == 0) continue;
+      for (int i = tid; i < BK_WARPS * 256 / 2; i += BK_THREADS) reinterpret_cast<u32*> (s_cnt)[i] = 0;
+      __syncthreads ();
+      u32 idx[BK_IPT], dig[BK_IPT], rank[BK_IPT];
+#pragma unroll
+      for (int r = 0; r < BK_IPT; r++) {
+        const u32 i = (u32) wid * (32 * BK_IPT) + r * 32 + lane;
+        u32 d = 256, id = 0;
+        if (i < n) { id = cur[i]; d = (s_w32[2 * ((size_t) word * BK_CAP + id) + half] >> sh) & mask; }
+        idx[r] = id; dig[r] = d;
+        const u32 peers = __match_any_sync (0xffffffffu, d);
+        const int leader = __ffs (peers) - 1;
+        u32 old = 0;
+        if (lane == leader && d < 256) { old = s_cnt[wid * 256 + d]; s_cnt[wid * 256 + d] = (unsigned short) (old + __popc (peers)); }
+        old = __shfl_sync (0xffffffffu, old, leader);
+        rank[r] = old + __popc (peers & lt_mask);
+        __syncwarp ();
+      }
+      __syncthreads ();
+      { // thread t owns digit t: offsets in (digit-major, warp-minor) order
+        u32 c[BK_WARPS], sum = 0;
+#pragma unroll
+        for (int w = 0; w < BK_WARPS; w++) { c[w] = s_cnt[w * 256 + tid]; sum += c[w]; }
+        u32 tot;
+        u32 ex = blk_excl_scan<BK_THREADS> (sum, s_warp, &tot);
+#pragma unroll
+        for (int w = 0; w < BK_WARPS; w++) { s_cnt[w * 256 + tid] = (unsigned short) ex; ex += c[w]; }
+      }
+      __syncthreads ();
+#pragma unroll
+      for (int r = 0; r < BK_IPT; r++)
+        if (dig[r] < 256) nxt[s_cnt[wid * 256 + dig[r]] + rank[r]] = (unsigned short) idx[r];
+      __syncthreads ();
+      unsigned short *t = cur; cur = nxt; nxt = t;
+    }
+    // record at DESCENDING position p
+    auto rec_at = [&] (u32 p) {
+      const u32 id = cur[n - 1 - p];
+      Rec<W> r;
+#pragma unroll
+      for (int j = 0; j < W; j++) r.w[j] = s_w[j * BK_CAP + id];
+      return r;
+    };
+    // ---- S1: heads of runs of equal (base, ctx0, ctx1, length)  (hopo_counter.c:355-365) ------------------
+    u32 n_dist, n_keep, n_groups, n_idx, ctotal;
+    {
+      const u32 p0 = tid * BK_IPT;
+      u32 hmask = 0;
+      if (p0 < n) {
+        Rec<W> prev;
+        if (p0) prev = rec_at (p0 - 1);
+#pragma unroll
+        for (int r = 0; r < BK_IPT; r++) {
+          const u32 p = p0 + r;
+          if (p < n) {
+            Rec<W> x = rec_at (p);
+            if (p == 0 || !same_tract<W> (x, prev)) hmask |= 1u << r;
+            prev = x;
+          }
+        }
+      }
+      u32 dpos = blk_excl_scan<BK_THREADS> (__popc (hmask), s_warp, &n_dist);
+#pragma unroll
+      for (int r = 0; r < BK_IPT; r++) if ((hmask >> r) & 1) s_aux[dpos++] = (unsigned short) (p0 + r);
+    }
+    __syncthreads ();
+    // ---- S2: count, canon_flag (first | last: the flag is the lowest sort digit), QC filter (:367-374) ----
+    {
+      const u32 d0 = tid * BK_IPT;
+      u32 kmask = 0, packed[BK_IPT];
+#pragma unroll
+      for (int r = 0; r < BK_IPT; r++) {
+        const u32 d = d0 + r;
+        if (d < n_dist) {
+          const u32 s = s_aux[d], e = (d + 1 < n_dist) ? s_aux[d + 1] : n;
+          const u32 cnt = e - s; // <= BK_CAP: the 20-bit signed count field cannot wrap here
+          const u32 id_s = cur[n - 1 - s], id_e = cur[n - e];
+          const u32 flag = (u32) ((s_w[id_s] | s_w[id_e]) & 3);
+          const bool keep = remove_biased ? (flag == 3) : (cnt > 1);
+          if (keep) kmask |= 1u << r;
+          packed[r] = s | (cnt << 12) | (flag << 28);
+        }
+      }
+      u32 kpos = blk_excl_scan<BK_THREADS> (__popc (kmask), s_warp, &n_keep);
+#pragma unroll
+      for (int r = 0; r < BK_IPT; r++) if ((kmask >> r) & 1) s_val[kpos++] = packed[r];
+    }
+    __syncthreads ();
+    // ---- S3: context groups over the kept list + prefix sums of their counts (:388-404) -------------------
+    {
+      const u32 j0 = tid * BK_IPT;
+      u32 gmask = 0, csum = 0, c[BK_IPT];
+      if (j0 < n_keep) {
+        Rec<W> prev;
+        if (j0) prev = rec_at (s_val[j0 - 1] & 0xfff);
+#pragma unroll
+        for (int r = 0; r < BK_IPT; r++) {
+          const u32 j = j0 + r;
+          c[r] = 0;
+          if (j < n_keep) {
+            const u32 v = s_val[j];
+            c[r] = (v >> 12) & 0xffff;
+            csum += c[r];
+            Rec<W> x = rec_at (v & 0xfff);
+            if (j == 0 || !same_context<W> (x, prev)) gmask |= 1u << r;
+            prev = x;
+          }
+        }
+      }
+      u32 gpos = blk_excl_scan<BK_THREADS> (__popc (gmask), s_warp, &n_groups);
+      u32 cpos = blk_excl_scan<BK_THREADS> (csum, s_warp, &ctotal);
+      __syncthreads (); // every S2 read of s_aux is done (it is reused for the group starts)
+#pragma unroll
+      for (int r = 0; r < BK_IPT; r++) {
+        const u32 j = j0 + r;
+        if (j < n_keep) {
+          s_sum[j] = cpos; cpos += c[r];
+          if ((gmask >> r) & 1) s_aux[gpos++] = (unsigned short) j;
+        }
+      }
+    }
+    __syncthreads ();
+    // ---- S4: groups whose summed count reaches min_coverage -> (idx_initial, idx_final), bucket-local -------
+    {
+      const u32 g0 = tid * BK_IPT;
+      u32 imask = 0, js[BK_IPT], je[BK_IPT];
+#pragma unroll
+      for (int r = 0; r < BK_IPT; r++) {
+        const u32 g = g0 + r;
+        if (g < n_groups) {
+          js[r] = s_aux[g];
+          je[r] = (g + 1 < n_groups) ? s_aux[g + 1] : n_keep;
+          const u32 hi = (je[r] < n_keep) ? s_sum[je[r]] : ctotal;
+          if ((int) (hi - s_sum[js[r]]) >= min_coverage) imask |= 1u << r;
+        }
+      }
+      u32 ipos = blk_excl_scan<BK_THREADS> (__popc (imask), s_warp, &n_idx);
+#pragma unroll
+      for (int r = 0; r < BK_IPT; r++)
+        if ((imask >> r) & 1) { out_idx_i[start + ipos] = js[r]; out_idx_f[start + ipos] = je[r]; ipos++; }
+    }
+    // ---- S5: kept records, compact, at the bucket's own offset ----------------------------------------------
+    for (u32 j = tid; j < n_keep; j += BK_THREADS) {
+      const u32 v = s_val[j];
+      Rec<W> x = rec_at (v & 0xfff);
+      x.w[0] = (x.w[0] & ~3ULL) | (u64) (v >> 28);
+      store_rec<W> (out_rec, (size_t) start + j, x);
+      out_cnt[start + j] = (v >> 12) & 0xffff;
+    }
+    if (tid == 0) bstat[b] = make_uint4 (n_dist, n_keep, n_idx, 0);
+    __syncthreads ();
+  }
+}
+
+// ------------------------------------------------------------------------------------------ totals -------
+__global__ void __launch_bounds__ (PLAN_THREADS)
+totals_kernel (const uint4 *__restrict__ bstat, u32 *__restrict__ meta, u32 *__restrict__ koff, u32 *__restrict__ ioff)
+{
+  __shared__ u32 s_warp[PLAN_THREADS / 32 + 1];
+  const u32 nb = meta[META_NBUCKETS];
+  const u32 ipt = (nb + PLAN_THREADS - 1) / PLAN_THREADS;
+  const u32 b0 = threadIdx.x * ipt, b1 = (b0 + ipt < nb) ? b0 + ipt : nb;
+  u32 sd = 0, sk = 0, si = 0;
+  for (u32 b = b0; b < b1; b++) { uint4 s = bstat[b]; sd += s.x; sk += s.y; si += s.z; }
+  u32 td, tk, ti;
+  blk_excl_scan<PLAN_THREADS> (sd, s_warp, &td);
+  u32 ek = blk_excl_scan<PLAN_THREADS> (sk, s_warp, &tk);
+  u32 ei = blk_excl_scan<PLAN_THREADS> (si, s_warp, &ti);
+  for (u32 b = b0; b < b1; b++) { uint4 s = bstat[b]; koff[b] = ek; ioff[b] = ei; ek += s.y; ei += s.z; }
+  if (threadIdx.x == 0) { meta[META_NDIST] = td; meta[META_NKEEP] = tk; meta[META_NIDX] = ti; }
+}
+
+// ------------------------------------------------------------------------------- coverage hash + pack ----
+#define COV_EMPTY 0xffffffffu
+__device__ __forceinline__ void cov_insert (u32 *__restrict__ keys, u32 *__restrict__ vals, u32 mask, u32 key, u32 w)
+{
+  u32 slot = (key * 0x9E3779B1u) >> 7;
+  for (;;) {
+    slot &= mask;
+    u32 prev = keys[slot];
+    if (prev != key) {
+      if (prev != COV_EMPTY) { slot++; continue; }
+      prev = atomicCAS (&keys[slot], COV_EMPTY, key);
+      if (prev != COV_EMPTY && prev != key) { slot++; continue; }
+    }
+    atomicAdd (&vals[slot], w);
+    return;
+  }
+}
+
+// one warp per bucket: final 40-byte hopo_element (src/hopo_counter.h:34-49) as it stands at the BWA boundary, global
+// idx_initial / idx_final, and the two (flank & 0x7fffffff, count) pairs of every kept record (hopo_counter.c:427-432)
+template <int W>
+__global__ void __launch_bounds__ (256)
+pack_kernel (const u64 *__restrict__ out_rec, const u32 *__restrict__ out_cnt, const u32 *__restrict__ out_idx_i, const u32 *__restrict__ out_idx_f,
+             const u32 *__restrict__ bkt_start, const uint4 *__restrict__ bstat, const u32 *__restrict__ koff, const u32 *__restrict__ ioff,
+             const u32 *__restrict__ meta, int k, u64 *__restrict__ out40, int *__restrict__ idx_initial, int *__restrict__ idx_final,
+             u32 *__restrict__ cov_keys, u32 *__restrict__ cov_vals, u32 cov_mask)
+{
+  const u32 nb = meta[META_NBUCKETS];
+  const int lane = threadIdx.x & 31;
+  const u32 warps = gridDim.x * (256 / 32);
+  for (u32 b = blockIdx.x * (256 / 32) + (threadIdx.x >> 5); b < nb; b += warps) {
+    const uint4 s = bstat[b];
+    const u32 start = bkt_start[b], ko = koff[b], io = ioff[b];
+    for (u32 j = lane; j < s.y; j += 32) {
+      Rec<W> r = load_rec<W> (out_rec, (size_t) start + j);
+      const int cnt = sext_field ((long long) out_cnt[start + j], 20); // the reference's count:20 signed bit-field
+      // gcc x86-64 bit-field order from the LSB: base:2 length:10 count:20 mismatches:12 multi:3 neg_strand:2 canon_flag:3
+      const u64 bits = ((u64) rec_base<W> (r, k) & 3) | (((u64) rec_len_field<W> (r) & 0x3ff) << 2) | (((u64) cnt & 0xfffff) << 12) |
+                       (0xffeULL << 32) | (((u64) rec_flag<W> (r) & 7) << 49);
+      const u64 c0 = rec_ctx0<W> (r, k), c1 = rec_ctx1<W> (r, k);
+      u64 *o = out40 + 5 * (size_t) (ko + j);
+      o[0] = c0; o[1] = c1; o[2] = bits;
+      o[3] = ~0ULL; // read_offset = -1 (hopo_counter.c:511), loc_ref_id = -1 (:297)
+      o[4] = ~0ULL; // loc_pos = loc_last = -1
+      cov_insert (cov_keys, cov_vals, cov_mask, (u32) (c0 & 0x7fffffffULL), (u32) cnt);
+      cov_insert (cov_keys, cov_vals, cov_mask, (u32) (c1 & 0x7fffffffULL), (u32) cnt);
+    }
+    for (u32 t = lane; t < s.z; t += 32) {
+      idx_initial[io + t] = (int) (ko + out_idx_i[start + t]);
+      idx_final[io + t] = (int) (ko + out_idx_f[start + t]);
+    }
+  }
+}
+
+// coverage = largest summed weight of any key (empirical_frequency.c:254-277 sorted by frequency, hopo_counter.c:434)
+__global__ void __launch_bounds__ (256)
+cov_max_kernel (const u32 *__restrict__ keys, const u32 *__restrict__ vals, u32 n_slots, int *__restrict__ cov)
+{
+  int best = INT_MIN;
+  for (u32 i = blockIdx.x * 256 + threadIdx.x; i < n_slots; i += gridDim.x * 256)
+    if (keys[i] != COV_EMPTY) { int v = (int) vals[i]; best = v > best ? v : best; }
+#pragma unroll
+  for (int d = 16; d; d >>= 1) { int o = __shfl_xor_sync (0xffffffffu, best, d); best = o > best ? o : best; }
+  if ((threadIdx.x & 31) == 0 && best != INT_MIN) atomicMax (cov, best);
+}

@@ -11,15 +11,20 @@
 #include "tjb_gpu.h"
 #include "tjb_common.cuh"
 #include "tjb_scan.cuh"
+#include "tjb_bucket.cuh"
 #include "tjb_sort.cuh"
 #include "tjb_reduce.cuh"
 
 #define TJB_VERSION_STR "tatajuba_b200 0.1 (sm_100a)"
-#define TJB_CHUNK_BYTES (64u << 20) // host->device chunk of decoded reads
+#define TJB_CHUNK_BYTES (64u << 20)      // files path: pinned chunk of decoded reads
+#define TJB_HOST_CHUNK_BYTES (32u << 20) // host-buffer path: H2D chunk overlapped with the scan of the previous one
 
-enum KernelId { K_SCAN = 0, K_SORT_HIST, K_SORT_SCATTER, K_PSCAN, K_RLE, K_GROUP, K_COVERAGE, K_PACK, K_COUNT };
-static const char *kKernelNames[K_COUNT] = {"tjb_scan_kernel", "rsort_hist_kernel", "rsort_scatter_kernel", "pscan_kernels",
-                                            "rle_kernels", "group_kernels", "coverage_kernels", "pack_hopo_kernel"};
+enum KernelId { K_SCAN = 0, K_PLAN, K_PARTITION, K_BUCKET, K_TOTALS, K_PACK, K_COVMAX, K_RECHIST,
+                // global multi-pass path, only for buckets too large for shared memory
+                K_SORT_HIST, K_SORT_SCATTER, K_PSCAN, K_RLE, K_GROUP, K_COUNT };
+static const char *kKernelNames[K_COUNT] = {"tjb_scan_kernel", "plan_kernel", "partition_kernel", "bucket_reduce_kernel", "totals_kernel",
+                                            "pack_kernel", "cov_max_kernel", "rec_hist_kernel", "rsort_hist_kernel",
+                                            "rsort_scatter_kernel", "pscan_kernels", "rle_kernels", "group_kernels"};
 
 struct DevBuf {
   void *p = nullptr;
@@ -49,12 +54,21 @@ struct tjb_ctx {
   unsigned long long n_raw_known = 0, n_skip_known = 0;
   const uint8_t *pend_ptr = nullptr; size_t pend_len = 0; bool pend = false; // scan launched, overflow not checked yet
   unsigned long long *d_counters = nullptr; // [0] = n_raw, [1] = skipped non-ACGTU runs
-  u32 *d_totals = nullptr;                  // small device scalars
+  u32 *d_totals = nullptr;                  // small device scalars (global multi-pass path)
   int *d_cov = nullptr;
-  DevBuf hist, ptmp, heads, pos, seg, drec, dcount, keep, kpos, krec, kcount, cw, csum, gkeep, gkpos, pairs_a, pairs_b, out40,
-      idx_i, idx_f;
+  // bucketed reduce: bin histogram (filled by the scan), splitters, per-bucket results
+  int bin_bits = TJB_MAX_BIN_BITS;
+  bool hist_dirty = false;                  // a chunk was re-scanned after an overflow: rebuild the histogram from the records
+  u32 *d_bin_hist = nullptr, *d_bkt_start = nullptr, *d_cursor = nullptr, *d_meta = nullptr, *d_koff = nullptr, *d_ioff = nullptr;
+  unsigned short *d_lut = nullptr;
+  uint4 *d_bstat = nullptr;
+  unsigned long long *h_sync = nullptr;     // pinned: [0..1] counters, [2..] meta words
+  DevBuf out_cnt, out_ii, out_if, cov_tab;
+  DevBuf hist, ptmp, heads, pos, seg, drec, dcount, keep, kpos, krec, kcount, cw, csum, gkeep, gkpos, out40, idx_i, idx_f;
 
   cudaEvent_t ev_t0 = nullptr, ev_t1 = nullptr;
+  cudaStream_t copy_stream = nullptr; // host-buffer path: H2D copies overlap the scan of the previous chunk
+  cudaEvent_t ev_ready = nullptr, ev_copied[2] = {nullptr, nullptr}, ev_scanned[2] = {nullptr, nullptr};
 };
 
 // ------------------------------------------------------------------------------------------- helpers ----
@@ -183,7 +197,18 @@ static int grow_records (tjb_ctx *ctx, size_t want_records)
   return 0;
 }
 
-static int begin_sample (tjb_ctx *ctx, const tjb_opts *opt)
+// bins of the partition plan: enough that a bin holds ~BK_CAP/8 records on average, at most what the context has
+static int choose_bin_bits (size_t n_bytes_hint, int k)
+{
+  const int W = tjb_rec_words (k);
+  const int max_bits = W == 2 ? (4 * k + 1 < TJB_MAX_BIN_BITS ? 4 * k + 1 : TJB_MAX_BIN_BITS) : TJB_MAX_BIN_BITS;
+  int F = 4;
+  if (n_bytes_hint == 0) F = TJB_MAX_BIN_BITS; // size unknown (streamed files)
+  else { size_t est = n_bytes_hint / 32; while (F < TJB_MAX_BIN_BITS && (est >> F) > BK_CAP / 8) F++; }
+  return F < max_bits ? F : max_bits;
+}
+
+static int begin_sample (tjb_ctx *ctx, const tjb_opts *opt, size_t n_bytes_hint)
 {
   if (!opt || opt->kmer_size < 2 || opt->kmer_size > 32 || opt->min_tract_size < 1 || opt->min_coverage < 0) {
     ctx->err = "options out of range (kmer_size 2..32, min_tract_size >= 1, min_coverage >= 0)";
@@ -194,28 +219,32 @@ static int begin_sample (tjb_ctx *ctx, const tjb_opts *opt)
   if (W != ctx->rec_words) { ctx->rec_words = W; ctx->rec_capacity = ctx->rec_a.cap / (W * sizeof (u64)); }
   ctx->n_raw_known = ctx->n_skip_known = 0;
   ctx->pend = false;
+  ctx->hist_dirty = false;
+  ctx->bin_bits = choose_bin_bits (n_bytes_hint, opt->kmer_size);
   CU (cudaMemsetAsync (ctx->d_counters, 0, 2 * sizeof (unsigned long long), ctx->stream));
+  CU (cudaMemsetAsync (ctx->d_bin_hist, 0, sizeof (u32) << ctx->bin_bits, ctx->stream));
   return 0;
 }
 
 static int launch_scan (tjb_ctx *ctx, const uint8_t *d_seqs, size_t n, const tjb_opts *opt)
 {
-  long long n_tiles = (long long) ((n + SCAN_TILE - 1) / SCAN_TILE);
+  long long n_tiles = (long long) ((n + SW_TILE - 1) / SW_TILE); // one 2 KiB tile per warp at a time
   if (!n_tiles) return 0;
   int min_len = opt->min_tract_size < 2 ? 2 : opt->min_tract_size;
-  long long grid = n_tiles < (long long) ctx->sm_count * 4 ? n_tiles : (long long) ctx->sm_count * 4;
-  // algorithmic bytes of this launch: every sequence byte read once (+ 8W bytes per emitted record, added by the caller)
+  long long want = (n_tiles + SCAN_WARPS - 1) / SCAN_WARPS;
+  long long grid = want < (long long) ctx->sm_count * 4 ? want : (long long) ctx->sm_count * 4;
+  // algorithmic bytes of this launch: every sequence byte read once (+ 8W bytes per emitted record, added at finalise)
   if (ctx->rec_words == 2)
-    LAUNCH (K_SCAN, n, (tjb_scan_kernel<2><<<(u32) grid, SCAN_THREADS, 0, ctx->stream>>> (d_seqs, (long long) n, opt->kmer_size, min_len, (u64*) ctx->rec_a.p, ctx->rec_capacity, ctx->d_counters, n_tiles)));
+    LAUNCH (K_SCAN, n, (tjb_scan_kernel<2><<<(u32) grid, SCAN_THREADS, scan_smem_bytes<2> (), ctx->stream>>> (d_seqs, (long long) n, opt->kmer_size, min_len, (u64*) ctx->rec_a.p, ctx->rec_capacity, ctx->d_counters, n_tiles, ctx->d_bin_hist, ctx->bin_bits)));
   else
-    LAUNCH (K_SCAN, n, (tjb_scan_kernel<3><<<(u32) grid, SCAN_THREADS, 0, ctx->stream>>> (d_seqs, (long long) n, opt->kmer_size, min_len, (u64*) ctx->rec_a.p, ctx->rec_capacity, ctx->d_counters, n_tiles)));
+    LAUNCH (K_SCAN, n, (tjb_scan_kernel<3><<<(u32) grid, SCAN_THREADS, scan_smem_bytes<3> (), ctx->stream>>> (d_seqs, (long long) n, opt->kmer_size, min_len, (u64*) ctx->rec_a.p, ctx->rec_capacity, ctx->d_counters, n_tiles, ctx->d_bin_hist, ctx->bin_bits)));
   CU (cudaGetLastError ());
   return 0;
 }
 
 // Launches the scan of one device-resident chunk (asynchronous).  The record array is grown beforehand to an estimate;
-// scan_resolve() then synchronises and, if the chunk overflowed the array (overflowing records are counted but never
-// written), grows it to the exact size and re-runs the chunk from the pre-chunk counter values.
+// overflowing records are counted but never written, so the overflow is detected at the next synchronisation
+// (scan_resolve(), or the first synchronisation of finalise for a single-chunk sample) and the chunk re-scanned.
 static int scan_launch (tjb_ctx *ctx, const uint8_t *d_seqs, size_t n, const tjb_opts *opt)
 {
   size_t guess = (size_t) ctx->n_raw_known + n / 16 + 65536;
@@ -224,122 +253,177 @@ static int scan_launch (tjb_ctx *ctx, const uint8_t *d_seqs, size_t n, const tjb
   ctx->pend_ptr = d_seqs; ctx->pend_len = n; ctx->pend = true;
   return 0;
 }
+// re-scan of the pending chunk after an overflow: cnt0 = the (too large) record count the first attempt reported
+static int scan_redo (tjb_ctx *ctx, const tjb_opts *opt, unsigned long long cnt0)
+{
+  unsigned long long back[2] = {ctx->n_raw_known, ctx->n_skip_known};
+  TRY (grow_records (ctx, (size_t) cnt0 + 1024));
+  CU (cudaMemcpyAsync (ctx->d_counters, back, sizeof (back), cudaMemcpyHostToDevice, ctx->stream));
+  CU (cudaStreamSynchronize (ctx->stream)); // `back` lives on this stack frame
+  ctx->hist_dirty = true;                   // the first attempt already counted this chunk's bins
+  return launch_scan (ctx, ctx->pend_ptr, ctx->pend_len, opt);
+}
 static int scan_resolve (tjb_ctx *ctx, const tjb_opts *opt)
 {
   if (!ctx->pend) return 0;
-  ctx->pend = false;
   unsigned long long cnt[2];
   CU (cudaMemcpyAsync (cnt, ctx->d_counters, sizeof (cnt), cudaMemcpyDeviceToHost, ctx->stream));
   CU (cudaStreamSynchronize (ctx->stream));
   if (cnt[0] > ctx->rec_capacity) {
-    unsigned long long back[2] = {ctx->n_raw_known, ctx->n_skip_known};
-    TRY (grow_records (ctx, (size_t) cnt[0] + 1024));
-    CU (cudaMemcpyAsync (ctx->d_counters, back, sizeof (back), cudaMemcpyHostToDevice, ctx->stream));
-    TRY (launch_scan (ctx, ctx->pend_ptr, ctx->pend_len, opt));
+    TRY (scan_redo (ctx, opt, cnt[0]));
     CU (cudaMemcpyAsync (cnt, ctx->d_counters, sizeof (cnt), cudaMemcpyDeviceToHost, ctx->stream));
     CU (cudaStreamSynchronize (ctx->stream));
   }
+  ctx->pend = false;
   ctx->n_raw_known = cnt[0];
   ctx->n_skip_known = cnt[1];
   return 0;
 }
-static int scan_chunk (tjb_ctx *ctx, const uint8_t *d_seqs, size_t n, const tjb_opts *opt)
-{
-  TRY (scan_launch (ctx, d_seqs, n, opt));
-  return scan_resolve (ctx, opt);
-}
 
 // --------------------------------------------------------------------------------------- finalise -------
+// Global multi-pass reduce of ONE bucket that does not fit in shared memory: LSD radix sort over every digit,
+// run-length count, QC filter, context groups.  Results land where bucket_reduce_kernel would have put them.
 template <int W>
-static int finalise_t (tjb_ctx *ctx, const tjb_opts *opt, tjb_counter_out *out)
+static int reduce_oversize_bucket (tjb_ctx *ctx, const tjb_opts *opt, u32 b, u32 start, u32 n)
 {
   const int k = opt->kmer_size;
   cudaStream_t st = ctx->stream;
-  unsigned long long cnt[2];
-  CU (cudaMemcpyAsync (cnt, ctx->d_counters, sizeof (cnt), cudaMemcpyDeviceToHost, st));
-  CU (cudaStreamSynchronize (st));
-  out->n_raw = (int64_t) cnt[0];
-  out->n_skipped_nonacgt = (int64_t) cnt[1];
-  if (cnt[0] == 0) { out->status = TJB_NO_HT; return 0; }
-  if (cnt[0] > (unsigned long long) INT32_MAX) { ctx->err = "more than INT32_MAX tract observations"; return TJB_ERR_TOO_LARGE; }
-  const u32 n = (u32) cnt[0];
-
-  // 1. sort (hopo_counter.c:351)
-  TRY (ensure (ctx, ctx->rec_b, (size_t) n * W * sizeof (u64)));
+  TRY (ensure (ctx, ctx->drec, (size_t) n * W * 8)); // scratch of n records
+  u64 *in = (u64*) ctx->rec_b.p + (size_t) start * W, *tmp = (u64*) ctx->drec.p;
   u64 *sorted = nullptr;
-  TRY ((radix_sort<W> (ctx, (u64*) ctx->rec_a.p, (u64*) ctx->rec_b.p, n, tract_digits (W, k), &sorted)));
-
-  // 2. run-length count (:352-365) + QC filter (:367-374)
+  TRY ((radix_sort<W> (ctx, in, tmp, n, tract_digits (W, k), &sorted)));
   TRY (ensure (ctx, ctx->heads, (size_t) n * 4)); TRY (ensure (ctx, ctx->pos, (size_t) n * 4)); TRY (ensure (ctx, ctx->seg, (size_t) n * 4));
   TRY (ensure (ctx, ctx->ptmp, pscan_tmp_elems (n) * 4 + 64));
   u32 *heads = (u32*) ctx->heads.p, *pos = (u32*) ctx->pos.p, *seg = (u32*) ctx->seg.p, *ptmp = (u32*) ctx->ptmp.p;
   u32 h_tot[4];
-  LAUNCH (K_RLE, 16 * W * n, (head_kernel<W, 0><<<nblk (n, RED_THREADS), RED_THREADS, 0, st>>> (sorted, n, heads)));
+  LAUNCH (K_RLE, 16 * W * (size_t) n, (head_kernel<W, 0><<<nblk (n, RED_THREADS), RED_THREADS, 0, st>>> (sorted, n, heads)));
   TRY (exclusive_scan (ctx, heads, pos, n, ptmp, ctx->d_totals + 0));
   CU (cudaMemcpyAsync (h_tot, ctx->d_totals, 4, cudaMemcpyDeviceToHost, st));
-  LAUNCH (K_RLE, 12 * n, (seg_start_kernel<<<nblk (n, RED_THREADS), RED_THREADS, 0, st>>> (heads, pos, n, seg)));
+  LAUNCH (K_RLE, 12 * (size_t) n, (seg_start_kernel<<<nblk (n, RED_THREADS), RED_THREADS, 0, st>>> (heads, pos, n, seg)));
   CU (cudaStreamSynchronize (st));
   const u32 n_dist = h_tot[0];
-  out->n_distinct = n_dist;
-  TRY (ensure (ctx, ctx->drec, (size_t) n_dist * W * 8)); TRY (ensure (ctx, ctx->dcount, (size_t) n_dist * 4));
-  TRY (ensure (ctx, ctx->keep, (size_t) n_dist * 4)); TRY (ensure (ctx, ctx->kpos, (size_t) n_dist * 4));
-  LAUNCH (K_RLE, (16 * W + 12) * (size_t) n_dist, (rle_emit_kernel<W><<<nblk (n_dist, RED_THREADS), RED_THREADS, 0, st>>> (sorted, n, seg, n_dist, opt->remove_biased, (u64*) ctx->drec.p, (int*) ctx->dcount.p, (u32*) ctx->keep.p)));
+  // distinct records: into whichever of {in, tmp} does not hold the sorted array
+  u64 *drec = (sorted == in) ? tmp : in;
+  TRY (ensure (ctx, ctx->dcount, (size_t) n_dist * 4)); TRY (ensure (ctx, ctx->keep, (size_t) n_dist * 4)); TRY (ensure (ctx, ctx->kpos, (size_t) n_dist * 4));
+  LAUNCH (K_RLE, (16 * W + 12) * (size_t) n_dist, (rle_emit_kernel<W><<<nblk (n_dist, RED_THREADS), RED_THREADS, 0, st>>> (sorted, n, seg, n_dist, opt->remove_biased, drec, (int*) ctx->dcount.p, (u32*) ctx->keep.p)));
   TRY (exclusive_scan (ctx, (u32*) ctx->keep.p, (u32*) ctx->kpos.p, n_dist, ptmp, ctx->d_totals + 1));
   CU (cudaMemcpyAsync (h_tot, ctx->d_totals + 1, 4, cudaMemcpyDeviceToHost, st));
   CU (cudaStreamSynchronize (st));
   const u32 n_keep = h_tot[0];
+  u32 n_idx = 0;
+  if (n_keep) {
+    // kept records go straight to the bucket's output slot (rec_a doubles as the compact output array)
+    u64 *krec = (u64*) ctx->rec_a.p + (size_t) start * W;
+    int *kcount = (int*) ctx->out_cnt.p + start;
+    LAUNCH (K_RLE, (16 * W + 8) * (size_t) n_keep, (compact_kernel<W><<<nblk (n_dist, RED_THREADS), RED_THREADS, 0, st>>> (drec, (int*) ctx->dcount.p, (u32*) ctx->keep.p, (u32*) ctx->kpos.p, n_dist, krec, kcount)));
+    TRY (ensure (ctx, ctx->cw, (size_t) n_keep * 4)); TRY (ensure (ctx, ctx->csum, (size_t) n_keep * 4));
+    TRY (ensure (ctx, ctx->gkeep, (size_t) n_keep * 4)); TRY (ensure (ctx, ctx->gkpos, (size_t) n_keep * 4));
+    LAUNCH (K_GROUP, 16 * W * (size_t) n_keep, (head_kernel<W, 1><<<nblk (n_keep, RED_THREADS), RED_THREADS, 0, st>>> (krec, n_keep, heads)));
+    TRY (exclusive_scan (ctx, heads, pos, n_keep, ptmp, ctx->d_totals + 0));
+    LAUNCH (K_GROUP, 12 * (size_t) n_keep, (seg_start_kernel<<<nblk (n_keep, RED_THREADS), RED_THREADS, 0, st>>> (heads, pos, n_keep, seg)));
+    LAUNCH (K_GROUP, 8 * (size_t) n_keep, (icopy_kernel<<<nblk (n_keep, RED_THREADS), RED_THREADS, 0, st>>> (kcount, n_keep, (u32*) ctx->cw.p)));
+    TRY (exclusive_scan (ctx, (u32*) ctx->cw.p, (u32*) ctx->csum.p, n_keep, ptmp, ctx->d_totals + 2));
+    CU (cudaMemcpyAsync (h_tot, ctx->d_totals, 4, cudaMemcpyDeviceToHost, st));
+    CU (cudaStreamSynchronize (st));
+    const u32 n_groups = h_tot[0];
+    LAUNCH (K_GROUP, 12 * (size_t) n_groups, (group_keep_kernel<<<nblk (n_groups, RED_THREADS), RED_THREADS, 0, st>>> (seg, n_groups, n_keep, (u32*) ctx->csum.p, ctx->d_totals + 2, opt->min_coverage, (u32*) ctx->gkeep.p)));
+    TRY (exclusive_scan (ctx, (u32*) ctx->gkeep.p, (u32*) ctx->gkpos.p, n_groups, ptmp, ctx->d_totals + 3));
+    CU (cudaMemcpyAsync (h_tot, ctx->d_totals + 3, 4, cudaMemcpyDeviceToHost, st));
+    LAUNCH (K_GROUP, 16 * (size_t) n_groups, (group_emit_kernel<<<nblk (n_groups, RED_THREADS), RED_THREADS, 0, st>>> (seg, (u32*) ctx->gkeep.p, (u32*) ctx->gkpos.p, n_groups, n_keep, (int*) ctx->out_ii.p + start, (int*) ctx->out_if.p + start)));
+    CU (cudaStreamSynchronize (st));
+    n_idx = h_tot[0];
+  }
+  uint4 stat = make_uint4 (n_dist, n_keep, n_idx, 0);
+  CU (cudaMemcpyAsync (ctx->d_bstat + b, &stat, sizeof (stat), cudaMemcpyHostToDevice, st));
+  CU (cudaStreamSynchronize (st));
+  return 0;
+}
+
+static DigitList digit_list (int W, int k)
+{
+  DigitList dl;
+  std::vector<DigitDesc> v = tract_digits (W, k);
+  dl.n = (int) v.size ();
+  for (int i = 0; i < dl.n; i++) { dl.word[i] = (unsigned char) v[i].word; dl.shift[i] = (unsigned char) v[i].shift; dl.nbits[i] = (unsigned char) v[i].nbits; }
+  return dl;
+}
+
+template <int W>
+static int finalise_t (tjb_ctx *ctx, const tjb_opts *opt, tjb_counter_out *out, bool *overflow)
+{
+  const int k = opt->kmer_size, F = ctx->bin_bits;
+  cudaStream_t st = ctx->stream;
+  const unsigned long long cap = ctx->rec_capacity;
+  *overflow = false;
+  if (!cap) { // nothing was ever scanned (empty input)
+    out->status = TJB_NO_HT;
+    return 0;
+  }
+  // workspace that scales with the record capacity; rec_a is reused as the compact output array once partitioned
+  TRY (ensure (ctx, ctx->rec_b, (size_t) cap * W * 8));
+  TRY (ensure (ctx, ctx->out_cnt, (size_t) cap * 4)); TRY (ensure (ctx, ctx->out_ii, (size_t) cap * 4)); TRY (ensure (ctx, ctx->out_if, (size_t) cap * 4));
+  u64 *rec_a = (u64*) ctx->rec_a.p, *rec_b = (u64*) ctx->rec_b.p;
+  const u32 grid = (u32) ctx->sm_count;
+
+  if (ctx->hist_dirty) {
+    CU (cudaMemsetAsync (ctx->d_bin_hist, 0, sizeof (u32) << F, st));
+    LAUNCH (K_RECHIST, 0, (rec_hist_kernel<W><<<grid * 8, 256, 0, st>>> (rec_a, ctx->d_counters, cap, k, F, ctx->d_bin_hist)));
+    ctx->hist_dirty = false;
+  }
+  LAUNCH (K_PLAN, 10 << F, (plan_kernel<<<1, PLAN_THREADS, 0, st>>> (ctx->d_bin_hist, F, ctx->d_counters, cap, ctx->d_bkt_start, ctx->d_lut, ctx->d_cursor, ctx->d_meta)));
+  LAUNCH (K_PARTITION, 0, (partition_kernel<W><<<grid * 8, 256, 0, st>>> (rec_a, rec_b, ctx->d_counters, cap, k, F, ctx->d_lut, ctx->d_cursor)));
+  LAUNCH (K_BUCKET, 0, (bucket_reduce_kernel<W><<<grid * (W == 2 ? 3 : 1), BK_THREADS, bucket_smem_bytes<W> (), st>>> (rec_b, ctx->d_bkt_start, ctx->d_meta, cap, digit_list (W, k), opt->remove_biased, opt->min_coverage, rec_a, (u32*) ctx->out_cnt.p, (u32*) ctx->out_ii.p, (u32*) ctx->out_if.p, ctx->d_bstat)));
+  LAUNCH (K_TOTALS, 0, (totals_kernel<<<1, PLAN_THREADS, 0, st>>> (ctx->d_bstat, ctx->d_meta, ctx->d_koff, ctx->d_ioff)));
+  CU (cudaGetLastError ());
+  // ---- synchronisation 1: counts --------------------------------------------------------------------------
+  unsigned long long *hs = ctx->h_sync;
+  u32 *hm = (u32*) (hs + 2);
+  CU (cudaMemcpyAsync (hs, ctx->d_counters, 2 * sizeof (unsigned long long), cudaMemcpyDeviceToHost, st));
+  CU (cudaMemcpyAsync (hm, ctx->d_meta, META_WORDS * sizeof (u32), cudaMemcpyDeviceToHost, st));
+  CU (cudaStreamSynchronize (st));
+  if (hs[0] > cap) { *overflow = true; return 0; } // the record array overflowed: everything above worked on garbage
+  out->n_raw = (int64_t) hs[0];
+  out->n_skipped_nonacgt = (int64_t) hs[1];
+  if (hs[0] == 0) { out->status = TJB_NO_HT; return 0; }
+  if (hs[0] > (unsigned long long) INT32_MAX) { ctx->err = "more than INT32_MAX tract observations"; return TJB_ERR_TOO_LARGE; }
+  const u32 n = (u32) hs[0], n_buckets = hm[META_NBUCKETS];
+  if (hm[META_NOVERSIZE]) { // rare: buckets that do not fit in shared memory go through the global multi-pass path
+    std::vector<u32> h_start (n_buckets + 1);
+    std::vector<uint4> h_stat (n_buckets);
+    CU (cudaMemcpyAsync (h_start.data (), ctx->d_bkt_start, (n_buckets + 1) * sizeof (u32), cudaMemcpyDeviceToHost, st));
+    CU (cudaMemcpyAsync (h_stat.data (), ctx->d_bstat, n_buckets * sizeof (uint4), cudaMemcpyDeviceToHost, st));
+    CU (cudaStreamSynchronize (st));
+    for (u32 b = 0; b < n_buckets; b++)
+      if (h_stat[b].w) TRY ((reduce_oversize_bucket<W> (ctx, opt, b, h_start[b], h_start[b + 1] - h_start[b])));
+    rec_a = (u64*) ctx->rec_a.p;
+    LAUNCH (K_TOTALS, 0, (totals_kernel<<<1, PLAN_THREADS, 0, st>>> (ctx->d_bstat, ctx->d_meta, ctx->d_koff, ctx->d_ioff)));
+    CU (cudaMemcpyAsync (hm, ctx->d_meta, META_WORDS * sizeof (u32), cudaMemcpyDeviceToHost, st));
+    CU (cudaStreamSynchronize (st));
+  }
+  const u32 n_keep = hm[META_NKEEP], n_idx = hm[META_NIDX];
+  out->n_distinct = hm[META_NDIST];
+  // algorithmic bytes of the launches above, now that the counts are known
+  ctx->stats[K_PARTITION].bytes_algorithmic += (int64_t) 16 * W * n;
+  ctx->stats[K_BUCKET].bytes_algorithmic += (int64_t) 8 * W * n + (int64_t) (8 * W + 4) * n_keep + 8 * (int64_t) n_idx;
+  ctx->stats[K_TOTALS].bytes_algorithmic += (int64_t) 24 * n_buckets;
   if (!n_keep) { out->status = TJB_NO_HT_AFTER_QC; return 0; }
-  TRY (ensure (ctx, ctx->krec, (size_t) n_keep * W * 8)); TRY (ensure (ctx, ctx->kcount, (size_t) n_keep * 4));
-  u64 *krec = (u64*) ctx->krec.p; int *kcount = (int*) ctx->kcount.p;
-  LAUNCH (K_RLE, (16 * W + 8) * (size_t) n_keep, (compact_kernel<W><<<nblk (n_dist, RED_THREADS), RED_THREADS, 0, st>>> ((u64*) ctx->drec.p, (int*) ctx->dcount.p, (u32*) ctx->keep.p, (u32*) ctx->kpos.p, n_dist, krec, kcount)));
-
-  // 3. context groups above min coverage (:388-413); heads/pos/seg are free again (n_keep <= n)
-  TRY (ensure (ctx, ctx->cw, (size_t) n_keep * 4)); TRY (ensure (ctx, ctx->csum, (size_t) n_keep * 4));
-  TRY (ensure (ctx, ctx->gkeep, (size_t) n_keep * 4)); TRY (ensure (ctx, ctx->gkpos, (size_t) n_keep * 4));
-  LAUNCH (K_GROUP, 16 * W * (size_t) n_keep, (head_kernel<W, 1><<<nblk (n_keep, RED_THREADS), RED_THREADS, 0, st>>> (krec, n_keep, heads)));
-  TRY (exclusive_scan (ctx, heads, pos, n_keep, ptmp, ctx->d_totals + 0));
-  LAUNCH (K_GROUP, 12 * (size_t) n_keep, (seg_start_kernel<<<nblk (n_keep, RED_THREADS), RED_THREADS, 0, st>>> (heads, pos, n_keep, seg)));
-  LAUNCH (K_GROUP, 8 * (size_t) n_keep, (icopy_kernel<<<nblk (n_keep, RED_THREADS), RED_THREADS, 0, st>>> (kcount, n_keep, (u32*) ctx->cw.p)));
-  TRY (exclusive_scan (ctx, (u32*) ctx->cw.p, (u32*) ctx->csum.p, n_keep, ptmp, ctx->d_totals + 2));
-  CU (cudaMemcpyAsync (h_tot, ctx->d_totals, 4, cudaMemcpyDeviceToHost, st));
-  CU (cudaStreamSynchronize (st));
-  const u32 n_groups = h_tot[0];
-  LAUNCH (K_GROUP, 12 * (size_t) n_groups, (group_keep_kernel<<<nblk (n_groups, RED_THREADS), RED_THREADS, 0, st>>> (seg, n_groups, n_keep, (u32*) ctx->csum.p, ctx->d_totals + 2, opt->min_coverage, (u32*) ctx->gkeep.p)));
-  TRY (exclusive_scan (ctx, (u32*) ctx->gkeep.p, (u32*) ctx->gkpos.p, n_groups, ptmp, ctx->d_totals + 3));
-  CU (cudaMemcpyAsync (h_tot, ctx->d_totals + 3, 4, cudaMemcpyDeviceToHost, st));
-  CU (cudaStreamSynchronize (st));
-  const u32 n_idx = h_tot[0];
   if (!n_idx) { out->status = TJB_NO_CTX_ABOVE_COVERAGE; return 0; }
-  TRY (ensure (ctx, ctx->idx_i, (size_t) n_idx * 4)); TRY (ensure (ctx, ctx->idx_f, (size_t) n_idx * 4));
-  LAUNCH (K_GROUP, 16 * (size_t) n_groups, (group_emit_kernel<<<nblk (n_groups, RED_THREADS), RED_THREADS, 0, st>>> (seg, (u32*) ctx->gkeep.p, (u32*) ctx->gkpos.p, n_groups, n_keep, (int*) ctx->idx_i.p, (int*) ctx->idx_f.p)));
 
-  // 4. coverage (:420-438)
-  const u32 n2 = 2 * n_keep;
-  TRY (ensure (ctx, ctx->pairs_a, (size_t) n2 * 8)); TRY (ensure (ctx, ctx->pairs_b, (size_t) n2 * 8));
-  TRY (ensure (ctx, ctx->heads, (size_t) n2 * 4)); TRY (ensure (ctx, ctx->pos, (size_t) n2 * 4)); TRY (ensure (ctx, ctx->seg, (size_t) n2 * 4));
-  TRY (ensure (ctx, ctx->cw, (size_t) n2 * 4)); TRY (ensure (ctx, ctx->csum, (size_t) n2 * 4));
-  heads = (u32*) ctx->heads.p; pos = (u32*) ctx->pos.p; seg = (u32*) ctx->seg.p;
-  LAUNCH (K_COVERAGE, (8 * W + 4 + 16) * (size_t) n_keep, (cov_pairs_kernel<W><<<nblk (n_keep, RED_THREADS), RED_THREADS, 0, st>>> (krec, kcount, n_keep, k, (u64*) ctx->pairs_a.p)));
-  std::vector<DigitDesc> cdig;
-  add_digits (cdig, 0, 32, 31);
-  u64 *psorted = nullptr;
-  TRY ((radix_sort<1> (ctx, (u64*) ctx->pairs_a.p, (u64*) ctx->pairs_b.p, n2, cdig, &psorted)));
-  ptmp = (u32*) ctx->ptmp.p;
-  LAUNCH (K_COVERAGE, 20 * (size_t) n2, (head_kernel<1, 2><<<nblk (n2, RED_THREADS), RED_THREADS, 0, st>>> (psorted, n2, heads)));
-  TRY (exclusive_scan (ctx, heads, pos, n2, ptmp, ctx->d_totals + 0));
-  LAUNCH (K_COVERAGE, 12 * (size_t) n2, (seg_start_kernel<<<nblk (n2, RED_THREADS), RED_THREADS, 0, st>>> (heads, pos, n2, seg)));
-  LAUNCH (K_COVERAGE, 12 * (size_t) n2, (lo32_kernel<<<nblk (n2, RED_THREADS), RED_THREADS, 0, st>>> (psorted, n2, (u32*) ctx->cw.p)));
-  TRY (exclusive_scan (ctx, (u32*) ctx->cw.p, (u32*) ctx->csum.p, n2, ptmp, ctx->d_totals + 2));
+  // ---- reference-layout elements, global group indices, coverage (:420-438) ---------------------------------
+  u32 slots = 1024;
+  while (slots < 4u * n_keep) slots <<= 1; // two keys per record, load factor <= 0.5
+  TRY (ensure (ctx, ctx->cov_tab, (size_t) slots * 8));
+  TRY (ensure (ctx, ctx->out40, (size_t) n_keep * 40)); TRY (ensure (ctx, ctx->idx_i, (size_t) n_idx * 4)); TRY (ensure (ctx, ctx->idx_f, (size_t) n_idx * 4));
+  u32 *cov_keys = (u32*) ctx->cov_tab.p, *cov_vals = cov_keys + slots;
+  CU (cudaMemsetAsync (cov_keys, 0xff, (size_t) slots * 4, st));
+  CU (cudaMemsetAsync (cov_vals, 0, (size_t) slots * 4, st));
   int cov_init = INT_MIN;
   CU (cudaMemcpyAsync (ctx->d_cov, &cov_init, 4, cudaMemcpyHostToDevice, st));
-  CU (cudaMemcpyAsync (h_tot, ctx->d_totals, 4, cudaMemcpyDeviceToHost, st));
-  CU (cudaStreamSynchronize (st));
-  const u32 n_cseg = h_tot[0];
-  LAUNCH (K_COVERAGE, 12 * (size_t) n_cseg, (cov_max_kernel<<<nblk (n_cseg, RED_THREADS), RED_THREADS, 0, st>>> (seg, n_cseg, n2, (u32*) ctx->csum.p, ctx->d_totals + 2, ctx->d_cov)));
-
-  // 5. reference-layout elements + copy out into malloc'ed host memory (the reference free()s these)
-  TRY (ensure (ctx, ctx->out40, (size_t) n_keep * 40));
-  LAUNCH (K_PACK, (8 * W + 4 + 40) * (size_t) n_keep, (pack_hopo_kernel<W><<<nblk (n_keep, RED_THREADS), RED_THREADS, 0, st>>> (krec, kcount, n_keep, k, (u64*) ctx->out40.p)));
+  LAUNCH (K_PACK, (8 * W + 4 + 40) * (size_t) n_keep + 16 * (size_t) n_idx,
+          (pack_kernel<W><<<nblk (n_buckets, 8), 256, 0, st>>> (rec_a, (u32*) ctx->out_cnt.p, (u32*) ctx->out_ii.p, (u32*) ctx->out_if.p, ctx->d_bkt_start, ctx->d_bstat, ctx->d_koff, ctx->d_ioff, ctx->d_meta, k, (u64*) ctx->out40.p, (int*) ctx->idx_i.p, (int*) ctx->idx_f.p, cov_keys, cov_vals, slots - 1)));
+  LAUNCH (K_COVMAX, 8 * (size_t) slots, (cov_max_kernel<<<nblk (slots, 256 * 8), 256, 0, st>>> (cov_keys, cov_vals, slots, ctx->d_cov)));
+  CU (cudaGetLastError ());
+  // copy out into malloc'ed host memory (the reference free()s these)
   out->elem = malloc ((size_t) n_keep * 40);
   out->idx_initial = (int32_t*) malloc ((size_t) n_idx * 4);
   out->idx_final = (int32_t*) malloc ((size_t) n_idx * 4);
@@ -349,7 +433,7 @@ static int finalise_t (tjb_ctx *ctx, const tjb_opts *opt, tjb_counter_out *out)
   CU (cudaMemcpyAsync (out->idx_initial, ctx->idx_i.p, (size_t) n_idx * 4, cudaMemcpyDeviceToHost, st));
   CU (cudaMemcpyAsync (out->idx_final, ctx->idx_f.p, (size_t) n_idx * 4, cudaMemcpyDeviceToHost, st));
   CU (cudaMemcpyAsync (&cov, ctx->d_cov, 4, cudaMemcpyDeviceToHost, st));
-  CU (cudaStreamSynchronize (st));
+  CU (cudaStreamSynchronize (st)); // ---- synchronisation 2
   out->n_elem = (int32_t) n_keep;
   out->n_idx = (int32_t) n_idx;
   out->coverage = cov;
@@ -357,9 +441,14 @@ static int finalise_t (tjb_ctx *ctx, const tjb_opts *opt, tjb_counter_out *out)
   return 0;
 }
 
+#define TJB_INTERNAL_RETRY 100 // the record array overflowed; ctx->h_sync[0] holds the number of records needed
+
 static int finalise (tjb_ctx *ctx, const tjb_opts *opt, tjb_counter_out *out)
 {
-  int rc = ctx->rec_words == 2 ? finalise_t<2> (ctx, opt, out) : finalise_t<3> (ctx, opt, out);
+  bool overflow = false;
+  int rc = ctx->rec_words == 2 ? finalise_t<2> (ctx, opt, out, &overflow) : finalise_t<3> (ctx, opt, out, &overflow);
+  ctx->pend = false;
+  if (rc == 0 && overflow) return TJB_INTERNAL_RETRY;
   if (rc == 0) {
     // scan wrote 8W bytes per record on top of the sequence bytes it read
     ctx->stats[K_SCAN].bytes_algorithmic += (int64_t) out->n_raw * 8 * ctx->rec_words;
@@ -419,7 +508,23 @@ int tjb_ctx_create (int device, tjb_ctx **pctx)
   if ((e = cudaMalloc (&ctx->d_counters, 2 * sizeof (unsigned long long))) != cudaSuccess) return fail (e);
   if ((e = cudaMalloc (&ctx->d_totals, 16 * sizeof (u32))) != cudaSuccess) return fail (e);
   if ((e = cudaMalloc (&ctx->d_cov, sizeof (int))) != cudaSuccess) return fail (e);
+  if ((e = cudaStreamCreateWithFlags (&ctx->copy_stream, cudaStreamNonBlocking)) != cudaSuccess) return fail (e);
+  if ((e = cudaMalloc (&ctx->d_bin_hist, TJB_MAX_BINS * sizeof (u32))) != cudaSuccess) return fail (e);
+  if ((e = cudaMalloc (&ctx->d_bkt_start, (TJB_MAX_BINS + 1) * sizeof (u32))) != cudaSuccess) return fail (e);
+  if ((e = cudaMalloc (&ctx->d_cursor, TJB_MAX_BINS * sizeof (u32))) != cudaSuccess) return fail (e);
+  if ((e = cudaMalloc (&ctx->d_koff, TJB_MAX_BINS * sizeof (u32))) != cudaSuccess) return fail (e);
+  if ((e = cudaMalloc (&ctx->d_ioff, TJB_MAX_BINS * sizeof (u32))) != cudaSuccess) return fail (e);
+  if ((e = cudaMalloc (&ctx->d_lut, TJB_MAX_BINS * sizeof (unsigned short))) != cudaSuccess) return fail (e);
+  if ((e = cudaMalloc (&ctx->d_bstat, TJB_MAX_BINS * sizeof (uint4))) != cudaSuccess) return fail (e);
+  if ((e = cudaMalloc (&ctx->d_meta, META_WORDS * sizeof (u32))) != cudaSuccess) return fail (e);
+  if ((e = cudaMallocHost ((void**) &ctx->h_sync, 16 * sizeof (unsigned long long))) != cudaSuccess) return fail (e);
+  if ((e = cudaFuncSetAttribute (tjb_scan_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) scan_smem_bytes<2> ())) != cudaSuccess) return fail (e);
+  if ((e = cudaFuncSetAttribute (tjb_scan_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) scan_smem_bytes<3> ())) != cudaSuccess) return fail (e);
+  if ((e = cudaFuncSetAttribute (bucket_reduce_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) bucket_smem_bytes<2> ())) != cudaSuccess) return fail (e);
+  if ((e = cudaFuncSetAttribute (bucket_reduce_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) bucket_smem_bytes<3> ())) != cudaSuccess) return fail (e);
   cudaEventCreate (&ctx->ev_t0); cudaEventCreate (&ctx->ev_t1);
+  cudaEventCreateWithFlags (&ctx->ev_ready, cudaEventDisableTiming);
+  for (int i = 0; i < 2; i++) { cudaEventCreateWithFlags (&ctx->ev_copied[i], cudaEventDisableTiming); cudaEventCreateWithFlags (&ctx->ev_scanned[i], cudaEventDisableTiming); }
   *pctx = ctx;
   return 0;
 }
@@ -433,12 +538,18 @@ void tjb_ctx_destroy (tjb_ctx *ctx)
   for (cudaEvent_t e : ctx->free_events) cudaEventDestroy (e);
   DevBuf *bufs[] = {&ctx->d_chunk[0], &ctx->d_chunk[1], &ctx->rec_a, &ctx->rec_b, &ctx->hist, &ctx->ptmp, &ctx->heads, &ctx->pos, &ctx->seg,
                     &ctx->drec, &ctx->dcount, &ctx->keep, &ctx->kpos, &ctx->krec, &ctx->kcount, &ctx->cw, &ctx->csum, &ctx->gkeep,
-                    &ctx->gkpos, &ctx->pairs_a, &ctx->pairs_b, &ctx->out40, &ctx->idx_i, &ctx->idx_f};
+                    &ctx->gkpos, &ctx->out40, &ctx->idx_i, &ctx->idx_f, &ctx->out_cnt, &ctx->out_ii, &ctx->out_if, &ctx->cov_tab};
   for (DevBuf *b : bufs) if (b->p) cudaFree (b->p);
   for (int i = 0; i < 2; i++) { if (ctx->h_pinned[i]) cudaFreeHost (ctx->h_pinned[i]); if (ctx->h_free[i]) cudaEventDestroy (ctx->h_free[i]); }
   if (ctx->d_counters) cudaFree (ctx->d_counters);
   if (ctx->d_totals) cudaFree (ctx->d_totals);
   if (ctx->d_cov) cudaFree (ctx->d_cov);
+  void *small[] = {ctx->d_bin_hist, ctx->d_bkt_start, ctx->d_cursor, ctx->d_koff, ctx->d_ioff, ctx->d_lut, ctx->d_bstat, ctx->d_meta};
+  for (void *q : small) if (q) cudaFree (q);
+  if (ctx->h_sync) cudaFreeHost (ctx->h_sync);
+  if (ctx->copy_stream) { cudaStreamSynchronize (ctx->copy_stream); cudaStreamDestroy (ctx->copy_stream); }
+  if (ctx->ev_ready) cudaEventDestroy (ctx->ev_ready);
+  for (int i = 0; i < 2; i++) { if (ctx->ev_copied[i]) cudaEventDestroy (ctx->ev_copied[i]); if (ctx->ev_scanned[i]) cudaEventDestroy (ctx->ev_scanned[i]); }
   if (ctx->ev_t0) cudaEventDestroy (ctx->ev_t0);
   if (ctx->ev_t1) cudaEventDestroy (ctx->ev_t1);
   if (ctx->stream) cudaStreamDestroy (ctx->stream);
@@ -470,11 +581,19 @@ int tjb_count_sample_device (tjb_ctx *ctx, const void *d_seqs, size_t n_bytes, c
 {
   if (!ctx || !out || (n_bytes && !d_seqs)) return TJB_ERR_ARG;
   if (((uintptr_t) d_seqs) & 15) { ctx->err = "device buffer must be 16-byte aligned"; return TJB_ERR_ARG; }
-  out_reset (out);
-  TRY (begin_sample (ctx, opt));
-  CU (cudaEventRecord (ctx->ev_t0, ctx->stream));
-  TRY (scan_chunk (ctx, (const uint8_t*) d_seqs, n_bytes, opt));
-  int rc = finalise (ctx, opt, out);
+  size_t want = n_bytes / 16 + 65536; // records; the scan counts what does not fit, then the sample is redone
+  int rc = 0;
+  for (int attempt = 0; attempt < 3; attempt++) {
+    out_reset (out);
+    TRY (begin_sample (ctx, opt, n_bytes));
+    CU (cudaEventRecord (ctx->ev_t0, ctx->stream));
+    TRY (grow_records (ctx, want));
+    TRY (launch_scan (ctx, (const uint8_t*) d_seqs, n_bytes, opt));
+    rc = finalise (ctx, opt, out);
+    if (rc != TJB_INTERNAL_RETRY) break;
+    want = (size_t) ctx->h_sync[0] + 1024;
+  }
+  if (rc == TJB_INTERNAL_RETRY) { ctx->err = "record array overflow persisted"; return TJB_ERR_CUDA; }
   if (rc < 0) return rc;
   CU (cudaEventRecord (ctx->ev_t1, ctx->stream));
   CU (cudaEventSynchronize (ctx->ev_t1));
@@ -492,25 +611,43 @@ static size_t whole_reads_prefix (const uint8_t *p, size_t len, size_t remaining
   return nl ? (size_t) ((const uint8_t*) nl - p) + 1 : 0;
 }
 
+// Host buffer: chunks are copied on the context's copy stream while the previous chunk is scanned on the compute
+// stream (two device chunk buffers); one optimistic pass, redone with the exact record capacity after an overflow.
 int tjb_count_sample_host (tjb_ctx *ctx, const uint8_t *seqs, size_t n_bytes, const tjb_opts *opt, tjb_counter_out *out)
 {
   if (!ctx || !out || (n_bytes && !seqs)) return TJB_ERR_ARG;
-  out_reset (out);
-  TRY (begin_sample (ctx, opt));
-  CU (cudaEventRecord (ctx->ev_t0, ctx->stream));
-  const size_t max_chunk = 512u << 20;
-  size_t off = 0;
-  int which = 0;
-  while (off < n_bytes) {
-    size_t len = whole_reads_prefix (seqs + off, max_chunk < n_bytes - off ? max_chunk : n_bytes - off, n_bytes - off);
-    if (!len) { ctx->err = "a single read exceeds the chunk size"; return TJB_ERR_TOO_LARGE; }
-    TRY (ensure (ctx, ctx->d_chunk[which], (len + 15) & ~(size_t) 15));
-    CU (cudaMemcpyAsync (ctx->d_chunk[which].p, seqs + off, len, cudaMemcpyHostToDevice, ctx->stream));
-    TRY (scan_chunk (ctx, (const uint8_t*) ctx->d_chunk[which].p, len, opt));
-    off += len;
-    which ^= 1;
+  const size_t max_chunk = TJB_HOST_CHUNK_BYTES;
+  size_t want = n_bytes / 16 + 65536;
+  int rc = 0;
+  for (int attempt = 0; attempt < 3; attempt++) {
+    out_reset (out);
+    TRY (begin_sample (ctx, opt, n_bytes));
+    CU (cudaEventRecord (ctx->ev_t0, ctx->stream));
+    TRY (grow_records (ctx, want));
+    for (int i = 0; i < 2; i++) TRY (ensure (ctx, ctx->d_chunk[i], (max_chunk < n_bytes ? max_chunk : n_bytes) + 16));
+    CU (cudaEventRecord (ctx->ev_ready, ctx->stream));            // workspace set up / previous sample done
+    CU (cudaStreamWaitEvent (ctx->copy_stream, ctx->ev_ready, 0));
+    size_t off = 0;
+    int which = 0;
+    bool used[2] = {false, false};
+    while (off < n_bytes) {
+      size_t len = whole_reads_prefix (seqs + off, max_chunk < n_bytes - off ? max_chunk : n_bytes - off, n_bytes - off);
+      if (!len) { ctx->err = "a single read exceeds the chunk size"; return TJB_ERR_TOO_LARGE; }
+      if (used[which]) CU (cudaStreamWaitEvent (ctx->copy_stream, ctx->ev_scanned[which], 0)); // buffer free again
+      CU (cudaMemcpyAsync (ctx->d_chunk[which].p, seqs + off, len, cudaMemcpyHostToDevice, ctx->copy_stream));
+      CU (cudaEventRecord (ctx->ev_copied[which], ctx->copy_stream));
+      CU (cudaStreamWaitEvent (ctx->stream, ctx->ev_copied[which], 0));
+      TRY (launch_scan (ctx, (const uint8_t*) ctx->d_chunk[which].p, len, opt));
+      CU (cudaEventRecord (ctx->ev_scanned[which], ctx->stream));
+      used[which] = true;
+      off += len;
+      which ^= 1;
+    }
+    rc = finalise (ctx, opt, out);
+    if (rc != TJB_INTERNAL_RETRY) break;
+    want = (size_t) ctx->h_sync[0] + 1024;
   }
-  int rc = finalise (ctx, opt, out);
+  if (rc == TJB_INTERNAL_RETRY) { ctx->err = "record array overflow persisted"; return TJB_ERR_CUDA; }
   if (rc < 0) return rc;
   CU (cudaEventRecord (ctx->ev_t1, ctx->stream));
   CU (cudaEventSynchronize (ctx->ev_t1));
@@ -524,7 +661,7 @@ int tjb_count_sample_files (tjb_ctx *ctx, const char *const *files, int n_files,
 {
   if (!ctx || !out || !files || n_files < 1 || n_files > 2) return TJB_ERR_ARG;
   out_reset (out);
-  TRY (begin_sample (ctx, opt));
+  TRY (begin_sample (ctx, opt, 0));
   for (int i = 0; i < 2; i++) {
     if (!ctx->h_pinned[i]) CU (cudaMallocHost ((void**) &ctx->h_pinned[i], TJB_CHUNK_BYTES));
     if (!ctx->h_free[i]) CU (cudaEventCreateWithFlags (&ctx->h_free[i], cudaEventDisableTiming));
