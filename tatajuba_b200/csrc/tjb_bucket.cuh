@@ -179,7 +179,22 @@ partition_kernel (const u64 *__restrict__ in, u64 *__restrict__ out, const unsig
 template <int W> constexpr size_t bucket_smem_bytes ()
 {
   return (size_t) W * BK_CAP * 8 /* s_w */ + 2 * BK_CAP * 2 /* perm */ + BK_WARPS * 256 * 2 /* counts */ + BK_CAP * 2 /* aux */ +
-         BK_CAP * 4 /* val */ + BK_CAP * 4 /* sum */;
+         BK_CAP * 4 /* val */ + BK_CAP * 4 /* sum */ + BK_CAP * 4 /* per-record strand counts */;
+}
+#define BK_EMPTY 0xffffffffu
+#define BK_RANKSORT_MAX 128 // up to this many distinct keys a bucket is ordered by comparison counting instead of radix passes
+
+// a > b in the reference's order (base, ctx0, ctx1, length), hopo_counter.c:28-38; the flag bits do not take part
+template <int W> __device__ __forceinline__ bool rec_greater (const Rec<W> &a, const Rec<W> &b);
+template <> __device__ __forceinline__ bool rec_greater<2> (const Rec<2> &a, const Rec<2> &b)
+{ return a.w[1] != b.w[1] ? a.w[1] > b.w[1] : (a.w[0] >> 2) > (b.w[0] >> 2); }
+template <> __device__ __forceinline__ bool rec_greater<3> (const Rec<3> &a, const Rec<3> &b)
+{
+  const u64 ba = (a.w[0] >> 12) & 1, bb = (b.w[0] >> 12) & 1;
+  if (ba != bb) return ba > bb;
+  if (a.w[2] != b.w[2]) return a.w[2] > b.w[2];
+  if (a.w[1] != b.w[1]) return a.w[1] > b.w[1];
+  return ((a.w[0] >> 2) & 0x3ff) > ((b.w[0] >> 2) & 0x3ff);
 }
 
 template <int W>
@@ -197,6 +212,9 @@ bucket_reduce_kernel (const u64 *__restrict__ recs, const u32 *__restrict__ bkt_
   unsigned short *s_aux = s_cnt + BK_WARPS * 256;                            // [BK_CAP]
   u32 *s_val = reinterpret_cast<u32*> (s_aux + BK_CAP);                      // [BK_CAP]
   u32 *s_sum = s_val + BK_CAP;                                               // [BK_CAP]
+  u32 *s_tab = s_val;                                                        // [2 * BK_CAP] de-duplication hash table; dead before
+                                                                             // s_val / s_sum are first written
+  u32 *s_cntrec = s_sum + BK_CAP;                                            // [BK_CAP] fwd count | rev count << 16 of a representative
   __shared__ u32 s_warp[BK_WARPS + 1];
   __shared__ u32 s_bucket;
   __shared__ u32 s_diff[2 * W];
@@ -230,7 +248,6 @@ bucket_reduce_kernel (const u64 *__restrict__ recs, const u32 *__restrict__ bkt_
         Rec<W> r = load_rec<W> (recs, (size_t) start + i);
 #pragma unroll
         for (int j = 0; j < W; j++) { s_w[j * BK_CAP + i] = r.w[j]; d[j] |= r.w[j] ^ f.w[j]; }
-        s_perm0[i] = (unsigned short) i;
       }
 #pragma unroll
       for (int j = 0; j < W; j++) {
@@ -239,79 +256,122 @@ bucket_reduce_kernel (const u64 *__restrict__ recs, const u32 *__restrict__ bkt_
       }
     }
     __syncthreads ();
-    // ---- LSD radix sort of the index permutation, ascending; digits on which the whole bucket agrees are skipped
+    // ---- de-duplication: at sequencing depth D every (base, ctx0, ctx1, length) shows up ~D times, so count the copies
+    // in a shared-memory hash table first (run-length count of hopo_counter.c:355-365 without the sort) and sort only
+    // the distinct observations.  Table entry = index of the first record seen with that key (its representative);
+    // s_cntrec[representative] = forward-strand copies | reverse-strand copies << 16 (canon_flag = which are non-zero, :362)
+    u32 tsize = 64;
+    while (tsize < 2 * n) tsize <<= 1;
+    for (u32 i = tid; i < tsize; i += BK_THREADS) s_tab[i] = BK_EMPTY;
+    for (u32 i = tid; i < n; i += BK_THREADS) s_cntrec[i] = 0;
+    __syncthreads ();
+    for (u32 i = tid; i < n; i += BK_THREADS) {
+      Rec<W> x;
+#pragma unroll
+      for (int j = 0; j < W; j++) x.w[j] = s_w[j * BK_CAP + i];
+      u32 h = (u32) (x.w[0] >> 2) * 0x9E3779B1u ^ (u32) (x.w[0] >> 34) * 0x85EBCA6Bu ^ (u32) x.w[1] * 0xC2B2AE35u ^ (u32) (x.w[1] >> 32) * 0x27D4EB2Fu;
+      if (W == 3) h ^= (u32) x.w[W - 1] * 0x165667B1u ^ (u32) (x.w[W - 1] >> 32) * 0x9E3779B1u;
+      h ^= h >> 15; h *= 0x2C1B3C6Du; h ^= h >> 13;
+      u32 slot = h & (tsize - 1), rep;
+      for (;;) {
+        u32 c = s_tab[slot];
+        if (c == BK_EMPTY) { c = atomicCAS (&s_tab[slot], BK_EMPTY, i); if (c == BK_EMPTY) { rep = i; break; } }
+        Rec<W> y;
+#pragma unroll
+        for (int j = 0; j < W; j++) y.w[j] = s_w[j * BK_CAP + c];
+        if (same_tract<W> (x, y)) { rep = c; break; }
+        slot = (slot + 1) & (tsize - 1);
+      }
+      atomicAdd (&s_cntrec[rep], (x.w[0] & 1) ? 1u : 0x10000u); // flag 1 = forward, 2 = reverse complement
+    }
+    __syncthreads ();
+    u32 n_dist;
+    { // representatives -> s_perm0[0 .. n_dist)
+      const u32 per = tsize / BK_THREADS ? tsize / BK_THREADS : 1, t0 = tid * per;
+      u32 cnt = 0;
+      for (u32 i = t0; i < t0 + per && i < tsize; i++) cnt += s_tab[i] != BK_EMPTY;
+      u32 pos = blk_excl_scan<BK_THREADS> (cnt, s_warp, &n_dist);
+      for (u32 i = t0; i < t0 + per && i < tsize; i++) { const u32 c = s_tab[i]; if (c != BK_EMPTY) s_perm0[pos++] = (unsigned short) c; }
+    }
+    __syncthreads ();
+    // ---- sort the distinct observations, ascending in `cur` ------------------------------------------------------
     unsigned short *cur = s_perm0, *nxt = s_perm1;
-    for (int q = 0; q < dl.n; q++) {
-      const int word = dl.word[q], shift = dl.shift[q];
-      const u32 mask = (1u << dl.nbits[q]) - 1;
-      const int half = shift >> 5, sh = shift & 31;
-      if (((s_diff[2 * word + half] >> sh) & mask) == 0) continue;
-      for (int i = tid; i < BK_WARPS * 256 / 2; i += BK_THREADS) reinterpret_cast<u32*> (s_cnt)[i] = 0;
-      __syncthreads ();
-      u32 idx[BK_IPT], dig[BK_IPT], rank[BK_IPT];
+    if (n_dist <= BK_RANKSORT_MAX) {
+      // few keys (the usual case at high depth): rank by comparison, one key per thread, broadcast reads
+      if ((u32) tid < n_dist) {
+        const u32 id = cur[tid];
+        Rec<W> x;
 #pragma unroll
-      for (int r = 0; r < BK_IPT; r++) {
-        const u32 i = (u32) wid * (32 * BK_IPT) + r * 32 + lane;
-        u32 d = 256, id = 0;
-        if (i < n) { id = cur[i]; d = (s_w32[2 * ((size_t) word * BK_CAP + id) + half] >> sh) & mask; }
-        idx[r] = id; dig[r] = d;
-        const u32 peers = __match_any_sync (0xffffffffu, d);
-        const int leader = __ffs (peers) - 1;
-        u32 old = 0;
-        if (lane == leader && d < 256) { old = s_cnt[wid * 256 + d]; s_cnt[wid * 256 + d] = (unsigned short) (old + __popc (peers)); }
-        old = __shfl_sync (0xffffffffu, old, leader);
-        rank[r] = old + __popc (peers & lt_mask);
-        __syncwarp ();
+        for (int j = 0; j < W; j++) x.w[j] = s_w[j * BK_CAP + id];
+        u32 less = 0;
+        for (u32 o = 0; o < n_dist; o++) {
+          const u32 oid = cur[o];
+          Rec<W> y;
+#pragma unroll
+          for (int j = 0; j < W; j++) y.w[j] = s_w[j * BK_CAP + oid];
+          less += rec_greater<W> (x, y);
+        }
+        nxt[less] = (unsigned short) id;
       }
-      __syncthreads ();
-      { // thread t owns digit t: offsets in (digit-major, warp-minor) order
-        u32 c[BK_WARPS], sum = 0;
-#pragma unroll
-        for (int w = 0; w < BK_WARPS; w++) { c[w] = s_cnt[w * 256 + tid]; sum += c[w]; }
-        u32 tot;
-        u32 ex = blk_excl_scan<BK_THREADS> (sum, s_warp, &tot);
-#pragma unroll
-        for (int w = 0; w < BK_WARPS; w++) { s_cnt[w * 256 + tid] = (unsigned short) ex; ex += c[w]; }
-      }
-      __syncthreads ();
-#pragma unroll
-      for (int r = 0; r < BK_IPT; r++)
-        if (dig[r] < 256) nxt[s_cnt[wid * 256 + dig[r]] + rank[r]] = (unsigned short) idx[r];
       __syncthreads ();
       unsigned short *t = cur; cur = nxt; nxt = t;
+    } else {
+      // LSD radix sort of the index permutation; digits on which the whole bucket agrees are skipped
+      const u32 ipt = (n_dist + BK_THREADS - 1) / BK_THREADS; // items per thread in a pass
+      for (int q = 0; q < dl.n; q++) {
+        const int word = dl.word[q], shift = dl.shift[q];
+        const u32 mask = (1u << dl.nbits[q]) - 1;
+        const int half = shift >> 5, sh = shift & 31;
+        if (((s_diff[2 * word + half] >> sh) & mask) == 0) continue;
+        for (int i = tid; i < BK_WARPS * 256 / 2; i += BK_THREADS) reinterpret_cast<u32*> (s_cnt)[i] = 0;
+        __syncthreads ();
+#pragma unroll 1
+        for (u32 r = 0; r < ipt; r++) { // warp w owns items [w * 32 * ipt, (w + 1) * 32 * ipt): stable
+          const u32 i = (u32) wid * (32 * ipt) + r * 32 + lane;
+          u32 d = 256;
+          if (i < n_dist) d = (s_w32[2 * ((size_t) word * BK_CAP + cur[i]) + half] >> sh) & mask;
+          const u32 peers = __match_any_sync (0xffffffffu, d);
+          const int leader = __ffs (peers) - 1;
+          u32 old = 0;
+          if (lane == leader && d < 256) { old = s_cnt[wid * 256 + d]; s_cnt[wid * 256 + d] = (unsigned short) (old + __popc (peers)); }
+          old = __shfl_sync (0xffffffffu, old, leader);
+          if (i < n_dist) s_aux[i] = (unsigned short) (old + __popc (peers & lt_mask)); // rank among the warp's equal digits
+          __syncwarp ();
+        }
+        __syncthreads ();
+        { // thread t owns digit t: offsets in (digit-major, warp-minor) order
+          u32 c[BK_WARPS], sum = 0;
+#pragma unroll
+          for (int w = 0; w < BK_WARPS; w++) { c[w] = s_cnt[w * 256 + tid]; sum += c[w]; }
+          u32 tot;
+          u32 ex = blk_excl_scan<BK_THREADS> (sum, s_warp, &tot);
+#pragma unroll
+          for (int w = 0; w < BK_WARPS; w++) { s_cnt[w * 256 + tid] = (unsigned short) ex; ex += c[w]; }
+        }
+        __syncthreads ();
+#pragma unroll 1
+        for (u32 r = 0; r < ipt; r++) {
+          const u32 i = (u32) wid * (32 * ipt) + r * 32 + lane;
+          if (i < n_dist) {
+            const u32 id = cur[i], d = (s_w32[2 * ((size_t) word * BK_CAP + id) + half] >> sh) & mask;
+            nxt[s_cnt[wid * 256 + d] + s_aux[i]] = (unsigned short) id;
+          }
+        }
+        __syncthreads ();
+        unsigned short *t = cur; cur = nxt; nxt = t;
+      }
     }
-    // record at DESCENDING position p
+    // distinct record at DESCENDING position p
+    auto id_at = [&] (u32 p) -> u32 { return cur[n_dist - 1 - p]; };
     auto rec_at = [&] (u32 p) {
-      const u32 id = cur[n - 1 - p];
+      const u32 id = id_at (p);
       Rec<W> r;
 #pragma unroll
       for (int j = 0; j < W; j++) r.w[j] = s_w[j * BK_CAP + id];
       return r;
     };
-    // ---- S1: heads of runs of equal (base, ctx0, ctx1, length)  (hopo_counter.c:355-365) ------------------
-    u32 n_dist, n_keep, n_groups, n_idx, ctotal;
-    {
-      const u32 p0 = tid * BK_IPT;
-      u32 hmask = 0;
-      if (p0 < n) {
-        Rec<W> prev;
-        if (p0) prev = rec_at (p0 - 1);
-#pragma unroll
-        for (int r = 0; r < BK_IPT; r++) {
-          const u32 p = p0 + r;
-          if (p < n) {
-            Rec<W> x = rec_at (p);
-            if (p == 0 || !same_tract<W> (x, prev)) hmask |= 1u << r;
-            prev = x;
-          }
-        }
-      }
-      u32 dpos = blk_excl_scan<BK_THREADS> (__popc (hmask), s_warp, &n_dist);
-#pragma unroll
-      for (int r = 0; r < BK_IPT; r++) if ((hmask >> r) & 1) s_aux[dpos++] = (unsigned short) (p0 + r);
-    }
-    __syncthreads ();
-    // ---- S2: count, canon_flag (first | last: the flag is the lowest sort digit), QC filter (:367-374) ----
+    u32 n_keep, n_groups, n_idx, ctotal;
+    // ---- S2: count, canon_flag, QC filter (hopo_counter.c:361-362, 367-374) ----------------------------------
     {
       const u32 d0 = tid * BK_IPT;
       u32 kmask = 0, packed[BK_IPT];
@@ -319,13 +379,12 @@ bucket_reduce_kernel (const u64 *__restrict__ recs, const u32 *__restrict__ bkt_
       for (int r = 0; r < BK_IPT; r++) {
         const u32 d = d0 + r;
         if (d < n_dist) {
-          const u32 s = s_aux[d], e = (d + 1 < n_dist) ? s_aux[d + 1] : n;
-          const u32 cnt = e - s; // <= BK_CAP: the 20-bit signed count field cannot wrap here
-          const u32 id_s = cur[n - 1 - s], id_e = cur[n - e];
-          const u32 flag = (u32) ((s_w[id_s] | s_w[id_e]) & 3);
+          const u32 c = s_cntrec[id_at (d)];
+          const u32 cnt = (c & 0xffff) + (c >> 16); // <= BK_CAP: the 20-bit signed count field cannot wrap here
+          const u32 flag = ((c & 0xffff) ? 1u : 0u) | ((c >> 16) ? 2u : 0u);
           const bool keep = remove_biased ? (flag == 3) : (cnt > 1);
           if (keep) kmask |= 1u << r;
-          packed[r] = s | (cnt << 12) | (flag << 28);
+          packed[r] = d | (cnt << 12) | (flag << 28);
         }
       }
       u32 kpos = blk_excl_scan<BK_THREADS> (__popc (kmask), s_warp, &n_keep);
