@@ -123,6 +123,19 @@ def _host_ptr(seqs):
     return C.c_void_p(seqs.data_ptr()), seqs.numel()
 
 
+class _OutOwner:
+    """keeps a tjb_counter_out alive while numpy views of its arrays exist; free()s it afterwards"""
+
+    def __init__(self, lib, out):
+        self.lib, self.out = lib, out
+
+    def __del__(self):
+        try:
+            self.lib.tjb_counter_out_free(C.byref(self.out))
+        except Exception:
+            pass
+
+
 class HopoCounter:
     """struct hopo_counter_struct at the BWA boundary (src/hopo_counter.h:51-59)"""
 
@@ -143,17 +156,21 @@ class HopoCounter:
         hc = cls(opt)
         hc.status = out.status
         hc.n_elem, hc.n_idx, hc.coverage = out.n_elem, out.n_idx, out.coverage
+        # zero-copy views of the malloc()'ed arrays; the owner frees them when the last view is gone
+        owner = _OutOwner(lib, out)
         if out.n_elem:
-            hc.elem = np.zeros(out.n_elem, dtype=HOPO_DTYPE)
-            C.memmove(hc.elem.ctypes.data, out.elem, 40 * out.n_elem)
+            raw = (C.c_uint8 * (40 * out.n_elem)).from_address(out.elem)
+            raw._owner = owner
+            hc.elem = np.ctypeslib.as_array(raw).view(HOPO_DTYPE)
         if out.n_idx:
-            hc.idx_initial = np.ctypeslib.as_array(out.idx_initial, (out.n_idx,)).copy()
-            hc.idx_final = np.ctypeslib.as_array(out.idx_final, (out.n_idx,)).copy()
+            for name in ("idx_initial", "idx_final"):
+                arr = (C.c_int32 * out.n_idx).from_address(C.addressof(getattr(out, name).contents))
+                arr._owner = owner
+                setattr(hc, name, np.ctypeslib.as_array(arr))
         hc.name = out.name.decode() if out.name else None
         for f in ("n_reads", "n_bases", "n_raw", "n_distinct", "n_skipped_nonacgt", "ms_decode", "ms_device"):
             setattr(hc, f, getattr(out, f))
         hc.finalised = True
-        lib.tjb_counter_out_free(C.byref(out))
         return hc
 
 
