@@ -241,11 +241,11 @@ static int begin_sample (tjb_ctx *ctx, const tjb_opts *opt, size_t n_bytes_hint)
 
 static int launch_scan (tjb_ctx *ctx, const uint8_t *d_seqs, size_t n, const tjb_opts *opt)
 {
-  long long n_tiles = (long long) ((n + SW_TILE - 1) / SW_TILE); // one 2 KiB tile per warp at a time
+  long long n_tiles = (long long) ((n + SW_TILE - 1) / SW_TILE); // one window of SW_TILE owned bytes per warp at a time
   if (!n_tiles) return 0;
   int min_len = opt->min_tract_size < 2 ? 2 : opt->min_tract_size;
   long long want = (n_tiles + SCAN_WARPS - 1) / SCAN_WARPS;
-  long long grid = want < (long long) ctx->sm_count * 4 ? want : (long long) ctx->sm_count * 4;
+  long long grid = want < (long long) ctx->sm_count * SCAN_CTAS_PER_SM ? want : (long long) ctx->sm_count * SCAN_CTAS_PER_SM;
   // algorithmic bytes of this launch: every sequence byte read once (+ 8W bytes per emitted record, added at finalise)
   if (ctx->rec_words == 2)
     LAUNCH (K_SCAN, n, (tjb_scan_kernel<2><<<(u32) grid, SCAN_THREADS, scan_smem_bytes<2> (), ctx->stream>>> (d_seqs, (long long) n, opt->kmer_size, min_len, (u64*) ctx->rec_a.p, ctx->rec_capacity, ctx->d_counters, n_tiles, ctx->d_bin_hist, ctx->bin_bits)));

@@ -4,50 +4,60 @@
 // 285-307), which walk one read at a time, byte by byte, on one CPU thread.  Here a whole chunk of reads
 // ("SEQ\nSEQ\n...", '\n' = read separator, written by csrc/tjb_fastq.c) is scanned by the full grid.
 //
-// The kernel is instruction-issue bound (the reads are touched once, at HBM speed), so (1) the common path works on
-// 32-bit words, and (2) every WARP is autonomous: it owns 2 KiB tiles, stages them with a 1-D bulk async copy
-// (cp.async.bulk -> UBLKCP, completion on a warp-private mbarrier, double buffered so that tile t+1 is in flight
-// while tile t is processed) and never meets another warp at a barrier.
+// The reads are touched once, at HBM speed, so the kernel is bound by the integer pipe (LOP3/SHF/PRMT issue at half
+// rate on sm_100): the design minimises ALU-pipe instructions per input byte and keeps every WARP autonomous.  A warp
+// owns windows of 2048 staged bytes (1952 owned + 32 left / 64 right halo), fetched by ONE 1-D bulk async copy
+// (cp.async.bulk -> UBLKCP) onto a warp-private mbarrier, double buffered; there is no block barrier after set-up.
 //
-//   phase A  per 512-byte row, every lane squeezes its 16 bytes into a 32-bit word of 2-bit "gray" codes,
-//            (byte >> 1) & 3 = A0 C1 T2 G3, with one AND + one multiply per 4 bytes.  Runs are detected on that word
-//            (funnel shifts against the neighbouring groups): a position is a CANDIDATE when min(max(m,2),4) equal
-//            codes start there and the previous code differs.  Equal bytes have equal codes, so every byte run of
-//            that length lies inside exactly one code run; code runs that are not byte runs (N next to G, '\n' next
-//            to C, lower case ...) are sorted out exactly in phase B.  Candidates are queued per warp (ballot
-//            compaction) and processed 32 at a time, one per lane;
-//   phase B  run end by word compares; both flanks are read as k bytes re-aligned with PRMT, validated against
-//            "ACTG"[code] (any other byte, the read separator included, shows up as a non-zero difference) and
-//            packed 4 bases per multiply; strand canonicalisation is a 64-bit bit reversal (hopo_counter.c:239-246).
-//            A flank holding a separator rejects the tract (the reference's s >= k and e <= L-k-1 rules, :229,
-//            :232).  Anything unusual (non-ACGT byte in the run or a flank, U, lower case, a run or flank leaving the
-//            staged window) takes the byte-exact slow path, which restates the reference loop literally.  Records
-//            are staged per warp and appended to the global array with one atomicAdd per ~50 records; the bin
-//            histogram of the partition plan (tjb_bucket.cuh) is accumulated here too.
+//   pass 1   every lane turns 16 bytes into (a) one 32-bit word of 2-bit "gray" codes (byte >> 1) & 3 = A0 C1 T2 G3
+//            (AND + one multiply per 4 bytes), (b) a 16-bit mask of non-letter bytes (bit 6 clear: the read
+//            separator; sign-replicating PRMT + two DP4A), (c) one "bad group" bit: some byte is neither one of
+//            "ACGT" nor looks like a separator (bytes re-derived from their codes by PRMT look-ups, two words per
+//            look-up, compared with a DP4A sum of squares).  The three derived arrays (codes 512 B, masks 256 B,
+//            bad bits 16 B per window) stay in shared memory, double buffered; everything after pass 1 works on them;
+//   pass 2   code-run starts (candidates: min(max(m,2),4) equal codes, previous code differs) by funnel shifts on the
+//            code words; one shuffle prefix sum per window compacts them into a per-warp FIFO that is carried over
+//            window boundaries, so phase B always runs on 32 candidates;
+//   phase B  one candidate per lane, no byte is touched: run end, both flanks (2k bits each) and the read-boundary
+//            test are funnel shifts over the derived arrays.  A separator anywhere in [s-k, e+k] rejects the tract
+//            (the reference's s >= k and e <= L-k-1 rules, hopo_counter.c:229, :232); a bad group in that span (N,
+//            lower case, U, IUPAC, a control byte ...), a run of 32+ codes or a non-letter that is not '\n' sends the
+//            candidate to the byte-exact slow path, which restates the reference loop literally.  Strand
+//            canonicalisation is a 64-bit bit reversal (:239-246).  Records are staged per warp and appended to the
+//            global array with one atomicAdd per ~50 records; the bin histogram of the partition plan
+//            (tjb_bucket.cuh) is accumulated here too.
 //
-// Tiles own the code runs that START inside them.
+// Windows own the code runs that START inside their owned bytes.
 #pragma once
 #include "tjb_common.cuh"
 #include "tjb_bucket.cuh" // rec_bin(): the scan also accumulates the bin histogram the partition plan is made from
 
-
 #define SCAN_WARPS 8
 #define SCAN_THREADS (SCAN_WARPS * 32)
-#define SW_TILE 2048                  // bytes owned by one warp tile
-#define SW_HALO_L 64                  // >= k + 4, multiple of 16
-#define SW_HALO_R 128
-#define SW_BYTES (SW_HALO_L + SW_TILE + SW_HALO_R)
-#define SW_ROWS (SW_TILE / 512)
-#define SW_QCAP 320                   // candidate queue: < 32 left over + at most 256 new per row
+#define SCAN_CTAS_PER_SM 3
+#define SW_WIN 2048                   // staged bytes per window = 128 groups of 16 = 4 rows of 32 lanes
+#define SW_HALO_L 32                  // >= k, multiple of 16
+#define SW_HALO_R 64                  // >= 31 (longest fast-path run) + k + 1
+#define SW_TILE (SW_WIN - SW_HALO_L - SW_HALO_R) // 1952 owned bytes
+#define SW_GROUPS (SW_WIN / 16)
+#define SW_G0 (SW_HALO_L / 16)        // owned groups [SW_G0, SW_G1)
+#define SW_G1 (SW_G0 + SW_TILE / 16)
+#define SW_ROWS (SW_GROUPS / 32)
+#define SW_RING 512                   // candidate FIFO (< 32 carried + at most 480 new per round)
 #define SW_RCAP 64                    // staged records per warp; flushed when more than SW_RCAP - 32 are pending
 #define SCAN_GRAY_MUL 0x00820820u     // ((w & 0x06060606) * this) >> 24 = the four 2-bit codes of w's bytes
 #define SCAN_GRAY_LUT 0x47544341u     // code -> byte: 'A' 'C' 'T' 'G'
+#define SCAN_LUT_A 0x00430041u        // PRMT look-up on (code << 1): bytes 0 / 2 = 'A' / 'C'
+#define SCAN_LUT_B 0x00470054u        //                              bytes 4 / 6 = 'T' / 'G'
 
 template <int W> struct ScanWarpSmem {
-  uint8_t raw[2][SW_BYTES + 16];      // two stages; 16 pad bytes read (never used) by the flank word loads
+  uint8_t raw[2][SW_WIN];             // two stages of sequence bytes
+  u32 codes[2][SW_GROUPS];            // 16 gray codes per word, byte j of the group in bits 2j..2j+1
+  u32 nl[2][SW_GROUPS / 2 + 4];       // bit i of the array = byte i of the window has bit 6 clear; 4 pad words
+  u32 bad[2][8];                      // bit g = group g holds a byte that is neither ACGT nor separator-like
   u64 rec[SW_RCAP * W];
   unsigned long long bar[2];          // mbarriers of the two stages
-  unsigned short cand[SW_QCAP];
+  unsigned short ring[SW_RING];       // candidates: stage << 11 | window offset of the code-run start
 };
 template <int W> constexpr size_t scan_smem_bytes () { return SCAN_WARPS * sizeof (ScanWarpSmem<W>) + 512; }
 
@@ -77,35 +87,21 @@ __device__ __forceinline__ void mbar_wait (unsigned long long *b, u32 parity)
   asm volatile ("{\n .reg .pred p;\n WAIT_%=:\n mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n @p bra DONE_%=;\n bra WAIT_%=;\n DONE_%=:\n}"
                 :: "r"(smem_u32 (b)), "r"(parity) : "memory");
 }
-
-// k bytes starting at shared-memory offset pos -> 2-bit gray codes, base j in bits 2j..2j+1.
-// bad != 0 when any of the k bytes is not one of "ACGT" (upper case); sep != 0 when one of them is the read separator.
-__device__ __forceinline__ u64 flank_gray (const u32 *raw32, int pos, int nw, u32 tail_mask, u32 &bad, u32 &sep)
+__device__ __forceinline__ int dp4a_su (u32 a_signed, u32 b_unsigned, int c)
 {
-  const int a = pos >> 2;
-  const u32 sel = 0x3210u + 0x1111u * (u32) (pos & 3);
-  u32 lo = 0, hi = 0, acc = 0, sacc = 0;
-  u32 w_lo = raw32[a];
-#pragma unroll
-  for (int j = 0; j < 8; j++) {
-    if (j >= nw) break;
-    const u32 w_hi = raw32[a + j + 1];
-    const u32 w = __byte_perm (w_lo, w_hi, sel);
-    w_lo = w_hi;
-    u32 m = w & 0x06060606u;
-    const u32 y = m >> 1, t = y | (y >> 4);
-    u32 d = w ^ __byte_perm (SCAN_GRAY_LUT, 0, __byte_perm (t, 0, 0x4420));
-    const u32 x = w ^ 0x0A0A0A0Au;
-    u32 z = ~(((x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | x) & 0x80808080u;
-    if (j == nw - 1) { d &= tail_mask; m &= tail_mask; z &= tail_mask; }
-    acc |= d;
-    sacc |= z;
-    const u32 c8 = (m * SCAN_GRAY_MUL) >> 24;
-    if (j < 4) lo |= c8 << (8 * j); else hi |= c8 << (8 * (j - 4));
-  }
-  bad = acc;
-  sep = sacc;
-  return ((u64) hi << 32) | lo;
+  int d;
+  asm ("dp4a.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a_signed), "r"(b_unsigned), "r"(c));
+  return d;
+}
+// mask of the x lowest bits, any x (<= 0 -> 0, >= 32 -> all)
+__device__ __forceinline__ u32 low_mask (int x) { return x <= 0 ? 0u : (x >= 32 ? 0xffffffffu : ((1u << x) - 1u)); }
+
+// 64 bits of a 2-bit code array starting at code index p (bit 2p)
+__device__ __forceinline__ u64 codes_at (const u32 *codes, int p)
+{
+  const int q = p >> 4, sh = (p & 15) << 1;
+  const u32 a0 = codes[q], a1 = codes[q + 1], a2 = codes[q + 2];
+  return ((u64) __funnelshift_r (a1, a2, sh) << 32) | __funnelshift_r (a0, a1, sh);
 }
 
 // reverse complement of a k-base word of BINARY codes (A0 C1 G2 T3), base j in bits 2j..2j+1
@@ -116,9 +112,15 @@ __device__ __forceinline__ u64 revcomp2 (u64 x, int k)
   const u64 mask = (k == 32) ? ~0ULL : ((1ULL << (2 * k)) - 1);
   return ~y & mask;
 }
+__device__ __forceinline__ u32 prmt (u32 a, u32 b, u32 sel)
+{
+  u32 d;
+  asm ("prmt.b32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(sel)); // default mode: selector bit 3 replicates the sign
+  return d;
+}
 
 template <int W>
-__global__ void __launch_bounds__ (SCAN_THREADS, 4)
+__global__ void __launch_bounds__ (SCAN_THREADS, SCAN_CTAS_PER_SM)
 tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_len, u64 *__restrict__ out,
                  unsigned long long capacity, unsigned long long *__restrict__ counters, long long n_tiles,
                  u32 *__restrict__ bin_hist, int bin_bits)
@@ -128,38 +130,36 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
   uint8_t *s_lutf = scan_smem + SCAN_WARPS * sizeof (ScanWarpSmem<W>), *s_lutr = s_lutf + 256;
 
   const int tid = threadIdx.x, lane = tid & 31;
-  const u32 lt_mask = (1u << lane) - 1;
   {
     const int f = tjb_code_fwd (tid); // SCAN_THREADS == 256
     s_lutf[tid] = (uint8_t) f;
     s_lutr[tid] = (uint8_t) (f < 4 ? 3 - f : f);
   }
-  if (lane < 8) reinterpret_cast<u32*> (S->raw[lane >> 2] + SW_BYTES)[lane & 3] = 0x0A0A0A0Au;
   if (lane == 0) {
     mbar_init (&S->bar[0], 1);
     mbar_init (&S->bar[1], 1);
     asm volatile ("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   const int cand_len = min_len < 4 ? min_len : 4;
-  const int nw = (k + 3) >> 2;
-  const u32 tail_mask = (k & 3) ? ((1u << (8 * (k & 3))) - 1) : 0xffffffffu;
+  const u64 kmask = (k == 32) ? ~0ULL : ((1ULL << (2 * k)) - 1);
   __syncthreads (); // the only block-wide barrier: LUTs and mbarriers are set up
 
   const long long n_warps = (long long) gridDim.x * SCAN_WARPS;
   u32 nrec = 0, nskip = 0, parity = 0;
+  u32 head = 0, tail = 0, n_old = 0; // candidate FIFO; n_old = entries that belong to the previous window
 
-  // a tile is "interior" when its whole window [g0, g0 + SW_BYTES) lies inside the buffer: one bulk copy stages it
-  auto interior = [&] (long long t) { const long long g0 = t * SW_TILE - SW_HALO_L; return g0 >= 0 && g0 + SW_BYTES <= n; };
+  // a window is "interior" when [g0, g0 + SW_WIN) lies inside the buffer: one bulk copy stages it
+  auto interior = [&] (long long t) { const long long g0 = t * SW_TILE - SW_HALO_L; return g0 >= 0 && g0 + SW_WIN <= n; };
   auto stage_tile = [&] (long long t, int st) {
     const long long g0 = t * SW_TILE - SW_HALO_L;
     if (interior (t)) {
       if (lane == 0) {
         asm volatile ("fence.proxy.async.shared::cta;" ::: "memory"); // generic-proxy accesses of this stage are done
-        mbar_expect_tx (&S->bar[st], SW_BYTES);
-        bulk_g2s (S->raw[st], buf + g0, SW_BYTES, &S->bar[st]);
+        mbar_expect_tx (&S->bar[st], SW_WIN);
+        bulk_g2s (S->raw[st], buf + g0, SW_WIN, &S->bar[st]);
       }
-    } else { // first / last tiles: bytes outside the buffer read as separators
-      for (int i = lane; i < SW_BYTES / 4; i += 32) {
+    } else { // first / last windows: bytes outside the buffer read as separators
+      for (int i = lane; i < SW_WIN / 4; i += 32) {
         u32 w = 0;
 #pragma unroll
         for (int j = 0; j < 4; j++) { const long long p = g0 + 4 * i + j; w |= (u32) ((p >= 0 && p < n) ? buf[p] : (uint8_t) '\n') << (8 * j); }
@@ -179,55 +179,67 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
     __syncwarp ();
   };
 
-  // ---- phase B: one candidate (window offset s of a code-run start, or -1) per lane ----------------------------
-  auto process_batch = [&] (int s, const uint8_t *raw, long long g0) {
-    const u32 *raw32 = reinterpret_cast<const u32*> (raw);
+  // ---- phase B: one candidate per lane (cnd = stage << 11 | window offset of a code-run start, or -1) -----------
+  // cur_st / cur_g0: the window whose bytes are still staged; candidates of the previous window (old_g0) only have
+  // their derived arrays left and read bytes, on the rare paths that need them, from global memory.
+  auto process_batch = [&] (int cnd, int cur_st, long long cur_g0, long long old_g0) {
     bool emit = false, slow = false;
     Rec<W> r;
-    int gray = 0;
-    if (s >= 0) {
-      const int ch = raw[s];
-      gray = (ch >> 1) & 3;
-      // first byte after s that differs from ch (word compares on the re-aligned bytes s+1, s+2, ...)
-      int p = s + 1;
-      {
-        const u32 sel = 0x3210u + 0x1111u * (u32) (p & 3);
-        const u32 pat = (u32) ch * 0x01010101u;
-        int a = p >> 2;
-        u32 w_lo = raw32[a];
-        for (;;) {
-          const u32 w_hi = raw32[a + 1];
-          const u32 x = __byte_perm (w_lo, w_hi, sel) ^ pat;
-          const u32 nz = (((x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | x) & 0x80808080u;
-          if (nz) { p += (__ffs (nz) - 1) >> 3; break; }
-          p += 4; a++; w_lo = w_hi;
-          if (p >= SW_BYTES) break;
-        }
-      }
-      // the code run must end where the byte run ends (else: N next to G, '\n' next to C, ... -> exact path)
-      slow = p >= SW_BYTES - 4 || ((raw[p] >> 1) & 3) == gray || (p + k + 4 >= SW_BYTES) ||
-             ch != (int) ((SCAN_GRAY_LUT >> (8 * gray)) & 0xff);
-      const int e = p - 1;
-      if (!slow && e - s + 1 >= min_len) {
-        u32 badl, badr, sepl, sepr;
-        const u64 gl = flank_gray (raw32, s - k, nw, tail_mask, badl, sepl);
-        const u64 gr = flank_gray (raw32, e + 1, nw, tail_mask, badr, sepr);
-        if (badl | badr) {
-          // a separator inside a flank: the tract is closer than k to a read end (hopo_counter.c:229, :232);
-          // any other byte (N, lower case, U, ...): byte-exact path
-          slow = !(sepl | sepr);
-        } else {
-          const u64 m5 = 0x5555555555555555ULL;
-          const u64 bl = gl ^ ((gl >> 1) & m5), br = gr ^ ((gr >> 1) & m5); // gray -> A0 C1 G2 T3
-          u64 ctx0, ctx1;
-          if (gray < 2) { ctx0 = bl; ctx1 = br; }                       // A / C tract: forward strand, :233-238
-          else { ctx0 = revcomp2 (br, k); ctx1 = revcomp2 (bl, k); }    // T / G tract: reverse complement, :239-246
-          r = pack_rec<W> (ctx0, ctx1, gray & 1, sext_field (e - s + 1, 10), gray < 2 ? 1 : 2, k);
-          atomicAdd (&bin_hist[rec_bin<W> (r, k, bin_bits)], 1u);
-          emit = true;
+    int gray = 0, s = 0, par = 0;
+    if (cnd >= 0) {
+      par = cnd >> 11; s = cnd & (SW_WIN - 1);
+      const u32 *codes = S->codes[par];
+      const u64 win = codes_at (codes, s); // codes s .. s+31
+      gray = (int) ((u32) win & 3u);
+      const u32 pat = (u32) gray * 0x55555555u;
+      u32 x0 = (u32) win ^ pat, x1 = (u32) (win >> 32) ^ pat;
+      x0 = (x0 | (x0 >> 1)) & 0x55555555u;
+      x1 = (x1 | (x1 >> 1)) & 0x55555555u;
+      const int len = x0 ? ((__ffs (x0) - 1) >> 1) : (x1 ? 16 + ((__ffs (x1) - 1) >> 1) : 32);
+      if (len >= 32) slow = true; // long run: may leave the window
+      else if (len >= min_len) {
+        const int P = s - k, nspan = 2 * k + len; // [P, P + nspan) = left flank, run, right flank
+        const int gl = P >> 4, ng = ((P + nspan - 1) >> 4) - gl + 1;
+        const u32 *bad = S->bad[par];
+        if (__funnelshift_r (bad[gl >> 5], bad[(gl >> 5) + 1], gl & 31) & low_mask (ng)) slow = true;
+        else {
+          const u32 *nlw = S->nl[par];
+          const int q = P >> 5, sh = P & 31;
+          const u32 n0 = nlw[q], n1 = nlw[q + 1], n2 = nlw[q + 2], n3 = nlw[q + 3];
+          const u32 m0 = __funnelshift_r (n0, n1, sh) & low_mask (nspan);
+          const u32 m1 = __funnelshift_r (n1, n2, sh) & low_mask (nspan - 32);
+          const u32 m2 = __funnelshift_r (n2, n3, sh) & low_mask (nspan - 64);
+          if (m0 | m1 | m2) {
+            // Non-letters in the span.  Every byte of the span is ACGT or separator-like here, so if they all are
+            // the separator itself the tract is closer than k to a read end (hopo_counter.c:229, :232) and every
+            // byte run of this code run is rejected; 0x08 / 0x0E / 0x1D pass the pass-1 test too: exact path.
+#pragma unroll
+            for (int i = 0; i < 3; i++) {
+              u32 mm = i == 0 ? m0 : (i == 1 ? m1 : m2);
+              while (mm) {
+                const int pos = P + 32 * i + __ffs (mm) - 1;
+                mm &= mm - 1;
+                int b;
+                if (par == cur_st) b = S->raw[par][pos];
+                else { const long long gp = old_g0 + pos; b = (gp >= 0 && gp < n) ? buf[gp] : '\n'; }
+                if (b != '\n') slow = true;
+              }
+            }
+          } else {
+            const u64 gl64 = codes_at (codes, P) & kmask, gr64 = codes_at (codes, s + len) & kmask;
+            const u64 m5 = 0x5555555555555555ULL;
+            const u64 bl = gl64 ^ ((gl64 >> 1) & m5), br = gr64 ^ ((gr64 >> 1) & m5); // gray -> A0 C1 G2 T3
+            u64 ctx0, ctx1;
+            if (gray < 2) { ctx0 = bl; ctx1 = br; }                       // A / C tract: forward strand, :233-238
+            else { ctx0 = revcomp2 (br, k); ctx1 = revcomp2 (bl, k); }    // T / G tract: reverse complement, :239-246
+            r = pack_rec<W> (ctx0, ctx1, gray & 1, sext_field (len, 10), gray < 2 ? 1 : 2, k);
+            atomicAdd (&bin_hist[rec_bin<W> (r, k, bin_bits)], 1u);
+            emit = true;
+          }
         }
       }
     }
+    const u32 lt_mask = (1u << lane) - 1;
     const u32 em = __ballot_sync (0xffffffffu, emit);
     if (emit) {
       const u32 slot = nrec + __popc (em & lt_mask);
@@ -237,9 +249,12 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
     nrec += __popc (em);
     if (slow) {
       // byte-exact restatement of the reference loop over every byte run inside this code run
+      const long long g0 = par == cur_st ? cur_g0 : old_g0;
+      const uint8_t *raw = S->raw[par];
+      const bool staged = par == cur_st;
       auto byte_at = [&] (long long gp) -> int {
         const long long rel = gp - g0;
-        if (rel >= 0 && rel < SW_BYTES) return raw[rel];
+        if (staged && rel >= 0 && rel < SW_WIN) return raw[rel];
         return (gp >= 0 && gp < n) ? buf[gp] : '\n';
       };
       long long ps = g0 + s;
@@ -250,7 +265,7 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
         while (pe + 1 < n && byte_at (pe + 1) == b0) pe++;
         const long long len = pe - ps + 1;
         const int code = s_lutf[b0];
-        // cheap exits first: most code runs that are not byte runs are a C tract touching a read separator
+        // cheap exits first
         if (len >= min_len && code != 5 && byte_at (ps - 1) != '\n' && byte_at (pe + 1) != '\n') {
           bool ok = true;
           u64 ctx0 = 0, ctx1 = 0;
@@ -278,7 +293,7 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
     if (nrec > SW_RCAP - 32) flush ();
   };
 
-  // ---- main loop: this warp's tiles, tile t+n_warps in flight while tile t is processed ----------------------
+  // ---- main loop: this warp's windows, window t+n_warps in flight while window t is processed ------------------
   long long t = (long long) blockIdx.x * SCAN_WARPS + (tid >> 5);
   int st = 0;
   if (t < n_tiles) stage_tile (t, 0);
@@ -286,40 +301,96 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
     if (t + n_warps < n_tiles) stage_tile (t + n_warps, st ^ 1);
     if (interior (t)) { mbar_wait (&S->bar[st], (parity >> st) & 1); parity ^= 1u << st; }
     else __syncwarp ();
-    const uint8_t *raw = S->raw[st];
-    const u32 *raw32 = reinterpret_cast<const u32*> (raw);
-    const long long g0 = t * SW_TILE - SW_HALO_L;
-    u32 nq = 0;
-    for (int row = 0; row < SW_ROWS; row++) {
-      // ---- phase A: gray codes of my 16 bytes, code-run starts ---------------------------------------------
-      const int grp = SW_HALO_L / 16 + row * 32 + lane;
-      const uint4 v = *reinterpret_cast<const uint4*> (raw + 16 * grp);
-      const u32 p0 = (v.x & 0x06060606u) * SCAN_GRAY_MUL, p1 = (v.y & 0x06060606u) * SCAN_GRAY_MUL;
-      const u32 p2 = (v.z & 0x06060606u) * SCAN_GRAY_MUL, p3 = (v.w & 0x06060606u) * SCAN_GRAY_MUL;
-      const u32 c = __byte_perm (__byte_perm (p0, p1, 0x0073), __byte_perm (p2, p3, 0x0073), 0x5410);
-      const u32 wprev = raw32[4 * grp - 1], wnext = raw32[4 * grp + 4];
-      const u32 cn = ((wnext & 0x00060606u) * SCAN_GRAY_MUL) >> 24; // next three bases
-      const u32 cpw = (wprev << 5) & 0xC0000000u;                    // previous base, in the top two bits
-      u32 tt = c ^ __funnelshift_r (c, cn, 2);
-      if (cand_len >= 3) tt |= c ^ __funnelshift_r (c, cn, 4);
-      if (cand_len >= 4) tt |= c ^ __funnelshift_r (c, cn, 6);
-      const u32 dp = c ^ __funnelshift_l (cpw, c, 2);
-      u32 cs = ~(tt | (tt >> 1)) & (dp | (dp >> 1)) & 0x55555555u;
-      // ballot compaction into the warp's queue (a lane rarely holds more than one start)
-      for (;;) {
-        const u32 m = __ballot_sync (0xffffffffu, cs != 0);
-        if (!m) break;
-        if (cs) {
-          S->cand[nq + __popc (m & lt_mask)] = (unsigned short) (16 * grp + ((__ffs (cs) - 1) >> 1));
-          cs &= cs - 1;
-        }
-        nq += __popc (m);
+    const long long g0 = t * SW_TILE - SW_HALO_L, old_g0 = g0 - n_warps * SW_TILE;
+    u32 *codes = S->codes[st];
+    u32 c[SW_ROWS];
+    {
+      // ---- pass 1: 16 bytes per lane and row -> gray codes, non-letter mask, bad-group bit -------------------
+      const uint4 *raw128 = reinterpret_cast<const uint4*> (S->raw[st]);
+      unsigned short *nl16 = reinterpret_cast<unsigned short*> (S->nl[st]);
+#pragma unroll
+      for (int row = 0; row < SW_ROWS; row++) {
+        const int grp = row * 32 + lane;
+        const uint4 v = raw128[grp];
+        const u32 w0 = v.x, w1 = v.y, w2 = v.z, w3 = v.w;
+        const u32 m0 = w0 & 0x06060606u, m1 = w1 & 0x06060606u, m2 = w2 & 0x06060606u, m3 = w3 & 0x06060606u;
+        const u32 p0 = m0 * SCAN_GRAY_MUL, p1 = m1 * SCAN_GRAY_MUL, p2 = m2 * SCAN_GRAY_MUL, p3 = m3 * SCAN_GRAY_MUL;
+        c[row] = __byte_perm (__byte_perm (p0, p1, 0x0073), __byte_perm (p2, p3, 0x0073), 0x5410);
+        // letters have bit 6 set: 0xFF per letter byte, 0x00 per non-letter byte (sign-replicating PRMT on 2w)
+        const u32 e0 = prmt (w0 + w0, 0, 0xBA98), e1 = prmt (w1 + w1, 0, 0xBA98);
+        const u32 e2 = prmt (w2 + w2, 0, 0xBA98), e3 = prmt (w3 + w3, 0, 0xBA98);
+        // non-letters are moved onto the letter their code stands for if they are '\n' (0x0A ^ 0x49 = 'C')
+        const u32 f0 = w0 ^ (~e0 & 0x49494949u), f1 = w1 ^ (~e1 & 0x49494949u);
+        const u32 f2 = w2 ^ (~e2 & 0x49494949u), f3 = w3 ^ (~e3 & 0x49494949u);
+        // expected bytes from the codes: one PRMT look-up per 4 bytes, the selectors of two words interleaved
+        const u32 z01 = m1 * 16u + m0, z23 = m3 * 16u + m2;
+        const u32 xa = prmt (SCAN_LUT_A, SCAN_LUT_B, z01), xb = prmt (SCAN_LUT_A, SCAN_LUT_B, z01 >> 16);
+        const u32 xc = prmt (SCAN_LUT_A, SCAN_LUT_B, z23), xd = prmt (SCAN_LUT_A, SCAN_LUT_B, z23 >> 16);
+        const u32 d0 = f0 ^ prmt (xa, xb, 0x6420), d1 = f1 ^ prmt (xa, xb, 0x7531);
+        const u32 d2 = f2 ^ prmt (xc, xd, 0x6420), d3 = f3 ^ prmt (xc, xd, 0x7531);
+        const u32 acc = __dp4a (d0, d0, __dp4a (d1, d1, __dp4a (d2, d2, __dp4a (d3, d3, 0u))));
+        // bit j of the mask = byte j is a non-letter: 255 - sum of the weights of the letters (signed -1 bytes)
+        const int lo8 = dp4a_su (e1, 0x80402010u, dp4a_su (e0, 0x08040201u, 255));
+        const int hi8 = dp4a_su (e3, 0x80402010u, dp4a_su (e2, 0x08040201u, 255));
+        nl16[grp] = (unsigned short) (hi8 * 256 + lo8);
+        codes[grp] = c[row];
+        const u32 bb = __ballot_sync (0xffffffffu, acc != 0);
+        if (lane == 0) S->bad[st][row] = bb;
       }
-      __syncwarp ();
-      while (nq >= 32) { nq -= 32; process_batch ((int) S->cand[nq + lane], raw, g0); }
     }
-    if (nq) process_batch (lane < (int) nq ? (int) S->cand[lane] : -1, raw, g0);
-    __syncwarp (); // every lane is done with this stage before it is refilled
+    __syncwarp ();
+    // ---- pass 2: code-run starts of the owned groups, two rows per 32-bit word (even bits / odd bits) ----------
+    u32 A = 0, B = 0;
+#pragma unroll
+    for (int row = 0; row < SW_ROWS; row++) {
+      const int grp = row * 32 + lane;
+      const u32 cc = c[row], cn = codes[(grp + 1) & (SW_GROUPS - 1)], cp = codes[(grp - 1) & (SW_GROUPS - 1)];
+      u32 tt = cc ^ __funnelshift_r (cc, cn, 2);
+      if (cand_len >= 3) tt |= cc ^ __funnelshift_r (cc, cn, 4);
+      if (cand_len >= 4) tt |= cc ^ __funnelshift_r (cc, cn, 6);
+      const u32 dp = cc ^ __funnelshift_l (cp, cc, 2);
+      u32 cs = ~(tt | (tt >> 1)) & (dp | (dp >> 1)) & 0x55555555u;
+      if (grp < SW_G0 || grp >= SW_G1) cs = 0;
+      if (row < 2) A |= cs << (row & 1); else B |= cs << (row & 1);
+    }
+    // ---- compaction into the FIFO (at most 15 per lane and round), full batches of 32 go to phase B ------------
+    for (;;) {
+      const int have = __popc (A) + __popc (B), mine = have < 15 ? have : 15;
+      int inc = mine;
+#pragma unroll
+      for (int d = 1; d < 32; d <<= 1) { const int u = __shfl_up_sync (0xffffffffu, inc, d); if (lane >= d) inc += u; }
+      const int total = __shfl_sync (0xffffffffu, inc, 31);
+      if (total) {
+        u32 slot = tail + (u32) (inc - mine);
+        for (int i = 0; i < mine; i++) {
+          int b, rw;
+          if (A) { b = __ffs (A) - 1; A &= A - 1; rw = b & 1; }
+          else { b = __ffs (B) - 1; B &= B - 1; rw = 2 + (b & 1); }
+          S->ring[slot & (SW_RING - 1)] = (unsigned short) ((st << 11) | (16 * (32 * rw + lane) + (b >> 1)));
+          slot++;
+        }
+        tail += (u32) total;
+        __syncwarp ();
+        while (tail - head >= 32) {
+          process_batch ((int) S->ring[(head + lane) & (SW_RING - 1)], st, g0, old_g0);
+          head += 32;
+          n_old = n_old > 32 ? n_old - 32 : 0;
+        }
+      }
+      if (!__any_sync (0xffffffffu, (A | B) != 0)) break;
+    }
+    // candidates of the previous window must go before its derived arrays are overwritten by the next window
+    if (n_old) {
+      const u32 cnt = tail - head;
+      process_batch (lane < (int) cnt ? (int) S->ring[(head + lane) & (SW_RING - 1)] : -1, st, g0, old_g0);
+      head = tail;
+    }
+    n_old = tail - head;
+    __syncwarp (); // every lane is done with the other stage's arrays and this stage's bytes are consumed
+  }
+  if (tail != head) { // what is left belongs to the last window, whose bytes are still staged
+    const long long tl = t - n_warps;
+    process_batch (lane < (int) (tail - head) ? (int) S->ring[(head + lane) & (SW_RING - 1)] : -1, st ^ 1, tl * SW_TILE - SW_HALO_L, 0);
   }
   if (nrec) flush ();
 #pragma unroll
