@@ -43,12 +43,14 @@
 #define SW_G0 (SW_HALO_L / 16)        // owned groups [SW_G0, SW_G1)
 #define SW_G1 (SW_G0 + SW_TILE / 16)
 #define SW_ROWS (SW_GROUPS / 32)
-#define SW_RING 512                   // candidate FIFO (< 32 carried + at most 480 new per round)
+#define SW_QCAP 512                   // candidate queue (< 32 carried + at most 480 new per round)
 #define SW_RCAP 64                    // staged records per warp; flushed when more than SW_RCAP - 32 are pending
 #define SCAN_GRAY_MUL 0x00820820u     // ((w & 0x06060606) * this) >> 24 = the four 2-bit codes of w's bytes
 #define SCAN_GRAY_LUT 0x47544341u     // code -> byte: 'A' 'C' 'T' 'G'
-#define SCAN_LUT_A 0x00430041u        // PRMT look-up on (code << 1): bytes 0 / 2 = 'A' / 'C'
-#define SCAN_LUT_B 0x00470054u        //                              bytes 4 / 6 = 'T' / 'G'
+// PRMT look-up on (code << 1 | non-letter): letters A C T G in the even slots; odd slots: only code 1 can be a
+// non-letter, the separator 0x0A; the other three hold a byte whose own code differs from the slot's (never equal)
+#define SCAN_LUT_A 0x0A43FF41u
+#define SCAN_LUT_B 0x00470054u
 
 template <int W> struct ScanWarpSmem {
   uint8_t raw[2][SW_WIN];             // two stages of sequence bytes
@@ -57,7 +59,7 @@ template <int W> struct ScanWarpSmem {
   u32 bad[2][8];                      // bit g = group g holds a byte that is neither ACGT nor separator-like
   u64 rec[SW_RCAP * W];
   unsigned long long bar[2];          // mbarriers of the two stages
-  unsigned short ring[SW_RING];       // candidates: stage << 11 | window offset of the code-run start
+  unsigned short cand[SW_QCAP];       // candidates: stage << 11 | row pair << 10 | lane << 5 | bit (see pass 2)
 };
 template <int W> constexpr size_t scan_smem_bytes () { return SCAN_WARPS * sizeof (ScanWarpSmem<W>) + 512; }
 
@@ -94,7 +96,12 @@ __device__ __forceinline__ int dp4a_su (u32 a_signed, u32 b_unsigned, int c)
   return d;
 }
 // mask of the x lowest bits, any x (<= 0 -> 0, >= 32 -> all)
-__device__ __forceinline__ u32 low_mask (int x) { return x <= 0 ? 0u : (x >= 32 ? 0xffffffffu : ((1u << x) - 1u)); }
+__device__ __forceinline__ u32 low_mask (int x)
+{
+  u32 d;
+  asm ("bmsk.clamp.b32 %0, %1, %2;" : "=r"(d) : "r"(0), "r"(x < 0 ? 0 : x));
+  return d;
+}
 
 // 64 bits of a 2-bit code array starting at code index p (bit 2p)
 __device__ __forceinline__ u64 codes_at (const u32 *codes, int p)
@@ -179,15 +186,16 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
     __syncwarp ();
   };
 
-  // ---- phase B: one candidate per lane (cnd = stage << 11 | window offset of a code-run start, or -1) -----------
+  // ---- phase B: one candidate per lane (a queue entry, or -1) ---------------------------------------------------
   // cur_st / cur_g0: the window whose bytes are still staged; candidates of the previous window (old_g0) only have
-  // their derived arrays left and read bytes, on the rare paths that need them, from global memory.
+  // their derived arrays left; the slow path reads their bytes from global memory.
   auto process_batch = [&] (int cnd, int cur_st, long long cur_g0, long long old_g0) {
     bool emit = false, slow = false;
     Rec<W> r;
     int gray = 0, s = 0, par = 0;
     if (cnd >= 0) {
-      par = cnd >> 11; s = cnd & (SW_WIN - 1);
+      par = cnd >> 11;
+      s = (cnd & 0x400) | ((cnd & 1) << 9) | ((cnd >> 1) & 0x1FF); // 1024 * row pair + 512 * (bit & 1) + 16 * lane + bit / 2
       const u32 *codes = S->codes[par];
       const u64 win = codes_at (codes, s); // codes s .. s+31
       gray = (int) ((u32) win & 3u);
@@ -203,29 +211,15 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
         const u32 *bad = S->bad[par];
         if (__funnelshift_r (bad[gl >> 5], bad[(gl >> 5) + 1], gl & 31) & low_mask (ng)) slow = true;
         else {
+          // every byte of the span is one of "ACGT" or the separator: a separator anywhere in it means that the
+          // tract is closer than k to a read end (hopo_counter.c:229, :232), for every byte run of this code run
           const u32 *nlw = S->nl[par];
           const int q = P >> 5, sh = P & 31;
           const u32 n0 = nlw[q], n1 = nlw[q + 1], n2 = nlw[q + 2], n3 = nlw[q + 3];
           const u32 m0 = __funnelshift_r (n0, n1, sh) & low_mask (nspan);
           const u32 m1 = __funnelshift_r (n1, n2, sh) & low_mask (nspan - 32);
           const u32 m2 = __funnelshift_r (n2, n3, sh) & low_mask (nspan - 64);
-          if (m0 | m1 | m2) {
-            // Non-letters in the span.  Every byte of the span is ACGT or separator-like here, so if they all are
-            // the separator itself the tract is closer than k to a read end (hopo_counter.c:229, :232) and every
-            // byte run of this code run is rejected; 0x08 / 0x0E / 0x1D pass the pass-1 test too: exact path.
-#pragma unroll
-            for (int i = 0; i < 3; i++) {
-              u32 mm = i == 0 ? m0 : (i == 1 ? m1 : m2);
-              while (mm) {
-                const int pos = P + 32 * i + __ffs (mm) - 1;
-                mm &= mm - 1;
-                int b;
-                if (par == cur_st) b = S->raw[par][pos];
-                else { const long long gp = old_g0 + pos; b = (gp >= 0 && gp < n) ? buf[gp] : '\n'; }
-                if (b != '\n') slow = true;
-              }
-            }
-          } else {
+          if (!(m0 | m1 | m2)) {
             const u64 gl64 = codes_at (codes, P) & kmask, gr64 = codes_at (codes, s + len) & kmask;
             const u64 m5 = 0x5555555555555555ULL;
             const u64 bl = gl64 ^ ((gl64 >> 1) & m5), br = gr64 ^ ((gr64 >> 1) & m5); // gray -> A0 C1 G2 T3
@@ -295,13 +289,19 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
 
   // ---- main loop: this warp's windows, window t+n_warps in flight while window t is processed ------------------
   long long t = (long long) blockIdx.x * SCAN_WARPS + (tid >> 5);
+  const long long stride = n_warps * SW_TILE;
+  long long g0 = t * SW_TILE - SW_HALO_L;
   int st = 0;
-  if (t < n_tiles) stage_tile (t, 0);
-  for (; t < n_tiles; t += n_warps, st ^= 1) {
-    if (t + n_warps < n_tiles) stage_tile (t + n_warps, st ^ 1);
-    if (interior (t)) { mbar_wait (&S->bar[st], (parity >> st) & 1); parity ^= 1u << st; }
+  bool in_cur = false;
+  if (t < n_tiles) { in_cur = interior (t); stage_tile (t, 0); }
+  const u32 hdr = (u32) lane << 5;
+  for (; t < n_tiles; t += n_warps, g0 += stride, st ^= 1) {
+    bool in_next = false;
+    if (t + n_warps < n_tiles) { in_next = interior (t + n_warps); stage_tile (t + n_warps, st ^ 1); }
+    if (in_cur) { mbar_wait (&S->bar[st], (parity >> st) & 1); parity ^= 1u << st; }
     else __syncwarp ();
-    const long long g0 = t * SW_TILE - SW_HALO_L, old_g0 = g0 - n_warps * SW_TILE;
+    in_cur = in_next;
+    const long long old_g0 = g0 - stride;
     u32 *codes = S->codes[st];
     u32 c[SW_ROWS];
     {
@@ -319,15 +319,15 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
         // letters have bit 6 set: 0xFF per letter byte, 0x00 per non-letter byte (sign-replicating PRMT on 2w)
         const u32 e0 = prmt (w0 + w0, 0, 0xBA98), e1 = prmt (w1 + w1, 0, 0xBA98);
         const u32 e2 = prmt (w2 + w2, 0, 0xBA98), e3 = prmt (w3 + w3, 0, 0xBA98);
-        // non-letters are moved onto the letter their code stands for if they are '\n' (0x0A ^ 0x49 = 'C')
-        const u32 f0 = w0 ^ (~e0 & 0x49494949u), f1 = w1 ^ (~e1 & 0x49494949u);
-        const u32 f2 = w2 ^ (~e2 & 0x49494949u), f3 = w3 ^ (~e3 & 0x49494949u);
-        // expected bytes from the codes: one PRMT look-up per 4 bytes, the selectors of two words interleaved
-        const u32 z01 = m1 * 16u + m0, z23 = m3 * 16u + m2;
+        // look-up selectors: code << 1 | non-letter, the nibbles of two words interleaved in one register
+        const u32 s0 = m0 | (~e0 & 0x01010101u), s1 = m1 | (~e1 & 0x01010101u);
+        const u32 s2 = m2 | (~e2 & 0x01010101u), s3 = m3 | (~e3 & 0x01010101u);
+        const u32 z01 = s1 * 16u + s0, z23 = s3 * 16u + s2;
         const u32 xa = prmt (SCAN_LUT_A, SCAN_LUT_B, z01), xb = prmt (SCAN_LUT_A, SCAN_LUT_B, z01 >> 16);
         const u32 xc = prmt (SCAN_LUT_A, SCAN_LUT_B, z23), xd = prmt (SCAN_LUT_A, SCAN_LUT_B, z23 >> 16);
-        const u32 d0 = f0 ^ prmt (xa, xb, 0x6420), d1 = f1 ^ prmt (xa, xb, 0x7531);
-        const u32 d2 = f2 ^ prmt (xc, xd, 0x6420), d3 = f3 ^ prmt (xc, xd, 0x7531);
+        // the bytes their codes stand for, against the bytes themselves: sum of squared differences over the group
+        const u32 d0 = w0 ^ prmt (xa, xb, 0x6420), d1 = w1 ^ prmt (xa, xb, 0x7531);
+        const u32 d2 = w2 ^ prmt (xc, xd, 0x6420), d3 = w3 ^ prmt (xc, xd, 0x7531);
         const u32 acc = __dp4a (d0, d0, __dp4a (d1, d1, __dp4a (d2, d2, __dp4a (d3, d3, 0u))));
         // bit j of the mask = byte j is a non-letter: 255 - sum of the weights of the letters (signed -1 bytes)
         const int lo8 = dp4a_su (e1, 0x80402010u, dp4a_su (e0, 0x08040201u, 255));
@@ -339,7 +339,8 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
       }
     }
     __syncwarp ();
-    // ---- pass 2: code-run starts of the owned groups, two rows per 32-bit word (even bits / odd bits) ----------
+    // ---- pass 2: code-run starts of the owned groups.  A = rows 0 (even bits) and 1 (odd bits), B = rows 2 and 3:
+    // bit b of A is byte b / 2 of group 32 * (b & 1) + lane
     u32 A = 0, B = 0;
 #pragma unroll
     for (int row = 0; row < SW_ROWS; row++) {
@@ -350,10 +351,11 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
       if (cand_len >= 4) tt |= cc ^ __funnelshift_r (cc, cn, 6);
       const u32 dp = cc ^ __funnelshift_l (cp, cc, 2);
       u32 cs = ~(tt | (tt >> 1)) & (dp | (dp >> 1)) & 0x55555555u;
-      if (grp < SW_G0 || grp >= SW_G1) cs = 0;
+      if (row == 0 && lane < SW_G0) cs = 0;                       // halo groups are owned by the neighbouring windows
+      if (row == SW_ROWS - 1 && lane >= SW_G1 - 32 * (SW_ROWS - 1)) cs = 0;
       if (row < 2) A |= cs << (row & 1); else B |= cs << (row & 1);
     }
-    // ---- compaction into the FIFO (at most 15 per lane and round), full batches of 32 go to phase B ------------
+    // ---- compaction into the queue (at most 15 per lane and round); full batches of 32 go to phase B ------------
     for (;;) {
       const int have = __popc (A) + __popc (B), mine = have < 15 ? have : 15;
       int inc = mine;
@@ -361,37 +363,48 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
       for (int d = 1; d < 32; d <<= 1) { const int u = __shfl_up_sync (0xffffffffu, inc, d); if (lane >= d) inc += u; }
       const int total = __shfl_sync (0xffffffffu, inc, 31);
       if (total) {
-        u32 slot = tail + (u32) (inc - mine);
-        for (int i = 0; i < mine; i++) {
-          int b, rw;
-          if (A) { b = __ffs (A) - 1; A &= A - 1; rw = b & 1; }
-          else { b = __ffs (B) - 1; B &= B - 1; rw = 2 + (b & 1); }
-          S->ring[slot & (SW_RING - 1)] = (unsigned short) ((st << 11) | (16 * (32 * rw + lane) + (b >> 1)));
-          slot++;
-        }
+        unsigned short *qp = S->cand + tail + (u32) (inc - mine);
+        const u32 ha = ((u32) st << 11) | hdr, hb = ha | 0x400u;
+        int left = mine;
+        while (A && left) { const int b = __ffs (A) - 1; A &= A - 1; *qp++ = (unsigned short) (ha + b); left--; }
+        while (B && left) { const int b = __ffs (B) - 1; B &= B - 1; *qp++ = (unsigned short) (hb + b); left--; }
         tail += (u32) total;
         __syncwarp ();
         while (tail - head >= 32) {
-          process_batch ((int) S->ring[(head + lane) & (SW_RING - 1)], st, g0, old_g0);
+          process_batch ((int) S->cand[head + lane], st, g0, old_g0);
           head += 32;
           n_old = n_old > 32 ? n_old - 32 : 0;
         }
       }
-      if (!__any_sync (0xffffffffu, (A | B) != 0)) break;
+      const bool more = __any_sync (0xffffffffu, (A | B) != 0);
+      if (!more && !n_old) break;
+      // candidates of the previous window must go before its derived arrays are overwritten by the next window
+      if (n_old) {
+        process_batch (lane < (int) (tail - head) ? (int) S->cand[head + lane] : -1, st, g0, old_g0);
+        head = tail;
+        n_old = 0;
+      }
+      if (!more) break;
+      { // rare: more than 15 candidates in one lane; move what is left to the front and go again
+        const u32 cnt = tail - head;
+        const unsigned short v = lane < (int) cnt ? S->cand[head + lane] : (unsigned short) 0;
+        __syncwarp ();
+        if (lane < (int) cnt) S->cand[lane] = v;
+        head = 0; tail = cnt;
+        __syncwarp ();
+      }
     }
-    // candidates of the previous window must go before its derived arrays are overwritten by the next window
-    if (n_old) {
+    { // what is left (< 32 candidates) moves to the front of the queue and waits for the next window
       const u32 cnt = tail - head;
-      process_batch (lane < (int) cnt ? (int) S->ring[(head + lane) & (SW_RING - 1)] : -1, st, g0, old_g0);
-      head = tail;
+      const unsigned short v = lane < (int) cnt ? S->cand[head + lane] : (unsigned short) 0;
+      __syncwarp ();
+      if (lane < (int) cnt) S->cand[lane] = v;
+      head = 0; tail = cnt; n_old = cnt;
     }
-    n_old = tail - head;
     __syncwarp (); // every lane is done with the other stage's arrays and this stage's bytes are consumed
   }
-  if (tail != head) { // what is left belongs to the last window, whose bytes are still staged
-    const long long tl = t - n_warps;
-    process_batch (lane < (int) (tail - head) ? (int) S->ring[(head + lane) & (SW_RING - 1)] : -1, st ^ 1, tl * SW_TILE - SW_HALO_L, 0);
-  }
+  if (tail != head) // what is left belongs to the last window, whose bytes are still staged
+    process_batch (lane < (int) (tail - head) ? (int) S->cand[head + lane] : -1, st ^ 1, g0 - stride, 0);
   if (nrec) flush ();
 #pragma unroll
   for (int d = 16; d; d >>= 1) nskip += __shfl_xor_sync (0xffffffffu, nskip, d);
