@@ -8,7 +8,7 @@ import os
 import subprocess
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "lib", "libtjb_gpu.so")
+LIB_PATH = os.environ.get("TJB_LIB") or os.path.join(HERE, "lib", "libtjb_gpu.so")  # TJB_LIB: kernel-variant experiments
 CSRC = os.path.join(HERE, "csrc")
 
 # every symbol include/tjb_gpu.h declares (checked by tests/test_abi.py)

@@ -34,7 +34,9 @@
 
 #define SCAN_WARPS 8
 #define SCAN_THREADS (SCAN_WARPS * 32)
+#ifndef SCAN_CTAS_PER_SM
 #define SCAN_CTAS_PER_SM 3
+#endif
 #define SW_WIN 2048                   // staged bytes per window = 128 groups of 16 = 4 rows of 32 lanes
 #define SW_HALO_L 32                  // >= k, multiple of 16
 #define SW_HALO_R 64                  // >= 31 (longest fast-path run) + k + 1
@@ -43,8 +45,13 @@
 #define SW_G0 (SW_HALO_L / 16)        // owned groups [SW_G0, SW_G1)
 #define SW_G1 (SW_G0 + SW_TILE / 16)
 #define SW_ROWS (SW_GROUPS / 32)
-#define SW_QCAP 512                   // candidate queue (< 32 carried + at most 480 new per round)
+#ifndef SW_QCAP
+#define SW_QCAP 512                   // candidate queue: < 32 carried + at most 32 * SW_QUOTA new per round
+#endif
+#define SW_QUOTA ((SW_QCAP - 32) / 32)
+#ifndef SW_RCAP
 #define SW_RCAP 64                    // staged records per warp; flushed when more than SW_RCAP - 32 are pending
+#endif
 #define SCAN_GRAY_MUL 0x00820820u     // ((w & 0x06060606) * this) >> 24 = the four 2-bit codes of w's bytes
 #define SCAN_GRAY_LUT 0x47544341u     // code -> byte: 'A' 'C' 'T' 'G'
 // PRMT look-up on (code << 1 | non-letter): letters A C T G in the even slots; odd slots: only code 1 can be a
@@ -355,9 +362,9 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
       if (row == SW_ROWS - 1 && lane >= SW_G1 - 32 * (SW_ROWS - 1)) cs = 0;
       if (row < 2) A |= cs << (row & 1); else B |= cs << (row & 1);
     }
-    // ---- compaction into the queue (at most 15 per lane and round); full batches of 32 go to phase B ------------
+    // ---- compaction into the queue (at most SW_QUOTA per lane and round); full batches of 32 go to phase B ------------
     for (;;) {
-      const int have = __popc (A) + __popc (B), mine = have < 15 ? have : 15;
+      const int have = __popc (A) + __popc (B), mine = have < SW_QUOTA ? have : SW_QUOTA;
       int inc = mine;
 #pragma unroll
       for (int d = 1; d < 32; d <<= 1) { const int u = __shfl_up_sync (0xffffffffu, inc, d); if (lane >= d) inc += u; }
@@ -385,7 +392,7 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
         n_old = 0;
       }
       if (!more) break;
-      { // rare: more than 15 candidates in one lane; move what is left to the front and go again
+      { // rare: more than SW_QUOTA candidates in one lane; move what is left to the front and go again
         const u32 cnt = tail - head;
         const unsigned short v = lane < (int) cnt ? S->cand[head + lane] : (unsigned short) 0;
         __syncwarp ();
