@@ -113,6 +113,20 @@ int tjb_count_sample (const char *const *files, int n_files, const tjb_opts *opt
 
 void tjb_counter_out_free (tjb_counter_out *out);
 
+/* ---- cross-sample exchange (SURVEY.md section 8 e): the step between finalise_hopo_counter() steps 0-4 and the
+ * mapper call.  The reference builds one mapper query per indexed context group from the group's first = longest
+ * record (src/hopo_counter.c:513-520) and maps every sample separately (src/genome_set.c:75, 90).  A "query row"
+ * is that record as 3 x uint64 {context[0], context[1], base | length_field << 8}.  Ranks exchange their rows
+ * (NCCL allgather, tatajuba_b200/genome_set.py); tjb_union_queries_device() then returns the DISTINCT rows over
+ * all samples in the reference's order (hopo_counter.c:28-38, descending) and, per input row, its index in that
+ * union, so that each distinct query is mapped once and the result scattered back to every sample's groups. */
+/* rows: 3 * in->n_idx uint64 (host).  Returns n_idx or a negative error. */
+int tjb_query_rows (const tjb_counter_out *in, uint64_t *rows);
+/* d_rows: 3 * n_rows uint64 in DEVICE memory; d_union: device buffer of 3 * n_rows uint64 (the first 3 * *n_union
+ * are written); d_index: device int32[n_rows] or NULL.  Synchronous. */
+int tjb_union_queries_device (tjb_ctx *ctx, const void *d_rows, int64_t n_rows, int kmer_size, void *d_union,
+                              int64_t *n_union, void *d_index);
+
 /* host FASTQ/FASTA(.gz) decoder on its own (kseq semantics): appends "SEQ\n" per record to dst (capacity cap);
  * returns bytes written (0 = end of file), <0 on error.  Exposed for tests and for callers that feed
  * tjb_count_sample_host themselves. */

@@ -183,3 +183,39 @@ class Restatement:
             C.memmove(out.ctypes.data, p, n * REC_DTYPE.itemsize)
         self.lib.tjbo_free(p)
         return out, int(skipped.value)
+
+
+# ---- cross-sample exchange (SURVEY.md section 8 e): numpy restatement, test infrastructure only -----------------
+def query_rows_oracle(elem40, idx_initial):
+    """one row per indexed group from its first = longest record (reference src/hopo_counter.c:513-520):
+    {context[0], context[1], base | length_field << 8}"""
+    e = np.asarray(elem40).view(np.uint64).reshape(-1, 5)[np.asarray(idx_initial, dtype=np.int64)]
+    rows = np.empty((len(e), 3), np.uint64)
+    rows[:, 0], rows[:, 1] = e[:, 0], e[:, 1]
+    rows[:, 2] = (e[:, 2] & np.uint64(1)) | (((e[:, 2] >> np.uint64(2)) & np.uint64(0x3ff)) << np.uint64(8))
+    return rows
+
+
+def union_oracle(tables):
+    """distinct rows over all tables in the reference's descending (base, ctx0, ctx1, length) order
+    (compare_hopo_element_decreasing, src/hopo_counter.c:28-38; length is a signed 10-bit field) and, per table,
+    the index of each row in the union"""
+    rows = np.concatenate([np.asarray(t, np.uint64).reshape(-1, 3) for t in tables]) if tables else np.zeros((0, 3), np.uint64)
+    if len(rows) == 0:
+        return rows, [np.zeros(0, np.int32) for _ in tables]
+    base = (rows[:, 2] & np.uint64(1)).astype(np.int64)
+    lf = ((rows[:, 2] >> np.uint64(8)) & np.uint64(0x3ff)).astype(np.int64)
+    length = np.where(lf >= 512, lf - 1024, lf)
+    order = np.lexsort((length, rows[:, 1], rows[:, 0], base))[::-1]  # last key is the primary one
+    srt = rows[order]
+    new = np.ones(len(srt), bool)
+    new[1:] = np.any(srt[1:] != srt[:-1], axis=1)
+    seg = np.cumsum(new) - 1
+    union = srt[new]
+    index = np.empty(len(rows), np.int32)
+    index[order] = seg
+    out, off = [], 0
+    for t in tables:
+        out.append(index[off:off + len(t)])
+        off += len(t)
+    return union, out

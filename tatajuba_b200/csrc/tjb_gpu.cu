@@ -14,6 +14,7 @@
 #include "tjb_bucket.cuh"
 #include "tjb_sort.cuh"
 #include "tjb_reduce.cuh"
+#include "tjb_union.cuh"
 
 #define TJB_VERSION_STR "tatajuba_b200 0.1 (sm_100a)"
 #define TJB_CHUNK_BYTES (64u << 20)      // files path: pinned chunk of decoded reads
@@ -21,10 +22,10 @@
 
 enum KernelId { K_SCAN = 0, K_PLAN, K_PARTITION, K_BUCKET, K_TOTALS, K_PACK, K_COVMAX, K_RECHIST,
                 // global multi-pass path, only for buckets too large for shared memory
-                K_SORT_HIST, K_SORT_SCATTER, K_PSCAN, K_RLE, K_GROUP, K_COUNT };
+                K_SORT_HIST, K_SORT_SCATTER, K_PSCAN, K_RLE, K_GROUP, K_UNION, K_COUNT };
 static const char *kKernelNames[K_COUNT] = {"tjb_scan_kernel", "plan_kernel", "partition_kernel", "bucket_reduce_kernel", "totals_kernel",
                                             "pack_kernel", "cov_max_kernel", "rec_hist_kernel", "rsort_hist_kernel",
-                                            "rsort_scatter_kernel", "pscan_kernels", "rle_kernels", "group_kernels"};
+                                            "rsort_scatter_kernel", "pscan_kernels", "rle_kernels", "group_kernels", "union_kernels"};
 
 struct DevBuf {
   void *p = nullptr;
@@ -490,6 +491,33 @@ static int finalise (tjb_ctx *ctx, const tjb_opts *opt, tjb_counter_out *out)
 
 static void out_reset (tjb_counter_out *out) { memset (out, 0, sizeof (*out)); }
 
+// ---- union of query rows over samples (tjb_union.cuh): pack, LSD sort, heads, emit, index -----------------------
+template <int W>
+static int union_t (tjb_ctx *ctx, const u64 *d_rows, u32 n, int k, u64 *d_union, int64_t *n_union, int *d_index)
+{
+  cudaStream_t st = ctx->stream;
+  TRY (grow_records (ctx, n));
+  TRY (ensure (ctx, ctx->rec_b, (size_t) n * W * 8));
+  TRY (ensure (ctx, ctx->heads, (size_t) n * 4)); TRY (ensure (ctx, ctx->pos, (size_t) n * 4));
+  TRY (ensure (ctx, ctx->ptmp, pscan_tmp_elems (n) * 4 + 64));
+  u64 *a = (u64*) ctx->rec_a.p, *b = (u64*) ctx->rec_b.p, *sorted = nullptr;
+  u32 *heads = (u32*) ctx->heads.p, *pos = (u32*) ctx->pos.p;
+  LAUNCH (K_UNION, (24 + 8 * W) * (size_t) n, (rows_to_rec_kernel<W><<<nblk (n, UNI_THREADS), UNI_THREADS, 0, st>>> (d_rows, n, k, a)));
+  TRY ((radix_sort<W> (ctx, a, b, n, tract_digits (W, k), &sorted)));
+  LAUNCH (K_UNION, 16 * W * (size_t) n, (head_kernel<W, 0><<<nblk (n, RED_THREADS), RED_THREADS, 0, st>>> (sorted, n, heads)));
+  TRY (exclusive_scan (ctx, heads, pos, n, (u32*) ctx->ptmp.p, ctx->d_totals + 0));
+  LAUNCH (K_UNION, (8 * W + 32) * (size_t) n, (union_emit_kernel<W><<<nblk (n, UNI_THREADS), UNI_THREADS, 0, st>>> (sorted, heads, pos, n, ctx->d_totals + 0, k, d_union)));
+  if (d_index)
+    LAUNCH (K_UNION, (24 + 4) * (size_t) n, (union_index_kernel<W><<<nblk (n, UNI_THREADS), UNI_THREADS, 0, st>>> (d_rows, n, k, sorted, heads, pos, ctx->d_totals + 0, d_index)));
+  CU (cudaGetLastError ());
+  u32 h_tot = 0;
+  CU (cudaMemcpyAsync (&h_tot, ctx->d_totals, 4, cudaMemcpyDeviceToHost, st));
+  CU (cudaStreamSynchronize (st));
+  resolve_events (ctx);
+  *n_union = h_tot;
+  return 0;
+}
+
 // ------------------------------------------------------------------------------------------- C ABI ------
 extern "C" {
 
@@ -744,6 +772,35 @@ int tjb_count_sample (const char *const *files, int n_files, const tjb_opts *opt
     cache.m[device] = ctx;
   } else ctx = it->second;
   return tjb_count_sample_files (ctx, files, n_files, opt, out);
+}
+
+// ---- cross-sample exchange: query rows and their union (tjb_union.cuh) ------------------------------------------
+int tjb_query_rows (const tjb_counter_out *in, uint64_t *rows)
+{
+  if (!in || (in->n_idx && (!rows || !in->elem || !in->idx_initial))) return TJB_ERR_ARG;
+  const uint64_t *e = (const uint64_t*) in->elem;
+  for (int32_t g = 0; g < in->n_idx; g++) { // first = longest record of the group (hopo_counter.c:513-520)
+    const uint64_t *r = e + 5 * (size_t) in->idx_initial[g];
+    rows[3 * (size_t) g] = r[0];
+    rows[3 * (size_t) g + 1] = r[1];
+    rows[3 * (size_t) g + 2] = (r[2] & 1) | (((r[2] >> 2) & 0x3ff) << 8); // base:2 length:10 bit-fields
+  }
+  return in->n_idx;
+}
+
+int tjb_union_queries_device (tjb_ctx *ctx, const void *d_rows, int64_t n_rows, int kmer_size, void *d_union, int64_t *n_union, void *d_index)
+{
+  if (!ctx || !n_union || n_rows < 0 || (n_rows && (!d_rows || !d_union))) return TJB_ERR_ARG;
+  if (kmer_size < 2 || kmer_size > 32) { ctx->err = "kmer_size out of range (2..32)"; return TJB_ERR_ARG; }
+  if (n_rows > (int64_t) INT32_MAX) { ctx->err = "more than INT32_MAX query rows"; return TJB_ERR_TOO_LARGE; }
+  *n_union = 0;
+  if (!n_rows) return 0;
+  CU (cudaSetDevice (ctx->device));
+  const int W = tjb_rec_words (kmer_size);
+  if (W != ctx->rec_words) { ctx->rec_words = W; ctx->rec_capacity = ctx->rec_a.cap / (W * sizeof (u64)); }
+  ctx->n_raw_known = 0; // nothing of a previous sample needs to survive a reallocation
+  return W == 2 ? union_t<2> (ctx, (const u64*) d_rows, (u32) n_rows, kmer_size, (u64*) d_union, n_union, (int*) d_index)
+                : union_t<3> (ctx, (const u64*) d_rows, (u32) n_rows, kmer_size, (u64*) d_union, n_union, (int*) d_index);
 }
 
 void tjb_counter_out_free (tjb_counter_out *out)
