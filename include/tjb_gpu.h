@@ -127,6 +127,18 @@ int tjb_query_rows (const tjb_counter_out *in, uint64_t *rows);
 int tjb_union_queries_device (tjb_ctx *ctx, const void *d_rows, int64_t n_rows, int kmer_size, void *d_union,
                               int64_t *n_union, void *d_index);
 
+/* ---- cross-sample merge after the mapper (reference src/genome_set.c:195-289).  Inputs: the per-sample context
+ * tables of the SURVIVING samples (remove_empty_genomes, genome_set.c:132-142, already applied; sample ids are the
+ * compacted ones, :100), concatenated sample after sample, each sorted by location: location (1-D flattened genome
+ * position, context_histogram.h location), base, mode_context_length, and the histogram name ("LEFT-B-RIGHT",
+ * name_stride bytes per row, NUL padded).  Outputs, per element of the merged vector (g_tract_vector concat[],
+ * genome_set.c:250-289): sample, row index inside the sample, tract_id (:208-222, rows compared with the first row of
+ * the current tract by context_histograms_overlap, context_histogram.c:87-110, with -l = levenshtein_distance).
+ * Host-side sequential merge (no device work); returns the number of merged rows or a negative error. */
+int tjb_merge_tracts (int32_t n_samples, const int32_t *n_hist, const int32_t *location, const int32_t *base,
+                      const int32_t *mode_len, const char *names, int32_t name_stride, int32_t levenshtein_distance,
+                      int32_t *out_sample, int32_t *out_index, int32_t *out_tract_id);
+
 /* host FASTQ/FASTA(.gz) decoder on its own (kseq semantics): appends "SEQ\n" per record to dst (capacity cap);
  * returns bytes written (0 = end of file), <0 on error.  Exposed for tests and for callers that feed
  * tjb_count_sample_host themselves. */

@@ -219,3 +219,28 @@ def union_oracle(tables):
         out.append(index[off:off + len(t)])
         off += len(t)
     return union, out
+
+
+def reference_merge_tracts(tables, levenshtein_distance=2):
+    """the compiled reference's own cross-sample merge (oracle/shim ref_merge_tracts); same inputs / outputs as
+    tatajuba_b200.genome_set.merge_tracts"""
+    lib = C.CDLL(REF_SO)
+    n_hist = np.array([len(t["location"]) for t in tables], np.int32)
+    total = int(n_hist.sum())
+    cat = lambda k: np.ascontiguousarray(np.concatenate([np.asarray(t[k], np.int32) for t in tables]))  # noqa: E731
+    loc, base, mlen = cat("location"), cat("base"), cat("mode_context_length")
+    stride = max(t["name"].shape[1] for t in tables if len(t["location"]))
+    names = np.zeros((total, stride), np.uint8)
+    off = 0
+    for t in tables:
+        n = len(t["location"])
+        if n:
+            names[off:off + n, : t["name"].shape[1]] = np.asarray(t["name"]).view(np.uint8).reshape(n, -1)
+        off += n
+    out = [np.empty(total, np.int32) for _ in range(3)]
+    p = lambda a: C.c_void_p(a.ctypes.data)  # noqa: E731
+    lib.ref_merge_tracts.restype = C.c_int
+    rc = lib.ref_merge_tracts(C.c_int(len(tables)), p(n_hist), p(loc), p(base), p(mlen), p(names), C.c_int(stride),
+                              C.c_int(levenshtein_distance), p(out[0]), p(out[1]), p(out[2]))
+    assert rc == total
+    return tuple(out)

@@ -149,3 +149,60 @@ void ref_dump_free (ref_dump_t *d)
 }
 
 size_t ref_sizeof_hopo_element (void) { return sizeof (hopo_element); }
+
+/* ---- cross-sample merge (genome_set.c:195-289): the reference's own g_tract_vector_concatenate_tracts() and
+ * context_histograms_overlap() run on context_histograms built from plain arrays.  The tract_id loop below follows
+ * genome_set.c:208-222 line by line; the summary statistics that loop also feeds (update_g_tract_summary_...) need
+ * complete mapped histograms and are not part of the merge order / tract ids checked here. */
+#include "genome_set.h"
+int
+ref_merge_tracts (int n_genome, const int *n_hist, const int *location, const int *base, const int *mode_len,
+                  const char *names, int name_stride, int lev_distance, int *out_genome, int *out_index, int *out_tract_id)
+{
+  tatajuba_options_t opt = make_opt (25, 4, 5, 1, 0);
+  opt.levenshtein_distance = lev_distance;
+  genomic_context_list_t *genome = (genomic_context_list_t*) malloc ((size_t) n_genome * sizeof (genomic_context_list_t));
+  int off = 0, n_total = 0;
+  for (int g = 0; g < n_genome; g++) { /* samples are already compacted (remove_empty_genomes, genome_set.c:97) */
+    genome[g] = (genomic_context_list_t) calloc (1, sizeof (struct genomic_context_list_struct));
+    genome[g]->opt = opt;
+    genome[g]->n_hist = n_hist[g];
+    genome[g]->hist = (context_histogram_t*) malloc ((size_t) (n_hist[g] ? n_hist[g] : 1) * sizeof (context_histogram_t));
+    for (int j = 0; j < n_hist[g]; j++, off++) {
+      context_histogram_t ch = (context_histogram_t) calloc (1, sizeof (struct context_histogram_struct));
+      ch->location = location[off];
+      ch->base = base[off];
+      ch->mode_context_length = mode_len[off];
+      ch->name = strndup (names + (size_t) off * name_stride, name_stride);
+      ch->index = g;        /* genome_set.c:100 */
+      ch->n_tracts = j;     /* stash: index inside the sample (untouched by the functions under test) */
+      genome[g]->hist[j] = ch;
+    }
+    n_total += n_hist[g];
+  }
+  g_tract_vector_t tract = (g_tract_vector_t) calloc (1, sizeof (struct g_tract_vector_struct));
+  g_tract_vector_concatenate_tracts (tract, genome, n_genome);
+  if (tract->n_concat > 0) {
+    int i, prev, lev = 0;
+    tract->concat[0]->tract_id = 0;
+    for (prev = 0, i = 1; i < tract->n_concat; i++) {
+      bool is_same = context_histograms_overlap (tract->concat[i], tract->concat[prev], &lev, opt);
+      if (!is_same) { tract->concat[i]->tract_id = tract->concat[prev]->tract_id + 1; prev = i; }
+      else tract->concat[i]->tract_id = tract->concat[prev]->tract_id;
+    }
+  }
+  for (int i = 0; i < tract->n_concat; i++) {
+    out_genome[i] = tract->concat[i]->index;
+    out_index[i] = tract->concat[i]->n_tracts;
+    out_tract_id[i] = tract->concat[i]->tract_id;
+  }
+  int n_concat = tract->n_concat;
+  free (tract->concat); free (tract);
+  for (int g = 0; g < n_genome; g++) {
+    for (int j = 0; j < genome[g]->n_hist; j++) { free (genome[g]->hist[j]->name); free (genome[g]->hist[j]); }
+    free (genome[g]->hist); free (genome[g]);
+  }
+  free (genome);
+  (void) n_total;
+  return n_concat;
+}

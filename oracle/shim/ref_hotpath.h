@@ -32,6 +32,14 @@ int ref_hotpath_run_buffer (const char *buf, size_t n_bytes, int kmer_size, int 
 void ref_dump_free (ref_dump_t *d);
 size_t ref_sizeof_hopo_element (void);
 
+/* Cross-sample merge: the reference's g_tract_vector_concatenate_tracts() (genome_set.c:250-289) and
+ * context_histograms_overlap() (context_histogram.c:87-110) on per-sample histogram tables given as flat arrays
+ * (samples concatenated, each sorted by location; names = name_stride bytes per histogram).  Outputs, per element of
+ * the merged vector: sample, index inside the sample, tract_id (genome_set.c:208-222).  Returns n_concat. */
+int ref_merge_tracts (int n_genome, const int *n_hist, const int *location, const int *base, const int *mode_len,
+                      const char *names, int name_stride, int lev_distance, int *out_genome, int *out_index,
+                      int *out_tract_id);
+
 #ifdef __cplusplus
 }
 #endif

@@ -16,7 +16,7 @@ EXPORTS = [
     "tjb_version", "tjb_strerror", "tjb_ctx_last_error", "tjb_ctx_create", "tjb_ctx_destroy", "tjb_ctx_stream",
     "tjb_ctx_set_profiling", "tjb_ctx_kernel_stats", "tjb_ctx_reset_kernel_stats", "tjb_ctx_launch_count",
     "tjb_count_sample_files", "tjb_count_sample_host", "tjb_count_sample_device", "tjb_count_sample",
-    "tjb_counter_out_free", "tjb_query_rows", "tjb_union_queries_device", "tjb_reader_open", "tjb_reader_fill", "tjb_reader_close",
+    "tjb_counter_out_free", "tjb_query_rows", "tjb_union_queries_device", "tjb_merge_tracts", "tjb_reader_open", "tjb_reader_fill", "tjb_reader_close",
 ]
 
 
@@ -81,6 +81,7 @@ def load():
     lib.tjb_counter_out_free.restype = None
     lib.tjb_query_rows.argtypes = [pout, vp]
     lib.tjb_union_queries_device.argtypes = [vp, vp, i64, i32, vp, C.POINTER(i64), vp]
+    lib.tjb_merge_tracts.argtypes = [i32, vp, vp, vp, vp, vp, i32, i32, vp, vp, vp]
     lib.tjb_reader_open.restype = vp
     lib.tjb_reader_open.argtypes = [cp]
     lib.tjb_reader_fill.restype = i64

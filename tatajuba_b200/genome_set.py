@@ -112,3 +112,43 @@ def union_queries(ctx, tables, kmer_size):
         per_sample.append(index[off:off + m])
         off += m
     return union, per_sample
+
+
+def surviving_samples(alive):
+    """remove_empty_genomes + index labelling (src/genome_set.c:97-100, 132-142): samples without any mapped HT are
+    dropped BEFORE sample ids are assigned, so ids depend on which samples survive.  alive: one flag per sample.
+    Returns {original sample -> compacted id}."""
+    ids, j = {}, 0
+    for s, a in enumerate(alive):
+        if a:
+            ids[s] = j
+            j += 1
+    if not ids:
+        raise RuntimeError("No sample has any tract mapped to reference genome")  # genome_set.c:137
+    return ids
+
+
+def merge_tracts(tables, levenshtein_distance=2):
+    """g_tract_vector_concatenate_tracts + tract ids (src/genome_set.c:195-289) over the per-sample post-mapping tables
+    of the surviving samples.  tables: list of dicts with int32 arrays `location` (ascending), `base`,
+    `mode_context_length` and a bytes array `name` of shape (n, stride).  Returns (sample, index, tract_id)."""
+    lib = _lib.load()
+    n_hist = np.array([len(t["location"]) for t in tables], np.int32)
+    total = int(n_hist.sum())
+    cat = lambda k, dt: np.ascontiguousarray(np.concatenate([np.asarray(t[k], dt) for t in tables]) if total else np.zeros(0, dt))  # noqa: E731
+    loc, base, mlen = cat("location", np.int32), cat("base", np.int32), cat("mode_context_length", np.int32)
+    stride = max([t["name"].shape[1] for t in tables if len(t["location"])] or [1])
+    names = np.zeros((total, stride), np.uint8)
+    off = 0
+    for t in tables:
+        n = len(t["location"])
+        if n:
+            names[off:off + n, : t["name"].shape[1]] = np.asarray(t["name"]).view(np.uint8).reshape(n, -1)
+        off += n
+    out = [np.empty(total, np.int32) for _ in range(3)]
+    p = lambda a: C.c_void_p(a.ctypes.data)  # noqa: E731
+    rc = lib.tjb_merge_tracts(len(tables), p(n_hist), p(loc), p(base), p(mlen), p(names), stride, int(levenshtein_distance),
+                              p(out[0]), p(out[1]), p(out[2]))
+    if rc != total:
+        raise RuntimeError(f"tjb_merge_tracts: {rc}")
+    return tuple(out)

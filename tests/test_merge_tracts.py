@@ -1,0 +1,52 @@
+"""Cross-sample merge (reference src/genome_set.c:195-289): tjb_merge_tracts vs golden vectors made by the compiled
+reference, and vs the compiled reference itself when oracle/_ref is available.  Host-only (no GPU needed)."""
+import os
+import sys
+
+import numpy as np
+import pytest
+
+sys.path.insert(0, os.path.dirname(__file__))
+from merge_cases import CASES, make_tables  # noqa: E402
+from oracle import pyoracle  # noqa: E402
+from tatajuba_b200 import genome_set  # noqa: E402
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden", "merge_tracts.npz")
+
+
+@pytest.mark.parametrize("case", CASES)
+@pytest.mark.parametrize("lev", [2, 0])
+def test_merge_matches_golden(built, case, lev):
+    seed, ns, nsites = case
+    z = np.load(GOLD)
+    s, i, t = genome_set.merge_tracts(make_tables(seed, ns, nsites), lev)
+    assert np.array_equal(s, z[f"c{seed}_l{lev}_sample"])
+    assert np.array_equal(i, z[f"c{seed}_l{lev}_index"])
+    assert np.array_equal(t, z[f"c{seed}_l{lev}_tract"])
+
+
+@pytest.mark.parametrize("seed", range(20, 30))
+def test_merge_matches_compiled_reference(reference, seed):
+    rng = np.random.default_rng(seed)
+    tables = make_tables(seed, int(rng.integers(1, 9)), int(rng.integers(5, 400)), k=int(rng.integers(2, 33)))
+    lev = int(rng.integers(0, 4))
+    got = genome_set.merge_tracts(tables, lev)
+    want = pyoracle.reference_merge_tracts(tables, lev)
+    for a, b in zip(got, want):
+        assert np.array_equal(a, b)
+
+
+def test_merge_properties(built):
+    tables = make_tables(9, 6, 500)
+    s, i, t = genome_set.merge_tracts(tables)
+    loc = np.array([tables[a]["location"][b] for a, b in zip(s, i)])
+    assert np.all(np.diff(loc) >= 0)                      # ordered by location
+    assert np.all(np.diff(t) >= 0) and t[0] == 0 and np.all(np.diff(t) <= 1)
+    seen = sorted(zip(s.tolist(), i.tolist()))
+    assert seen == [(a, b) for a in range(len(tables)) for b in range(len(tables[a]["location"]))]  # a permutation
+
+
+def test_surviving_samples():
+    assert genome_set.surviving_samples([True, False, True, True]) == {0: 0, 2: 1, 3: 2}
+    with pytest.raises(RuntimeError):
+        genome_set.surviving_samples([False, False])
