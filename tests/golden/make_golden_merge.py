@@ -17,5 +17,5 @@ for seed, ns, nsites in CASES:
     for lev in (2, 0):
         s, i, t = pyoracle.reference_merge_tracts(make_tables(seed, ns, nsites), lev)
         out[f"c{seed}_l{lev}_sample"], out[f"c{seed}_l{lev}_index"], out[f"c{seed}_l{lev}_tract"] = s, i, t
-np.savez_compressed(os.path.join(HERE, "merge_tracts.npz"), **out)
+np.savez_compressed(os.path.join(HERE, "merge", "merge_tracts.npz"), **out)
 print("wrote", len(out), "arrays")

@@ -11,7 +11,7 @@ from merge_cases import CASES, make_tables  # noqa: E402
 from oracle import pyoracle  # noqa: E402
 from tatajuba_b200 import genome_set  # noqa: E402
 
-GOLD = os.path.join(os.path.dirname(__file__), "golden", "merge_tracts.npz")
+GOLD = os.path.join(os.path.dirname(__file__), "golden", "merge", "merge_tracts.npz")
 
 
 @pytest.mark.parametrize("case", CASES)
