@@ -206,6 +206,22 @@ def main():
     ms_e2e = max_over_ranks(e0.elapsed_time(e1))
     d2h = 40 * hh.n_elem + 8 * hh.n_idx + 64
 
+    # ---- cross-sample exchange: query rows -> allgather over the ranks -> union on the GPU ---------
+    from tatajuba_b200 import genome_set
+    exch = []
+    for _ in range(3):
+        barrier()
+        t0 = time.perf_counter()
+        rows = genome_set.query_rows(hh)
+        tables = genome_set.allgather_tables({rank: rows}, world)
+        union, _index = genome_set.union_queries(ctx, tables, K)
+        torch.cuda.synchronize()
+        exch.append((time.perf_counter() - t0) * 1e3)
+    ms_exchange = max_over_ranks(min(exch))
+    exchange = {"ms": ms_exchange, "samples": world, "rows": int(sum(len(t) for t in tables)), "n_union": int(len(union)),
+                "collective": "none (1 rank)" if world == 1 else "nccl all_gather_into_tensor x2",
+                "note": "outside the timed steps: once per run, after every sample has been counted"}
+
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -233,7 +249,13 @@ def main():
                      "share_of_kernel_time": scan["ms_total"] / kernel_ms if kernel_ms else None},
         "kernels": {s["name"]: {"launches": s["launches"], "ms_total": round(s["ms_total"], 4)} for s in stats},
         "clocks": clocks,
+        "exchange": exchange,
     }
+    tp = os.path.join(ROOT, "profiles", "scan_traffic.json")  # dram bytes of one scan launch from an ncu --set full capture
+    if os.path.exists(tp):
+        tr = json.load(open(tp))
+        line["roofline"]["traffic"] = tr["dram_bytes_read"] + tr["dram_bytes_write"]
+        line["roofline"]["traffic_source"] = tr.get("source")
     if not args.no_cpu_baseline:
         line["cpu_baseline"] = cpu_baseline(buf, min(CPU_SAMPLE_READS, n_reads))
     print(json.dumps(line))
