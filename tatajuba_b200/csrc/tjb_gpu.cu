@@ -55,6 +55,7 @@ struct tjb_ctx {
   unsigned long long n_raw_known = 0, n_skip_known = 0;
   const uint8_t *pend_ptr = nullptr; size_t pend_len = 0; bool pend = false; // scan launched, overflow not checked yet
   unsigned long long *d_counters = nullptr; // [0] = n_raw, [1] = skipped non-ACGTU runs
+  u32 *d_tile_ctr = nullptr;                // scan kernel: next window to hand out
   u32 *d_totals = nullptr;                  // small device scalars (global multi-pass path)
   int *d_cov = nullptr;
   // bucketed reduce: bin histogram (filled by the scan), splitters, per-bucket results
@@ -246,13 +247,14 @@ static int launch_scan (tjb_ctx *ctx, const uint8_t *d_seqs, size_t n, const tjb
   long long n_tiles = (long long) ((n + SW_TILE - 1) / SW_TILE); // one window of SW_TILE owned bytes per warp at a time
   if (!n_tiles) return 0;
   int min_len = opt->min_tract_size < 2 ? 2 : opt->min_tract_size;
+  CU (cudaMemsetAsync (ctx->d_tile_ctr, 0, sizeof (u32), ctx->stream)); // window tickets of this launch
   long long want = (n_tiles + SCAN_WARPS - 1) / SCAN_WARPS;
   long long grid = want < (long long) ctx->sm_count * SCAN_CTAS_PER_SM ? want : (long long) ctx->sm_count * SCAN_CTAS_PER_SM;
   // algorithmic bytes of this launch: every sequence byte read once (+ 8W bytes per emitted record, added at finalise)
   if (ctx->rec_words == 2)
-    LAUNCH (K_SCAN, n, (tjb_scan_kernel<2><<<(u32) grid, SCAN_THREADS, scan_smem_bytes<2> (), ctx->stream>>> (d_seqs, (long long) n, opt->kmer_size, min_len, (u64*) ctx->rec_a.p, ctx->rec_capacity, ctx->d_counters, n_tiles, ctx->d_bin_hist, ctx->bin_bits)));
+    LAUNCH (K_SCAN, n, (tjb_scan_kernel<2><<<(u32) grid, SCAN_THREADS, scan_smem_bytes<2> (), ctx->stream>>> (d_seqs, (long long) n, opt->kmer_size, min_len, (u64*) ctx->rec_a.p, ctx->rec_capacity, ctx->d_counters, n_tiles, ctx->d_bin_hist, ctx->bin_bits, ctx->d_tile_ctr)));
   else
-    LAUNCH (K_SCAN, n, (tjb_scan_kernel<3><<<(u32) grid, SCAN_THREADS, scan_smem_bytes<3> (), ctx->stream>>> (d_seqs, (long long) n, opt->kmer_size, min_len, (u64*) ctx->rec_a.p, ctx->rec_capacity, ctx->d_counters, n_tiles, ctx->d_bin_hist, ctx->bin_bits)));
+    LAUNCH (K_SCAN, n, (tjb_scan_kernel<3><<<(u32) grid, SCAN_THREADS, scan_smem_bytes<3> (), ctx->stream>>> (d_seqs, (long long) n, opt->kmer_size, min_len, (u64*) ctx->rec_a.p, ctx->rec_capacity, ctx->d_counters, n_tiles, ctx->d_bin_hist, ctx->bin_bits, ctx->d_tile_ctr)));
   CU (cudaGetLastError ());
   return 0;
 }
@@ -591,6 +593,7 @@ int tjb_ctx_create (int device, tjb_ctx **pctx)
   if ((e = cudaStreamCreateWithFlags (&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) return fail (e);
   if ((e = cudaMalloc (&ctx->d_counters, 2 * sizeof (unsigned long long))) != cudaSuccess) return fail (e);
   if ((e = cudaMalloc (&ctx->d_totals, 16 * sizeof (u32))) != cudaSuccess) return fail (e);
+  if ((e = cudaMalloc (&ctx->d_tile_ctr, sizeof (u32))) != cudaSuccess) return fail (e);
   if ((e = cudaMalloc (&ctx->d_cov, sizeof (int))) != cudaSuccess) return fail (e);
   if ((e = cudaStreamCreateWithFlags (&ctx->copy_stream, cudaStreamNonBlocking)) != cudaSuccess) return fail (e);
   if ((e = cudaMalloc (&ctx->d_bin_hist, TJB_MAX_BINS * sizeof (u32))) != cudaSuccess) return fail (e);
@@ -627,6 +630,7 @@ void tjb_ctx_destroy (tjb_ctx *ctx)
   for (int i = 0; i < 2; i++) { if (ctx->h_pinned[i]) cudaFreeHost (ctx->h_pinned[i]); if (ctx->h_free[i]) cudaEventDestroy (ctx->h_free[i]); }
   if (ctx->d_counters) cudaFree (ctx->d_counters);
   if (ctx->d_totals) cudaFree (ctx->d_totals);
+  if (ctx->d_tile_ctr) cudaFree (ctx->d_tile_ctr);
   if (ctx->d_cov) cudaFree (ctx->d_cov);
   void *small[] = {ctx->d_bin_hist, ctx->d_bkt_start, ctx->d_cursor, ctx->d_koff, ctx->d_ioff, ctx->d_lut, ctx->d_bstat, ctx->d_meta};
   for (void *q : small) if (q) cudaFree (q);

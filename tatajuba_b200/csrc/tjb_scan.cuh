@@ -54,10 +54,10 @@
 #endif
 #define SCAN_GRAY_MUL 0x00820820u     // ((w & 0x06060606) * this) >> 24 = the four 2-bit codes of w's bytes
 #define SCAN_GRAY_LUT 0x47544341u     // code -> byte: 'A' 'C' 'T' 'G'
-// PRMT look-up on (code << 1 | non-letter): letters A C T G in the even slots; odd slots: only code 1 can be a
+// PRMT look-up on (code << 1 | letter): letters A C T G in the odd slots; even slots: only code 1 can be a
 // non-letter, the separator 0x0A; the other three hold a byte whose own code differs from the slot's (never equal)
-#define SCAN_LUT_A 0x0A43FF41u
-#define SCAN_LUT_B 0x00470054u
+#define SCAN_LUT_A 0x430A41FFu
+#define SCAN_LUT_B 0x47005400u
 
 template <int W> struct ScanWarpSmem {
   uint8_t raw[2][SW_WIN];             // two stages of sequence bytes
@@ -96,10 +96,16 @@ __device__ __forceinline__ void mbar_wait (unsigned long long *b, u32 parity)
   asm volatile ("{\n .reg .pred p;\n WAIT_%=:\n mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n @p bra DONE_%=;\n bra WAIT_%=;\n DONE_%=:\n}"
                 :: "r"(smem_u32 (b)), "r"(parity) : "memory");
 }
-__device__ __forceinline__ int dp4a_su (u32 a_signed, u32 b_unsigned, int c)
+__device__ __forceinline__ int dp4a_us (u32 a_unsigned, u32 b_signed, int c)
 {
   int d;
-  asm ("dp4a.s32.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a_signed), "r"(b_unsigned), "r"(c));
+  asm ("dp4a.u32.s32 %0, %1, %2, %3;" : "=r"(d) : "r"(a_unsigned), "r"(b_signed), "r"(c));
+  return d;
+}
+__device__ __forceinline__ u32 mad_hi (u32 a, u32 b, u32 c) // IMAD.HI: right shifts on the FMA pipe
+{
+  u32 d;
+  asm ("mad.hi.u32 %0, %1, %2, %3;" : "=r"(d) : "r"(a), "r"(b), "r"(c));
   return d;
 }
 // mask of the x lowest bits, any x (<= 0 -> 0, >= 32 -> all)
@@ -137,7 +143,7 @@ template <int W>
 __global__ void __launch_bounds__ (SCAN_THREADS, SCAN_CTAS_PER_SM)
 tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_len, u64 *__restrict__ out,
                  unsigned long long capacity, unsigned long long *__restrict__ counters, long long n_tiles,
-                 u32 *__restrict__ bin_hist, int bin_bits)
+                 u32 *__restrict__ bin_hist, int bin_bits, u32 *__restrict__ tile_ctr)
 {
   extern __shared__ __align__ (16) unsigned char scan_smem[];
   ScanWarpSmem<W> *S = reinterpret_cast<ScanWarpSmem<W>*> (scan_smem) + (threadIdx.x >> 5);
@@ -158,7 +164,6 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
   const u64 kmask = (k == 32) ? ~0ULL : ((1ULL << (2 * k)) - 1);
   __syncthreads (); // the only block-wide barrier: LUTs and mbarriers are set up
 
-  const long long n_warps = (long long) gridDim.x * SCAN_WARPS;
   u32 nrec = 0, nskip = 0, parity = 0;
   u32 head = 0, tail = 0, n_old = 0; // candidate FIFO; n_old = entries that belong to the previous window
 
@@ -295,20 +300,24 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
   };
 
   // ---- main loop: this warp's windows, window t+n_warps in flight while window t is processed ------------------
-  long long t = (long long) blockIdx.x * SCAN_WARPS + (tid >> 5);
-  const long long stride = n_warps * SW_TILE;
-  long long g0 = t * SW_TILE - SW_HALO_L;
+  // windows are handed out by a global ticket counter (SMs on the two dies do not run at the same speed, a static
+  // deal leaves a tail); the ticket of the window after next is requested one window ahead, its latency is hidden
+  u32 t_cur = 0, t_nxt = 0, t_fut = 0;
+  if (lane == 0) t_cur = atomicAdd (tile_ctr, 2u);
+  t_cur = __shfl_sync (0xffffffffu, t_cur, 0);
+  t_nxt = t_cur + 1;
+  long long g0 = (long long) t_cur * SW_TILE - SW_HALO_L, old_g0 = 0;
   int st = 0;
   bool in_cur = false;
-  if (t < n_tiles) { in_cur = interior (t); stage_tile (t, 0); }
+  if (t_cur < n_tiles) { in_cur = interior (t_cur); stage_tile (t_cur, 0); }
   const u32 hdr = (u32) lane << 5;
-  for (; t < n_tiles; t += n_warps, g0 += stride, st ^= 1) {
+  for (; t_cur < n_tiles; st ^= 1) {
+    if (lane == 0) t_fut = atomicAdd (tile_ctr, 1u);
     bool in_next = false;
-    if (t + n_warps < n_tiles) { in_next = interior (t + n_warps); stage_tile (t + n_warps, st ^ 1); }
+    if (t_nxt < n_tiles) { in_next = interior (t_nxt); stage_tile (t_nxt, st ^ 1); }
     if (in_cur) { mbar_wait (&S->bar[st], (parity >> st) & 1); parity ^= 1u << st; }
     else __syncwarp ();
     in_cur = in_next;
-    const long long old_g0 = g0 - stride;
     u32 *codes = S->codes[st];
     u32 c[SW_ROWS];
     {
@@ -323,23 +332,21 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
         const u32 m0 = w0 & 0x06060606u, m1 = w1 & 0x06060606u, m2 = w2 & 0x06060606u, m3 = w3 & 0x06060606u;
         const u32 p0 = m0 * SCAN_GRAY_MUL, p1 = m1 * SCAN_GRAY_MUL, p2 = m2 * SCAN_GRAY_MUL, p3 = m3 * SCAN_GRAY_MUL;
         c[row] = __byte_perm (__byte_perm (p0, p1, 0x0073), __byte_perm (p2, p3, 0x0073), 0x5410);
-        // letters have bit 6 set: 0xFF per letter byte, 0x00 per non-letter byte (sign-replicating PRMT on 2w)
-        const u32 e0 = prmt (w0 + w0, 0, 0xBA98), e1 = prmt (w1 + w1, 0, 0xBA98);
-        const u32 e2 = prmt (w2 + w2, 0, 0xBA98), e3 = prmt (w3 + w3, 0, 0xBA98);
-        // look-up selectors: code << 1 | non-letter, the nibbles of two words interleaved in one register
-        const u32 s0 = m0 | (~e0 & 0x01010101u), s1 = m1 | (~e1 & 0x01010101u);
-        const u32 s2 = m2 | (~e2 & 0x01010101u), s3 = m3 | (~e3 & 0x01010101u);
-        const u32 z01 = s1 * 16u + s0, z23 = s3 * 16u + s2;
+        // letters have bit 6 set.  Look-up selectors: code << 1 | letter, the nibbles of two words interleaved in one
+        // register; the flag bits are moved by multiply-high (FMA pipe), the integer pipe is the bottleneck
+        const u32 a0 = w0 & 0x40404040u, a1 = w1 & 0x40404040u, a2 = w2 & 0x40404040u, a3 = w3 & 0x40404040u;
+        const u32 z01 = (m1 * 16u + m0) | mad_hi (a1, 1u << 30, __umulhi (a0, 1u << 26));
+        const u32 z23 = (m3 * 16u + m2) | mad_hi (a3, 1u << 30, __umulhi (a2, 1u << 26));
         const u32 xa = prmt (SCAN_LUT_A, SCAN_LUT_B, z01), xb = prmt (SCAN_LUT_A, SCAN_LUT_B, z01 >> 16);
         const u32 xc = prmt (SCAN_LUT_A, SCAN_LUT_B, z23), xd = prmt (SCAN_LUT_A, SCAN_LUT_B, z23 >> 16);
         // the bytes their codes stand for, against the bytes themselves: sum of squared differences over the group
         const u32 d0 = w0 ^ prmt (xa, xb, 0x6420), d1 = w1 ^ prmt (xa, xb, 0x7531);
         const u32 d2 = w2 ^ prmt (xc, xd, 0x6420), d3 = w3 ^ prmt (xc, xd, 0x7531);
         const u32 acc = __dp4a (d0, d0, __dp4a (d1, d1, __dp4a (d2, d2, __dp4a (d3, d3, 0u))));
-        // bit j of the mask = byte j is a non-letter: 255 - sum of the weights of the letters (signed -1 bytes)
-        const int lo8 = dp4a_su (e1, 0x80402010u, dp4a_su (e0, 0x08040201u, 255));
-        const int hi8 = dp4a_su (e3, 0x80402010u, dp4a_su (e2, 0x08040201u, 255));
-        nl16[grp] = (unsigned short) (hi8 * 256 + lo8);
+        // bit j of the mask = byte j is a non-letter: 64 * (255 - sum of the weights of the letters), bytes are 0x40 / 0
+        const int lo8 = dp4a_us (a1, 0x80C0E0F0u, dp4a_us (a0, 0xF8FCFEFFu, 255 * 64));
+        const int hi8 = dp4a_us (a3, 0x80C0E0F0u, dp4a_us (a2, 0xF8FCFEFFu, 255 * 64));
+        nl16[grp] = (unsigned short) __umulhi ((u32) (hi8 * 256 + lo8), 1u << 26);
         codes[grp] = c[row];
         const u32 bb = __ballot_sync (0xffffffffu, acc != 0);
         if (lane == 0) S->bad[st][row] = bb;
@@ -408,10 +415,14 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
       if (lane < (int) cnt) S->cand[lane] = v;
       head = 0; tail = cnt; n_old = cnt;
     }
+    old_g0 = g0;
+    t_cur = t_nxt;
+    t_nxt = __shfl_sync (0xffffffffu, t_fut, 0);
+    g0 = (long long) t_cur * SW_TILE - SW_HALO_L;
     __syncwarp (); // every lane is done with the other stage's arrays and this stage's bytes are consumed
   }
   if (tail != head) // what is left belongs to the last window, whose bytes are still staged
-    process_batch (lane < (int) (tail - head) ? (int) S->cand[head + lane] : -1, st ^ 1, g0 - stride, 0);
+    process_batch (lane < (int) (tail - head) ? (int) S->cand[head + lane] : -1, st ^ 1, old_g0, 0);
   if (nrec) flush ();
 #pragma unroll
   for (int d = 16; d; d >>= 1) nskip += __shfl_xor_sync (0xffffffffu, nskip, d);
