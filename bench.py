@@ -180,7 +180,8 @@ def main():
     ctx.set_profiling(2)
     ctx.reset_kernel_stats()
     sampler = ClockSampler(local_rank)
-    sampler.start()
+    if rank == 0:  # one poller per job: 8 nvidia-smi loops would steal host cores from the ranks' launch threads
+        sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     e0.record(stream)
@@ -189,7 +190,7 @@ def main():
     e1.record(stream)
     barrier()
     ms = max_over_ranks(e0.elapsed_time(e1))
-    clocks = sampler.summary()
+    clocks = sampler.summary() if rank == 0 else None
     stats = ctx.kernel_stats()
     launches = ctx.launch_count()
     ctx.set_profiling(0)
