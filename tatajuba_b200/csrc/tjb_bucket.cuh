@@ -27,7 +27,8 @@
 #define BK_CAP (BK_THREADS * BK_IPT) // records per on-chip bucket
 #define BK_CAPH (BK_CAP / 2)
 #define PLAN_THREADS 1024
-#define TJB_MAX_BIN_BITS 16
+#define TJB_MAX_BIN_BITS 20
+#define PLAN_REG_BIN_BITS 16 // up to this many bits the planning CTA keeps its bins in registers (plan_kernel), above: plan_big_kernel
 #define TJB_MAX_BINS (1 << TJB_MAX_BIN_BITS)
 #define BK_CURSOR_STRIDE 32 // one partition cursor per 128-byte line: L2 atomics serialise per sector, not per address
 
@@ -36,7 +37,7 @@ enum { META_NBUCKETS = 0, META_NOVERSIZE = 1, META_TICKET = 2, META_N = 3, META_
 
 struct DigitList { int n; unsigned char word[28], shift[28], nbits[28]; };
 
-// bin = top F bits of the context (base, ctx0[, ctx1]); F <= 16
+// bin = top F bits of the context (base, ctx0[, ctx1]); F <= TJB_MAX_BIN_BITS
 template <int W> __device__ __forceinline__ u32 rec_bin (const Rec<W> &r, int k, int F);
 template <> __device__ __forceinline__ u32 rec_bin<2> (const Rec<2> &r, int k, int F)
 {
@@ -97,7 +98,7 @@ rec_hist_kernel (const u64 *__restrict__ recs, const unsigned long long *__restr
 template <int IPT>
 __global__ void __launch_bounds__ (PLAN_THREADS)
 plan_kernel (const u32 *__restrict__ bin_hist, int F, const unsigned long long *__restrict__ counters, unsigned long long capacity,
-             u32 *__restrict__ bkt_start, unsigned short *__restrict__ lut, u32 *__restrict__ cursor, u32 *__restrict__ meta)
+             u32 *__restrict__ bkt_start, u32 *__restrict__ lut, u32 *__restrict__ cursor, u32 *__restrict__ meta, u32 max_buckets)
 {
   __shared__ u32 s_warp[PLAN_THREADS / 32 + 1];
   const u32 NB = 1u << F;
@@ -144,24 +145,70 @@ plan_kernel (const u32 *__restrict__ bin_hist, int F, const unsigned long long *
 #pragma unroll
     for (int i = IPT - 1; i >= 0; i--) {
       const bool head = (t == 0 && i == IPT - 1) || (p / BK_CAPH != (p - hp) / BK_CAPH);
-      if (head) { bkt_start[b] = p; cursor[(size_t) b * BK_CURSOR_STRIDE] = p; b++; }
+      // (more heads than max_buckets only after a record-array overflow: the sample is redone anyway)
+      if (head) { if (b < max_buckets) { bkt_start[b] = p; cursor[(size_t) b * BK_CURSOR_STRIDE] = p; } b++; }
       hp = h[i]; p += h[i];
-      h[i] = b - 1; // bucket of bin lo + i (a range that does not start with a head continues bucket b - 1)
+      h[i] = b - 1 < max_buckets ? b - 1 : max_buckets - 1; // bucket of bin lo + i (a range that does not start with a head continues bucket b - 1)
     }
-    if (IPT >= 8) { // 16-byte stores of the bin -> bucket table
+    if (IPT >= 4) { // 16-byte stores of the bin -> bucket table
 #pragma unroll
-      for (int i = 0; i < IPT / 8; i++) {
-        uint4 v;
-        v.x = h[8 * i] | (h[8 * i + 1] << 16); v.y = h[8 * i + 2] | (h[8 * i + 3] << 16);
-        v.z = h[8 * i + 4] | (h[8 * i + 5] << 16); v.w = h[8 * i + 6] | (h[8 * i + 7] << 16);
-        *reinterpret_cast<uint4*> (lut + lo + 8 * i) = v;
-      }
+      for (int i = 0; i < IPT / 4; i++)
+        *reinterpret_cast<uint4*> (lut + lo + 4 * i) = make_uint4 (h[4 * i], h[4 * i + 1], h[4 * i + 2], h[4 * i + 3]);
     } else {
 #pragma unroll
-      for (int i = 0; i < IPT; i++) lut[lo + i] = (unsigned short) h[i];
+      for (int i = 0; i < IPT; i++) lut[lo + i] = h[i];
     }
   }
   if (t == 0) {
+    if (nb_total > max_buckets) nb_total = max_buckets;
+    bkt_start[nb_total] = total;
+    meta[META_NBUCKETS] = nb_total;
+    meta[META_NOVERSIZE] = 0;
+    meta[META_TICKET] = 0;
+    unsigned long long n = counters[0] < capacity ? counters[0] : capacity;
+    meta[META_N] = (u32) n;
+  }
+}
+
+// The same plan for more bins than fit in the registers of one CTA (F > PLAN_REG_BIN_BITS: deep or very large
+// samples, where 2^16 bins would hold more than BK_CAPH records each): every thread walks its 2^F / 1024 bins three
+// times from L2 (sum, count heads, emit) instead of keeping them in registers.
+__global__ void __launch_bounds__ (PLAN_THREADS)
+plan_big_kernel (const u32 *__restrict__ bin_hist, int F, const unsigned long long *__restrict__ counters, unsigned long long capacity,
+                 u32 *__restrict__ bkt_start, u32 *__restrict__ lut, u32 *__restrict__ cursor, u32 *__restrict__ meta, u32 max_buckets)
+{
+  __shared__ u32 s_warp[PLAN_THREADS / 32 + 1];
+  const u32 NB = 1u << F, ipt = NB / PLAN_THREADS; // F > 10: every thread owns ipt >= 64 bins
+  const u32 t = threadIdx.x;
+  const u32 lo = NB - (t + 1) * ipt;
+  u32 sum = 0;
+  for (u32 i = 0; i < ipt; i += 4) { const uint4 v = *reinterpret_cast<const uint4*> (bin_hist + lo + i); sum += v.x + v.y + v.z + v.w; }
+  u32 total;
+  const u32 P0 = blk_excl_scan<PLAN_THREADS> (sum, s_warp, &total);
+  const u32 hprev = t > 0 ? bin_hist[lo + ipt] : 0;
+  u32 nheads = 0;
+  {
+    u32 p = P0, hp = hprev;
+    for (u32 i = ipt; i-- > 0;) {
+      const u32 hi = bin_hist[lo + i];
+      nheads += (t == 0 && i == ipt - 1) || (p / BK_CAPH != (p - hp) / BK_CAPH);
+      hp = hi; p += hi;
+    }
+  }
+  u32 nb_total;
+  u32 b = blk_excl_scan<PLAN_THREADS> (nheads, s_warp, &nb_total);
+  {
+    u32 p = P0, hp = hprev;
+    for (u32 i = ipt; i-- > 0;) {
+      const u32 hi = bin_hist[lo + i];
+      const bool head = (t == 0 && i == ipt - 1) || (p / BK_CAPH != (p - hp) / BK_CAPH);
+      if (head) { if (b < max_buckets) { bkt_start[b] = p; cursor[(size_t) b * BK_CURSOR_STRIDE] = p; } b++; }
+      hp = hi; p += hi;
+      lut[lo + i] = b - 1 < max_buckets ? b - 1 : max_buckets - 1;
+    }
+  }
+  if (t == 0) {
+    if (nb_total > max_buckets) nb_total = max_buckets;
     bkt_start[nb_total] = total;
     meta[META_NBUCKETS] = nb_total;
     meta[META_NOVERSIZE] = 0;
@@ -175,7 +222,7 @@ plan_kernel (const u32 *__restrict__ bin_hist, int F, const unsigned long long *
 template <int W>
 __global__ void __launch_bounds__ (256)
 partition_kernel (const u64 *__restrict__ in, u64 *__restrict__ out, const unsigned long long *__restrict__ counters,
-                  unsigned long long capacity, int k, int F, const unsigned short *__restrict__ lut, u32 *__restrict__ cursor)
+                  unsigned long long capacity, int k, int F, const u32 *__restrict__ lut, u32 *__restrict__ cursor)
 {
   const unsigned long long n = counters[0] < capacity ? counters[0] : capacity;
   const size_t stride = (size_t) gridDim.x * 256;

@@ -59,11 +59,13 @@ struct tjb_ctx {
   u32 *d_totals = nullptr;                  // small device scalars (global multi-pass path)
   int *d_cov = nullptr;
   // bucketed reduce: bin histogram (filled by the scan), splitters, per-bucket results
-  int bin_bits = TJB_MAX_BIN_BITS;
+  int bin_bits = PLAN_REG_BIN_BITS;
   bool hist_dirty = false;                  // a chunk was re-scanned after an overflow: rebuild the histogram from the records
-  u32 *d_bin_hist = nullptr, *d_bkt_start = nullptr, *d_cursor = nullptr, *d_meta = nullptr, *d_koff = nullptr, *d_ioff = nullptr;
-  unsigned short *d_lut = nullptr;
+  u32 *d_bin_hist = nullptr, *d_lut = nullptr, *d_meta = nullptr;            // per bin (2^TJB_MAX_BIN_BITS)
+  u32 *d_bkt_start = nullptr, *d_cursor = nullptr, *d_koff = nullptr, *d_ioff = nullptr; // per bucket (views of the DevBufs below)
   uint4 *d_bstat = nullptr;
+  DevBuf b_bkt_start, b_cursor, b_koff, b_ioff, b_bstat;
+  u32 max_buckets = 0;
   unsigned long long *h_sync = nullptr;     // pinned: [0..1] counters, [2..] meta words
   char *h_out = nullptr; size_t h_out_cap = 0; // pinned staging of the results
   DevBuf out_cnt, out_ii, out_if, cov_tab;
@@ -213,14 +215,17 @@ static int grow_records (tjb_ctx *ctx, size_t want_records)
   return 0;
 }
 
-// bins of the partition plan: enough that a bin holds ~BK_CAP/8 records on average, at most what the context has
-static int choose_bin_bits (size_t n_bytes_hint, int k)
+// bins of the partition plan: enough that a bin holds ~BK_CAP/8 records on average, at most what the context has.
+// Expected records: a run of >= m equal bases starts at a position with probability 3/4 * 4^-(m-1).
+static int choose_bin_bits (size_t n_bytes_hint, int k, int min_tract)
 {
   const int W = tjb_rec_words (k);
-  const int max_bits = W == 2 ? (4 * k + 1 < TJB_MAX_BIN_BITS ? 4 * k + 1 : TJB_MAX_BIN_BITS) : TJB_MAX_BIN_BITS;
+  const int max_bits = W == 2 ? (4 * k + 1 < TJB_MAX_BIN_BITS ? 4 * k + 1 : TJB_MAX_BIN_BITS)
+                              : (2 * k + 1 < TJB_MAX_BIN_BITS ? 2 * k + 1 : TJB_MAX_BIN_BITS);
+  const int m = min_tract < 2 ? 2 : (min_tract > 8 ? 8 : min_tract);
   int F = 4;
-  if (n_bytes_hint == 0) F = TJB_MAX_BIN_BITS; // size unknown (streamed files)
-  else { size_t est = n_bytes_hint / 64; while (F < TJB_MAX_BIN_BITS && (est >> F) > BK_CAP / 8) F++; }
+  if (n_bytes_hint == 0) F = PLAN_REG_BIN_BITS; // size unknown (streamed files)
+  else { size_t est = (n_bytes_hint * 3 / 4) >> (2 * (m - 1)); while (F < TJB_MAX_BIN_BITS && (est >> F) > BK_CAP / 8) F++; }
   return F < max_bits ? F : max_bits;
 }
 
@@ -236,7 +241,7 @@ static int begin_sample (tjb_ctx *ctx, const tjb_opts *opt, size_t n_bytes_hint)
   ctx->n_raw_known = ctx->n_skip_known = 0;
   ctx->pend = false;
   ctx->hist_dirty = false;
-  ctx->bin_bits = choose_bin_bits (n_bytes_hint, opt->kmer_size);
+  ctx->bin_bits = choose_bin_bits (n_bytes_hint, opt->kmer_size, opt->min_tract_size);
   CU (cudaMemsetAsync (ctx->d_counters, 0, 2 * sizeof (unsigned long long), ctx->stream));
   CU (cudaMemsetAsync (ctx->d_bin_hist, 0, sizeof (u32) << ctx->bin_bits, ctx->stream));
   return 0;
@@ -382,6 +387,15 @@ static int finalise_t (tjb_ctx *ctx, const tjb_opts *opt, tjb_counter_out *out, 
   TRY (ensure (ctx, ctx->out_cnt, (size_t) cap * 4)); TRY (ensure (ctx, ctx->out_ii, (size_t) cap * 4)); TRY (ensure (ctx, ctx->out_if, (size_t) cap * 4));
   u64 *rec_a = (u64*) ctx->rec_a.p, *rec_b = (u64*) ctx->rec_b.p;
   const u32 grid = (u32) ctx->sm_count;
+  // per-bucket tables: a bucket starts where the running record count crosses a multiple of BK_CAPH
+  const u32 max_buckets = (u32) (cap / BK_CAPH) + 2;
+  TRY (ensure (ctx, ctx->b_bkt_start, ((size_t) max_buckets + 1) * 4));
+  TRY (ensure (ctx, ctx->b_cursor, (size_t) max_buckets * BK_CURSOR_STRIDE * 4));
+  TRY (ensure (ctx, ctx->b_koff, (size_t) max_buckets * 4)); TRY (ensure (ctx, ctx->b_ioff, (size_t) max_buckets * 4));
+  TRY (ensure (ctx, ctx->b_bstat, (size_t) max_buckets * sizeof (uint4)));
+  ctx->d_bkt_start = (u32*) ctx->b_bkt_start.p; ctx->d_cursor = (u32*) ctx->b_cursor.p;
+  ctx->d_koff = (u32*) ctx->b_koff.p; ctx->d_ioff = (u32*) ctx->b_ioff.p; ctx->d_bstat = (uint4*) ctx->b_bstat.p;
+  ctx->max_buckets = max_buckets;
 
   if (ctx->hist_dirty) {
     CU (cudaMemsetAsync (ctx->d_bin_hist, 0, sizeof (u32) << F, st));
@@ -390,7 +404,10 @@ static int finalise_t (tjb_ctx *ctx, const tjb_opts *opt, tjb_counter_out *out, 
   }
   {
     const int ipt = F > 10 ? 1 << (F - 10) : 1; // bins per thread of the single planning CTA
-#define PLAN_CASE(I) case I: LAUNCH (K_PLAN, 10 << F, (plan_kernel<I><<<1, PLAN_THREADS, 0, st>>> (ctx->d_bin_hist, F, ctx->d_counters, cap, ctx->d_bkt_start, ctx->d_lut, ctx->d_cursor, ctx->d_meta))); break;
+#define PLAN_CASE(I) case I: LAUNCH (K_PLAN, 10 << F, (plan_kernel<I><<<1, PLAN_THREADS, 0, st>>> (ctx->d_bin_hist, F, ctx->d_counters, cap, ctx->d_bkt_start, ctx->d_lut, ctx->d_cursor, ctx->d_meta, max_buckets))); break;
+    if (F > PLAN_REG_BIN_BITS)
+      LAUNCH (K_PLAN, 18 << F, (plan_big_kernel<<<1, PLAN_THREADS, 0, st>>> (ctx->d_bin_hist, F, ctx->d_counters, cap, ctx->d_bkt_start, ctx->d_lut, ctx->d_cursor, ctx->d_meta, max_buckets)));
+    else
     switch (ipt) { PLAN_CASE (1) PLAN_CASE (2) PLAN_CASE (4) PLAN_CASE (8) PLAN_CASE (16) PLAN_CASE (32) PLAN_CASE (64) }
 #undef PLAN_CASE
   }
@@ -597,12 +614,7 @@ int tjb_ctx_create (int device, tjb_ctx **pctx)
   if ((e = cudaMalloc (&ctx->d_cov, sizeof (int))) != cudaSuccess) return fail (e);
   if ((e = cudaStreamCreateWithFlags (&ctx->copy_stream, cudaStreamNonBlocking)) != cudaSuccess) return fail (e);
   if ((e = cudaMalloc (&ctx->d_bin_hist, TJB_MAX_BINS * sizeof (u32))) != cudaSuccess) return fail (e);
-  if ((e = cudaMalloc (&ctx->d_bkt_start, (TJB_MAX_BINS + 1) * sizeof (u32))) != cudaSuccess) return fail (e);
-  if ((e = cudaMalloc (&ctx->d_cursor, (size_t) TJB_MAX_BINS * BK_CURSOR_STRIDE * sizeof (u32))) != cudaSuccess) return fail (e);
-  if ((e = cudaMalloc (&ctx->d_koff, TJB_MAX_BINS * sizeof (u32))) != cudaSuccess) return fail (e);
-  if ((e = cudaMalloc (&ctx->d_ioff, TJB_MAX_BINS * sizeof (u32))) != cudaSuccess) return fail (e);
-  if ((e = cudaMalloc (&ctx->d_lut, TJB_MAX_BINS * sizeof (unsigned short))) != cudaSuccess) return fail (e);
-  if ((e = cudaMalloc (&ctx->d_bstat, TJB_MAX_BINS * sizeof (uint4))) != cudaSuccess) return fail (e);
+  if ((e = cudaMalloc (&ctx->d_lut, TJB_MAX_BINS * sizeof (u32))) != cudaSuccess) return fail (e);
   if ((e = cudaMalloc (&ctx->d_meta, META_WORDS * sizeof (u32))) != cudaSuccess) return fail (e);
   if ((e = cudaMallocHost ((void**) &ctx->h_sync, 16 * sizeof (unsigned long long))) != cudaSuccess) return fail (e);
   if ((e = cudaFuncSetAttribute (tjb_scan_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) scan_smem_bytes<2> ())) != cudaSuccess) return fail (e);
@@ -632,7 +644,7 @@ void tjb_ctx_destroy (tjb_ctx *ctx)
   if (ctx->d_totals) cudaFree (ctx->d_totals);
   if (ctx->d_tile_ctr) cudaFree (ctx->d_tile_ctr);
   if (ctx->d_cov) cudaFree (ctx->d_cov);
-  void *small[] = {ctx->d_bin_hist, ctx->d_bkt_start, ctx->d_cursor, ctx->d_koff, ctx->d_ioff, ctx->d_lut, ctx->d_bstat, ctx->d_meta};
+  void *small[] = {ctx->d_bin_hist, ctx->d_lut, ctx->d_meta, ctx->b_bkt_start.p, ctx->b_cursor.p, ctx->b_koff.p, ctx->b_ioff.p, ctx->b_bstat.p};
   for (void *q : small) if (q) cudaFree (q);
   if (ctx->h_sync) cudaFreeHost (ctx->h_sync);
   if (ctx->h_out) cudaFreeHost (ctx->h_out);

@@ -144,3 +144,32 @@ def test_gpu_full_size_properties(ctx):
     d2 = torch.from_numpy(np.ascontiguousarray(rows[perm]).reshape(-1)).cuda()
     b = ctx.count_device(d2.data_ptr(), d2.numel(), opt)
     pyoracle.assert_same_boundary(as_boundary(a), as_boundary(b), "shuffle invariance")
+
+
+@pytest.mark.parametrize("k,m,depth", [(25, 2, 150), (32, 2, 150)])
+def test_gpu_many_bins_and_record_overflow(ctx, restatement, k, m, depth):
+    """m = 2 on ~105 MB of reads: ~19 % of the positions start a tract, so the first record-array estimate overflows
+    (the sample is redone with the exact size) and the partition plan needs more than 2^16 bins (plan_big_kernel)"""
+    buf = synth.sample_buffer(700_000, depth, seed=21)
+    check(ctx, restatement, buf, k, m, 5, True, f"many bins k={k} m={m}", device_too=False)
+
+
+def test_gpu_deep_long_flank_properties(ctx):
+    """BASELINE config 5 shape at reduced genome size (k = 32, m = 3, 300x): descending order, QC invariants, shuffle
+    invariance; the full-size sample (1.5 Gbases) takes ~9 ms on the device"""
+    import torch
+    buf = synth.sample_buffer(1_000_000, 300, seed=3)
+    opt = TatajubaOptions(32, 3, 5, True)
+    d = torch.from_numpy(buf).cuda()
+    a = ctx.count_device(d.data_ptr(), d.numel(), opt)
+    assert a.status == 0 and a.n_raw > 5_000_000
+    e = a.elem
+    f = pyoracle.unpack_bits(e["bits"])
+    key = np.stack([f["base"].astype(np.uint64), e["ctx0"], e["ctx1"], (f["length"] + 512).astype(np.uint64)], 1)
+    assert np.array_equal(np.lexsort(key.T[::-1])[::-1], np.arange(len(e)))
+    assert np.all(f["canon_flag"] == 3)
+    rows = buf.reshape(-1, 151)
+    perm = np.random.default_rng(1).permutation(rows.shape[0])
+    d2 = torch.from_numpy(np.ascontiguousarray(rows[perm]).reshape(-1)).cuda()
+    b = ctx.count_device(d2.data_ptr(), d2.numel(), opt)
+    pyoracle.assert_same_boundary(as_boundary(a), as_boundary(b), "shuffle invariance (deep, k=32)")
