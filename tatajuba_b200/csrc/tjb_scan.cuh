@@ -45,6 +45,9 @@
 #define SW_G0 (SW_HALO_L / 16)        // owned groups [SW_G0, SW_G1)
 #define SW_G1 (SW_G0 + SW_TILE / 16)
 #define SW_ROWS (SW_GROUPS / 32)
+#ifndef SW_CHUNK
+#define SW_CHUNK 4                    // consecutive windows per ticket (power of two, >= 2)
+#endif
 #ifndef SW_QCAP
 #define SW_QCAP 512                   // candidate queue: < 32 carried + at most 32 * SW_QUOTA new per round
 #endif
@@ -161,6 +164,11 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
     asm volatile ("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   const int cand_len = min_len < 4 ? min_len : 4;
+  // powers of two (and -1) as run-time values: n < 2^62, so kq0 is zero, but the compiler cannot fold the multiplies
+  // into integer-pipe shifts / logic
+  const u32 kq0 = (u32) ((unsigned long long) n >> 62);
+  const u32 kq4 = 16u + kq0, kq16 = (1u << 16) + kq0, kq26 = (1u << 26) + kq0, kq30 = (1u << 30) + kq0, kq31 = (1u << 31) + kq0;
+  const u32 kqm1 = 0xffffffffu + kq0;
   const u64 kmask = (k == 32) ? ~0ULL : ((1ULL << (2 * k)) - 1);
   __syncthreads (); // the only block-wide barrier: LUTs and mbarriers are set up
 
@@ -302,17 +310,21 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
   // ---- main loop: this warp's windows, window t+n_warps in flight while window t is processed ------------------
   // windows are handed out by a global ticket counter (SMs on the two dies do not run at the same speed, a static
   // deal leaves a tail); the ticket of the window after next is requested one window ahead, its latency is hidden
+  // (SW_CHUNK consecutive windows per ticket: one counter served 258 K atomics in 250 us and its latency showed)
   u32 t_cur = 0, t_nxt = 0, t_fut = 0;
-  if (lane == 0) t_cur = atomicAdd (tile_ctr, 2u);
-  t_cur = __shfl_sync (0xffffffffu, t_cur, 0);
+  bool want_ticket = false;
+  if (lane == 0) t_fut = atomicAdd (tile_ctr, 2u);
+  t_fut = __shfl_sync (0xffffffffu, t_fut, 0);
+  t_cur = t_fut * SW_CHUNK;
   t_nxt = t_cur + 1;
+  t_fut++; // the second chunk of the first request
   long long g0 = (long long) t_cur * SW_TILE - SW_HALO_L, old_g0 = 0;
   int st = 0;
   bool in_cur = false;
   if (t_cur < n_tiles) { in_cur = interior (t_cur); stage_tile (t_cur, 0); }
   const u32 hdr = (u32) lane << 5;
   for (; t_cur < n_tiles; st ^= 1) {
-    if (lane == 0) t_fut = atomicAdd (tile_ctr, 1u);
+    if (want_ticket) { if (lane == 0) t_fut = atomicAdd (tile_ctr, 1u); want_ticket = false; }
     bool in_next = false;
     if (t_nxt < n_tiles) { in_next = interior (t_nxt); stage_tile (t_nxt, st ^ 1); }
     if (in_cur) { mbar_wait (&S->bar[st], (parity >> st) & 1); parity ^= 1u << st; }
@@ -333,20 +345,22 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
         const u32 p0 = m0 * SCAN_GRAY_MUL, p1 = m1 * SCAN_GRAY_MUL, p2 = m2 * SCAN_GRAY_MUL, p3 = m3 * SCAN_GRAY_MUL;
         c[row] = __byte_perm (__byte_perm (p0, p1, 0x0073), __byte_perm (p2, p3, 0x0073), 0x5410);
         // letters have bit 6 set.  Look-up selectors: code << 1 | letter, the nibbles of two words interleaved in one
-        // register; the flag bits are moved by multiply-high (FMA pipe), the integer pipe is the bottleneck
+        // register.  The integer pipe is the bottleneck, so shifts, adds and the word comparison are multiply-adds
+        // with multipliers the compiler cannot see through (kq*): they issue on the FMA pipe.
         const u32 a0 = w0 & 0x40404040u, a1 = w1 & 0x40404040u, a2 = w2 & 0x40404040u, a3 = w3 & 0x40404040u;
-        const u32 z01 = (m1 * 16u + m0) | mad_hi (a1, 1u << 30, __umulhi (a0, 1u << 26));
-        const u32 z23 = (m3 * 16u + m2) | mad_hi (a3, 1u << 30, __umulhi (a2, 1u << 26));
-        const u32 xa = prmt (SCAN_LUT_A, SCAN_LUT_B, z01), xb = prmt (SCAN_LUT_A, SCAN_LUT_B, z01 >> 16);
-        const u32 xc = prmt (SCAN_LUT_A, SCAN_LUT_B, z23), xd = prmt (SCAN_LUT_A, SCAN_LUT_B, z23 >> 16);
-        // the bytes their codes stand for, against the bytes themselves: sum of squared differences over the group
-        const u32 d0 = w0 ^ prmt (xa, xb, 0x6420), d1 = w1 ^ prmt (xa, xb, 0x7531);
-        const u32 d2 = w2 ^ prmt (xc, xd, 0x6420), d3 = w3 ^ prmt (xc, xd, 0x7531);
+        const u32 z01 = mad_hi (a1, kq30, mad_hi (a0, kq26, m1 * kq4 + m0)); // m0 | m1 << 4 | a0 >> 6 | a1 >> 2
+        const u32 z23 = mad_hi (a3, kq30, mad_hi (a2, kq26, m3 * kq4 + m2));
+        const u32 xa = prmt (SCAN_LUT_A, SCAN_LUT_B, z01), xb = prmt (SCAN_LUT_A, SCAN_LUT_B, __umulhi (z01, kq16));
+        const u32 xc = prmt (SCAN_LUT_A, SCAN_LUT_B, z23), xd = prmt (SCAN_LUT_A, SCAN_LUT_B, __umulhi (z23, kq16));
+        // the bytes their codes stand for, against the bytes themselves (word differences: zero iff equal), then the
+        // sum of the squared bytes of the differences over the group
+        const u32 d0 = prmt (xa, xb, 0x6420) * kqm1 + w0, d1 = prmt (xa, xb, 0x7531) * kqm1 + w1;
+        const u32 d2 = prmt (xc, xd, 0x6420) * kqm1 + w2, d3 = prmt (xc, xd, 0x7531) * kqm1 + w3;
         const u32 acc = __dp4a (d0, d0, __dp4a (d1, d1, __dp4a (d2, d2, __dp4a (d3, d3, 0u))));
         // bit j of the mask = byte j is a non-letter: 64 * (255 - sum of the weights of the letters), bytes are 0x40 / 0
         const int lo8 = dp4a_us (a1, 0x80C0E0F0u, dp4a_us (a0, 0xF8FCFEFFu, 255 * 64));
         const int hi8 = dp4a_us (a3, 0x80C0E0F0u, dp4a_us (a2, 0xF8FCFEFFu, 255 * 64));
-        nl16[grp] = (unsigned short) __umulhi ((u32) (hi8 * 256 + lo8), 1u << 26);
+        nl16[grp] = (unsigned short) __umulhi ((u32) (hi8 * 256 + lo8), kq26);
         codes[grp] = c[row];
         const u32 bb = __ballot_sync (0xffffffffu, acc != 0);
         if (lane == 0) S->bad[st][row] = bb;
@@ -364,7 +378,7 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
       if (cand_len >= 3) tt |= cc ^ __funnelshift_r (cc, cn, 4);
       if (cand_len >= 4) tt |= cc ^ __funnelshift_r (cc, cn, 6);
       const u32 dp = cc ^ __funnelshift_l (cp, cc, 2);
-      u32 cs = ~(tt | (tt >> 1)) & (dp | (dp >> 1)) & 0x55555555u;
+      u32 cs = ~(tt | __umulhi (tt, kq31)) & (dp | __umulhi (dp, kq31)) & 0x55555555u; // x >> 1 on the FMA pipe
       if (row == 0 && lane < SW_G0) cs = 0;                       // halo groups are owned by the neighbouring windows
       if (row == SW_ROWS - 1 && lane >= SW_G1 - 32 * (SW_ROWS - 1)) cs = 0;
       if (row < 2) A |= cs << (row & 1); else B |= cs << (row & 1);
@@ -417,7 +431,8 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
     }
     old_g0 = g0;
     t_cur = t_nxt;
-    t_nxt = __shfl_sync (0xffffffffu, t_fut, 0);
+    if ((t_nxt & (SW_CHUNK - 1)) != SW_CHUNK - 1) t_nxt++;
+    else { t_nxt = __shfl_sync (0xffffffffu, t_fut, 0) * SW_CHUNK; want_ticket = true; }
     g0 = (long long) t_cur * SW_TILE - SW_HALO_L;
     __syncwarp (); // every lane is done with the other stage's arrays and this stage's bytes are consumed
   }

@@ -17,11 +17,18 @@ ap.add_argument("--coverage", type=int, default=100)
 ap.add_argument("-k", type=int, default=25)
 ap.add_argument("-m", type=int, default=4)
 ap.add_argument("--error", type=float, default=0.0)
+ap.add_argument("--stats", action="store_true", help="per-kernel CUDA-event times of the last step")
 a = ap.parse_args()
 buf = synth.sample_buffer(a.genome, a.coverage, seed=1, error_rate=a.error)
 d = torch.from_numpy(buf).cuda()
 ctx = Context(0)
 opt = TatajubaOptions(a.k, a.m, 5, True)
-for _ in range(a.steps):
+for i in range(a.steps):
+    if a.stats and i == a.steps - 1:
+        ctx.set_profiling(2)
+        ctx.reset_kernel_stats()
     hc = ctx.count_device(d.data_ptr(), d.numel(), opt)
+if a.stats:
+    for s in ctx.kernel_stats():
+        print(f"  {s['name']:24s} launches={s['launches']:4d} ms={s['ms_total']:8.3f}")
 print(f"n_raw={hc.n_raw} n_distinct={hc.n_distinct} n_elem={hc.n_elem} n_idx={hc.n_idx} coverage={hc.coverage} ms_device={hc.ms_device:.3f}")
