@@ -173,3 +173,34 @@ def test_gpu_deep_long_flank_properties(ctx):
     d2 = torch.from_numpy(np.ascontiguousarray(rows[perm]).reshape(-1)).cuda()
     b = ctx.count_device(d2.data_ptr(), d2.numel(), opt)
     pyoracle.assert_same_boundary(as_boundary(a), as_boundary(b), "shuffle invariance (deep, k=32)")
+
+
+def _fuzz_buffer(rng, n_reads, alphabet, weights, max_len):
+    reads = []
+    for _ in range(n_reads):
+        L = int(rng.integers(0, max_len))
+        r = rng.choice(alphabet, size=L, p=weights)
+        # homopolymer runs of every kind, also of odd bytes, at random places
+        for _ in range(int(rng.integers(0, 4))):
+            if L < 4:
+                break
+            s = int(rng.integers(0, L - 1))
+            r[s:s + int(rng.integers(2, 40))] = rng.choice(alphabet, p=weights)
+        reads.append(r.tobytes())
+    return b"\n".join(reads) + (b"\n" if rng.random() < 0.7 else b"")
+
+
+@pytest.mark.parametrize("seed", range(12))
+def test_gpu_fuzz_arbitrary_bytes(ctx, restatement, seed):
+    """random reads over an alphabet with every class of byte the scan distinguishes: ACGT, lower case, U/u, N and
+    IUPAC letters, '*', '-', '.', digits, control bytes that look like the separator to the pass-1 look-up
+    (0x08, 0x0E, 0x1D), '\\r', bytes >= 0x80; random read lengths (also empty and shorter than k)"""
+    rng = np.random.default_rng(1000 + seed)
+    odd = list(b"acgtuUNnRYKMSWBDHV*-.09@[`{\r\t ") + [0x08, 0x0E, 0x1D, 0x0B, 0x02, 0x4A, 0x4B, 0x80, 0xC1, 0xFF, 0x7F, 0x00]
+    alphabet = np.array(list(b"ACGT") + odd, np.uint8)
+    p_odd = [0.0, 0.002, 0.02, 0.3][seed % 4]
+    weights = np.array([(1 - p_odd) / 4] * 4 + [p_odd / len(odd)] * len(odd))
+    weights /= weights.sum()
+    buf = _fuzz_buffer(rng, int(rng.integers(200, 3000)), alphabet, weights, int(rng.choice([30, 160, 700])))
+    k, m = int(rng.integers(2, 33)), int(rng.integers(1, 7))
+    check(ctx, restatement, buf, k, m, int(rng.integers(0, 4)), bool(rng.integers(0, 2)), f"fuzz seed={seed} k={k} m={m}")

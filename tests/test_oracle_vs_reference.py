@@ -88,3 +88,35 @@ def test_nonacgt_runs_are_counted_and_skipped(restatement):
     buf = fl + b"NNNNN" + fl + b"\n" + fl + b"AAAA" + fl + b"\n"
     recs, skipped = restatement.scan_buffer(buf, 25, 4)
     assert skipped == 1 and len(recs) == 1 and recs[0]["length"] == 4
+
+
+@pytest.mark.parametrize("seed", range(8))
+def test_restatement_equals_reference_on_arbitrary_bytes(restatement, reference, seed):
+    """flanks and run neighbourhoods with every class of byte (lower case, U, IUPAC, punctuation, control bytes, bytes
+    below 0x80); qualifying runs of non-ACGTU bytes are excluded (undefined behaviour in the reference, fenced), and so
+    are bytes >= 0x80: the reference indexes dna_in_2_bits[] with a signed char (src/hopo_counter.c:236-245), i.e. out
+    of bounds; the restatement and the GPU path code them as "not ACGT" (0)"""
+    rng = np.random.default_rng(500 + seed)
+    odd = np.array(list(b"acgtuUNnRYKMSWBDHV*-.09@[`{\r\t ") + [0x08, 0x0E, 0x1D, 0x0B, 0x02, 0x4A, 0x4B, 0x7F, 0x00], np.uint8)
+    acgtu = set(b"ACGTUacgtu")
+    reads = []
+    for _ in range(int(rng.integers(300, 1500))):
+        L = int(rng.integers(0, 400))
+        r = rng.choice(np.frombuffer(b"ACGT", np.uint8), size=L)
+        for _ in range(int(rng.integers(0, 5))):  # homopolymer runs of real bases (either case, U)
+            if L < 4:
+                break
+            s = int(rng.integers(0, L - 1))
+            r[s:s + int(rng.integers(2, 30))] = rng.choice(np.frombuffer(b"ACGTacgtUu", np.uint8))
+        hit = rng.random(L) < [0.0, 0.01, 0.05, 0.2][seed % 4]
+        r[hit] = rng.choice(odd, size=int(hit.sum()))
+        for i in range(1, L):  # no run of two or more equal non-ACGTU bytes
+            if r[i] == r[i - 1] and int(r[i]) not in acgtu:
+                r[i] = ord("A") if r[i - 1] != ord("A") else ord("C")
+        reads.append(r.tobytes())
+    buf = b"\n".join(reads) + b"\n"
+    k, m = int(rng.integers(2, 33)), int(rng.integers(1, 6))
+    a = restatement.run_buffer(buf, k, m, 1, False)
+    b = reference.run_buffer(buf, k, m, 1, False)
+    assert a.n_skipped_nonacgt == 0
+    pyoracle.assert_same_boundary(a, b, f"arbitrary bytes seed={seed} k={k} m={m}")
