@@ -189,22 +189,32 @@ plan_big_kernel (const u32 *__restrict__ bin_hist, int F, const unsigned long lo
   u32 nheads = 0;
   {
     u32 p = P0, hp = hprev;
-    for (u32 i = ipt; i-- > 0;) {
-      const u32 hi = bin_hist[lo + i];
-      nheads += (t == 0 && i == ipt - 1) || (p / BK_CAPH != (p - hp) / BK_CAPH);
-      hp = hi; p += hi;
+    for (u32 i = ipt; i > 0; i -= 4) { // 16-byte loads, bins walked from the highest to the lowest
+      const uint4 v = *reinterpret_cast<const uint4*> (bin_hist + lo + i - 4);
+      const u32 h4[4] = {v.w, v.z, v.y, v.x};
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        nheads += (t == 0 && i == ipt && j == 0) || (p / BK_CAPH != (p - hp) / BK_CAPH);
+        hp = h4[j]; p += h4[j];
+      }
     }
   }
   u32 nb_total;
   u32 b = blk_excl_scan<PLAN_THREADS> (nheads, s_warp, &nb_total);
   {
     u32 p = P0, hp = hprev;
-    for (u32 i = ipt; i-- > 0;) {
-      const u32 hi = bin_hist[lo + i];
-      const bool head = (t == 0 && i == ipt - 1) || (p / BK_CAPH != (p - hp) / BK_CAPH);
-      if (head) { if (b < max_buckets) { bkt_start[b] = p; cursor[(size_t) b * BK_CURSOR_STRIDE] = p; } b++; }
-      hp = hi; p += hi;
-      lut[lo + i] = b - 1 < max_buckets ? b - 1 : max_buckets - 1;
+    for (u32 i = ipt; i > 0; i -= 4) {
+      const uint4 v = *reinterpret_cast<const uint4*> (bin_hist + lo + i - 4);
+      const u32 h4[4] = {v.w, v.z, v.y, v.x};
+      u32 l4[4];
+#pragma unroll
+      for (int j = 0; j < 4; j++) {
+        const bool head = (t == 0 && i == ipt && j == 0) || (p / BK_CAPH != (p - hp) / BK_CAPH);
+        if (head) { if (b < max_buckets) { bkt_start[b] = p; cursor[(size_t) b * BK_CURSOR_STRIDE] = p; } b++; }
+        hp = h4[j]; p += h4[j];
+        l4[j] = b - 1 < max_buckets ? b - 1 : max_buckets - 1;
+      }
+      *reinterpret_cast<uint4*> (lut + lo + i - 4) = make_uint4 (l4[3], l4[2], l4[1], l4[0]);
     }
   }
   if (t == 0) {
