@@ -4,7 +4,10 @@
 #include <climits>
 #include <cstdlib>
 #include <cstring>
+#include <condition_variable>
 #include <map>
+#include <mutex>
+#include <thread>
 #include <string>
 #include <vector>
 
@@ -17,7 +20,7 @@
 #include "tjb_union.cuh"
 
 #define TJB_VERSION_STR "tatajuba_b200 0.1 (sm_100a)"
-#define TJB_CHUNK_BYTES (64u << 20)      // files path: pinned chunk of decoded reads
+#define TJB_CHUNK_BYTES (32u << 20)      // files path: pinned chunk of decoded reads (two per decoder thread)
 #define TJB_HOST_CHUNK_BYTES (32u << 20) // host-buffer path: H2D chunk overlapped with the scan of the previous one
 
 enum KernelId { K_SCAN = 0, K_PLAN, K_PARTITION, K_BUCKET, K_TOTALS, K_PACK, K_COVMAX, K_RECHIST,
@@ -45,8 +48,8 @@ struct tjb_ctx {
   std::vector<cudaEvent_t> free_events;
   int sm_count = 148;
 
-  uint8_t *h_pinned[2] = {nullptr, nullptr};
-  cudaEvent_t h_free[2] = {nullptr, nullptr}; // pinned buffer i may be overwritten once this has fired
+  uint8_t *h_pinned[4] = {nullptr, nullptr, nullptr, nullptr}; // files path: two chunks per decoder thread
+  cudaEvent_t h_free[4] = {nullptr, nullptr, nullptr, nullptr}; // pinned chunk i may be overwritten once this has fired
   DevBuf d_chunk[2];
 
   DevBuf rec_a, rec_b; // raw tract observations + sort ping-pong
@@ -412,7 +415,7 @@ static int finalise_t (tjb_ctx *ctx, const tjb_opts *opt, tjb_counter_out *out, 
 #undef PLAN_CASE
   }
   LAUNCH (K_PARTITION, 0, (partition_kernel<W><<<grid * 8, 256, 0, st>>> (rec_a, rec_b, ctx->d_counters, cap, k, F, ctx->d_lut, ctx->d_cursor)));
-  LAUNCH (K_BUCKET, 0, (bucket_reduce_kernel<W><<<grid * (W == 2 ? 3 : 1), BK_THREADS, bucket_smem_bytes<W> (), st>>> (rec_b, ctx->d_bkt_start, ctx->d_meta, cap, digit_list (W, k), opt->remove_biased, opt->min_coverage, rec_a, (u32*) ctx->out_cnt.p, (u32*) ctx->out_ii.p, (u32*) ctx->out_if.p, ctx->d_bstat)));
+  LAUNCH (K_BUCKET, 0, (bucket_reduce_kernel<W><<<grid * (W == 2 ? 3 : 2), BK_THREADS, bucket_smem_bytes<W> (), st>>> (rec_b, ctx->d_bkt_start, ctx->d_meta, cap, digit_list (W, k), opt->remove_biased, opt->min_coverage, rec_a, (u32*) ctx->out_cnt.p, (u32*) ctx->out_ii.p, (u32*) ctx->out_if.p, ctx->d_bstat)));
   LAUNCH (K_TOTALS, 0, (totals_kernel<<<1, PLAN_THREADS, 0, st>>> (ctx->d_bstat, ctx->d_meta, ctx->d_koff, ctx->d_ioff)));
   CU (cudaGetLastError ());
   // ---- synchronisation 1: counts --------------------------------------------------------------------------
@@ -568,6 +571,36 @@ static int union_t (tjb_ctx *ctx, const u64 *d_rows, u32 n, int k, u64 *d_union,
   return 0;
 }
 
+// ---- file feed: one decoder thread per FASTQ file, two pinned chunks each -----------------
+struct FeedSlot { uint8_t *pin = nullptr; cudaEvent_t free_ev = nullptr; int64_t got = 0; int state = 0; /* 0 empty, 1 full */ };
+struct FileFeed {
+  std::mutex mu;
+  std::condition_variable cv;
+  FeedSlot slot[2][2];
+  int64_t n_reads[2] = {0, 0}, n_bases[2] = {0, 0};
+  double ms_decode[2] = {0., 0.};
+  bool abort = false;
+};
+static void file_feed_worker (FileFeed *f, int p, tjb_reader *rd, int device)
+{
+  cudaSetDevice (device);
+  for (int i = 0;; i ^= 1) {
+    FeedSlot &s = f->slot[p][i];
+    {
+      std::unique_lock<std::mutex> lk (f->mu);
+      f->cv.wait (lk, [&] { return s.state == 0 || f->abort; });
+      if (f->abort) return;
+    }
+    cudaEventSynchronize (s.free_ev); // the copy engine has drained this pinned chunk (no-op before its first use)
+    auto t0 = std::chrono::steady_clock::now ();
+    const int64_t got = tjb_reader_fill (rd, s.pin, TJB_CHUNK_BYTES, &f->n_reads[p], &f->n_bases[p]);
+    f->ms_decode[p] += std::chrono::duration<double, std::milli> (std::chrono::steady_clock::now () - t0).count ();
+    { std::lock_guard<std::mutex> lk (f->mu); s.got = got; s.state = 1; }
+    f->cv.notify_all ();
+    if (got <= 0) return;
+  }
+}
+
 // ------------------------------------------------------------------------------------------- C ABI ------
 extern "C" {
 
@@ -639,7 +672,7 @@ void tjb_ctx_destroy (tjb_ctx *ctx)
                     &ctx->drec, &ctx->dcount, &ctx->keep, &ctx->kpos, &ctx->krec, &ctx->kcount, &ctx->cw, &ctx->csum, &ctx->gkeep,
                     &ctx->gkpos, &ctx->out40, &ctx->idx_i, &ctx->idx_f, &ctx->out_cnt, &ctx->out_ii, &ctx->out_if, &ctx->cov_tab};
   for (DevBuf *b : bufs) if (b->p) cudaFree (b->p);
-  for (int i = 0; i < 2; i++) { if (ctx->h_pinned[i]) cudaFreeHost (ctx->h_pinned[i]); if (ctx->h_free[i]) cudaEventDestroy (ctx->h_free[i]); }
+  for (int i = 0; i < 4; i++) { if (ctx->h_pinned[i]) cudaFreeHost (ctx->h_pinned[i]); if (ctx->h_free[i]) cudaEventDestroy (ctx->h_free[i]); }
   if (ctx->d_counters) cudaFree (ctx->d_counters);
   if (ctx->d_totals) cudaFree (ctx->d_totals);
   if (ctx->d_tile_ctr) cudaFree (ctx->d_tile_ctr);
@@ -763,39 +796,56 @@ int tjb_count_sample_files (tjb_ctx *ctx, const char *const *files, int n_files,
   if (!ctx || !out || !files || n_files < 1 || n_files > 2) return TJB_ERR_ARG;
   out_reset (out);
   TRY (begin_sample (ctx, opt, 0));
-  for (int i = 0; i < 2; i++) {
+  for (int i = 0; i < 2 * n_files; i++) {
     if (!ctx->h_pinned[i]) CU (cudaMallocHost ((void**) &ctx->h_pinned[i], TJB_CHUNK_BYTES));
     if (!ctx->h_free[i]) CU (cudaEventCreateWithFlags (&ctx->h_free[i], cudaEventDisableTiming));
-    TRY (ensure (ctx, ctx->d_chunk[i], TJB_CHUNK_BYTES));
   }
+  for (int i = 0; i < 2; i++) TRY (ensure (ctx, ctx->d_chunk[i], TJB_CHUNK_BYTES));
   CU (cudaEventRecord (ctx->ev_t0, ctx->stream));
-  double ms_decode = 0.;
-  int which = 0;
+  // One decoder thread per file (R1 and R2 inflate and parse concurrently; the order of the reads does not matter to
+  // the counter), two pinned chunks each; this thread copies and scans whatever chunk is ready.
+  FileFeed feed;
+  tjb_reader *rd[2] = {nullptr, nullptr};
   for (int f = 0; f < n_files; f++) {
-    tjb_reader *rd = tjb_reader_open (files[f]);
-    if (!rd) { ctx->err = std::string ("cannot open ") + files[f]; return TJB_ERR_IO; }
-    for (;;) {
-      // pinned buffer `which` was handed to the copy engine two chunks ago; wait until that copy has drained it
-      cudaEventSynchronize (ctx->h_free[which]);
-      // host decode of this chunk overlaps with the H2D copy + scan of the previous one (still in flight)
-      auto t0 = std::chrono::steady_clock::now ();
-      int64_t got = tjb_reader_fill (rd, ctx->h_pinned[which], TJB_CHUNK_BYTES, &out->n_reads, &out->n_bases);
-      ms_decode += std::chrono::duration<double, std::milli> (std::chrono::steady_clock::now () - t0).count ();
-      if (got < 0) { tjb_reader_close (rd); ctx->err = std::string ("decode failed: ") + files[f]; return (int) got; }
-      if (got == 0) break;
-      int rc = scan_resolve (ctx, opt); // previous chunk: record count known, overflow handled
-      if (rc < 0) { tjb_reader_close (rd); return rc; }
-      CU (cudaMemcpyAsync (ctx->d_chunk[which].p, ctx->h_pinned[which], (size_t) got, cudaMemcpyHostToDevice, ctx->stream));
-      CU (cudaEventRecord (ctx->h_free[which], ctx->stream));
-      rc = scan_launch (ctx, (const uint8_t*) ctx->d_chunk[which].p, (size_t) got, opt);
-      if (rc < 0) { tjb_reader_close (rd); return rc; }
-      which ^= 1;
-    }
-    tjb_reader_close (rd);
+    rd[f] = tjb_reader_open (files[f]);
+    if (!rd[f]) { for (int g = 0; g < f; g++) tjb_reader_close (rd[g]); ctx->err = std::string ("cannot open ") + files[f]; return TJB_ERR_IO; }
+    for (int i = 0; i < 2; i++) { feed.slot[f][i].pin = ctx->h_pinned[2 * f + i]; feed.slot[f][i].free_ev = ctx->h_free[2 * f + i]; }
   }
+  std::thread workers[2];
+  for (int f = 0; f < n_files; f++) workers[f] = std::thread (file_feed_worker, &feed, f, rd[f], ctx->device);
+  int rc = 0, alive = n_files, turn[2] = {0, 0}, which = 0;
+  bool finished[2] = {false, false};
+  while (alive > 0 && rc >= 0) {
+    int p = -1;
+    {
+      std::unique_lock<std::mutex> lk (feed.mu);
+      feed.cv.wait (lk, [&] { for (int q = 0; q < n_files; q++) if (!finished[q] && feed.slot[q][turn[q]].state == 1) { p = q; return true; } return false; });
+    }
+    FeedSlot &sl = feed.slot[p][turn[p]];
+    if (sl.got <= 0) { // end of this file (0) or a decode error (< 0)
+      finished[p] = true; alive--;
+      if (sl.got < 0) { rc = (int) sl.got; ctx->err = std::string ("decode failed: ") + files[p]; }
+      continue;
+    }
+    rc = scan_resolve (ctx, opt); // previous chunk: record count known, overflow handled
+    if (rc >= 0) {
+      cudaError_t e = cudaMemcpyAsync (ctx->d_chunk[which].p, sl.pin, (size_t) sl.got, cudaMemcpyHostToDevice, ctx->stream);
+      if (e == cudaSuccess) e = cudaEventRecord (sl.free_ev, ctx->stream); // the decoder waits for it before refilling
+      if (e != cudaSuccess) { ctx->err = std::string ("chunk copy: ") + cudaGetErrorString (e); rc = TJB_ERR_CUDA; }
+    }
+    if (rc >= 0) rc = scan_launch (ctx, (const uint8_t*) ctx->d_chunk[which].p, (size_t) sl.got, opt);
+    { std::lock_guard<std::mutex> lk (feed.mu); sl.state = 0; }
+    feed.cv.notify_all ();
+    turn[p] ^= 1;
+    which ^= 1;
+  }
+  { std::lock_guard<std::mutex> lk (feed.mu); feed.abort = true; }
+  feed.cv.notify_all ();
+  for (int f = 0; f < n_files; f++) { workers[f].join (); tjb_reader_close (rd[f]); }
+  if (rc < 0) return rc;
+  for (int f = 0; f < n_files; f++) { out->n_reads += feed.n_reads[f]; out->n_bases += feed.n_bases[f]; out->ms_decode += feed.ms_decode[f]; }
   TRY (scan_resolve (ctx, opt));
-  out->ms_decode = ms_decode;
-  int rc = finalise (ctx, opt, out);
+  rc = finalise (ctx, opt, out);
   if (rc < 0) return rc;
   CU (cudaEventRecord (ctx->ev_t1, ctx->stream));
   CU (cudaEventSynchronize (ctx->ev_t1));
