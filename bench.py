@@ -256,6 +256,28 @@ def main():
         if world > 1:
             dist.destroy_process_group()
         return
+    # ---- from FASTQ files (host decode inside): bounded sample, 1-GPU runs only (information, SURVEY.md 8d iii) -----
+    files_leg = None
+    if world == 1:
+        import tempfile
+        from tatajuba_b200 import synth
+        n_fr = 400_000  # reads (60 Mbases): writing the full sample as .gz from Python would take minutes
+        rows = buf[: n_fr * (READ_LEN + 1)].reshape(n_fr, READ_LEN + 1)
+        files_leg = {"sample": f"first {n_fr} reads of the workload written as paired FASTQ (R1/R2), plain and gzip -1",
+                     "decoder_threads": 2}
+        with tempfile.TemporaryDirectory() as d:
+            for ext in (".fastq", ".fastq.gz"):
+                r1, r2 = os.path.join(d, "s_R1" + ext), os.path.join(d, "s_R2" + ext)
+                synth.write_fastq(r1, rows[0::2])
+                synth.write_fastq(r2, rows[1::2])
+                best = None
+                for _ in range(3):
+                    t0 = time.perf_counter()
+                    hf = ctx.count_files([r1, r2], opt)
+                    dt = time.perf_counter() - t0
+                    best = dt if best is None else min(best, dt)
+                files_leg["gz" if ext.endswith(".gz") else "plain"] = {"value": hf.n_bases / best, "unit": "bases/s",
+                                                                        "ms": best * 1e3, "bases": int(hf.n_bases)}
     peak, peak_src = load_peaks()
     scan = next(s for s in stats if s["name"] == "tjb_scan_kernel")
     scan_ms = scan["ms_total"] / scan["launches"]
@@ -280,6 +302,7 @@ def main():
         "kernels": {s["name"]: {"launches": s["launches"], "ms_total": round(s["ms_total"], 4)} for s in stats},
         "clocks": clocks,
         "exchange": exchange,
+        "from_files": files_leg,
     }
     tp = os.path.join(ROOT, "profiles", "scan_traffic.json")  # dram bytes of one scan launch from an ncu --set full capture
     if os.path.exists(tp):
