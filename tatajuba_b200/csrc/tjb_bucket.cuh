@@ -30,6 +30,12 @@
 #define TJB_MAX_BIN_BITS 20
 #define PLAN_REG_BIN_BITS 16 // up to this many bits the planning CTA keeps its bins in registers (plan_kernel), above: plan_big_kernel
 #define TJB_MAX_BINS (1 << TJB_MAX_BIN_BITS)
+#ifndef PART_GRID
+#define PART_GRID 8   // partition CTAs (of 256 threads) per SM
+#endif
+#ifndef PART_UNROLL
+#define PART_UNROLL 4 // records in flight per thread of the partition kernel
+#endif
 #define BK_CURSOR_STRIDE 32 // one partition cursor per 128-byte line: L2 atomics serialise per sector, not per address
 
 // meta[] slots (device u32)
@@ -236,15 +242,15 @@ partition_kernel (const u64 *__restrict__ in, u64 *__restrict__ out, const unsig
 {
   const unsigned long long n = counters[0] < capacity ? counters[0] : capacity;
   const size_t stride = (size_t) gridDim.x * 256;
-  for (size_t i0 = (size_t) blockIdx.x * 256 + threadIdx.x; i0 < n; i0 += 4 * stride) {
-    Rec<W> r[4];
-    u32 pos[4];
+  for (size_t i0 = (size_t) blockIdx.x * 256 + threadIdx.x; i0 < n; i0 += PART_UNROLL * stride) {
+    Rec<W> r[PART_UNROLL];
+    u32 pos[PART_UNROLL];
 #pragma unroll
-    for (int u = 0; u < 4; u++) { size_t i = i0 + u * stride; if (i < n) r[u] = load_rec<W> (in, i); }
+    for (int u = 0; u < PART_UNROLL; u++) { size_t i = i0 + u * stride; if (i < n) r[u] = load_rec<W> (in, i); }
 #pragma unroll
-    for (int u = 0; u < 4; u++) { size_t i = i0 + u * stride; if (i < n) pos[u] = atomicAdd (&cursor[(size_t) lut[rec_bin<W> (r[u], k, F)] * BK_CURSOR_STRIDE], 1u); }
+    for (int u = 0; u < PART_UNROLL; u++) { size_t i = i0 + u * stride; if (i < n) pos[u] = atomicAdd (&cursor[(size_t) lut[rec_bin<W> (r[u], k, F)] * BK_CURSOR_STRIDE], 1u); }
 #pragma unroll
-    for (int u = 0; u < 4; u++) { size_t i = i0 + u * stride; if (i < n && pos[u] < capacity) store_rec<W> (out, pos[u], r[u]); }
+    for (int u = 0; u < PART_UNROLL; u++) { size_t i = i0 + u * stride; if (i < n && pos[u] < capacity) store_rec<W> (out, pos[u], r[u]); }
   }
 }
 
