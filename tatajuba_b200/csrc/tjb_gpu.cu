@@ -1,6 +1,7 @@
 // libtjb_gpu: context, workspace, stream orchestration and the C ABI declared in include/tjb_gpu.h.
 // Device work only — there is no host fallback for any compute step in this file.
 #include <chrono>
+#include <emmintrin.h>
 #include <climits>
 #include <cstdlib>
 #include <cstring>
@@ -152,6 +153,28 @@ struct Trace { // TJB_TRACE=1: host wall-clock of the stages of one call, on std
   }
   ~Trace () { if (on) fprintf (stderr, "[tjb]%s\n", line.c_str ()); }
 };
+
+// pinned staging -> caller's memory with streaming stores: the destination is never read back here, so the
+// read-for-ownership of every line is skipped (measured: 220 -> 195 us for the 2.8 MB of config 2; a second copying
+// thread did not help, its chunks finished later than the main thread's)
+static void copy_streaming (void *dst, const void *src, size_t n)
+{
+  char *d = (char*) dst;
+  const char *s = (const char*) src;
+  size_t head = (16 - ((uintptr_t) d & 15)) & 15;
+  if (head > n) head = n;
+  memcpy (d, s, head);
+  d += head; s += head; n -= head;
+  size_t blocks = n / 64;
+  for (size_t i = 0; i < blocks; i++, d += 64, s += 64) {
+    const __m128i a = _mm_loadu_si128 ((const __m128i*) s), b = _mm_loadu_si128 ((const __m128i*) (s + 16));
+    const __m128i c = _mm_loadu_si128 ((const __m128i*) (s + 32)), e = _mm_loadu_si128 ((const __m128i*) (s + 48));
+    _mm_stream_si128 ((__m128i*) d, a); _mm_stream_si128 ((__m128i*) (d + 16), b);
+    _mm_stream_si128 ((__m128i*) (d + 32), c); _mm_stream_si128 ((__m128i*) (d + 48), e);
+  }
+  _mm_sfence ();
+  memcpy (d, s, n - blocks * 64);
+}
 
 static inline u32 nblk (size_t n, u32 per) { return (u32) ((n + per - 1) / per); }
 
@@ -503,7 +526,7 @@ static int finalise_t (tjb_ctx *ctx, const tjb_opts *opt, tjb_counter_out *out, 
     }
     for (int c = 0; c < NCH; c++) {
       CU (cudaEventSynchronize (ev[c]));
-      memcpy ((char*) out->elem + lo[c], ctx->h_out + lo[c], lo[c + 1] - lo[c]);
+      copy_streaming ((char*) out->elem + lo[c], ctx->h_out + lo[c], lo[c + 1] - lo[c]);
       ctx->free_events.push_back (ev[c]);
     }
     memcpy (out->idx_initial, ctx->h_out + eb, ib);
