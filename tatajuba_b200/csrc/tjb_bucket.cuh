@@ -23,7 +23,12 @@
 
 #define BK_THREADS 256
 #define BK_WARPS (BK_THREADS / 32)
+#ifndef BK_IPT
 #define BK_IPT 8
+#endif
+#ifndef BK_CTAS2
+#define BK_CTAS2 3 // bucket CTAs per SM, 2-word records (shared memory and registers allow 3 at BK_IPT 8)
+#endif
 #define BK_CAP (BK_THREADS * BK_IPT) // records per on-chip bucket
 #define BK_CAPH (BK_CAP / 2)
 #define PLAN_THREADS 1024
@@ -277,7 +282,7 @@ template <> __device__ __forceinline__ bool rec_greater<3> (const Rec<3> &a, con
 }
 
 template <int W>
-__global__ void __launch_bounds__ (BK_THREADS)
+__global__ void __launch_bounds__ (BK_THREADS, W == 2 ? BK_CTAS2 : 2)
 bucket_reduce_kernel (const u64 *__restrict__ recs, const u32 *__restrict__ bkt_start, u32 *__restrict__ meta, unsigned long long capacity,
                       DigitList dl, int remove_biased, int min_coverage, u64 *__restrict__ out_rec, u32 *__restrict__ out_cnt,
                       u32 *__restrict__ out_idx_i, u32 *__restrict__ out_idx_f, uint4 *__restrict__ bstat)

@@ -438,7 +438,7 @@ static int finalise_t (tjb_ctx *ctx, const tjb_opts *opt, tjb_counter_out *out, 
 #undef PLAN_CASE
   }
   LAUNCH (K_PARTITION, 0, (partition_kernel<W><<<grid * PART_GRID, 256, 0, st>>> (rec_a, rec_b, ctx->d_counters, cap, k, F, ctx->d_lut, ctx->d_cursor)));
-  LAUNCH (K_BUCKET, 0, (bucket_reduce_kernel<W><<<grid * (W == 2 ? 3 : 2), BK_THREADS, bucket_smem_bytes<W> (), st>>> (rec_b, ctx->d_bkt_start, ctx->d_meta, cap, digit_list (W, k), opt->remove_biased, opt->min_coverage, rec_a, (u32*) ctx->out_cnt.p, (u32*) ctx->out_ii.p, (u32*) ctx->out_if.p, ctx->d_bstat)));
+  LAUNCH (K_BUCKET, 0, (bucket_reduce_kernel<W><<<grid * (W == 2 ? BK_CTAS2 : 2), BK_THREADS, bucket_smem_bytes<W> (), st>>> (rec_b, ctx->d_bkt_start, ctx->d_meta, cap, digit_list (W, k), opt->remove_biased, opt->min_coverage, rec_a, (u32*) ctx->out_cnt.p, (u32*) ctx->out_ii.p, (u32*) ctx->out_if.p, ctx->d_bstat)));
   LAUNCH (K_TOTALS, 0, (totals_kernel<<<1, PLAN_THREADS, 0, st>>> (ctx->d_bstat, ctx->d_meta, ctx->d_koff, ctx->d_ioff)));
   CU (cudaGetLastError ());
   // ---- synchronisation 1: counts --------------------------------------------------------------------------

@@ -175,10 +175,13 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
   u32 nrec = 0, nskip = 0, parity = 0;
   u32 head = 0, tail = 0, n_old = 0; // candidate FIFO; n_old = entries that belong to the previous window
 
-  // a window is "interior" when [g0, g0 + SW_WIN) lies inside the buffer: one bulk copy stages it
-  auto interior = [&] (long long t) { const long long g0 = t * SW_TILE - SW_HALO_L; return g0 >= 0 && g0 + SW_WIN <= n; };
-  auto stage_tile = [&] (long long t, int st) {
-    const long long g0 = t * SW_TILE - SW_HALO_L;
+  // a window is "interior" when [g0, g0 + SW_WIN) lies inside the buffer: one bulk copy stages it.  g0 >= 0 from
+  // window 1 on; the last interior window is the largest t with t * SW_TILE - SW_HALO_L + SW_WIN <= n
+  const long long t_int = n >= SW_WIN - SW_HALO_L ? (n - (SW_WIN - SW_HALO_L)) / SW_TILE : 0; // 0: none (window 0 never is)
+  const u32 t_last_interior = t_int > 0xffffffffLL ? 0xffffffffu : (u32) t_int;
+  auto interior = [&] (u32 t) { return t >= 1u && t <= t_last_interior; };
+  auto stage_tile = [&] (u32 t, int st) {
+    const long long g0 = (long long) t * SW_TILE - SW_HALO_L;
     if (interior (t)) {
       if (lane == 0) {
         asm volatile ("fence.proxy.async.shared::cta;" ::: "memory"); // generic-proxy accesses of this stage are done
