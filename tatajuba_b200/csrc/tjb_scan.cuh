@@ -37,24 +37,25 @@
 #ifndef SCAN_CTAS_PER_SM
 #define SCAN_CTAS_PER_SM 3
 #endif
-#define SW_WIN 2048                   // staged bytes per window = 128 groups of 16 = 4 rows of 32 lanes
+#ifndef SW_ROWS
+#define SW_ROWS 8                     // 16-byte groups per lane and window (even, <= 8)
+#endif
+#define SW_WIN (SW_ROWS * 512)        // staged bytes per window = SW_ROWS rows of 32 groups of 16 bytes
 #define SW_HALO_L 32                  // >= k, multiple of 16
 #define SW_HALO_R 64                  // >= 31 (longest fast-path run) + k + 1
-#define SW_TILE (SW_WIN - SW_HALO_L - SW_HALO_R) // 1952 owned bytes
+#define SW_TILE (SW_WIN - SW_HALO_L - SW_HALO_R) // owned bytes (4000 of 4096)
 #define SW_GROUPS (SW_WIN / 16)
 #define SW_G0 (SW_HALO_L / 16)        // owned groups [SW_G0, SW_G1)
 #define SW_G1 (SW_G0 + SW_TILE / 16)
-#define SW_ROWS (SW_GROUPS / 32)
 #ifndef SW_CHUNK
-#define SW_CHUNK 4                    // consecutive windows per ticket (power of two, >= 2)
+#define SW_CHUNK (SW_ROWS >= 8 ? 2 : 4) // consecutive windows per ticket (power of two, >= 2)
 #endif
 #ifndef SW_QCAP
-#define SW_QCAP 512                   // candidate queue: < 32 carried + at most 32 * SW_QUOTA new per round
+#define SW_QCAP 512                   // candidate queue (linear; moved to the front when the next round may not fit)
 #endif
-#define SW_QUOTA ((SW_QCAP - 32) / 32)
-#ifndef SW_RCAP
-#define SW_RCAP 64                    // staged records per warp; flushed when more than SW_RCAP - 32 are pending
-#endif
+#define SW_QUOTA 7                    // new candidates per lane and round: three bit planes of the ballot prefix sum
+#define SW_RCAP(W) ((W) == 2 ? 64 : 48) // staged records per warp (three CTAs of 8 warps must fit in 228 KB); flushed
+                                      // when more than SW_RCAP - 32 are pending
 #define SCAN_GRAY_MUL 0x00820820u     // ((w & 0x06060606) * this) >> 24 = the four 2-bit codes of w's bytes
 #define SCAN_GRAY_LUT 0x47544341u     // code -> byte: 'A' 'C' 'T' 'G'
 // PRMT look-up on (code << 1 | letter): letters A C T G in the odd slots; even slots: only code 1 can be a
@@ -63,14 +64,15 @@
 #define SCAN_LUT_B 0x47005400u
 
 template <int W> struct ScanWarpSmem {
-  uint8_t raw[2][SW_WIN];             // two stages of sequence bytes
+  alignas (16) uint8_t raw[SW_WIN];   // sequence bytes of the window in pass 1; refilled for the next window right after
   u32 codes[2][SW_GROUPS];            // 16 gray codes per word, byte j of the group in bits 2j..2j+1
   u32 nl[2][SW_GROUPS / 2 + 4];       // bit i of the array = byte i of the window has bit 6 clear; 4 pad words
-  u32 bad[2][8];                      // bit g = group g holds a byte that is neither ACGT nor separator-like
-  u64 rec[SW_RCAP * W];
-  unsigned long long bar[2];          // mbarriers of the two stages
-  unsigned short cand[SW_QCAP];       // candidates: stage << 11 | row pair << 10 | lane << 5 | bit (see pass 2)
+  u32 bad[2][SW_ROWS + 4];            // bit g = group g holds a byte that is neither ACGT nor separator-like
+  alignas (16) u64 rec[SW_RCAP (W) * W];
+  unsigned long long bar;             // mbarrier of the raw bytes
+  unsigned short cand[SW_QCAP];       // candidates: stage << 15 | row pair << 10 | lane << 5 | bit (see pass 2)
 };
+static_assert (sizeof (ScanWarpSmem<2>) % 16 == 0 && sizeof (ScanWarpSmem<3>) % 16 == 0, "warp slices must stay 16-byte aligned");
 template <int W> constexpr size_t scan_smem_bytes () { return SCAN_WARPS * sizeof (ScanWarpSmem<W>) + 512; }
 
 // forward code table: A0 C1 G2 T/U3 (either case), 4 = any other byte, 5 = '\n' (read separator)
@@ -159,8 +161,7 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
     s_lutr[tid] = (uint8_t) (f < 4 ? 3 - f : f);
   }
   if (lane == 0) {
-    mbar_init (&S->bar[0], 1);
-    mbar_init (&S->bar[1], 1);
+    mbar_init (&S->bar, 1);
     asm volatile ("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
   const int cand_len = min_len < 4 ? min_len : 4;
@@ -180,20 +181,21 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
   const long long t_int = n >= SW_WIN - SW_HALO_L ? (n - (SW_WIN - SW_HALO_L)) / SW_TILE : 0; // 0: none (window 0 never is)
   const u32 t_last_interior = t_int > 0xffffffffLL ? 0xffffffffu : (u32) t_int;
   auto interior = [&] (u32 t) { return t >= 1u && t <= t_last_interior; };
-  auto stage_tile = [&] (u32 t, int st) {
+  // the caller has made sure (__syncwarp) that every lane is done reading the previous window's bytes
+  auto stage_tile = [&] (u32 t) {
     const long long g0 = (long long) t * SW_TILE - SW_HALO_L;
     if (interior (t)) {
       if (lane == 0) {
-        asm volatile ("fence.proxy.async.shared::cta;" ::: "memory"); // generic-proxy accesses of this stage are done
-        mbar_expect_tx (&S->bar[st], SW_WIN);
-        bulk_g2s (S->raw[st], buf + g0, SW_WIN, &S->bar[st]);
+        asm volatile ("fence.proxy.async.shared::cta;" ::: "memory"); // generic-proxy accesses of the buffer are done
+        mbar_expect_tx (&S->bar, SW_WIN);
+        bulk_g2s (S->raw, buf + g0, SW_WIN, &S->bar);
       }
     } else { // first / last windows: bytes outside the buffer read as separators
       for (int i = lane; i < SW_WIN / 4; i += 32) {
         u32 w = 0;
 #pragma unroll
         for (int j = 0; j < 4; j++) { const long long p = g0 + 4 * i + j; w |= (u32) ((p >= 0 && p < n) ? buf[p] : (uint8_t) '\n') << (8 * j); }
-        reinterpret_cast<u32*> (S->raw[st])[i] = w;
+        reinterpret_cast<u32*> (S->raw)[i] = w;
       }
     }
   };
@@ -201,24 +203,30 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
     unsigned long long base = 0;
     if (lane == 0) base = atomicAdd (&counters[0], (unsigned long long) nrec);
     base = __shfl_sync (0xffffffffu, base, 0);
-    for (u32 i = lane; i < nrec * W; i += 32) {
-      const unsigned long long r = base + i / W;
-      if (r < capacity) out[r * W + (i % W)] = S->rec[i];
+    if (W == 2 && base + nrec <= capacity) { // one record = one 16-byte store
+      const ulonglong2 *src = reinterpret_cast<const ulonglong2*> (S->rec);
+      ulonglong2 *dst = reinterpret_cast<ulonglong2*> (out) + base;
+      for (u32 i = lane; i < nrec; i += 32) dst[i] = src[i];
+    } else {
+      for (u32 i = lane; i < nrec * W; i += 32) {
+        const unsigned long long r = base + i / W;
+        if (r < capacity) out[r * W + (i % W)] = S->rec[i];
+      }
     }
     nrec = 0;
     __syncwarp ();
   };
 
   // ---- phase B: one candidate per lane (a queue entry, or -1) ---------------------------------------------------
-  // cur_st / cur_g0: the window whose bytes are still staged; candidates of the previous window (old_g0) only have
-  // their derived arrays left; the slow path reads their bytes from global memory.
+  // cur_st / cur_g0: the current window; candidates carried over from the previous one start at old_g0.  Only the
+  // derived arrays are in shared memory at this point: the slow path reads its bytes from global memory (L2 hits).
   auto process_batch = [&] (int cnd, int cur_st, long long cur_g0, long long old_g0) {
     bool emit = false, slow = false;
     Rec<W> r;
     int gray = 0, s = 0, par = 0;
     if (cnd >= 0) {
-      par = cnd >> 11;
-      s = (cnd & 0x400) | ((cnd & 1) << 9) | ((cnd >> 1) & 0x1FF); // 1024 * row pair + 512 * (bit & 1) + 16 * lane + bit / 2
+      par = cnd >> 15;
+      s = (cnd & 0xC00) | ((cnd & 1) << 9) | ((cnd >> 1) & 0x1FF); // 1024 * row pair + 512 * (bit & 1) + 16 * lane + bit / 2
       const u32 *codes = S->codes[par];
       const u64 win = codes_at (codes, s); // codes s .. s+31
       gray = (int) ((u32) win & 3u);
@@ -256,10 +264,9 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
         }
       }
     }
-    const u32 lt_mask = (1u << lane) - 1;
     const u32 em = __ballot_sync (0xffffffffu, emit);
     if (emit) {
-      const u32 slot = nrec + __popc (em & lt_mask);
+      const u32 slot = nrec + __popc (em & ((1u << lane) - 1));
 #pragma unroll
       for (int j = 0; j < W; j++) S->rec[slot * W + j] = r.w[j];
     }
@@ -267,13 +274,7 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
     if (slow) {
       // byte-exact restatement of the reference loop over every byte run inside this code run
       const long long g0 = par == cur_st ? cur_g0 : old_g0;
-      const uint8_t *raw = S->raw[par];
-      const bool staged = par == cur_st;
-      auto byte_at = [&] (long long gp) -> int {
-        const long long rel = gp - g0;
-        if (staged && rel >= 0 && rel < SW_WIN) return raw[rel];
-        return (gp >= 0 && gp < n) ? buf[gp] : '\n';
-      };
+      auto byte_at = [&] (long long gp) -> int { return (gp >= 0 && gp < n) ? buf[gp] : '\n'; };
       long long ps = g0 + s;
       while (ps < n) {
         const int b0 = byte_at (ps);
@@ -307,10 +308,10 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
       }
     }
     __syncwarp ();
-    if (nrec > SW_RCAP - 32) flush ();
+    if (nrec > SW_RCAP (W) - 32) flush ();
   };
 
-  // ---- main loop: this warp's windows, window t+n_warps in flight while window t is processed ------------------
+  // ---- main loop: this warp's windows; the bytes of window t+1 are fetched while window t is in pass 2 / phase B ----
   // windows are handed out by a global ticket counter (SMs on the two dies do not run at the same speed, a static
   // deal leaves a tail); the ticket of the window after next is requested one window ahead, its latency is hidden
   // (SW_CHUNK consecutive windows per ticket: one counter served 258 K atomics in 250 us and its latency showed)
@@ -324,20 +325,27 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
   long long g0 = (long long) t_cur * SW_TILE - SW_HALO_L, old_g0 = 0;
   int st = 0;
   bool in_cur = false;
-  if (t_cur < n_tiles) { in_cur = interior (t_cur); stage_tile (t_cur, 0); }
+  if (t_cur < n_tiles) { in_cur = interior (t_cur); stage_tile (t_cur); }
   const u32 hdr = (u32) lane << 5;
+  const u32 lt_lanes = (1u << lane) - 1;
+  // the queue is linear: what is left moves to the front only when the next round might not fit behind it
+  auto queue_to_front = [&] () {
+    const u32 cnt = tail - head; // < 32
+    const unsigned short v = lane < (int) cnt ? S->cand[head + lane] : (unsigned short) 0;
+    __syncwarp ();
+    if (lane < (int) cnt) S->cand[lane] = v;
+    head = 0; tail = cnt;
+    __syncwarp ();
+  };
   for (; t_cur < n_tiles; st ^= 1) {
     if (want_ticket) { if (lane == 0) t_fut = atomicAdd (tile_ctr, 1u); want_ticket = false; }
-    bool in_next = false;
-    if (t_nxt < n_tiles) { in_next = interior (t_nxt); stage_tile (t_nxt, st ^ 1); }
-    if (in_cur) { mbar_wait (&S->bar[st], (parity >> st) & 1); parity ^= 1u << st; }
+    if (in_cur) { mbar_wait (&S->bar, parity); parity ^= 1u; }
     else __syncwarp ();
-    in_cur = in_next;
     u32 *codes = S->codes[st];
     u32 c[SW_ROWS];
     {
       // ---- pass 1: 16 bytes per lane and row -> gray codes, non-letter mask, bad-group bit -------------------
-      const uint4 *raw128 = reinterpret_cast<const uint4*> (S->raw[st]);
+      const uint4 *raw128 = reinterpret_cast<const uint4*> (S->raw);
       unsigned short *nl16 = reinterpret_cast<unsigned short*> (S->nl[st]);
 #pragma unroll
       for (int row = 0; row < SW_ROWS; row++) {
@@ -369,10 +377,14 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
         if (lane == 0) S->bad[st][row] = bb;
       }
     }
-    __syncwarp ();
-    // ---- pass 2: code-run starts of the owned groups.  A = rows 0 (even bits) and 1 (odd bits), B = rows 2 and 3:
-    // bit b of A is byte b / 2 of group 32 * (b & 1) + lane
-    u32 A = 0, B = 0;
+    __syncwarp (); // the derived arrays are complete and nobody reads the bytes any more:
+    in_cur = false;
+    if (t_nxt < n_tiles) { in_cur = interior (t_nxt); stage_tile (t_nxt); } // fetch the next window over them
+    // ---- pass 2: code-run starts of the owned groups.  Rows 2j (even bits) and 2j+1 (odd bits) share cand_bits[j]:
+    // bit b = byte b / 2 of group 64 * j + 32 * (b & 1) + lane
+    u32 cb[SW_ROWS / 2];
+#pragma unroll
+    for (int j = 0; j < SW_ROWS / 2; j++) cb[j] = 0;
 #pragma unroll
     for (int row = 0; row < SW_ROWS; row++) {
       const int grp = row * 32 + lane;
@@ -384,21 +396,28 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
       u32 cs = ~(tt | __umulhi (tt, kq31)) & (dp | __umulhi (dp, kq31)) & 0x55555555u; // x >> 1 on the FMA pipe
       if (row == 0 && lane < SW_G0) cs = 0;                       // halo groups are owned by the neighbouring windows
       if (row == SW_ROWS - 1 && lane >= SW_G1 - 32 * (SW_ROWS - 1)) cs = 0;
-      if (row < 2) A |= cs << (row & 1); else B |= cs << (row & 1);
+      cb[row >> 1] |= cs << (row & 1);
     }
-    // ---- compaction into the queue (at most SW_QUOTA per lane and round); full batches of 32 go to phase B ------------
+    // ---- compaction into the queue (at most SW_QUOTA per lane and round); full batches of 32 go to phase B ------
     for (;;) {
-      const int have = __popc (A) + __popc (B), mine = have < SW_QUOTA ? have : SW_QUOTA;
-      int inc = mine;
+      if (tail + 32 * SW_QUOTA > SW_QCAP) queue_to_front ();
+      int have = 0;
 #pragma unroll
-      for (int d = 1; d < 32; d <<= 1) { const int u = __shfl_up_sync (0xffffffffu, inc, d); if (lane >= d) inc += u; }
-      const int total = __shfl_sync (0xffffffffu, inc, 31);
+      for (int j = 0; j < SW_ROWS / 2; j++) have += __popc (cb[j]);
+      const int mine = have < SW_QUOTA ? have : SW_QUOTA;
+      // prefix sum over the lanes from the ballots of the three bits of the counts
+      const u32 b0 = __ballot_sync (0xffffffffu, mine & 1), b1 = __ballot_sync (0xffffffffu, mine & 2), b2 = __ballot_sync (0xffffffffu, mine & 4);
+      const int total = __popc (b0) + 2 * __popc (b1) + 4 * __popc (b2);
       if (total) {
-        unsigned short *qp = S->cand + tail + (u32) (inc - mine);
-        const u32 ha = ((u32) st << 11) | hdr, hb = ha | 0x400u;
+        unsigned short *qp = S->cand + tail + (u32) (__popc (b0 & lt_lanes) + 2 * __popc (b1 & lt_lanes) + 4 * __popc (b2 & lt_lanes));
         int left = mine;
-        while (A && left) { const int b = __ffs (A) - 1; A &= A - 1; *qp++ = (unsigned short) (ha + b); left--; }
-        while (B && left) { const int b = __ffs (B) - 1; B &= B - 1; *qp++ = (unsigned short) (hb + b); left--; }
+#pragma unroll
+        for (int j = 0; j < SW_ROWS / 2; j++) {
+          const u32 h = ((u32) st << 15) | ((u32) j << 10) | hdr;
+          u32 m = cb[j];
+          while (m && left) { const int b = __ffs (m) - 1; m &= m - 1; *qp++ = (unsigned short) (h + b); left--; }
+          cb[j] = m;
+        }
         tail += (u32) total;
         __syncwarp ();
         while (tail - head >= 32) {
@@ -407,7 +426,10 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
           n_old = n_old > 32 ? n_old - 32 : 0;
         }
       }
-      const bool more = __any_sync (0xffffffffu, (A | B) != 0);
+      bool mine_left = false;
+#pragma unroll
+      for (int j = 0; j < SW_ROWS / 2; j++) mine_left = mine_left || cb[j] != 0;
+      const bool more = __any_sync (0xffffffffu, mine_left);
       if (!more && !n_old) break;
       // candidates of the previous window must go before its derived arrays are overwritten by the next window
       if (n_old) {
@@ -416,28 +438,13 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
         n_old = 0;
       }
       if (!more) break;
-      { // rare: more than SW_QUOTA candidates in one lane; move what is left to the front and go again
-        const u32 cnt = tail - head;
-        const unsigned short v = lane < (int) cnt ? S->cand[head + lane] : (unsigned short) 0;
-        __syncwarp ();
-        if (lane < (int) cnt) S->cand[lane] = v;
-        head = 0; tail = cnt;
-        __syncwarp ();
-      }
     }
-    { // what is left (< 32 candidates) moves to the front of the queue and waits for the next window
-      const u32 cnt = tail - head;
-      const unsigned short v = lane < (int) cnt ? S->cand[head + lane] : (unsigned short) 0;
-      __syncwarp ();
-      if (lane < (int) cnt) S->cand[lane] = v;
-      head = 0; tail = cnt; n_old = cnt;
-    }
+    n_old = tail - head; // what is left (< 32 candidates) waits for the next window
     old_g0 = g0;
     t_cur = t_nxt;
     if ((t_nxt & (SW_CHUNK - 1)) != SW_CHUNK - 1) t_nxt++;
     else { t_nxt = __shfl_sync (0xffffffffu, t_fut, 0) * SW_CHUNK; want_ticket = true; }
     g0 = (long long) t_cur * SW_TILE - SW_HALO_L;
-    __syncwarp (); // every lane is done with the other stage's arrays and this stage's bytes are consumed
   }
   if (tail != head) // what is left belongs to the last window, whose bytes are still staged
     process_batch (lane < (int) (tail - head) ? (int) S->cand[head + lane] : -1, st ^ 1, old_g0, 0);
