@@ -129,13 +129,15 @@ __device__ __forceinline__ u64 codes_at (const u32 *codes, int p)
   return ((u64) __funnelshift_r (a1, a2, sh) << 32) | __funnelshift_r (a0, a1, sh);
 }
 
-// reverse complement of a k-base word of BINARY codes (A0 C1 G2 T3), base j in bits 2j..2j+1
-__device__ __forceinline__ u64 revcomp2 (u64 x, int k)
+// reverse complement of a k-base word of GRAY codes (A0 C1 T2 G3, base j in bits 2j..2j+1), as BINARY codes
+// (A0 C1 G2 T3).  The bit reversal also swaps the two bits of every base: a base (h, l) arrives as (l, h).  Its
+// binary code is (h, h ^ l), the complement of that (~h, ~(h ^ l)): the high bit from the swapped low bit, the low
+// bit from the XOR of both.
+__device__ __forceinline__ u64 revcomp_gray (u64 g, int k, u64 kmask)
 {
-  u64 y = __brevll (x) >> (64 - 2 * k); // k >= 2; reverses the base order and the two bits of every base
-  y = ((y & 0x5555555555555555ULL) << 1) | ((y >> 1) & 0x5555555555555555ULL);
-  const u64 mask = (k == 32) ? ~0ULL : ((1ULL << (2 * k)) - 1);
-  return ~y & mask;
+  const u64 y = __brevll (g) >> (64 - 2 * k); // k >= 2
+  const u64 m5 = 0x5555555555555555ULL;
+  return ~(((y & m5) << 1) | ((y ^ (y >> 1)) & m5)) & kmask;
 }
 __device__ __forceinline__ u32 prmt (u32 a, u32 b, u32 sel)
 {
@@ -206,7 +208,9 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
     if (W == 2 && base + nrec <= capacity) { // one record = one 16-byte store
       const ulonglong2 *src = reinterpret_cast<const ulonglong2*> (S->rec);
       ulonglong2 *dst = reinterpret_cast<ulonglong2*> (out) + base;
-      for (u32 i = lane; i < nrec; i += 32) dst[i] = src[i];
+      static_assert (SW_RCAP (2) <= 64, "two stores per lane cover the staging area");
+      if ((u32) lane < nrec) dst[lane] = src[lane];
+      if ((u32) lane + 32 < nrec) dst[lane + 32] = src[lane + 32];
     } else {
       for (u32 i = lane; i < nrec * W; i += 32) {
         const unsigned long long r = base + i / W;
@@ -253,10 +257,9 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
           if (!(m0 | m1 | m2)) {
             const u64 gl64 = codes_at (codes, P) & kmask, gr64 = codes_at (codes, s + len) & kmask;
             const u64 m5 = 0x5555555555555555ULL;
-            const u64 bl = gl64 ^ ((gl64 >> 1) & m5), br = gr64 ^ ((gr64 >> 1) & m5); // gray -> A0 C1 G2 T3
             u64 ctx0, ctx1;
-            if (gray < 2) { ctx0 = bl; ctx1 = br; }                       // A / C tract: forward strand, :233-238
-            else { ctx0 = revcomp2 (br, k); ctx1 = revcomp2 (bl, k); }    // T / G tract: reverse complement, :239-246
+            if (gray < 2) { ctx0 = gl64 ^ ((gl64 >> 1) & m5); ctx1 = gr64 ^ ((gr64 >> 1) & m5); } // A / C tract: forward strand, gray -> A0 C1 G2 T3, :233-238
+            else { ctx0 = revcomp_gray (gr64, k, kmask); ctx1 = revcomp_gray (gl64, k, kmask); } // T / G tract: reverse complement, :239-246
             r = pack_rec<W> (ctx0, ctx1, gray & 1, sext_field (len, 10), gray < 2 ? 1 : 2, k);
             atomicAdd (&bin_hist[rec_bin<W> (r, k, bin_bits)], 1u);
             emit = true;
@@ -407,16 +410,27 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
       const int mine = have < SW_QUOTA ? have : SW_QUOTA;
       // prefix sum over the lanes from the ballots of the three bits of the counts
       const u32 b0 = __ballot_sync (0xffffffffu, mine & 1), b1 = __ballot_sync (0xffffffffu, mine & 2), b2 = __ballot_sync (0xffffffffu, mine & 4);
+      const bool capped = __any_sync (0xffffffffu, have > SW_QUOTA); // rare: some lane keeps candidates for another round
       const int total = __popc (b0) + 2 * __popc (b1) + 4 * __popc (b2);
       if (total) {
         unsigned short *qp = S->cand + tail + (u32) (__popc (b0 & lt_lanes) + 2 * __popc (b1 & lt_lanes) + 4 * __popc (b2 & lt_lanes));
-        int left = mine;
+        if (!capped) {
 #pragma unroll
-        for (int j = 0; j < SW_ROWS / 2; j++) {
-          const u32 h = ((u32) st << 15) | ((u32) j << 10) | hdr;
-          u32 m = cb[j];
-          while (m && left) { const int b = __ffs (m) - 1; m &= m - 1; *qp++ = (unsigned short) (h + b); left--; }
-          cb[j] = m;
+          for (int j = 0; j < SW_ROWS / 2; j++) {
+            const u32 h = ((u32) st << 15) | ((u32) j << 10) | hdr;
+            u32 m = cb[j];
+            while (m) { const int b = __ffs (m) - 1; m &= m - 1; *qp++ = (unsigned short) (h + b); }
+            cb[j] = 0;
+          }
+        } else {
+          int left = mine;
+#pragma unroll
+          for (int j = 0; j < SW_ROWS / 2; j++) {
+            const u32 h = ((u32) st << 15) | ((u32) j << 10) | hdr;
+            u32 m = cb[j];
+            while (m && left) { const int b = __ffs (m) - 1; m &= m - 1; *qp++ = (unsigned short) (h + b); left--; }
+            cb[j] = m;
+          }
         }
         tail += (u32) total;
         __syncwarp ();
@@ -426,10 +440,7 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
           n_old = n_old > 32 ? n_old - 32 : 0;
         }
       }
-      bool mine_left = false;
-#pragma unroll
-      for (int j = 0; j < SW_ROWS / 2; j++) mine_left = mine_left || cb[j] != 0;
-      const bool more = __any_sync (0xffffffffu, mine_left);
+      const bool more = capped; // a capped lane has bits left
       if (!more && !n_old) break;
       // candidates of the previous window must go before its derived arrays are overwritten by the next window
       if (n_old) {
