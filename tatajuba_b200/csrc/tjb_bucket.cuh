@@ -302,6 +302,7 @@ bucket_reduce_kernel (const u64 *__restrict__ recs, const u32 *__restrict__ bkt_
   __shared__ u32 s_warp[BK_WARPS + 1];
   __shared__ u32 s_bucket;
   __shared__ u32 s_diff[2 * W];
+  __shared__ u32 s_ndist;
 
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const u32 lt_mask = (1u << lane) - 1;
@@ -309,6 +310,7 @@ bucket_reduce_kernel (const u64 *__restrict__ recs, const u32 *__restrict__ bkt_
   for (;;) {
     if (tid == 0) s_bucket = atomicAdd (&meta[META_TICKET], 1u);
     if (tid < 2 * W) s_diff[tid] = 0;
+    if (tid == 2 * W) s_ndist = 0;
     __syncthreads ();
     const u32 b = s_bucket;
     if (b >= meta[META_NBUCKETS]) break;
@@ -344,12 +346,16 @@ bucket_reduce_kernel (const u64 *__restrict__ recs, const u32 *__restrict__ bkt_
     // in a shared-memory hash table first (run-length count of hopo_counter.c:355-365 without the sort) and sort only
     // the distinct observations.  Table entry = index of the first record seen with that key (its representative);
     // s_cntrec[representative] = forward-strand copies | reverse-strand copies << 16 (canon_flag = which are non-zero, :362)
-    u32 tsize = 64;
-    while (tsize < 2 * n) tsize <<= 1;
+    const u32 tsize = n <= 32 ? 64u : 1u << (32 - __clz (2 * n - 1)); // power of two >= max(64, 2 n)
     for (u32 i = tid; i < tsize; i += BK_THREADS) s_tab[i] = BK_EMPTY;
     for (u32 i = tid; i < n; i += BK_THREADS) s_cntrec[i] = 0;
     __syncthreads ();
-    for (u32 i = tid; i < n; i += BK_THREADS) {
+    // the record that claims a table slot is the representative of its key and appends itself to s_perm0 (one
+    // shared-memory atomic per warp and round; the order is arbitrary, the keys are distinct and get sorted below)
+    for (u32 i0 = 0; i0 < n; i0 += BK_THREADS) {
+      const u32 i = i0 + tid;
+      bool is_new = false;
+      if (i < n) {
       Rec<W> x;
 #pragma unroll
       for (int j = 0; j < W; j++) x.w[j] = s_w[j * BK_CAP + i];
@@ -367,17 +373,18 @@ bucket_reduce_kernel (const u64 *__restrict__ recs, const u32 *__restrict__ bkt_
         slot = (slot + 1) & (tsize - 1);
       }
       atomicAdd (&s_cntrec[rep], (x.w[0] & 1) ? 1u : 0x10000u); // flag 1 = forward, 2 = reverse complement
+      is_new = rep == i;
+      }
+      const u32 nb = __ballot_sync (0xffffffffu, is_new);
+      if (nb) {
+        u32 base = 0;
+        if (lane == 0) base = atomicAdd (&s_ndist, (u32) __popc (nb));
+        base = __shfl_sync (0xffffffffu, base, 0);
+        if (is_new) s_perm0[base + __popc (nb & lt_mask)] = (unsigned short) i;
+      }
     }
     __syncthreads ();
-    u32 n_dist;
-    { // representatives -> s_perm0[0 .. n_dist)
-      const u32 per = tsize / BK_THREADS ? tsize / BK_THREADS : 1, t0 = tid * per;
-      u32 cnt = 0;
-      for (u32 i = t0; i < t0 + per && i < tsize; i++) cnt += s_tab[i] != BK_EMPTY;
-      u32 pos = blk_excl_scan<BK_THREADS> (cnt, s_warp, &n_dist);
-      for (u32 i = t0; i < t0 + per && i < tsize; i++) { const u32 c = s_tab[i]; if (c != BK_EMPTY) s_perm0[pos++] = (unsigned short) c; }
-    }
-    __syncthreads ();
+    const u32 n_dist = s_ndist;
     // ---- sort the distinct observations, ascending in `cur` ------------------------------------------------------
     unsigned short *cur = s_perm0, *nxt = s_perm1;
     if (n_dist <= BK_RANKSORT_MAX) {
