@@ -225,16 +225,33 @@ def main():
     ctx.set_profiling(0)
 
     # ---- end-to-end arm: pinned host buffer -> C ABI -> host results ----------------------------------
-    for _ in range(2):
-        ctx.count_host(h_pinned, opt)
-    barrier()
-    e0.record(stream)
-    for _ in range(args.steps):
-        hh = ctx.count_host(h_pinned, opt)
-    e1.record(stream)
-    barrier()
-    ms_e2e = max_over_ranks(e0.elapsed_time(e1))
+    # (large host buffers cross PCIe 2-bit packed + exceptions, packed by host threads inside the timed region and
+    # rebuilt on the device; TJB_HOST_PACK=0 = the bytes as they are, timed next to it over 3 steps)
+    def e2e_arm(steps):
+        for _ in range(2):
+            ctx.count_host(h_pinned, opt)
+        barrier()
+        ctx.reset_kernel_stats()
+        e0.record(stream)
+        for _ in range(steps):
+            h = ctx.count_host(h_pinned, opt)
+        e1.record(stream)
+        barrier()
+        return max_over_ranks(e0.elapsed_time(e1)) / steps, ctx.h2d_bytes() // steps, h
+    packing = os.environ.get("TJB_HOST_PACK")
+    os.environ["TJB_HOST_PACK"] = "0"
+    ms_plain, h2d_plain, _ = e2e_arm(3)
+    if packing is None:
+        del os.environ["TJB_HOST_PACK"]
+    else:
+        os.environ["TJB_HOST_PACK"] = packing
+    ms_e2e_step, h2d, hh = e2e_arm(args.steps)
+    ms_e2e = ms_e2e_step * args.steps
     d2h = 40 * hh.n_elem + 8 * hh.n_idx + 64
+    transfer = {"mode": "2-bit packed + exceptions" if h2d < n_bytes else "plain", "host_bytes_per_step": n_bytes,
+                "host_threads": os.cpu_count() if packing is None else packing,
+                "plain": {"ms_per_step": ms_plain, "h2d_bytes_per_step": h2d_plain,
+                          "value": world * n_bases / (ms_plain * 1e-3), "unit": "bases/s"}}
 
     # ---- cross-sample exchange: query rows -> allgather over the ranks -> union on the GPU ---------
     from tatajuba_b200 import genome_set
@@ -293,7 +310,8 @@ def main():
                    "l2": "input (503 MB) larger than L2 (126 MB); no flush needed", "n_raw": hc.n_raw,
                    "n_distinct": hc.n_distinct, "n_elem": hc.n_elem, "n_idx": hc.n_idx, "coverage": hc.coverage},
         "e2e": {"value": world * n_bases * args.steps / (ms_e2e * 1e-3), "unit": "bases/s",
-                "ms_per_step": ms_e2e / args.steps, "h2d_bytes_per_step": n_bytes, "d2h_bytes_per_step": d2h},
+                "ms_per_step": ms_e2e / args.steps, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+                "transfer": transfer},
         "gpu_launches": launches,
         "roofline": {"kernel": "tjb_scan_kernel", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "peak_source": peak_src, "traffic": None,

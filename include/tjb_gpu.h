@@ -93,6 +93,11 @@ int  tjb_ctx_kernel_stats (tjb_ctx *ctx, tjb_kernel_stat *stats, int max_stats);
 void tjb_ctx_reset_kernel_stats (tjb_ctx *ctx);
 /* kernels launched by this context since creation (or since reset_kernel_stats) */
 int64_t tjb_ctx_launch_count (const tjb_ctx *ctx);
+/* bytes tjb_count_sample_host() has sent host -> device since the last tjb_ctx_reset_kernel_stats().  Large host
+ * buffers cross PCIe as 2-bit codes plus (position, byte) pairs for every byte that is not one of "ACGT" and are
+ * rebuilt byte for byte on the device, so this is less than the bytes handed in (environment TJB_HOST_PACK=0 sends
+ * them as they are, TJB_HOST_PACK=n packs with n threads; default one per hardware thread, at most 32). */
+int64_t tjb_ctx_htod_bytes (const tjb_ctx *ctx);
 
 /* Whole replaced span from FASTQ/FASTA(.gz) files: n_files = 1 (single end) or 2 (R1 then R2 into one counter,
  * genome_set.c:72-73).  Host C decode (kseq semantics, src/kseq.h:172-212) into pinned double-buffered chunks,

@@ -14,7 +14,7 @@ CSRC = os.path.join(HERE, "csrc")
 # every symbol include/tjb_gpu.h declares (checked by tests/test_abi.py)
 EXPORTS = [
     "tjb_version", "tjb_strerror", "tjb_ctx_last_error", "tjb_ctx_create", "tjb_ctx_destroy", "tjb_ctx_stream",
-    "tjb_ctx_set_profiling", "tjb_ctx_kernel_stats", "tjb_ctx_reset_kernel_stats", "tjb_ctx_launch_count",
+    "tjb_ctx_set_profiling", "tjb_ctx_kernel_stats", "tjb_ctx_reset_kernel_stats", "tjb_ctx_launch_count", "tjb_ctx_htod_bytes",
     "tjb_count_sample_files", "tjb_count_sample_host", "tjb_count_sample_device", "tjb_count_sample",
     "tjb_counter_out_free", "tjb_query_rows", "tjb_union_queries_device", "tjb_merge_tracts", "tjb_reader_open", "tjb_reader_fill", "tjb_reader_close",
 ]
@@ -72,6 +72,8 @@ def load():
     lib.tjb_ctx_reset_kernel_stats.restype = None
     lib.tjb_ctx_launch_count.restype = i64
     lib.tjb_ctx_launch_count.argtypes = [vp]
+    lib.tjb_ctx_htod_bytes.restype = i64
+    lib.tjb_ctx_htod_bytes.argtypes = [vp]
     po, pout = C.POINTER(TjbOpts), C.POINTER(TjbCounterOut)
     lib.tjb_count_sample_files.argtypes = [vp, C.POINTER(cp), i32, po, pout]
     lib.tjb_count_sample_host.argtypes = [vp, vp, sz, po, pout]

@@ -19,6 +19,7 @@
 #include "tjb_sort.cuh"
 #include "tjb_reduce.cuh"
 #include "tjb_union.cuh"
+#include "tjb_hostpack.h"
 
 #define TJB_VERSION_STR "tatajuba_b200 0.1 (sm_100a)"
 #define TJB_CHUNK_BYTES (32u << 20)      // files path: pinned chunk of decoded reads (two per decoder thread)
@@ -26,10 +27,10 @@
 
 enum KernelId { K_SCAN = 0, K_PLAN, K_PARTITION, K_BUCKET, K_TOTALS, K_PACK, K_COVMAX, K_RECHIST,
                 // global multi-pass path, only for buckets too large for shared memory
-                K_SORT_HIST, K_SORT_SCATTER, K_PSCAN, K_RLE, K_GROUP, K_UNION, K_COUNT };
+                K_SORT_HIST, K_SORT_SCATTER, K_PSCAN, K_RLE, K_GROUP, K_UNION, K_UNPACK, K_COUNT };
 static const char *kKernelNames[K_COUNT] = {"tjb_scan_kernel", "plan_kernel", "partition_kernel", "bucket_reduce_kernel", "totals_kernel",
                                             "pack_kernel", "cov_max_kernel", "rec_hist_kernel", "rsort_hist_kernel",
-                                            "rsort_scatter_kernel", "pscan_kernels", "rle_kernels", "group_kernels", "union_kernels"};
+                                            "rsort_scatter_kernel", "pscan_kernels", "rle_kernels", "group_kernels", "union_kernels", "unpack_kernels"};
 
 struct DevBuf {
   void *p = nullptr;
@@ -44,6 +45,7 @@ struct tjb_ctx {
   std::string err;
   int profiling = 0; // 0 off, 1 scan kernel only, 2 every kernel
   int64_t launches = 0;
+  int64_t h2d_bytes = 0; // host-buffer path: bytes sent host -> device
   tjb_kernel_stat stats[K_COUNT];
   std::vector<PendingEvent> pending;
   std::vector<cudaEvent_t> free_events;
@@ -52,6 +54,10 @@ struct tjb_ctx {
   uint8_t *h_pinned[4] = {nullptr, nullptr, nullptr, nullptr}; // files path: two chunks per decoder thread
   cudaEvent_t h_free[4] = {nullptr, nullptr, nullptr, nullptr}; // pinned chunk i may be overwritten once this has fired
   DevBuf d_chunk[2];
+  // host-buffer path with 2-bit packed transfers (tjb_hostpack.h): packer threads, pinned and device staging per chunk slot
+  tjb_packer *packer = nullptr;
+  uint8_t *h_pk[2] = {nullptr, nullptr}; uint32_t *h_exc_pos[2] = {nullptr, nullptr}; uint8_t *h_exc_val[2] = {nullptr, nullptr};
+  DevBuf d_pk[2], d_exc_pos[2], d_exc_val[2];
 
   DevBuf rec_a, rec_b; // raw tract observations + sort ping-pong
   size_t rec_capacity = 0; // records rec_a can hold
@@ -691,7 +697,14 @@ void tjb_ctx_destroy (tjb_ctx *ctx)
   if (ctx->stream) cudaStreamSynchronize (ctx->stream);
   resolve_events (ctx);
   for (cudaEvent_t e : ctx->free_events) cudaEventDestroy (e);
-  DevBuf *bufs[] = {&ctx->d_chunk[0], &ctx->d_chunk[1], &ctx->rec_a, &ctx->rec_b, &ctx->hist, &ctx->ptmp, &ctx->heads, &ctx->pos, &ctx->seg,
+  if (ctx->packer) tjb_packer_destroy (ctx->packer);
+  for (int i = 0; i < 2; i++) {
+    if (ctx->h_pk[i]) cudaFreeHost (ctx->h_pk[i]);
+    if (ctx->h_exc_pos[i]) cudaFreeHost (ctx->h_exc_pos[i]);
+    if (ctx->h_exc_val[i]) cudaFreeHost (ctx->h_exc_val[i]);
+  }
+  DevBuf *bufs[] = {&ctx->d_pk[0], &ctx->d_pk[1], &ctx->d_exc_pos[0], &ctx->d_exc_pos[1], &ctx->d_exc_val[0], &ctx->d_exc_val[1],
+                    &ctx->d_chunk[0], &ctx->d_chunk[1], &ctx->rec_a, &ctx->rec_b, &ctx->hist, &ctx->ptmp, &ctx->heads, &ctx->pos, &ctx->seg,
                     &ctx->drec, &ctx->dcount, &ctx->keep, &ctx->kpos, &ctx->krec, &ctx->kcount, &ctx->cw, &ctx->csum, &ctx->gkeep,
                     &ctx->gkpos, &ctx->out40, &ctx->idx_i, &ctx->idx_f, &ctx->out_cnt, &ctx->out_ii, &ctx->out_if, &ctx->cov_tab};
   for (DevBuf *b : bufs) if (b->p) cudaFree (b->p);
@@ -730,9 +743,11 @@ void tjb_ctx_reset_kernel_stats (tjb_ctx *ctx)
   if (!ctx) return;
   for (int i = 0; i < K_COUNT; i++) { ctx->stats[i].launches = 0; ctx->stats[i].ms_total = 0; ctx->stats[i].bytes_algorithmic = 0; }
   ctx->launches = 0;
+  ctx->h2d_bytes = 0;
 }
 
 int64_t tjb_ctx_launch_count (const tjb_ctx *ctx) { return ctx ? ctx->launches : 0; }
+int64_t tjb_ctx_htod_bytes (const tjb_ctx *ctx) { return ctx ? ctx->h2d_bytes : 0; }
 
 int tjb_count_sample_device (tjb_ctx *ctx, const void *d_seqs, size_t n_bytes, const tjb_opts *opt, tjb_counter_out *out)
 {
@@ -768,14 +783,69 @@ static size_t whole_reads_prefix (const uint8_t *p, size_t len, size_t remaining
   return nl ? (size_t) ((const uint8_t*) nl - p) + 1 : 0;
 }
 
+// ---- 2-bit packed chunks (tjb_hostpack.h) back to the bytes the scan reads -------------------------------------------
+// one thread per packed word = 16 bases = one 16-byte store; PRMT looks the letters up ("ACTG" by gray code)
+__global__ void __launch_bounds__ (256) unpack_kernel (const u32 *__restrict__ packed, size_t n_words, uint4 *__restrict__ out)
+{
+  for (size_t i = (size_t) blockIdx.x * 256 + threadIdx.x; i < n_words; i += (size_t) gridDim.x * 256) {
+    const u32 p = packed[i];
+    u32 w[4];
+#pragma unroll
+    for (int j = 0; j < 4; j++) {
+      u32 y = (p >> (8 * j)) & 0xffu;      // four 2-bit codes -> four nibbles
+      y = (y | (y << 4)) & 0x0F0Fu;
+      y = (y | (y << 2)) & 0x3333u;
+      w[j] = __byte_perm (SCAN_GRAY_LUT, 0u, y);
+    }
+    out[i] = make_uint4 (w[0], w[1], w[2], w[3]);
+  }
+}
+// every byte that is not one of "ACGT" (read separators, N, lower case, ...) travels as (position, byte)
+__global__ void __launch_bounds__ (256) unpack_exc_kernel (const u32 *__restrict__ pos, const uint8_t *__restrict__ val, u32 n, uint8_t *__restrict__ out)
+{
+  const u32 i = blockIdx.x * 256 + threadIdx.x;
+  if (i < n) out[pos[i]] = val[i];
+}
+
+#define TJB_PACK_MIN_BYTES ((size_t) 8 << 20)          // below this the packer threads are not worth waking
+#define TJB_PACK_EXC_CAP (TJB_HOST_CHUNK_BYTES / 16)   // exceptions per chunk before it is sent unpacked (reads of >= ~20 bases)
+static bool packed_transfer_enabled (tjb_ctx *ctx, size_t n_bytes)
+{
+  const char *e = getenv ("TJB_HOST_PACK"); // "0" disables, a number > 0 sets the thread count
+  if (e && atoi (e) == 0) return false;
+  if (n_bytes < TJB_PACK_MIN_BYTES) return false;
+  if (!ctx->packer) {
+    ctx->packer = tjb_packer_create (e ? atoi (e) : 0);
+    if (!ctx->packer) return false;
+  }
+  if (tjb_packer_threads (ctx->packer) < 4 && !e) return false; // PCIe beats a few cores
+  for (int i = 0; i < 2; i++) {
+    if (!ctx->h_pk[i] && cudaMallocHost ((void**) &ctx->h_pk[i], TJB_HOST_CHUNK_BYTES / 4 + 64) != cudaSuccess) return false;
+    if (!ctx->h_exc_pos[i] && cudaMallocHost ((void**) &ctx->h_exc_pos[i], (size_t) TJB_PACK_EXC_CAP * 4) != cudaSuccess) return false;
+    if (!ctx->h_exc_val[i] && cudaMallocHost ((void**) &ctx->h_exc_val[i], TJB_PACK_EXC_CAP) != cudaSuccess) return false;
+    if (ensure (ctx, ctx->d_pk[i], TJB_HOST_CHUNK_BYTES / 4 + 64) || ensure (ctx, ctx->d_exc_pos[i], (size_t) TJB_PACK_EXC_CAP * 4) ||
+        ensure (ctx, ctx->d_exc_val[i], TJB_PACK_EXC_CAP)) return false;
+  }
+  return true;
+}
+struct PackerSession { // the packer threads spin for the duration of one call
+  tjb_packer *p;
+  explicit PackerSession (tjb_packer *q) : p (q) { if (p) tjb_packer_begin (p); }
+  ~PackerSession () { if (p) tjb_packer_end (p); }
+};
+
 // Host buffer: chunks are copied on the context's copy stream while the previous chunk is scanned on the compute
 // stream (two device chunk buffers); one optimistic pass, redone with the exact record capacity after an overflow.
+// Large inputs cross PCIe 2-bit packed (host threads pack chunk i+1 while chunk i is copied, unpacked and scanned).
 int tjb_count_sample_host (tjb_ctx *ctx, const uint8_t *seqs, size_t n_bytes, const tjb_opts *opt, tjb_counter_out *out)
 {
   if (!ctx || !out || (n_bytes && !seqs)) return TJB_ERR_ARG;
   const size_t max_chunk = TJB_HOST_CHUNK_BYTES;
   size_t want = n_bytes / 16 + 65536;
   int rc = 0;
+  CU (cudaSetDevice (ctx->device));
+  const bool packed = packed_transfer_enabled (ctx, n_bytes);
+  PackerSession session (packed ? ctx->packer : nullptr);
   for (int attempt = 0; attempt < 3; attempt++) {
     out_reset (out);
     TRY (begin_sample (ctx, opt, n_bytes));
@@ -790,8 +860,32 @@ int tjb_count_sample_host (tjb_ctx *ctx, const uint8_t *seqs, size_t n_bytes, co
     while (off < n_bytes) {
       size_t len = whole_reads_prefix (seqs + off, max_chunk < n_bytes - off ? max_chunk : n_bytes - off, n_bytes - off);
       if (!len) { ctx->err = "a single read exceeds the chunk size"; return TJB_ERR_TOO_LARGE; }
+      long n_exc = -1;
+      if (packed) {
+        if (used[which]) CU (cudaEventSynchronize (ctx->ev_copied[which])); // the slot's pinned staging has been read
+        n_exc = tjb_packer_run (ctx->packer, seqs + off, len, ctx->h_pk[which], ctx->h_exc_pos[which], ctx->h_exc_val[which], TJB_PACK_EXC_CAP);
+      }
       if (used[which]) CU (cudaStreamWaitEvent (ctx->copy_stream, ctx->ev_scanned[which], 0)); // buffer free again
-      CU (cudaMemcpyAsync (ctx->d_chunk[which].p, seqs + off, len, cudaMemcpyHostToDevice, ctx->copy_stream));
+      if (n_exc >= 0) {
+        const size_t n_words = (len + 15) / 16;
+        CU (cudaMemcpyAsync (ctx->d_pk[which].p, ctx->h_pk[which], (len + 3) / 4, cudaMemcpyHostToDevice, ctx->copy_stream));
+        if (n_exc) {
+          CU (cudaMemcpyAsync (ctx->d_exc_pos[which].p, ctx->h_exc_pos[which], (size_t) n_exc * 4, cudaMemcpyHostToDevice, ctx->copy_stream));
+          CU (cudaMemcpyAsync (ctx->d_exc_val[which].p, ctx->h_exc_val[which], (size_t) n_exc, cudaMemcpyHostToDevice, ctx->copy_stream));
+        }
+        ctx->h2d_bytes += (int64_t) ((len + 3) / 4 + (size_t) n_exc * 5);
+        const u32 g = (u32) (nblk (n_words, 256) < (size_t) ctx->sm_count * 8 ? nblk (n_words, 256) : (size_t) ctx->sm_count * 8);
+        unpack_kernel<<<g, 256, 0, ctx->copy_stream>>> ((const u32*) ctx->d_pk[which].p, n_words, (uint4*) ctx->d_chunk[which].p);
+        ctx->launches++; ctx->stats[K_UNPACK].launches++; ctx->stats[K_UNPACK].bytes_algorithmic += (int64_t) (len + (len + 3) / 4);
+        if (n_exc) {
+          unpack_exc_kernel<<<(u32) nblk ((size_t) n_exc, 256), 256, 0, ctx->copy_stream>>> ((const u32*) ctx->d_exc_pos[which].p, (const uint8_t*) ctx->d_exc_val[which].p, (u32) n_exc, (uint8_t*) ctx->d_chunk[which].p);
+          ctx->launches++; ctx->stats[K_UNPACK].launches++; ctx->stats[K_UNPACK].bytes_algorithmic += (int64_t) n_exc * 6;
+        }
+        CU (cudaGetLastError ());
+      } else {
+        CU (cudaMemcpyAsync (ctx->d_chunk[which].p, seqs + off, len, cudaMemcpyHostToDevice, ctx->copy_stream));
+        ctx->h2d_bytes += (int64_t) len;
+      }
       CU (cudaEventRecord (ctx->ev_copied[which], ctx->copy_stream));
       CU (cudaStreamWaitEvent (ctx->stream, ctx->ev_copied[which], 0));
       TRY (launch_scan (ctx, (const uint8_t*) ctx->d_chunk[which].p, len, opt));

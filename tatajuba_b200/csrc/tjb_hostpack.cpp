@@ -1,0 +1,228 @@
+// Host-side 2-bit packing of sequence bytes (see tjb_hostpack.h).  Plain C++ threads; the inner loop is AVX2 when the
+// CPU has it (checked at run time), scalar otherwise.
+#include "tjb_hostpack.h"
+
+#include <atomic>
+#include <condition_variable>
+#include <mutex>
+#include <string.h>
+#include <thread>
+#include <vector>
+#if defined(__x86_64__)
+#include <immintrin.h>
+#define TJB_PAUSE() _mm_pause ()
+#else
+#define TJB_PAUSE() do { } while (0)
+#endif
+
+// spin-wait step: a few hundred pauses, then give the core away (several ranks may share the host cores)
+static inline void spin_step (unsigned &spins)
+{
+  if (++spins < 512) TJB_PAUSE (); else { spins = 0; std::this_thread::yield (); }
+}
+
+static inline bool is_acgt (uint8_t b) { return b == 'A' || b == 'C' || b == 'G' || b == 'T'; }
+
+long tjb_pack_scalar (const uint8_t *src, size_t n, uint8_t *packed, uint32_t *exc_pos, uint8_t *exc_val, size_t cap, uint32_t pos0)
+{
+  size_t ne = 0;
+  for (size_t i = 0; i < n; i += 4) {
+    unsigned v = 0;
+    for (size_t j = 0; j < 4 && i + j < n; j++) {
+      const uint8_t b = src[i + j];
+      v |= ((b >> 1) & 3u) << (2 * j);
+      if (!is_acgt (b)) {
+        if (ne >= cap) return -1;
+        exc_pos[ne] = pos0 + (uint32_t) (i + j);
+        exc_val[ne] = b;
+        ne++;
+      }
+    }
+    packed[i >> 2] = (uint8_t) v;
+  }
+  return (long) ne;
+}
+
+#if defined(__x86_64__)
+// n is a multiple of 32 here
+__attribute__ ((target ("avx2"))) static long pack_avx2 (const uint8_t *src, size_t n, uint8_t *packed, uint32_t *exc_pos, uint8_t *exc_val,
+                                                          size_t cap, uint32_t pos0)
+{
+  const __m256i three = _mm256_set1_epi8 (3);
+  const __m256i lut = _mm256_setr_epi8 ('A', 'C', 'T', 'G', 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 'A', 'C', 'T', 'G', 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0);
+  const __m256i w14 = _mm256_set1_epi16 (0x0401);     // bytes (1, 4): c0 + 4 c1 per 16-bit lane
+  const __m256i w116 = _mm256_set1_epi32 (0x00100001); // words (1, 16): + 16 (c2 + 4 c3) per 32-bit lane
+  const __m256i pick = _mm256_setr_epi8 (0, 4, 8, 12, -1, -1, -1, -1, -1, -1, -1, -1, -1, -1, -1, -1, 0, 4, 8, 12, -1, -1, -1, -1, -1, -1, -1, -1, -1, -1, -1, -1);
+  size_t ne = 0;
+  for (size_t i = 0; i < n; i += 32) {
+    const __m256i v = _mm256_loadu_si256 ((const __m256i*) (src + i));
+    const __m256i c = _mm256_and_si256 (_mm256_srli_epi16 (v, 1), three);
+    const __m256i ok = _mm256_cmpeq_epi8 (_mm256_shuffle_epi8 (lut, c), v);
+    const __m256i t = _mm256_madd_epi16 (_mm256_maddubs_epi16 (c, w14), w116); // one packed byte per 32-bit lane
+    const __m256i q = _mm256_shuffle_epi8 (t, pick);
+    uint32_t lo = (uint32_t) _mm256_cvtsi256_si32 (q), hi = (uint32_t) _mm256_extract_epi32 (q, 4);
+    memcpy (packed + (i >> 2), &lo, 4);
+    memcpy (packed + (i >> 2) + 4, &hi, 4);
+    uint32_t bad = ~(uint32_t) _mm256_movemask_epi8 (ok);
+    while (bad) {
+      const int j = __builtin_ctz (bad);
+      bad &= bad - 1;
+      if (ne >= cap) return -1;
+      exc_pos[ne] = pos0 + (uint32_t) (i + j);
+      exc_val[ne] = src[i + j];
+      ne++;
+    }
+  }
+  return (long) ne;
+}
+#endif
+
+static long pack_range (const uint8_t *src, size_t n, uint8_t *packed, uint32_t *exc_pos, uint8_t *exc_val, size_t cap, uint32_t pos0)
+{
+  size_t body = 0;
+  long ne = 0;
+#if defined(__x86_64__)
+  static const bool have_avx2 = __builtin_cpu_supports ("avx2");
+  if (have_avx2) {
+    body = n & ~(size_t) 31;
+    ne = pack_avx2 (src, body, packed, exc_pos, exc_val, cap, pos0);
+    if (ne < 0) return -1;
+  }
+#endif
+  const long nt = tjb_pack_scalar (src + body, n - body, packed + (body >> 2), exc_pos + ne, exc_val + ne, cap - (size_t) ne, pos0 + (uint32_t) body);
+  return nt < 0 ? -1 : ne + nt;
+}
+
+#define TJB_PACK_BLOCK ((size_t) 64 << 10) // bytes per unit of work (a multiple of 32): shares are drawn, not dealt
+
+struct tjb_packer {
+  int T = 1;
+  std::vector<std::thread> th;
+  std::mutex mu;
+  std::condition_variable cv;
+  bool active = false, quit = false;      // guarded by mu
+  std::atomic<bool> spinning{false};
+  std::atomic<uint64_t> gen{0};           // jobs issued so far; every worker takes part in every job exactly once
+  std::atomic<uint64_t> done{0};
+  // the job
+  const uint8_t *src = nullptr; size_t n = 0, cap = 0, n_blocks = 0;
+  uint8_t *packed = nullptr; uint32_t *exc_pos = nullptr; uint8_t *exc_val = nullptr;
+  std::atomic<size_t> next_block{0}, exc_total{0};
+  std::atomic<bool> overflow{false};
+  std::vector<std::vector<uint32_t>> lpos; // exceptions of the block a participant is working on
+  std::vector<std::vector<uint8_t>> lval;
+};
+
+// participants 0 .. T-1 are the workers, T is the calling thread.  Blocks are drawn from a counter, so a participant
+// that lost its core for a while costs one block, not a share; a block's exceptions are appended to the chunk's list
+// at an offset reserved with one atomic (their order does not matter: the device scatters them by position).
+static void packer_take_part (tjb_packer *p, int who)
+{
+  uint32_t *lp = p->lpos[who].data ();
+  uint8_t *lv = p->lval[who].data ();
+  for (;;) {
+    const size_t b = p->next_block.fetch_add (1, std::memory_order_relaxed);
+    if (b >= p->n_blocks) break;
+    const size_t lo = b * TJB_PACK_BLOCK, hi = lo + TJB_PACK_BLOCK < p->n ? lo + TJB_PACK_BLOCK : p->n;
+    const long cnt = pack_range (p->src + lo, hi - lo, p->packed + (lo >> 2), lp, lv, TJB_PACK_BLOCK, (uint32_t) lo);
+    if (cnt > 0) {
+      const size_t off = p->exc_total.fetch_add ((size_t) cnt, std::memory_order_relaxed);
+      if (off + (size_t) cnt <= p->cap) {
+        memcpy (p->exc_pos + off, lp, (size_t) cnt * sizeof (uint32_t));
+        memcpy (p->exc_val + off, lv, (size_t) cnt);
+      } else p->overflow.store (true, std::memory_order_relaxed);
+    }
+  }
+}
+
+static void packer_worker (tjb_packer *p, int tid)
+{
+  uint64_t seen = 0;
+  unsigned spins = 0;
+  for (;;) {
+    {
+      std::unique_lock<std::mutex> lk (p->mu);
+      p->cv.wait (lk, [&] { return p->quit || p->active; });
+      if (p->quit) return;
+    }
+    while (p->spinning.load (std::memory_order_acquire)) {
+      const uint64_t g = p->gen.load (std::memory_order_acquire);
+      if (g == seen) { spin_step (spins); continue; }
+      seen++; // jobs are issued one at a time: g == seen + 1
+      packer_take_part (p, tid);
+      p->done.fetch_add (1, std::memory_order_acq_rel);
+    }
+    // end () cleared `active` under the mutex before `spinning`: the wait at the top parks this worker again
+  }
+}
+
+tjb_packer *tjb_packer_create (int n_threads)
+{
+  if (n_threads <= 0) { // leave two hardware threads to the caller and the driver: the workers spin
+    n_threads = (int) std::thread::hardware_concurrency () - 2;
+    if (n_threads > 32) n_threads = 32;
+    if (n_threads < 1) n_threads = 1;
+  }
+  tjb_packer *p = new tjb_packer;
+  p->T = n_threads;
+  p->lpos.resize (n_threads + 1); p->lval.resize (n_threads + 1);
+  for (int t = 0; t <= n_threads; t++) { p->lpos[t].resize (TJB_PACK_BLOCK); p->lval[t].resize (TJB_PACK_BLOCK); }
+  for (int t = 0; t < n_threads; t++) p->th.emplace_back (packer_worker, p, t);
+  return p;
+}
+
+void tjb_packer_destroy (tjb_packer *p)
+{
+  if (!p) return;
+  { std::lock_guard<std::mutex> lk (p->mu); p->quit = true; p->active = false; }
+  p->spinning.store (false, std::memory_order_release);
+  p->cv.notify_all ();
+  for (auto &t : p->th) t.join ();
+  delete p;
+}
+
+int tjb_packer_threads (const tjb_packer *p) { return p ? p->T : 0; }
+
+void tjb_packer_begin (tjb_packer *p)
+{
+  { std::lock_guard<std::mutex> lk (p->mu); p->active = true; p->spinning.store (true, std::memory_order_release); }
+  p->cv.notify_all ();
+}
+
+void tjb_packer_end (tjb_packer *p)
+{
+  { std::lock_guard<std::mutex> lk (p->mu); p->active = false; p->spinning.store (false, std::memory_order_release); }
+  p->cv.notify_all ();
+}
+
+long tjb_packer_run (tjb_packer *p, const uint8_t *src, size_t n, uint8_t *packed, uint32_t *exc_pos, uint8_t *exc_val, size_t cap)
+{
+  if (!n) return 0;
+  p->src = src; p->n = n; p->packed = packed; p->exc_pos = exc_pos; p->exc_val = exc_val; p->cap = cap;
+  p->n_blocks = (n + TJB_PACK_BLOCK - 1) / TJB_PACK_BLOCK;
+  p->next_block.store (0, std::memory_order_relaxed);
+  p->exc_total.store (0, std::memory_order_relaxed);
+  p->overflow.store (false, std::memory_order_relaxed);
+  const uint64_t g = p->gen.fetch_add (1, std::memory_order_acq_rel) + 1;
+  packer_take_part (p, p->T); // the caller packs too instead of only waiting
+  unsigned spins = 0;
+  while (p->done.load (std::memory_order_acquire) < (uint64_t) p->T * g) spin_step (spins);
+  const size_t total = p->exc_total.load (std::memory_order_relaxed);
+  return (p->overflow.load (std::memory_order_relaxed) || total > cap) ? -1 : (long) total;
+}
+
+// test hook (tests/test_hostpack.py): one chunk through a fresh pool of `threads` workers
+extern "C" long tjb_hostpack_selftest (const uint8_t *src, size_t n, int threads, uint8_t *packed, uint32_t *exc_pos, uint8_t *exc_val, size_t cap)
+{
+  if (threads == 0) return tjb_pack_scalar (src, n, packed, exc_pos, exc_val, cap, 0);
+  tjb_packer *p = tjb_packer_create (threads);
+  tjb_packer_begin (p);
+  long r = -2;
+  for (int rep = 0; rep < 3; rep++) r = tjb_packer_run (p, src, n, packed, exc_pos, exc_val, cap); // the pool is reusable
+  tjb_packer_end (p);
+  tjb_packer_begin (p); // and can be parked and woken again
+  const long r2 = tjb_packer_run (p, src, n, packed, exc_pos, exc_val, cap);
+  tjb_packer_end (p);
+  tjb_packer_destroy (p);
+  return r == r2 ? r : -3;
+}

@@ -44,6 +44,11 @@ class Context:
 
     def __init__(self, device=0):
         self.lib = _lib.load()
+        # host-buffer path: the packer threads of the 2-bit transfer spin while a sample is fed, so ranks that share
+        # one host (torchrun: LOCAL_WORLD_SIZE) split the cores between them; fewer than 4 each = plain transfers
+        if "TJB_HOST_PACK" not in os.environ and int(os.environ.get("LOCAL_WORLD_SIZE", "1")) > 1:
+            share = (os.cpu_count() or 1) // int(os.environ["LOCAL_WORLD_SIZE"]) - 1
+            os.environ["TJB_HOST_PACK"] = str(share if share >= 4 else 0)
         h = C.c_void_p()
         rc = self.lib.tjb_ctx_create(int(device), C.byref(h))
         if rc < 0:
@@ -75,6 +80,10 @@ class Context:
 
     def launch_count(self):
         return int(self.lib.tjb_ctx_launch_count(self.h))
+
+    def h2d_bytes(self):
+        """bytes count_host() has sent over PCIe since the last reset_kernel_stats() (packed transfers send fewer)"""
+        return int(self.lib.tjb_ctx_htod_bytes(self.h))
 
     def stream(self):
         return self.lib.tjb_ctx_stream(self.h)

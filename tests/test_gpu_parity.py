@@ -204,3 +204,31 @@ def test_gpu_fuzz_arbitrary_bytes(ctx, restatement, seed):
     buf = _fuzz_buffer(rng, int(rng.integers(200, 3000)), alphabet, weights, int(rng.choice([30, 160, 700])))
     k, m = int(rng.integers(2, 33)), int(rng.integers(1, 7))
     check(ctx, restatement, buf, k, m, int(rng.integers(0, 4)), bool(rng.integers(0, 2)), f"fuzz seed={seed} k={k} m={m}")
+
+
+def test_gpu_packed_host_transfer_is_transparent(ctx, restatement, monkeypatch):
+    """Host buffers of 8 MiB and more cross PCIe 2-bit packed + exceptions and are rebuilt on the device
+    (csrc/tjb_hostpack.cpp): three chunks of reads with N, lower case and stray bytes sprinkled in must give the result
+    of the unpacked transfer, of the device-resident path and, on a prefix the oracle finishes quickly, of the oracle."""
+    import torch
+    buf = synth.sample_buffer(700_000, 100, seed=5).copy()  # 70 MB: three 32 MiB chunks
+    rng = np.random.default_rng(9)
+    pos = rng.integers(0, len(buf), size=20_000)
+    keep = buf[pos] != ord("\n")
+    buf[pos[keep]] = rng.choice(np.frombuffer(b"NnacgtRY.\x00\xff", np.uint8), size=int(keep.sum()))
+    opt = TatajubaOptions(25, 3, 5, True)
+    monkeypatch.setenv("TJB_HOST_PACK", "0")
+    plain = as_boundary(ctx.count_host(buf, opt))
+    monkeypatch.delenv("TJB_HOST_PACK")
+    launches0 = dict((s["name"], s["launches"]) for s in ctx.kernel_stats()).get("unpack_kernels", 0)
+    packed = as_boundary(ctx.count_host(buf, opt))
+    launches1 = dict((s["name"], s["launches"]) for s in ctx.kernel_stats()).get("unpack_kernels", 0)
+    assert launches1 >= launches0 + 6, "the packed transfer did not run (3 chunks x unpack + exceptions)"
+    pyoracle.assert_same_boundary(packed, plain, "packed vs plain transfer")
+    d = torch.from_numpy(buf).cuda()
+    pyoracle.assert_same_boundary(packed, as_boundary(ctx.count_device(d.data_ptr(), d.numel(), opt)), "packed vs device")
+    monkeypatch.setenv("TJB_HOST_PACK", "3")  # odd thread count: shares that do not divide the chunk evenly
+    pyoracle.assert_same_boundary(as_boundary(ctx.count_host(buf, opt)), plain, "packed (3 threads) vs plain")
+    monkeypatch.delenv("TJB_HOST_PACK")
+    small = buf[: 151 * 60_000]  # 9 MB: still packed, small enough for the oracle
+    check(ctx, restatement, small, 25, 3, 5, True, "packed transfer vs oracle", device_too=False)
