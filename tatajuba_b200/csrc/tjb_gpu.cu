@@ -54,8 +54,7 @@ struct tjb_ctx {
   uint8_t *h_pinned[4] = {nullptr, nullptr, nullptr, nullptr}; // files path: two chunks per decoder thread
   cudaEvent_t h_free[4] = {nullptr, nullptr, nullptr, nullptr}; // pinned chunk i may be overwritten once this has fired
   DevBuf d_chunk[2];
-  // host-buffer path with 2-bit packed transfers (tjb_hostpack.h): packer threads, pinned and device staging per chunk slot
-  tjb_packer *packer = nullptr;
+  // host-buffer path with 2-bit packed transfers (tjb_hostpack.h): pinned and device staging per chunk slot
   uint8_t *h_pk[2] = {nullptr, nullptr}; uint32_t *h_exc_pos[2] = {nullptr, nullptr}; uint8_t *h_exc_val[2] = {nullptr, nullptr};
   DevBuf d_pk[2], d_exc_pos[2], d_exc_val[2];
 
@@ -697,7 +696,6 @@ void tjb_ctx_destroy (tjb_ctx *ctx)
   if (ctx->stream) cudaStreamSynchronize (ctx->stream);
   resolve_events (ctx);
   for (cudaEvent_t e : ctx->free_events) cudaEventDestroy (e);
-  if (ctx->packer) tjb_packer_destroy (ctx->packer);
   for (int i = 0; i < 2; i++) {
     if (ctx->h_pk[i]) cudaFreeHost (ctx->h_pk[i]);
     if (ctx->h_exc_pos[i]) cudaFreeHost (ctx->h_exc_pos[i]);
@@ -809,16 +807,25 @@ __global__ void __launch_bounds__ (256) unpack_exc_kernel (const u32 *__restrict
 
 #define TJB_PACK_MIN_BYTES ((size_t) 8 << 20)          // below this the packer threads are not worth waking
 #define TJB_PACK_EXC_CAP (TJB_HOST_CHUNK_BYTES / 16)   // exceptions per chunk before it is sent unpacked (reads of >= ~20 bases)
+// ONE pool of packer threads per process, shared by every context (the reference feeds several GPUs from OpenMP
+// threads of one process: a pool per context would oversubscribe the host).  Chunks of different contexts take turns;
+// the pool spins while at least one call is feeding a sample and is parked otherwise.  Never destroyed.
+static std::mutex g_packer_mu;       // pool creation and the session count
+static std::mutex g_packer_run_mu;   // one chunk at a time
+static tjb_packer *g_packer = nullptr;
+static int g_packer_sessions = 0;
+
 static bool packed_transfer_enabled (tjb_ctx *ctx, size_t n_bytes)
 {
-  const char *e = getenv ("TJB_HOST_PACK"); // "0" disables, a number > 0 sets the thread count
+  const char *e = getenv ("TJB_HOST_PACK"); // "0" disables, a number > 0 sets the thread count (first use decides)
   if (e && atoi (e) == 0) return false;
   if (n_bytes < TJB_PACK_MIN_BYTES) return false;
-  if (!ctx->packer) {
-    ctx->packer = tjb_packer_create (e ? atoi (e) : 0);
-    if (!ctx->packer) return false;
+  {
+    std::lock_guard<std::mutex> lk (g_packer_mu);
+    if (!g_packer) g_packer = tjb_packer_create (e ? atoi (e) : 0);
+    if (!g_packer) return false;
+    if (tjb_packer_threads (g_packer) < 4 && !e) return false; // PCIe beats a few cores
   }
-  if (tjb_packer_threads (ctx->packer) < 4 && !e) return false; // PCIe beats a few cores
   for (int i = 0; i < 2; i++) {
     if (!ctx->h_pk[i] && cudaMallocHost ((void**) &ctx->h_pk[i], TJB_HOST_CHUNK_BYTES / 4 + 64) != cudaSuccess) return false;
     if (!ctx->h_exc_pos[i] && cudaMallocHost ((void**) &ctx->h_exc_pos[i], (size_t) TJB_PACK_EXC_CAP * 4) != cudaSuccess) return false;
@@ -828,10 +835,20 @@ static bool packed_transfer_enabled (tjb_ctx *ctx, size_t n_bytes)
   }
   return true;
 }
-struct PackerSession { // the packer threads spin for the duration of one call
-  tjb_packer *p;
-  explicit PackerSession (tjb_packer *q) : p (q) { if (p) tjb_packer_begin (p); }
-  ~PackerSession () { if (p) tjb_packer_end (p); }
+struct PackerSession { // the packer threads spin while at least one call is feeding a sample
+  bool on;
+  explicit PackerSession (bool enable) : on (enable)
+  {
+    if (!on) return;
+    std::lock_guard<std::mutex> lk (g_packer_mu);
+    if (g_packer_sessions++ == 0) tjb_packer_begin (g_packer);
+  }
+  ~PackerSession ()
+  {
+    if (!on) return;
+    std::lock_guard<std::mutex> lk (g_packer_mu);
+    if (--g_packer_sessions == 0) tjb_packer_end (g_packer);
+  }
 };
 
 // Host buffer: chunks are copied on the context's copy stream while the previous chunk is scanned on the compute
@@ -845,7 +862,7 @@ int tjb_count_sample_host (tjb_ctx *ctx, const uint8_t *seqs, size_t n_bytes, co
   int rc = 0;
   CU (cudaSetDevice (ctx->device));
   const bool packed = packed_transfer_enabled (ctx, n_bytes);
-  PackerSession session (packed ? ctx->packer : nullptr);
+  PackerSession session (packed);
   for (int attempt = 0; attempt < 3; attempt++) {
     out_reset (out);
     TRY (begin_sample (ctx, opt, n_bytes));
@@ -863,7 +880,8 @@ int tjb_count_sample_host (tjb_ctx *ctx, const uint8_t *seqs, size_t n_bytes, co
       long n_exc = -1;
       if (packed) {
         if (used[which]) CU (cudaEventSynchronize (ctx->ev_copied[which])); // the slot's pinned staging has been read
-        n_exc = tjb_packer_run (ctx->packer, seqs + off, len, ctx->h_pk[which], ctx->h_exc_pos[which], ctx->h_exc_val[which], TJB_PACK_EXC_CAP);
+        std::lock_guard<std::mutex> lk (g_packer_run_mu);
+        n_exc = tjb_packer_run (g_packer, seqs + off, len, ctx->h_pk[which], ctx->h_exc_pos[which], ctx->h_exc_val[which], TJB_PACK_EXC_CAP);
       }
       if (used[which]) CU (cudaStreamWaitEvent (ctx->copy_stream, ctx->ev_scanned[which], 0)); // buffer free again
       if (n_exc >= 0) {

@@ -227,8 +227,23 @@ def test_gpu_packed_host_transfer_is_transparent(ctx, restatement, monkeypatch):
     pyoracle.assert_same_boundary(packed, plain, "packed vs plain transfer")
     d = torch.from_numpy(buf).cuda()
     pyoracle.assert_same_boundary(packed, as_boundary(ctx.count_device(d.data_ptr(), d.numel(), opt)), "packed vs device")
-    monkeypatch.setenv("TJB_HOST_PACK", "3")  # odd thread count: shares that do not divide the chunk evenly
-    pyoracle.assert_same_boundary(as_boundary(ctx.count_host(buf, opt)), plain, "packed (3 threads) vs plain")
-    monkeypatch.delenv("TJB_HOST_PACK")
+    other = Context(0)  # the packer pool is shared by the contexts of a process
+    try:
+        pyoracle.assert_same_boundary(as_boundary(other.count_host(buf, opt)), plain, "packed (second context) vs plain")
+        # two host threads feeding at once (the reference's OpenMP loop): sessions overlap, chunks take turns in the pool
+        import threading
+        res = [None, None]
+
+        def feed(i, c):
+            res[i] = as_boundary(c.count_host(buf, opt))
+        th = [threading.Thread(target=feed, args=(i, c)) for i, c in enumerate((ctx, other))]
+        for t in th:
+            t.start()
+        for t in th:
+            t.join()
+        for i in range(2):
+            pyoracle.assert_same_boundary(res[i], plain, f"packed, concurrent feeder {i} vs plain")
+    finally:
+        other.close()
     small = buf[: 151 * 60_000]  # 9 MB: still packed, small enough for the oracle
     check(ctx, restatement, small, 25, 3, 5, True, "packed transfer vs oracle", device_too=False)
