@@ -56,6 +56,20 @@ class ClockSampler(threading.Thread):
         except Exception:
             pass
 
+    def poll(self):
+        """one sample from the calling thread (the timed loop calls it mid-way: a guaranteed in-region sample)"""
+        if not self.nvml:
+            return
+        nv, h = self.nvml
+        try:
+            r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
+            self.rows.append([str(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)), str(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))] +
+                             ["Active" if r & b else "Not Active" for b in
+                              (nv.nvmlClocksThrottleReasonHwSlowdown, nv.nvmlClocksThrottleReasonHwThermalSlowdown,
+                               nv.nvmlClocksThrottleReasonSwThermalSlowdown, nv.nvmlClocksThrottleReasonSwPowerCap)])
+        except Exception:
+            pass
+
     def run(self):
         if self.nvml:
             nv, h = self.nvml
@@ -67,10 +81,11 @@ class ClockSampler(threading.Thread):
                     sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
                     r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
                     self.rows.append([str(sm), str(mx)] + ["Active" if r & b else "Not Active" for b in bits])
-                    time.sleep(0.004)
+                    time.sleep(0.001 if len(self.rows) < 8 else 0.01)
                 return
-            except Exception:
-                pass
+            except Exception as e:
+                self.nvml = None
+                sys.stderr.write(f"[bench] NVML sampling failed ({e}); falling back to nvidia-smi\n")
         while not self.stop_flag:
             try:
                 o = subprocess.run(["nvidia-smi", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits", "-i",
@@ -89,7 +104,7 @@ class ClockSampler(threading.Thread):
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
         reasons = [n for i, n in enumerate(names) if any(len(r) > 2 + i and r[2 + i] == "Active" for r in self.rows)]
         return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": mx or None, "reasons": reasons,
-                "samples": len(self.rows)}
+                "samples": len(self.rows), "source": "nvml" if self.nvml else "nvidia-smi"}
 
 
 def make_sample(rank, n_reads=None):
@@ -238,8 +253,10 @@ def main():
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     e0.record(stream)
-    for _ in range(args.steps):
+    for i in range(args.steps):
         hc = ctx.count_device(d_buf.data_ptr(), n_bytes, opt)
+        if rank == 0 and i == args.steps // 2:
+            sampler.poll()
     e1.record(stream)
     barrier()
     ms = max_over_ranks(e0.elapsed_time(e1))
