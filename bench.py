@@ -56,20 +56,6 @@ class ClockSampler(threading.Thread):
         except Exception:
             pass
 
-    def poll(self):
-        """one sample from the calling thread (the timed loop calls it mid-way: a guaranteed in-region sample)"""
-        if not self.nvml:
-            return
-        nv, h = self.nvml
-        try:
-            r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
-            self.rows.append([str(nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)), str(nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM))] +
-                             ["Active" if r & b else "Not Active" for b in
-                              (nv.nvmlClocksThrottleReasonHwSlowdown, nv.nvmlClocksThrottleReasonHwThermalSlowdown,
-                               nv.nvmlClocksThrottleReasonSwThermalSlowdown, nv.nvmlClocksThrottleReasonSwPowerCap)])
-        except Exception:
-            pass
-
     def run(self):
         if self.nvml:
             nv, h = self.nvml
@@ -81,7 +67,7 @@ class ClockSampler(threading.Thread):
                     sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
                     r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
                     self.rows.append([str(sm), str(mx)] + ["Active" if r & b else "Not Active" for b in bits])
-                    time.sleep(0.001 if len(self.rows) < 8 else 0.01)
+                    time.sleep(0.003)
                 return
             except Exception as e:
                 self.nvml = None
@@ -226,6 +212,8 @@ def main():
     def max_over_ranks(x):
         if world == 1:
             return x
+        if os.environ.get("BENCH_DEBUG"):
+            sys.stderr.write(f"[bench] rank {rank}: {x:.3f} ms\n")
         t = torch.tensor([x], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
@@ -248,15 +236,13 @@ def main():
     ctx.set_profiling(2)
     ctx.reset_kernel_stats()
     sampler = ClockSampler(local_rank)
-    if rank == 0:  # one poller per job: 8 nvidia-smi loops would steal host cores from the ranks' launch threads
+    if rank == 0 and not os.environ.get("BENCH_NO_SAMPLER"):  # one poller per job: 8 nvidia-smi loops would steal host cores from the ranks' launch threads
         sampler.start()
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     barrier()
     e0.record(stream)
-    for i in range(args.steps):
+    for _ in range(args.steps):
         hc = ctx.count_device(d_buf.data_ptr(), n_bytes, opt)
-        if rank == 0 and i == args.steps // 2:
-            sampler.poll()
     e1.record(stream)
     barrier()
     ms = max_over_ranks(e0.elapsed_time(e1))
