@@ -196,6 +196,16 @@ def main():
         run_reference_arm(args, rank)
         return
 
+    # The result arrays are malloc()ed by the library and free()d by this script every step.  Keep freed memory in the
+    # heap (no trim, no mmap per array): otherwise whether a step pays ~0.5 ms of page faults for fresh pages depends
+    # on what else touched the allocator (seen: the first timed steps after an NCCL barrier), which is not the path.
+    try:
+        import ctypes
+        libc = ctypes.CDLL("libc.so.6")
+        libc.mallopt(-1, 1 << 30)  # M_TRIM_THRESHOLD
+        libc.mallopt(-3, 1 << 30)  # M_MMAP_THRESHOLD
+    except Exception:
+        pass
     import torch
     import torch.distributed as dist
     from tatajuba_b200 import Context, TatajubaOptions
@@ -334,7 +344,8 @@ def main():
         "scaling": "weak", "vs_baseline": None, "dtype": "u8/u64", "data": "synthetic",
         "config": {"workload": "configs[1]: one sample per GPU, 5 Mbp genome, 100x, 2x150 bp PE, k=25 m=4 i=5",
                    "bases_per_gpu": n_bases, "reads_per_gpu": n_reads, "input_bytes": n_bytes,
-                   "l2": "input (503 MB) larger than L2 (126 MB); no flush needed", "n_raw": hc.n_raw,
+                   "l2": "input (503 MB) larger than L2 (126 MB); no flush needed",
+                   "malloc": "M_TRIM_THRESHOLD / M_MMAP_THRESHOLD = 1 GiB: freed result arrays stay in the heap", "n_raw": hc.n_raw,
                    "n_distinct": hc.n_distinct, "n_elem": hc.n_elem, "n_idx": hc.n_idx, "coverage": hc.coverage},
         "e2e": {"value": world * n_bases * args.steps / (ms_e2e * 1e-3), "unit": "bases/s",
                 "ms_per_step": ms_e2e / args.steps, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
