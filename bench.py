@@ -67,7 +67,7 @@ class ClockSampler(threading.Thread):
                     sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
                     r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
                     self.rows.append([str(sm), str(mx)] + ["Active" if r & b else "Not Active" for b in bits])
-                    time.sleep(0.003)
+                    time.sleep(0.02)  # a query takes the driver's lock for ~1 ms on an 8-GPU box: keep them rare
                 return
             except Exception as e:
                 self.nvml = None
