@@ -335,6 +335,41 @@ static int scan_resolve (tjb_ctx *ctx, const tjb_opts *opt)
   return 0;
 }
 
+// ONE pool of packer threads per process, shared by every context (the reference feeds several GPUs from OpenMP
+// threads of one process: a pool per context would oversubscribe the host).  Chunks of different contexts take turns;
+// the pool spins while at least one call is feeding a sample and is parked otherwise.  Never destroyed.
+static std::mutex g_packer_mu;       // pool creation and the session count
+static std::mutex g_packer_run_mu;   // one chunk at a time
+static tjb_packer *g_packer = nullptr;
+static int g_packer_sessions = 0;
+
+// the pool, created on first use; nullptr when TJB_HOST_PACK=0 or the host has fewer than 4 threads to give
+static tjb_packer *host_pool ()
+{
+  const char *e = getenv ("TJB_HOST_PACK"); // "0" disables, a number > 0 sets the thread count (first use decides)
+  if (e && atoi (e) == 0) return nullptr;
+  std::lock_guard<std::mutex> lk (g_packer_mu);
+  if (!g_packer) g_packer = tjb_packer_create (e ? atoi (e) : 0);
+  if (!g_packer || (tjb_packer_threads (g_packer) < 4 && !e)) return nullptr;
+  return g_packer;
+}
+
+struct PackerSession { // the packer threads spin while at least one call is feeding a sample
+  bool on;
+  explicit PackerSession (bool enable) : on (enable)
+  {
+    if (!on) return;
+    std::lock_guard<std::mutex> lk (g_packer_mu);
+    if (g_packer_sessions++ == 0) tjb_packer_begin (g_packer);
+  }
+  ~PackerSession ()
+  {
+    if (!on) return;
+    std::lock_guard<std::mutex> lk (g_packer_mu);
+    if (--g_packer_sessions == 0) tjb_packer_end (g_packer);
+  }
+};
+
 // --------------------------------------------------------------------------------------- finalise -------
 // Global multi-pass reduce of ONE bucket that does not fit in shared memory: LSD radix sort over every digit,
 // run-length count, QC filter, context groups.  Results land where bucket_reduce_kernel would have put them.
@@ -454,6 +489,10 @@ static int finalise_t (tjb_ctx *ctx, const tjb_opts *opt, tjb_counter_out *out, 
   CU (cudaMemcpyAsync (hs, ctx->d_counters, 2 * sizeof (unsigned long long), cudaMemcpyDeviceToHost, st));
   CU (cudaMemcpyAsync (hm, ctx->d_meta, META_WORDS * sizeof (u32), cudaMemcpyDeviceToHost, st));
   tr.mark ("enqueue1");
+  // the copy-out below is bound by ONE host thread copying out of the pinned staging buffer (~20 GB/s): when the
+  // previous result was large, wake the host pool now (its wake-up hides under the kernels) and let it share the copy
+  const bool pool_copy = ctx->last_keep * 40 >= ((size_t) 512 << 10) && host_pool () != nullptr;
+  PackerSession copy_session (pool_copy);
   // The result arrays are malloc()ed (the reference free()s them) and fresh heap memory costs a page fault per 4 KiB
   // on first touch (measured: up to 1.2 ms for the 2.8 MB of config 2, depending on what the allocator has cached).
   // The host has nothing to do until the kernels above finish (~0.4 ms), so arrays sized like the previous sample's
@@ -566,7 +605,11 @@ static int finalise_t (tjb_ctx *ctx, const tjb_opts *opt, tjb_counter_out *out, 
     }
     for (int c = 0; c < NCH; c++) {
       CU (cudaEventSynchronize (ev[c]));
-      copy_streaming ((char*) out->elem + lo[c], ctx->h_out + lo[c], lo[c + 1] - lo[c]);
+      if (pool_copy) {
+        std::lock_guard<std::mutex> lk (g_packer_run_mu);
+        tjb_packer_copy (g_packer, (char*) out->elem + lo[c], ctx->h_out + lo[c], lo[c + 1] - lo[c]);
+      } else
+        copy_streaming ((char*) out->elem + lo[c], ctx->h_out + lo[c], lo[c + 1] - lo[c]);
       ctx->free_events.push_back (ev[c]);
     }
     memcpy (out->idx_initial, ctx->h_out + eb, ib);
@@ -846,25 +889,10 @@ __global__ void __launch_bounds__ (256) unpack_exc_kernel (const u32 *__restrict
 
 #define TJB_PACK_MIN_BYTES ((size_t) 8 << 20)          // below this the packer threads are not worth waking
 #define TJB_PACK_EXC_CAP (TJB_HOST_CHUNK_BYTES / 16)   // exceptions per chunk before it is sent unpacked (reads of >= ~20 bases)
-// ONE pool of packer threads per process, shared by every context (the reference feeds several GPUs from OpenMP
-// threads of one process: a pool per context would oversubscribe the host).  Chunks of different contexts take turns;
-// the pool spins while at least one call is feeding a sample and is parked otherwise.  Never destroyed.
-static std::mutex g_packer_mu;       // pool creation and the session count
-static std::mutex g_packer_run_mu;   // one chunk at a time
-static tjb_packer *g_packer = nullptr;
-static int g_packer_sessions = 0;
-
 static bool packed_transfer_enabled (tjb_ctx *ctx, size_t n_bytes)
 {
-  const char *e = getenv ("TJB_HOST_PACK"); // "0" disables, a number > 0 sets the thread count (first use decides)
-  if (e && atoi (e) == 0) return false;
   if (n_bytes < TJB_PACK_MIN_BYTES) return false;
-  {
-    std::lock_guard<std::mutex> lk (g_packer_mu);
-    if (!g_packer) g_packer = tjb_packer_create (e ? atoi (e) : 0);
-    if (!g_packer) return false;
-    if (tjb_packer_threads (g_packer) < 4 && !e) return false; // PCIe beats a few cores
-  }
+  if (!host_pool ()) return false; // PCIe beats a few cores
   for (int i = 0; i < 2; i++) {
     if (!ctx->h_pk[i] && cudaMallocHost ((void**) &ctx->h_pk[i], TJB_HOST_CHUNK_BYTES / 4 + 64) != cudaSuccess) return false;
     if (!ctx->h_exc_pos[i] && cudaMallocHost ((void**) &ctx->h_exc_pos[i], (size_t) TJB_PACK_EXC_CAP * 4) != cudaSuccess) return false;
@@ -874,21 +902,6 @@ static bool packed_transfer_enabled (tjb_ctx *ctx, size_t n_bytes)
   }
   return true;
 }
-struct PackerSession { // the packer threads spin while at least one call is feeding a sample
-  bool on;
-  explicit PackerSession (bool enable) : on (enable)
-  {
-    if (!on) return;
-    std::lock_guard<std::mutex> lk (g_packer_mu);
-    if (g_packer_sessions++ == 0) tjb_packer_begin (g_packer);
-  }
-  ~PackerSession ()
-  {
-    if (!on) return;
-    std::lock_guard<std::mutex> lk (g_packer_mu);
-    if (--g_packer_sessions == 0) tjb_packer_end (g_packer);
-  }
-};
 
 // Host buffer: chunks are copied on the context's copy stream while the previous chunk is scanned on the compute
 // stream (two device chunk buffers); one optimistic pass, redone with the exact record capacity after an overflow.

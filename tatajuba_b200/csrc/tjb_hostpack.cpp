@@ -93,6 +93,7 @@ static long pack_range (const uint8_t *src, size_t n, uint8_t *packed, uint32_t 
   return nt < 0 ? -1 : ne + nt;
 }
 
+#define TJB_COPY_BLOCK ((size_t) 32 << 10) // bytes per unit of a copy job
 #define TJB_PACK_BLOCK ((size_t) 64 << 10) // bytes per unit of work (a multiple of 32): shares are drawn, not dealt
 
 struct tjb_packer {
@@ -107,6 +108,7 @@ struct tjb_packer {
   // the job
   const uint8_t *src = nullptr; size_t n = 0, cap = 0, n_blocks = 0;
   uint8_t *packed = nullptr; uint32_t *exc_pos = nullptr; uint8_t *exc_val = nullptr;
+  uint8_t *copy_dst = nullptr;            // non-null: the job is a plain copy src -> copy_dst (tjb_packer_copy)
   std::atomic<size_t> next_block{0}, exc_total{0};
   std::atomic<bool> overflow{false};
   std::vector<std::vector<uint32_t>> lpos; // exceptions of the block a participant is working on
@@ -116,8 +118,38 @@ struct tjb_packer {
 // participants 0 .. T-1 are the workers, T is the calling thread.  Blocks are drawn from a counter, so a participant
 // that lost its core for a while costs one block, not a share; a block's exceptions are appended to the chunk's list
 // at an offset reserved with one atomic (their order does not matter: the device scatters them by position).
+// destination is written once and not read back here: streaming stores skip the read-for-ownership of its lines
+static void copy_block (uint8_t *d, const uint8_t *s, size_t n)
+{
+#if defined(__x86_64__)
+  size_t head = (16 - ((uintptr_t) d & 15)) & 15;
+  if (head > n) head = n;
+  memcpy (d, s, head);
+  d += head; s += head; n -= head;
+  const size_t blocks = n / 64;
+  for (size_t i = 0; i < blocks; i++, d += 64, s += 64) {
+    const __m128i a = _mm_loadu_si128 ((const __m128i*) s), b = _mm_loadu_si128 ((const __m128i*) (s + 16));
+    const __m128i c = _mm_loadu_si128 ((const __m128i*) (s + 32)), e = _mm_loadu_si128 ((const __m128i*) (s + 48));
+    _mm_stream_si128 ((__m128i*) d, a); _mm_stream_si128 ((__m128i*) (d + 16), b);
+    _mm_stream_si128 ((__m128i*) (d + 32), c); _mm_stream_si128 ((__m128i*) (d + 48), e);
+  }
+  _mm_sfence ();
+  memcpy (d, s, n - blocks * 64);
+#else
+  memcpy (d, s, n);
+#endif
+}
+
 static void packer_take_part (tjb_packer *p, int who)
 {
+  if (p->copy_dst) {
+    for (;;) {
+      const size_t b = p->next_block.fetch_add (1, std::memory_order_relaxed);
+      if (b >= p->n_blocks) return;
+      const size_t lo = b * TJB_COPY_BLOCK, hi = lo + TJB_COPY_BLOCK < p->n ? lo + TJB_COPY_BLOCK : p->n;
+      copy_block (p->copy_dst + lo, p->src + lo, hi - lo);
+    }
+  }
   uint32_t *lp = p->lpos[who].data ();
   uint8_t *lv = p->lval[who].data ();
   for (;;) {
@@ -199,6 +231,7 @@ long tjb_packer_run (tjb_packer *p, const uint8_t *src, size_t n, uint8_t *packe
 {
   if (!n) return 0;
   p->src = src; p->n = n; p->packed = packed; p->exc_pos = exc_pos; p->exc_val = exc_val; p->cap = cap;
+  p->copy_dst = nullptr;
   p->n_blocks = (n + TJB_PACK_BLOCK - 1) / TJB_PACK_BLOCK;
   p->next_block.store (0, std::memory_order_relaxed);
   p->exc_total.store (0, std::memory_order_relaxed);
@@ -209,6 +242,18 @@ long tjb_packer_run (tjb_packer *p, const uint8_t *src, size_t n, uint8_t *packe
   while (p->done.load (std::memory_order_acquire) < (uint64_t) p->T * g) spin_step (spins);
   const size_t total = p->exc_total.load (std::memory_order_relaxed);
   return (p->overflow.load (std::memory_order_relaxed) || total > cap) ? -1 : (long) total;
+}
+
+void tjb_packer_copy (tjb_packer *p, void *dst, const void *src, size_t n)
+{
+  if (!n) return;
+  p->src = (const uint8_t*) src; p->n = n; p->copy_dst = (uint8_t*) dst;
+  p->n_blocks = (n + TJB_COPY_BLOCK - 1) / TJB_COPY_BLOCK;
+  p->next_block.store (0, std::memory_order_relaxed);
+  const uint64_t g = p->gen.fetch_add (1, std::memory_order_acq_rel) + 1;
+  packer_take_part (p, p->T);
+  unsigned spins = 0;
+  while (p->done.load (std::memory_order_acquire) < (uint64_t) p->T * g) spin_step (spins);
 }
 
 // test hook (tests/test_hostpack.py): one chunk through a fresh pool of `threads` workers
@@ -222,7 +267,13 @@ extern "C" long tjb_hostpack_selftest (const uint8_t *src, size_t n, int threads
   tjb_packer_end (p);
   tjb_packer_begin (p); // and can be parked and woken again
   const long r2 = tjb_packer_run (p, src, n, packed, exc_pos, exc_val, cap);
+  // the same pool copies: packed -> a scratch buffer and back must leave it unchanged
+  const size_t np = (n + 3) / 4;
+  std::vector<uint8_t> tmp (np + 1, 0xAA);
+  tjb_packer_begin (p);
+  tjb_packer_copy (p, tmp.data (), packed, np);
+  const bool same = memcmp (tmp.data (), packed, np) == 0 && tmp[np] == 0xAA;
   tjb_packer_end (p);
   tjb_packer_destroy (p);
-  return r == r2 ? r : -3;
+  return !same ? -4 : r == r2 ? r : -3;
 }

@@ -22,5 +22,7 @@ void tjb_packer_end (tjb_packer *p);
 // Packs src[0, n) into packed[0, (n + 3) / 4) and the exceptions into exc_pos / exc_val (capacity cap).  Returns the
 // number of exceptions, or -1 when they do not fit (the caller then sends the chunk as it is).
 long tjb_packer_run (tjb_packer *p, const uint8_t *src, size_t n, uint8_t *packed, uint32_t *exc_pos, uint8_t *exc_val, size_t cap);
+// dst[0, n) = src[0, n) by the pool and the caller together (between begin and end), 64 KiB blocks, streaming stores
+void tjb_packer_copy (tjb_packer *p, void *dst, const void *src, size_t n);
 // single-threaded, portable restatement (tests, small inputs)
 long tjb_pack_scalar (const uint8_t *src, size_t n, uint8_t *packed, uint32_t *exc_pos, uint8_t *exc_val, size_t cap, uint32_t pos0);
