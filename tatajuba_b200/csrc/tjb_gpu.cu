@@ -588,18 +588,20 @@ static int finalise_t (tjb_ctx *ctx, const tjb_opts *opt, tjb_counter_out *out, 
       CU (cudaMallocHost ((void**) &ctx->h_out, total + total / 4));
       ctx->h_out_cap = total + total / 4;
     }
-    const int NCH = 4;
-    cudaEvent_t ev[NCH];
-    size_t lo[NCH + 1];
+    static const int nch_env = getenv ("TJB_OUT_CHUNKS") ? atoi (getenv ("TJB_OUT_CHUNKS")) : 0;
+    const int NCH = nch_env >= 1 && nch_env <= 8 ? nch_env : 4;
+    cudaEvent_t ev[8];
+    size_t lo[9];
     for (int c = 0; c <= NCH; c++) lo[c] = (eb * c / NCH) / 40 * 40;
     lo[NCH] = eb;
+    // the index arrays travel with the first chunk, so that their host copy runs under the DMA of the later chunks
     for (int c = 0; c < NCH; c++) {
-      CU (cudaMemcpyAsync (ctx->h_out + lo[c], (const char*) ctx->out40.p + lo[c], lo[c + 1] - lo[c], cudaMemcpyDeviceToHost, st));
-      if (c == NCH - 1) {
+      if (c == 0) {
         CU (cudaMemcpyAsync (ctx->h_out + eb, ctx->idx_i.p, ib, cudaMemcpyDeviceToHost, st));
         CU (cudaMemcpyAsync (ctx->h_out + eb + ib, ctx->idx_f.p, ib, cudaMemcpyDeviceToHost, st));
         CU (cudaMemcpyAsync (ctx->h_out + eb + 2 * ib, ctx->d_cov, 4, cudaMemcpyDeviceToHost, st));
       }
+      CU (cudaMemcpyAsync (ctx->h_out + lo[c], (const char*) ctx->out40.p + lo[c], lo[c + 1] - lo[c], cudaMemcpyDeviceToHost, st));
       ev[c] = get_event (ctx);
       CU (cudaEventRecord (ev[c], st));
     }
@@ -610,11 +612,13 @@ static int finalise_t (tjb_ctx *ctx, const tjb_opts *opt, tjb_counter_out *out, 
         tjb_packer_copy (g_packer, (char*) out->elem + lo[c], ctx->h_out + lo[c], lo[c + 1] - lo[c]);
       } else
         copy_streaming ((char*) out->elem + lo[c], ctx->h_out + lo[c], lo[c + 1] - lo[c]);
+      if (c == 0) {
+        memcpy (out->idx_initial, ctx->h_out + eb, ib);
+        memcpy (out->idx_final, ctx->h_out + eb + ib, ib);
+        memcpy (&cov, ctx->h_out + eb + 2 * ib, 4);
+      }
       ctx->free_events.push_back (ev[c]);
     }
-    memcpy (out->idx_initial, ctx->h_out + eb, ib);
-    memcpy (out->idx_final, ctx->h_out + eb + ib, ib);
-    memcpy (&cov, ctx->h_out + eb + 2 * ib, 4);
   }
   tr.mark ("d2h_enqueue");
   CU (cudaStreamSynchronize (st)); // ---- synchronisation 2
