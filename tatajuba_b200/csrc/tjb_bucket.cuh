@@ -13,7 +13,7 @@
 //   partition_kernel     grid      rec_a -> rec_b, bucket-contiguous (order inside a bucket is irrelevant)
 //   bucket_reduce_kernel grid      per bucket: smem LSD sort + RLE + QC + groups; compact output at the bucket start
 //   totals_kernel        1 CTA     exclusive scans of the per-bucket kept / group counts
-//   pack_kernel          grid      reference-layout 40-byte hopo_element + idx arrays + coverage hash inserts
+//   pack_kernel          grid      the 24 varying bytes of every reference-layout hopo_element + idx arrays + coverage hash inserts
 //   cov_max_kernel       grid      coverage = max over the hash table
 //
 // Buckets with more than BK_CAP records (one bin holding > BK_CAP/2 observations: very short k or a pathological
@@ -591,7 +591,7 @@ template <int W>
 __global__ void __launch_bounds__ (256)
 pack_kernel (const u64 *__restrict__ out_rec, const u32 *__restrict__ out_cnt, const u32 *__restrict__ out_idx_i, const u32 *__restrict__ out_idx_f,
              const u32 *__restrict__ bkt_start, const uint4 *__restrict__ bstat, const u32 *__restrict__ koff, const u32 *__restrict__ ioff,
-             const u32 *__restrict__ meta, int k, u64 *__restrict__ out40, int *__restrict__ idx_initial, int *__restrict__ idx_final,
+             const u32 *__restrict__ meta, int k, u64 *__restrict__ out24, int *__restrict__ idx_initial, int *__restrict__ idx_final,
              u32 *__restrict__ cov_keys, u32 *__restrict__ cov_vals, u32 cov_mask)
 {
   const u32 nb = meta[META_NBUCKETS];
@@ -607,10 +607,10 @@ pack_kernel (const u64 *__restrict__ out_rec, const u32 *__restrict__ out_cnt, c
       const u64 bits = ((u64) rec_base<W> (r, k) & 3) | (((u64) rec_len_field<W> (r) & 0x3ff) << 2) | (((u64) cnt & 0xfffff) << 12) |
                        (0xffeULL << 32) | (((u64) rec_flag<W> (r) & 7) << 49);
       const u64 c0 = rec_ctx0<W> (r, k), c1 = rec_ctx1<W> (r, k);
-      u64 *o = out40 + 5 * (size_t) (ko + j);
+      // the other 16 bytes of a hopo_element are constants at this point (read_offset = -1, hopo_counter.c:511;
+      // loc_ref_id = loc_pos = loc_last = -1, :297): the host appends them, they do not cross PCIe
+      u64 *o = out24 + 3 * (size_t) (ko + j);
       o[0] = c0; o[1] = c1; o[2] = bits;
-      o[3] = ~0ULL; // read_offset = -1 (hopo_counter.c:511), loc_ref_id = -1 (:297)
-      o[4] = ~0ULL; // loc_pos = loc_last = -1
       cov_insert (cov_keys, cov_vals, cov_mask, (u32) (c0 & 0x7fffffffULL), (u32) cnt);
       cov_insert (cov_keys, cov_vals, cov_mask, (u32) (c1 & 0x7fffffffULL), (u32) cnt);
     }

@@ -2,7 +2,6 @@
 // Device work only — there is no host fallback for any compute step in this file.
 #include <chrono>
 #include <sys/mman.h>
-#include <emmintrin.h>
 #include <climits>
 #include <cstdlib>
 #include <cstring>
@@ -160,28 +159,6 @@ struct Trace { // TJB_TRACE=1: host wall-clock of the stages of one call, on std
   }
   ~Trace () { if (on) fprintf (stderr, "[tjb]%s\n", line.c_str ()); }
 };
-
-// pinned staging -> caller's memory with streaming stores: the destination is never read back here, so the
-// read-for-ownership of every line is skipped (measured: 220 -> 195 us for the 2.8 MB of config 2; a second copying
-// thread did not help, its chunks finished later than the main thread's)
-static void copy_streaming (void *dst, const void *src, size_t n)
-{
-  char *d = (char*) dst;
-  const char *s = (const char*) src;
-  size_t head = (16 - ((uintptr_t) d & 15)) & 15;
-  if (head > n) head = n;
-  memcpy (d, s, head);
-  d += head; s += head; n -= head;
-  size_t blocks = n / 64;
-  for (size_t i = 0; i < blocks; i++, d += 64, s += 64) {
-    const __m128i a = _mm_loadu_si128 ((const __m128i*) s), b = _mm_loadu_si128 ((const __m128i*) (s + 16));
-    const __m128i c = _mm_loadu_si128 ((const __m128i*) (s + 32)), e = _mm_loadu_si128 ((const __m128i*) (s + 48));
-    _mm_stream_si128 ((__m128i*) d, a); _mm_stream_si128 ((__m128i*) (d + 16), b);
-    _mm_stream_si128 ((__m128i*) (d + 32), c); _mm_stream_si128 ((__m128i*) (d + 48), e);
-  }
-  _mm_sfence ();
-  memcpy (d, s, n - blocks * 64);
-}
 
 static inline u32 nblk (size_t n, u32 per) { return (u32) ((n + per - 1) / per); }
 
@@ -343,14 +320,13 @@ static std::mutex g_packer_run_mu;   // one chunk at a time
 static tjb_packer *g_packer = nullptr;
 static int g_packer_sessions = 0;
 
-// the pool, created on first use; nullptr when TJB_HOST_PACK=0 or the host has fewer than 4 threads to give
+// the pool, created on first use; nullptr when TJB_HOST_PACK=0
 static tjb_packer *host_pool ()
 {
   const char *e = getenv ("TJB_HOST_PACK"); // "0" disables, a number > 0 sets the thread count (first use decides)
   if (e && atoi (e) == 0) return nullptr;
   std::lock_guard<std::mutex> lk (g_packer_mu);
   if (!g_packer) g_packer = tjb_packer_create (e ? atoi (e) : 0);
-  if (!g_packer || (tjb_packer_threads (g_packer) < 4 && !e)) return nullptr;
   return g_packer;
 }
 
@@ -553,13 +529,13 @@ static int finalise_t (tjb_ctx *ctx, const tjb_opts *opt, tjb_counter_out *out, 
   u32 slots = 1024;
   while (slots < 4u * n_keep) slots <<= 1; // two keys per record, load factor <= 0.5
   TRY (ensure (ctx, ctx->cov_tab, (size_t) slots * 8));
-  TRY (ensure (ctx, ctx->out40, (size_t) n_keep * 40)); TRY (ensure (ctx, ctx->idx_i, (size_t) n_idx * 4)); TRY (ensure (ctx, ctx->idx_f, (size_t) n_idx * 4));
+  TRY (ensure (ctx, ctx->out40, (size_t) n_keep * 24)); TRY (ensure (ctx, ctx->idx_i, (size_t) n_idx * 4)); TRY (ensure (ctx, ctx->idx_f, (size_t) n_idx * 4));
   u32 *cov_keys = (u32*) ctx->cov_tab.p, *cov_vals = cov_keys + slots;
   CU (cudaMemsetAsync (cov_keys, 0xff, (size_t) slots * 4, st));
   CU (cudaMemsetAsync (cov_vals, 0, (size_t) slots * 4, st));
   int cov_init = INT_MIN;
   CU (cudaMemcpyAsync (ctx->d_cov, &cov_init, 4, cudaMemcpyHostToDevice, st));
-  LAUNCH (K_PACK, (8 * W + 4 + 40) * (size_t) n_keep + 16 * (size_t) n_idx,
+  LAUNCH (K_PACK, (8 * W + 4 + 24) * (size_t) n_keep + 16 * (size_t) n_idx,
           (pack_kernel<W><<<nblk (n_buckets, 8), 256, 0, st>>> (rec_a, (u32*) ctx->out_cnt.p, (u32*) ctx->out_ii.p, (u32*) ctx->out_if.p, ctx->d_bkt_start, ctx->d_bstat, ctx->d_koff, ctx->d_ioff, ctx->d_meta, k, (u64*) ctx->out40.p, (int*) ctx->idx_i.p, (int*) ctx->idx_f.p, cov_keys, cov_vals, slots - 1)));
   LAUNCH (K_COVMAX, 8 * (size_t) slots, (cov_max_kernel<<<nblk (slots, 256 * 8), 256, 0, st>>> (cov_keys, cov_vals, slots, ctx->d_cov)));
   CU (cudaGetLastError ());
@@ -581,7 +557,8 @@ static int finalise_t (tjb_ctx *ctx, const tjb_opts *opt, tjb_counter_out *out, 
   int cov = 0;
   {
     // pinned staging in chunks: the DMA of chunk i+1 overlaps the host copy of chunk i into the caller's memory
-    const size_t eb = (size_t) n_keep * 40, ib = (size_t) n_idx * 4, total = eb + 2 * ib + 16;
+    // an element crosses PCIe as its 24 varying bytes; the host appends the constant 16 while it copies
+    const size_t eb = (size_t) n_keep * 24, ib = (size_t) n_idx * 4, total = eb + 2 * ib + 16;
     if (total > ctx->h_out_cap) {
       if (ctx->h_out) CU (cudaFreeHost (ctx->h_out));
       ctx->h_out = nullptr; ctx->h_out_cap = 0;
@@ -592,8 +569,8 @@ static int finalise_t (tjb_ctx *ctx, const tjb_opts *opt, tjb_counter_out *out, 
     const int NCH = nch_env >= 1 && nch_env <= 8 ? nch_env : 4;
     cudaEvent_t ev[8];
     size_t lo[9];
-    for (int c = 0; c <= NCH; c++) lo[c] = (eb * c / NCH) / 40 * 40;
-    lo[NCH] = eb;
+    for (int c = 0; c <= NCH; c++) lo[c] = (size_t) n_keep * c / NCH; // in elements
+    lo[NCH] = n_keep;
     // the index arrays travel with the first chunk, so that their host copy runs under the DMA of the later chunks
     for (int c = 0; c < NCH; c++) {
       if (c == 0) {
@@ -601,7 +578,7 @@ static int finalise_t (tjb_ctx *ctx, const tjb_opts *opt, tjb_counter_out *out, 
         CU (cudaMemcpyAsync (ctx->h_out + eb + ib, ctx->idx_f.p, ib, cudaMemcpyDeviceToHost, st));
         CU (cudaMemcpyAsync (ctx->h_out + eb + 2 * ib, ctx->d_cov, 4, cudaMemcpyDeviceToHost, st));
       }
-      CU (cudaMemcpyAsync (ctx->h_out + lo[c], (const char*) ctx->out40.p + lo[c], lo[c + 1] - lo[c], cudaMemcpyDeviceToHost, st));
+      CU (cudaMemcpyAsync (ctx->h_out + 24 * lo[c], (const char*) ctx->out40.p + 24 * lo[c], 24 * (lo[c + 1] - lo[c]), cudaMemcpyDeviceToHost, st));
       ev[c] = get_event (ctx);
       CU (cudaEventRecord (ev[c], st));
     }
@@ -609,9 +586,9 @@ static int finalise_t (tjb_ctx *ctx, const tjb_opts *opt, tjb_counter_out *out, 
       CU (cudaEventSynchronize (ev[c]));
       if (pool_copy) {
         std::lock_guard<std::mutex> lk (g_packer_run_mu);
-        tjb_packer_copy (g_packer, (char*) out->elem + lo[c], ctx->h_out + lo[c], lo[c + 1] - lo[c]);
+        tjb_packer_expand (g_packer, (char*) out->elem + 40 * lo[c], ctx->h_out + 24 * lo[c], lo[c + 1] - lo[c]);
       } else
-        copy_streaming ((char*) out->elem + lo[c], ctx->h_out + lo[c], lo[c + 1] - lo[c]);
+        tjb_expand_rows ((char*) out->elem + 40 * lo[c], ctx->h_out + 24 * lo[c], lo[c + 1] - lo[c]);
       if (c == 0) {
         memcpy (out->idx_initial, ctx->h_out + eb, ib);
         memcpy (out->idx_final, ctx->h_out + eb + ib, ib);
@@ -896,7 +873,8 @@ __global__ void __launch_bounds__ (256) unpack_exc_kernel (const u32 *__restrict
 static bool packed_transfer_enabled (tjb_ctx *ctx, size_t n_bytes)
 {
   if (n_bytes < TJB_PACK_MIN_BYTES) return false;
-  if (!host_pool ()) return false; // PCIe beats a few cores
+  tjb_packer *pool = host_pool ();
+  if (!pool || tjb_packer_threads (pool) < 4) return false; // PCIe beats a few cores
   for (int i = 0; i < 2; i++) {
     if (!ctx->h_pk[i] && cudaMallocHost ((void**) &ctx->h_pk[i], TJB_HOST_CHUNK_BYTES / 4 + 64) != cudaSuccess) return false;
     if (!ctx->h_exc_pos[i] && cudaMallocHost ((void**) &ctx->h_exc_pos[i], (size_t) TJB_PACK_EXC_CAP * 4) != cudaSuccess) return false;

@@ -108,7 +108,8 @@ struct tjb_packer {
   // the job
   const uint8_t *src = nullptr; size_t n = 0, cap = 0, n_blocks = 0;
   uint8_t *packed = nullptr; uint32_t *exc_pos = nullptr; uint8_t *exc_val = nullptr;
-  uint8_t *copy_dst = nullptr;            // non-null: the job is a plain copy src -> copy_dst (tjb_packer_copy)
+  uint8_t *copy_dst = nullptr;            // non-null: the job is a copy src -> copy_dst (tjb_packer_copy / _expand)
+  bool expand = false;                    // ... of n 24-byte rows into 40-byte elements
   std::atomic<size_t> next_block{0}, exc_total{0};
   std::atomic<bool> overflow{false};
   std::vector<std::vector<uint32_t>> lpos; // exceptions of the block a participant is working on
@@ -140,8 +141,54 @@ static void copy_block (uint8_t *d, const uint8_t *s, size_t n)
 #endif
 }
 
+// 24-byte rows {ctx0, ctx1, bit-fields} -> 40-byte hopo_element: the trailing four int32 are all -1 at this point
+static void expand_block (uint8_t *dst, const uint8_t *src, size_t n_rows)
+{
+  size_t i = 0;
+#if defined(__x86_64__)
+  auto one = [&] (size_t r) {
+    long long v[3];
+    memcpy (v, src + 24 * r, 24);
+    long long *d = (long long*) (dst + 40 * r); // malloc()ed base, multiples of 40: 8-byte aligned
+    _mm_stream_si64 (d, v[0]); _mm_stream_si64 (d + 1, v[1]); _mm_stream_si64 (d + 2, v[2]);
+    _mm_stream_si64 (d + 3, -1LL); _mm_stream_si64 (d + 4, -1LL);
+  };
+  if (n_rows && ((uintptr_t) dst & 15)) one (i++); // elements are 40 bytes: every other one starts 16-byte aligned
+  const __m128i ones = _mm_set1_epi32 (-1);
+  for (; i + 2 <= n_rows; i += 2) { // two elements = 48 bytes in, five 16-byte streaming stores out
+    const __m128i a = _mm_loadu_si128 ((const __m128i*) (src + 24 * i)), b = _mm_loadu_si128 ((const __m128i*) (src + 24 * i + 16));
+    const __m128i c = _mm_loadu_si128 ((const __m128i*) (src + 24 * i + 32));
+    __m128i *d = (__m128i*) (dst + 40 * i);
+    _mm_stream_si128 (d, a);                              // ctx0, ctx1
+    _mm_stream_si128 (d + 1, _mm_unpacklo_epi64 (b, ones)); // bits, -1
+    _mm_stream_si128 (d + 2, _mm_unpackhi_epi64 (ones, b)); // -1, ctx0'
+    _mm_stream_si128 (d + 3, c);                          // ctx1', bits'
+    _mm_stream_si128 (d + 4, ones);                       // -1, -1
+  }
+  if (i < n_rows) one (i++);
+  _mm_sfence ();
+#else
+  for (; i < n_rows; i++) {
+    long long v[3];
+    memcpy (v, src + 24 * i, 24);
+    long long *d = (long long*) (dst + 40 * i);
+    d[0] = v[0]; d[1] = v[1]; d[2] = v[2]; d[3] = -1LL; d[4] = -1LL;
+  }
+#endif
+}
+void tjb_expand_rows (void *dst, const void *src, size_t n_rows) { expand_block ((uint8_t*) dst, (const uint8_t*) src, n_rows); }
+#define TJB_EXPAND_BLOCK ((size_t) 1024)  // rows per unit of an expand job
+
 static void packer_take_part (tjb_packer *p, int who)
 {
+  if (p->copy_dst && p->expand) {
+    for (;;) {
+      const size_t b = p->next_block.fetch_add (1, std::memory_order_relaxed);
+      if (b >= p->n_blocks) return;
+      const size_t lo = b * TJB_EXPAND_BLOCK, hi = lo + TJB_EXPAND_BLOCK < p->n ? lo + TJB_EXPAND_BLOCK : p->n;
+      expand_block (p->copy_dst + 40 * lo, p->src + 24 * lo, hi - lo);
+    }
+  }
   if (p->copy_dst) {
     for (;;) {
       const size_t b = p->next_block.fetch_add (1, std::memory_order_relaxed);
@@ -247,8 +294,20 @@ long tjb_packer_run (tjb_packer *p, const uint8_t *src, size_t n, uint8_t *packe
 void tjb_packer_copy (tjb_packer *p, void *dst, const void *src, size_t n)
 {
   if (!n) return;
-  p->src = (const uint8_t*) src; p->n = n; p->copy_dst = (uint8_t*) dst;
+  p->src = (const uint8_t*) src; p->n = n; p->copy_dst = (uint8_t*) dst; p->expand = false;
   p->n_blocks = (n + TJB_COPY_BLOCK - 1) / TJB_COPY_BLOCK;
+  p->next_block.store (0, std::memory_order_relaxed);
+  const uint64_t g = p->gen.fetch_add (1, std::memory_order_acq_rel) + 1;
+  packer_take_part (p, p->T);
+  unsigned spins = 0;
+  while (p->done.load (std::memory_order_acquire) < (uint64_t) p->T * g) spin_step (spins);
+}
+
+void tjb_packer_expand (tjb_packer *p, void *dst, const void *src, size_t n_rows)
+{
+  if (!n_rows) return;
+  p->src = (const uint8_t*) src; p->n = n_rows; p->copy_dst = (uint8_t*) dst; p->expand = true;
+  p->n_blocks = (n_rows + TJB_EXPAND_BLOCK - 1) / TJB_EXPAND_BLOCK;
   p->next_block.store (0, std::memory_order_relaxed);
   const uint64_t g = p->gen.fetch_add (1, std::memory_order_acq_rel) + 1;
   packer_take_part (p, p->T);
@@ -272,8 +331,17 @@ extern "C" long tjb_hostpack_selftest (const uint8_t *src, size_t n, int threads
   std::vector<uint8_t> tmp (np + 1, 0xAA);
   tjb_packer_begin (p);
   tjb_packer_copy (p, tmp.data (), packed, np);
-  const bool same = memcmp (tmp.data (), packed, np) == 0 && tmp[np] == 0xAA;
+  bool same = memcmp (tmp.data (), packed, np) == 0 && tmp[np] == 0xAA;
+  { // and expands 24-byte rows: the packed bytes serve as rows
+    const size_t rows = np / 24;
+    std::vector<long long> e (5 * rows + 1, 0x5555);
+    tjb_packer_expand (p, e.data (), packed, rows);
+    for (size_t i = 0; i < rows && same; i++)
+      same = memcmp (&e[5 * i], packed + 24 * i, 24) == 0 && e[5 * i + 3] == -1LL && e[5 * i + 4] == -1LL;
+    same = same && e[5 * rows] == 0x5555;
+  }
   tjb_packer_end (p);
   tjb_packer_destroy (p);
   return !same ? -4 : r == r2 ? r : -3;
 }
+extern "C" void tjb_hostpack_expand_hook (void *dst, const void *src, size_t n_rows) { tjb_expand_rows (dst, src, n_rows); }

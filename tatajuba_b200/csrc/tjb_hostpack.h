@@ -24,5 +24,9 @@ void tjb_packer_end (tjb_packer *p);
 long tjb_packer_run (tjb_packer *p, const uint8_t *src, size_t n, uint8_t *packed, uint32_t *exc_pos, uint8_t *exc_val, size_t cap);
 // dst[0, n) = src[0, n) by the pool and the caller together (between begin and end), 64 KiB blocks, streaming stores
 void tjb_packer_copy (tjb_packer *p, void *dst, const void *src, size_t n);
+// dst[40 i .. 40 i + 40) = src[24 i .. 24 i + 24) followed by four int32 -1, for i < n_rows (the result elements cross PCIe
+// without their constant tail); _rows = on the calling thread alone
+void tjb_packer_expand (tjb_packer *p, void *dst, const void *src, size_t n_rows);
+void tjb_expand_rows (void *dst, const void *src, size_t n_rows);
 // single-threaded, portable restatement (tests, small inputs)
 long tjb_pack_scalar (const uint8_t *src, size_t n, uint8_t *packed, uint32_t *exc_pos, uint8_t *exc_val, size_t cap, uint32_t pos0);

@@ -44,11 +44,12 @@ class Context:
 
     def __init__(self, device=0):
         self.lib = _lib.load()
-        # host-buffer path: the packer threads of the 2-bit transfer spin while a sample is fed, so ranks that share
-        # one host (torchrun: LOCAL_WORLD_SIZE) split the cores between them; fewer than 4 each = plain transfers
+        # the host pool (2-bit packing of host buffers, copy-out of the results) spins while a sample is processed, so
+        # ranks that share one host (torchrun: LOCAL_WORLD_SIZE) split the cores between them; with fewer than 4
+        # threads the library sends host buffers as they are and uses the pool for the copy-out only
         if "TJB_HOST_PACK" not in os.environ and int(os.environ.get("LOCAL_WORLD_SIZE", "1")) > 1:
             share = (os.cpu_count() or 1) // int(os.environ["LOCAL_WORLD_SIZE"]) - 1
-            os.environ["TJB_HOST_PACK"] = str(share if share >= 4 else 0)
+            os.environ["TJB_HOST_PACK"] = str(max(share, 0))
         h = C.c_void_p()
         rc = self.lib.tjb_ctx_create(int(device), C.byref(h))
         if rc < 0:

@@ -64,3 +64,21 @@ def test_pack_reports_exception_overflow():
 def test_pack_empty():
     ne, packed, _, _ = run(np.zeros(0, np.uint8), 2)
     assert ne == 0 and len(packed) == 0
+
+
+@pytest.mark.parametrize("n_rows", [0, 1, 2, 3, 8, 1001])
+@pytest.mark.parametrize("shift", [0, 1])  # destination starting on an even / odd element (16-byte aligned or not)
+def test_expand_rows(n_rows, shift):
+    """24 varying bytes per result element -> the reference's 40-byte hopo_element with its constant tail of -1s"""
+    lib = _lib.load()
+    fn = lib.tjb_hostpack_expand_hook
+    fn.restype = None
+    fn.argtypes = [C.c_void_p, C.c_void_p, C.c_size_t]
+    rng = np.random.default_rng(n_rows)
+    src = rng.integers(0, 2**63, size=(n_rows + shift, 3), dtype=np.int64)
+    dst = np.full((n_rows + shift + 1, 5), 7, np.int64)
+    assert dst.ctypes.data % 16 == 0
+    fn(dst[shift:].ctypes.data, src[shift:].ctypes.data, n_rows)
+    assert np.array_equal(dst[shift:shift + n_rows, :3], src[shift:])
+    assert np.all(dst[shift:shift + n_rows, 3:] == -1)
+    assert np.all(dst[:shift] == 7) and np.all(dst[shift + n_rows:] == 7)  # nothing outside the range is written
