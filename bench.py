@@ -52,7 +52,10 @@ class ClockSampler(threading.Thread):
         try:
             import pynvml
             pynvml.nvmlInit()
-            self.nvml = (pynvml, pynvml.nvmlDeviceGetHandleByIndex(index))
+            h = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.mx = pynvml.nvmlDeviceGetMaxClockInfo(h, pynvml.NVML_CLOCK_SM)
+            pynvml.nvmlDeviceGetClockInfo(h, pynvml.NVML_CLOCK_SM)  # the first query of a process is the slow one
+            self.nvml = (pynvml, h)
         except Exception:
             pass
 
@@ -62,11 +65,12 @@ class ClockSampler(threading.Thread):
             bits = [nv.nvmlClocksThrottleReasonHwSlowdown, nv.nvmlClocksThrottleReasonHwThermalSlowdown,
                     nv.nvmlClocksThrottleReasonSwThermalSlowdown, nv.nvmlClocksThrottleReasonSwPowerCap]
             try:
-                mx = nv.nvmlDeviceGetMaxClockInfo(h, nv.NVML_CLOCK_SM)
-                while not self.stop_flag:
+                while True:  # at least one sample, taken as the timed region starts
                     sm = nv.nvmlDeviceGetClockInfo(h, nv.NVML_CLOCK_SM)
                     r = nv.nvmlDeviceGetCurrentClocksThrottleReasons(h)
-                    self.rows.append([str(sm), str(mx)] + ["Active" if r & b else "Not Active" for b in bits])
+                    self.rows.append([str(sm), str(self.mx)] + ["Active" if r & b else "Not Active" for b in bits])
+                    if self.stop_flag:
+                        break
                     time.sleep(0.02)  # a query takes the driver's lock for ~1 ms on an 8-GPU box: keep them rare
                 return
             except Exception as e:
