@@ -592,15 +592,20 @@ __global__ void __launch_bounds__ (256)
 pack_kernel (const u64 *__restrict__ out_rec, const u32 *__restrict__ out_cnt, const u32 *__restrict__ out_idx_i, const u32 *__restrict__ out_idx_f,
              const u32 *__restrict__ bkt_start, const uint4 *__restrict__ bstat, const u32 *__restrict__ koff, const u32 *__restrict__ ioff,
              const u32 *__restrict__ meta, int k, u64 *__restrict__ out24, int *__restrict__ idx_initial, int *__restrict__ idx_final,
-             u32 *__restrict__ cov_keys, u32 *__restrict__ cov_vals, u32 cov_mask)
+             u32 *__restrict__ cov_keys, u32 *__restrict__ cov_vals, u32 cov_mask, u32 max_keep, u32 max_idx, unsigned long long capacity)
 {
+  // The host may launch this kernel before it knows the counts, into arrays sized from the previous sample (max_keep,
+  // max_idx; the coverage table holds 2 max_keep keys at load <= 0.5): nothing is written beyond them, and the host
+  // repeats the launch with exact sizes when the counts turn out larger (or the record array had overflowed).
   const u32 nb = meta[META_NBUCKETS];
   const int lane = threadIdx.x & 31;
   const u32 warps = gridDim.x * (256 / 32);
   for (u32 b = blockIdx.x * (256 / 32) + (threadIdx.x >> 5); b < nb; b += warps) {
     const uint4 s = bstat[b];
     const u32 start = bkt_start[b], ko = koff[b], io = ioff[b];
+    if ((unsigned long long) start + s.y > capacity || (unsigned long long) start + s.z > capacity) continue;
     for (u32 j = lane; j < s.y; j += 32) {
+      if (ko + j >= max_keep) break;
       Rec<W> r = load_rec<W> (out_rec, (size_t) start + j);
       const int cnt = sext_field ((long long) out_cnt[start + j], 20); // the reference's count:20 signed bit-field
       // gcc x86-64 bit-field order from the LSB: base:2 length:10 count:20 mismatches:12 multi:3 neg_strand:2 canon_flag:3
@@ -615,6 +620,7 @@ pack_kernel (const u64 *__restrict__ out_rec, const u32 *__restrict__ out_cnt, c
       cov_insert (cov_keys, cov_vals, cov_mask, (u32) (c1 & 0x7fffffffULL), (u32) cnt);
     }
     for (u32 t = lane; t < s.z; t += 32) {
+      if (io + t >= max_idx) break;
       idx_initial[io + t] = (int) (ko + out_idx_i[start + t]);
       idx_final[io + t] = (int) (ko + out_idx_f[start + t]);
     }

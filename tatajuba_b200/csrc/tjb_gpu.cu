@@ -459,11 +459,41 @@ static int finalise_t (tjb_ctx *ctx, const tjb_opts *opt, tjb_counter_out *out, 
   LAUNCH (K_BUCKET, 0, (bucket_reduce_kernel<W><<<grid * (W == 2 ? BK_CTAS2 : 2), BK_THREADS, bucket_smem_bytes<W> (), st>>> (rec_b, ctx->d_bkt_start, ctx->d_meta, cap, digit_list (W, k), opt->remove_biased, opt->min_coverage, rec_a, (u32*) ctx->out_cnt.p, (u32*) ctx->out_ii.p, (u32*) ctx->out_if.p, ctx->d_bstat)));
   LAUNCH (K_TOTALS, 0, (totals_kernel<<<1, PLAN_THREADS, 0, st>>> (ctx->d_bstat, ctx->d_meta, ctx->d_koff, ctx->d_ioff)));
   CU (cudaGetLastError ());
+  // elements + group indices + coverage, into arrays for max_keep records / max_idx groups
+  const int cov_init = INT_MIN;
+  auto launch_pack = [&] (u32 max_keep, u32 max_idx) -> int {
+    u32 slots = 1024;
+    while (slots < 4u * max_keep) slots <<= 1; // two keys per record, load factor <= 0.5
+    TRY (ensure (ctx, ctx->cov_tab, (size_t) slots * 8));
+    TRY (ensure (ctx, ctx->out40, (size_t) max_keep * 24)); TRY (ensure (ctx, ctx->idx_i, (size_t) max_idx * 4)); TRY (ensure (ctx, ctx->idx_f, (size_t) max_idx * 4));
+    u32 *cov_keys = (u32*) ctx->cov_tab.p, *cov_vals = cov_keys + slots;
+    CU (cudaMemsetAsync (cov_keys, 0xff, (size_t) slots * 4, st));
+    CU (cudaMemsetAsync (cov_vals, 0, (size_t) slots * 4, st));
+    CU (cudaMemcpyAsync (ctx->d_cov, &cov_init, 4, cudaMemcpyHostToDevice, st));
+    LAUNCH (K_PACK, (8 * W + 4 + 24) * (size_t) max_keep + 16 * (size_t) max_idx,
+            (pack_kernel<W><<<grid * 4, 256, 0, st>>> ((const u64*) ctx->rec_a.p, (u32*) ctx->out_cnt.p, (u32*) ctx->out_ii.p, (u32*) ctx->out_if.p, ctx->d_bkt_start, ctx->d_bstat, ctx->d_koff, ctx->d_ioff, ctx->d_meta, k, (u64*) ctx->out40.p, (int*) ctx->idx_i.p, (int*) ctx->idx_f.p, cov_keys, cov_vals, slots - 1, max_keep, max_idx, cap)));
+    LAUNCH (K_COVMAX, 8 * (size_t) slots, (cov_max_kernel<<<nblk (slots, 256 * 8), 256, 0, st>>> (cov_keys, cov_vals, slots, ctx->d_cov)));
+    CU (cudaGetLastError ());
+    return 0;
+  };
   // ---- synchronisation 1: counts --------------------------------------------------------------------------
   unsigned long long *hs = ctx->h_sync;
   u32 *hm = (u32*) (hs + 2);
   CU (cudaMemcpyAsync (hs, ctx->d_counters, 2 * sizeof (unsigned long long), cudaMemcpyDeviceToHost, st));
   CU (cudaMemcpyAsync (hm, ctx->d_meta, META_WORDS * sizeof (u32), cudaMemcpyDeviceToHost, st));
+  cudaEvent_t ev_counts = get_event (ctx);
+  CU (cudaEventRecord (ev_counts, st));
+  // The counts are only known after this round trip, but samples of one run are alike: launch the last kernels now,
+  // sized from the previous sample (+12 %), so that they run while the host handles the counts; they are launched
+  // again with the exact sizes in the rare case that the guess was too small.
+  bool spec_packed = false;
+  u32 spec_max_keep = 0, spec_max_idx = 0;
+  if (ctx->last_keep && ctx->last_idx) {
+    spec_max_keep = (u32) (ctx->last_keep + ctx->last_keep / 8 + 256);
+    spec_max_idx = (u32) (ctx->last_idx + ctx->last_idx / 8 + 256);
+    TRY (launch_pack (spec_max_keep, spec_max_idx));
+    spec_packed = true;
+  }
   tr.mark ("enqueue1");
   // the copy-out below is bound by ONE host thread copying out of the pinned staging buffer (~20 GB/s): when the
   // previous result was large, wake the host pool now (its wake-up hides under the kernels) and let it share the copy
@@ -495,7 +525,8 @@ static int finalise_t (tjb_ctx *ctx, const tjb_opts *opt, tjb_counter_out *out, 
     } else spec.keep = spec.idx = 0;
   }
   tr.mark ("prealloc");
-  CU (cudaStreamSynchronize (st));
+  CU (cudaEventSynchronize (ev_counts));
+  ctx->free_events.push_back (ev_counts);
   tr.mark ("sync1");
   if (hs[0] > cap) { *overflow = true; return 0; } // the record array overflowed: everything above worked on garbage
   out->n_raw = (int64_t) hs[0];
@@ -526,19 +557,8 @@ static int finalise_t (tjb_ctx *ctx, const tjb_opts *opt, tjb_counter_out *out, 
   if (!n_idx) { out->status = TJB_NO_CTX_ABOVE_COVERAGE; return 0; }
 
   // ---- reference-layout elements, global group indices, coverage (:420-438) ---------------------------------
-  u32 slots = 1024;
-  while (slots < 4u * n_keep) slots <<= 1; // two keys per record, load factor <= 0.5
-  TRY (ensure (ctx, ctx->cov_tab, (size_t) slots * 8));
-  TRY (ensure (ctx, ctx->out40, (size_t) n_keep * 24)); TRY (ensure (ctx, ctx->idx_i, (size_t) n_idx * 4)); TRY (ensure (ctx, ctx->idx_f, (size_t) n_idx * 4));
-  u32 *cov_keys = (u32*) ctx->cov_tab.p, *cov_vals = cov_keys + slots;
-  CU (cudaMemsetAsync (cov_keys, 0xff, (size_t) slots * 4, st));
-  CU (cudaMemsetAsync (cov_vals, 0, (size_t) slots * 4, st));
-  int cov_init = INT_MIN;
-  CU (cudaMemcpyAsync (ctx->d_cov, &cov_init, 4, cudaMemcpyHostToDevice, st));
-  LAUNCH (K_PACK, (8 * W + 4 + 24) * (size_t) n_keep + 16 * (size_t) n_idx,
-          (pack_kernel<W><<<nblk (n_buckets, 8), 256, 0, st>>> (rec_a, (u32*) ctx->out_cnt.p, (u32*) ctx->out_ii.p, (u32*) ctx->out_if.p, ctx->d_bkt_start, ctx->d_bstat, ctx->d_koff, ctx->d_ioff, ctx->d_meta, k, (u64*) ctx->out40.p, (int*) ctx->idx_i.p, (int*) ctx->idx_f.p, cov_keys, cov_vals, slots - 1)));
-  LAUNCH (K_COVMAX, 8 * (size_t) slots, (cov_max_kernel<<<nblk (slots, 256 * 8), 256, 0, st>>> (cov_keys, cov_vals, slots, ctx->d_cov)));
-  CU (cudaGetLastError ());
+  if (!(spec_packed && n_keep <= spec_max_keep && n_idx <= spec_max_idx && !hm[META_NOVERSIZE]))
+    TRY (launch_pack (n_keep, n_idx)); // not launched ahead, or the previous sample's sizes were too small
   tr.mark ("enqueue2");
   // copy out into malloc'ed host memory (the reference free()s these).  Measured on B200 for 2.8 MB: the driver's
   // pageable path 250 us; pinned staging in 4 chunks with the host copy of chunk i under the DMA of chunk i+1 220 us
