@@ -247,3 +247,14 @@ def test_gpu_packed_host_transfer_is_transparent(ctx, restatement, monkeypatch):
         other.close()
     small = buf[: 151 * 60_000]  # 9 MB: still packed, small enough for the oracle
     check(ctx, restatement, small, 25, 3, 5, True, "packed transfer vs oracle", device_too=False)
+
+
+def test_gpu_result_size_changes_between_samples(ctx, restatement):
+    """a context sizes the result arrays and the last kernels of a sample from the previous sample's counts (they are
+    allocated / launched before the counts are known): alternate small and 20x larger samples, and an empty one"""
+    small = synth.sample_buffer(20_000, 40, seed=21)
+    big = synth.sample_buffer(400_000, 60, seed=22)
+    for i, buf in enumerate((small, big, small, big, big, small)):
+        check(ctx, restatement, buf, 25, 4, 5, True, f"alternating sample {i}")
+    check(ctx, restatement, small[:0], 25, 4, 5, True, "empty after large", device_too=False)
+    check(ctx, restatement, big, 25, 4, 5, True, "large after empty")
