@@ -3,6 +3,8 @@
 #include "tjb_hostpack.h"
 
 #include <atomic>
+#include <sched.h>
+#include <stdio.h>
 #include <condition_variable>
 #include <mutex>
 #include <string.h>
@@ -235,10 +237,30 @@ static void packer_worker (tjb_packer *p, int tid)
   }
 }
 
+// hardware threads this process may actually use: the affinity mask, capped by a cgroup v2 CPU quota if there is one
+// (spinning workers beyond that are worse than none)
+static int usable_cpus ()
+{
+  int n = (int) std::thread::hardware_concurrency ();
+#if defined(__linux__)
+  cpu_set_t set;
+  if (sched_getaffinity (0, sizeof (set), &set) == 0) { const int c = CPU_COUNT (&set); if (c > 0 && (n <= 0 || c < n)) n = c; }
+  if (FILE *f = fopen ("/sys/fs/cgroup/cpu.max", "r")) {
+    long long quota = 0, period = 0;
+    if (fscanf (f, "%lld %lld", &quota, &period) == 2 && quota > 0 && period > 0) {
+      const int q = (int) ((quota + period - 1) / period);
+      if (q < n) n = q;
+    }
+    fclose (f);
+  }
+#endif
+  return n < 1 ? 1 : n;
+}
+
 tjb_packer *tjb_packer_create (int n_threads)
 {
   if (n_threads <= 0) { // leave two hardware threads to the caller and the driver: the workers spin
-    n_threads = (int) std::thread::hardware_concurrency () - 2;
+    n_threads = usable_cpus () - 2;
     if (n_threads > 32) n_threads = 32;
     if (n_threads < 1) n_threads = 1;
   }

@@ -48,7 +48,8 @@ class Context:
         # ranks that share one host (torchrun: LOCAL_WORLD_SIZE) split the cores between them; with fewer than 4
         # threads the library sends host buffers as they are and uses the pool for the copy-out only
         if "TJB_HOST_PACK" not in os.environ and int(os.environ.get("LOCAL_WORLD_SIZE", "1")) > 1:
-            share = (os.cpu_count() or 1) // int(os.environ["LOCAL_WORLD_SIZE"]) - 1
+            cpus = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+            share = cpus // int(os.environ["LOCAL_WORLD_SIZE"]) - 1
             os.environ["TJB_HOST_PACK"] = str(max(share, 0))
         h = C.c_void_p()
         rc = self.lib.tjb_ctx_create(int(device), C.byref(h))
