@@ -63,28 +63,29 @@ template <> __device__ __forceinline__ u32 rec_bin<3> (const Rec<3> &r, int k, i
 }
 
 // ------------------------------------------------------------------------------- block scan helpers ------
-// exclusive scan of one value per thread over a block of NT threads; *total = block sum.  Two barriers.
+// exclusive scan of one value per thread over a block of NT threads; *total = block sum.  ONE barrier: every warp
+// scans the warp totals itself, and consecutive calls alternate between the two halves of s_warp (phase), so a warp
+// that runs ahead into the next call writes the other half; the call after that is behind the next call's barrier,
+// which no warp passes before every warp has read this call's totals.  All threads must pass the same phase.
 template <int NT>
-__device__ __forceinline__ u32 blk_excl_scan (u32 v, u32 *s_warp /*[NT/32 + 1]*/, u32 *total)
+__device__ __forceinline__ u32 blk_excl_scan (u32 v, u32 *s_warp /*[2 * NT / 32]*/, int &phase, u32 *total)
 {
+  constexpr int NW = NT / 32;
   const int lane = threadIdx.x & 31, wid = threadIdx.x >> 5;
+  u32 *buf = s_warp + phase * NW;
+  phase ^= 1;
   u32 inc = v;
 #pragma unroll
   for (int d = 1; d < 32; d <<= 1) { u32 t = __shfl_up_sync (0xffffffffu, inc, d); if (lane >= d) inc += t; }
-  if (lane == 31) s_warp[wid] = inc;
+  if (lane == 31) buf[wid] = inc;
   __syncthreads ();
-  if (wid == 0) {
-    u32 w = lane < NT / 32 ? s_warp[lane] : 0, winc = w;
+  const u32 w = lane < NW ? buf[lane] : 0;
+  u32 winc = w;
 #pragma unroll
-    for (int d = 1; d < 32; d <<= 1) { u32 t = __shfl_up_sync (0xffffffffu, winc, d); if (lane >= d) winc += t; }
-    if (lane < NT / 32) s_warp[lane] = winc - w;
-    if (lane == 31) s_warp[NT / 32] = winc;
-  }
-  __syncthreads ();
-  u32 r = s_warp[wid] + inc - v;
-  *total = s_warp[NT / 32];
-  __syncthreads (); // s_warp may be reused immediately
-  return r;
+  for (int d = 1; d < NW; d <<= 1) { u32 t = __shfl_up_sync (0xffffffffu, winc, d); if (lane >= d) winc += t; }
+  const u32 before = __shfl_sync (0xffffffffu, winc - w, wid);
+  *total = __shfl_sync (0xffffffffu, winc, NW - 1);
+  return before + inc - v;
 }
 
 // ------------------------------------------------------------------------------- histogram (fallback) ----
@@ -111,7 +112,8 @@ __global__ void __launch_bounds__ (PLAN_THREADS)
 plan_kernel (const u32 *__restrict__ bin_hist, int F, const unsigned long long *__restrict__ counters, unsigned long long capacity,
              u32 *__restrict__ bkt_start, u32 *__restrict__ lut, u32 *__restrict__ cursor, u32 *__restrict__ meta, u32 max_buckets)
 {
-  __shared__ u32 s_warp[PLAN_THREADS / 32 + 1];
+  __shared__ u32 s_warp[2 * (PLAN_THREADS / 32)];
+  int scan_phase = 0;
   const u32 NB = 1u << F;
   const u32 t = threadIdx.x;
   const bool active = t * IPT < NB;       // NB < PLAN_THREADS * IPT only when IPT == 1
@@ -136,7 +138,7 @@ plan_kernel (const u32 *__restrict__ bin_hist, int F, const unsigned long long *
 #pragma unroll
   for (int i = 0; i < IPT; i++) sum += h[i];
   u32 total;
-  const u32 P0 = blk_excl_scan<PLAN_THREADS> (sum, s_warp, &total);
+  const u32 P0 = blk_excl_scan<PLAN_THREADS> (sum, s_warp, scan_phase, &total);
   // records of the bin walked just before my first one (bin lo + IPT)
   const u32 hprev = (active && t > 0) ? bin_hist[lo + IPT] : 0;
   u32 nheads = 0;
@@ -150,7 +152,7 @@ plan_kernel (const u32 *__restrict__ bin_hist, int F, const unsigned long long *
     }
   }
   u32 nb_total;
-  u32 b = blk_excl_scan<PLAN_THREADS> (nheads, s_warp, &nb_total); // index of my first head
+  u32 b = blk_excl_scan<PLAN_THREADS> (nheads, s_warp, scan_phase, &nb_total); // index of my first head
   if (active) {
     u32 p = P0, hp = hprev;
 #pragma unroll
@@ -188,14 +190,15 @@ __global__ void __launch_bounds__ (PLAN_THREADS)
 plan_big_kernel (const u32 *__restrict__ bin_hist, int F, const unsigned long long *__restrict__ counters, unsigned long long capacity,
                  u32 *__restrict__ bkt_start, u32 *__restrict__ lut, u32 *__restrict__ cursor, u32 *__restrict__ meta, u32 max_buckets)
 {
-  __shared__ u32 s_warp[PLAN_THREADS / 32 + 1];
+  __shared__ u32 s_warp[2 * (PLAN_THREADS / 32)];
+  int scan_phase = 0;
   const u32 NB = 1u << F, ipt = NB / PLAN_THREADS; // F > 10: every thread owns ipt >= 64 bins
   const u32 t = threadIdx.x;
   const u32 lo = NB - (t + 1) * ipt;
   u32 sum = 0;
   for (u32 i = 0; i < ipt; i += 4) { const uint4 v = *reinterpret_cast<const uint4*> (bin_hist + lo + i); sum += v.x + v.y + v.z + v.w; }
   u32 total;
-  const u32 P0 = blk_excl_scan<PLAN_THREADS> (sum, s_warp, &total);
+  const u32 P0 = blk_excl_scan<PLAN_THREADS> (sum, s_warp, scan_phase, &total);
   const u32 hprev = t > 0 ? bin_hist[lo + ipt] : 0;
   u32 nheads = 0;
   {
@@ -211,7 +214,7 @@ plan_big_kernel (const u32 *__restrict__ bin_hist, int F, const unsigned long lo
     }
   }
   u32 nb_total;
-  u32 b = blk_excl_scan<PLAN_THREADS> (nheads, s_warp, &nb_total);
+  u32 b = blk_excl_scan<PLAN_THREADS> (nheads, s_warp, scan_phase, &nb_total);
   {
     u32 p = P0, hp = hprev;
     for (u32 i = ipt; i > 0; i -= 4) {
@@ -299,7 +302,8 @@ bucket_reduce_kernel (const u64 *__restrict__ recs, const u32 *__restrict__ bkt_
   u32 *s_tab = s_val;                                                        // [2 * BK_CAP] de-duplication hash table; dead before
                                                                              // s_val / s_sum are first written
   u32 *s_cntrec = s_sum + BK_CAP;                                            // [BK_CAP] fwd count | rev count << 16 of a representative
-  __shared__ u32 s_warp[BK_WARPS + 1];
+  __shared__ u32 s_warp[2 * BK_WARPS];
+  int scan_phase = 0;
   __shared__ u32 s_bucket;
   __shared__ u32 s_diff[2 * W];
   __shared__ u32 s_ndist;
@@ -435,7 +439,7 @@ bucket_reduce_kernel (const u64 *__restrict__ recs, const u32 *__restrict__ bkt_
 #pragma unroll
           for (int w = 0; w < BK_WARPS; w++) { c[w] = s_cnt[w * 256 + tid]; sum += c[w]; }
           u32 tot;
-          u32 ex = blk_excl_scan<BK_THREADS> (sum, s_warp, &tot);
+          u32 ex = blk_excl_scan<BK_THREADS> (sum, s_warp, scan_phase, &tot);
 #pragma unroll
           for (int w = 0; w < BK_WARPS; w++) { s_cnt[w * 256 + tid] = (unsigned short) ex; ex += c[w]; }
         }
@@ -478,7 +482,7 @@ bucket_reduce_kernel (const u64 *__restrict__ recs, const u32 *__restrict__ bkt_
           packed[r] = d | (cnt << 12) | (flag << 28);
         }
       }
-      u32 kpos = blk_excl_scan<BK_THREADS> (__popc (kmask), s_warp, &n_keep);
+      u32 kpos = blk_excl_scan<BK_THREADS> (__popc (kmask), s_warp, scan_phase, &n_keep);
 #pragma unroll
       for (int r = 0; r < BK_IPT; r++) if ((kmask >> r) & 1) s_val[kpos++] = packed[r];
     }
@@ -504,8 +508,8 @@ bucket_reduce_kernel (const u64 *__restrict__ recs, const u32 *__restrict__ bkt_
           }
         }
       }
-      u32 gpos = blk_excl_scan<BK_THREADS> (__popc (gmask), s_warp, &n_groups);
-      u32 cpos = blk_excl_scan<BK_THREADS> (csum, s_warp, &ctotal);
+      u32 gpos = blk_excl_scan<BK_THREADS> (__popc (gmask), s_warp, scan_phase, &n_groups);
+      u32 cpos = blk_excl_scan<BK_THREADS> (csum, s_warp, scan_phase, &ctotal);
       __syncthreads (); // every S2 read of s_aux is done (it is reused for the group starts)
 #pragma unroll
       for (int r = 0; r < BK_IPT; r++) {
@@ -531,7 +535,7 @@ bucket_reduce_kernel (const u64 *__restrict__ recs, const u32 *__restrict__ bkt_
           if ((int) (hi - s_sum[js[r]]) >= min_coverage) imask |= 1u << r;
         }
       }
-      u32 ipos = blk_excl_scan<BK_THREADS> (__popc (imask), s_warp, &n_idx);
+      u32 ipos = blk_excl_scan<BK_THREADS> (__popc (imask), s_warp, scan_phase, &n_idx);
 #pragma unroll
       for (int r = 0; r < BK_IPT; r++)
         if ((imask >> r) & 1) { out_idx_i[start + ipos] = js[r]; out_idx_f[start + ipos] = je[r]; ipos++; }
@@ -553,16 +557,17 @@ bucket_reduce_kernel (const u64 *__restrict__ recs, const u32 *__restrict__ bkt_
 __global__ void __launch_bounds__ (PLAN_THREADS)
 totals_kernel (const uint4 *__restrict__ bstat, u32 *__restrict__ meta, u32 *__restrict__ koff, u32 *__restrict__ ioff)
 {
-  __shared__ u32 s_warp[PLAN_THREADS / 32 + 1];
+  __shared__ u32 s_warp[2 * (PLAN_THREADS / 32)];
+  int scan_phase = 0;
   const u32 nb = meta[META_NBUCKETS];
   const u32 ipt = (nb + PLAN_THREADS - 1) / PLAN_THREADS;
   const u32 b0 = threadIdx.x * ipt, b1 = (b0 + ipt < nb) ? b0 + ipt : nb;
   u32 sd = 0, sk = 0, si = 0;
   for (u32 b = b0; b < b1; b++) { uint4 s = bstat[b]; sd += s.x; sk += s.y; si += s.z; }
   u32 td, tk, ti;
-  blk_excl_scan<PLAN_THREADS> (sd, s_warp, &td);
-  u32 ek = blk_excl_scan<PLAN_THREADS> (sk, s_warp, &tk);
-  u32 ei = blk_excl_scan<PLAN_THREADS> (si, s_warp, &ti);
+  blk_excl_scan<PLAN_THREADS> (sd, s_warp, scan_phase, &td);
+  u32 ek = blk_excl_scan<PLAN_THREADS> (sk, s_warp, scan_phase, &tk);
+  u32 ei = blk_excl_scan<PLAN_THREADS> (si, s_warp, scan_phase, &ti);
   for (u32 b = b0; b < b1; b++) { uint4 s = bstat[b]; koff[b] = ek; ioff[b] = ei; ek += s.y; ei += s.z; }
   if (threadIdx.x == 0) { meta[META_NDIST] = td; meta[META_NKEEP] = tk; meta[META_NIDX] = ti; }
 }
