@@ -327,6 +327,7 @@ bucket_reduce_kernel (const u64 *__restrict__ recs, const u32 *__restrict__ bkt_
       __syncthreads ();
       continue;
     }
+    const u32 tsize = n <= 32 ? 64u : 1u << (32 - __clz (2 * n - 1)); // hash table: power of two >= max(64, 2 n)
     // ---- load the bucket; remember which key bits differ at all ------------------------------------------
     {
       u64 d[W];
@@ -334,6 +335,10 @@ bucket_reduce_kernel (const u64 *__restrict__ recs, const u32 *__restrict__ bkt_
       for (int j = 0; j < W; j++) d[j] = 0;
       Rec<W> f;
       if (n) f = load_rec<W> (recs, start);
+      // (the hash table and the per-record counters of the de-duplication below are cleared here, under the latency of
+      // the loads; their arrays were last read before the barrier that ended the previous bucket)
+      for (u32 i = tid; i < tsize; i += BK_THREADS) s_tab[i] = BK_EMPTY;
+      for (u32 i = tid; i < n; i += BK_THREADS) s_cntrec[i] = 0;
       for (u32 i = tid; i < n; i += BK_THREADS) {
         Rec<W> r = load_rec<W> (recs, (size_t) start + i);
 #pragma unroll
@@ -350,10 +355,6 @@ bucket_reduce_kernel (const u64 *__restrict__ recs, const u32 *__restrict__ bkt_
     // in a shared-memory hash table first (run-length count of hopo_counter.c:355-365 without the sort) and sort only
     // the distinct observations.  Table entry = index of the first record seen with that key (its representative);
     // s_cntrec[representative] = forward-strand copies | reverse-strand copies << 16 (canon_flag = which are non-zero, :362)
-    const u32 tsize = n <= 32 ? 64u : 1u << (32 - __clz (2 * n - 1)); // power of two >= max(64, 2 n)
-    for (u32 i = tid; i < tsize; i += BK_THREADS) s_tab[i] = BK_EMPTY;
-    for (u32 i = tid; i < n; i += BK_THREADS) s_cntrec[i] = 0;
-    __syncthreads ();
     // the record that claims a table slot is the representative of its key and appends itself to s_perm0 (one
     // shared-memory atomic per warp and round; the order is arbitrary, the keys are distinct and get sorted below)
     for (u32 i0 = 0; i0 < n; i0 += BK_THREADS) {
@@ -508,8 +509,12 @@ bucket_reduce_kernel (const u64 *__restrict__ recs, const u32 *__restrict__ bkt_
           }
         }
       }
-      u32 gpos = blk_excl_scan<BK_THREADS> (__popc (gmask), s_warp, scan_phase, &n_groups);
-      u32 cpos = blk_excl_scan<BK_THREADS> (csum, s_warp, scan_phase, &ctotal);
+      // one scan for both: the counts of a bucket sum to at most BK_CAP < 2^16, the groups to at most BK_CAP
+      static_assert (BK_CAP < (1 << 16), "two 16-bit sums per scanned word");
+      u32 both_total;
+      const u32 both = blk_excl_scan<BK_THREADS> (((u32) __popc (gmask) << 16) | csum, s_warp, scan_phase, &both_total);
+      u32 gpos = both >> 16, cpos = both & 0xffffu;
+      n_groups = both_total >> 16; ctotal = both_total & 0xffffu;
       __syncthreads (); // every S2 read of s_aux is done (it is reused for the group starts)
 #pragma unroll
       for (int r = 0; r < BK_IPT; r++) {
