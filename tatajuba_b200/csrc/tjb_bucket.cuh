@@ -311,19 +311,27 @@ bucket_reduce_kernel (const u64 *__restrict__ recs, const u32 *__restrict__ bkt_
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const u32 lt_mask = (1u << lane) - 1;
 
-  for (;;) {
+  // ticket of the next bucket + the per-bucket words; published by the barrier that ends a round (one barrier serves
+  // both the reuse of the shared arrays and the hand-over)
+  auto next_bucket = [&] () {
     if (tid == 0) s_bucket = atomicAdd (&meta[META_TICKET], 1u);
     if (tid < 2 * W) s_diff[tid] = 0;
     if (tid == 2 * W) s_ndist = 0;
-    __syncthreads ();
+  };
+  const u32 n_buckets = meta[META_NBUCKETS];
+  next_bucket ();
+  __syncthreads ();
+  for (;;) {
     const u32 b = s_bucket;
-    if (b >= meta[META_NBUCKETS]) break;
+    if (b >= n_buckets) break;
     unsigned long long st = bkt_start[b], en = bkt_start[b + 1];
     if (st > capacity) st = capacity;
     if (en > capacity) en = capacity;
     const u32 start = (u32) st, n = (u32) (en - st);
     if (n > BK_CAP) { // reduced by the global multi-pass path (host reads the flag after the first sync)
       if (tid == 0) { bstat[b] = make_uint4 (0, 0, 0, 1); atomicAdd (&meta[META_NOVERSIZE], 1u); }
+      __syncthreads (); // every thread has read s_bucket
+      next_bucket ();
       __syncthreads ();
       continue;
     }
@@ -515,7 +523,7 @@ bucket_reduce_kernel (const u64 *__restrict__ recs, const u32 *__restrict__ bkt_
       const u32 both = blk_excl_scan<BK_THREADS> (((u32) __popc (gmask) << 16) | csum, s_warp, scan_phase, &both_total);
       u32 gpos = both >> 16, cpos = both & 0xffffu;
       n_groups = both_total >> 16; ctotal = both_total & 0xffffu;
-      __syncthreads (); // every S2 read of s_aux is done (it is reused for the group starts)
+      // (s_aux and s_sum, written next, were last read before the barrier that ended the sort / the de-duplication)
 #pragma unroll
       for (int r = 0; r < BK_IPT; r++) {
         const u32 j = j0 + r;
@@ -554,6 +562,7 @@ bucket_reduce_kernel (const u64 *__restrict__ recs, const u32 *__restrict__ bkt_
       out_cnt[start + j] = (v >> 12) & 0xffff;
     }
     if (tid == 0) bstat[b] = make_uint4 (n_dist, n_keep, n_idx, 0);
+    next_bucket ();
     __syncthreads ();
   }
 }
