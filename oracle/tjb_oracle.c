@@ -36,6 +36,8 @@ static void scan_read (const uint8_t *seq, int64_t L, int k, int m, recvec *out,
 {
   int min_len = m < 2 ? 2 : m; /* the length test only happens in the "same as previous" branch (:227-229) */
   int64_t s = 0;
+  tjbo_rec last; /* context[], hopo_base_int and reverse_forward_flag of the last tract emitted for this read (:222) */
+  int have_last = 0;
   while (s < L) {
     int64_t e = s;
     while (e + 1 < L && seq[e + 1] == seq[s]) e++;
@@ -51,6 +53,7 @@ static void scan_read (const uint8_t *seq, int64_t L, int k, int m, recvec *out,
         }
         x.base = f; x.flag = 1;
         push (out, x);
+        last = x; have_last = 1;
       } else if (f > r) { /* G or T/U: reverse complement (:239-246) */
         for (int j = 0; j < k; j++) {
           x.ctx[0] |= (uint64_t) (code_rev (seq[e + k - j]) & 3) << (2 * j);
@@ -58,7 +61,15 @@ static void scan_read (const uint8_t *seq, int64_t L, int k, int m, recvec *out,
         }
         x.base = r; x.flag = 2;
         push (out, x);
-      } else (*skipped)++; /* non-ACGTU run: reference behaviour undefined; fenced */
+        last = x; have_last = 1;
+      } else if (have_last) {
+        /* run of a byte that is none of ACGTU (e.g. NNNN): neither branch is taken and add_kmer_to_hopo_counter() is
+         * called with the variables of the previous tract of this read (:233-248): its context, base and flag, with
+         * the length of THIS run */
+        x = last; x.length = sext (len, 10);
+        push (out, x);
+      } else (*skipped)++; /* no earlier tract in this read: the reference reads an uninitialised context[] and
+                              hopo_base_int (undefined behaviour); fenced: counted and skipped */
     }
     s = e + 1;
   }

@@ -32,8 +32,10 @@ typedef struct {
 typedef struct {
   int status;                /* same codes as ref_dump_t.status / tjb_counter_out.status */
   int64_t n_raw;             /* emitted tract observations */
-  int64_t n_skipped_nonacgt; /* qualifying runs of a non-ACGTU byte: undefined behaviour in the reference
-                                (hopo_counter.c:233-248, neither branch taken), counted and skipped here */
+  int64_t n_skipped_nonacgt; /* qualifying runs of a non-ACGTU byte with NO earlier tract in the same read: the
+                                reference emits uninitialised stack there (hopo_counter.c:222, 233-248), counted and
+                                skipped here.  With an earlier tract the reference re-emits that tract's context,
+                                base and flag with this run's length (well defined): replicated */
   int64_t n_distinct;        /* after the run-length count, before the QC filter */
   int32_t n_elem, n_idx, coverage;
   tjbo_rec *elem;            /* n_elem records in the reference's order */

@@ -1,7 +1,8 @@
 // Segmented run-length reduction of sorted tract observations into per-context tract-length histograms.
 //
-// Replaces steps 1-4 of finalise_hopo_counter() and estimate_coverage_hopo_counter() (reference
-// src/hopo_counter.c:352-413, 420-438), all of which are sequential loops over the sorted element array.
+// Global multi-pass fallback for ONE bucket that does not fit in shared memory (tjb_gpu.cu: reduce_oversize_bucket):
+// steps 1-4 of finalise_hopo_counter() (reference src/hopo_counter.c:352-413), sequential loops over the sorted
+// element array in the reference.
 // Input: records sorted ASCENDING on (base, ctx0, ctx1, length, flag).  All outputs are written back to front,
 // i.e. in the reference's DESCENDING order.
 #pragma once
@@ -10,7 +11,7 @@
 #define RED_THREADS 256
 
 // head[i] = 1 when record i starts a new segment.  MODE 0: (base,ctx0,ctx1,length) changes; MODE 1: (base,ctx0,ctx1)
-// changes; MODE 2 (W = 1, coverage pairs): bits 32..63 change
+// changes
 template <int W, int MODE>
 __global__ void __launch_bounds__ (RED_THREADS) head_kernel (const u64 *__restrict__ a, u32 n, u32 *__restrict__ head)
 {
@@ -20,8 +21,7 @@ __global__ void __launch_bounds__ (RED_THREADS) head_kernel (const u64 *__restri
   if (i) {
     Rec<W> x = load_rec<W> (a, i), y = load_rec<W> (a, i - 1);
     if (MODE == 0) h = !same_tract<W> (x, y);
-    else if (MODE == 1) h = !same_context<W> (x, y);
-    else h = (x.w[0] >> 32) != (y.w[0] >> 32);
+    else h = !same_context<W> (x, y);
   }
   head[i] = h;
 }
@@ -91,55 +91,8 @@ group_emit_kernel (const u32 *__restrict__ gstart, const u32 *__restrict__ gkeep
   idx_final[o] = (int) ((g + 1 < n_groups) ? gstart[g + 1] : n_keep);
 }
 
-// coverage (hopo_counter.c:427-432): two (key, weight) pairs per kept record, key = low 31 bits of each flank
-template <int W>
-__global__ void __launch_bounds__ (RED_THREADS)
-cov_pairs_kernel (const u64 *__restrict__ k_rec, const int *__restrict__ k_count, u32 n_keep, int k, u64 *__restrict__ pairs)
-{
-  u32 i = blockIdx.x * RED_THREADS + threadIdx.x;
-  if (i >= n_keep) return;
-  Rec<W> r = load_rec<W> (k_rec, i);
-  u64 w = (u64) (u32) k_count[i];
-  pairs[i] = ((rec_ctx0<W> (r, k) & 0x7fffffffULL) << 32) | w;
-  pairs[n_keep + i] = ((rec_ctx1<W> (r, k) & 0x7fffffffULL) << 32) | w;
-}
-__global__ void __launch_bounds__ (RED_THREADS) lo32_kernel (const u64 *__restrict__ a, u32 n, u32 *__restrict__ lo)
-{
-  u32 i = blockIdx.x * RED_THREADS + threadIdx.x;
-  if (i < n) lo[i] = (u32) a[i];
-}
 __global__ void __launch_bounds__ (RED_THREADS) icopy_kernel (const int *__restrict__ a, u32 n, u32 *__restrict__ o)
 {
   u32 i = blockIdx.x * RED_THREADS + threadIdx.x;
   if (i < n) o[i] = (u32) a[i];
-}
-// coverage = max over distinct keys of the summed weights (empirical_frequency.c:254-277, hopo_counter.c:434)
-__global__ void __launch_bounds__ (RED_THREADS)
-cov_max_kernel (const u32 *__restrict__ seg_start, u32 n_seg, u32 n, const u32 *__restrict__ wsum, const u32 *__restrict__ wtotal, int *__restrict__ cov)
-{
-  u32 g = blockIdx.x * RED_THREADS + threadIdx.x;
-  if (g >= n_seg) return;
-  u32 hi = (g + 1 < n_seg) ? wsum[seg_start[g + 1]] : *wtotal;
-  int sum = (int) (hi - wsum[seg_start[g]]);
-  atomicMax (cov, sum);
-  (void) n;
-}
-
-// final table -> reference-layout 40-byte hopo_element (src/hopo_counter.h:34-49) as it stands at the BWA boundary
-template <int W>
-__global__ void __launch_bounds__ (RED_THREADS)
-pack_hopo_kernel (const u64 *__restrict__ k_rec, const int *__restrict__ k_count, u32 n_keep, int k, u64 *__restrict__ out40)
-{
-  u32 i = blockIdx.x * RED_THREADS + threadIdx.x;
-  if (i >= n_keep) return;
-  Rec<W> r = load_rec<W> (k_rec, i);
-  // gcc x86-64 bit-field order from the LSB: base:2 length:10 count:20 mismatches:12 multi:3 neg_strand:2 canon_flag:3
-  u64 bits = ((u64) rec_base<W> (r, k) & 3) | (((u64) rec_len_field<W> (r) & 0x3ff) << 2) |
-             (((u64) k_count[i] & 0xfffff) << 12) | (0xffeULL << 32) | (((u64) rec_flag<W> (r) & 7) << 49);
-  u64 *o = out40 + 5 * (size_t) i;
-  o[0] = rec_ctx0<W> (r, k);
-  o[1] = rec_ctx1<W> (r, k);
-  o[2] = bits;
-  o[3] = ~0ULL; // read_offset = -1 (hopo_counter.c:511), loc_ref_id = -1 (:297)
-  o[4] = ~0ULL; // loc_pos = loc_last = -1
 }

@@ -124,3 +124,34 @@ def adversarial_reads(k=25, seed=3, wrap_lengths=False):
     for _ in range(40):
         reads.append(rnd(int(rng.integers(2 * k - 5, 2 * k + 120))))
     return reads
+
+
+def nrun_reads(k=25, seed=17, n_reads=400, p_run=0.03, lead_tract=True):
+    """reads with qualifying runs of bytes that are none of ACGTU ("NNNN", "nnn", "----", "RRRRR") placed AFTER a real
+    tract of the same read: the reference then re-emits that tract's context, base and flag with the run's length
+    (src/hopo_counter.c:233-248; well defined, unlike a run that is the FIRST tract of its read, which emits
+    uninitialised stack).  lead_tract=True starts every read with flank + tract + flank so that no run is first;
+    False leaves first-of-read runs in (only for the restatement / CUDA comparison: they are fenced)."""
+    rng = np.random.default_rng(seed)
+    odd = [b"N", b"n", b"-", b"R", b"*", b"."]
+    fl = (b"GATC" * 8)[:max(k, 2)]
+
+    def body(n):
+        out = bytearray()
+        while len(out) < n:
+            u = rng.random()
+            if u < p_run:
+                out += odd[int(rng.integers(0, len(odd)))] * int(rng.integers(2, 12))
+            elif u < 2.5 * p_run:
+                out += bytes([b"ACGTacgtU"[int(rng.integers(0, 9))]]) * int(rng.integers(2, 12))
+            else:
+                out.append(b"ACGT"[int(rng.integers(0, 4))])
+        return bytes(out)
+    reads = []
+    for i in range(n_reads):
+        lead = b""
+        if lead_tract:
+            base = [c for c in b"ACGT" if c != fl[-1] and c != fl[0]][i % 2]  # must not extend into a flank
+            lead = fl + bytes([base]) * int(rng.integers(6, 10)) + fl
+        reads.append(lead + body(int(rng.integers(2 * k, 2 * k + 400))) + fl)
+    return reads

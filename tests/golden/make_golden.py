@@ -8,6 +8,8 @@ Outputs (small, committed):
   fixture_k{K}_m{M}.npz     BWA-boundary state of the compiled reference on that fixture
   synth_k{K}_m{M}.npz       same on a seeded synthetic sample (tatajuba_b200.synth.sample_buffer(60000, 20, seed=21))
   adversarial_k{K}.npz      same on synth.adversarial_reads(K) x3
+  nrun_k{K}_m{M}.npz        same on synth.nrun_reads(K, seed=17): runs of N / n / - / R ... that FOLLOW a tract of the same read
+                            (the defined half of src/hopo_counter.c:233-248: the previous tract's context is re-emitted)
 """
 import gzip
 import os
@@ -55,6 +57,9 @@ def main():
     for k in (25, 32):
         abuf = b"\n".join(synth.adversarial_reads(k) * 3) + b"\n"
         save(f"adversarial_k{k}.npz", ref.run_buffer(abuf, k, 2, 2, False), k=k, m=2, min_coverage=2, remove_biased=0)
+    for k, m in [(25, 4), (32, 3), (7, 2)]:
+        nbuf = b"\n".join(synth.nrun_reads(k, seed=17)) + b"\n"
+        save(f"nrun_k{k}_m{m}.npz", ref.run_buffer(nbuf, k, m, 1, False), k=k, m=m, min_coverage=1, remove_biased=0)
 
 
 if __name__ == "__main__":

@@ -23,6 +23,8 @@ def golden_input(name):
     if name.startswith("synth"):
         return synth.sample_buffer(60_000, 20, seed=21).tobytes()
     k = int(re.search(r"_k(\d+)", name).group(1))
+    if name.startswith("nrun"):
+        return b"\n".join(synth.nrun_reads(k, seed=17)) + b"\n"
     return b"\n".join(synth.adversarial_reads(k) * 3) + b"\n"
 
 
@@ -36,7 +38,7 @@ GOLDENS = sorted(os.path.basename(p) for p in glob.glob(os.path.join(GOLD, "*.np
 
 
 def test_goldens_exist():
-    assert len(GOLDENS) >= 9
+    assert len(GOLDENS) >= 12
 
 
 @pytest.mark.parametrize("name", GOLDENS)

@@ -79,6 +79,22 @@ def test_gpu_nonacgt_runs_and_separators(ctx, restatement):
     check(ctx, restatement, buf[:-1], 25, 4, 1, False, "no trailing newline")
 
 
+@pytest.mark.parametrize("k,m", [(25, 4), (32, 3), (2, 1), (7, 2), (26, 5)])
+def test_gpu_nonacgt_runs_after_a_tract(ctx, restatement, k, m):
+    """defined half of src/hopo_counter.c:233-248 (re-emission of the previous tract's context with the run's length)
+    and, with lead_tract=False, the fenced half (first tract of a read) mixed in"""
+    for seed, lead in [(0, True), (1, True), (2, False), (3, False)]:
+        buf = b"\n".join(synth.nrun_reads(k, seed, lead_tract=lead)) + b"\n"
+        want = check(ctx, restatement, buf, k, m, 1, False, f"N runs k={k} seed={seed}")
+        assert lead is False or want.n_skipped_nonacgt == 0
+    # a long read: the walk back to the previous tract crosses scan windows
+    rng = np.random.default_rng(5)
+    fl = (b"GATC" * 8)[:max(k, 2)]
+    body = b"".join(bytes(rng.choice(np.frombuffer(b"ACGT", np.uint8), size=int(rng.integers(10, 3000))).tobytes()) + b"N" * int(rng.integers(2, 40))
+                    for _ in range(30))
+    check(ctx, restatement, fl + b"CCCCCC" + fl + body + fl + b"\n", k, m, 1, False, "long read with N runs")
+
+
 def test_gpu_drop_paths(ctx, restatement):
     one = b"GATC" * 8 + b"AAAAA" + b"CTAG" * 8 + b"\n"
     for buf, rb, cov, status in [(b"ACGTACGTAC\nACGT\n\n", True, 5, 1), (b"", True, 5, 1), (one, False, 5, 2),

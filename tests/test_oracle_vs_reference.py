@@ -90,6 +90,24 @@ def test_nonacgt_runs_are_counted_and_skipped(restatement):
     assert skipped == 1 and len(recs) == 1 and recs[0]["length"] == 4
 
 
+@pytest.mark.parametrize("k,m,rb", [(25, 4, False), (32, 3, True), (2, 1, False), (7, 2, False), (13, 5, False), (27, 6, False)])
+def test_nonacgt_runs_after_a_tract_match_reference(restatement, reference, k, m, rb):
+    """the DEFINED half of src/hopo_counter.c:233-248: a qualifying run of a byte that is none of ACGTU which follows a
+    tract of the same read re-emits that tract's context, base and flag with the run's length"""
+    for seed in range(4):
+        buf = b"\n".join(synth.nrun_reads(k, seed)) + b"\n"
+        a = restatement.run_buffer(buf, k, m, 1, rb)
+        b = reference.run_buffer(buf, k, m, 1, rb)
+        assert a.n_skipped_nonacgt == 0
+        pyoracle.assert_same_boundary(a, b, f"N runs k={k} m={m} seed={seed}")
+    fl = b"GATC" * 8
+    buf = fl + b"AAAA" + fl + b"NNNNN" + fl + b"\n" + fl + b"TTTT" + fl + b"NNNN" + fl + b"nnnnnn" + fl + b"CC" + fl + b"---" + fl + b"\n"
+    recs, skipped = restatement.scan_buffer(buf, 25, 4)
+    assert skipped == 0 and [int(x) for x in recs["length"]] == [4, 5, 4, 4, 6]
+    assert recs[1]["ctx0"] == recs[0]["ctx0"] and recs[3]["flag"] == 2 and recs[4]["ctx1"] == recs[2]["ctx1"]
+    pyoracle.assert_same_boundary(restatement.run_buffer(buf, 25, 4, 1, False), reference.run_buffer(buf, 25, 4, 1, False), "hand-made")
+
+
 @pytest.mark.parametrize("seed", range(8))
 def test_restatement_equals_reference_on_arbitrary_bytes(restatement, reference, seed):
     """flanks and run neighbourhoods with every class of byte (lower case, U, IUPAC, punctuation, control bytes, bytes
