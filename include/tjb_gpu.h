@@ -65,6 +65,9 @@ typedef struct {
   int64_t n_skipped_nonacgt; /* qualifying runs of a non-ACGTU byte (undefined behaviour in the reference,
                                 hopo_counter.c:233-248): counted and skipped, see DESIGN.md                 */
   double  ms_decode, ms_device; /* host FASTQ decode wall time; device time (CUDA events) for scan+reduce */
+  int32_t arena;             /* non-zero: elem / idx_initial / idx_final point into the context's result arena
+                                (TJB_RESULT_ARENA): not to be free()d, valid until the context counts its next sample */
+  int32_t reserved;
 } tjb_counter_out;
 
 typedef struct tjb_ctx tjb_ctx; /* one per (host thread, device): stream, pinned double buffers, device workspace */
@@ -88,6 +91,14 @@ void tjb_ctx_destroy (tjb_ctx *ctx);
 /* the context's stream as a cudaStream_t cast to void* (for callers that time with their own events) */
 void *tjb_ctx_stream (tjb_ctx *ctx);
 int  tjb_ctx_set_profiling (tjb_ctx *ctx, int on);
+/* Where the result arrays live.  TJB_RESULT_MALLOC (default): malloc()ed copies owned by the caller, as the reference
+ * needs them (it realloc()s and free()s hc->elem, hopo_counter.c:180-183, 562).  TJB_RESULT_ARENA: pointers into the
+ * context's pinned result arena, which the device writes directly: no host copy, no page faults; the arrays are valid
+ * until this context counts its next sample (callers that only read the boundary state, e.g. to build mapper queries). */
+enum { TJB_RESULT_MALLOC = 0, TJB_RESULT_ARENA = 1 };
+int  tjb_ctx_set_result_mode (tjb_ctx *ctx, int mode);
+/* usable CUDA devices (0 without a driver); the binding deals samples to devices by thread number */
+int  tjb_device_count (void);
 /* returns the number of kernels with at least one launch since the last reset; fills up to max_stats entries */
 int  tjb_ctx_kernel_stats (tjb_ctx *ctx, tjb_kernel_stat *stats, int max_stats);
 void tjb_ctx_reset_kernel_stats (tjb_ctx *ctx);
@@ -118,6 +129,29 @@ int tjb_count_sample (const char *const *files, int n_files, const tjb_opts *opt
 
 void tjb_counter_out_free (tjb_counter_out *out);
 
+/* ---- one sample in pieces (SURVEY.md section 8 e, "by read chunk within a sample"): every GPU scans its share of the
+ * reads into its own aggregation table (distinct (base, contexts, length) -> count per strand); the tables are exported
+ * as rows, exchanged (NCCL allgather, tatajuba_b200/genome_set.py) and imported (counts added per strand, which is what
+ * one scan of all the reads would have counted: + and | are associative); QC, context groups and coverage
+ * (hopo_counter.c:367-438) run once, on the complete table, in tjb_sample_finalise().
+ *   tjb_sample_begin -> tjb_sample_scan_device (any number of chunks) -> [tjb_sample_export -> exchange ->
+ *   tjb_sample_import (the other ranks' rows)] -> tjb_sample_finalise
+ * tjb_count_sample_device() is begin + scan + finalise.  A row is row_words = W + 1 uint64: the W key words of the
+ * internal record layout (csrc/tjb_common.cuh; W = 2 for k <= 26, 3 above) and forward count | reverse count << 32.
+ * TJB_ERR_TOO_LARGE from export / finalise: the table was sized too small for what arrived; begin the sample again
+ * (the next tjb_sample_begin sizes it from what was seen). */
+int tjb_sample_begin (tjb_ctx *ctx, const tjb_opts *opt, size_t n_bytes_hint);
+/* distinct observations the table of the current sample can take, and a way to size the NEXT tjb_sample_begin for a
+ * known number (ranks agree on the sum of their exported rows before they import, so that none of them overflows) */
+int64_t tjb_ctx_table_capacity (const tjb_ctx *ctx);
+int tjb_ctx_reserve_entries (tjb_ctx *ctx, int64_t n_entries);
+int tjb_sample_scan_device (tjb_ctx *ctx, const void *d_seqs, size_t n_bytes);
+/* table -> rows (once per sample; synchronous).  d_rows = NULL: only *n_rows and *row_words are returned, so that the
+ * caller can size its device buffer; otherwise up to max_rows rows are copied to d_rows (device memory). */
+int tjb_sample_export (tjb_ctx *ctx, void *d_rows, int64_t max_rows, int64_t *n_rows, int32_t *row_words);
+int tjb_sample_import (tjb_ctx *ctx, const void *d_rows, int64_t n_rows);
+int tjb_sample_finalise (tjb_ctx *ctx, tjb_counter_out *out);
+
 /* ---- cross-sample exchange (SURVEY.md section 8 e): the step between finalise_hopo_counter() steps 0-4 and the
  * mapper call.  The reference builds one mapper query per indexed context group from the group's first = longest
  * record (src/hopo_counter.c:513-520) and maps every sample separately (src/genome_set.c:75, 90).  A "query row"
@@ -127,6 +161,9 @@ void tjb_counter_out_free (tjb_counter_out *out);
  * union, so that each distinct query is mapped once and the result scattered back to every sample's groups. */
 /* rows: 3 * in->n_idx uint64 (host).  Returns n_idx or a negative error. */
 int tjb_query_rows (const tjb_counter_out *in, uint64_t *rows);
+/* the same rows for the sample this context counted LAST, written on the device from the device-resident result
+ * (d_rows: device buffer of 3 * max_rows uint64); nothing crosses PCIe.  Returns n_idx (0 for a dropped sample). */
+int tjb_query_rows_device (tjb_ctx *ctx, void *d_rows, int64_t max_rows);
 /* d_rows: 3 * n_rows uint64 in DEVICE memory; d_union: device buffer of 3 * n_rows uint64 (the first 3 * *n_union
  * are written); d_index: device int32[n_rows] or NULL.  Synchronous. */
 int tjb_union_queries_device (tjb_ctx *ctx, const void *d_rows, int64_t n_rows, int kmer_size, void *d_union,

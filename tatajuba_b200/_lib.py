@@ -16,7 +16,9 @@ EXPORTS = [
     "tjb_version", "tjb_strerror", "tjb_ctx_last_error", "tjb_ctx_create", "tjb_ctx_destroy", "tjb_ctx_stream",
     "tjb_ctx_set_profiling", "tjb_ctx_kernel_stats", "tjb_ctx_reset_kernel_stats", "tjb_ctx_launch_count", "tjb_ctx_htod_bytes",
     "tjb_count_sample_files", "tjb_count_sample_host", "tjb_count_sample_device", "tjb_count_sample",
-    "tjb_counter_out_free", "tjb_query_rows", "tjb_union_queries_device", "tjb_merge_tracts", "tjb_reader_open", "tjb_reader_fill", "tjb_reader_close",
+    "tjb_counter_out_free", "tjb_ctx_set_result_mode", "tjb_device_count", "tjb_sample_begin", "tjb_sample_scan_device",
+    "tjb_ctx_table_capacity", "tjb_ctx_reserve_entries",
+    "tjb_sample_export", "tjb_sample_import", "tjb_sample_finalise", "tjb_query_rows_device", "tjb_query_rows", "tjb_union_queries_device", "tjb_merge_tracts", "tjb_reader_open", "tjb_reader_fill", "tjb_reader_close",
 ]
 
 
@@ -30,7 +32,7 @@ class TjbCounterOut(C.Structure):
                 ("elem", C.c_void_p), ("idx_initial", C.POINTER(C.c_int32)), ("idx_final", C.POINTER(C.c_int32)),
                 ("name", C.c_char_p), ("n_reads", C.c_int64), ("n_bases", C.c_int64), ("n_raw", C.c_int64),
                 ("n_distinct", C.c_int64), ("n_skipped_nonacgt", C.c_int64), ("ms_decode", C.c_double),
-                ("ms_device", C.c_double)]
+                ("ms_device", C.c_double), ("arena", C.c_int32), ("reserved", C.c_int32)]
 
 
 class TjbKernelStat(C.Structure):
@@ -81,6 +83,16 @@ def load():
     lib.tjb_count_sample.argtypes = [C.POINTER(cp), i32, po, i32, pout]
     lib.tjb_counter_out_free.argtypes = [pout]
     lib.tjb_counter_out_free.restype = None
+    lib.tjb_ctx_set_result_mode.argtypes = [vp, i32]
+    lib.tjb_sample_begin.argtypes = [vp, po, sz]
+    lib.tjb_ctx_table_capacity.restype = i64
+    lib.tjb_ctx_table_capacity.argtypes = [vp]
+    lib.tjb_ctx_reserve_entries.argtypes = [vp, i64]
+    lib.tjb_sample_scan_device.argtypes = [vp, vp, sz]
+    lib.tjb_sample_export.argtypes = [vp, vp, i64, C.POINTER(i64), C.POINTER(C.c_int32)]
+    lib.tjb_sample_import.argtypes = [vp, vp, i64]
+    lib.tjb_sample_finalise.argtypes = [vp, pout]
+    lib.tjb_query_rows_device.argtypes = [vp, vp, i64]
     lib.tjb_query_rows.argtypes = [pout, vp]
     lib.tjb_union_queries_device.argtypes = [vp, vp, i64, i32, vp, C.POINTER(i64), vp]
     lib.tjb_merge_tracts.argtypes = [i32, vp, vp, vp, vp, vp, i32, i32, vp, vp, vp]

@@ -1,25 +1,28 @@
-// Bucketed sort + segmented run-length reduction of tract observations (the main reduce path).
+// Bucketed sort + reduction of the DISTINCT tract observations (the reduce path after the aggregation table).
 //
 // Replaces qsort + the sequential loops of finalise_hopo_counter() and estimate_coverage_hopo_counter()
-// (reference src/hopo_counter.c:351-413, 420-438).  Instead of ~14 full-array LSD passes over the 112..138-bit
-// keys, the records are moved ONCE (an MSD partition on the top F bits of (base, ctx0), F <= 16, with splitters
-// chosen from the histogram the scan kernel accumulates), and every bucket (<= BK_CAP records, sized to stay in
-// shared memory) is then sorted on chip by an LSD radix sort over the remaining digits and reduced in the same
-// CTA: run-length count (:352-365), strand-bias / singleton QC (:367-374) and the context groups above the
-// minimum coverage (:388-404).  A context (base, ctx0, ctx1) never straddles two buckets because the partition
-// looks at context bits only.  Everything is produced in the reference's DESCENDING order.
+// (reference src/hopo_counter.c:351-413, 420-438).  The run-length count of :352-365 has already happened in the
+// aggregation table the scan fills (tjb_table.cuh); what arrives here are weighted records: key (base, ctx0, ctx1,
+// length) + count word (forward | reverse << 32).  They are moved ONCE (an MSD partition on the top F bits of
+// (base, ctx0[, ctx1]), F <= 20, splitters chosen from the histogram the scan accumulates when it creates a table
+// entry), and every bucket (<= BK_CAP records, sized to stay in shared memory) is sorted on chip (comparison counting
+// for <= 128 records, LSD radix over the digits that differ otherwise) and reduced in the same CTA: weights of equal
+// keys added (a key can arrive in several records, see tjb_table.cuh), strand-bias / singleton QC (:367-374) and the
+// context groups above the minimum coverage (:388-404).  A context (base, ctx0, ctx1) never straddles two buckets
+// because the partition looks at context bits only.  Everything is produced in the reference's DESCENDING order.
 //
-//   plan_kernel          1 CTA     bin histogram -> splitters (buckets of < BK_CAP records), bin -> bucket LUT
-//   partition_kernel     grid      rec_a -> rec_b, bucket-contiguous (order inside a bucket is irrelevant)
-//   bucket_reduce_kernel grid      per bucket: smem LSD sort + RLE + QC + groups; compact output at the bucket start
-//   totals_kernel        1 CTA     exclusive scans of the per-bucket kept / group counts
-//   pack_kernel          grid      the 24 varying bytes of every reference-layout hopo_element + idx arrays + coverage hash inserts
-//   cov_max_kernel       grid      coverage = max over the hash table
+//   plan_kernel           1 CTA     bin histogram -> splitters (buckets of < BK_CAP records), bin -> bucket LUT
+//   wpartition_kernel     grid      table entries + overflow list -> weighted records, bucket-contiguous
+//   wbucket_reduce_kernel grid      per bucket: smem sort + merge + QC + groups; compact output at the bucket start
+//   totals_kernel         1 CTA     exclusive scans of the per-bucket kept / group counts
+//   pack_kernel           grid      reference-layout 40-byte hopo_element rows + idx arrays + coverage hash inserts
+//   cov_max_kernel        grid      coverage = max over the hash table
 //
-// Buckets with more than BK_CAP records (one bin holding > BK_CAP/2 observations: very short k or a pathological
-// sample) are flagged and reduced by the multi-pass global path in tjb_sort.cuh / tjb_reduce.cuh instead.
+// Buckets with more than BK_CAP records (one bin holding > BK_CAP/2 distinct observations: pathological samples) are
+// flagged and reduced by the multi-pass global path in tjb_sort.cuh / tjb_reduce.cuh instead.
 #pragma once
 #include "tjb_common.cuh"
+#include "tjb_table.cuh"
 
 #define BK_THREADS 256
 #define BK_WARPS (BK_THREADS / 32)
@@ -88,19 +91,6 @@ __device__ __forceinline__ u32 blk_excl_scan (u32 v, u32 *s_warp /*[2 * NT / 32]
   return before + inc - v;
 }
 
-// ------------------------------------------------------------------------------- histogram (fallback) ----
-// the scan kernel accumulates the bin histogram itself; this kernel rebuilds it from the records after a
-// record-array overflow forced a chunk to be re-scanned
-template <int W>
-__global__ void __launch_bounds__ (256)
-rec_hist_kernel (const u64 *__restrict__ recs, const unsigned long long *__restrict__ counters, unsigned long long capacity, int k, int F,
-                 u32 *__restrict__ bin_hist)
-{
-  unsigned long long n = counters[0] < capacity ? counters[0] : capacity;
-  for (size_t i = (size_t) blockIdx.x * 256 + threadIdx.x; i < n; i += (size_t) gridDim.x * 256)
-    atomicAdd (&bin_hist[rec_bin<W> (load_rec<W> (recs, i), k, F)], 1u);
-}
-
 // ------------------------------------------------------------------------------------------- plan --------
 // Bins are walked from the highest to the lowest (descending key order).  P[j] = number of records in bins before
 // j in that order; bins whose P falls into the same window of BK_CAPH records form one bucket, so a bucket holds
@@ -109,7 +99,7 @@ rec_hist_kernel (const u64 *__restrict__ recs, const unsigned long long *__restr
 // kernel is in flight at once (the first version walked them with dependent scalar loads: 195 us for 32 Ki bins).
 template <int IPT>
 __global__ void __launch_bounds__ (PLAN_THREADS)
-plan_kernel (const u32 *__restrict__ bin_hist, int F, const unsigned long long *__restrict__ counters, unsigned long long capacity,
+plan_kernel (const u32 *__restrict__ bin_hist, int F, unsigned long long capacity,
              u32 *__restrict__ bkt_start, u32 *__restrict__ lut, u32 *__restrict__ cursor, u32 *__restrict__ meta, u32 max_buckets)
 {
   __shared__ u32 s_warp[2 * (PLAN_THREADS / 32)];
@@ -178,8 +168,7 @@ plan_kernel (const u32 *__restrict__ bin_hist, int F, const unsigned long long *
     meta[META_NBUCKETS] = nb_total;
     meta[META_NOVERSIZE] = 0;
     meta[META_TICKET] = 0;
-    unsigned long long n = counters[0] < capacity ? counters[0] : capacity;
-    meta[META_N] = (u32) n;
+    meta[META_N] = (u32) (total < capacity ? total : capacity); // weighted records (more than the capacity: the sample is redone)
   }
 }
 
@@ -187,7 +176,7 @@ plan_kernel (const u32 *__restrict__ bin_hist, int F, const unsigned long long *
 // samples, where 2^16 bins would hold more than BK_CAPH records each): every thread walks its 2^F / 1024 bins three
 // times from L2 (sum, count heads, emit) instead of keeping them in registers.
 __global__ void __launch_bounds__ (PLAN_THREADS)
-plan_big_kernel (const u32 *__restrict__ bin_hist, int F, const unsigned long long *__restrict__ counters, unsigned long long capacity,
+plan_big_kernel (const u32 *__restrict__ bin_hist, int F, unsigned long long capacity,
                  u32 *__restrict__ bkt_start, u32 *__restrict__ lut, u32 *__restrict__ cursor, u32 *__restrict__ meta, u32 max_buckets)
 {
   __shared__ u32 s_warp[2 * (PLAN_THREADS / 32)];
@@ -237,39 +226,58 @@ plan_big_kernel (const u32 *__restrict__ bin_hist, int F, const unsigned long lo
     meta[META_NBUCKETS] = nb_total;
     meta[META_NOVERSIZE] = 0;
     meta[META_TICKET] = 0;
-    unsigned long long n = counters[0] < capacity ? counters[0] : capacity;
-    meta[META_N] = (u32) n;
+    meta[META_N] = (u32) (total < capacity ? total : capacity); // weighted records (more than the capacity: the sample is redone)
   }
 }
 
 // --------------------------------------------------------------------------------------- partition -------
+// Walks the aggregation table (and the overflow list) and moves every entry to its bucket as a weighted record.
+// Also sums the weights: the number of tract observations of the sample (hc->n_elem before finalise_hopo_counter).
 template <int W>
 __global__ void __launch_bounds__ (256)
-partition_kernel (const u64 *__restrict__ in, u64 *__restrict__ out, const unsigned long long *__restrict__ counters,
-                  unsigned long long capacity, int k, int F, const u32 *__restrict__ lut, u32 *__restrict__ cursor)
+wpartition_kernel (AggTable tab, const u64 *__restrict__ ovf, unsigned long long *__restrict__ counters, unsigned long long ovf_capacity,
+                   int k, int F, const u32 *__restrict__ lut, u32 *__restrict__ cursor, u64 *__restrict__ wkey,
+                   unsigned long long *__restrict__ wcnt, unsigned long long list_cap)
 {
-  const unsigned long long n = counters[0] < capacity ? counters[0] : capacity;
-  const size_t stride = (size_t) gridDim.x * 256;
-  for (size_t i0 = (size_t) blockIdx.x * 256 + threadIdx.x; i0 < n; i0 += PART_UNROLL * stride) {
-    Rec<W> r[PART_UNROLL];
-    u32 pos[PART_UNROLL];
+  const size_t stride = (size_t) gridDim.x * 256, n_slots = (size_t) tab.mask + 1;
+  unsigned long long n_obs = 0;
+  for (size_t s0 = (size_t) blockIdx.x * 256 + threadIdx.x; s0 < n_slots; s0 += PART_UNROLL * stride) {
+    unsigned long long c[PART_UNROLL];
 #pragma unroll
-    for (int u = 0; u < PART_UNROLL; u++) { size_t i = i0 + u * stride; if (i < n) r[u] = load_rec<W> (in, i); }
+    for (int u = 0; u < PART_UNROLL; u++) { const size_t sl = s0 + u * stride; c[u] = sl < n_slots ? tab.cnt[sl] : 0ULL; }
 #pragma unroll
-    for (int u = 0; u < PART_UNROLL; u++) { size_t i = i0 + u * stride; if (i < n) pos[u] = atomicAdd (&cursor[(size_t) lut[rec_bin<W> (r[u], k, F)] * BK_CURSOR_STRIDE], 1u); }
-#pragma unroll
-    for (int u = 0; u < PART_UNROLL; u++) { size_t i = i0 + u * stride; if (i < n && pos[u] < capacity) store_rec<W> (out, pos[u], r[u]); }
+    for (int u = 0; u < PART_UNROLL; u++) {
+      if (!c[u]) continue;
+      const Rec<W> key = table_key_at<W> (tab, (u32) (s0 + u * stride));
+      const u32 pos = atomicAdd (&cursor[(size_t) lut[rec_bin<W> (key, k, F)] * BK_CURSOR_STRIDE], 1u);
+      if (pos < list_cap) { store_rec<W> (wkey, pos, key); wcnt[pos] = c[u]; }
+      n_obs += (u32) c[u] + ((u32) (c[u] >> 32) & 0x7fffffffu);
+    }
   }
+  const unsigned long long n_ovf = counters[CTR_OVERFLOW] < ovf_capacity ? counters[CTR_OVERFLOW] : ovf_capacity;
+  for (size_t i = (size_t) blockIdx.x * 256 + threadIdx.x; i < n_ovf; i += stride) {
+    Rec<W> r = load_rec<W> (ovf, i);
+    const unsigned long long c = flag_weight (r.w[0]);
+    r.w[0] &= ~3ULL;
+    const u32 pos = atomicAdd (&cursor[(size_t) lut[rec_bin<W> (r, k, F)] * BK_CURSOR_STRIDE], 1u);
+    if (pos < list_cap) { store_rec<W> (wkey, pos, r); wcnt[pos] = c; }
+    n_obs++;
+  }
+#pragma unroll
+  for (int d = 16; d; d >>= 1) n_obs += __shfl_xor_sync (0xffffffffu, n_obs, d);
+  if ((threadIdx.x & 31) == 0 && n_obs) atomicAdd (&counters[CTR_NRAW], n_obs);
 }
 
 // ---------------------------------------------------------------------------------- bucket reduce --------
-template <int W> constexpr size_t bucket_smem_bytes ()
+template <int W> constexpr size_t wbucket_smem_bytes ()
 {
   return (size_t) W * BK_CAP * 8 /* s_w */ + 2 * BK_CAP * 2 /* perm */ + BK_WARPS * 256 * 2 /* counts */ + BK_CAP * 2 /* aux */ +
-         BK_CAP * 4 /* val */ + BK_CAP * 4 /* sum */ + BK_CAP * 4 /* per-record strand counts */;
+         BK_CAP * 4 /* val */ + BK_CAP * 4 /* kept counts */ + BK_CAP * 4 /* sum */;
 }
-#define BK_EMPTY 0xffffffffu
-#define BK_RANKSORT_MAX 128 // up to this many distinct keys a bucket is ordered by comparison counting instead of radix passes
+#define BK_RANKSORT_MAX 128 // up to this many records a bucket is ordered by comparison counting instead of radix passes
+enum { QC_SEEN_TWICE = 0,   // "-b": keep count > 1                 (hopo_counter.c:371-373)
+       QC_BOTH_STRANDS = 1, // default: keep canon_flag == 3        (:368-370)
+       QC_KEEP_ALL = 2 };   // union of mapper queries (tjb_union.cuh): nothing is filtered
 
 // a > b in the reference's order (base, ctx0, ctx1, length), hopo_counter.c:28-38; the flag bits do not take part
 template <int W> __device__ __forceinline__ bool rec_greater (const Rec<W> &a, const Rec<W> &b);
@@ -286,27 +294,25 @@ template <> __device__ __forceinline__ bool rec_greater<3> (const Rec<3> &a, con
 
 template <int W>
 __global__ void __launch_bounds__ (BK_THREADS, W == 2 ? BK_CTAS2 : 2)
-bucket_reduce_kernel (const u64 *__restrict__ recs, const u32 *__restrict__ bkt_start, u32 *__restrict__ meta, unsigned long long capacity,
-                      DigitList dl, int remove_biased, int min_coverage, u64 *__restrict__ out_rec, u32 *__restrict__ out_cnt,
-                      u32 *__restrict__ out_idx_i, u32 *__restrict__ out_idx_f, uint4 *__restrict__ bstat)
+wbucket_reduce_kernel (const u64 *__restrict__ wkey, const unsigned long long *__restrict__ wcnt, const u32 *__restrict__ bkt_start,
+                       u32 *__restrict__ meta, unsigned long long capacity, DigitList dl, int qc_mode, int min_coverage,
+                       u64 *__restrict__ out_rec, u32 *__restrict__ out_cnt, u32 *__restrict__ out_idx_i, u32 *__restrict__ out_idx_f,
+                       uint4 *__restrict__ bstat)
 {
   extern __shared__ __align__ (16) unsigned char smem[];
   u64 *s_w = reinterpret_cast<u64*> (smem);                                  // [W][BK_CAP]
   const u32 *s_w32 = reinterpret_cast<const u32*> (smem);
   unsigned short *s_perm0 = reinterpret_cast<unsigned short*> (s_w + W * BK_CAP);
   unsigned short *s_perm1 = s_perm0 + BK_CAP;
-  unsigned short *s_cnt = s_perm1 + BK_CAP;                                  // [BK_WARPS][256]
+  unsigned short *s_cnt = s_perm1 + BK_CAP;                                  // [BK_WARPS][256] radix counters
   unsigned short *s_aux = s_cnt + BK_WARPS * 256;                            // [BK_CAP]
-  u32 *s_val = reinterpret_cast<u32*> (s_aux + BK_CAP);                      // [BK_CAP]
-  u32 *s_sum = s_val + BK_CAP;                                               // [BK_CAP]
-  u32 *s_tab = s_val;                                                        // [2 * BK_CAP] de-duplication hash table; dead before
-                                                                             // s_val / s_sum are first written
-  u32 *s_cntrec = s_sum + BK_CAP;                                            // [BK_CAP] fwd count | rev count << 16 of a representative
+  u32 *s_val = reinterpret_cast<u32*> (s_aux + BK_CAP);                      // [BK_CAP] kept j -> descending position | flag << 28
+  u32 *s_kcnt = s_val + BK_CAP;                                              // [BK_CAP] kept j -> count (signed 20-bit field value)
+  u32 *s_sum = s_kcnt + BK_CAP;                                              // [BK_CAP] exclusive prefix sums of the kept counts
   __shared__ u32 s_warp[2 * BK_WARPS];
   int scan_phase = 0;
   __shared__ u32 s_bucket;
   __shared__ u32 s_diff[2 * W];
-  __shared__ u32 s_ndist;
 
   const int tid = threadIdx.x, lane = tid & 31, wid = tid >> 5;
   const u32 lt_mask = (1u << lane) - 1;
@@ -316,7 +322,6 @@ bucket_reduce_kernel (const u64 *__restrict__ recs, const u32 *__restrict__ bkt_
   auto next_bucket = [&] () {
     if (tid == 0) s_bucket = atomicAdd (&meta[META_TICKET], 1u);
     if (tid < 2 * W) s_diff[tid] = 0;
-    if (tid == 2 * W) s_ndist = 0;
   };
   const u32 n_buckets = meta[META_NBUCKETS];
   next_bucket ();
@@ -328,29 +333,25 @@ bucket_reduce_kernel (const u64 *__restrict__ recs, const u32 *__restrict__ bkt_
     if (st > capacity) st = capacity;
     if (en > capacity) en = capacity;
     const u32 start = (u32) st, n = (u32) (en - st);
-    if (n > BK_CAP) { // reduced by the global multi-pass path (host reads the flag after the first sync)
+    if (n > BK_CAP) { // reduced by the global multi-pass path (host reads the flag after the synchronisation)
       if (tid == 0) { bstat[b] = make_uint4 (0, 0, 0, 1); atomicAdd (&meta[META_NOVERSIZE], 1u); }
       __syncthreads (); // every thread has read s_bucket
       next_bucket ();
       __syncthreads ();
       continue;
     }
-    const u32 tsize = n <= 32 ? 64u : 1u << (32 - __clz (2 * n - 1)); // hash table: power of two >= max(64, 2 n)
     // ---- load the bucket; remember which key bits differ at all ------------------------------------------
     {
       u64 d[W];
 #pragma unroll
       for (int j = 0; j < W; j++) d[j] = 0;
       Rec<W> f;
-      if (n) f = load_rec<W> (recs, start);
-      // (the hash table and the per-record counters of the de-duplication below are cleared here, under the latency of
-      // the loads; their arrays were last read before the barrier that ended the previous bucket)
-      for (u32 i = tid; i < tsize; i += BK_THREADS) s_tab[i] = BK_EMPTY;
-      for (u32 i = tid; i < n; i += BK_THREADS) s_cntrec[i] = 0;
+      if (n) f = load_rec<W> (wkey, start);
       for (u32 i = tid; i < n; i += BK_THREADS) {
-        Rec<W> r = load_rec<W> (recs, (size_t) start + i);
+        Rec<W> r = load_rec<W> (wkey, (size_t) start + i);
 #pragma unroll
         for (int j = 0; j < W; j++) { s_w[j * BK_CAP + i] = r.w[j]; d[j] |= r.w[j] ^ f.w[j]; }
+        s_perm0[i] = (unsigned short) i;
       }
 #pragma unroll
       for (int j = 0; j < W; j++) {
@@ -359,69 +360,29 @@ bucket_reduce_kernel (const u64 *__restrict__ recs, const u32 *__restrict__ bkt_
       }
     }
     __syncthreads ();
-    // ---- de-duplication: at sequencing depth D every (base, ctx0, ctx1, length) shows up ~D times, so count the copies
-    // in a shared-memory hash table first (run-length count of hopo_counter.c:355-365 without the sort) and sort only
-    // the distinct observations.  Table entry = index of the first record seen with that key (its representative);
-    // s_cntrec[representative] = forward-strand copies | reverse-strand copies << 16 (canon_flag = which are non-zero, :362)
-    // the record that claims a table slot is the representative of its key and appends itself to s_perm0 (one
-    // shared-memory atomic per warp and round; the order is arbitrary, the keys are distinct and get sorted below)
-    for (u32 i0 = 0; i0 < n; i0 += BK_THREADS) {
-      const u32 i = i0 + tid;
-      bool is_new = false;
-      if (i < n) {
-      Rec<W> x;
-#pragma unroll
-      for (int j = 0; j < W; j++) x.w[j] = s_w[j * BK_CAP + i];
-      u32 h = (u32) (x.w[0] >> 2) * 0x9E3779B1u ^ (u32) (x.w[0] >> 34) * 0x85EBCA6Bu ^ (u32) x.w[1] * 0xC2B2AE35u ^ (u32) (x.w[1] >> 32) * 0x27D4EB2Fu;
-      if (W == 3) h ^= (u32) x.w[W - 1] * 0x165667B1u ^ (u32) (x.w[W - 1] >> 32) * 0x9E3779B1u;
-      h ^= h >> 15; h *= 0x2C1B3C6Du; h ^= h >> 13;
-      u32 slot = h & (tsize - 1), rep;
-      for (;;) {
-        u32 c = s_tab[slot];
-        if (c == BK_EMPTY) { c = atomicCAS (&s_tab[slot], BK_EMPTY, i); if (c == BK_EMPTY) { rep = i; break; } }
-        Rec<W> y;
-#pragma unroll
-        for (int j = 0; j < W; j++) y.w[j] = s_w[j * BK_CAP + c];
-        if (same_tract<W> (x, y)) { rep = c; break; }
-        slot = (slot + 1) & (tsize - 1);
-      }
-      atomicAdd (&s_cntrec[rep], (x.w[0] & 1) ? 1u : 0x10000u); // flag 1 = forward, 2 = reverse complement
-      is_new = rep == i;
-      }
-      const u32 nb = __ballot_sync (0xffffffffu, is_new);
-      if (nb) {
-        u32 base = 0;
-        if (lane == 0) base = atomicAdd (&s_ndist, (u32) __popc (nb));
-        base = __shfl_sync (0xffffffffu, base, 0);
-        if (is_new) s_perm0[base + __popc (nb & lt_mask)] = (unsigned short) i;
-      }
-    }
-    __syncthreads ();
-    const u32 n_dist = s_ndist;
-    // ---- sort the distinct observations, ascending in `cur` ------------------------------------------------------
+    // ---- sort the records, ascending in `cur` (equal keys end up next to each other) ---------------------------
     unsigned short *cur = s_perm0, *nxt = s_perm1;
-    if (n_dist <= BK_RANKSORT_MAX) {
-      // few keys (the usual case at high depth): rank by comparison, one key per thread, broadcast reads
-      if ((u32) tid < n_dist) {
-        const u32 id = cur[tid];
+    if (n <= BK_RANKSORT_MAX) {
+      // few records (the usual case at high depth): rank by comparison, one record per thread, broadcast reads; equal
+      // keys are ranked by their index
+      if ((u32) tid < n) {
         Rec<W> x;
 #pragma unroll
-        for (int j = 0; j < W; j++) x.w[j] = s_w[j * BK_CAP + id];
+        for (int j = 0; j < W; j++) x.w[j] = s_w[j * BK_CAP + tid];
         u32 less = 0;
-        for (u32 o = 0; o < n_dist; o++) {
-          const u32 oid = cur[o];
+        for (u32 o = 0; o < n; o++) {
           Rec<W> y;
 #pragma unroll
-          for (int j = 0; j < W; j++) y.w[j] = s_w[j * BK_CAP + oid];
-          less += rec_greater<W> (x, y);
+          for (int j = 0; j < W; j++) y.w[j] = s_w[j * BK_CAP + o];
+          less += rec_greater<W> (x, y) || (o < (u32) tid && same_tract<W> (x, y));
         }
-        nxt[less] = (unsigned short) id;
+        nxt[less] = (unsigned short) tid;
       }
       __syncthreads ();
       unsigned short *t = cur; cur = nxt; nxt = t;
     } else {
       // LSD radix sort of the index permutation; digits on which the whole bucket agrees are skipped
-      const u32 ipt = (n_dist + BK_THREADS - 1) / BK_THREADS; // items per thread in a pass
+      const u32 ipt = (n + BK_THREADS - 1) / BK_THREADS; // items per thread in a pass
       for (int q = 0; q < dl.n; q++) {
         const int word = dl.word[q], shift = dl.shift[q];
         const u32 mask = (1u << dl.nbits[q]) - 1;
@@ -433,13 +394,13 @@ bucket_reduce_kernel (const u64 *__restrict__ recs, const u32 *__restrict__ bkt_
         for (u32 r = 0; r < ipt; r++) { // warp w owns items [w * 32 * ipt, (w + 1) * 32 * ipt): stable
           const u32 i = (u32) wid * (32 * ipt) + r * 32 + lane;
           u32 d = 256;
-          if (i < n_dist) d = (s_w32[2 * ((size_t) word * BK_CAP + cur[i]) + half] >> sh) & mask;
+          if (i < n) d = (s_w32[2 * ((size_t) word * BK_CAP + cur[i]) + half] >> sh) & mask;
           const u32 peers = __match_any_sync (0xffffffffu, d);
           const int leader = __ffs (peers) - 1;
           u32 old = 0;
           if (lane == leader && d < 256) { old = s_cnt[wid * 256 + d]; s_cnt[wid * 256 + d] = (unsigned short) (old + __popc (peers)); }
           old = __shfl_sync (0xffffffffu, old, leader);
-          if (i < n_dist) s_aux[i] = (unsigned short) (old + __popc (peers & lt_mask)); // rank among the warp's equal digits
+          if (i < n) s_aux[i] = (unsigned short) (old + __popc (peers & lt_mask)); // rank among the warp's equal digits
           __syncwarp ();
         }
         __syncthreads ();
@@ -456,7 +417,7 @@ bucket_reduce_kernel (const u64 *__restrict__ recs, const u32 *__restrict__ bkt_
 #pragma unroll 1
         for (u32 r = 0; r < ipt; r++) {
           const u32 i = (u32) wid * (32 * ipt) + r * 32 + lane;
-          if (i < n_dist) {
+          if (i < n) {
             const u32 id = cur[i], d = (s_w32[2 * ((size_t) word * BK_CAP + id) + half] >> sh) & mask;
             nxt[s_cnt[wid * 256 + d] + s_aux[i]] = (unsigned short) id;
           }
@@ -465,8 +426,8 @@ bucket_reduce_kernel (const u64 *__restrict__ recs, const u32 *__restrict__ bkt_
         unsigned short *t = cur; cur = nxt; nxt = t;
       }
     }
-    // distinct record at DESCENDING position p
-    auto id_at = [&] (u32 p) -> u32 { return cur[n_dist - 1 - p]; };
+    // record at DESCENDING position p
+    auto id_at = [&] (u32 p) -> u32 { return cur[n - 1 - p]; };
     auto rec_at = [&] (u32 p) {
       const u32 id = id_at (p);
       Rec<W> r;
@@ -474,26 +435,45 @@ bucket_reduce_kernel (const u64 *__restrict__ recs, const u32 *__restrict__ bkt_
       for (int j = 0; j < W; j++) r.w[j] = s_w[j * BK_CAP + id];
       return r;
     };
-    u32 n_keep, n_groups, n_idx, ctotal;
-    // ---- S2: count, canon_flag, QC filter (hopo_counter.c:361-362, 367-374) ----------------------------------
+    u32 n_dist, n_keep, n_groups, n_idx, ctotal;
+    // ---- S2: weights of equal keys added, count, canon_flag, QC filter (hopo_counter.c:355-374) -----------------
     {
-      const u32 d0 = tid * BK_IPT;
-      u32 kmask = 0, packed[BK_IPT];
+      const u32 p0 = tid * BK_IPT;
+      unsigned long long cw[BK_IPT];
 #pragma unroll
-      for (int r = 0; r < BK_IPT; r++) {
-        const u32 d = d0 + r;
-        if (d < n_dist) {
-          const u32 c = s_cntrec[id_at (d)];
-          const u32 cnt = (c & 0xffff) + (c >> 16); // <= BK_CAP: the 20-bit signed count field cannot wrap here
-          const u32 flag = ((c & 0xffff) ? 1u : 0u) | ((c >> 16) ? 2u : 0u);
-          const bool keep = remove_biased ? (flag == 3) : (cnt > 1);
-          if (keep) kmask |= 1u << r;
-          packed[r] = d | (cnt << 12) | (flag << 28);
+      for (int r = 0; r < BK_IPT; r++) cw[r] = p0 + r < n ? wcnt[(size_t) start + id_at (p0 + r)] : 0ULL; // all loads in flight
+      u32 hmask = 0, kmask = 0, packed[BK_IPT], kc[BK_IPT];
+      if (p0 < n) {
+        Rec<W> prev;
+        if (p0) prev = rec_at (p0 - 1);
+#pragma unroll
+        for (int r = 0; r < BK_IPT; r++) {
+          const u32 p = p0 + r;
+          if (p < n) {
+            const Rec<W> x = rec_at (p);
+            if (p == 0 || !same_tract<W> (x, prev)) { // first record of its key: add the weights of the rest of the run
+              u32 cf = (u32) cw[r], cr = (u32) (cw[r] >> 32) & 0x7fffffffu;
+              for (u32 q = p + 1; q < n && same_tract<W> (rec_at (q), x); q++) {
+                const unsigned long long c = wcnt[(size_t) start + id_at (q)];
+                cf += (u32) c; cr += (u32) (c >> 32) & 0x7fffffffu;
+              }
+              const int cnt = sext_field ((long long) cf + (long long) cr, 20); // the reference's count:20 signed bit-field
+              const u32 flag = (cf ? 1u : 0u) | (cr ? 2u : 0u);
+              const bool keep = qc_mode == QC_BOTH_STRANDS ? flag == 3 : (qc_mode == QC_SEEN_TWICE ? cnt > 1 : true);
+              hmask |= 1u << r;
+              if (keep) { kmask |= 1u << r; packed[r] = p | (flag << 28); kc[r] = (u32) cnt; }
+            }
+            prev = x;
+          }
         }
       }
-      u32 kpos = blk_excl_scan<BK_THREADS> (__popc (kmask), s_warp, scan_phase, &n_keep);
+      static_assert (BK_CAP < (1 << 16), "two 16-bit sums per scanned word");
+      u32 both_total;
+      const u32 both = blk_excl_scan<BK_THREADS> (((u32) __popc (hmask) << 16) | (u32) __popc (kmask), s_warp, scan_phase, &both_total);
+      n_dist = both_total >> 16; n_keep = both_total & 0xffffu;
+      u32 kpos = both & 0xffffu;
 #pragma unroll
-      for (int r = 0; r < BK_IPT; r++) if ((kmask >> r) & 1) s_val[kpos++] = packed[r];
+      for (int r = 0; r < BK_IPT; r++) if ((kmask >> r) & 1) { s_val[kpos] = packed[r]; s_kcnt[kpos] = kc[r]; kpos++; }
     }
     __syncthreads ();
     // ---- S3: context groups over the kept list + prefix sums of their counts (:388-404) -------------------
@@ -508,22 +488,17 @@ bucket_reduce_kernel (const u64 *__restrict__ recs, const u32 *__restrict__ bkt_
           const u32 j = j0 + r;
           c[r] = 0;
           if (j < n_keep) {
-            const u32 v = s_val[j];
-            c[r] = (v >> 12) & 0xffff;
+            c[r] = s_kcnt[j];
             csum += c[r];
-            Rec<W> x = rec_at (v & 0xfff);
+            Rec<W> x = rec_at (s_val[j] & 0xfff);
             if (j == 0 || !same_context<W> (x, prev)) gmask |= 1u << r;
             prev = x;
           }
         }
       }
-      // one scan for both: the counts of a bucket sum to at most BK_CAP < 2^16, the groups to at most BK_CAP
-      static_assert (BK_CAP < (1 << 16), "two 16-bit sums per scanned word");
-      u32 both_total;
-      const u32 both = blk_excl_scan<BK_THREADS> (((u32) __popc (gmask) << 16) | csum, s_warp, scan_phase, &both_total);
-      u32 gpos = both >> 16, cpos = both & 0xffffu;
-      n_groups = both_total >> 16; ctotal = both_total & 0xffffu;
-      // (s_aux and s_sum, written next, were last read before the barrier that ended the sort / the de-duplication)
+      u32 gpos = blk_excl_scan<BK_THREADS> ((u32) __popc (gmask), s_warp, scan_phase, &n_groups);
+      u32 cpos = blk_excl_scan<BK_THREADS> (csum, s_warp, scan_phase, &ctotal); // u32 wrap-around = the reference's int sums
+      // (s_aux and s_sum, written next, were last read before the barrier that ended the sort)
 #pragma unroll
       for (int r = 0; r < BK_IPT; r++) {
         const u32 j = j0 + r;
@@ -559,7 +534,7 @@ bucket_reduce_kernel (const u64 *__restrict__ recs, const u32 *__restrict__ bkt_
       Rec<W> x = rec_at (v & 0xfff);
       x.w[0] = (x.w[0] & ~3ULL) | (u64) (v >> 28);
       store_rec<W> (out_rec, (size_t) start + j, x);
-      out_cnt[start + j] = (v >> 12) & 0xffff;
+      out_cnt[start + j] = s_kcnt[j];
     }
     if (tid == 0) bstat[b] = make_uint4 (n_dist, n_keep, n_idx, 0);
     next_bucket ();
@@ -605,38 +580,51 @@ __device__ __forceinline__ void cov_insert (u32 *__restrict__ keys, u32 *__restr
 }
 
 // one warp per bucket: final 40-byte hopo_element (src/hopo_counter.h:34-49) as it stands at the BWA boundary, global
-// idx_initial / idx_final, and the two (flank & 0x7fffffff, count) pairs of every kept record (hopo_counter.c:427-432)
+// idx_initial / idx_final, and the two (flank & 0x7fffffff, count) pairs of every kept record (hopo_counter.c:427-432).
+// out40 may be device memory or mapped pinned host memory (the result arena): rows are staged per warp in shared
+// memory so that every store instruction of the warp covers 256 contiguous bytes.
 template <int W>
 __global__ void __launch_bounds__ (256)
 pack_kernel (const u64 *__restrict__ out_rec, const u32 *__restrict__ out_cnt, const u32 *__restrict__ out_idx_i, const u32 *__restrict__ out_idx_f,
              const u32 *__restrict__ bkt_start, const uint4 *__restrict__ bstat, const u32 *__restrict__ koff, const u32 *__restrict__ ioff,
-             const u32 *__restrict__ meta, int k, u64 *__restrict__ out24, int *__restrict__ idx_initial, int *__restrict__ idx_final,
+             const u32 *__restrict__ meta, int k, u64 *__restrict__ out40, int *__restrict__ idx_initial, int *__restrict__ idx_final,
              u32 *__restrict__ cov_keys, u32 *__restrict__ cov_vals, u32 cov_mask, u32 max_keep, u32 max_idx, unsigned long long capacity)
 {
-  // The host may launch this kernel before it knows the counts, into arrays sized from the previous sample (max_keep,
+  // The host launches this kernel before it knows the counts, into arrays sized from the previous sample (max_keep,
   // max_idx; the coverage table holds 2 max_keep keys at load <= 0.5): nothing is written beyond them, and the host
   // repeats the launch with exact sizes when the counts turn out larger (or the record array had overflowed).
+  __shared__ u64 s_stage[256 / 32][32 * 5];
   const u32 nb = meta[META_NBUCKETS];
   const int lane = threadIdx.x & 31;
+  u64 *stage = s_stage[threadIdx.x >> 5];
   const u32 warps = gridDim.x * (256 / 32);
   for (u32 b = blockIdx.x * (256 / 32) + (threadIdx.x >> 5); b < nb; b += warps) {
     const uint4 s = bstat[b];
     const u32 start = bkt_start[b], ko = koff[b], io = ioff[b];
     if ((unsigned long long) start + s.y > capacity || (unsigned long long) start + s.z > capacity) continue;
-    for (u32 j = lane; j < s.y; j += 32) {
-      if (ko + j >= max_keep) break;
-      Rec<W> r = load_rec<W> (out_rec, (size_t) start + j);
-      const int cnt = sext_field ((long long) out_cnt[start + j], 20); // the reference's count:20 signed bit-field
-      // gcc x86-64 bit-field order from the LSB: base:2 length:10 count:20 mismatches:12 multi:3 neg_strand:2 canon_flag:3
-      const u64 bits = ((u64) rec_base<W> (r, k) & 3) | (((u64) rec_len_field<W> (r) & 0x3ff) << 2) | (((u64) cnt & 0xfffff) << 12) |
-                       (0xffeULL << 32) | (((u64) rec_flag<W> (r) & 7) << 49);
-      const u64 c0 = rec_ctx0<W> (r, k), c1 = rec_ctx1<W> (r, k);
-      // the other 16 bytes of a hopo_element are constants at this point (read_offset = -1, hopo_counter.c:511;
-      // loc_ref_id = loc_pos = loc_last = -1, :297): the host appends them, they do not cross PCIe
-      u64 *o = out24 + 3 * (size_t) (ko + j);
-      o[0] = c0; o[1] = c1; o[2] = bits;
-      cov_insert (cov_keys, cov_vals, cov_mask, (u32) (c0 & 0x7fffffffULL), (u32) cnt);
-      cov_insert (cov_keys, cov_vals, cov_mask, (u32) (c1 & 0x7fffffffULL), (u32) cnt);
+    for (u32 j0 = 0; j0 < s.y; j0 += 32) {
+      if (ko + j0 >= max_keep) break;
+      const u32 j = j0 + lane;
+      u32 rows = s.y - j0 < 32u ? s.y - j0 : 32u;
+      if (ko + j0 + rows > max_keep) rows = max_keep - (ko + j0);
+      if ((u32) lane < rows) {
+        Rec<W> r = load_rec<W> (out_rec, (size_t) start + j);
+        const int cnt = sext_field ((long long) out_cnt[start + j], 20); // the reference's count:20 signed bit-field
+        // gcc x86-64 bit-field order from the LSB: base:2 length:10 count:20 mismatches:12 multi:3 neg_strand:2 canon_flag:3
+        const u64 bits = ((u64) rec_base<W> (r, k) & 3) | (((u64) rec_len_field<W> (r) & 0x3ff) << 2) | (((u64) cnt & 0xfffff) << 12) |
+                         (0xffeULL << 32) | (((u64) rec_flag<W> (r) & 7) << 49);
+        const u64 c0 = rec_ctx0<W> (r, k), c1 = rec_ctx1<W> (r, k);
+        stage[5 * lane] = c0; stage[5 * lane + 1] = c1; stage[5 * lane + 2] = bits;
+        stage[5 * lane + 3] = ~0ULL; // read_offset = -1 (hopo_counter.c:511), loc_ref_id = -1 (:297)
+        stage[5 * lane + 4] = ~0ULL; // loc_pos = loc_last = -1
+        cov_insert (cov_keys, cov_vals, cov_mask, (u32) (c0 & 0x7fffffffULL), (u32) cnt);
+        cov_insert (cov_keys, cov_vals, cov_mask, (u32) (c1 & 0x7fffffffULL), (u32) cnt);
+      }
+      __syncwarp ();
+      u64 *o = out40 + 5 * (size_t) (ko + j0);
+#pragma unroll
+      for (int t = 0; t < 5; t++) { const u32 w = t * 32 + lane; if (w < 5 * rows) o[w] = stage[w]; }
+      __syncwarp ();
     }
     for (u32 t = lane; t < s.z; t += 32) {
       if (io + t >= max_idx) break;

@@ -100,5 +100,12 @@ __host__ __device__ __forceinline__ int sext_field (long long v, int bits)
   return (int) ((v ^ m) - m);
 }
 
+// device counters of one sample (unsigned long long each)
+enum { CTR_OVERFLOW = 0, // observations deferred to the overflow list (tjb_table.cuh)
+       CTR_SKIP = 1,     // fenced runs (non-ACGTU run that is the first tract of its read)
+       CTR_ENTRIES = 2,  // entries of the aggregation table
+       CTR_NRAW = 3,     // tract observations = sum of all weights (hc->n_elem before finalise_hopo_counter)
+       CTR_WORDS = 4 };
+
 // one digit of an LSD radix pass: bits [shift, shift+nbits) of word `word`
 struct DigitDesc { int word, shift, nbits; };

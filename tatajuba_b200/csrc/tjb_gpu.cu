@@ -2,6 +2,7 @@
 // Device work only — there is no host fallback for any compute step in this file.
 #include <chrono>
 #include <sys/mman.h>
+#include <sys/stat.h>
 #include <climits>
 #include <cstdlib>
 #include <cstring>
@@ -25,12 +26,13 @@
 #define TJB_CHUNK_BYTES (32u << 20)      // files path: pinned chunk of decoded reads (two per decoder thread)
 #define TJB_HOST_CHUNK_BYTES (32u << 20) // host-buffer path: H2D chunk overlapped with the scan of the previous one
 
-enum KernelId { K_SCAN = 0, K_PLAN, K_PARTITION, K_BUCKET, K_TOTALS, K_PACK, K_COVMAX, K_RECHIST,
+enum KernelId { K_SCAN = 0, K_PLAN, K_PARTITION, K_BUCKET, K_TOTALS, K_PACK, K_COVMAX,
                 // global multi-pass path, only for buckets too large for shared memory
-                K_SORT_HIST, K_SORT_SCATTER, K_PSCAN, K_RLE, K_GROUP, K_UNION, K_UNPACK, K_COUNT };
-static const char *kKernelNames[K_COUNT] = {"tjb_scan_kernel", "plan_kernel", "partition_kernel", "bucket_reduce_kernel", "totals_kernel",
-                                            "pack_kernel", "cov_max_kernel", "rec_hist_kernel", "rsort_hist_kernel",
-                                            "rsort_scatter_kernel", "pscan_kernels", "rle_kernels", "group_kernels", "union_kernels", "unpack_kernels"};
+                K_SORT_HIST, K_SORT_SCATTER, K_PSCAN, K_RLE, K_GROUP, K_UNION, K_UNPACK, K_TABLE, K_COUNT };
+static const char *kKernelNames[K_COUNT] = {"tjb_scan_kernel", "plan_kernel", "wpartition_kernel", "wbucket_reduce_kernel", "totals_kernel",
+                                            "pack_kernel", "cov_max_kernel", "rsort_hist_kernel",
+                                            "rsort_scatter_kernel", "pscan_kernels", "rle_kernels", "group_kernels", "union_kernels", "unpack_kernels",
+                                            "table_kernels"};
 
 struct DevBuf {
   void *p = nullptr;
@@ -39,14 +41,25 @@ struct DevBuf {
 
 struct PendingEvent { int kid; cudaEvent_t a, b; };
 
+// device scalars of one sample, one allocation so that they come back in one copy
+struct ResultBlock {
+  unsigned long long counters[CTR_WORDS];
+  u32 meta[META_WORDS];
+  int cov;
+  u32 pad;
+};
+
 struct tjb_ctx {
   int device = 0;
   cudaStream_t stream = nullptr;
   std::string err;
   int profiling = 0; // 0 off, 1 scan kernel only, 2 every kernel
+  int result_mode = TJB_RESULT_MALLOC;
+  bool result_dma = false; // results leave through a device staging array + DMA instead of mapped stores of the pack kernel
   int64_t launches = 0;
   int64_t h2d_bytes = 0; // host-buffer path: bytes sent host -> device
-  size_t last_keep = 0, last_idx = 0; // sizes of the previous sample's result: the next one is allocated ahead (finalise_t)
+  size_t last_keep = 0, last_idx = 0, last_entries = 0; // sizes of the previous sample: the next one is sized ahead
+  size_t want_entries = 0;                              // set when a sample has to be redone with a larger table
   tjb_kernel_stat stats[K_COUNT];
   std::vector<PendingEvent> pending;
   std::vector<cudaEvent_t> free_events;
@@ -59,27 +72,32 @@ struct tjb_ctx {
   uint8_t *h_pk[2] = {nullptr, nullptr}; uint32_t *h_exc_pos[2] = {nullptr, nullptr}; uint8_t *h_exc_val[2] = {nullptr, nullptr};
   DevBuf d_pk[2], d_exc_pos[2], d_exc_val[2];
 
-  DevBuf rec_a, rec_b; // raw tract observations + sort ping-pong
-  size_t rec_capacity = 0; // records rec_a can hold
+  // ---- the sample being counted ----
+  tjb_opts opt = {0, 0, 0, 0, 0};
+  bool in_sample = false;
+  int64_t exported_rows = -1;               // rows of the table as exported for an exchange (-1: not exported yet)
   int rec_words = 0;
-  unsigned long long n_raw_known = 0, n_skip_known = 0;
-  const uint8_t *pend_ptr = nullptr; size_t pend_len = 0; bool pend = false; // scan launched, overflow not checked yet
-  unsigned long long *d_counters = nullptr; // [0] = n_raw, [1] = skipped non-ACGTU runs
+  int bin_bits = 8;
+  DevBuf tab_keys, tab_cnt;                 // aggregation table (tjb_table.cuh)
+  size_t tab_slots = 0;
+  DevBuf ovf;                               // observations the table could not take, raw records
+  size_t ovf_capacity = 0;
+  DevBuf wkey, wcnt, okey;                  // weighted records bucket by bucket; compact per-bucket output
+  size_t list_cap = 0;
+  ResultBlock *d_res = nullptr, *h_res = nullptr; // device scalars and their pinned mirror
   u32 *d_tile_ctr = nullptr;                // scan kernel: next window to hand out
   u32 *d_totals = nullptr;                  // small device scalars (global multi-pass path)
-  int *d_cov = nullptr;
-  // bucketed reduce: bin histogram (filled by the scan), splitters, per-bucket results
-  int bin_bits = PLAN_REG_BIN_BITS;
-  bool hist_dirty = false;                  // a chunk was re-scanned after an overflow: rebuild the histogram from the records
-  u32 *d_bin_hist = nullptr, *d_lut = nullptr, *d_meta = nullptr;            // per bin (2^TJB_MAX_BIN_BITS)
+  u32 *d_bin_hist = nullptr, *d_lut = nullptr;                               // per bin (2^TJB_MAX_BIN_BITS)
   u32 *d_bkt_start = nullptr, *d_cursor = nullptr, *d_koff = nullptr, *d_ioff = nullptr; // per bucket (views of the DevBufs below)
   uint4 *d_bstat = nullptr;
   DevBuf b_bkt_start, b_cursor, b_koff, b_ioff, b_bstat;
   u32 max_buckets = 0;
-  unsigned long long *h_sync = nullptr;     // pinned: [0..1] counters, [2..] meta words
-  char *h_out = nullptr; size_t h_out_cap = 0; // pinned staging of the results
-  DevBuf out_cnt, out_ii, out_if, cov_tab;
-  DevBuf hist, ptmp, heads, pos, seg, drec, dcount, keep, kpos, krec, kcount, cw, csum, gkeep, gkpos, out40, idx_i, idx_f;
+  // results: pinned, device-mapped arena {elem[keep_cap] (40 B), idx_initial[idx_cap], idx_final[idx_cap]}
+  char *h_arena = nullptr, *d_arena = nullptr;
+  size_t arena_keep_cap = 0, arena_idx_cap = 0;
+  DevBuf out_cnt, out_ii, out_if, cov_tab, out40, idx_i, idx_f, qrows;
+  DevBuf hist, ptmp, heads, pos, seg, drec, dcount, keep, kpos, krec, cw, csum, gkeep, gkpos;
+  DevBuf uni_a, uni_b;                      // union of query rows
 
   cudaEvent_t ev_t0 = nullptr, ev_t1 = nullptr;
   cudaStream_t copy_stream = nullptr; // host-buffer path: H2D copies overlap the scan of the previous chunk
@@ -161,6 +179,7 @@ struct Trace { // TJB_TRACE=1: host wall-clock of the stages of one call, on std
 };
 
 static inline u32 nblk (size_t n, u32 per) { return (u32) ((n + per - 1) / per); }
+static inline size_t pow2_at_least (size_t x) { size_t p = 1; while (p < x) p <<= 1; return p; }
 
 // ------------------------------------------------------------------------------------ scan + sort -------
 static int exclusive_scan (tjb_ctx *ctx, const u32 *in, u32 *out, size_t n, u32 *tmp, u32 *total_out)
@@ -192,7 +211,8 @@ static std::vector<DigitDesc> tract_digits (int W, int k)
   return v;
 }
 
-template <int W>
+// S = words per record (the digits only look at the key words)
+template <int S>
 static int radix_sort (tjb_ctx *ctx, u64 *a, u64 *b, size_t n, const std::vector<DigitDesc> &digits, u64 **sorted)
 {
   u32 n_tiles = nblk (n, RSORT_TILE);
@@ -201,44 +221,42 @@ static int radix_sort (tjb_ctx *ctx, u64 *a, u64 *b, size_t n, const std::vector
   TRY (ensure (ctx, ctx->ptmp, pscan_tmp_elems (hn > n ? hn : n) * sizeof (u32) + 64));
   u32 *hist = (u32*) ctx->hist.p;
   for (const DigitDesc &dd : digits) {
-    LAUNCH (K_SORT_HIST, 8 * W * n, (rsort_hist_kernel<W><<<n_tiles, RSORT_THREADS, 0, ctx->stream>>> (a, n, dd, hist, n_tiles)));
+    LAUNCH (K_SORT_HIST, 8 * S * n, (rsort_hist_kernel<S><<<n_tiles, RSORT_THREADS, 0, ctx->stream>>> (a, n, dd, hist, n_tiles)));
     TRY (exclusive_scan (ctx, hist, hist, hn, (u32*) ctx->ptmp.p, nullptr));
-    LAUNCH (K_SORT_SCATTER, 16 * W * n, (rsort_scatter_kernel<W><<<n_tiles, RSORT_THREADS, 0, ctx->stream>>> (a, b, n, dd, hist, n_tiles)));
+    LAUNCH (K_SORT_SCATTER, 16 * S * n, (rsort_scatter_kernel<S><<<n_tiles, RSORT_THREADS, 0, ctx->stream>>> (a, b, n, dd, hist, n_tiles)));
     u64 *t = a; a = b; b = t;
   }
   *sorted = a;
   return 0;
 }
 
-static int grow_records (tjb_ctx *ctx, size_t want_records)
-{
-  if (want_records <= ctx->rec_capacity) return 0;
-  size_t bytes = want_records * ctx->rec_words * sizeof (u64);
-  void *np = nullptr;
-  CU (cudaMalloc (&np, bytes));
-  if (ctx->rec_a.p && ctx->n_raw_known)
-    CU (cudaMemcpyAsync (np, ctx->rec_a.p, (size_t) ctx->n_raw_known * ctx->rec_words * sizeof (u64), cudaMemcpyDeviceToDevice, ctx->stream));
-  CU (cudaStreamSynchronize (ctx->stream));
-  if (ctx->rec_a.p) CU (cudaFree (ctx->rec_a.p));
-  ctx->rec_a.p = np; ctx->rec_a.cap = bytes;
-  ctx->rec_capacity = want_records;
-  return 0;
-}
-
-// bins of the partition plan: enough that a bin holds ~BK_CAP/8 records on average, at most what the context has.
-// Expected records: a run of >= m equal bases starts at a position with probability 3/4 * 4^-(m-1).
-static int choose_bin_bits (size_t n_bytes_hint, int k, int min_tract)
+// bins of the partition plan: enough that a bin holds ~BK_CAP/8 weighted records on average
+static int choose_bin_bits (size_t est_records, int k)
 {
   const int W = tjb_rec_words (k);
   const int max_bits = W == 2 ? (4 * k + 1 < TJB_MAX_BIN_BITS ? 4 * k + 1 : TJB_MAX_BIN_BITS)
                               : (2 * k + 1 < TJB_MAX_BIN_BITS ? 2 * k + 1 : TJB_MAX_BIN_BITS);
-  const int m = min_tract < 2 ? 2 : (min_tract > 8 ? 8 : min_tract);
   int F = 4;
-  if (n_bytes_hint == 0) F = PLAN_REG_BIN_BITS; // size unknown (streamed files)
-  else { size_t est = (n_bytes_hint * 3 / 4) >> (2 * (m - 1)); while (F < TJB_MAX_BIN_BITS && (est >> F) > BK_CAP / 8) F++; }
+  while (F < TJB_MAX_BIN_BITS && (est_records >> F) > BK_CAP / 8) F++;
   return F < max_bits ? F : max_bits;
 }
 
+// Table entries to expect before anything of the sample has been seen: a run of >= m equal bases starts at a position
+// with probability 3/4 * 4^-(m-1); that many observations, every one of them distinct in the worst case.
+static size_t estimate_entries (size_t n_bytes_hint, int min_tract)
+{
+  const int m = min_tract < 2 ? 2 : (min_tract > 8 ? 8 : min_tract);
+  if (!n_bytes_hint) return (size_t) 1 << 20; // size unknown
+  const size_t est = (n_bytes_hint * 3 / 4) >> (2 * (m - 1));
+  return est < 4096 ? 4096 : est;
+}
+
+#define TJB_MAX_TABLE_SLOTS ((size_t) 1 << 28)
+
+// Sizes and clears the per-sample device state.  Everything that depends on how many DISTINCT observations the sample
+// holds (table slots, overflow list, weighted record arrays, bins) is sized from the previous sample of this context
+// (samples of one run are alike) or, for the first one, from the input size; a sample that does not fit is detected
+// at the synchronisation that ends it and redone with ctx->want_entries.
 static int begin_sample (tjb_ctx *ctx, const tjb_opts *opt, size_t n_bytes_hint)
 {
   if (!opt || opt->kmer_size < 2 || opt->kmer_size > 32 || opt->min_tract_size < 1 || opt->min_coverage < 0) {
@@ -246,69 +264,52 @@ static int begin_sample (tjb_ctx *ctx, const tjb_opts *opt, size_t n_bytes_hint)
     return TJB_ERR_ARG;
   }
   CU (cudaSetDevice (ctx->device));
-  int W = tjb_rec_words (opt->kmer_size);
-  if (W != ctx->rec_words) { ctx->rec_words = W; ctx->rec_capacity = ctx->rec_a.cap / (W * sizeof (u64)); }
-  ctx->n_raw_known = ctx->n_skip_known = 0;
-  ctx->pend = false;
-  ctx->hist_dirty = false;
-  ctx->bin_bits = choose_bin_bits (n_bytes_hint, opt->kmer_size, opt->min_tract_size);
-  CU (cudaMemsetAsync (ctx->d_counters, 0, 2 * sizeof (unsigned long long), ctx->stream));
+  ctx->opt = *opt;
+  const int W = tjb_rec_words (opt->kmer_size);
+  ctx->rec_words = W;
+  size_t est = ctx->want_entries ? ctx->want_entries
+             : (ctx->last_entries ? ctx->last_entries + ctx->last_entries / 4 + 1024 : estimate_entries (n_bytes_hint, opt->min_tract_size));
+  ctx->want_entries = 0;
+  size_t slots = pow2_at_least (3 * est);
+  if (slots < ((size_t) 1 << 16)) slots = (size_t) 1 << 16;
+  if (slots > TJB_MAX_TABLE_SLOTS) slots = TJB_MAX_TABLE_SLOTS;
+  ctx->tab_slots = slots;
+  ctx->ovf_capacity = est / 8 < 65536 ? 65536 : est / 8;
+  ctx->list_cap = slots / 2 + ctx->ovf_capacity;
+  ctx->bin_bits = choose_bin_bits (est, opt->kmer_size);
+  TRY (ensure (ctx, ctx->tab_keys, slots * W * 8));
+  TRY (ensure (ctx, ctx->tab_cnt, slots * 8));
+  TRY (ensure (ctx, ctx->ovf, ctx->ovf_capacity * W * 8));
+  CU (cudaMemsetAsync (ctx->d_res, 0, sizeof (ResultBlock), ctx->stream));
+  CU (cudaMemsetAsync (ctx->tab_cnt.p, 0, slots * 8, ctx->stream));
   CU (cudaMemsetAsync (ctx->d_bin_hist, 0, sizeof (u32) << ctx->bin_bits, ctx->stream));
+  ctx->in_sample = true;
+  ctx->exported_rows = -1;
   return 0;
 }
 
-static int launch_scan (tjb_ctx *ctx, const uint8_t *d_seqs, size_t n, const tjb_opts *opt)
+static AggTable table_of (tjb_ctx *ctx)
+{
+  AggTable t;
+  t.keys = (u64*) ctx->tab_keys.p; t.cnt = (unsigned long long*) ctx->tab_cnt.p; t.mask = (u32) (ctx->tab_slots - 1);
+  return t;
+}
+
+static int launch_scan (tjb_ctx *ctx, const uint8_t *d_seqs, size_t n)
 {
   long long n_tiles = (long long) ((n + SW_TILE - 1) / SW_TILE); // one window of SW_TILE owned bytes per warp at a time
   if (!n_tiles) return 0;
+  const tjb_opts *opt = &ctx->opt;
   int min_len = opt->min_tract_size < 2 ? 2 : opt->min_tract_size;
   CU (cudaMemsetAsync (ctx->d_tile_ctr, 0, sizeof (u32), ctx->stream)); // window tickets of this launch
   long long want = (n_tiles + SCAN_WARPS - 1) / SCAN_WARPS;
   long long grid = want < (long long) ctx->sm_count * SCAN_CTAS_PER_SM ? want : (long long) ctx->sm_count * SCAN_CTAS_PER_SM;
-  // algorithmic bytes of this launch: every sequence byte read once (+ 8W bytes per emitted record, added at finalise)
+  // algorithmic bytes of this launch: every sequence byte read once (+ the table traffic per observation, added at finalise)
   if (ctx->rec_words == 2)
-    LAUNCH (K_SCAN, n, (tjb_scan_kernel<2><<<(u32) grid, SCAN_THREADS, scan_smem_bytes<2> (), ctx->stream>>> (d_seqs, (long long) n, opt->kmer_size, min_len, (u64*) ctx->rec_a.p, ctx->rec_capacity, ctx->d_counters, n_tiles, ctx->d_bin_hist, ctx->bin_bits, ctx->d_tile_ctr)));
+    LAUNCH (K_SCAN, n, (tjb_scan_kernel<2><<<(u32) grid, SCAN_THREADS, scan_smem_bytes<2> (), ctx->stream>>> (d_seqs, (long long) n, opt->kmer_size, min_len, table_of (ctx), (u64*) ctx->ovf.p, ctx->ovf_capacity, ctx->d_res->counters, n_tiles, ctx->d_bin_hist, ctx->bin_bits, ctx->d_tile_ctr)));
   else
-    LAUNCH (K_SCAN, n, (tjb_scan_kernel<3><<<(u32) grid, SCAN_THREADS, scan_smem_bytes<3> (), ctx->stream>>> (d_seqs, (long long) n, opt->kmer_size, min_len, (u64*) ctx->rec_a.p, ctx->rec_capacity, ctx->d_counters, n_tiles, ctx->d_bin_hist, ctx->bin_bits, ctx->d_tile_ctr)));
+    LAUNCH (K_SCAN, n, (tjb_scan_kernel<3><<<(u32) grid, SCAN_THREADS, scan_smem_bytes<3> (), ctx->stream>>> (d_seqs, (long long) n, opt->kmer_size, min_len, table_of (ctx), (u64*) ctx->ovf.p, ctx->ovf_capacity, ctx->d_res->counters, n_tiles, ctx->d_bin_hist, ctx->bin_bits, ctx->d_tile_ctr)));
   CU (cudaGetLastError ());
-  return 0;
-}
-
-// Launches the scan of one device-resident chunk (asynchronous).  The record array is grown beforehand to an estimate;
-// overflowing records are counted but never written, so the overflow is detected at the next synchronisation
-// (scan_resolve(), or the first synchronisation of finalise for a single-chunk sample) and the chunk re-scanned.
-static int scan_launch (tjb_ctx *ctx, const uint8_t *d_seqs, size_t n, const tjb_opts *opt)
-{
-  size_t guess = (size_t) ctx->n_raw_known + n / 16 + 65536;
-  TRY (grow_records (ctx, guess));
-  TRY (launch_scan (ctx, d_seqs, n, opt));
-  ctx->pend_ptr = d_seqs; ctx->pend_len = n; ctx->pend = true;
-  return 0;
-}
-// re-scan of the pending chunk after an overflow: cnt0 = the (too large) record count the first attempt reported
-static int scan_redo (tjb_ctx *ctx, const tjb_opts *opt, unsigned long long cnt0)
-{
-  unsigned long long back[2] = {ctx->n_raw_known, ctx->n_skip_known};
-  TRY (grow_records (ctx, (size_t) cnt0 + 1024));
-  CU (cudaMemcpyAsync (ctx->d_counters, back, sizeof (back), cudaMemcpyHostToDevice, ctx->stream));
-  CU (cudaStreamSynchronize (ctx->stream)); // `back` lives on this stack frame
-  ctx->hist_dirty = true;                   // the first attempt already counted this chunk's bins
-  return launch_scan (ctx, ctx->pend_ptr, ctx->pend_len, opt);
-}
-static int scan_resolve (tjb_ctx *ctx, const tjb_opts *opt)
-{
-  if (!ctx->pend) return 0;
-  unsigned long long cnt[2];
-  CU (cudaMemcpyAsync (cnt, ctx->d_counters, sizeof (cnt), cudaMemcpyDeviceToHost, ctx->stream));
-  CU (cudaStreamSynchronize (ctx->stream));
-  if (cnt[0] > ctx->rec_capacity) {
-    TRY (scan_redo (ctx, opt, cnt[0]));
-    CU (cudaMemcpyAsync (cnt, ctx->d_counters, sizeof (cnt), cudaMemcpyDeviceToHost, ctx->stream));
-    CU (cudaStreamSynchronize (ctx->stream));
-  }
-  ctx->pend = false;
-  ctx->n_raw_known = cnt[0];
-  ctx->n_skip_known = cnt[1];
   return 0;
 }
 
@@ -347,44 +348,49 @@ struct PackerSession { // the packer threads spin while at least one call is fee
 };
 
 // --------------------------------------------------------------------------------------- finalise -------
-// Global multi-pass reduce of ONE bucket that does not fit in shared memory: LSD radix sort over every digit,
-// run-length count, QC filter, context groups.  Results land where bucket_reduce_kernel would have put them.
+static int qc_mode_of (const tjb_opts *opt) { return opt->remove_biased ? QC_BOTH_STRANDS : QC_SEEN_TWICE; }
+
+// Global multi-pass reduce of ONE bucket that does not fit in shared memory: the weighted records are gathered into
+// (key, count) rows, LSD radix sorted over every key digit, equal keys merged, QC filter, context groups.  Results land
+// where wbucket_reduce_kernel would have put them.
 template <int W>
-static int reduce_oversize_bucket (tjb_ctx *ctx, const tjb_opts *opt, u32 b, u32 start, u32 n)
+static int reduce_oversize_bucket (tjb_ctx *ctx, int qc_mode, int min_coverage, int k, u32 b, u32 start, u32 n)
 {
-  const int k = opt->kmer_size;
+  constexpr int S = W + 1;
   cudaStream_t st = ctx->stream;
-  TRY (ensure (ctx, ctx->drec, (size_t) n * W * 8)); // scratch of n records
-  u64 *in = (u64*) ctx->rec_b.p + (size_t) start * W, *tmp = (u64*) ctx->drec.p;
+  TRY (ensure (ctx, ctx->drec, (size_t) n * S * 8));
+  TRY (ensure (ctx, ctx->krec, (size_t) n * S * 8));
+  u64 *in = (u64*) ctx->drec.p, *tmp = (u64*) ctx->krec.p;
+  u64 *wkey = (u64*) ctx->wkey.p + (size_t) start * W;
+  LAUNCH (K_RLE, (16 * W + 16) * (size_t) n, (wgather_kernel<W><<<nblk (n, RED_THREADS), RED_THREADS, 0, st>>> (wkey, (const unsigned long long*) ctx->wcnt.p + start, n, in)));
   u64 *sorted = nullptr;
-  TRY ((radix_sort<W> (ctx, in, tmp, n, tract_digits (W, k), &sorted)));
+  TRY ((radix_sort<S> (ctx, in, tmp, n, tract_digits (W, k), &sorted)));
   TRY (ensure (ctx, ctx->heads, (size_t) n * 4)); TRY (ensure (ctx, ctx->pos, (size_t) n * 4)); TRY (ensure (ctx, ctx->seg, (size_t) n * 4));
   TRY (ensure (ctx, ctx->ptmp, pscan_tmp_elems (n) * 4 + 64));
   u32 *heads = (u32*) ctx->heads.p, *pos = (u32*) ctx->pos.p, *seg = (u32*) ctx->seg.p, *ptmp = (u32*) ctx->ptmp.p;
   u32 h_tot[4];
-  LAUNCH (K_RLE, 16 * W * (size_t) n, (head_kernel<W, 0><<<nblk (n, RED_THREADS), RED_THREADS, 0, st>>> (sorted, n, heads)));
+  LAUNCH (K_RLE, 16 * S * (size_t) n, (head_kernel<W, 0, S><<<nblk (n, RED_THREADS), RED_THREADS, 0, st>>> (sorted, n, heads)));
   TRY (exclusive_scan (ctx, heads, pos, n, ptmp, ctx->d_totals + 0));
   CU (cudaMemcpyAsync (h_tot, ctx->d_totals, 4, cudaMemcpyDeviceToHost, st));
   LAUNCH (K_RLE, 12 * (size_t) n, (seg_start_kernel<<<nblk (n, RED_THREADS), RED_THREADS, 0, st>>> (heads, pos, n, seg)));
   CU (cudaStreamSynchronize (st));
   const u32 n_dist = h_tot[0];
-  // distinct records: into whichever of {in, tmp} does not hold the sorted array
-  u64 *drec = (sorted == in) ? tmp : in;
+  // distinct records: the bucket's slice of the weighted list is free now (its rows were gathered)
+  u64 *drec = wkey;
   TRY (ensure (ctx, ctx->dcount, (size_t) n_dist * 4)); TRY (ensure (ctx, ctx->keep, (size_t) n_dist * 4)); TRY (ensure (ctx, ctx->kpos, (size_t) n_dist * 4));
-  LAUNCH (K_RLE, (16 * W + 12) * (size_t) n_dist, (rle_emit_kernel<W><<<nblk (n_dist, RED_THREADS), RED_THREADS, 0, st>>> (sorted, n, seg, n_dist, opt->remove_biased, drec, (int*) ctx->dcount.p, (u32*) ctx->keep.p)));
+  LAUNCH (K_RLE, (16 * W + 12) * (size_t) n_dist, (wrle_emit_kernel<W><<<nblk (n_dist, RED_THREADS), RED_THREADS, 0, st>>> (sorted, n, seg, n_dist, qc_mode, drec, (int*) ctx->dcount.p, (u32*) ctx->keep.p)));
   TRY (exclusive_scan (ctx, (u32*) ctx->keep.p, (u32*) ctx->kpos.p, n_dist, ptmp, ctx->d_totals + 1));
   CU (cudaMemcpyAsync (h_tot, ctx->d_totals + 1, 4, cudaMemcpyDeviceToHost, st));
   CU (cudaStreamSynchronize (st));
   const u32 n_keep = h_tot[0];
   u32 n_idx = 0;
   if (n_keep) {
-    // kept records go straight to the bucket's output slot (rec_a doubles as the compact output array)
-    u64 *krec = (u64*) ctx->rec_a.p + (size_t) start * W;
+    u64 *krec = (u64*) ctx->okey.p + (size_t) start * W;
     int *kcount = (int*) ctx->out_cnt.p + start;
     LAUNCH (K_RLE, (16 * W + 8) * (size_t) n_keep, (compact_kernel<W><<<nblk (n_dist, RED_THREADS), RED_THREADS, 0, st>>> (drec, (int*) ctx->dcount.p, (u32*) ctx->keep.p, (u32*) ctx->kpos.p, n_dist, krec, kcount)));
     TRY (ensure (ctx, ctx->cw, (size_t) n_keep * 4)); TRY (ensure (ctx, ctx->csum, (size_t) n_keep * 4));
     TRY (ensure (ctx, ctx->gkeep, (size_t) n_keep * 4)); TRY (ensure (ctx, ctx->gkpos, (size_t) n_keep * 4));
-    LAUNCH (K_GROUP, 16 * W * (size_t) n_keep, (head_kernel<W, 1><<<nblk (n_keep, RED_THREADS), RED_THREADS, 0, st>>> (krec, n_keep, heads)));
+    LAUNCH (K_GROUP, 16 * W * (size_t) n_keep, (head_kernel<W, 1, W><<<nblk (n_keep, RED_THREADS), RED_THREADS, 0, st>>> (krec, n_keep, heads)));
     TRY (exclusive_scan (ctx, heads, pos, n_keep, ptmp, ctx->d_totals + 0));
     LAUNCH (K_GROUP, 12 * (size_t) n_keep, (seg_start_kernel<<<nblk (n_keep, RED_THREADS), RED_THREADS, 0, st>>> (heads, pos, n_keep, seg)));
     LAUNCH (K_GROUP, 8 * (size_t) n_keep, (icopy_kernel<<<nblk (n_keep, RED_THREADS), RED_THREADS, 0, st>>> (kcount, n_keep, (u32*) ctx->cw.p)));
@@ -392,7 +398,7 @@ static int reduce_oversize_bucket (tjb_ctx *ctx, const tjb_opts *opt, u32 b, u32
     CU (cudaMemcpyAsync (h_tot, ctx->d_totals, 4, cudaMemcpyDeviceToHost, st));
     CU (cudaStreamSynchronize (st));
     const u32 n_groups = h_tot[0];
-    LAUNCH (K_GROUP, 12 * (size_t) n_groups, (group_keep_kernel<<<nblk (n_groups, RED_THREADS), RED_THREADS, 0, st>>> (seg, n_groups, n_keep, (u32*) ctx->csum.p, ctx->d_totals + 2, opt->min_coverage, (u32*) ctx->gkeep.p)));
+    LAUNCH (K_GROUP, 12 * (size_t) n_groups, (group_keep_kernel<<<nblk (n_groups, RED_THREADS), RED_THREADS, 0, st>>> (seg, n_groups, n_keep, (u32*) ctx->csum.p, ctx->d_totals + 2, min_coverage, (u32*) ctx->gkeep.p)));
     TRY (exclusive_scan (ctx, (u32*) ctx->gkeep.p, (u32*) ctx->gkpos.p, n_groups, ptmp, ctx->d_totals + 3));
     CU (cudaMemcpyAsync (h_tot, ctx->d_totals + 3, 4, cudaMemcpyDeviceToHost, st));
     LAUNCH (K_GROUP, 16 * (size_t) n_groups, (group_emit_kernel<<<nblk (n_groups, RED_THREADS), RED_THREADS, 0, st>>> (seg, (u32*) ctx->gkeep.p, (u32*) ctx->gkpos.p, n_groups, n_keep, (int*) ctx->out_ii.p + start, (int*) ctx->out_if.p + start)));
@@ -414,22 +420,34 @@ static DigitList digit_list (int W, int k)
   return dl;
 }
 
-template <int W>
-static int finalise_t (tjb_ctx *ctx, const tjb_opts *opt, tjb_counter_out *out, bool *overflow)
+// the result arena: pinned host memory the device can store into (results are written by pack_kernel, no copy engine
+// and no staging copy on the way); grown geometrically, contents valid until the context counts its next sample
+static int ensure_arena (tjb_ctx *ctx, size_t keep, size_t idx)
 {
-  const int k = opt->kmer_size, F = ctx->bin_bits;
+  if (keep <= ctx->arena_keep_cap && idx <= ctx->arena_idx_cap) return 0;
+  CU (cudaStreamSynchronize (ctx->stream));
+  if (ctx->h_arena) CU (cudaFreeHost (ctx->h_arena));
+  ctx->h_arena = ctx->d_arena = nullptr;
+  const size_t kc = keep + keep / 4 + 4096 > ctx->arena_keep_cap ? keep + keep / 4 + 4096 : ctx->arena_keep_cap;
+  const size_t ic = idx + idx / 4 + 4096 > ctx->arena_idx_cap ? idx + idx / 4 + 4096 : ctx->arena_idx_cap;
+  ctx->arena_keep_cap = ctx->arena_idx_cap = 0;
+  CU (cudaHostAlloc ((void**) &ctx->h_arena, kc * 40 + ic * 8, cudaHostAllocMapped | cudaHostAllocPortable));
+  CU (cudaHostGetDevicePointer ((void**) &ctx->d_arena, ctx->h_arena, 0));
+  ctx->arena_keep_cap = kc; ctx->arena_idx_cap = ic;
+  return 0;
+}
+
+#define TJB_INTERNAL_RETRY 100 // the sample did not fit the table / lists it was sized for; ctx->want_entries is set
+
+// plan -> partition -> bucket reduce -> totals, all asynchronous (the scalars stay on the device)
+template <int W>
+static int reduce_launch (tjb_ctx *ctx, int qc_mode, int min_coverage)
+{
+  const int k = ctx->opt.kmer_size, F = ctx->bin_bits;
   cudaStream_t st = ctx->stream;
-  const unsigned long long cap = ctx->rec_capacity;
-  *overflow = false;
-  Trace tr;
-  if (!cap) { // nothing was ever scanned (empty input)
-    out->status = TJB_NO_HT;
-    return 0;
-  }
-  // workspace that scales with the record capacity; rec_a is reused as the compact output array once partitioned
-  TRY (ensure (ctx, ctx->rec_b, (size_t) cap * W * 8));
+  const unsigned long long cap = ctx->list_cap;
+  TRY (ensure (ctx, ctx->wkey, (size_t) cap * W * 8)); TRY (ensure (ctx, ctx->wcnt, (size_t) cap * 8)); TRY (ensure (ctx, ctx->okey, (size_t) cap * W * 8));
   TRY (ensure (ctx, ctx->out_cnt, (size_t) cap * 4)); TRY (ensure (ctx, ctx->out_ii, (size_t) cap * 4)); TRY (ensure (ctx, ctx->out_if, (size_t) cap * 4));
-  u64 *rec_a = (u64*) ctx->rec_a.p, *rec_b = (u64*) ctx->rec_b.p;
   const u32 grid = (u32) ctx->sm_count;
   // per-bucket tables: a bucket starts where the running record count crosses a multiple of BK_CAPH
   const u32 max_buckets = (u32) (cap / BK_CAPH) + 2;
@@ -440,72 +458,119 @@ static int finalise_t (tjb_ctx *ctx, const tjb_opts *opt, tjb_counter_out *out, 
   ctx->d_bkt_start = (u32*) ctx->b_bkt_start.p; ctx->d_cursor = (u32*) ctx->b_cursor.p;
   ctx->d_koff = (u32*) ctx->b_koff.p; ctx->d_ioff = (u32*) ctx->b_ioff.p; ctx->d_bstat = (uint4*) ctx->b_bstat.p;
   ctx->max_buckets = max_buckets;
-
-  if (ctx->hist_dirty) {
-    CU (cudaMemsetAsync (ctx->d_bin_hist, 0, sizeof (u32) << F, st));
-    LAUNCH (K_RECHIST, 0, (rec_hist_kernel<W><<<grid * 8, 256, 0, st>>> (rec_a, ctx->d_counters, cap, k, F, ctx->d_bin_hist)));
-    ctx->hist_dirty = false;
-  }
+  u32 *d_meta = ctx->d_res->meta;
+  unsigned long long *d_counters = ctx->d_res->counters;
   {
     const int ipt = F > 10 ? 1 << (F - 10) : 1; // bins per thread of the single planning CTA
-#define PLAN_CASE(I) case I: LAUNCH (K_PLAN, 10 << F, (plan_kernel<I><<<1, PLAN_THREADS, 0, st>>> (ctx->d_bin_hist, F, ctx->d_counters, cap, ctx->d_bkt_start, ctx->d_lut, ctx->d_cursor, ctx->d_meta, max_buckets))); break;
+#define PLAN_CASE(I) case I: LAUNCH (K_PLAN, 10 << F, (plan_kernel<I><<<1, PLAN_THREADS, 0, st>>> (ctx->d_bin_hist, F, cap, ctx->d_bkt_start, ctx->d_lut, ctx->d_cursor, d_meta, max_buckets))); break;
     if (F > PLAN_REG_BIN_BITS)
-      LAUNCH (K_PLAN, 18 << F, (plan_big_kernel<<<1, PLAN_THREADS, 0, st>>> (ctx->d_bin_hist, F, ctx->d_counters, cap, ctx->d_bkt_start, ctx->d_lut, ctx->d_cursor, ctx->d_meta, max_buckets)));
+      LAUNCH (K_PLAN, 18 << F, (plan_big_kernel<<<1, PLAN_THREADS, 0, st>>> (ctx->d_bin_hist, F, cap, ctx->d_bkt_start, ctx->d_lut, ctx->d_cursor, d_meta, max_buckets)));
     else
     switch (ipt) { PLAN_CASE (1) PLAN_CASE (2) PLAN_CASE (4) PLAN_CASE (8) PLAN_CASE (16) PLAN_CASE (32) PLAN_CASE (64) }
 #undef PLAN_CASE
   }
-  LAUNCH (K_PARTITION, 0, (partition_kernel<W><<<grid * PART_GRID, 256, 0, st>>> (rec_a, rec_b, ctx->d_counters, cap, k, F, ctx->d_lut, ctx->d_cursor)));
-  LAUNCH (K_BUCKET, 0, (bucket_reduce_kernel<W><<<grid * (W == 2 ? BK_CTAS2 : 2), BK_THREADS, bucket_smem_bytes<W> (), st>>> (rec_b, ctx->d_bkt_start, ctx->d_meta, cap, digit_list (W, k), opt->remove_biased, opt->min_coverage, rec_a, (u32*) ctx->out_cnt.p, (u32*) ctx->out_ii.p, (u32*) ctx->out_if.p, ctx->d_bstat)));
-  LAUNCH (K_TOTALS, 0, (totals_kernel<<<1, PLAN_THREADS, 0, st>>> (ctx->d_bstat, ctx->d_meta, ctx->d_koff, ctx->d_ioff)));
+  {
+    const size_t want = nblk (ctx->tab_slots, 256 * PART_UNROLL);
+    const u32 g = (u32) (want < (size_t) grid * PART_GRID ? (want ? want : 1) : (size_t) grid * PART_GRID);
+    LAUNCH (K_PARTITION, 8 * ctx->tab_slots, (wpartition_kernel<W><<<g, 256, 0, st>>> (table_of (ctx), (const u64*) ctx->ovf.p, d_counters, ctx->ovf_capacity, k, F, ctx->d_lut, ctx->d_cursor, (u64*) ctx->wkey.p, (unsigned long long*) ctx->wcnt.p, cap)));
+  }
+  LAUNCH (K_BUCKET, 0, (wbucket_reduce_kernel<W><<<grid * (W == 2 ? BK_CTAS2 : 2), BK_THREADS, wbucket_smem_bytes<W> (), st>>> ((const u64*) ctx->wkey.p, (const unsigned long long*) ctx->wcnt.p, ctx->d_bkt_start, d_meta, cap, digit_list (W, k), qc_mode, min_coverage, (u64*) ctx->okey.p, (u32*) ctx->out_cnt.p, (u32*) ctx->out_ii.p, (u32*) ctx->out_if.p, ctx->d_bstat)));
+  LAUNCH (K_TOTALS, 0, (totals_kernel<<<1, PLAN_THREADS, 0, st>>> (ctx->d_bstat, d_meta, ctx->d_koff, ctx->d_ioff)));
   CU (cudaGetLastError ());
-  // elements + group indices + coverage, into arrays for max_keep records / max_idx groups
+  return 0;
+}
+
+// after a synchronisation that brought ctx->h_res back: did the sample fit what it was sized for?
+static bool sample_overflowed (tjb_ctx *ctx)
+{
+  const ResultBlock *hr = ctx->h_res;
+  const unsigned long long n_ovf = hr->counters[CTR_OVERFLOW], n_ent = hr->counters[CTR_ENTRIES];
+  if (n_ovf > ctx->ovf_capacity || n_ent > ctx->tab_slots / 2 || n_ent + n_ovf > ctx->list_cap) {
+    // the table or the overflow list was too small for this sample: everything after the scan worked on a part of it
+    ctx->want_entries = (size_t) (n_ent + n_ovf) * 2 + 4096;
+    return true;
+  }
+  ctx->last_entries = (size_t) (n_ent + n_ovf);
+  return false;
+}
+
+// rare: buckets that do not fit in shared memory go through the global multi-pass path; totals again, h_res refreshed
+template <int W>
+static int reduce_oversize_buckets (tjb_ctx *ctx, int qc_mode, int min_coverage)
+{
+  cudaStream_t st = ctx->stream;
+  const u32 n_buckets = ctx->h_res->meta[META_NBUCKETS];
+  std::vector<u32> h_start (n_buckets + 1);
+  std::vector<uint4> h_stat (n_buckets);
+  CU (cudaMemcpyAsync (h_start.data (), ctx->d_bkt_start, (n_buckets + 1) * sizeof (u32), cudaMemcpyDeviceToHost, st));
+  CU (cudaMemcpyAsync (h_stat.data (), ctx->d_bstat, n_buckets * sizeof (uint4), cudaMemcpyDeviceToHost, st));
+  CU (cudaStreamSynchronize (st));
+  for (u32 b = 0; b < n_buckets; b++)
+    if (h_stat[b].w) TRY ((reduce_oversize_bucket<W> (ctx, qc_mode, min_coverage, ctx->opt.kmer_size, b, h_start[b], h_start[b + 1] - h_start[b])));
+  LAUNCH (K_TOTALS, 0, (totals_kernel<<<1, PLAN_THREADS, 0, st>>> (ctx->d_bstat, ctx->d_res->meta, ctx->d_koff, ctx->d_ioff)));
+  CU (cudaMemcpyAsync (ctx->h_res, ctx->d_res, sizeof (ResultBlock), cudaMemcpyDeviceToHost, st));
+  CU (cudaStreamSynchronize (st));
+  return 0;
+}
+
+// reduce -> pack + coverage -> ONE synchronisation (a second one only when a sample turns out larger than the arena
+// it was packed into, or holds buckets that do not fit in shared memory)
+template <int W>
+static int finalise_t (tjb_ctx *ctx, tjb_counter_out *out, int qc_mode)
+{
+  const tjb_opts *opt = &ctx->opt;
+  const int k = opt->kmer_size;
+  cudaStream_t st = ctx->stream;
+  const unsigned long long cap = ctx->list_cap;
+  const u32 grid = (u32) ctx->sm_count;
+  Trace tr;
+  TRY ((reduce_launch<W> (ctx, qc_mode, opt->min_coverage)));
+  u32 *d_meta = ctx->d_res->meta;
+  // elements + group indices + coverage, into the arena (capacity: the previous sample's counts + 25 %, at least 4 Ki)
   const int cov_init = INT_MIN;
-  auto launch_pack = [&] (u32 max_keep, u32 max_idx) -> int {
+  auto launch_pack = [&] () -> int {
+    const u32 max_keep = (u32) ctx->arena_keep_cap, max_idx = (u32) ctx->arena_idx_cap;
     u32 slots = 1024;
     while (slots < 4u * max_keep) slots <<= 1; // two keys per record, load factor <= 0.5
     TRY (ensure (ctx, ctx->cov_tab, (size_t) slots * 8));
-    TRY (ensure (ctx, ctx->out40, (size_t) max_keep * 24)); TRY (ensure (ctx, ctx->idx_i, (size_t) max_idx * 4)); TRY (ensure (ctx, ctx->idx_f, (size_t) max_idx * 4));
     u32 *cov_keys = (u32*) ctx->cov_tab.p, *cov_vals = cov_keys + slots;
+    u64 *o40 = (u64*) ctx->d_arena;
+    int *oi = (int*) (ctx->d_arena + (size_t) max_keep * 40), *of = oi + max_idx;
+    if (ctx->result_dma) {
+      TRY (ensure (ctx, ctx->out40, (size_t) max_keep * 40)); TRY (ensure (ctx, ctx->idx_i, (size_t) max_idx * 4)); TRY (ensure (ctx, ctx->idx_f, (size_t) max_idx * 4));
+      o40 = (u64*) ctx->out40.p; oi = (int*) ctx->idx_i.p; of = (int*) ctx->idx_f.p;
+    }
     CU (cudaMemsetAsync (cov_keys, 0xff, (size_t) slots * 4, st));
     CU (cudaMemsetAsync (cov_vals, 0, (size_t) slots * 4, st));
-    CU (cudaMemcpyAsync (ctx->d_cov, &cov_init, 4, cudaMemcpyHostToDevice, st));
-    LAUNCH (K_PACK, (8 * W + 4 + 24) * (size_t) max_keep + 16 * (size_t) max_idx,
-            (pack_kernel<W><<<grid * 4, 256, 0, st>>> ((const u64*) ctx->rec_a.p, (u32*) ctx->out_cnt.p, (u32*) ctx->out_ii.p, (u32*) ctx->out_if.p, ctx->d_bkt_start, ctx->d_bstat, ctx->d_koff, ctx->d_ioff, ctx->d_meta, k, (u64*) ctx->out40.p, (int*) ctx->idx_i.p, (int*) ctx->idx_f.p, cov_keys, cov_vals, slots - 1, max_keep, max_idx, cap)));
-    LAUNCH (K_COVMAX, 8 * (size_t) slots, (cov_max_kernel<<<nblk (slots, 256 * 8), 256, 0, st>>> (cov_keys, cov_vals, slots, ctx->d_cov)));
+    CU (cudaMemcpyAsync (&ctx->d_res->cov, &cov_init, 4, cudaMemcpyHostToDevice, st));
+    LAUNCH (K_PACK, (8 * W + 4 + 40) * (size_t) ctx->last_keep + 16 * (size_t) ctx->last_idx,
+            (pack_kernel<W><<<grid * 4, 256, 0, st>>> ((const u64*) ctx->okey.p, (u32*) ctx->out_cnt.p, (u32*) ctx->out_ii.p, (u32*) ctx->out_if.p, ctx->d_bkt_start, ctx->d_bstat, ctx->d_koff, ctx->d_ioff, d_meta, k, o40, oi, of, cov_keys, cov_vals, slots - 1, max_keep, max_idx, cap)));
+    LAUNCH (K_COVMAX, 8 * (size_t) slots, (cov_max_kernel<<<nblk (slots, 256 * 8), 256, 0, st>>> (cov_keys, cov_vals, slots, &ctx->d_res->cov)));
     CU (cudaGetLastError ());
+    if (ctx->result_dma) { // one copy of what the previous sample needed (+ 12 %); the rest follows after the counts if it was more
+      const size_t sk = ctx->last_keep ? ctx->last_keep + ctx->last_keep / 8 + 256 : 0, si = ctx->last_idx ? ctx->last_idx + ctx->last_idx / 8 + 256 : 0;
+      const size_t ck = sk < max_keep ? sk : max_keep, ci = si < max_idx ? si : max_idx;
+      if (ck) CU (cudaMemcpyAsync (ctx->h_arena, ctx->out40.p, ck * 40, cudaMemcpyDeviceToHost, st));
+      if (ci) {
+        CU (cudaMemcpyAsync (ctx->h_arena + (size_t) max_keep * 40, ctx->idx_i.p, ci * 4, cudaMemcpyDeviceToHost, st));
+        CU (cudaMemcpyAsync (ctx->h_arena + (size_t) max_keep * 40 + (size_t) max_idx * 4, ctx->idx_f.p, ci * 4, cudaMemcpyDeviceToHost, st));
+      }
+    }
+    CU (cudaMemcpyAsync (ctx->h_res, ctx->d_res, sizeof (ResultBlock), cudaMemcpyDeviceToHost, st));
     return 0;
   };
-  // ---- synchronisation 1: counts --------------------------------------------------------------------------
-  unsigned long long *hs = ctx->h_sync;
-  u32 *hm = (u32*) (hs + 2);
-  CU (cudaMemcpyAsync (hs, ctx->d_counters, 2 * sizeof (unsigned long long), cudaMemcpyDeviceToHost, st));
-  CU (cudaMemcpyAsync (hm, ctx->d_meta, META_WORDS * sizeof (u32), cudaMemcpyDeviceToHost, st));
-  cudaEvent_t ev_counts = get_event (ctx);
-  CU (cudaEventRecord (ev_counts, st));
-  // The counts are only known after this round trip, but samples of one run are alike: launch the last kernels now,
-  // sized from the previous sample (+12 %), so that they run while the host handles the counts; they are launched
-  // again with the exact sizes in the rare case that the guess was too small.
-  bool spec_packed = false;
-  u32 spec_max_keep = 0, spec_max_idx = 0;
-  if (ctx->last_keep && ctx->last_idx) {
-    spec_max_keep = (u32) (ctx->last_keep + ctx->last_keep / 8 + 256);
-    spec_max_idx = (u32) (ctx->last_idx + ctx->last_idx / 8 + 256);
-    TRY (launch_pack (spec_max_keep, spec_max_idx));
-    spec_packed = true;
-  }
-  tr.mark ("enqueue1");
-  // the copy-out below is bound by ONE host thread copying out of the pinned staging buffer (~20 GB/s): when the
-  // previous result was large, wake the host pool now (its wake-up hides under the kernels) and let it share the copy
-  const bool pool_copy = ctx->last_keep * 40 >= ((size_t) 512 << 10) && host_pool () != nullptr;
-  PackerSession copy_session (pool_copy);
-  // The result arrays are malloc()ed (the reference free()s them) and fresh heap memory costs a page fault per 4 KiB
-  // on first touch (measured: up to 1.2 ms for the 2.8 MB of config 2, depending on what the allocator has cached).
-  // The host has nothing to do until the kernels above finish (~0.4 ms), so arrays sized like the previous sample's
-  // result (+12 %) are allocated and touched now; they are trimmed or replaced once the real sizes are known.
+  TRY (ensure_arena (ctx, ctx->last_keep + ctx->last_keep / 8 + 256, ctx->last_idx + ctx->last_idx / 8 + 256));
+  TRY (launch_pack ());
+  tr.mark ("enqueue");
+  // The result arrays of the default mode are malloc()ed (the reference free()s them) and fresh heap memory costs a page
+  // fault per 4 KiB on first touch (measured: up to 1.2 ms for 2.8 MB, depending on what the allocator has cached).
+  // The host has nothing to do until the kernels above finish, so arrays sized like the previous sample's result
+  // (+12 %) are allocated and touched now; they are trimmed or replaced once the real sizes are known.
   struct Spec { void *elem = nullptr, *ii = nullptr, *fi = nullptr; size_t keep = 0, idx = 0;
                 ~Spec () { free (elem); free (ii); free (fi); } } spec;
-  if (ctx->last_keep && ctx->last_idx) {
+  const bool pool_copy = ctx->result_mode == TJB_RESULT_MALLOC && ctx->last_keep * 40 >= ((size_t) 512 << 10) && host_pool () != nullptr;
+  PackerSession copy_session (pool_copy);
+  if (ctx->result_mode == TJB_RESULT_MALLOC && ctx->last_keep && ctx->last_idx) {
     spec.keep = ctx->last_keep + ctx->last_keep / 8 + 256;
     spec.idx = ctx->last_idx + ctx->last_idx / 8 + 256;
     spec.elem = malloc (spec.keep * 40); spec.ii = malloc (spec.idx * 4); spec.fi = malloc (spec.idx * 4);
@@ -525,157 +590,181 @@ static int finalise_t (tjb_ctx *ctx, const tjb_opts *opt, tjb_counter_out *out, 
     } else spec.keep = spec.idx = 0;
   }
   tr.mark ("prealloc");
-  CU (cudaEventSynchronize (ev_counts));
-  ctx->free_events.push_back (ev_counts);
-  tr.mark ("sync1");
-  if (hs[0] > cap) { *overflow = true; return 0; } // the record array overflowed: everything above worked on garbage
-  out->n_raw = (int64_t) hs[0];
-  out->n_skipped_nonacgt = (int64_t) hs[1];
-  if (hs[0] == 0) { out->status = TJB_NO_HT; return 0; }
-  if (hs[0] > (unsigned long long) INT32_MAX) { ctx->err = "more than INT32_MAX tract observations"; return TJB_ERR_TOO_LARGE; }
-  const u32 n = (u32) hs[0], n_buckets = hm[META_NBUCKETS];
-  if (hm[META_NOVERSIZE]) { // rare: buckets that do not fit in shared memory go through the global multi-pass path
-    std::vector<u32> h_start (n_buckets + 1);
-    std::vector<uint4> h_stat (n_buckets);
-    CU (cudaMemcpyAsync (h_start.data (), ctx->d_bkt_start, (n_buckets + 1) * sizeof (u32), cudaMemcpyDeviceToHost, st));
-    CU (cudaMemcpyAsync (h_stat.data (), ctx->d_bstat, n_buckets * sizeof (uint4), cudaMemcpyDeviceToHost, st));
-    CU (cudaStreamSynchronize (st));
-    for (u32 b = 0; b < n_buckets; b++)
-      if (h_stat[b].w) TRY ((reduce_oversize_bucket<W> (ctx, opt, b, h_start[b], h_start[b + 1] - h_start[b])));
-    rec_a = (u64*) ctx->rec_a.p;
-    LAUNCH (K_TOTALS, 0, (totals_kernel<<<1, PLAN_THREADS, 0, st>>> (ctx->d_bstat, ctx->d_meta, ctx->d_koff, ctx->d_ioff)));
-    CU (cudaMemcpyAsync (hm, ctx->d_meta, META_WORDS * sizeof (u32), cudaMemcpyDeviceToHost, st));
-    CU (cudaStreamSynchronize (st));
-  }
-  const u32 n_keep = hm[META_NKEEP], n_idx = hm[META_NIDX];
-  out->n_distinct = hm[META_NDIST];
+  CU (cudaStreamSynchronize (st)); // ---- the synchronisation of the sample
+  tr.mark ("sync");
+  const ResultBlock *hr = ctx->h_res;
+  if (sample_overflowed (ctx)) return TJB_INTERNAL_RETRY;
+  out->n_raw = (int64_t) hr->counters[CTR_NRAW];
+  out->n_skipped_nonacgt = (int64_t) hr->counters[CTR_SKIP];
+  if (hr->counters[CTR_NRAW] == 0) { out->status = TJB_NO_HT; return 0; }
+  if (hr->counters[CTR_NRAW] > (unsigned long long) INT32_MAX) { ctx->err = "more than INT32_MAX tract observations"; return TJB_ERR_TOO_LARGE; }
+  const u32 n_buckets = hr->meta[META_NBUCKETS];
+  bool repack = false;
+  if (hr->meta[META_NOVERSIZE]) { TRY ((reduce_oversize_buckets<W> (ctx, qc_mode, opt->min_coverage))); repack = true; }
+  const u32 n_keep = hr->meta[META_NKEEP], n_idx = hr->meta[META_NIDX];
+  out->n_distinct = hr->meta[META_NDIST];
   // algorithmic bytes of the launches above, now that the counts are known
-  ctx->stats[K_PARTITION].bytes_algorithmic += (int64_t) 16 * W * n;
-  ctx->stats[K_BUCKET].bytes_algorithmic += (int64_t) 8 * W * n + (int64_t) (8 * W + 4) * n_keep + 8 * (int64_t) n_idx;
+  ctx->stats[K_SCAN].bytes_algorithmic += (int64_t) (8 * W + 16) * out->n_raw; // key compared + count word updated per observation
+  ctx->stats[K_PARTITION].bytes_algorithmic += (int64_t) (16 * W + 16) * (int64_t) ctx->last_entries;
+  ctx->stats[K_BUCKET].bytes_algorithmic += (int64_t) (8 * W + 8) * (int64_t) ctx->last_entries + (int64_t) (8 * W + 4) * n_keep + 8 * (int64_t) n_idx;
   ctx->stats[K_TOTALS].bytes_algorithmic += (int64_t) 24 * n_buckets;
   if (!n_keep) { out->status = TJB_NO_HT_AFTER_QC; return 0; }
   if (!n_idx) { out->status = TJB_NO_CTX_ABOVE_COVERAGE; return 0; }
-
   // ---- reference-layout elements, global group indices, coverage (:420-438) ---------------------------------
-  if (!(spec_packed && n_keep <= spec_max_keep && n_idx <= spec_max_idx && !hm[META_NOVERSIZE]))
-    TRY (launch_pack (n_keep, n_idx)); // not launched ahead, or the previous sample's sizes were too small
-  tr.mark ("enqueue2");
-  // copy out into malloc'ed host memory (the reference free()s these).  Measured on B200 for 2.8 MB: the driver's
-  // pageable path 250 us; pinned staging in 4 chunks with the host copy of chunk i under the DMA of chunk i+1 220 us
-  // (the single-threaded host copy into the caller's memory is what is left).
+  const size_t sent_keep = ctx->last_keep ? ctx->last_keep + ctx->last_keep / 8 + 256 : 0, sent_idx = ctx->last_idx ? ctx->last_idx + ctx->last_idx / 8 + 256 : 0;
+  if (repack || n_keep > ctx->arena_keep_cap || n_idx > ctx->arena_idx_cap) {
+    TRY (ensure_arena (ctx, n_keep, n_idx)); // not packed completely: the arena was sized for a smaller sample
+    ctx->last_keep = n_keep; ctx->last_idx = n_idx;
+    TRY (launch_pack ());
+    CU (cudaStreamSynchronize (st));
+  } else if (ctx->result_dma && (n_keep > sent_keep || n_idx > sent_idx)) { // packed, but only a part has been copied
+    const size_t mk = ctx->arena_keep_cap, mi = ctx->arena_idx_cap;
+    CU (cudaMemcpyAsync (ctx->h_arena, ctx->out40.p, (size_t) n_keep * 40, cudaMemcpyDeviceToHost, st));
+    CU (cudaMemcpyAsync (ctx->h_arena + mk * 40, ctx->idx_i.p, (size_t) n_idx * 4, cudaMemcpyDeviceToHost, st));
+    CU (cudaMemcpyAsync (ctx->h_arena + mk * 40 + mi * 4, ctx->idx_f.p, (size_t) n_idx * 4, cudaMemcpyDeviceToHost, st));
+    CU (cudaStreamSynchronize (st));
+  }
+  tr.mark ("pack");
   ctx->last_keep = n_keep; ctx->last_idx = n_idx;
-  if (spec.keep >= n_keep && spec.idx >= n_idx) { // allocated ahead: give back what is not needed
-    void *e = realloc (spec.elem, (size_t) n_keep * 40), *a = realloc (spec.ii, (size_t) n_idx * 4), *b = realloc (spec.fi, (size_t) n_idx * 4);
-    out->elem = e ? e : spec.elem; out->idx_initial = (int32_t*) (a ? a : spec.ii); out->idx_final = (int32_t*) (b ? b : spec.fi);
-    spec.elem = spec.ii = spec.fi = nullptr;
+  const char *a_elem = ctx->h_arena, *a_ii = ctx->h_arena + ctx->arena_keep_cap * 40, *a_fi = a_ii + ctx->arena_idx_cap * 4;
+  if (ctx->result_mode == TJB_RESULT_ARENA) { // the caller reads the arena; valid until this context counts its next sample
+    out->elem = (void*) a_elem; out->idx_initial = (int32_t*) a_ii; out->idx_final = (int32_t*) a_fi;
+    out->arena = 1;
   } else {
-    out->elem = malloc ((size_t) n_keep * 40);
-    out->idx_initial = (int32_t*) malloc ((size_t) n_idx * 4);
-    out->idx_final = (int32_t*) malloc ((size_t) n_idx * 4);
+    if (spec.keep >= n_keep && spec.idx >= n_idx) { // allocated ahead: give back what is not needed
+      void *e = realloc (spec.elem, (size_t) n_keep * 40), *a = realloc (spec.ii, (size_t) n_idx * 4), *b = realloc (spec.fi, (size_t) n_idx * 4);
+      out->elem = e ? e : spec.elem; out->idx_initial = (int32_t*) (a ? a : spec.ii); out->idx_final = (int32_t*) (b ? b : spec.fi);
+      spec.elem = spec.ii = spec.fi = nullptr;
+    } else {
+      out->elem = malloc ((size_t) n_keep * 40);
+      out->idx_initial = (int32_t*) malloc ((size_t) n_idx * 4);
+      out->idx_final = (int32_t*) malloc ((size_t) n_idx * 4);
+    }
+    if (!out->elem || !out->idx_initial || !out->idx_final) { ctx->err = "malloc failed"; return TJB_ERR_NOMEM; }
+    if (pool_copy) {
+      std::lock_guard<std::mutex> lk (g_packer_run_mu);
+      tjb_packer_copy (g_packer, out->elem, a_elem, (size_t) n_keep * 40);
+    } else memcpy (out->elem, a_elem, (size_t) n_keep * 40);
+    memcpy (out->idx_initial, a_ii, (size_t) n_idx * 4);
+    memcpy (out->idx_final, a_fi, (size_t) n_idx * 4);
+    tr.mark ("copy");
   }
-  if (!out->elem || !out->idx_initial || !out->idx_final) { ctx->err = "malloc failed"; return TJB_ERR_NOMEM; }
-  int cov = 0;
-  {
-    // pinned staging in chunks: the DMA of chunk i+1 overlaps the host copy of chunk i into the caller's memory
-    // an element crosses PCIe as its 24 varying bytes; the host appends the constant 16 while it copies
-    const size_t eb = (size_t) n_keep * 24, ib = (size_t) n_idx * 4, total = eb + 2 * ib + 16;
-    if (total > ctx->h_out_cap) {
-      if (ctx->h_out) CU (cudaFreeHost (ctx->h_out));
-      ctx->h_out = nullptr; ctx->h_out_cap = 0;
-      CU (cudaMallocHost ((void**) &ctx->h_out, total + total / 4));
-      ctx->h_out_cap = total + total / 4;
-    }
-    static const int nch_env = getenv ("TJB_OUT_CHUNKS") ? atoi (getenv ("TJB_OUT_CHUNKS")) : 0;
-    const int NCH = nch_env >= 1 && nch_env <= 8 ? nch_env : 4;
-    cudaEvent_t ev[8];
-    size_t lo[9];
-    for (int c = 0; c <= NCH; c++) lo[c] = (size_t) n_keep * c / NCH; // in elements
-    lo[NCH] = n_keep;
-    // the index arrays travel with the first chunk, so that their host copy runs under the DMA of the later chunks
-    for (int c = 0; c < NCH; c++) {
-      if (c == 0) {
-        CU (cudaMemcpyAsync (ctx->h_out + eb, ctx->idx_i.p, ib, cudaMemcpyDeviceToHost, st));
-        CU (cudaMemcpyAsync (ctx->h_out + eb + ib, ctx->idx_f.p, ib, cudaMemcpyDeviceToHost, st));
-        CU (cudaMemcpyAsync (ctx->h_out + eb + 2 * ib, ctx->d_cov, 4, cudaMemcpyDeviceToHost, st));
-      }
-      CU (cudaMemcpyAsync (ctx->h_out + 24 * lo[c], (const char*) ctx->out40.p + 24 * lo[c], 24 * (lo[c + 1] - lo[c]), cudaMemcpyDeviceToHost, st));
-      ev[c] = get_event (ctx);
-      CU (cudaEventRecord (ev[c], st));
-    }
-    for (int c = 0; c < NCH; c++) {
-      CU (cudaEventSynchronize (ev[c]));
-      if (pool_copy) {
-        std::lock_guard<std::mutex> lk (g_packer_run_mu);
-        tjb_packer_expand (g_packer, (char*) out->elem + 40 * lo[c], ctx->h_out + 24 * lo[c], lo[c + 1] - lo[c]);
-      } else
-        tjb_expand_rows ((char*) out->elem + 40 * lo[c], ctx->h_out + 24 * lo[c], lo[c + 1] - lo[c]);
-      if (c == 0) {
-        memcpy (out->idx_initial, ctx->h_out + eb, ib);
-        memcpy (out->idx_final, ctx->h_out + eb + ib, ib);
-        memcpy (&cov, ctx->h_out + eb + 2 * ib, 4);
-      }
-      ctx->free_events.push_back (ev[c]);
-    }
-  }
-  tr.mark ("d2h_enqueue");
-  CU (cudaStreamSynchronize (st)); // ---- synchronisation 2
-  tr.mark ("sync2");
   out->n_elem = (int32_t) n_keep;
   out->n_idx = (int32_t) n_idx;
-  out->coverage = cov;
+  out->coverage = hr->cov;
   out->status = TJB_OK;
   return 0;
 }
 
-#define TJB_INTERNAL_RETRY 100 // the record array overflowed; ctx->h_sync[0] holds the number of records needed
-
-static int finalise (tjb_ctx *ctx, const tjb_opts *opt, tjb_counter_out *out)
+static int finalise (tjb_ctx *ctx, tjb_counter_out *out)
 {
-  bool overflow = false;
-  int rc = ctx->rec_words == 2 ? finalise_t<2> (ctx, opt, out, &overflow) : finalise_t<3> (ctx, opt, out, &overflow);
-  ctx->pend = false;
-  if (rc == 0 && overflow) return TJB_INTERNAL_RETRY;
-  if (rc == 0) {
-    // scan wrote 8W bytes per record on top of the sequence bytes it read
-    ctx->stats[K_SCAN].bytes_algorithmic += (int64_t) out->n_raw * 8 * ctx->rec_words;
-  }
+  const int qc = qc_mode_of (&ctx->opt);
+  int rc = ctx->rec_words == 2 ? finalise_t<2> (ctx, out, qc) : finalise_t<3> (ctx, out, qc);
+  ctx->in_sample = false;
   cudaStreamSynchronize (ctx->stream);
   resolve_events (ctx);
+  if (rc == TJB_INTERNAL_RETRY) return rc;
   if (rc < 0 || out->status != TJB_OK) { // the reference leaves an "empty counter" (n_elem = 0)
-    free (out->elem); free (out->idx_initial); free (out->idx_final);
+    if (!out->arena) { free (out->elem); free (out->idx_initial); free (out->idx_final); }
     out->elem = nullptr; out->idx_initial = out->idx_final = nullptr;
-    out->n_elem = out->n_idx = 0; out->coverage = 0;
+    out->n_elem = out->n_idx = 0; out->coverage = 0; out->arena = 0;
   }
   return rc;
 }
 
 static void out_reset (tjb_counter_out *out) { memset (out, 0, sizeof (*out)); }
 
-// ---- union of query rows over samples (tjb_union.cuh): pack, LSD sort, heads, emit, index -----------------------
+// ---- union of query rows over samples (tjb_union.cuh): the rows go through the aggregation table and the bucket
+// reduce like the observations of a sample, with nothing filtered --------------------------------------------------
 template <int W>
 static int union_t (tjb_ctx *ctx, const u64 *d_rows, u32 n, int k, u64 *d_union, int64_t *n_union, int *d_index)
 {
   cudaStream_t st = ctx->stream;
-  TRY (grow_records (ctx, n));
-  TRY (ensure (ctx, ctx->rec_b, (size_t) n * W * 8));
-  TRY (ensure (ctx, ctx->heads, (size_t) n * 4)); TRY (ensure (ctx, ctx->pos, (size_t) n * 4));
-  TRY (ensure (ctx, ctx->ptmp, pscan_tmp_elems (n) * 4 + 64));
-  u64 *a = (u64*) ctx->rec_a.p, *b = (u64*) ctx->rec_b.p, *sorted = nullptr;
-  u32 *heads = (u32*) ctx->heads.p, *pos = (u32*) ctx->pos.p;
-  LAUNCH (K_UNION, (24 + 8 * W) * (size_t) n, (rows_to_rec_kernel<W><<<nblk (n, UNI_THREADS), UNI_THREADS, 0, st>>> (d_rows, n, k, a)));
-  TRY ((radix_sort<W> (ctx, a, b, n, tract_digits (W, k), &sorted)));
-  LAUNCH (K_UNION, 16 * W * (size_t) n, (head_kernel<W, 0><<<nblk (n, RED_THREADS), RED_THREADS, 0, st>>> (sorted, n, heads)));
-  TRY (exclusive_scan (ctx, heads, pos, n, (u32*) ctx->ptmp.p, ctx->d_totals + 0));
-  LAUNCH (K_UNION, (8 * W + 32) * (size_t) n, (union_emit_kernel<W><<<nblk (n, UNI_THREADS), UNI_THREADS, 0, st>>> (sorted, heads, pos, n, ctx->d_totals + 0, k, d_union)));
-  if (d_index)
-    LAUNCH (K_UNION, (24 + 4) * (size_t) n, (union_index_kernel<W><<<nblk (n, UNI_THREADS), UNI_THREADS, 0, st>>> (d_rows, n, k, sorted, heads, pos, ctx->d_totals + 0, d_index)));
-  CU (cudaGetLastError ());
-  u32 h_tot = 0;
-  CU (cudaMemcpyAsync (&h_tot, ctx->d_totals, 4, cudaMemcpyDeviceToHost, st));
-  CU (cudaStreamSynchronize (st));
-  resolve_events (ctx);
-  *n_union = h_tot;
-  return 0;
+  tjb_opts opt = {k, 2, 0, 0, 0};
+  for (int attempt = 0; attempt < 4; attempt++) {
+    if (!ctx->want_entries) ctx->want_entries = (size_t) n + 1024; // every row distinct in the worst case
+    const size_t keep_entries = ctx->last_entries;                 // sizes of the samples this context counts stay as they are
+    TRY (begin_sample (ctx, &opt, 0));
+    LAUNCH (K_UNION, (24 + 8 * W + 16) * (size_t) n, (rows_insert_kernel<W><<<nblk (n, UNI_THREADS), UNI_THREADS, 0, st>>> (d_rows, n, k, table_of (ctx), (u64*) ctx->ovf.p, ctx->ovf_capacity, ctx->d_res->counters, ctx->d_bin_hist, ctx->bin_bits)));
+    TRY ((reduce_launch<W> (ctx, QC_KEEP_ALL, INT_MIN)));
+    auto emit = [&] () -> int {
+      LAUNCH (K_UNION, (8 * W + 24) * (size_t) n, (union_rows_kernel<W><<<(u32) ctx->sm_count * 4, UNI_THREADS, 0, st>>> ((const u64*) ctx->okey.p, ctx->d_bkt_start, ctx->d_bstat, ctx->d_koff, ctx->d_res->meta, k, d_union, n, ctx->list_cap)));
+      if (d_index)
+        LAUNCH (K_UNION, (24 + 4) * (size_t) n, (union_index_kernel<<<nblk (n, UNI_THREADS), UNI_THREADS, 0, st>>> (d_rows, n, d_union, ctx->d_res->meta, n, d_index)));
+      CU (cudaGetLastError ());
+      CU (cudaMemcpyAsync (ctx->h_res, ctx->d_res, sizeof (ResultBlock), cudaMemcpyDeviceToHost, st));
+      CU (cudaStreamSynchronize (st));
+      return 0;
+    };
+    TRY (emit ());
+    ctx->in_sample = false;
+    const bool redo = sample_overflowed (ctx);
+    ctx->last_entries = keep_entries;
+    if (redo) continue;
+    if (ctx->h_res->meta[META_NOVERSIZE]) { TRY ((reduce_oversize_buckets<W> (ctx, QC_KEEP_ALL, INT_MIN))); TRY (emit ()); }
+    resolve_events (ctx);
+    *n_union = ctx->h_res->meta[META_NKEEP];
+    return 0;
+  }
+  ctx->err = "union: table overflow persisted";
+  return TJB_ERR_CUDA;
+}
+
+// ---- a sample's table as rows, and rows added to a table (one sample counted in pieces on several GPUs) ------------
+// table entries + overflow list -> rows of W + 1 words {key words without the flag bits, forward | reverse << 32}
+template <int W>
+__global__ void __launch_bounds__ (256)
+table_export_kernel (AggTable tab, const u64 *__restrict__ ovf, const unsigned long long *__restrict__ counters, unsigned long long ovf_capacity,
+                     u64 *__restrict__ rows, unsigned long long *__restrict__ n_rows, unsigned long long max_rows)
+{
+  const size_t stride = (size_t) gridDim.x * 256, n_slots = (size_t) tab.mask + 1;
+  const unsigned long long n_ovf = counters[CTR_OVERFLOW] < ovf_capacity ? counters[CTR_OVERFLOW] : ovf_capacity;
+  for (size_t i = (size_t) blockIdx.x * 256 + threadIdx.x; i < n_slots + n_ovf; i += stride) {
+    Rec<W> key;
+    unsigned long long c;
+    if (i < n_slots) {
+      c = tab.cnt[i];
+      if (!c) continue;
+      key = table_key_at<W> (tab, (u32) i);
+    } else {
+      key = load_rec<W> (ovf, i - n_slots);
+      c = flag_weight (key.w[0]);
+      key.w[0] &= ~3ULL;
+    }
+    const unsigned long long pos = atomicAdd (n_rows, 1ULL);
+    if (pos < max_rows) {
+#pragma unroll
+      for (int j = 0; j < W; j++) rows[(size_t) (W + 1) * pos + j] = key.w[j];
+      rows[(size_t) (W + 1) * pos + W] = c;
+    }
+  }
+}
+
+// rows of another rank's table added to this context's table (sum of counts per strand = what one scan of all the
+// chunks would have counted: + and | are associative)
+template <int W>
+__global__ void __launch_bounds__ (256)
+table_import_kernel (const u64 *__restrict__ rows, unsigned long long n, int k, AggTable tab, u64 *__restrict__ ovf, unsigned long long ovf_capacity,
+                     unsigned long long *__restrict__ counters, u32 *__restrict__ bin_hist, int bin_bits)
+{
+  for (size_t i = (size_t) blockIdx.x * 256 + threadIdx.x; i < n; i += (size_t) gridDim.x * 256) {
+    Rec<W> key;
+#pragma unroll
+    for (int j = 0; j < W; j++) key.w[j] = rows[(size_t) (W + 1) * i + j];
+    unsigned long long c = rows[(size_t) (W + 1) * i + W];
+    const int res = table_add<W> (tab, key, c);
+    if (res == TAB_NEW) { atomicAdd (&counters[CTR_ENTRIES], 1ULL); atomicAdd (&bin_hist[rec_bin<W> (key, k, bin_bits)], 1u); }
+    else if (res == TAB_DEFER) {
+      // The overflow list holds observations of weight 1, not weighted rows.  An entry is only busy for the few
+      // instructions between its claim and its publication, so the row is simply tried again (bounded: nobody is
+      // waited for); if it still cannot be placed the table is too full and the sample is flagged for a redo.
+      int again = TAB_DEFER;
+      for (int t = 0; t < 64 && again == TAB_DEFER; t++) { __nanosleep (200); again = table_add<W> (tab, key, c); }
+      if (again == TAB_NEW) { atomicAdd (&counters[CTR_ENTRIES], 1ULL); atomicAdd (&bin_hist[rec_bin<W> (key, k, bin_bits)], 1u); }
+      else if (again == TAB_DEFER) atomicAdd (&counters[CTR_OVERFLOW], ovf_capacity + 1);
+    }
+  }
+  (void) ovf;
 }
 
 // ---- file feed: one decoder thread per FASTQ file, two pinned chunks each -----------------
@@ -706,6 +795,21 @@ static void file_feed_worker (FileFeed *f, int p, tjb_reader *rd, int device)
     f->cv.notify_all ();
     if (got <= 0) return;
   }
+}
+
+// sequence bytes to expect from a FASTQ/FASTA file, from its size: half of a FASTQ is qualities, gzip -1 shrinks
+// such a file ~4x.  Only sizes the aggregation table of a context's first sample (a wrong guess costs a redo).
+static size_t sequence_bytes_hint (const char *const *files, int n_files)
+{
+  size_t total = 0;
+  for (int f = 0; f < n_files; f++) {
+    struct stat sb;
+    if (stat (files[f], &sb) != 0 || sb.st_size <= 0) return 0;
+    const size_t nl = strlen (files[f]);
+    const bool gz = nl > 3 && strcmp (files[f] + nl - 3, ".gz") == 0;
+    total += (size_t) sb.st_size * (gz ? 4 : 1) / 2;
+  }
+  return total;
 }
 
 // ------------------------------------------------------------------------------------------- C ABI ------
@@ -748,22 +852,22 @@ int tjb_ctx_create (int device, tjb_ctx **pctx)
   if (prop.major < 10) { delete ctx; return TJB_ERR_CUDA; } // kernels are built for sm_100a only
   ctx->sm_count = prop.multiProcessorCount;
   if ((e = cudaStreamCreateWithFlags (&ctx->stream, cudaStreamNonBlocking)) != cudaSuccess) return fail (e);
-  if ((e = cudaMalloc (&ctx->d_counters, 2 * sizeof (unsigned long long))) != cudaSuccess) return fail (e);
+  if ((e = cudaMalloc ((void**) &ctx->d_res, sizeof (ResultBlock))) != cudaSuccess) return fail (e);
+  if ((e = cudaMallocHost ((void**) &ctx->h_res, sizeof (ResultBlock))) != cudaSuccess) return fail (e);
   if ((e = cudaMalloc (&ctx->d_totals, 16 * sizeof (u32))) != cudaSuccess) return fail (e);
   if ((e = cudaMalloc (&ctx->d_tile_ctr, sizeof (u32))) != cudaSuccess) return fail (e);
-  if ((e = cudaMalloc (&ctx->d_cov, sizeof (int))) != cudaSuccess) return fail (e);
   if ((e = cudaStreamCreateWithFlags (&ctx->copy_stream, cudaStreamNonBlocking)) != cudaSuccess) return fail (e);
   if ((e = cudaMalloc (&ctx->d_bin_hist, TJB_MAX_BINS * sizeof (u32))) != cudaSuccess) return fail (e);
   if ((e = cudaMalloc (&ctx->d_lut, TJB_MAX_BINS * sizeof (u32))) != cudaSuccess) return fail (e);
-  if ((e = cudaMalloc (&ctx->d_meta, META_WORDS * sizeof (u32))) != cudaSuccess) return fail (e);
-  if ((e = cudaMallocHost ((void**) &ctx->h_sync, 16 * sizeof (unsigned long long))) != cudaSuccess) return fail (e);
   if ((e = cudaFuncSetAttribute (tjb_scan_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) scan_smem_bytes<2> ())) != cudaSuccess) return fail (e);
   if ((e = cudaFuncSetAttribute (tjb_scan_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) scan_smem_bytes<3> ())) != cudaSuccess) return fail (e);
-  if ((e = cudaFuncSetAttribute (bucket_reduce_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) bucket_smem_bytes<2> ())) != cudaSuccess) return fail (e);
-  if ((e = cudaFuncSetAttribute (bucket_reduce_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) bucket_smem_bytes<3> ())) != cudaSuccess) return fail (e);
+  if ((e = cudaFuncSetAttribute (wbucket_reduce_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) wbucket_smem_bytes<2> ())) != cudaSuccess) return fail (e);
+  if ((e = cudaFuncSetAttribute (wbucket_reduce_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) wbucket_smem_bytes<3> ())) != cudaSuccess) return fail (e);
   cudaEventCreate (&ctx->ev_t0); cudaEventCreate (&ctx->ev_t1);
   cudaEventCreateWithFlags (&ctx->ev_ready, cudaEventDisableTiming);
   for (int i = 0; i < 2; i++) { cudaEventCreateWithFlags (&ctx->ev_copied[i], cudaEventDisableTiming); cudaEventCreateWithFlags (&ctx->ev_scanned[i], cudaEventDisableTiming); }
+  const char *rp = getenv ("TJB_RESULT_PATH"); // "dma": results through a device staging array and the copy engine
+  ctx->result_dma = rp && strcmp (rp, "dma") == 0;
   *pctx = ctx;
   return 0;
 }
@@ -781,19 +885,16 @@ void tjb_ctx_destroy (tjb_ctx *ctx)
     if (ctx->h_exc_val[i]) cudaFreeHost (ctx->h_exc_val[i]);
   }
   DevBuf *bufs[] = {&ctx->d_pk[0], &ctx->d_pk[1], &ctx->d_exc_pos[0], &ctx->d_exc_pos[1], &ctx->d_exc_val[0], &ctx->d_exc_val[1],
-                    &ctx->d_chunk[0], &ctx->d_chunk[1], &ctx->rec_a, &ctx->rec_b, &ctx->hist, &ctx->ptmp, &ctx->heads, &ctx->pos, &ctx->seg,
-                    &ctx->drec, &ctx->dcount, &ctx->keep, &ctx->kpos, &ctx->krec, &ctx->kcount, &ctx->cw, &ctx->csum, &ctx->gkeep,
-                    &ctx->gkpos, &ctx->out40, &ctx->idx_i, &ctx->idx_f, &ctx->out_cnt, &ctx->out_ii, &ctx->out_if, &ctx->cov_tab};
+                    &ctx->d_chunk[0], &ctx->d_chunk[1], &ctx->tab_keys, &ctx->tab_cnt, &ctx->ovf, &ctx->wkey, &ctx->wcnt, &ctx->okey,
+                    &ctx->hist, &ctx->ptmp, &ctx->heads, &ctx->pos, &ctx->seg, &ctx->drec, &ctx->dcount, &ctx->keep, &ctx->kpos, &ctx->krec,
+                    &ctx->cw, &ctx->csum, &ctx->gkeep, &ctx->gkpos, &ctx->out40, &ctx->idx_i, &ctx->idx_f, &ctx->qrows, &ctx->out_cnt, &ctx->out_ii,
+                    &ctx->out_if, &ctx->cov_tab, &ctx->uni_a, &ctx->uni_b, &ctx->b_bkt_start, &ctx->b_cursor, &ctx->b_koff, &ctx->b_ioff, &ctx->b_bstat};
   for (DevBuf *b : bufs) if (b->p) cudaFree (b->p);
   for (int i = 0; i < 4; i++) { if (ctx->h_pinned[i]) cudaFreeHost (ctx->h_pinned[i]); if (ctx->h_free[i]) cudaEventDestroy (ctx->h_free[i]); }
-  if (ctx->d_counters) cudaFree (ctx->d_counters);
-  if (ctx->d_totals) cudaFree (ctx->d_totals);
-  if (ctx->d_tile_ctr) cudaFree (ctx->d_tile_ctr);
-  if (ctx->d_cov) cudaFree (ctx->d_cov);
-  void *small[] = {ctx->d_bin_hist, ctx->d_lut, ctx->d_meta, ctx->b_bkt_start.p, ctx->b_cursor.p, ctx->b_koff.p, ctx->b_ioff.p, ctx->b_bstat.p};
+  void *small[] = {ctx->d_res, ctx->d_totals, ctx->d_tile_ctr, ctx->d_bin_hist, ctx->d_lut};
   for (void *q : small) if (q) cudaFree (q);
-  if (ctx->h_sync) cudaFreeHost (ctx->h_sync);
-  if (ctx->h_out) cudaFreeHost (ctx->h_out);
+  if (ctx->h_res) cudaFreeHost (ctx->h_res);
+  if (ctx->h_arena) cudaFreeHost (ctx->h_arena);
   if (ctx->copy_stream) { cudaStreamSynchronize (ctx->copy_stream); cudaStreamDestroy (ctx->copy_stream); }
   if (ctx->ev_ready) cudaEventDestroy (ctx->ev_ready);
   for (int i = 0; i < 2; i++) { if (ctx->ev_copied[i]) cudaEventDestroy (ctx->ev_copied[i]); if (ctx->ev_scanned[i]) cudaEventDestroy (ctx->ev_scanned[i]); }
@@ -806,6 +907,13 @@ void tjb_ctx_destroy (tjb_ctx *ctx)
 void *tjb_ctx_stream (tjb_ctx *ctx) { return ctx ? (void*) ctx->stream : nullptr; }
 
 int tjb_ctx_set_profiling (tjb_ctx *ctx, int on) { if (!ctx) return TJB_ERR_ARG; ctx->profiling = on; return 0; }
+
+int tjb_ctx_set_result_mode (tjb_ctx *ctx, int mode)
+{
+  if (!ctx || (mode != TJB_RESULT_MALLOC && mode != TJB_RESULT_ARENA)) return TJB_ERR_ARG;
+  ctx->result_mode = mode;
+  return 0;
+}
 
 int tjb_ctx_kernel_stats (tjb_ctx *ctx, tjb_kernel_stat *stats, int max_stats)
 {
@@ -826,26 +934,25 @@ void tjb_ctx_reset_kernel_stats (tjb_ctx *ctx)
 int64_t tjb_ctx_launch_count (const tjb_ctx *ctx) { return ctx ? ctx->launches : 0; }
 int64_t tjb_ctx_htod_bytes (const tjb_ctx *ctx) { return ctx ? ctx->h2d_bytes : 0; }
 
+#define TJB_MAX_ATTEMPTS 5 // a sample is redone with a larger table when it holds more distinct observations than it was sized for
+
 int tjb_count_sample_device (tjb_ctx *ctx, const void *d_seqs, size_t n_bytes, const tjb_opts *opt, tjb_counter_out *out)
 {
   if (!ctx || !out || (n_bytes && !d_seqs)) return TJB_ERR_ARG;
   if (((uintptr_t) d_seqs) & 15) { ctx->err = "device buffer must be 16-byte aligned"; return TJB_ERR_ARG; }
-  size_t want = n_bytes / 16 + 65536; // records; the scan counts what does not fit, then the sample is redone
   int rc = 0;
   Trace tr;
-  for (int attempt = 0; attempt < 3; attempt++) {
+  for (int attempt = 0; attempt < TJB_MAX_ATTEMPTS; attempt++) {
     out_reset (out);
     TRY (begin_sample (ctx, opt, n_bytes));
     CU (cudaEventRecord (ctx->ev_t0, ctx->stream));
-    TRY (grow_records (ctx, want));
-    TRY (launch_scan (ctx, (const uint8_t*) d_seqs, n_bytes, opt));
+    TRY (launch_scan (ctx, (const uint8_t*) d_seqs, n_bytes));
     tr.mark ("device:scan_enqueue");
-    rc = finalise (ctx, opt, out);
+    rc = finalise (ctx, out);
     tr.mark ("finalise");
     if (rc != TJB_INTERNAL_RETRY) break;
-    want = (size_t) ctx->h_sync[0] + 1024;
   }
-  if (rc == TJB_INTERNAL_RETRY) { ctx->err = "record array overflow persisted"; return TJB_ERR_CUDA; }
+  if (rc == TJB_INTERNAL_RETRY) { ctx->err = "aggregation table overflow persisted"; return TJB_ERR_CUDA; }
   if (rc < 0) return rc;
   CU (cudaEventRecord (ctx->ev_t1, ctx->stream));
   CU (cudaEventSynchronize (ctx->ev_t1));
@@ -894,7 +1001,7 @@ static bool packed_transfer_enabled (tjb_ctx *ctx, size_t n_bytes)
 {
   if (n_bytes < TJB_PACK_MIN_BYTES) return false;
   tjb_packer *pool = host_pool ();
-  if (!pool || tjb_packer_threads (pool) < 4) return false; // PCIe beats a few cores
+  if (!pool || tjb_packer_threads (pool) < 2) return false; // PCIe beats one core
   for (int i = 0; i < 2; i++) {
     if (!ctx->h_pk[i] && cudaMallocHost ((void**) &ctx->h_pk[i], TJB_HOST_CHUNK_BYTES / 4 + 64) != cudaSuccess) return false;
     if (!ctx->h_exc_pos[i] && cudaMallocHost ((void**) &ctx->h_exc_pos[i], (size_t) TJB_PACK_EXC_CAP * 4) != cudaSuccess) return false;
@@ -905,34 +1012,45 @@ static bool packed_transfer_enabled (tjb_ctx *ctx, size_t n_bytes)
   return true;
 }
 
+// can the copy engine read this host range directly (pinned memory)?  Pageable memory is staged by the driver, chunk
+// by chunk and synchronously, so sending such chunks unpacked does not overlap with anything.
+static bool host_range_is_pinned (const void *p)
+{
+  cudaPointerAttributes at;
+  if (cudaPointerGetAttributes (&at, p) != cudaSuccess) { cudaGetLastError (); return false; }
+  return at.type == cudaMemoryTypeHost;
+}
+
 // Host buffer: chunks are copied on the context's copy stream while the previous chunk is scanned on the compute
-// stream (two device chunk buffers); one optimistic pass, redone with the exact record capacity after an overflow.
-// Large inputs cross PCIe 2-bit packed (host threads pack chunk i+1 while chunk i is copied, unpacked and scanned).
+// stream (two device chunk buffers).  Large inputs cross PCIe 2-bit packed (host threads pack chunk i+1 while chunk i is
+// copied, unpacked and scanned); when the caller's memory is pinned, every third chunk travels as it is instead, so that
+// the copy engine (~55 GB/s of plain bytes) and the packer threads (~70 GB/s) work on different chunks at the same time.
 int tjb_count_sample_host (tjb_ctx *ctx, const uint8_t *seqs, size_t n_bytes, const tjb_opts *opt, tjb_counter_out *out)
 {
   if (!ctx || !out || (n_bytes && !seqs)) return TJB_ERR_ARG;
   const size_t max_chunk = TJB_HOST_CHUNK_BYTES;
-  size_t want = n_bytes / 16 + 65536;
   int rc = 0;
   CU (cudaSetDevice (ctx->device));
   const bool packed = packed_transfer_enabled (ctx, n_bytes);
+  static const int mix_env = getenv ("TJB_PLAIN_EVERY") ? atoi (getenv ("TJB_PLAIN_EVERY")) : 3; // 0: every chunk packed
+  const int plain_every = packed && mix_env > 1 && host_range_is_pinned (seqs) ? mix_env : 0;
   PackerSession session (packed);
-  for (int attempt = 0; attempt < 3; attempt++) {
+  for (int attempt = 0; attempt < TJB_MAX_ATTEMPTS; attempt++) {
     out_reset (out);
     TRY (begin_sample (ctx, opt, n_bytes));
     CU (cudaEventRecord (ctx->ev_t0, ctx->stream));
-    TRY (grow_records (ctx, want));
     for (int i = 0; i < 2; i++) TRY (ensure (ctx, ctx->d_chunk[i], (max_chunk < n_bytes ? max_chunk : n_bytes) + 16));
     CU (cudaEventRecord (ctx->ev_ready, ctx->stream));            // workspace set up / previous sample done
     CU (cudaStreamWaitEvent (ctx->copy_stream, ctx->ev_ready, 0));
     size_t off = 0;
-    int which = 0;
+    int which = 0, chunk_no = 0;
     bool used[2] = {false, false};
     while (off < n_bytes) {
       size_t len = whole_reads_prefix (seqs + off, max_chunk < n_bytes - off ? max_chunk : n_bytes - off, n_bytes - off);
       if (!len) { ctx->err = "a single read exceeds the chunk size"; return TJB_ERR_TOO_LARGE; }
       long n_exc = -1;
-      if (packed) {
+      const bool plain_turn = plain_every && (chunk_no % plain_every) == plain_every - 1;
+      if (packed && !plain_turn) {
         if (used[which]) CU (cudaEventSynchronize (ctx->ev_copied[which])); // the slot's pinned staging has been read
         std::lock_guard<std::mutex> lk (g_packer_run_mu);
         n_exc = tjb_packer_run (g_packer, seqs + off, len, ctx->h_pk[which], ctx->h_exc_pos[which], ctx->h_exc_val[which], TJB_PACK_EXC_CAP);
@@ -960,17 +1078,17 @@ int tjb_count_sample_host (tjb_ctx *ctx, const uint8_t *seqs, size_t n_bytes, co
       }
       CU (cudaEventRecord (ctx->ev_copied[which], ctx->copy_stream));
       CU (cudaStreamWaitEvent (ctx->stream, ctx->ev_copied[which], 0));
-      TRY (launch_scan (ctx, (const uint8_t*) ctx->d_chunk[which].p, len, opt));
+      TRY (launch_scan (ctx, (const uint8_t*) ctx->d_chunk[which].p, len));
       CU (cudaEventRecord (ctx->ev_scanned[which], ctx->stream));
       used[which] = true;
       off += len;
       which ^= 1;
+      chunk_no++;
     }
-    rc = finalise (ctx, opt, out);
+    rc = finalise (ctx, out);
     if (rc != TJB_INTERNAL_RETRY) break;
-    want = (size_t) ctx->h_sync[0] + 1024;
   }
-  if (rc == TJB_INTERNAL_RETRY) { ctx->err = "record array overflow persisted"; return TJB_ERR_CUDA; }
+  if (rc == TJB_INTERNAL_RETRY) { ctx->err = "aggregation table overflow persisted"; return TJB_ERR_CUDA; }
   if (rc < 0) return rc;
   CU (cudaEventRecord (ctx->ev_t1, ctx->stream));
   CU (cudaEventSynchronize (ctx->ev_t1));
@@ -980,19 +1098,21 @@ int tjb_count_sample_host (tjb_ctx *ctx, const uint8_t *seqs, size_t n_bytes, co
   return out->status;
 }
 
-int tjb_count_sample_files (tjb_ctx *ctx, const char *const *files, int n_files, const tjb_opts *opt, tjb_counter_out *out)
+static int count_files_once (tjb_ctx *ctx, const char *const *files, int n_files, const tjb_opts *opt, tjb_counter_out *out)
 {
-  if (!ctx || !out || !files || n_files < 1 || n_files > 2) return TJB_ERR_ARG;
   out_reset (out);
-  TRY (begin_sample (ctx, opt, 0));
+  TRY (begin_sample (ctx, opt, sequence_bytes_hint (files, n_files)));
   for (int i = 0; i < 2 * n_files; i++) {
     if (!ctx->h_pinned[i]) CU (cudaMallocHost ((void**) &ctx->h_pinned[i], TJB_CHUNK_BYTES));
     if (!ctx->h_free[i]) CU (cudaEventCreateWithFlags (&ctx->h_free[i], cudaEventDisableTiming));
   }
   for (int i = 0; i < 2; i++) TRY (ensure (ctx, ctx->d_chunk[i], TJB_CHUNK_BYTES));
   CU (cudaEventRecord (ctx->ev_t0, ctx->stream));
+  CU (cudaEventRecord (ctx->ev_ready, ctx->stream));
+  CU (cudaStreamWaitEvent (ctx->copy_stream, ctx->ev_ready, 0));
   // One decoder thread per file (R1 and R2 inflate and parse concurrently; the order of the reads does not matter to
-  // the counter), two pinned chunks each; this thread copies and scans whatever chunk is ready.
+  // the counter), two pinned chunks each; this thread copies (copy stream) and scans (compute stream) whatever chunk
+  // is ready, the copy of a chunk running under the scan of the one before.
   FileFeed feed;
   tjb_reader *rd[2] = {nullptr, nullptr};
   for (int f = 0; f < n_files; f++) {
@@ -1003,7 +1123,7 @@ int tjb_count_sample_files (tjb_ctx *ctx, const char *const *files, int n_files,
   std::thread workers[2];
   for (int f = 0; f < n_files; f++) workers[f] = std::thread (file_feed_worker, &feed, f, rd[f], ctx->device);
   int rc = 0, alive = n_files, turn[2] = {0, 0}, which = 0;
-  bool finished[2] = {false, false};
+  bool finished[2] = {false, false}, used[2] = {false, false};
   while (alive > 0 && rc >= 0) {
     int p = -1;
     {
@@ -1016,13 +1136,16 @@ int tjb_count_sample_files (tjb_ctx *ctx, const char *const *files, int n_files,
       if (sl.got < 0) { rc = (int) sl.got; ctx->err = std::string ("decode failed: ") + files[p]; }
       continue;
     }
-    rc = scan_resolve (ctx, opt); // previous chunk: record count known, overflow handled
-    if (rc >= 0) {
-      cudaError_t e = cudaMemcpyAsync (ctx->d_chunk[which].p, sl.pin, (size_t) sl.got, cudaMemcpyHostToDevice, ctx->stream);
-      if (e == cudaSuccess) e = cudaEventRecord (sl.free_ev, ctx->stream); // the decoder waits for it before refilling
-      if (e != cudaSuccess) { ctx->err = std::string ("chunk copy: ") + cudaGetErrorString (e); rc = TJB_ERR_CUDA; }
-    }
-    if (rc >= 0) rc = scan_launch (ctx, (const uint8_t*) ctx->d_chunk[which].p, (size_t) sl.got, opt);
+    cudaError_t e = cudaSuccess;
+    if (used[which]) e = cudaStreamWaitEvent (ctx->copy_stream, ctx->ev_scanned[which], 0); // device chunk free again
+    if (e == cudaSuccess) e = cudaMemcpyAsync (ctx->d_chunk[which].p, sl.pin, (size_t) sl.got, cudaMemcpyHostToDevice, ctx->copy_stream);
+    if (e == cudaSuccess) e = cudaEventRecord (sl.free_ev, ctx->copy_stream); // the decoder waits for it before refilling
+    if (e == cudaSuccess) e = cudaEventRecord (ctx->ev_copied[which], ctx->copy_stream);
+    if (e == cudaSuccess) e = cudaStreamWaitEvent (ctx->stream, ctx->ev_copied[which], 0);
+    if (e != cudaSuccess) { ctx->err = std::string ("chunk copy: ") + cudaGetErrorString (e); rc = TJB_ERR_CUDA; }
+    if (rc >= 0) rc = launch_scan (ctx, (const uint8_t*) ctx->d_chunk[which].p, (size_t) sl.got);
+    if (rc >= 0 && cudaEventRecord (ctx->ev_scanned[which], ctx->stream) != cudaSuccess) rc = TJB_ERR_CUDA;
+    used[which] = true;
     { std::lock_guard<std::mutex> lk (feed.mu); sl.state = 0; }
     feed.cv.notify_all ();
     turn[p] ^= 1;
@@ -1033,11 +1156,24 @@ int tjb_count_sample_files (tjb_ctx *ctx, const char *const *files, int n_files,
   for (int f = 0; f < n_files; f++) { workers[f].join (); tjb_reader_close (rd[f]); }
   if (rc < 0) return rc;
   for (int f = 0; f < n_files; f++) { out->n_reads += feed.n_reads[f]; out->n_bases += feed.n_bases[f]; out->ms_decode += feed.ms_decode[f]; }
-  TRY (scan_resolve (ctx, opt));
-  rc = finalise (ctx, opt, out);
+  return finalise (ctx, out);
+}
+
+int tjb_count_sample_files (tjb_ctx *ctx, const char *const *files, int n_files, const tjb_opts *opt, tjb_counter_out *out)
+{
+  if (!ctx || !out || !files || n_files < 1 || n_files > 2) return TJB_ERR_ARG;
+  int rc = 0;
+  for (int attempt = 0; attempt < TJB_MAX_ATTEMPTS; attempt++) { // a redo reads the files again
+    rc = count_files_once (ctx, files, n_files, opt, out);
+    if (rc != TJB_INTERNAL_RETRY) break;
+  }
+  if (rc == TJB_INTERNAL_RETRY) { ctx->err = "aggregation table overflow persisted"; return TJB_ERR_CUDA; }
   if (rc < 0) return rc;
   CU (cudaEventRecord (ctx->ev_t1, ctx->stream));
   CU (cudaEventSynchronize (ctx->ev_t1));
+  float ms = 0.f;
+  cudaEventElapsedTime (&ms, ctx->ev_t0, ctx->ev_t1);
+  out->ms_device = ms;
   size_t nl = strlen (files[0]);
   out->name = (char*) malloc (nl + 1);
   if (out->name) memcpy (out->name, files[0], nl + 1);
@@ -1061,6 +1197,98 @@ int tjb_count_sample (const char *const *files, int n_files, const tjb_opts *opt
   return tjb_count_sample_files (ctx, files, n_files, opt, out);
 }
 
+int tjb_device_count (void)
+{
+  int n = 0;
+  if (cudaGetDeviceCount (&n) != cudaSuccess) { cudaGetLastError (); return 0; }
+  return n;
+}
+
+// ---- one sample in pieces: read chunks counted on several GPUs, their tables exchanged and added ------
+int tjb_sample_begin (tjb_ctx *ctx, const tjb_opts *opt, size_t n_bytes_hint)
+{
+  if (!ctx) return TJB_ERR_ARG;
+  TRY (begin_sample (ctx, opt, n_bytes_hint));
+  CU (cudaEventRecord (ctx->ev_t0, ctx->stream));
+  return 0;
+}
+
+int64_t tjb_ctx_table_capacity (const tjb_ctx *ctx) { return ctx ? (int64_t) (ctx->tab_slots / 2) : 0; }
+
+int tjb_ctx_reserve_entries (tjb_ctx *ctx, int64_t n_entries)
+{
+  if (!ctx || n_entries < 0) return TJB_ERR_ARG;
+  ctx->want_entries = (size_t) n_entries + (size_t) n_entries / 8 + 4096;
+  return 0;
+}
+
+int tjb_sample_scan_device (tjb_ctx *ctx, const void *d_seqs, size_t n_bytes)
+{
+  if (!ctx || !ctx->in_sample || (n_bytes && !d_seqs)) return TJB_ERR_ARG;
+  if (((uintptr_t) d_seqs) & 15) { ctx->err = "device buffer must be 16-byte aligned"; return TJB_ERR_ARG; }
+  return launch_scan (ctx, (const uint8_t*) d_seqs, n_bytes);
+}
+
+int tjb_sample_export (tjb_ctx *ctx, void *d_rows, int64_t max_rows, int64_t *n_rows, int32_t *row_words)
+{
+  if (!ctx || !ctx->in_sample || !n_rows || max_rows < 0) return TJB_ERR_ARG;
+  const int W = ctx->rec_words;
+  if (row_words) *row_words = W + 1;
+  if (ctx->exported_rows < 0) { // table -> rows, once per sample (kept in the context until the sample ends)
+    const size_t cap_rows = ctx->list_cap;
+    TRY (ensure (ctx, ctx->uni_a, cap_rows * (W + 1) * 8 + 16));
+    unsigned long long *d_n = (unsigned long long*) ((char*) ctx->uni_a.p + cap_rows * (W + 1) * 8);
+    CU (cudaMemsetAsync (d_n, 0, 8, ctx->stream));
+    const u32 g = (u32) ctx->sm_count * 8;
+    if (W == 2) LAUNCH (K_TABLE, 8 * ctx->tab_slots, (table_export_kernel<2><<<g, 256, 0, ctx->stream>>> (table_of (ctx), (const u64*) ctx->ovf.p, ctx->d_res->counters, ctx->ovf_capacity, (u64*) ctx->uni_a.p, d_n, cap_rows)));
+    else LAUNCH (K_TABLE, 8 * ctx->tab_slots, (table_export_kernel<3><<<g, 256, 0, ctx->stream>>> (table_of (ctx), (const u64*) ctx->ovf.p, ctx->d_res->counters, ctx->ovf_capacity, (u64*) ctx->uni_a.p, d_n, cap_rows)));
+    CU (cudaGetLastError ());
+    unsigned long long h_n = 0;
+    CU (cudaMemcpyAsync (&h_n, d_n, 8, cudaMemcpyDeviceToHost, ctx->stream));
+    CU (cudaMemcpyAsync (ctx->h_res, ctx->d_res, sizeof (ResultBlock), cudaMemcpyDeviceToHost, ctx->stream));
+    CU (cudaStreamSynchronize (ctx->stream));
+    if (h_n > cap_rows || ctx->h_res->counters[CTR_OVERFLOW] > ctx->ovf_capacity) {
+      ctx->want_entries = (size_t) h_n * 2 + 4096; // the caller starts the sample again (tjb_sample_begin sizes from this)
+      ctx->err = "aggregation table too small for this chunk: begin the sample again";
+      return TJB_ERR_TOO_LARGE;
+    }
+    ctx->exported_rows = (int64_t) h_n;
+  }
+  *n_rows = ctx->exported_rows;
+  if (d_rows) {
+    const int64_t n = ctx->exported_rows < max_rows ? ctx->exported_rows : max_rows;
+    if (n) CU (cudaMemcpyAsync (d_rows, ctx->uni_a.p, (size_t) n * (W + 1) * 8, cudaMemcpyDeviceToDevice, ctx->stream));
+    CU (cudaStreamSynchronize (ctx->stream));
+  }
+  return 0;
+}
+
+int tjb_sample_import (tjb_ctx *ctx, const void *d_rows, int64_t n_rows)
+{
+  if (!ctx || !ctx->in_sample || n_rows < 0 || (n_rows && !d_rows)) return TJB_ERR_ARG;
+  if (!n_rows) return 0;
+  const u32 g = (u32) (nblk ((size_t) n_rows, 256) < (size_t) ctx->sm_count * 8 ? nblk ((size_t) n_rows, 256) : (size_t) ctx->sm_count * 8);
+  if (ctx->rec_words == 2) LAUNCH (K_TABLE, 40 * (size_t) n_rows, (table_import_kernel<2><<<g, 256, 0, ctx->stream>>> ((const u64*) d_rows, (unsigned long long) n_rows, ctx->opt.kmer_size, table_of (ctx), (u64*) ctx->ovf.p, ctx->ovf_capacity, ctx->d_res->counters, ctx->d_bin_hist, ctx->bin_bits)));
+  else LAUNCH (K_TABLE, 48 * (size_t) n_rows, (table_import_kernel<3><<<g, 256, 0, ctx->stream>>> ((const u64*) d_rows, (unsigned long long) n_rows, ctx->opt.kmer_size, table_of (ctx), (u64*) ctx->ovf.p, ctx->ovf_capacity, ctx->d_res->counters, ctx->d_bin_hist, ctx->bin_bits)));
+  CU (cudaGetLastError ());
+  return 0;
+}
+
+int tjb_sample_finalise (tjb_ctx *ctx, tjb_counter_out *out)
+{
+  if (!ctx || !ctx->in_sample || !out) return TJB_ERR_ARG;
+  out_reset (out);
+  int rc = finalise (ctx, out);
+  if (rc == TJB_INTERNAL_RETRY) { ctx->err = "aggregation table too small for this sample: begin the sample again"; return TJB_ERR_TOO_LARGE; }
+  if (rc < 0) return rc;
+  CU (cudaEventRecord (ctx->ev_t1, ctx->stream));
+  CU (cudaEventSynchronize (ctx->ev_t1));
+  float ms = 0.f;
+  cudaEventElapsedTime (&ms, ctx->ev_t0, ctx->ev_t1);
+  out->ms_device = ms;
+  return out->status;
+}
+
 // ---- cross-sample exchange: query rows and their union (tjb_union.cuh) ------------------------------------------
 int tjb_query_rows (const tjb_counter_out *in, uint64_t *rows)
 {
@@ -1075,6 +1303,23 @@ int tjb_query_rows (const tjb_counter_out *in, uint64_t *rows)
   return in->n_idx;
 }
 
+int tjb_query_rows_device (tjb_ctx *ctx, void *d_rows, int64_t max_rows)
+{
+  if (!ctx || max_rows < 0 || (max_rows && !d_rows)) return TJB_ERR_ARG;
+  if (ctx->in_sample) { ctx->err = "query rows are taken from the last counted sample"; return TJB_ERR_ARG; }
+  const int64_t n_idx = (int64_t) ctx->last_idx;
+  if (ctx->h_res->meta[META_NIDX] != (u32) n_idx) return 0; // the last sample was dropped: no rows
+  if (n_idx > max_rows) { ctx->err = "query row buffer too small"; return TJB_ERR_ARG; }
+  if (!n_idx) return 0;
+  const u32 g = (u32) ctx->sm_count * 4;
+  const int k = ctx->opt.kmer_size;
+  if (ctx->rec_words == 2) LAUNCH (K_UNION, 40 * (size_t) n_idx, (query_rows_kernel<2><<<g, UNI_THREADS, 0, ctx->stream>>> ((const u64*) ctx->okey.p, (const u32*) ctx->out_ii.p, ctx->d_bkt_start, ctx->d_bstat, ctx->d_ioff, ctx->d_res->meta, k, (u64*) d_rows, (u32) max_rows, ctx->list_cap)));
+  else LAUNCH (K_UNION, 48 * (size_t) n_idx, (query_rows_kernel<3><<<g, UNI_THREADS, 0, ctx->stream>>> ((const u64*) ctx->okey.p, (const u32*) ctx->out_ii.p, ctx->d_bkt_start, ctx->d_bstat, ctx->d_ioff, ctx->d_res->meta, k, (u64*) d_rows, (u32) max_rows, ctx->list_cap)));
+  CU (cudaGetLastError ());
+  CU (cudaStreamSynchronize (ctx->stream));
+  return (int) n_idx;
+}
+
 int tjb_union_queries_device (tjb_ctx *ctx, const void *d_rows, int64_t n_rows, int kmer_size, void *d_union, int64_t *n_union, void *d_index)
 {
   if (!ctx || !n_union || n_rows < 0 || (n_rows && (!d_rows || !d_union))) return TJB_ERR_ARG;
@@ -1084,8 +1329,6 @@ int tjb_union_queries_device (tjb_ctx *ctx, const void *d_rows, int64_t n_rows, 
   if (!n_rows) return 0;
   CU (cudaSetDevice (ctx->device));
   const int W = tjb_rec_words (kmer_size);
-  if (W != ctx->rec_words) { ctx->rec_words = W; ctx->rec_capacity = ctx->rec_a.cap / (W * sizeof (u64)); }
-  ctx->n_raw_known = 0; // nothing of a previous sample needs to survive a reallocation
   return W == 2 ? union_t<2> (ctx, (const u64*) d_rows, (u32) n_rows, kmer_size, (u64*) d_union, n_union, (int*) d_index)
                 : union_t<3> (ctx, (const u64*) d_rows, (u32) n_rows, kmer_size, (u64*) d_union, n_union, (int*) d_index);
 }
@@ -1093,8 +1336,10 @@ int tjb_union_queries_device (tjb_ctx *ctx, const void *d_rows, int64_t n_rows, 
 void tjb_counter_out_free (tjb_counter_out *out)
 {
   if (!out) return;
-  free (out->elem); free (out->idx_initial); free (out->idx_final); free (out->name);
+  if (!out->arena) { free (out->elem); free (out->idx_initial); free (out->idx_final); }
+  free (out->name);
   out->elem = nullptr; out->idx_initial = out->idx_final = nullptr; out->name = nullptr;
+  out->arena = 0;
 }
 
 } // extern "C"

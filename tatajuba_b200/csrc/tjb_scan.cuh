@@ -30,6 +30,7 @@
 // Windows own the code runs that START inside their owned bytes.
 #pragma once
 #include "tjb_common.cuh"
+#include "tjb_table.cuh"
 #include "tjb_bucket.cuh" // rec_bin(): the scan also accumulates the bin histogram the partition plan is made from
 
 #define SCAN_WARPS 8
@@ -148,7 +149,7 @@ __device__ __forceinline__ u32 prmt (u32 a, u32 b, u32 sel)
 
 template <int W>
 __global__ void __launch_bounds__ (SCAN_THREADS, SCAN_CTAS_PER_SM)
-tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_len, u64 *__restrict__ out,
+tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_len, AggTable tab, u64 *__restrict__ out,
                  unsigned long long capacity, unsigned long long *__restrict__ counters, long long n_tiles,
                  u32 *__restrict__ bin_hist, int bin_bits, u32 *__restrict__ tile_ctr)
 {
@@ -201,22 +202,39 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
       }
     }
   };
-  auto flush = [&] () { // staged records -> global array, one atomicAdd
-    unsigned long long base = 0;
-    if (lane == 0) base = atomicAdd (&counters[0], (unsigned long long) nrec);
-    base = __shfl_sync (0xffffffffu, base, 0);
-    if (W == 2 && base + nrec <= capacity) { // one record = one 16-byte store
-      const ulonglong2 *src = reinterpret_cast<const ulonglong2*> (S->rec);
-      ulonglong2 *dst = reinterpret_cast<ulonglong2*> (out) + base;
-      static_assert (SW_RCAP (2) <= 64, "two stores per lane cover the staging area");
-      if ((u32) lane < nrec) dst[lane] = src[lane];
-      if ((u32) lane + 32 < nrec) dst[lane + 32] = src[lane + 32];
-    } else {
-      for (u32 i = lane; i < nrec * W; i += 32) {
-        const unsigned long long r = base + i / W;
-        if (r < capacity) out[r * W + (i % W)] = S->rec[i];
+  // one observation into the aggregation table (tjb_table.cuh); a new entry is binned for the partition plan
+  auto add_obs = [&] (const Rec<W> &r) -> int {
+    Rec<W> key = r;
+    key.w[0] &= ~3ULL;
+    const int res = table_add<W> (tab, key, flag_weight (r.w[0]));
+    if (res == TAB_NEW) atomicAdd (&bin_hist[rec_bin<W> (key, k, bin_bits)], 1u);
+    return res;
+  };
+  auto flush = [&] () { // staged observations -> aggregation table; the few that cannot be placed -> overflow list
+    u32 n_new = 0;
+    for (u32 i0 = 0; i0 < nrec; i0 += 32) {
+      const u32 i = i0 + lane;
+      int res = TAB_ADDED;
+      Rec<W> r;
+      if (i < nrec) {
+#pragma unroll
+        for (int j = 0; j < W; j++) r.w[j] = S->rec[i * W + j];
+        res = add_obs (r);
+      }
+      n_new += __popc (__ballot_sync (0xffffffffu, res == TAB_NEW));
+      const u32 dm = __ballot_sync (0xffffffffu, res == TAB_DEFER);
+      if (dm) {
+        unsigned long long base = 0;
+        if (lane == 0) base = atomicAdd (&counters[CTR_OVERFLOW], (unsigned long long) __popc (dm));
+        base = __shfl_sync (0xffffffffu, base, 0);
+        if (res == TAB_DEFER) {
+          const unsigned long long pos = base + __popc (dm & ((1u << lane) - 1));
+          if (pos < capacity) store_rec<W> (out, pos, r);
+          atomicAdd (&bin_hist[rec_bin<W> (r, k, bin_bits)], 1u);
+        }
       }
     }
+    if (lane == 0 && n_new) atomicAdd (&counters[CTR_ENTRIES], (unsigned long long) n_new);
     nrec = 0;
     __syncwarp ();
   };
@@ -261,7 +279,6 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
             if (gray < 2) { ctx0 = gl64 ^ ((gl64 >> 1) & m5); ctx1 = gr64 ^ ((gr64 >> 1) & m5); } // A / C tract: forward strand, gray -> A0 C1 G2 T3, :233-238
             else { ctx0 = revcomp_gray (gr64, k, kmask); ctx1 = revcomp_gray (gl64, k, kmask); } // T / G tract: reverse complement, :239-246
             r = pack_rec<W> (ctx0, ctx1, gray & 1, sext_field (len, 10), gray < 2 ? 1 : 2, k);
-            atomicAdd (&bin_hist[rec_bin<W> (r, k, bin_bits)], 1u);
             emit = true;
           }
         }
@@ -291,11 +308,15 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
         }
         return ok;
       };
-      auto emit_slow = [&] (u64 ctx0, u64 ctx1, int code, long long len) { // rare path: straight to global
-        Rec<W> q = pack_rec<W> (ctx0, ctx1, code < 2 ? code : 3 - code, sext_field (len, 10), code < 2 ? 1 : 2, k);
-        atomicAdd (&bin_hist[rec_bin<W> (q, k, bin_bits)], 1u);
-        const unsigned long long pos = atomicAdd (&counters[0], 1ULL);
-        if (pos < capacity) store_rec<W> (out, pos, q);
+      auto emit_slow = [&] (u64 ctx0, u64 ctx1, int code, long long len) { // rare path: one lane on its own
+        const Rec<W> q = pack_rec<W> (ctx0, ctx1, code < 2 ? code : 3 - code, sext_field (len, 10), code < 2 ? 1 : 2, k);
+        const int res = add_obs (q);
+        if (res == TAB_NEW) atomicAdd (&counters[CTR_ENTRIES], 1ULL);
+        else if (res == TAB_DEFER) {
+          const unsigned long long pos = atomicAdd (&counters[CTR_OVERFLOW], 1ULL);
+          if (pos < capacity) store_rec<W> (out, pos, q);
+          atomicAdd (&bin_hist[rec_bin<W> (q, k, bin_bits)], 1u);
+        }
       };
       long long ps = g0 + s;
       while (ps < n) {
@@ -492,5 +513,5 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
   if (nrec) flush ();
 #pragma unroll
   for (int d = 16; d; d >>= 1) nskip += __shfl_xor_sync (0xffffffffu, nskip, d);
-  if (lane == 0 && nskip) atomicAdd (&counters[1], (unsigned long long) nskip);
+  if (lane == 0 && nskip) atomicAdd (&counters[CTR_SKIP], (unsigned long long) nskip);
 }

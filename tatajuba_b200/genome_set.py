@@ -114,6 +114,157 @@ def union_queries(ctx, tables, kmer_size):
     return union, per_sample
 
 
+# ---- device-resident exchange: nothing of the tables crosses PCIe between the count and the union ---------------------
+def query_rows_device(ctx, hc):
+    """(n_idx, 3) int64 CUDA tensor of the query rows of the sample `ctx` counted LAST (must be `hc`), written by the
+    device from the device-resident result (tjb_query_rows_device)"""
+    import torch
+    n = hc.n_idx if hc.status == TJB_OK else 0
+    t = torch.empty((max(n, 1), ROW_WORDS), dtype=torch.int64, device=torch.device("cuda", ctx.device))
+    got = ctx.query_rows_device(t.data_ptr(), n) if n else 0
+    return t[:got]
+
+
+def allgather_tables_device(local_tables, n_samples, group=None):
+    """like allgather_tables, for {sample id: (n, 3) int64 CUDA tensor}; the rows stay on the devices (NCCL moves them
+    GPU to GPU).  Returns (rows of all samples concatenated in global sample order, rows per sample) — only the
+    per-sample row counts visit the host."""
+    import torch
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()):
+        assert sorted(local_tables) == list(range(n_samples)), "single process: every sample must be local"
+        ts = [local_tables[s].reshape(-1, ROW_WORDS) for s in range(n_samples)]
+        return (torch.cat(ts) if ts else torch.empty((0, ROW_WORDS), dtype=torch.int64)), [int(t.shape[0]) for t in ts]
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    mine = samples_of_rank(n_samples, rank, world)
+    assert sorted(local_tables) == mine, f"rank {rank} must hold samples {mine}"
+    dev = local_tables[mine[0]].device if mine else torch.device("cuda", torch.cuda.current_device())
+    per_rank = (n_samples + world - 1) // world
+    counts = torch.zeros(per_rank, dtype=torch.int64)
+    for i, s in enumerate(mine):
+        counts[i] = local_tables[s].shape[0]
+    all_counts = torch.empty(world * per_rank, dtype=torch.int64, device=dev)
+    dist.all_gather_into_tensor(all_counts, counts.to(dev), group=group)
+    all_counts = all_counts.cpu().numpy().reshape(world, per_rank)
+    pad_rows = max(int(all_counts.sum(axis=1).max()), 1)
+    send = torch.zeros((pad_rows, ROW_WORDS), dtype=torch.int64, device=dev)
+    off = 0
+    for s in mine:
+        n = local_tables[s].shape[0]
+        send[off:off + n] = local_tables[s]
+        off += n
+    recv = torch.empty((world, pad_rows, ROW_WORDS), dtype=torch.int64, device=dev)
+    dist.all_gather_into_tensor(recv.view(-1), send.view(-1), group=group)
+    pieces, sizes = [None] * n_samples, [0] * n_samples
+    for r in range(world):
+        off = 0
+        for i, s in enumerate(samples_of_rank(n_samples, r, world)):
+            n = int(all_counts[r, i])
+            pieces[s], sizes[s] = recv[r, off:off + n], n
+            off += n
+    return torch.cat(pieces), sizes
+
+
+def union_queries_device(ctx, d_rows, kmer_size):
+    """d_rows: (n, 3) int64 CUDA tensor.  -> (union rows (n_union, 3) int64 CUDA tensor in the reference's descending
+    order, index of every input row in the union (n,) int32 CUDA tensor)"""
+    import torch
+    lib = _lib.load()
+    n = int(d_rows.shape[0])
+    d_rows = d_rows.contiguous()
+    d_union = torch.empty_like(d_rows)
+    d_index = torch.empty(max(n, 1), dtype=torch.int32, device=d_rows.device)
+    n_union = C.c_int64(0)
+    torch.cuda.current_stream(d_rows.device).synchronize()  # the rows were produced on torch's stream
+    rc = lib.tjb_union_queries_device(ctx.h, C.c_void_p(d_rows.data_ptr()), n, int(kmer_size),
+                                      C.c_void_p(d_union.data_ptr()), C.byref(n_union), C.c_void_p(d_index.data_ptr()))
+    ctx._check(rc)
+    return d_union[: n_union.value], d_index[:n]
+
+
+# ---- one sample in pieces: read chunks on several GPUs (SURVEY.md 8e "by read chunk within a sample") -----------------
+def count_sample_sharded(ctx, d_ptr, n_bytes, opt, group=None, total_bytes_hint=0):
+    """Every rank scans ITS chunk of the sample's reads (d_ptr / n_bytes: device-resident, whole reads) into its own
+    aggregation table; the tables are exchanged as rows with one allgather (NCCL over NVLink; gloo cannot move device
+    rows) and every rank adds the other ranks' rows to its table (counts per strand add up to what one scan of all the
+    reads would have counted), so that QC, context groups and coverage (hopo_counter.c:367-438) run on the complete
+    table.  Every rank returns the same HopoCounter, bit-identical to counting the whole sample on one GPU."""
+    import torch
+    import torch.distributed as dist
+    world = dist.get_world_size(group) if dist.is_initialized() else 1
+    rank = dist.get_rank(group) if dist.is_initialized() else 0
+    dev = torch.device("cuda", ctx.device)
+    for _attempt in range(4):
+        ctx.sample_begin(opt, total_bytes_hint or n_bytes * world)
+        ctx.sample_scan_device(d_ptr, n_bytes)
+        if world == 1:
+            return ctx.sample_finalise()
+        try:
+            n_rows, words = ctx.sample_export()
+            failed = 0
+        except Exception:  # table too small for this chunk: every rank starts again (the context remembers the size)
+            n_rows, words, failed = 0, tjb_rec_words(opt.kmer_size) + 1, 1
+        info = torch.tensor([n_rows, failed, ctx.table_capacity()], dtype=torch.int64, device=dev)
+        all_info = torch.empty((world, 3), dtype=torch.int64, device=dev)
+        dist.all_gather_into_tensor(all_info.view(-1), info, group=group)
+        all_info = all_info.cpu().numpy()
+        total = int(all_info[:, 0].sum())  # upper bound of the distinct observations of the whole sample
+        if all_info[:, 1].any() or (all_info[:, 2] < total).any():
+            # some rank's table cannot take the combined rows: every rank knows it and starts again, sized for the sum
+            ctx.reserve_entries(max(total, 2 * int(all_info[:, 0].max())))
+            continue
+        pad = max(int(all_info[:, 0].max()), 1)
+        send = torch.zeros((pad, words), dtype=torch.int64, device=dev)
+        if n_rows:
+            ctx.sample_export(send.data_ptr(), pad)
+        recv = torch.empty((world, pad, words), dtype=torch.int64, device=dev)
+        dist.all_gather_into_tensor(recv.view(-1), send.view(-1), group=group)
+        torch.cuda.current_stream(dev).synchronize()
+        for r in range(world):
+            if r != rank and all_info[r, 0]:
+                ctx.sample_import(recv[r].data_ptr(), int(all_info[r, 0]))
+        return ctx.sample_finalise()
+    raise RuntimeError("count_sample_sharded: aggregation table overflow persisted")
+
+
+def tjb_rec_words(k):
+    return 2 if k <= 26 else 3
+
+
+# ---- many samples per GPU: the reference's `#pragma omp parallel for schedule(dynamic)` over samples ------------------
+def count_samples(contexts, n_samples, count_one, on_done=None):
+    """Deals samples 0..n_samples-1 dynamically to `contexts` (tjb contexts of one or several devices, e.g. two per
+    GPU so that sample i's copy-out and host work overlap sample i+1's copy-in and scan), one host thread per context,
+    like the reference's OpenMP loop (src/genome_set.c:66-68).  count_one(ctx, sample) -> HopoCounter runs on the
+    context's thread (the library call releases the GIL); on_done(ctx, sample, hc), if given, runs on the same thread
+    right after (e.g. to take the device-resident query rows before the context counts its next sample).
+    Returns the list of results in sample order."""
+    import threading
+    results, nxt, lock, errors = [None] * n_samples, [0], threading.Lock(), []
+
+    def worker(ctx):
+        try:
+            while True:
+                with lock:
+                    s = nxt[0]
+                    nxt[0] += 1
+                if s >= n_samples:
+                    return
+                hc = count_one(ctx, s)
+                results[s] = on_done(ctx, s, hc) if on_done else hc
+        except Exception as e:  # noqa: BLE001
+            errors.append(e)
+    threads = [threading.Thread(target=worker, args=(c,)) for c in contexts[1:]]
+    for t in threads:
+        t.start()
+    worker(contexts[0])
+    for t in threads:
+        t.join()
+    if errors:
+        raise errors[0]
+    return results
+
+
 def surviving_samples(alive):
     """remove_empty_genomes + index labelling (src/genome_set.c:97-100, 132-142): samples without any mapped HT are
     dropped BEFORE sample ids are assigned, so ids depend on which samples survive.  alive: one flag per sample.

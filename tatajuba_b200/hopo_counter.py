@@ -77,6 +77,11 @@ class Context:
     def set_profiling(self, level):
         self.lib.tjb_ctx_set_profiling(self.h, int(level))
 
+    def set_result_mode(self, arena):
+        """arena=True: result arrays are views of the context's pinned result arena (written by the device, no host
+        copy), valid until this context counts its next sample; False (default): malloc()ed copies like the reference's"""
+        self._check(self.lib.tjb_ctx_set_result_mode(self.h, 1 if arena else 0))
+
     def reset_kernel_stats(self):
         self.lib.tjb_ctx_reset_kernel_stats(self.h)
 
@@ -119,6 +124,42 @@ class Context:
         self._check(self.lib.tjb_count_sample_device(self.h, C.c_void_p(int(d_ptr)), int(n_bytes), C.byref(o),
                                                      C.byref(out)))
         return HopoCounter._from_out(self.lib, out, opt)
+
+
+    # one sample in pieces (read chunks on several GPUs): begin -> scan... -> [export -> exchange -> import] -> finalise
+    def sample_begin(self, opt, n_bytes_hint=0):
+        o = opt.c_struct()
+        self._opt = opt
+        self._check(self.lib.tjb_sample_begin(self.h, C.byref(o), int(n_bytes_hint)))
+
+    def table_capacity(self):
+        return int(self.lib.tjb_ctx_table_capacity(self.h))
+
+    def reserve_entries(self, n):
+        self._check(self.lib.tjb_ctx_reserve_entries(self.h, int(n)))
+
+    def sample_scan_device(self, d_ptr, n_bytes):
+        self._check(self.lib.tjb_sample_scan_device(self.h, C.c_void_p(int(d_ptr)), int(n_bytes)))
+
+    def sample_export(self, d_ptr=None, max_rows=0):
+        """table of the sample so far as rows; without a destination only (n_rows, uint64 words per row) are returned,
+        with one (device address, capacity in rows) the rows are copied there as well.  Synchronous."""
+        n, w = C.c_int64(0), C.c_int32(0)
+        self._check(self.lib.tjb_sample_export(self.h, C.c_void_p(int(d_ptr)) if d_ptr else None, int(max_rows),
+                                               C.byref(n), C.byref(w)))
+        return int(n.value), int(w.value)
+
+    def sample_import(self, d_ptr, n_rows):
+        self._check(self.lib.tjb_sample_import(self.h, C.c_void_p(int(d_ptr)), int(n_rows)))
+
+    def sample_finalise(self):
+        out = TjbCounterOut()
+        self._check(self.lib.tjb_sample_finalise(self.h, C.byref(out)))
+        return HopoCounter._from_out(self.lib, out, self._opt)
+
+    def query_rows_device(self, d_ptr, max_rows):
+        """query rows of the sample counted last, written on the device; returns the number of rows"""
+        return self._check(self.lib.tjb_query_rows_device(self.h, C.c_void_p(int(d_ptr)), int(max_rows)))
 
 
 def _host_ptr(seqs):

@@ -53,10 +53,11 @@ def paired_reads(genome, coverage, read_len=150, insert=(250, 500), seed=7, erro
     out[0::2, :read_len] = r1
     out[1::2, :read_len] = r2
     out[:, read_len] = ord("\n")
-    if error_rate > 0:
-        body = out[:, :read_len]
-        err = rng.random(body.shape) < error_rate
-        body[err] = _ACGT[rng.integers(0, 4, size=int(err.sum()))]
+    if error_rate > 0:  # substitutions at random positions (a position drawn twice is substituted twice: harmless)
+        n_err = int(rng.binomial(2 * n_pairs * read_len, error_rate))
+        row = rng.integers(0, 2 * n_pairs, size=n_err)
+        col = rng.integers(0, read_len, size=n_err)
+        out[row, col] = _ACGT[rng.integers(0, 4, size=n_err)]
     return out
 
 

@@ -61,7 +61,7 @@ def test_abi_exports_every_declared_symbol(built):
 
 def test_struct_sizes_match_header(built):
     assert C.sizeof(_lib.TjbOpts) == 20
-    assert C.sizeof(_lib.TjbCounterOut) == 16 + 4 * 8 + 5 * 8 + 2 * 8
+    assert C.sizeof(_lib.TjbCounterOut) == 16 + 4 * 8 + 5 * 8 + 2 * 8 + 8
     assert C.sizeof(_lib.TjbKernelStat) == 48 + 3 * 8
 
 

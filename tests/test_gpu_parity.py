@@ -274,3 +274,152 @@ def test_gpu_result_size_changes_between_samples(ctx, restatement):
         check(ctx, restatement, buf, 25, 4, 5, True, f"alternating sample {i}")
     check(ctx, restatement, small[:0], 25, 4, 5, True, "empty after large", device_too=False)
     check(ctx, restatement, big, 25, 4, 5, True, "large after empty")
+
+
+# ---- full-size parity against the compiled reference (oracle/_ref travels to the GPU box) ----------------------------
+def _reference_or_skip():
+    if not pyoracle.Reference.available():
+        pytest.skip("oracle/_ref not present")
+    return pyoracle.Reference()
+
+
+@pytest.mark.parametrize("err", [0.0, 0.001, 0.01])
+def test_gpu_full_size_config2_matches_reference(ctx, err):
+    """BASELINE configs[1] at its own size (5 Mbp, 100x, 2x150 PE = 500 Mbases), without and with substitution errors
+    (0.1 % / 1 %: errors create singleton contexts, the opposite of the 64:1 de-duplication of the clean sample):
+    the compiled reference itself is the checker (~3-6 s per run)"""
+    import torch
+    ref = _reference_or_skip()
+    buf = synth.sample_buffer(5_000_000, 100, seed=1, error_rate=err)
+    want = ref.run_buffer(buf.tobytes(), 25, 4, 5, True)
+    opt = TatajubaOptions(25, 4, 5, True)
+    d = torch.from_numpy(buf).cuda()
+    pyoracle.assert_same_boundary(as_boundary(ctx.count_device(d.data_ptr(), d.numel(), opt)), want, f"config 2 err={err} [device]")
+    del d
+    pyoracle.assert_same_boundary(as_boundary(ctx.count_host(buf, opt)), want, f"config 2 err={err} [host]")
+
+
+def test_gpu_full_size_config5_matches_reference(ctx):
+    """BASELINE configs[4] at its own size: k = 32 (full 64-bit keys, 3-word records), m = 3, 300x of a 5 Mbp genome =
+    1.5 Gbases, ~39 M tract observations; compiled reference ~40 s"""
+    import torch
+    ref = _reference_or_skip()
+    buf = synth.sample_buffer(5_000_000, 300, seed=3)
+    want = ref.run_buffer(buf.tobytes(), 32, 3, 5, True)
+    opt = TatajubaOptions(32, 3, 5, True)
+    d = torch.from_numpy(buf).cuda()
+    got = ctx.count_device(d.data_ptr(), d.numel(), opt)
+    assert got.n_raw > 30_000_000
+    pyoracle.assert_same_boundary(as_boundary(got), want, "config 5 [device]")
+
+
+# ---- the aggregation table and what hangs off it -------------------------------------------------------------------
+def test_gpu_table_too_small_is_redone(ctx, restatement):
+    """a sample with more distinct observations than its table was sized for is detected at the synchronisation that
+    ends it and counted again with a larger table"""
+    buf = synth.sample_buffer(400_000, 40, seed=31, error_rate=0.02)
+    ctx.reserve_entries(16)  # the smallest table: 65536 slots
+    want = check(ctx, restatement, buf, 25, 3, 2, False, "table overflow", device_too=False)
+    assert want.n_distinct > 40_000
+    ctx.reserve_entries(16)
+    check(ctx, restatement, buf, 32, 2, 2, True, "table overflow k=32")
+
+
+@pytest.mark.parametrize("k", [25, 32])
+def test_gpu_oversize_bucket_goes_through_the_global_path(ctx, restatement, k):
+    """thousands of distinct contexts that agree on the 10 bases next to the tract fall into ONE bin of the partition
+    plan (it looks at the top <= 20 bits of the context): a bucket that does not fit in shared memory"""
+    rng = np.random.default_rng(77)
+    fixed = b"GTCAGTCAGT"
+    reads = []
+    for i in range(6000):
+        left = bytes(rng.choice(np.frombuffer(b"ACGT", np.uint8), size=k - 10).tobytes()) + fixed
+        right = b"C" + bytes(rng.choice(np.frombuffer(b"ACGT", np.uint8), size=k + 3).tobytes())
+        r = left + b"A" * int(rng.integers(4, 9)) + right
+        reads += [r, r, bytes(synth.revcomp(np.frombuffer(r, np.uint8)).tobytes())]
+    buf = b"\n".join(reads) + b"\n"
+    want = check(ctx, restatement, buf, k, 4, 2, True, f"oversize bucket k={k}")
+    assert want.n_elem > 5000
+    check(ctx, restatement, buf, k, 4, 2, False, f"oversize bucket k={k} -b")
+
+
+def test_gpu_result_arena_mode(ctx, restatement):
+    """TJB_RESULT_ARENA: the arrays are views of the context's pinned arena (written by the device), same contents"""
+    buf = synth.sample_buffer(300_000, 30, seed=41)
+    opt = TatajubaOptions()
+    want = restatement.run_buffer(buf, 25, 4, 5, True)
+    ctx.set_result_mode(True)
+    try:
+        for _ in range(3):
+            got = ctx.count_host(buf, opt)
+            pyoracle.assert_same_boundary(as_boundary(got), want, "arena mode")
+        small = ctx.count_host(buf[: 151 * 2000], opt)  # a dropped / tiny sample after a large one
+        assert small.status in (0, 2, 3)
+    finally:
+        ctx.set_result_mode(False)
+    pyoracle.assert_same_boundary(as_boundary(ctx.count_host(buf, opt)), want, "back to malloc mode")
+
+
+def test_gpu_sample_in_pieces(ctx, restatement):
+    """begin / scan chunks / finalise, and the export -> import hand-over between two contexts (what ranks do over
+    NCCL when one sample is split by read chunk, genome_set.count_sample_sharded): identical to counting it whole"""
+    import torch
+    for k, m, rb, err in [(25, 4, True, 0.0), (32, 3, False, 0.005)]:
+        buf = synth.sample_buffer(300_000, 40, seed=51, error_rate=err)
+        opt = TatajubaOptions(k, m, 5, rb)
+        want = restatement.run_buffer(buf, k, m, 5, rb)
+        cut = (buf.size // 3) // 151 * 151
+        a, b = torch.from_numpy(buf[:cut].copy()).cuda(), torch.from_numpy(buf[cut:].copy()).cuda()
+        ctx.sample_begin(opt, buf.size)
+        ctx.sample_scan_device(a.data_ptr(), a.numel())
+        ctx.sample_scan_device(b.data_ptr(), b.numel())
+        pyoracle.assert_same_boundary(as_boundary(ctx.sample_finalise()), want, f"two chunks, one table k={k}")
+        other = Context(0)
+        try:
+            ctx.sample_begin(opt, buf.size)
+            ctx.sample_scan_device(a.data_ptr(), a.numel())
+            other.sample_begin(opt, buf.size)
+            other.sample_scan_device(b.data_ptr(), b.numel())
+            n_rows, words = other.sample_export()
+            assert words == (3 if k <= 26 else 4) and n_rows > 1000
+            rows = torch.empty((n_rows, words), dtype=torch.int64, device="cuda")
+            other.sample_export(rows.data_ptr(), n_rows)
+            ctx.sample_import(rows.data_ptr(), n_rows)
+            pyoracle.assert_same_boundary(as_boundary(ctx.sample_finalise()), want, f"export -> import k={k}")
+            other.sample_finalise()
+        finally:
+            other.close()
+
+
+def test_gpu_query_rows_device_and_union(ctx, restatement):
+    """query rows written on the device = tjb_query_rows on the host result; device-resident union = numpy restatement"""
+    import torch
+    from tatajuba_b200 import genome_set
+    tables, dev_tables = [], {}
+    for s in range(3):
+        buf = synth.sample_buffer(200_000, 30, seed=61, sample=s, fraction=0.05)
+        hc = ctx.count_host(buf, TatajubaOptions())
+        dev_tables[s] = genome_set.query_rows_device(ctx, hc).clone()
+        tables.append(genome_set.query_rows(hc))
+        assert np.array_equal(dev_tables[s].cpu().numpy().view(np.uint64), tables[s])
+    rows, sizes = genome_set.allgather_tables_device(dev_tables, 3)
+    assert sizes == [len(t) for t in tables]
+    d_union, d_index = genome_set.union_queries_device(ctx, rows, 25)
+    want_union, want_index = pyoracle.union_oracle(tables)
+    assert np.array_equal(d_union.cpu().numpy().view(np.uint64), want_union)
+    assert np.array_equal(d_index.cpu().numpy(), np.concatenate(want_index))
+
+
+def test_gpu_many_samples_two_contexts(ctx, restatement):
+    """the reference's dynamic sample loop (genome_set.c:66-68) with two contexts on one device: every sample's result
+    is what one context gives on its own"""
+    from tatajuba_b200 import genome_set
+    bufs = [synth.sample_buffer(150_000, 30, seed=71, sample=s, fraction=0.05) for s in range(7)]
+    opt = TatajubaOptions()
+    other = Context(0)
+    try:
+        res = genome_set.count_samples([ctx, other], len(bufs), lambda c, s: c.count_host(bufs[s], opt))
+    finally:
+        other.close()
+    for s, hc in enumerate(res):
+        pyoracle.assert_same_boundary(as_boundary(hc), restatement.run_buffer(bufs[s], 25, 4, 5, True), f"sample {s}")
