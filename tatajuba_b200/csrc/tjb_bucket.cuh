@@ -91,15 +91,29 @@ __device__ __forceinline__ u32 blk_excl_scan (u32 v, u32 *s_warp /*[2 * NT / 32]
   return before + inc - v;
 }
 
+// --------------------------------------------------------------------------------------- prologue --------
+// clears the device scalars of a sample in one launch: result block (counters, meta; coverage = INT_MIN), the window
+// ticket of the first scan launch and the bins the scan is going to count
+__global__ void __launch_bounds__ (256)
+sample_prologue_kernel (u32 *__restrict__ res_words, int n_res_words, int cov_word, u32 *__restrict__ tile_ctr, u32 *__restrict__ bin_hist, u32 n_bins)
+{
+  const u32 t = blockIdx.x * 256 + threadIdx.x;
+  if (t < (u32) n_res_words) res_words[t] = t == (u32) cov_word ? 0x80000000u : 0u;
+  if (t == 0) *tile_ctr = 0;
+  for (u32 i = t; i < n_bins; i += gridDim.x * 256) bin_hist[i] = 0;
+}
+
 // ------------------------------------------------------------------------------------------- plan --------
 // Bins are walked from the highest to the lowest (descending key order).  P[j] = number of records in bins before
-// j in that order; bins whose P falls into the same window of BK_CAPH records form one bucket, so a bucket holds
-// fewer than BK_CAPH + (its last bin) records: at most BK_CAP unless a single bin exceeds BK_CAPH.
+// j in that order; bins whose P falls into the same window of 2^bshift records form one bucket, so a bucket holds
+// fewer than 2^bshift + (its last bin) records: at most BK_CAP unless a single bin exceeds BK_CAP - 2^bshift.  The
+// host picks bshift <= log2 (BK_CAPH) so that a sample's records spread over all SMs (a small sample in buckets of
+// ~128 records, which the bucket kernel orders by comparison counting instead of radix passes).
 // One CTA; thread t owns IPT consecutive bins, loaded up front with 16-byte loads so that every global load of the
 // kernel is in flight at once (the first version walked them with dependent scalar loads: 195 us for 32 Ki bins).
 template <int IPT>
 __global__ void __launch_bounds__ (PLAN_THREADS)
-plan_kernel (const u32 *__restrict__ bin_hist, int F, unsigned long long capacity,
+plan_kernel (const u32 *__restrict__ bin_hist, int F, int bshift, unsigned long long capacity,
              u32 *__restrict__ bkt_start, u32 *__restrict__ lut, u32 *__restrict__ cursor, u32 *__restrict__ meta, u32 max_buckets)
 {
   __shared__ u32 s_warp[2 * (PLAN_THREADS / 32)];
@@ -136,7 +150,7 @@ plan_kernel (const u32 *__restrict__ bin_hist, int F, unsigned long long capacit
     u32 p = P0, hp = hprev;
 #pragma unroll
     for (int i = IPT - 1; i >= 0; i--) {
-      const bool head = active && ((t == 0 && i == IPT - 1) || (p / BK_CAPH != (p - hp) / BK_CAPH));
+      const bool head = active && ((t == 0 && i == IPT - 1) || ((p >> bshift) != ((p - hp) >> bshift)));
       nheads += head;
       hp = h[i]; p += h[i];
     }
@@ -147,7 +161,7 @@ plan_kernel (const u32 *__restrict__ bin_hist, int F, unsigned long long capacit
     u32 p = P0, hp = hprev;
 #pragma unroll
     for (int i = IPT - 1; i >= 0; i--) {
-      const bool head = (t == 0 && i == IPT - 1) || (p / BK_CAPH != (p - hp) / BK_CAPH);
+      const bool head = (t == 0 && i == IPT - 1) || ((p >> bshift) != ((p - hp) >> bshift));
       // (more heads than max_buckets only after a record-array overflow: the sample is redone anyway)
       if (head) { if (b < max_buckets) { bkt_start[b] = p; cursor[(size_t) b * BK_CURSOR_STRIDE] = p; } b++; }
       hp = h[i]; p += h[i];
@@ -176,7 +190,7 @@ plan_kernel (const u32 *__restrict__ bin_hist, int F, unsigned long long capacit
 // samples, where 2^16 bins would hold more than BK_CAPH records each): every thread walks its 2^F / 1024 bins three
 // times from L2 (sum, count heads, emit) instead of keeping them in registers.
 __global__ void __launch_bounds__ (PLAN_THREADS)
-plan_big_kernel (const u32 *__restrict__ bin_hist, int F, unsigned long long capacity,
+plan_big_kernel (const u32 *__restrict__ bin_hist, int F, int bshift, unsigned long long capacity,
                  u32 *__restrict__ bkt_start, u32 *__restrict__ lut, u32 *__restrict__ cursor, u32 *__restrict__ meta, u32 max_buckets)
 {
   __shared__ u32 s_warp[2 * (PLAN_THREADS / 32)];
@@ -197,7 +211,7 @@ plan_big_kernel (const u32 *__restrict__ bin_hist, int F, unsigned long long cap
       const u32 h4[4] = {v.w, v.z, v.y, v.x};
 #pragma unroll
       for (int j = 0; j < 4; j++) {
-        nheads += (t == 0 && i == ipt && j == 0) || (p / BK_CAPH != (p - hp) / BK_CAPH);
+        nheads += (t == 0 && i == ipt && j == 0) || ((p >> bshift) != ((p - hp) >> bshift));
         hp = h4[j]; p += h4[j];
       }
     }
@@ -212,7 +226,7 @@ plan_big_kernel (const u32 *__restrict__ bin_hist, int F, unsigned long long cap
       u32 l4[4];
 #pragma unroll
       for (int j = 0; j < 4; j++) {
-        const bool head = (t == 0 && i == ipt && j == 0) || (p / BK_CAPH != (p - hp) / BK_CAPH);
+        const bool head = (t == 0 && i == ipt && j == 0) || ((p >> bshift) != ((p - hp) >> bshift));
         if (head) { if (b < max_buckets) { bkt_start[b] = p; cursor[(size_t) b * BK_CURSOR_STRIDE] = p; } b++; }
         hp = h4[j]; p += h4[j];
         l4[j] = b - 1 < max_buckets ? b - 1 : max_buckets - 1;
@@ -274,7 +288,7 @@ template <int W> constexpr size_t wbucket_smem_bytes ()
   return (size_t) W * BK_CAP * 8 /* s_w */ + 2 * BK_CAP * 2 /* perm */ + BK_WARPS * 256 * 2 /* counts */ + BK_CAP * 2 /* aux */ +
          BK_CAP * 4 /* val */ + BK_CAP * 4 /* kept counts */ + BK_CAP * 4 /* sum */;
 }
-#define BK_RANKSORT_MAX 128 // up to this many records a bucket is ordered by comparison counting instead of radix passes
+#define BK_RANKSORT_MAX BK_THREADS // up to this many records a bucket is ordered by comparison counting instead of radix passes
 enum { QC_SEEN_TWICE = 0,   // "-b": keep count > 1                 (hopo_counter.c:371-373)
        QC_BOTH_STRANDS = 1, // default: keep canon_flag == 3        (:368-370)
        QC_KEEP_ALL = 2 };   // union of mapper queries (tjb_union.cuh): nothing is filtered
@@ -562,27 +576,37 @@ totals_kernel (const uint4 *__restrict__ bstat, u32 *__restrict__ meta, u32 *__r
 }
 
 // ------------------------------------------------------------------------------- coverage hash + pack ----
-#define COV_EMPTY 0xffffffffu
+// coverage table: slot key = (flank & 0x7fffffff) + 1, 0 = empty (one memset clears keys and sums)
 __device__ __forceinline__ void cov_insert (u32 *__restrict__ keys, u32 *__restrict__ vals, u32 mask, u32 key, u32 w)
 {
   u32 slot = (key * 0x9E3779B1u) >> 7;
+  key += 1;
   for (;;) {
     slot &= mask;
     u32 prev = keys[slot];
     if (prev != key) {
-      if (prev != COV_EMPTY) { slot++; continue; }
-      prev = atomicCAS (&keys[slot], COV_EMPTY, key);
-      if (prev != COV_EMPTY && prev != key) { slot++; continue; }
+      if (prev != 0) { slot++; continue; }
+      prev = atomicCAS (&keys[slot], 0u, key);
+      if (prev != 0 && prev != key) { slot++; continue; }
     }
     atomicAdd (&vals[slot], w);
     return;
   }
 }
 
-// one warp per bucket: final 40-byte hopo_element (src/hopo_counter.h:34-49) as it stands at the BWA boundary, global
-// idx_initial / idx_final, and the two (flank & 0x7fffffff, count) pairs of every kept record (hopo_counter.c:427-432).
-// out40 may be device memory or mapped pinned host memory (the result arena): rows are staged per warp in shared
-// memory so that every store instruction of the warp covers 256 contiguous bytes.
+// bucket that holds global output position g: the LAST b with off[b] <= g (off = exclusive prefix sums of the per-bucket
+// counts: buckets that contribute nothing share their offset with the next one)
+__device__ __forceinline__ u32 bucket_of (const u32 *__restrict__ off, u32 nb, u32 g)
+{
+  u32 lo = 0, hi = nb - 1;
+  while (lo < hi) { const u32 mid = (lo + hi + 1) >> 1; if (off[mid] <= g) lo = mid; else hi = mid - 1; }
+  return lo;
+}
+
+// One thread per kept record: final 40-byte hopo_element (src/hopo_counter.h:34-49) as it stands at the BWA boundary,
+// and the two (flank & 0x7fffffff, count) pairs of the record (hopo_counter.c:427-432); one thread per context group:
+// global idx_initial / idx_final.  out40 may be device memory or mapped pinned host memory (the result arena): rows are
+// staged per warp in shared memory so that every store instruction of the warp covers 256 contiguous bytes.
 template <int W>
 __global__ void __launch_bounds__ (256)
 pack_kernel (const u64 *__restrict__ out_rec, const u32 *__restrict__ out_cnt, const u32 *__restrict__ out_idx_i, const u32 *__restrict__ out_idx_f,
@@ -592,44 +616,48 @@ pack_kernel (const u64 *__restrict__ out_rec, const u32 *__restrict__ out_cnt, c
 {
   // The host launches this kernel before it knows the counts, into arrays sized from the previous sample (max_keep,
   // max_idx; the coverage table holds 2 max_keep keys at load <= 0.5): nothing is written beyond them, and the host
-  // repeats the launch with exact sizes when the counts turn out larger (or the record array had overflowed).
+  // repeats the launch with exact sizes when the counts turn out larger (or the sample had to be redone).
   __shared__ u64 s_stage[256 / 32][32 * 5];
   const u32 nb = meta[META_NBUCKETS];
+  if (!nb) return;
   const int lane = threadIdx.x & 31;
   u64 *stage = s_stage[threadIdx.x >> 5];
-  const u32 warps = gridDim.x * (256 / 32);
-  for (u32 b = blockIdx.x * (256 / 32) + (threadIdx.x >> 5); b < nb; b += warps) {
-    const uint4 s = bstat[b];
-    const u32 start = bkt_start[b], ko = koff[b], io = ioff[b];
-    if ((unsigned long long) start + s.y > capacity || (unsigned long long) start + s.z > capacity) continue;
-    for (u32 j0 = 0; j0 < s.y; j0 += 32) {
-      if (ko + j0 >= max_keep) break;
-      const u32 j = j0 + lane;
-      u32 rows = s.y - j0 < 32u ? s.y - j0 : 32u;
-      if (ko + j0 + rows > max_keep) rows = max_keep - (ko + j0);
-      if ((u32) lane < rows) {
+  const u32 n_keep = meta[META_NKEEP] < max_keep ? meta[META_NKEEP] : max_keep;
+  const u32 n_idx = meta[META_NIDX] < max_idx ? meta[META_NIDX] : max_idx;
+  const u32 stride = gridDim.x * 256;
+  for (u32 g0 = (blockIdx.x * 256 + (threadIdx.x & ~31u)); g0 < n_keep; g0 += stride) { // g0: first record of this warp's 32
+    const u32 g = g0 + lane;
+    const u32 rows = n_keep - g0 < 32u ? n_keep - g0 : 32u;
+    if ((u32) lane < rows) {
+      const u32 b = bucket_of (koff, nb, g);
+      const u32 j = g - koff[b], start = bkt_start[b];
+      u64 c0 = 0, c1 = 0, bits = 0;
+      if ((unsigned long long) start + j < capacity) {
         Rec<W> r = load_rec<W> (out_rec, (size_t) start + j);
         const int cnt = sext_field ((long long) out_cnt[start + j], 20); // the reference's count:20 signed bit-field
         // gcc x86-64 bit-field order from the LSB: base:2 length:10 count:20 mismatches:12 multi:3 neg_strand:2 canon_flag:3
-        const u64 bits = ((u64) rec_base<W> (r, k) & 3) | (((u64) rec_len_field<W> (r) & 0x3ff) << 2) | (((u64) cnt & 0xfffff) << 12) |
-                         (0xffeULL << 32) | (((u64) rec_flag<W> (r) & 7) << 49);
-        const u64 c0 = rec_ctx0<W> (r, k), c1 = rec_ctx1<W> (r, k);
-        stage[5 * lane] = c0; stage[5 * lane + 1] = c1; stage[5 * lane + 2] = bits;
-        stage[5 * lane + 3] = ~0ULL; // read_offset = -1 (hopo_counter.c:511), loc_ref_id = -1 (:297)
-        stage[5 * lane + 4] = ~0ULL; // loc_pos = loc_last = -1
+        bits = ((u64) rec_base<W> (r, k) & 3) | (((u64) rec_len_field<W> (r) & 0x3ff) << 2) | (((u64) cnt & 0xfffff) << 12) |
+               (0xffeULL << 32) | (((u64) rec_flag<W> (r) & 7) << 49);
+        c0 = rec_ctx0<W> (r, k); c1 = rec_ctx1<W> (r, k);
         cov_insert (cov_keys, cov_vals, cov_mask, (u32) (c0 & 0x7fffffffULL), (u32) cnt);
         cov_insert (cov_keys, cov_vals, cov_mask, (u32) (c1 & 0x7fffffffULL), (u32) cnt);
       }
-      __syncwarp ();
-      u64 *o = out40 + 5 * (size_t) (ko + j0);
-#pragma unroll
-      for (int t = 0; t < 5; t++) { const u32 w = t * 32 + lane; if (w < 5 * rows) o[w] = stage[w]; }
-      __syncwarp ();
+      stage[5 * lane] = c0; stage[5 * lane + 1] = c1; stage[5 * lane + 2] = bits;
+      stage[5 * lane + 3] = ~0ULL; // read_offset = -1 (hopo_counter.c:511), loc_ref_id = -1 (:297)
+      stage[5 * lane + 4] = ~0ULL; // loc_pos = loc_last = -1
     }
-    for (u32 t = lane; t < s.z; t += 32) {
-      if (io + t >= max_idx) break;
-      idx_initial[io + t] = (int) (ko + out_idx_i[start + t]);
-      idx_final[io + t] = (int) (ko + out_idx_f[start + t]);
+    __syncwarp ();
+    u64 *o = out40 + 5 * (size_t) g0;
+#pragma unroll
+    for (int t = 0; t < 5; t++) { const u32 w = t * 32 + lane; if (w < 5 * rows) o[w] = stage[w]; }
+    __syncwarp ();
+  }
+  for (u32 t = blockIdx.x * 256 + threadIdx.x; t < n_idx; t += stride) {
+    const u32 b = bucket_of (ioff, nb, t);
+    const u32 start = bkt_start[b], ko = koff[b], u = t - ioff[b];
+    if ((unsigned long long) start + u < capacity) {
+      idx_initial[t] = (int) (ko + out_idx_i[start + u]);
+      idx_final[t] = (int) (ko + out_idx_f[start + u]);
     }
   }
 }
@@ -640,7 +668,7 @@ cov_max_kernel (const u32 *__restrict__ keys, const u32 *__restrict__ vals, u32 
 {
   int best = INT_MIN;
   for (u32 i = blockIdx.x * 256 + threadIdx.x; i < n_slots; i += gridDim.x * 256)
-    if (keys[i] != COV_EMPTY) { int v = (int) vals[i]; best = v > best ? v : best; }
+    if (keys[i] != 0) { int v = (int) vals[i]; best = v > best ? v : best; }
 #pragma unroll
   for (int d = 16; d; d >>= 1) { int o = __shfl_xor_sync (0xffffffffu, best, d); best = o > best ? o : best; }
   if ((threadIdx.x & 31) == 0 && best != INT_MIN) atomicMax (cov, best);

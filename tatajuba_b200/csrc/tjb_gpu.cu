@@ -75,10 +75,11 @@ struct tjb_ctx {
   // ---- the sample being counted ----
   tjb_opts opt = {0, 0, 0, 0, 0};
   bool in_sample = false;
+  int scan_launches = 0;                    // of this sample
   int64_t exported_rows = -1;               // rows of the table as exported for an exchange (-1: not exported yet)
   int rec_words = 0;
-  int bin_bits = 8;
-  DevBuf tab_keys, tab_cnt;                 // aggregation table (tjb_table.cuh)
+  int bin_bits = 8, bucket_shift = 10;      // partition plan: 2^bin_bits bins, bucket windows of 2^bucket_shift records
+  DevBuf tab;                               // aggregation table (tjb_table.cuh): counts, then keys
   size_t tab_slots = 0;
   DevBuf ovf;                               // observations the table could not take, raw records
   size_t ovf_capacity = 0;
@@ -230,14 +231,22 @@ static int radix_sort (tjb_ctx *ctx, u64 *a, u64 *b, size_t n, const std::vector
   return 0;
 }
 
-// bins of the partition plan: enough that a bin holds ~BK_CAP/8 weighted records on average
-static int choose_bin_bits (size_t est_records, int k)
+// records per bucket (2^bshift, the window of the partition plan): a sample's records spread over every CTA the bucket
+// kernel can have resident, between 64 (buckets of < 128 records are ordered by comparison counting) and BK_CAPH
+static int choose_bucket_shift (size_t est_records, int sm_count)
+{
+  int bshift = 6;
+  while ((1u << bshift) < BK_CAPH && (est_records >> (bshift + 1)) > (size_t) sm_count * 3) bshift++;
+  return bshift;
+}
+// bins of the partition plan: enough that a bin holds a quarter of a bucket window on average
+static int choose_bin_bits (size_t est_records, int bshift, int k)
 {
   const int W = tjb_rec_words (k);
   const int max_bits = W == 2 ? (4 * k + 1 < TJB_MAX_BIN_BITS ? 4 * k + 1 : TJB_MAX_BIN_BITS)
                               : (2 * k + 1 < TJB_MAX_BIN_BITS ? 2 * k + 1 : TJB_MAX_BIN_BITS);
   int F = 4;
-  while (F < TJB_MAX_BIN_BITS && (est_records >> F) > BK_CAP / 8) F++;
+  while (F < TJB_MAX_BIN_BITS && (est_records >> F) > ((size_t) 1 << bshift) / 4) F++;
   return F < max_bits ? F : max_bits;
 }
 
@@ -276,13 +285,19 @@ static int begin_sample (tjb_ctx *ctx, const tjb_opts *opt, size_t n_bytes_hint)
   ctx->tab_slots = slots;
   ctx->ovf_capacity = est / 8 < 65536 ? 65536 : est / 8;
   ctx->list_cap = slots / 2 + ctx->ovf_capacity;
-  ctx->bin_bits = choose_bin_bits (est, opt->kmer_size);
-  TRY (ensure (ctx, ctx->tab_keys, slots * W * 8));
-  TRY (ensure (ctx, ctx->tab_cnt, slots * 8));
+  ctx->bucket_shift = choose_bucket_shift (est, ctx->sm_count);
+  ctx->bin_bits = choose_bin_bits (est, ctx->bucket_shift, opt->kmer_size);
+  TRY (ensure (ctx, ctx->tab, table_bytes (slots, W)));
   TRY (ensure (ctx, ctx->ovf, ctx->ovf_capacity * W * 8));
-  CU (cudaMemsetAsync (ctx->d_res, 0, sizeof (ResultBlock), ctx->stream));
-  CU (cudaMemsetAsync (ctx->tab_cnt.p, 0, slots * 8, ctx->stream));
-  CU (cudaMemsetAsync (ctx->d_bin_hist, 0, sizeof (u32) << ctx->bin_bits, ctx->stream));
+  CU (cudaMemsetAsync (ctx->tab.p, 0, table_bytes (slots, W), ctx->stream));
+  {
+    const u32 n_bins = 1u << ctx->bin_bits;
+    const u32 g = n_bins / 256 < 1 ? 1 : (n_bins / 256 > (u32) ctx->sm_count * 4 ? (u32) ctx->sm_count * 4 : n_bins / 256);
+    sample_prologue_kernel<<<g, 256, 0, ctx->stream>>> ((u32*) ctx->d_res, (int) (sizeof (ResultBlock) / 4), (int) (offsetof (ResultBlock, cov) / 4), ctx->d_tile_ctr, ctx->d_bin_hist, n_bins);
+    ctx->launches++; ctx->stats[K_TABLE].launches++;
+    CU (cudaGetLastError ());
+  }
+  ctx->scan_launches = 0;
   ctx->in_sample = true;
   ctx->exported_rows = -1;
   return 0;
@@ -291,7 +306,7 @@ static int begin_sample (tjb_ctx *ctx, const tjb_opts *opt, size_t n_bytes_hint)
 static AggTable table_of (tjb_ctx *ctx)
 {
   AggTable t;
-  t.keys = (u64*) ctx->tab_keys.p; t.cnt = (unsigned long long*) ctx->tab_cnt.p; t.mask = (u32) (ctx->tab_slots - 1);
+  t.cnt = (unsigned long long*) ctx->tab.p; t.keys = (u64*) ctx->tab.p + ctx->tab_slots; t.mask = (u32) (ctx->tab_slots - 1);
   return t;
 }
 
@@ -301,7 +316,7 @@ static int launch_scan (tjb_ctx *ctx, const uint8_t *d_seqs, size_t n)
   if (!n_tiles) return 0;
   const tjb_opts *opt = &ctx->opt;
   int min_len = opt->min_tract_size < 2 ? 2 : opt->min_tract_size;
-  CU (cudaMemsetAsync (ctx->d_tile_ctr, 0, sizeof (u32), ctx->stream)); // window tickets of this launch
+  if (ctx->scan_launches++) CU (cudaMemsetAsync (ctx->d_tile_ctr, 0, sizeof (u32), ctx->stream)); // window tickets of this launch (the first: cleared by the prologue)
   long long want = (n_tiles + SCAN_WARPS - 1) / SCAN_WARPS;
   long long grid = want < (long long) ctx->sm_count * SCAN_CTAS_PER_SM ? want : (long long) ctx->sm_count * SCAN_CTAS_PER_SM;
   // algorithmic bytes of this launch: every sequence byte read once (+ the table traffic per observation, added at finalise)
@@ -449,8 +464,8 @@ static int reduce_launch (tjb_ctx *ctx, int qc_mode, int min_coverage)
   TRY (ensure (ctx, ctx->wkey, (size_t) cap * W * 8)); TRY (ensure (ctx, ctx->wcnt, (size_t) cap * 8)); TRY (ensure (ctx, ctx->okey, (size_t) cap * W * 8));
   TRY (ensure (ctx, ctx->out_cnt, (size_t) cap * 4)); TRY (ensure (ctx, ctx->out_ii, (size_t) cap * 4)); TRY (ensure (ctx, ctx->out_if, (size_t) cap * 4));
   const u32 grid = (u32) ctx->sm_count;
-  // per-bucket tables: a bucket starts where the running record count crosses a multiple of BK_CAPH
-  const u32 max_buckets = (u32) (cap / BK_CAPH) + 2;
+  // per-bucket tables: a bucket starts where the running record count crosses a multiple of 2^bucket_shift
+  const u32 max_buckets = (u32) (cap >> ctx->bucket_shift) + 2;
   TRY (ensure (ctx, ctx->b_bkt_start, ((size_t) max_buckets + 1) * 4));
   TRY (ensure (ctx, ctx->b_cursor, (size_t) max_buckets * BK_CURSOR_STRIDE * 4));
   TRY (ensure (ctx, ctx->b_koff, (size_t) max_buckets * 4)); TRY (ensure (ctx, ctx->b_ioff, (size_t) max_buckets * 4));
@@ -462,9 +477,9 @@ static int reduce_launch (tjb_ctx *ctx, int qc_mode, int min_coverage)
   unsigned long long *d_counters = ctx->d_res->counters;
   {
     const int ipt = F > 10 ? 1 << (F - 10) : 1; // bins per thread of the single planning CTA
-#define PLAN_CASE(I) case I: LAUNCH (K_PLAN, 10 << F, (plan_kernel<I><<<1, PLAN_THREADS, 0, st>>> (ctx->d_bin_hist, F, cap, ctx->d_bkt_start, ctx->d_lut, ctx->d_cursor, d_meta, max_buckets))); break;
+#define PLAN_CASE(I) case I: LAUNCH (K_PLAN, 10 << F, (plan_kernel<I><<<1, PLAN_THREADS, 0, st>>> (ctx->d_bin_hist, F, ctx->bucket_shift, cap, ctx->d_bkt_start, ctx->d_lut, ctx->d_cursor, d_meta, max_buckets))); break;
     if (F > PLAN_REG_BIN_BITS)
-      LAUNCH (K_PLAN, 18 << F, (plan_big_kernel<<<1, PLAN_THREADS, 0, st>>> (ctx->d_bin_hist, F, cap, ctx->d_bkt_start, ctx->d_lut, ctx->d_cursor, d_meta, max_buckets)));
+      LAUNCH (K_PLAN, 18 << F, (plan_big_kernel<<<1, PLAN_THREADS, 0, st>>> (ctx->d_bin_hist, F, ctx->bucket_shift, cap, ctx->d_bkt_start, ctx->d_lut, ctx->d_cursor, d_meta, max_buckets)));
     else
     switch (ipt) { PLAN_CASE (1) PLAN_CASE (2) PLAN_CASE (4) PLAN_CASE (8) PLAN_CASE (16) PLAN_CASE (32) PLAN_CASE (64) }
 #undef PLAN_CASE
@@ -528,7 +543,7 @@ static int finalise_t (tjb_ctx *ctx, tjb_counter_out *out, int qc_mode)
   u32 *d_meta = ctx->d_res->meta;
   // elements + group indices + coverage, into the arena (capacity: the previous sample's counts + 25 %, at least 4 Ki)
   const int cov_init = INT_MIN;
-  auto launch_pack = [&] () -> int {
+  auto launch_pack = [&] (bool again) -> int {
     const u32 max_keep = (u32) ctx->arena_keep_cap, max_idx = (u32) ctx->arena_idx_cap;
     u32 slots = 1024;
     while (slots < 4u * max_keep) slots <<= 1; // two keys per record, load factor <= 0.5
@@ -540,9 +555,8 @@ static int finalise_t (tjb_ctx *ctx, tjb_counter_out *out, int qc_mode)
       TRY (ensure (ctx, ctx->out40, (size_t) max_keep * 40)); TRY (ensure (ctx, ctx->idx_i, (size_t) max_idx * 4)); TRY (ensure (ctx, ctx->idx_f, (size_t) max_idx * 4));
       o40 = (u64*) ctx->out40.p; oi = (int*) ctx->idx_i.p; of = (int*) ctx->idx_f.p;
     }
-    CU (cudaMemsetAsync (cov_keys, 0xff, (size_t) slots * 4, st));
-    CU (cudaMemsetAsync (cov_vals, 0, (size_t) slots * 4, st));
-    CU (cudaMemcpyAsync (&ctx->d_res->cov, &cov_init, 4, cudaMemcpyHostToDevice, st));
+    CU (cudaMemsetAsync (cov_keys, 0, (size_t) slots * 8, st)); // keys and sums
+    if (again) CU (cudaMemcpyAsync (&ctx->d_res->cov, &cov_init, 4, cudaMemcpyHostToDevice, st)); // (the prologue set it for the first launch)
     LAUNCH (K_PACK, (8 * W + 4 + 40) * (size_t) ctx->last_keep + 16 * (size_t) ctx->last_idx,
             (pack_kernel<W><<<grid * 4, 256, 0, st>>> ((const u64*) ctx->okey.p, (u32*) ctx->out_cnt.p, (u32*) ctx->out_ii.p, (u32*) ctx->out_if.p, ctx->d_bkt_start, ctx->d_bstat, ctx->d_koff, ctx->d_ioff, d_meta, k, o40, oi, of, cov_keys, cov_vals, slots - 1, max_keep, max_idx, cap)));
     LAUNCH (K_COVMAX, 8 * (size_t) slots, (cov_max_kernel<<<nblk (slots, 256 * 8), 256, 0, st>>> (cov_keys, cov_vals, slots, &ctx->d_res->cov)));
@@ -560,7 +574,7 @@ static int finalise_t (tjb_ctx *ctx, tjb_counter_out *out, int qc_mode)
     return 0;
   };
   TRY (ensure_arena (ctx, ctx->last_keep + ctx->last_keep / 8 + 256, ctx->last_idx + ctx->last_idx / 8 + 256));
-  TRY (launch_pack ());
+  TRY (launch_pack (false));
   tr.mark ("enqueue");
   // The result arrays of the default mode are malloc()ed (the reference free()s them) and fresh heap memory costs a page
   // fault per 4 KiB on first touch (measured: up to 1.2 ms for 2.8 MB, depending on what the allocator has cached).
@@ -615,7 +629,7 @@ static int finalise_t (tjb_ctx *ctx, tjb_counter_out *out, int qc_mode)
   if (repack || n_keep > ctx->arena_keep_cap || n_idx > ctx->arena_idx_cap) {
     TRY (ensure_arena (ctx, n_keep, n_idx)); // not packed completely: the arena was sized for a smaller sample
     ctx->last_keep = n_keep; ctx->last_idx = n_idx;
-    TRY (launch_pack ());
+    TRY (launch_pack (true));
     CU (cudaStreamSynchronize (st));
   } else if (ctx->result_dma && (n_keep > sent_keep || n_idx > sent_idx)) { // packed, but only a part has been copied
     const size_t mk = ctx->arena_keep_cap, mi = ctx->arena_idx_cap;
@@ -673,6 +687,18 @@ static int finalise (tjb_ctx *ctx, tjb_counter_out *out)
 }
 
 static void out_reset (tjb_counter_out *out) { memset (out, 0, sizeof (*out)); }
+
+// device time of the call between ev_t0 and now (diagnostics): another round trip, so only when profiling is on
+static int device_time (tjb_ctx *ctx, tjb_counter_out *out)
+{
+  if (!ctx->profiling) return 0;
+  CU (cudaEventRecord (ctx->ev_t1, ctx->stream));
+  CU (cudaEventSynchronize (ctx->ev_t1));
+  float ms = 0.f;
+  cudaEventElapsedTime (&ms, ctx->ev_t0, ctx->ev_t1);
+  out->ms_device = ms;
+  return 0;
+}
 
 // ---- union of query rows over samples (tjb_union.cuh): the rows go through the aggregation table and the bucket
 // reduce like the observations of a sample, with nothing filtered --------------------------------------------------
@@ -885,7 +911,7 @@ void tjb_ctx_destroy (tjb_ctx *ctx)
     if (ctx->h_exc_val[i]) cudaFreeHost (ctx->h_exc_val[i]);
   }
   DevBuf *bufs[] = {&ctx->d_pk[0], &ctx->d_pk[1], &ctx->d_exc_pos[0], &ctx->d_exc_pos[1], &ctx->d_exc_val[0], &ctx->d_exc_val[1],
-                    &ctx->d_chunk[0], &ctx->d_chunk[1], &ctx->tab_keys, &ctx->tab_cnt, &ctx->ovf, &ctx->wkey, &ctx->wcnt, &ctx->okey,
+                    &ctx->d_chunk[0], &ctx->d_chunk[1], &ctx->tab, &ctx->ovf, &ctx->wkey, &ctx->wcnt, &ctx->okey,
                     &ctx->hist, &ctx->ptmp, &ctx->heads, &ctx->pos, &ctx->seg, &ctx->drec, &ctx->dcount, &ctx->keep, &ctx->kpos, &ctx->krec,
                     &ctx->cw, &ctx->csum, &ctx->gkeep, &ctx->gkpos, &ctx->out40, &ctx->idx_i, &ctx->idx_f, &ctx->qrows, &ctx->out_cnt, &ctx->out_ii,
                     &ctx->out_if, &ctx->cov_tab, &ctx->uni_a, &ctx->uni_b, &ctx->b_bkt_start, &ctx->b_cursor, &ctx->b_koff, &ctx->b_ioff, &ctx->b_bstat};
@@ -945,7 +971,7 @@ int tjb_count_sample_device (tjb_ctx *ctx, const void *d_seqs, size_t n_bytes, c
   for (int attempt = 0; attempt < TJB_MAX_ATTEMPTS; attempt++) {
     out_reset (out);
     TRY (begin_sample (ctx, opt, n_bytes));
-    CU (cudaEventRecord (ctx->ev_t0, ctx->stream));
+    if (ctx->profiling) CU (cudaEventRecord (ctx->ev_t0, ctx->stream));
     TRY (launch_scan (ctx, (const uint8_t*) d_seqs, n_bytes));
     tr.mark ("device:scan_enqueue");
     rc = finalise (ctx, out);
@@ -954,11 +980,7 @@ int tjb_count_sample_device (tjb_ctx *ctx, const void *d_seqs, size_t n_bytes, c
   }
   if (rc == TJB_INTERNAL_RETRY) { ctx->err = "aggregation table overflow persisted"; return TJB_ERR_CUDA; }
   if (rc < 0) return rc;
-  CU (cudaEventRecord (ctx->ev_t1, ctx->stream));
-  CU (cudaEventSynchronize (ctx->ev_t1));
-  float ms = 0.f;
-  cudaEventElapsedTime (&ms, ctx->ev_t0, ctx->ev_t1);
-  out->ms_device = ms;
+  TRY (device_time (ctx, out));
   tr.mark ("post");
   return out->status;
 }
@@ -1038,7 +1060,7 @@ int tjb_count_sample_host (tjb_ctx *ctx, const uint8_t *seqs, size_t n_bytes, co
   for (int attempt = 0; attempt < TJB_MAX_ATTEMPTS; attempt++) {
     out_reset (out);
     TRY (begin_sample (ctx, opt, n_bytes));
-    CU (cudaEventRecord (ctx->ev_t0, ctx->stream));
+    if (ctx->profiling) CU (cudaEventRecord (ctx->ev_t0, ctx->stream));
     for (int i = 0; i < 2; i++) TRY (ensure (ctx, ctx->d_chunk[i], (max_chunk < n_bytes ? max_chunk : n_bytes) + 16));
     CU (cudaEventRecord (ctx->ev_ready, ctx->stream));            // workspace set up / previous sample done
     CU (cudaStreamWaitEvent (ctx->copy_stream, ctx->ev_ready, 0));
@@ -1090,11 +1112,7 @@ int tjb_count_sample_host (tjb_ctx *ctx, const uint8_t *seqs, size_t n_bytes, co
   }
   if (rc == TJB_INTERNAL_RETRY) { ctx->err = "aggregation table overflow persisted"; return TJB_ERR_CUDA; }
   if (rc < 0) return rc;
-  CU (cudaEventRecord (ctx->ev_t1, ctx->stream));
-  CU (cudaEventSynchronize (ctx->ev_t1));
-  float ms = 0.f;
-  cudaEventElapsedTime (&ms, ctx->ev_t0, ctx->ev_t1);
-  out->ms_device = ms;
+  TRY (device_time (ctx, out));
   return out->status;
 }
 
@@ -1107,7 +1125,7 @@ static int count_files_once (tjb_ctx *ctx, const char *const *files, int n_files
     if (!ctx->h_free[i]) CU (cudaEventCreateWithFlags (&ctx->h_free[i], cudaEventDisableTiming));
   }
   for (int i = 0; i < 2; i++) TRY (ensure (ctx, ctx->d_chunk[i], TJB_CHUNK_BYTES));
-  CU (cudaEventRecord (ctx->ev_t0, ctx->stream));
+  if (ctx->profiling) CU (cudaEventRecord (ctx->ev_t0, ctx->stream));
   CU (cudaEventRecord (ctx->ev_ready, ctx->stream));
   CU (cudaStreamWaitEvent (ctx->copy_stream, ctx->ev_ready, 0));
   // One decoder thread per file (R1 and R2 inflate and parse concurrently; the order of the reads does not matter to
@@ -1169,11 +1187,7 @@ int tjb_count_sample_files (tjb_ctx *ctx, const char *const *files, int n_files,
   }
   if (rc == TJB_INTERNAL_RETRY) { ctx->err = "aggregation table overflow persisted"; return TJB_ERR_CUDA; }
   if (rc < 0) return rc;
-  CU (cudaEventRecord (ctx->ev_t1, ctx->stream));
-  CU (cudaEventSynchronize (ctx->ev_t1));
-  float ms = 0.f;
-  cudaEventElapsedTime (&ms, ctx->ev_t0, ctx->ev_t1);
-  out->ms_device = ms;
+  TRY (device_time (ctx, out));
   size_t nl = strlen (files[0]);
   out->name = (char*) malloc (nl + 1);
   if (out->name) memcpy (out->name, files[0], nl + 1);
@@ -1209,7 +1223,7 @@ int tjb_sample_begin (tjb_ctx *ctx, const tjb_opts *opt, size_t n_bytes_hint)
 {
   if (!ctx) return TJB_ERR_ARG;
   TRY (begin_sample (ctx, opt, n_bytes_hint));
-  CU (cudaEventRecord (ctx->ev_t0, ctx->stream));
+  if (ctx->profiling) CU (cudaEventRecord (ctx->ev_t0, ctx->stream));
   return 0;
 }
 
@@ -1281,11 +1295,7 @@ int tjb_sample_finalise (tjb_ctx *ctx, tjb_counter_out *out)
   int rc = finalise (ctx, out);
   if (rc == TJB_INTERNAL_RETRY) { ctx->err = "aggregation table too small for this sample: begin the sample again"; return TJB_ERR_TOO_LARGE; }
   if (rc < 0) return rc;
-  CU (cudaEventRecord (ctx->ev_t1, ctx->stream));
-  CU (cudaEventSynchronize (ctx->ev_t1));
-  float ms = 0.f;
-  cudaEventElapsedTime (&ms, ctx->ev_t0, ctx->ev_t1);
-  out->ms_device = ms;
+  TRY (device_time (ctx, out));
   return out->status;
 }
 

@@ -7,48 +7,47 @@
 // the run-length count and the canon_flag OR of :361-362 in one 64-bit add).  Everything after the scan works on the
 // DISTINCT observations ("weighted records": key + count word), 58 K instead of 3.75 M at BASELINE config 2.
 //
-// Slot protocol (no thread ever waits for another):
-//   cnt == 0                      empty.  CAS 0 -> BUSY claims the slot; the claimer stores the key, fences, and adds
-//                                 (weight + BUSY), which clears the busy bit (2^63 + 2^63 wraps) and publishes the slot
-//   cnt & BUSY                    being written by its claimer: the key cannot be compared yet -> the observation is
-//                                 DEFERRED to the overflow list (a few records per sample)
-//   otherwise                     ready: compare the key, add the weight on a match, else probe on (linear)
+// Slot protocol (no thread ever waits for another; keys AND counts are zeroed per sample, and no real key is zero: the
+// length field is biased by 512):
+//   key == mine                   add my weight to the slot's count word (one load + one RED: the common case)
+//   key == 0                      empty, or claimed a moment ago: CAS count 0 -> my weight claims the slot, the claimer
+//                                 then stores the key.  A thread that loses the CAS reads the key once more: mine ->
+//                                 add; still 0 -> the observation is DEFERRED to the overflow list; else probe on
+//   otherwise                     another key: probe on (linear)
 // After TAB_MAXPROBE probes the observation is deferred as well.  Deferred observations keep their raw form (one record
 // each, flag bits set); the partition kernel turns them into weighted records of weight 1, so a key may reach the
-// bucket kernel in several records: it adds the weights of equal keys after sorting.  Keys are never cleared: a
-// slot's key is only read once its count says it has been written for THIS sample (the count array is zeroed per sample).
+// bucket kernel in several records: it adds the weights of equal keys after sorting.  (A key can also end up in two
+// slots when a reader sees a slot half written and probes on: same remedy.)  W = 3 keys take two 16-byte halves
+// {w0, w1} {w2, w0}: the copy of the never-zero w0 in the second half tells a reader that both halves are there.
 #pragma once
 #include "tjb_common.cuh"
 
-#define TAB_BUSY (1ULL << 63)
 #ifndef TAB_MAXPROBE
 #define TAB_MAXPROBE 48
 #endif
 
 struct AggTable {
-  u64 *keys;                 // [slots][W]
-  unsigned long long *cnt;   // [slots] forward count | reverse count << 32 (bit 63: busy)
+  unsigned long long *cnt;   // [slots] forward count | reverse count << 32
+  u64 *keys;                 // [slots][2] (W = 2) or [slots][4] (W = 3), 16-byte aligned
   u32 mask;                  // slots - 1 (power of two)
 };
+__host__ __device__ inline int table_key_words (int W) { return W == 2 ? 2 : 4; }
+// bytes of a table of that many slots: counts first, keys behind them (one allocation, one memset per sample)
+__host__ __device__ inline size_t table_bytes (size_t slots, int W) { return slots * 8 * (1 + (size_t) table_key_words (W)); }
 
-__device__ __forceinline__ unsigned long long ld_relaxed_u64 (const unsigned long long *p) // from L2, never from a stale L1 line
+// the table lives in global memory: say so, or a pointer that went through a function call is treated as generic
+// (ATOM instead of RED, and a shared-memory path next to every atomic)
+__device__ __forceinline__ void red_add_global (unsigned long long *p, unsigned long long v)
+{ asm volatile ("red.global.add.u64 [%0], %1;" :: "l"(p), "l"(v) : "memory"); }
+__device__ __forceinline__ unsigned long long cas_global (unsigned long long *p, unsigned long long cmp, unsigned long long val)
 {
-  unsigned long long v;
-  asm volatile ("ld.relaxed.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-  return v;
-}
-__device__ __forceinline__ unsigned long long ld_acquire_u64 (const unsigned long long *p)
-{
-  unsigned long long v;
-  asm volatile ("ld.acquire.gpu.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
-  return v;
+  unsigned long long old;
+  asm volatile ("atom.global.cas.b64 %0, [%1], %2, %3;" : "=l"(old) : "l"(p), "l"(cmp), "l"(val) : "memory");
+  return old;
 }
 
 // weight of one raw observation: flag 1 = seen on the forward strand, 2 = reverse complement (hopo_counter.c:237, 245)
 __device__ __forceinline__ unsigned long long flag_weight (u64 w0) { return (w0 & 1) ? 1ULL : (1ULL << 32); }
-// canon_flag of a count word (:362) and the reference's signed 20-bit count field (hopo_counter.h:40)
-__device__ __forceinline__ u32 weight_flag (unsigned long long c) { return ((u32) c ? 1u : 0u) | ((u32) (c >> 32) & 0x7fffffffu ? 2u : 0u); }
-__device__ __forceinline__ int weight_count20 (unsigned long long c) { return sext_field ((long long) (u32) c + (long long) ((u32) (c >> 32) & 0x7fffffffu), 20); }
 
 template <int W> __device__ __forceinline__ u32 key_hash (const Rec<W> &r) // flag bits do not take part
 {
@@ -58,16 +57,27 @@ template <int W> __device__ __forceinline__ u32 key_hash (const Rec<W> &r) // fl
   return h;
 }
 
+// what a slot's key reads as: 0 = nothing there (yet), 1 = `key`, 2 = something else (another key, or a key half written)
+template <int W> __device__ __forceinline__ int table_probe (const AggTable &t, u32 slot, const Rec<W> &key)
+{
+  if (W == 2) {
+    const ulonglong2 v = __ldcg (reinterpret_cast<const ulonglong2*> (t.keys) + slot); // from L2: never a stale L1 line
+    if (v.x == key.w[0] && v.y == key.w[1]) return 1;
+    return v.x == 0 ? 0 : 2;
+  }
+  const ulonglong2 a = __ldcg (reinterpret_cast<const ulonglong2*> (t.keys) + 2 * (size_t) slot);
+  const ulonglong2 b = __ldcg (reinterpret_cast<const ulonglong2*> (t.keys) + 2 * (size_t) slot + 1);
+  if (a.x == key.w[0] && a.y == key.w[1] && b.x == key.w[2] && b.y == key.w[0]) return 1;
+  return (a.x == 0 && b.y == 0) ? 0 : 2;
+}
+
+// key of an occupied slot (after the kernel that filled the table has finished)
 template <int W> __device__ __forceinline__ Rec<W> table_key_at (const AggTable &t, u32 slot)
 {
   Rec<W> y;
-  if (W == 2) {
-    const ulonglong2 v = __ldcg (reinterpret_cast<const ulonglong2*> (t.keys) + slot);
-    y.w[0] = v.x; y.w[1] = v.y;
-  } else {
-#pragma unroll
-    for (int j = 0; j < W; j++) y.w[j] = __ldcg (t.keys + (size_t) W * slot + j);
-  }
+  const ulonglong2 a = __ldcg (reinterpret_cast<const ulonglong2*> (t.keys) + (W == 2 ? 1 : 2) * (size_t) slot);
+  y.w[0] = a.x; y.w[1] = a.y;
+  if (W == 3) y.w[W - 1] = __ldcg (t.keys + 4 * (size_t) slot + 2);
   return y;
 }
 
@@ -75,31 +85,27 @@ template <int W> __device__ __forceinline__ Rec<W> table_key_at (const AggTable 
 enum { TAB_ADDED = 0, TAB_NEW = 1, TAB_DEFER = 2 };
 
 // key: record words with the flag bits cleared.  Returns TAB_NEW when this call created the entry (the caller counts
-// entries and bins them), TAB_DEFER when the observation has to go to the overflow list.
-template <int W> __device__ __forceinline__ int table_add (const AggTable &t, const Rec<W> &key, unsigned long long weight)
+// entries and bins them), TAB_DEFER when the observation has to go to the overflow list.  One copy of the code per
+// kernel (it is called from several places of the scan, and the probe loop must not be unrolled into each of them).
+template <int W> __device__ __noinline__ int table_add (AggTable t, Rec<W> key, unsigned long long weight)
 {
   u32 slot = key_hash<W> (key) & t.mask;
+#pragma unroll 1
   for (int p = 0; p < TAB_MAXPROBE; p++, slot = (slot + 1) & t.mask) {
-    unsigned long long c = ld_acquire_u64 (t.cnt + slot);
-    if (c == 0) {
-      c = atomicCAS (t.cnt + slot, 0ULL, TAB_BUSY);
-      if (c == 0) {
+    int seen = table_probe<W> (t, slot, key);
+    if (seen == 0) {
+      if (cas_global (t.cnt + slot, 0ULL, weight) == 0ULL) {
         if (W == 2) __stcg (reinterpret_cast<ulonglong2*> (t.keys) + slot, make_ulonglong2 (key.w[0], key.w[1]));
         else {
-#pragma unroll
-          for (int j = 0; j < W; j++) __stcg (t.keys + (size_t) W * slot + j, key.w[j]);
+          __stcg (reinterpret_cast<ulonglong2*> (t.keys) + 2 * (size_t) slot, make_ulonglong2 (key.w[0], key.w[1]));
+          __stcg (reinterpret_cast<ulonglong2*> (t.keys) + 2 * (size_t) slot + 1, make_ulonglong2 (key.w[W - 1], key.w[0]));
         }
-        __threadfence (); // the key is visible before the count says so
-        atomicAdd (t.cnt + slot, weight + TAB_BUSY);
         return TAB_NEW;
       }
+      seen = table_probe<W> (t, slot, key); // claimed by somebody else a moment ago: its key may be there by now
+      if (seen == 0) return TAB_DEFER;
     }
-    if (c & TAB_BUSY) return TAB_DEFER;
-    const Rec<W> y = table_key_at<W> (t, slot);
-    bool eq = true;
-#pragma unroll
-    for (int j = 0; j < W; j++) eq = eq && (y.w[j] == key.w[j]);
-    if (eq) { atomicAdd (t.cnt + slot, weight); return TAB_ADDED; }
+    if (seen == 1) { red_add_global (t.cnt + slot, weight); return TAB_ADDED; }
   }
   return TAB_DEFER;
 }
