@@ -1,23 +1,34 @@
 #!/usr/bin/env python
-"""bench.py — FASTQ bases/s of the hot path (HT scan -> sort -> context histograms) on N B200s.
+"""bench.py — FASTQ bases/s of the hot path (HT scan -> context histograms) on N B200s.
 
-    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference] [--legs a,b,...]
     python -m torch.distributed.run --nnodes=1 --nproc-per-node N ... bench.py --gpus N ...
 
-Workload (BASELINE.json configs[1]): one E. coli-size sample per GPU — 5 Mbp random genome with injected
+Headline workload (BASELINE.json configs[1]): one E. coli-size sample per GPU — 5 Mbp random genome with injected
 tract-length polymorphism, 100x, 2x150 bp paired end = 500 Mbases (3.33 M reads), default -k 25 -m 4 -i 5.
-A step = one full pass of the replaced span (scan + sort + reduce + QC + groups + coverage + copy-out) over that
-sample.  `value`: reads resident in HBM when the timed region starts.  `e2e`: the same through the C ABI with the
-decoded reads in pinned HOST memory (H2D inside the call, results copied back to malloc'ed host memory).
-Weak scaling: every rank processes its own sample; no data-path collective on this part of the path.
+A step = one full pass of the replaced span (scan + aggregate + sort + QC + groups + coverage + results on the host)
+over that sample.  Every timed number is gated on parity: before any timing the unmodified reference (oracle/_ref)
+counts the SAME full sample and its state at the mapper call must equal ours, device-resident and from host memory.
+
+  value   reads resident in HBM when the timed region starts; the steps are dealt to two contexts of the GPU (the
+          reference's own loop over samples is a parallel one, src/genome_set.c:66-68), results in the pinned arena
+  e2e     the same through the reference-facing C ABI call with the decoded reads in pinned HOST memory: host -> device
+          copies inside, results in malloc()ed host memory as the binding needs them
+  extra legs (rank 0, in the same JSON line): the sample with 0.1 % and 1 % substitution errors, BASELINE configs[4]
+          (k=32 m=3 300x), configs[3] (96 samples, strong scaling over the ranks, exchange + union + merge inside the
+          timed region), the cross-sample exchange on its own, FASTQ files (host decode inside) beside the reference.
+--impl reference: the unmodified reference (oracle/_ref) on the host cores, the same samples, one thread per sample
+like its OpenMP loop (N samples on min(N, cores) threads at --gpus N).
 """
 import argparse
 import json
 import os
 import subprocess
 import sys
+import tempfile
 import threading
 import time
+from concurrent.futures import ThreadPoolExecutor
 
 ROOT = os.path.dirname(os.path.abspath(__file__))
 sys.path.insert(0, ROOT)
@@ -26,8 +37,10 @@ import numpy as np  # noqa: E402
 
 GENOME, COVERAGE, READ_LEN = 5_000_000, 100, 150
 K, M, MIN_COV = 25, 4, 5
-CPU_SAMPLE_READS = 1_000_000
 METRIC = "FASTQ bases/sec for HT scan+context histograms"
+WORKLOAD = "configs[1]: one sample per GPU, 5 Mbp genome, 100x, 2x150 bp PE, k=25 m=4 i=5"
+C4_SAMPLES, C4_GENOME, C4_COVERAGE, C4_FRACTION = 96, 1_700_000, 50, 0.05
+ALL_LEGS = ["errors", "c5", "c4", "exchange", "files"]
 
 
 def load_peaks():
@@ -38,7 +51,7 @@ def load_peaks():
 
 
 class ClockSampler(threading.Thread):
-    """samples nvidia-smi clocks / throttle reasons during the timed region"""
+    """samples SM clocks / throttle reasons during the timed region (NVML in-process; nvidia-smi as a fallback)"""
     Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
          "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
 
@@ -46,8 +59,7 @@ class ClockSampler(threading.Thread):
         super().__init__(daemon=True)
         self.index, self.rows, self.stop_flag = index, [], False
         # NVML in-process (a query costs microseconds); spawning nvidia-smi enumerates every GPU of the box under the
-        # driver's lock and was seen to stretch the steps of a 2-rank run by 25 %.  Initialised here, before the timed
-        # region, so that the first sample is taken as soon as the thread starts.
+        # driver's lock and was seen to stretch the steps of a 2-rank run by 25 %.
         self.nvml = None
         try:
             import pynvml
@@ -71,7 +83,7 @@ class ClockSampler(threading.Thread):
                     self.rows.append([str(sm), str(self.mx)] + ["Active" if r & b else "Not Active" for b in bits])
                     if self.stop_flag:
                         break
-                    time.sleep(0.02)  # a query takes the driver's lock for ~1 ms on an 8-GPU box: keep them rare
+                    time.sleep(0.005)
                 return
             except Exception as e:
                 self.nvml = None
@@ -97,102 +109,132 @@ class ClockSampler(threading.Thread):
                 "samples": len(self.rows), "source": "nvml" if self.nvml else "nvidia-smi"}
 
 
-def make_sample(rank, n_reads=None):
+def make_sample(sample, error_rate=0.0, genome=GENOME, coverage=COVERAGE, fraction=0.02):
     from tatajuba_b200 import synth
-    buf = synth.sample_buffer(GENOME, COVERAGE, seed=1, sample=rank, read_len=READ_LEN,
-                              max_pairs=None if n_reads is None else n_reads // 2)
-    return buf
+    return synth.sample_buffer(genome, coverage, seed=1, sample=sample, read_len=READ_LEN, error_rate=error_rate,
+                               fraction=fraction)
 
 
-def cpu_baseline(buf, n_reads):
-    """the reference's own code (oracle/_ref) — or the plain-C port if it did not travel — on a bounded sample"""
+class quiet_stderr:
+    """the reference prints per-sample banners on stderr"""
+
+    def __enter__(self):
+        sys.stderr.flush()
+        self.devnull, self.saved = os.open(os.devnull, os.O_WRONLY), os.dup(2)
+        os.dup2(self.devnull, 2)
+
+    def __exit__(self, *a):
+        os.dup2(self.saved, 2)
+        os.close(self.devnull)
+        os.close(self.saved)
+
+
+def reference_run(buf, k=K, m=M, cov=MIN_COV, rb=True):
+    """the unmodified reference on one sample, one thread -> (boundary state, seconds of the replaced span)"""
     from oracle import pyoracle
-    sample = buf[: n_reads * (READ_LEN + 1)]
-    bases = n_reads * READ_LEN
-    if pyoracle.Reference.available():
-        ref, kind = pyoracle.Reference(), "reference"
-        devnull, saved = os.open(os.devnull, os.O_WRONLY), os.dup(2)
-        os.dup2(devnull, 2)  # the reference prints per-sample banners on stderr
-        try:
-            t0 = time.perf_counter()
-            ref.run_buffer(sample.tobytes(), K, M, MIN_COV, True)
-            dt = time.perf_counter() - t0
-        finally:
-            os.dup2(saved, 2)
-            os.close(devnull)
-    else:
-        o, kind = pyoracle.Restatement(), "port"
-        t0 = time.perf_counter()
-        o.run_buffer(sample, K, M, MIN_COV, True)
-        dt = time.perf_counter() - t0
-    return {"value": bases / dt, "unit": "bases/s", "cores": 1, "kind": kind, "seconds": dt,
-            "sample": f"first {n_reads} reads ({bases / 1e6:.0f} Mbases) of the workload, decoded in host memory; "
-                      "update_hopo_counter_from_seq per read + finalise_hopo_counter up to the mapper call; the "
-                      "reference runs one sample on one thread (OpenMP is over samples only)"}
+    ref = pyoracle.Reference()
+    b = ref.run_buffer(buf, k, m, cov, rb)
+    return b, b.secs_scan + b.secs_finalise
 
 
-def cpu_all_cores(buf, n_reads):
-    """the reference's own parallelism is one OpenMP thread per SAMPLE (genome_set.c:67): with as many samples as host
-    cores in flight, every thread runs the same bounded sample; aggregate bases/s (information beside the 1-thread
-    number, which is what the reference does with the single sample of this workload)"""
-    from concurrent.futures import ThreadPoolExecutor
+def assert_parity(hc, want, what):
     from oracle import pyoracle
-    if not pyoracle.Reference.available():
-        return None
-    cores = os.cpu_count() or 1
-    sample = buf[: n_reads * (READ_LEN + 1)].tobytes()
-    refs = [pyoracle.Reference() for _ in range(cores)]
-    devnull, saved = os.open(os.devnull, os.O_WRONLY), os.dup(2)
-    os.dup2(devnull, 2)
-    try:
-        with ThreadPoolExecutor(cores) as ex:  # ctypes releases the GIL inside the C call
-            t0 = time.perf_counter()
-            list(ex.map(lambda r: r.run_buffer(sample, K, M, MIN_COV, True), refs))
-            dt = time.perf_counter() - t0
-    finally:
-        os.dup2(saved, 2)
-        os.close(devnull)
-    return {"value": cores * n_reads * READ_LEN / dt, "unit": "bases/s", "cores": cores, "seconds": dt,
-            "sample": f"{cores} concurrent copies of the bounded sample, one per thread"}
+    got = pyoracle.Boundary(hc.status, hc.n_raw, hc.elem, hc.idx_initial, hc.idx_final, hc.coverage)
+    pyoracle.assert_same_boundary(got, want, what)
 
 
+def n_bases_of(buf):
+    return buf.size // (READ_LEN + 1) * READ_LEN
+
+
+# --------------------------------------------------------------------------------------- reference arm ----
 def run_reference_arm(args, rank):
-    """--impl reference: the reference's CPU implementation on the host cores; rank 0 only"""
+    """--impl reference: the reference's CPU implementation on the host cores; rank 0 only.  One step = every one of
+    the N samples of the workload (N = --gpus) once, one thread per sample on min(N, cores) threads."""
     if rank != 0:
         return
-    n_reads = CPU_SAMPLE_READS
-    buf = make_sample(0, n_reads)
+    from oracle import pyoracle
+    kind = "reference" if pyoracle.Reference.available() else "port"
+    n = args.gpus
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    threads = min(n, cores)
+    with ThreadPoolExecutor(threads) as ex:
+        bufs = list(ex.map(make_sample, range(n)))
+    bases = sum(n_bases_of(b) for b in bufs)
+    workers = [pyoracle.Reference() if kind == "reference" else pyoracle.Restatement() for _ in range(n)]
+
+    def one(i):
+        return workers[i].run_buffer(bufs[i], K, M, MIN_COV, True)
     times = []
-    base = None
-    for i in range(args.warmup + args.steps):
-        base = cpu_baseline(buf, n_reads)
-        if i >= args.warmup:
-            times.append(base["seconds"])
+    with quiet_stderr(), ThreadPoolExecutor(threads) as ex:  # ctypes releases the GIL inside the C call
+        for i in range(args.warmup + args.steps):
+            t0 = time.perf_counter()
+            list(ex.map(one, range(n)))
+            dt = time.perf_counter() - t0
+            if i >= args.warmup:
+                times.append(dt)
     dt = sum(times) / len(times)
-    v = n_reads * READ_LEN / dt
-    base["value"] = v
-    try:
-        base["all_cores"] = cpu_all_cores(buf, n_reads)
-    except Exception as e:  # information only
-        base["all_cores"] = {"error": str(e)}
-    print(json.dumps({
+    v = bases / dt
+    line = {
         "impl": "reference", "metric": METRIC, "value": v, "unit": "bases/s", "n_gpus": args.gpus, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": dt * 1e3, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "u8/u64", "data": "synthetic",
-        "config": {"workload": "configs[1]: 5 Mbp genome, 100x, 2x150 bp PE, k=25 m=4 i=5 (bounded sample per step)",
-                   "reads_per_step": n_reads},
-        "cpu_baseline": base, "gpu_launches": 0,
-        "e2e": {"value": v, "unit": "bases/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}))
+        "config": {"workload": WORKLOAD, "same_config": True, "samples_per_step": n, "bases_per_step": bases,
+                   "span": "update_hopo_counter_from_seq per read + finalise_hopo_counter up to the mapper call, reads "
+                           "decoded in host memory (like the GPU arm's e2e)"},
+        "cpu_baseline": {"value": v, "unit": "bases/s", "cores": threads, "kind": kind, "host_cores": cores,
+                         "sample": f"the full workload: {n} sample(s) of {bases // n / 1e6:.0f} Mbases, one thread per sample "
+                                   "(the reference's OpenMP loop is over samples, src/genome_set.c:66-68)"},
+        "gpu_launches": 0,
+        "e2e": {"value": v, "unit": "bases/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    if "files" in args.legs and kind == "reference":
+        line["from_files"] = files_leg_reference(bufs[0])
+    print(json.dumps(line))
 
 
+FILES_READS = 400_000  # 60 Mbases: writing the full sample as .gz from Python would take minutes
+
+
+def write_files(d, buf):
+    from tatajuba_b200 import synth
+    rows = buf[: FILES_READS * (READ_LEN + 1)].reshape(FILES_READS, READ_LEN + 1)
+    out = {}
+    for ext in (".fastq", ".fastq.gz"):
+        r1, r2 = os.path.join(d, "s_R1" + ext), os.path.join(d, "s_R2" + ext)
+        synth.write_fastq(r1, rows[0::2])
+        synth.write_fastq(r2, rows[1::2])
+        out["gz" if ext.endswith(".gz") else "plain"] = [r1, r2]
+    return out
+
+
+def files_leg_reference(buf):
+    from oracle import pyoracle
+    ref = pyoracle.Reference()
+    leg = {"sample": f"first {FILES_READS} reads of the workload as paired FASTQ (R1/R2), plain and gzip -1; kseq decode inside",
+           "threads": 1}
+    with tempfile.TemporaryDirectory() as d, quiet_stderr():
+        for kind, files in write_files(d, buf).items():
+            best = None
+            for _ in range(2):
+                b = ref.run_files(files, K, M, MIN_COV, True)
+                dt = b.secs_scan + b.secs_finalise
+                best = dt if best is None else min(best, dt)
+            leg[kind] = {"value": FILES_READS * READ_LEN / best, "unit": "bases/s", "ms": best * 1e3}
+    return leg
+
+
+# --------------------------------------------------------------------------------------------- our arm ----
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=10)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--legs", default=",".join(ALL_LEGS), help="extra legs to run (comma separated; 'none' for the headline only)")
+    ap.add_argument("--contexts", type=int, default=2, help="contexts per GPU the steps are dealt to")
+    ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the parity gate / CPU baseline (kernel experiments only)")
     args = ap.parse_args()
+    args.legs = [x for x in args.legs.split(",") if x and x != "none"]
     rank = int(os.environ.get("RANK", 0))
     local_rank = int(os.environ.get("LOCAL_RANK", 0))
     world = int(os.environ.get("WORLD_SIZE", 1))
@@ -200,23 +242,14 @@ def main():
         run_reference_arm(args, rank)
         return
 
-    # The result arrays are malloc()ed by the library and free()d by this script every step.  Keep freed memory in the
-    # heap (no trim, no mmap per array): otherwise whether a step pays ~0.5 ms of page faults for fresh pages depends
-    # on what else touched the allocator (seen: the first timed steps after an NCCL barrier), which is not the path.
-    try:
-        import ctypes
-        libc = ctypes.CDLL("libc.so.6")
-        libc.mallopt(-1, 1 << 30)  # M_TRIM_THRESHOLD
-        libc.mallopt(-3, 1 << 30)  # M_MMAP_THRESHOLD
-    except Exception:
-        pass
     import torch
     import torch.distributed as dist
-    from tatajuba_b200 import Context, TatajubaOptions
+    from tatajuba_b200 import Context, TatajubaOptions, genome_set
     assert torch.cuda.is_available(), "bench.py needs a GPU (there is no CPU fallback)"
     torch.cuda.set_device(local_rank)
+    dev = torch.device("cuda", local_rank)
     if world > 1:
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        dist.init_process_group("nccl", device_id=dev)
 
     def barrier():
         if world > 1:
@@ -226,154 +259,303 @@ def main():
     def max_over_ranks(x):
         if world == 1:
             return x
-        if os.environ.get("BENCH_DEBUG"):
-            sys.stderr.write(f"[bench] rank {rank}: {x:.3f} ms\n")
         t = torch.tensor([x], dtype=torch.float64, device="cuda")
         dist.all_reduce(t, op=dist.ReduceOp.MAX)
         return float(t.item())
 
+    def all_ranks_ok(ok):
+        if world == 1:
+            return ok
+        t = torch.tensor([1 if ok else 0], dtype=torch.int64, device="cuda")
+        dist.all_reduce(t, op=dist.ReduceOp.MIN)
+        return bool(t.item())
+
     opt = TatajubaOptions(K, M, MIN_COV, True, paired_end=True)
+    ctxs = [Context(local_rank) for _ in range(max(1, args.contexts))]
+    ctx = ctxs[0]
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+
+    def timed(fn):
+        """device time of fn() between two events on an otherwise idle stream, bracketed by barriers; max over ranks"""
+        barrier()
+        e0.record()
+        out = fn()
+        torch.cuda.synchronize()
+        e1.record()
+        barrier()
+        return max_over_ranks(e0.elapsed_time(e1)), out
+
+    def count_steps(steps, count_one, contexts):
+        return genome_set.count_samples(contexts, steps, count_one)
+
+    def kernel_table(c, run, steps=5):
+        """per-kernel device times (events around every launch): a separate, untimed pass"""
+        c.set_profiling(2)
+        c.reset_kernel_stats()
+        for _ in range(steps):
+            run()
+        st = c.kernel_stats()
+        c.set_profiling(0)
+        return {s["name"]: {"launches": s["launches"] // steps, "us": round(s["ms_total"] / steps * 1e3, 1)} for s in st}
+
+    # ---- the sample, and the parity gate at full size (outside every timed region) ---------------------------------
     buf = make_sample(rank)
-    n_bytes = buf.size
-    n_reads = n_bytes // (READ_LEN + 1)
-    n_bases = n_reads * READ_LEN
-    ctx = Context(local_rank)
-    stream = torch.cuda.ExternalStream(ctx.stream(), device=local_rank)
+    n_bytes, n_bases, n_reads = buf.size, n_bases_of(buf), buf.size // (READ_LEN + 1)
     h_pinned = torch.from_numpy(buf).pin_memory()
     d_buf = h_pinned.cuda()
     torch.cuda.synchronize()
+    parity, cpu_base = "skipped (--no-cpu-baseline)", None
+    if not args.no_cpu_baseline:
+        from oracle import pyoracle
+        kind = "reference" if pyoracle.Reference.available() else "port"
+        with quiet_stderr():
+            if kind == "reference":
+                want, secs = reference_run(buf)
+            else:
+                t0 = time.perf_counter()
+                want = pyoracle.Restatement().run_buffer(buf, K, M, MIN_COV, True)
+                secs = time.perf_counter() - t0
+        assert_parity(ctx.count_device(d_buf.data_ptr(), n_bytes, opt), want, "parity gate, device-resident")
+        assert_parity(ctx.count_host(h_pinned, opt), want, "parity gate, host buffer")
+        ctx.set_result_mode(True)
+        assert_parity(ctx.count_device(d_buf.data_ptr(), n_bytes, opt), want, "parity gate, arena results")
+        ctx.set_result_mode(False)
+        parity = f"{kind}, full sample (state at the mapper call: elements, group indices, coverage; device, host and arena paths)"
+        cpu_base = {"value": n_bases / secs, "unit": "bases/s", "cores": 1, "kind": kind, "seconds": secs,
+                    "sample": f"the full sample ({n_bases / 1e6:.0f} Mbases) decoded in host memory, one thread (the reference "
+                              "parallelises over samples only); the same run is the parity gate"}
 
-    # ---- device-resident arm (value) + roofline of the dominant kernel --------------------------------
-    for _ in range(args.warmup):
-        hc = ctx.count_device(d_buf.data_ptr(), n_bytes, opt)
-    assert hc.status == 0
-    ctx.set_profiling(2)
-    ctx.reset_kernel_stats()
+    # ---- value: device-resident, steps dealt to the contexts of this GPU, results in the arena -----------------------
+    for c in ctxs:
+        c.set_result_mode(True)
+        for _ in range(args.warmup):
+            hc = c.count_device(d_buf.data_ptr(), n_bytes, opt)
+        assert hc.status == 0
+    stats0 = dict(n_raw=hc.n_raw, n_distinct=hc.n_distinct, n_elem=hc.n_elem, n_idx=hc.n_idx, coverage=hc.coverage)
+    for c in ctxs:
+        c.set_profiling(1)  # the scan kernel is timed live, inside the timed region (events on the context's stream)
+        c.reset_kernel_stats()
     sampler = ClockSampler(local_rank)
-    if rank == 0 and not os.environ.get("BENCH_NO_SAMPLER"):  # one poller per job: 8 nvidia-smi loops would steal host cores from the ranks' launch threads
+    if rank == 0 and not os.environ.get("BENCH_NO_SAMPLER"):
         sampler.start()
-    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-    barrier()
-    e0.record(stream)
-    for _ in range(args.steps):
-        hc = ctx.count_device(d_buf.data_ptr(), n_bytes, opt)
-    e1.record(stream)
-    barrier()
-    ms = max_over_ranks(e0.elapsed_time(e1))
+    ms, _ = timed(lambda: count_steps(args.steps, lambda c, s: c.count_device(d_buf.data_ptr(), n_bytes, opt), ctxs))
     clocks = sampler.summary() if rank == 0 else None
-    stats = ctx.kernel_stats()
-    launches = ctx.launch_count()
-    ctx.set_profiling(0)
+    scan_ms = scan_launches = scan_bytes = 0
+    launches = 0
+    for c in ctxs:
+        for s in c.kernel_stats():
+            if s["name"] == "tjb_scan_kernel":
+                scan_ms += s["ms_total"]; scan_launches += s["launches"]; scan_bytes += s["bytes_algorithmic"]
+        launches += c.launch_count()
+        c.set_profiling(0)
+    ms_single, _ = timed(lambda: [ctx.count_device(d_buf.data_ptr(), n_bytes, opt) for _ in range(args.steps)])
+    kernels = kernel_table(ctx, lambda: ctx.count_device(d_buf.data_ptr(), n_bytes, opt))
 
-    # ---- end-to-end arm: pinned host buffer -> C ABI -> host results ----------------------------------
-    # (large host buffers cross PCIe 2-bit packed + exceptions, packed by host threads inside the timed region and
-    # rebuilt on the device; TJB_HOST_PACK=0 = the bytes as they are, timed next to it over 3 steps)
-    def e2e_arm(steps):
+    # ---- e2e: pinned host buffer -> C ABI -> malloc()ed host results --------------------------------------------------
+    for c in ctxs:
+        c.set_result_mode(False)
         for _ in range(2):
-            ctx.count_host(h_pinned, opt)
-        barrier()
-        ctx.reset_kernel_stats()
-        e0.record(stream)
-        for _ in range(steps):
-            h = ctx.count_host(h_pinned, opt)
-        e1.record(stream)
-        barrier()
-        return max_over_ranks(e0.elapsed_time(e1)) / steps, ctx.h2d_bytes() // steps, h
+            hh = c.count_host(h_pinned, opt)
+        c.reset_kernel_stats()
+    ms_e2e, _ = timed(lambda: count_steps(args.steps, lambda c, s: c.count_host(h_pinned, opt), ctxs))
+    h2d = sum(c.h2d_bytes() for c in ctxs) // args.steps
+    d2h = 40 * hh.n_elem + 8 * hh.n_idx + 88
+    ms_e2e_single, _ = timed(lambda: [ctx.count_host(h_pinned, opt) for _ in range(max(3, args.steps // 2))])
+    ms_e2e_single /= max(3, args.steps // 2) / args.steps
     packing = os.environ.get("TJB_HOST_PACK")
     os.environ["TJB_HOST_PACK"] = "0"
-    ms_plain, h2d_plain, _ = e2e_arm(3)
+    ms_plain, _ = timed(lambda: [ctx.count_host(h_pinned, opt) for _ in range(3)])
     if packing is None:
         del os.environ["TJB_HOST_PACK"]
     else:
         os.environ["TJB_HOST_PACK"] = packing
-    ms_e2e_step, h2d, hh = e2e_arm(args.steps)
-    ms_e2e = ms_e2e_step * args.steps
-    d2h = 24 * hh.n_elem + 8 * hh.n_idx + 64  # an element crosses PCIe without its 16 constant bytes
     transfer = {"mode": "2-bit packed + exceptions" if h2d < n_bytes else "plain", "host_bytes_per_step": n_bytes,
-                "host_threads": os.cpu_count() if packing is None else packing,
-                "plain": {"ms_per_step": ms_plain, "h2d_bytes_per_step": h2d_plain,
-                          "value": world * n_bases / (ms_plain * 1e-3), "unit": "bases/s"}}
+                "one_context": {"ms_per_step": ms_e2e_single / args.steps},
+                "plain": {"ms_per_step": ms_plain / 3, "value": world * n_bases / (ms_plain / 3 * 1e-3), "unit": "bases/s"}}
 
-    # ---- cross-sample exchange: query rows -> allgather over the ranks -> union on the GPU ---------
-    from tatajuba_b200 import genome_set
-    exch = []
-    for _ in range(3):
-        barrier()
-        t0 = time.perf_counter()
-        rows = genome_set.query_rows(hh)
-        tables = genome_set.allgather_tables({rank: rows}, world)
-        union, _index = genome_set.union_queries(ctx, tables, K)
-        torch.cuda.synchronize()
-        exch.append((time.perf_counter() - t0) * 1e3)
-    ms_exchange = max_over_ranks(min(exch))
-    exchange = {"ms": ms_exchange, "samples": world, "rows": int(sum(len(t) for t in tables)), "n_union": int(len(union)),
-                "collective": "none (1 rank)" if world == 1 else "nccl all_gather_into_tensor x2",
-                "note": "outside the timed steps: once per run, after every sample has been counted"}
+    extra = {}
+    # ---- the sample with substitution errors (errors create singleton contexts: the opposite of the 64:1 collapse) ----
+    if "errors" in args.legs and world == 1:
+        extra["errors"] = {}
+        for err in (0.001, 0.01):
+            extra["errors"][str(err)] = single_sample_leg(ctxs, opt, make_sample(0, error_rate=err), args, timed, count_steps, kernel_table)
+    if "c5" in args.legs and world == 1:
+        from tatajuba_b200 import synth
+        c5 = synth.sample_buffer(GENOME, 300, seed=3)
+        extra["c5"] = single_sample_leg(ctxs, TatajubaOptions(32, 3, 5, True, paired_end=True), c5, args, timed, count_steps,
+                                        kernel_table, k=32, m=3, steps=max(3, args.steps // 2))
+        extra["c5"]["workload"] = "configs[4]: k=32 (3-word records), m=3, 300x of a 5 Mbp genome = 1.5 Gbases"
+        del c5
+    if "c4" in args.legs:
+        extra["c4"] = c4_leg(ctxs, rank, world, timed, all_ranks_ok, args)
+    if "exchange" in args.legs:
+        for c in ctxs:
+            c.set_result_mode(True)
+        hh = ctx.count_device(d_buf.data_ptr(), n_bytes, opt)
+        rows = genome_set.query_rows_device(ctx, hh).clone()
 
+        def exchange():
+            all_rows, sizes = genome_set.allgather_tables_device({rank: rows}, world)
+            return genome_set.union_queries_device(ctx, all_rows, K), sizes
+        exchange()
+        ms_x = min(timed(exchange)[0] for _ in range(3))
+        (uni, _idx), sizes = exchange()
+        extra["exchange"] = {"ms": ms_x, "samples": world, "rows": int(sum(sizes)), "n_union": int(uni.shape[0]),
+                             "collective": "none (1 rank)" if world == 1 else "nccl all_gather_into_tensor x2 (counts, rows), device to device",
+                             "path": "query rows written on the device, gathered GPU to GPU, union through the aggregation table"}
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
-    # ---- from FASTQ files (host decode inside): bounded sample, 1-GPU runs only (information, SURVEY.md 8d iii) -----
-    files_leg = None
-    if world == 1:
-        import tempfile
-        from tatajuba_b200 import synth
-        n_fr = 400_000  # reads (60 Mbases): writing the full sample as .gz from Python would take minutes
-        rows = buf[: n_fr * (READ_LEN + 1)].reshape(n_fr, READ_LEN + 1)
-        files_leg = {"sample": f"first {n_fr} reads of the workload written as paired FASTQ (R1/R2), plain and gzip -1",
-                     "decoder_threads": 2}
+    if "files" in args.legs and world == 1:
+        leg = {"sample": f"first {FILES_READS} reads of the workload as paired FASTQ (R1/R2), plain and gzip -1; host decode inside",
+               "decoder_threads": 2}
+        ctx.set_result_mode(False)
         with tempfile.TemporaryDirectory() as d:
-            for ext in (".fastq", ".fastq.gz"):
-                r1, r2 = os.path.join(d, "s_R1" + ext), os.path.join(d, "s_R2" + ext)
-                synth.write_fastq(r1, rows[0::2])
-                synth.write_fastq(r2, rows[1::2])
+            for kind, files in write_files(d, buf).items():
                 best = None
                 for _ in range(3):
                     t0 = time.perf_counter()
-                    hf = ctx.count_files([r1, r2], opt)
+                    hf = ctx.count_files(files, opt)
                     dt = time.perf_counter() - t0
                     best = dt if best is None else min(best, dt)
-                files_leg["gz" if ext.endswith(".gz") else "plain"] = {"value": hf.n_bases / best, "unit": "bases/s",
-                                                                        "ms": best * 1e3, "bases": int(hf.n_bases)}
+                leg[kind] = {"value": hf.n_bases / best, "unit": "bases/s", "ms": best * 1e3}
+        from oracle import pyoracle
+        if pyoracle.Reference.available() and not args.no_cpu_baseline:
+            leg["reference"] = files_leg_reference(buf)
+        extra["from_files"] = leg
+
     peak, peak_src = load_peaks()
-    scan = next(s for s in stats if s["name"] == "tjb_scan_kernel")
-    scan_ms = scan["ms_total"] / scan["launches"]
-    scan_bytes = scan["bytes_algorithmic"] / scan["launches"]
-    achieved = scan_bytes / (scan_ms * 1e-3) / 1e9
-    kernel_ms = sum(s["ms_total"] for s in stats)
+    scan_ms_l = scan_ms / max(scan_launches, 1)
+    scan_bytes_l = scan_bytes / max(scan_launches, 1)
+    achieved = scan_bytes_l / (scan_ms_l * 1e-3) / 1e9 if scan_ms_l else 0.0
+    kernel_us = sum(v["us"] for v in kernels.values())
     line = {
         "metric": METRIC, "value": world * n_bases * args.steps / (ms * 1e-3), "unit": "bases/s", "n_gpus": world,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms / args.steps, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "u8/u64", "data": "synthetic",
-        "config": {"workload": "configs[1]: one sample per GPU, 5 Mbp genome, 100x, 2x150 bp PE, k=25 m=4 i=5",
-                   "bases_per_gpu": n_bases, "reads_per_gpu": n_reads, "input_bytes": n_bytes,
-                   "l2": "input (503 MB) larger than L2 (126 MB); no flush needed",
-                   "malloc": "M_TRIM_THRESHOLD / M_MMAP_THRESHOLD = 1 GiB: freed result arrays stay in the heap", "n_raw": hc.n_raw,
-                   "n_distinct": hc.n_distinct, "n_elem": hc.n_elem, "n_idx": hc.n_idx, "coverage": hc.coverage},
-        "e2e": {"value": world * n_bases * args.steps / (ms_e2e * 1e-3), "unit": "bases/s",
-                "ms_per_step": ms_e2e / args.steps, "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
+        "config": {"workload": WORKLOAD, "bases_per_gpu": n_bases, "reads_per_gpu": n_reads, "input_bytes": n_bytes,
+                   "l2": "input (503 MB) larger than L2 (126 MB); no flush needed", "parity": parity,
+                   "contexts_per_gpu": len(ctxs), "one_context_ms_per_step": ms_single / args.steps, **stats0},
+        "e2e": {"value": world * n_bases * args.steps / (ms_e2e * 1e-3), "unit": "bases/s", "ms_per_step": ms_e2e / args.steps,
+                "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "results": "malloc()ed host arrays (reference layout)",
                 "transfer": transfer},
         "gpu_launches": launches,
         "roofline": {"kernel": "tjb_scan_kernel", "bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s",
                      "frac": achieved / peak, "peak_source": peak_src, "traffic": None,
-                     "ms_per_launch": scan_ms, "algorithmic_bytes_per_launch": scan_bytes,
-                     "share_of_kernel_time": scan["ms_total"] / kernel_ms if kernel_ms else None},
-        "kernels": {s["name"]: {"launches": s["launches"], "ms_total": round(s["ms_total"], 4)} for s in stats},
+                     "ms_per_launch": scan_ms_l, "algorithmic_bytes_per_launch": scan_bytes_l,
+                     "share_of_kernel_time": kernels.get("tjb_scan_kernel", {}).get("us", 0) / kernel_us if kernel_us else None,
+                     "pipeline": {"algorithmic_bytes_per_step": int(n_bytes + 96 * stats0["n_raw"]),
+                                  "note": "SURVEY.md 8(d): (1 + 96 rho) N bytes per sample over one context's step time",
+                                  "frac": (n_bytes + 96 * stats0["n_raw"]) / (ms_single / args.steps * 1e-3) / 1e9 / peak}},
+        "kernels": kernels,
         "clocks": clocks,
-        "exchange": exchange,
-        "from_files": files_leg,
     }
+    line.update(extra)
     tp = os.path.join(ROOT, "profiles", "scan_traffic.json")  # dram bytes of one scan launch from an ncu --set full capture
     if os.path.exists(tp):
         tr = json.load(open(tp))
         line["roofline"]["traffic"] = tr["dram_bytes_read"] + tr["dram_bytes_write"]
         line["roofline"]["traffic_source"] = tr.get("source")
-    if not args.no_cpu_baseline:
-        line["cpu_baseline"] = cpu_baseline(buf, min(CPU_SAMPLE_READS, n_reads))
+    if cpu_base:
+        line["cpu_baseline"] = cpu_base
     print(json.dumps(line))
     if world > 1:
         dist.destroy_process_group()
+
+
+def single_sample_leg(ctxs, opt, buf, args, timed, count_steps, kernel_table, k=K, m=M, steps=None):
+    """one sample, device-resident: parity against the reference at full size, steps over the contexts, kernel table"""
+    import torch
+    steps = steps or args.steps
+    d = torch.from_numpy(buf).cuda()
+    n = buf.size
+    leg = {"bases": n_bases_of(buf)}
+    for c in ctxs:
+        c.set_result_mode(True)
+    if not args.no_cpu_baseline:
+        from oracle import pyoracle
+        if pyoracle.Reference.available():
+            with quiet_stderr():
+                want, secs = reference_run(buf, k, m)
+            assert_parity(ctxs[0].count_device(d.data_ptr(), n, opt), want, f"parity, k={k} m={m}")
+            leg["parity"] = "reference, full sample"
+            leg["reference_bases_per_s"] = leg["bases"] / secs
+    for c in ctxs:
+        for _ in range(2):
+            hc = c.count_device(d.data_ptr(), n, opt)
+    ms, _ = timed(lambda: count_steps(steps, lambda c, s: c.count_device(d.data_ptr(), n, opt), ctxs))
+    ms1, _ = timed(lambda: [ctxs[0].count_device(d.data_ptr(), n, opt) for _ in range(steps)])
+    leg.update({"ms_per_step": ms / steps, "value": leg["bases"] * steps / (ms * 1e-3), "unit": "bases/s",
+                "one_context_ms_per_step": ms1 / steps, "n_raw": hc.n_raw, "n_distinct": hc.n_distinct, "n_elem": hc.n_elem,
+                "kernels": kernel_table(ctxs[0], lambda: ctxs[0].count_device(d.data_ptr(), n, opt), steps=3)})
+    return leg
+
+
+def c4_leg(ctxs, rank, world, timed, all_ranks_ok, args):
+    """BASELINE configs[3]: 96 samples of a 1.7 Mbp population (5 % of the tracts differ between samples), 50x PE.  Strong
+    scaling: the samples are dealt to the ranks, every rank deals ITS samples dynamically to its contexts (reads in
+    pinned host memory: H2D inside), then the query rows are exchanged (one allgather, GPU to GPU) and every rank
+    computes the union of the mapper queries; rank 0 runs the cross-sample merge (tjb_merge_tracts) on a stand-in
+    post-mapper table.  Everything between the first sample and the merged tract ids is inside the timed region."""
+    import torch
+    from tatajuba_b200 import TatajubaOptions, genome_set
+    opt = TatajubaOptions(K, M, MIN_COV, True, paired_end=True)
+    mine = genome_set.samples_of_rank(C4_SAMPLES, rank, world)
+    cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
+    threads = max(1, cores // max(1, int(os.environ.get("LOCAL_WORLD_SIZE", world))))
+    with ThreadPoolExecutor(threads) as ex:
+        bufs = list(ex.map(lambda s: make_sample(s, genome=C4_GENOME, coverage=C4_COVERAGE, fraction=C4_FRACTION), mine))
+    pinned = [torch.from_numpy(b).pin_memory() for b in bufs]
+    bases_total = C4_SAMPLES * n_bases_of(bufs[0])
+    parity = "skipped"
+    for c in ctxs:
+        c.set_result_mode(False)
+    if not args.no_cpu_baseline:
+        from oracle import pyoracle
+        if pyoracle.Reference.available():
+            refs = [pyoracle.Reference() for _ in range(threads)]
+            with quiet_stderr(), ThreadPoolExecutor(threads) as ex:
+                wants = list(ex.map(lambda i: refs[i % threads].run_buffer(bufs[i], K, M, MIN_COV, True), range(len(bufs))))
+            res = genome_set.count_samples(ctxs, len(bufs), lambda c, i: c.count_host(pinned[i], opt))
+            for i, hc in enumerate(res):
+                assert_parity(hc, wants[i], f"c4 sample {mine[i]}")
+            parity = f"reference, every one of the {C4_SAMPLES} samples at full size"
+    ok = all_ranks_ok(True)
+    assert ok
+    for c in ctxs:
+        c.set_result_mode(True)
+    ctx = ctxs[0]
+
+    def job():
+        rows = {}
+
+        def done(c, i, hc):  # on the context's thread, before it counts its next sample
+            rows[mine[i]] = genome_set.query_rows_device(c, hc).clone()
+            return hc.n_idx
+        genome_set.count_samples(ctxs, len(bufs), lambda c, i: c.count_host(pinned[i], opt), on_done=done)
+        all_rows, sizes = genome_set.allgather_tables_device(rows, C4_SAMPLES)
+        uni, idx = genome_set.union_queries_device(ctx, all_rows, K)
+        n_concat = 0
+        if rank == 0:  # stand-in post-mapper tables: one histogram per union row a sample has, at the row's rank as location
+            tables, off, idx_h = [], 0, idx.cpu().numpy()
+            for n in sizes:
+                loc = np.sort(idx_h[off:off + n]).astype(np.int32)
+                off += n
+                tables.append({"location": loc, "base": np.zeros(n, np.int32), "mode_context_length": np.full(n, 4, np.int32),
+                               "name": np.zeros((n, 1), np.uint8)})
+            n_concat = len(genome_set.merge_tracts(tables, 2)[0])
+        return int(uni.shape[0]), int(sum(sizes)), n_concat
+    job()
+    best, out = None, None
+    for _ in range(3):
+        ms, out = timed(job)
+        best = ms if best is None else min(best, ms)
+    return {"workload": f"configs[3]: {C4_SAMPLES} samples x {C4_GENOME / 1e6:.1f} Mbp x {C4_COVERAGE}x PE, tract polymorphism on {C4_FRACTION:.0%} of the tracts",
+            "scaling": "strong (the 96 samples are dealt to the ranks)", "ms": best, "value": bases_total / (best * 1e-3), "unit": "bases/s",
+            "samples_per_rank": len(mine), "contexts_per_gpu": len(ctxs), "bases_total": bases_total, "parity": parity,
+            "inside": "H2D of every sample, count, query rows on the device, allgather, union of mapper queries, merge of tract ids (rank 0)",
+            "n_union": out[0], "rows": out[1], "merged_rows": out[2]}
 
 
 if __name__ == "__main__":

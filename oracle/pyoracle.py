@@ -139,10 +139,38 @@ class Reference:
         self.lib.ref_hotpath_run_files(arr, len(files), k, m, min_coverage, int(remove_biased), C.byref(d))
         return self._collect(d)
 
-    def run_buffer(self, buf: bytes, k=25, m=4, min_coverage=5, remove_biased=True):
+    def run_buffer(self, buf, k=25, m=4, min_coverage=5, remove_biased=True):
+        """buf: bytes, or a contiguous numpy uint8 array (passed without a copy)"""
         d = _RefDump()
-        b = (C.c_char * len(buf)).from_buffer_copy(buf) if len(buf) else (C.c_char * 1)()
-        self.lib.ref_hotpath_run_buffer(b, C.c_size_t(len(buf)), k, m, min_coverage, int(remove_biased), C.byref(d))
+        if isinstance(buf, np.ndarray):
+            assert buf.dtype == np.uint8 and buf.flags["C_CONTIGUOUS"]
+            b, n = C.c_void_p(buf.ctypes.data if buf.size else 0), buf.size
+        else:
+            b, n = ((C.c_char * len(buf)).from_buffer_copy(buf) if len(buf) else (C.c_char * 1)()), len(buf)
+        self.lib.ref_hotpath_run_buffer(b, C.c_size_t(n), k, m, min_coverage, int(remove_biased), C.byref(d))
+        return self._collect(d)
+
+
+class PatchedReference(Reference):
+    """the reference sources with integration/tatajuba-libtjb_gpu.patch applied, behind the same boundary-capturing shim
+    (oracle/_ref/libref_hotpath_gpu.so): what the mapper sees when the binding counts on the GPU"""
+    SO = os.path.join(HERE, "_ref", "libref_hotpath_gpu.so")
+
+    def __init__(self):
+        if not os.path.exists(self.SO):
+            raise FileNotFoundError(self.SO)
+        self.lib = C.CDLL(self.SO)
+        self.lib.ref_sizeof_hopo_element.restype = C.c_size_t
+        assert self.lib.ref_sizeof_hopo_element() == 40
+
+    @staticmethod
+    def available():
+        return os.path.exists(PatchedReference.SO)
+
+    def run_files_gpu(self, files, k=25, m=4, min_coverage=5, remove_biased=True, device=0):
+        arr = (C.c_char_p * len(files))(*[os.fsencode(f) for f in files])
+        d = _RefDump()
+        self.lib.ref_hotpath_run_files_gpu(arr, len(files), k, m, min_coverage, int(remove_biased), int(device), C.byref(d))
         return self._collect(d)
 
 

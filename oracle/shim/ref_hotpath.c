@@ -118,6 +118,30 @@ ref_hotpath_run_files (const char *const *files, int n_files, int kmer_size, int
   return out->status;
 }
 
+#ifdef TJB_PATCHED
+/* the same with the sources patched by integration/tatajuba-libtjb_gpu.patch: new_hopo_counter_from_files_gpu() counts
+ * on the GPU, finalise_hopo_counter() goes straight to the mapper call, where the stub above captures the state */
+int
+ref_hotpath_run_files_gpu (const char *const *files, int n_files, int kmer_size, int min_tract_size,
+                           int min_coverage, int remove_biased, int device, ref_dump_t *out)
+{
+  tatajuba_options_t opt = make_opt (kmer_size, min_tract_size, min_coverage, remove_biased, n_files > 1);
+  reset_dump (out);
+  double t0 = now_secs ();
+  hopo_counter hc = new_hopo_counter_from_files_gpu (files[0], n_files > 1 ? files[1] : NULL, opt, device);
+  out->secs_scan = now_secs () - t0;
+  out->status = -1;
+  tl_hc = hc; tl_out = out;
+  tl_t_finalise_start = now_secs ();
+  finalise_hopo_counter (hc);
+  tl_hc = NULL; tl_out = NULL;
+  if (out->status != 0) out->status = hc->gpu_status; /* the mapper was never reached: the sample is excluded */
+  out->n_raw = -1; /* not kept by the binding (hc->n_elem before finalise is the GPU library's diagnostic n_raw) */
+  del_hopo_counter (hc);
+  return out->status;
+}
+#endif
+
 int
 ref_hotpath_run_buffer (const char *buf, size_t n_bytes, int kmer_size, int min_tract_size,
                         int min_coverage, int remove_biased, ref_dump_t *out)

@@ -26,6 +26,10 @@ typedef struct {
 /* files: 1 (single-end) or 2 (paired: R2 appended to the same counter, genome_set.c:72-73) FASTQ/FASTA(.gz) paths */
 int ref_hotpath_run_files (const char *const *files, int n_files, int kmer_size, int min_tract_size,
                            int min_coverage, int remove_biased, ref_dump_t *out);
+/* only in oracle/_ref/libref_hotpath_gpu.so (the sources patched by integration/tatajuba-libtjb_gpu.patch): the binding's
+ * new_hopo_counter_from_files_gpu() + finalise_hopo_counter(); n_raw is not reported (-1) */
+int ref_hotpath_run_files_gpu (const char *const *files, int n_files, int kmer_size, int min_tract_size,
+                               int min_coverage, int remove_biased, int device, ref_dump_t *out);
 /* buf: reads separated by '\n' (a trailing '\n' is optional); each read goes through update_hopo_counter_from_seq */
 int ref_hotpath_run_buffer (const char *buf, size_t n_bytes, int kmer_size, int min_tract_size,
                             int min_coverage, int remove_biased, ref_dump_t *out);

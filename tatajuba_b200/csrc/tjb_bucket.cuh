@@ -244,6 +244,49 @@ plan_big_kernel (const u32 *__restrict__ bin_hist, int F, int bshift, unsigned l
   }
 }
 
+// --------------------------------------------------------------------------------------- aggregate -------
+// The scan's records (one per observed tract) are added to the aggregation table (tjb_table.cuh): the run-length count
+// of hopo_counter.c:352-365 without a sort.  One record per thread and round, AGG_UNROLL rounds in flight; a thread
+// that creates an entry also counts it for the partition plan.
+#ifndef AGG_UNROLL
+#define AGG_UNROLL 4
+#endif
+template <int W>
+__global__ void __launch_bounds__ (256)
+aggregate_kernel (const u64 *__restrict__ recs, unsigned long long *__restrict__ counters, unsigned long long capacity, AggTable tab,
+                  u64 *__restrict__ ovf, unsigned long long ovf_capacity, int k, u32 *__restrict__ bin_hist, int F)
+{
+  const unsigned long long n = counters[CTR_RECORDS] < capacity ? counters[CTR_RECORDS] : capacity;
+  const size_t stride = (size_t) gridDim.x * 256;
+  const int lane = threadIdx.x & 31;
+  u32 n_new = 0;
+  for (size_t i0 = (size_t) blockIdx.x * 256 + threadIdx.x; i0 < n; i0 += AGG_UNROLL * stride) {
+    Rec<W> r[AGG_UNROLL];
+#pragma unroll
+    for (int u = 0; u < AGG_UNROLL; u++) { const size_t i = i0 + u * stride; if (i < n) r[u] = load_rec<W> (recs, i); }
+#pragma unroll
+    for (int u = 0; u < AGG_UNROLL; u++) {
+      const size_t i = i0 + u * stride;
+      int res = TAB_ADDED;
+      Rec<W> key;
+      if (i < n) {
+        key = r[u];
+        key.w[0] &= ~3ULL;
+        res = table_add<W> (tab, key, flag_weight (r[u].w[0]));
+        if (res != TAB_ADDED) atomicAdd (&bin_hist[rec_bin<W> (key, k, F)], 1u); // a new entry, or a record of the overflow list
+      }
+      n_new += res == TAB_NEW;
+      if (res == TAB_DEFER) {
+        const unsigned long long pos = atomicAdd (&counters[CTR_OVERFLOW], 1ULL);
+        if (pos < ovf_capacity) store_rec<W> (ovf, pos, r[u]);
+      }
+    }
+  }
+#pragma unroll
+  for (int d = 16; d; d >>= 1) n_new += __shfl_xor_sync (0xffffffffu, n_new, d);
+  if (lane == 0 && n_new) atomicAdd (&counters[CTR_ENTRIES], (unsigned long long) n_new);
+}
+
 // --------------------------------------------------------------------------------------- partition -------
 // Walks the aggregation table (and the overflow list) and moves every entry to its bucket as a weighted record.
 // Also sums the weights: the number of tract observations of the sample (hc->n_elem before finalise_hopo_counter).

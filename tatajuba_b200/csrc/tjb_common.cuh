@@ -105,7 +105,8 @@ enum { CTR_OVERFLOW = 0, // observations deferred to the overflow list (tjb_tabl
        CTR_SKIP = 1,     // fenced runs (non-ACGTU run that is the first tract of its read)
        CTR_ENTRIES = 2,  // entries of the aggregation table
        CTR_NRAW = 3,     // tract observations = sum of all weights (hc->n_elem before finalise_hopo_counter)
-       CTR_WORDS = 4 };
+       CTR_RECORDS = 4,  // records the scan appended to the record array (= observations, unless the array overflowed)
+       CTR_WORDS = 6 };
 
 // one digit of an LSD radix pass: bits [shift, shift+nbits) of word `word`
 struct DigitDesc { int word, shift, nbits; };

@@ -26,10 +26,10 @@
 #define TJB_CHUNK_BYTES (32u << 20)      // files path: pinned chunk of decoded reads (two per decoder thread)
 #define TJB_HOST_CHUNK_BYTES (32u << 20) // host-buffer path: H2D chunk overlapped with the scan of the previous one
 
-enum KernelId { K_SCAN = 0, K_PLAN, K_PARTITION, K_BUCKET, K_TOTALS, K_PACK, K_COVMAX,
+enum KernelId { K_SCAN = 0, K_AGGREGATE, K_PLAN, K_PARTITION, K_BUCKET, K_TOTALS, K_PACK, K_COVMAX,
                 // global multi-pass path, only for buckets too large for shared memory
                 K_SORT_HIST, K_SORT_SCATTER, K_PSCAN, K_RLE, K_GROUP, K_UNION, K_UNPACK, K_TABLE, K_COUNT };
-static const char *kKernelNames[K_COUNT] = {"tjb_scan_kernel", "plan_kernel", "wpartition_kernel", "wbucket_reduce_kernel", "totals_kernel",
+static const char *kKernelNames[K_COUNT] = {"tjb_scan_kernel", "aggregate_kernel", "plan_kernel", "wpartition_kernel", "wbucket_reduce_kernel", "totals_kernel",
                                             "pack_kernel", "cov_max_kernel", "rsort_hist_kernel",
                                             "rsort_scatter_kernel", "pscan_kernels", "rle_kernels", "group_kernels", "union_kernels", "unpack_kernels",
                                             "table_kernels"};
@@ -59,7 +59,7 @@ struct tjb_ctx {
   int64_t launches = 0;
   int64_t h2d_bytes = 0; // host-buffer path: bytes sent host -> device
   size_t last_keep = 0, last_idx = 0, last_entries = 0; // sizes of the previous sample: the next one is sized ahead
-  size_t want_entries = 0;                              // set when a sample has to be redone with a larger table
+  size_t want_entries = 0, want_records = 0;            // set when a sample has to be redone with a larger table / record array
   tjb_kernel_stat stats[K_COUNT];
   std::vector<PendingEvent> pending;
   std::vector<cudaEvent_t> free_events;
@@ -76,11 +76,14 @@ struct tjb_ctx {
   tjb_opts opt = {0, 0, 0, 0, 0};
   bool in_sample = false;
   int scan_launches = 0;                    // of this sample
+  bool records_pending = false, records_aggregated = false; // scan records not yet / already added to the table
   int64_t exported_rows = -1;               // rows of the table as exported for an exchange (-1: not exported yet)
   int rec_words = 0;
   int bin_bits = 8, bucket_shift = 10;      // partition plan: 2^bin_bits bins, bucket windows of 2^bucket_shift records
   DevBuf tab;                               // aggregation table (tjb_table.cuh): counts, then keys
   size_t tab_slots = 0;
+  DevBuf recs;                              // tract observations as the scan found them (one record each)
+  size_t rec_capacity = 0;
   DevBuf ovf;                               // observations the table could not take, raw records
   size_t ovf_capacity = 0;
   DevBuf wkey, wcnt, okey;                  // weighted records bucket by bucket; compact per-bucket output
@@ -286,9 +289,17 @@ static int begin_sample (tjb_ctx *ctx, const tjb_opts *opt, size_t n_bytes_hint)
   ctx->ovf_capacity = est / 8 < 65536 ? 65536 : est / 8;
   ctx->list_cap = slots / 2 + ctx->ovf_capacity;
   ctx->bucket_shift = choose_bucket_shift (est, ctx->sm_count);
+  { static const int forced = getenv ("TJB_BUCKET_SHIFT") ? atoi (getenv ("TJB_BUCKET_SHIFT")) : 0; // experiments
+    if (forced >= 5 && forced <= 10) ctx->bucket_shift = forced; }
   ctx->bin_bits = choose_bin_bits (est, ctx->bucket_shift, opt->kmer_size);
   TRY (ensure (ctx, ctx->tab, table_bytes (slots, W)));
   TRY (ensure (ctx, ctx->ovf, ctx->ovf_capacity * W * 8));
+  // the scan's records: a guess from the input size (a record per 16 bytes is ~10x what a random genome gives at -m 4);
+  // records that do not fit are counted, never written, and the sample is redone with the exact size
+  ctx->rec_capacity = ctx->want_records ? ctx->want_records : n_bytes_hint / 16 + 65536;
+  ctx->want_records = 0;
+  if (ctx->recs.cap / ((size_t) W * 8) > ctx->rec_capacity) ctx->rec_capacity = ctx->recs.cap / ((size_t) W * 8); // what is there already
+  TRY (ensure (ctx, ctx->recs, ctx->rec_capacity * W * 8));
   CU (cudaMemsetAsync (ctx->tab.p, 0, table_bytes (slots, W), ctx->stream));
   {
     const u32 n_bins = 1u << ctx->bin_bits;
@@ -298,6 +309,7 @@ static int begin_sample (tjb_ctx *ctx, const tjb_opts *opt, size_t n_bytes_hint)
     CU (cudaGetLastError ());
   }
   ctx->scan_launches = 0;
+  ctx->records_pending = ctx->records_aggregated = false;
   ctx->in_sample = true;
   ctx->exported_rows = -1;
   return 0;
@@ -316,14 +328,16 @@ static int launch_scan (tjb_ctx *ctx, const uint8_t *d_seqs, size_t n)
   if (!n_tiles) return 0;
   const tjb_opts *opt = &ctx->opt;
   int min_len = opt->min_tract_size < 2 ? 2 : opt->min_tract_size;
+  if (ctx->records_aggregated) { ctx->err = "the sample's table has been exported: no more reads can be scanned into it"; return TJB_ERR_ARG; }
+  ctx->records_pending = true;
   if (ctx->scan_launches++) CU (cudaMemsetAsync (ctx->d_tile_ctr, 0, sizeof (u32), ctx->stream)); // window tickets of this launch (the first: cleared by the prologue)
   long long want = (n_tiles + SCAN_WARPS - 1) / SCAN_WARPS;
   long long grid = want < (long long) ctx->sm_count * SCAN_CTAS_PER_SM ? want : (long long) ctx->sm_count * SCAN_CTAS_PER_SM;
-  // algorithmic bytes of this launch: every sequence byte read once (+ the table traffic per observation, added at finalise)
+  // algorithmic bytes of this launch: every sequence byte read once (+ 8W bytes per emitted record, added at finalise)
   if (ctx->rec_words == 2)
-    LAUNCH (K_SCAN, n, (tjb_scan_kernel<2><<<(u32) grid, SCAN_THREADS, scan_smem_bytes<2> (), ctx->stream>>> (d_seqs, (long long) n, opt->kmer_size, min_len, table_of (ctx), (u64*) ctx->ovf.p, ctx->ovf_capacity, ctx->d_res->counters, n_tiles, ctx->d_bin_hist, ctx->bin_bits, ctx->d_tile_ctr)));
+    LAUNCH (K_SCAN, n, (tjb_scan_kernel<2><<<(u32) grid, SCAN_THREADS, scan_smem_bytes<2> (), ctx->stream>>> (d_seqs, (long long) n, opt->kmer_size, min_len, (u64*) ctx->recs.p, ctx->rec_capacity, ctx->d_res->counters, n_tiles, ctx->d_tile_ctr)));
   else
-    LAUNCH (K_SCAN, n, (tjb_scan_kernel<3><<<(u32) grid, SCAN_THREADS, scan_smem_bytes<3> (), ctx->stream>>> (d_seqs, (long long) n, opt->kmer_size, min_len, table_of (ctx), (u64*) ctx->ovf.p, ctx->ovf_capacity, ctx->d_res->counters, n_tiles, ctx->d_bin_hist, ctx->bin_bits, ctx->d_tile_ctr)));
+    LAUNCH (K_SCAN, n, (tjb_scan_kernel<3><<<(u32) grid, SCAN_THREADS, scan_smem_bytes<3> (), ctx->stream>>> (d_seqs, (long long) n, opt->kmer_size, min_len, (u64*) ctx->recs.p, ctx->rec_capacity, ctx->d_res->counters, n_tiles, ctx->d_tile_ctr)));
   CU (cudaGetLastError ());
   return 0;
 }
@@ -454,6 +468,20 @@ static int ensure_arena (tjb_ctx *ctx, size_t keep, size_t idx)
 
 #define TJB_INTERNAL_RETRY 100 // the sample did not fit the table / lists it was sized for; ctx->want_entries is set
 
+// the scan's records into the aggregation table, once (grid sized for the record capacity: the count is on the device)
+template <int W>
+static int aggregate_launch (tjb_ctx *ctx)
+{
+  if (!ctx->records_pending) return 0;
+  const size_t want = nblk (ctx->rec_capacity < ((size_t) 1 << 24) ? ctx->rec_capacity : ((size_t) 1 << 24), 256 * AGG_UNROLL);
+  const u32 g = (u32) (want < (size_t) ctx->sm_count * 8 ? (want ? want : 1) : (size_t) ctx->sm_count * 8);
+  LAUNCH (K_AGGREGATE, 0, (aggregate_kernel<W><<<g, 256, 0, ctx->stream>>> ((const u64*) ctx->recs.p, ctx->d_res->counters, ctx->rec_capacity, table_of (ctx), (u64*) ctx->ovf.p, ctx->ovf_capacity, ctx->opt.kmer_size, ctx->d_bin_hist, ctx->bin_bits)));
+  CU (cudaGetLastError ());
+  ctx->records_pending = false;
+  ctx->records_aggregated = true;
+  return 0;
+}
+
 // plan -> partition -> bucket reduce -> totals, all asynchronous (the scalars stay on the device)
 template <int W>
 static int reduce_launch (tjb_ctx *ctx, int qc_mode, int min_coverage)
@@ -475,6 +503,7 @@ static int reduce_launch (tjb_ctx *ctx, int qc_mode, int min_coverage)
   ctx->max_buckets = max_buckets;
   u32 *d_meta = ctx->d_res->meta;
   unsigned long long *d_counters = ctx->d_res->counters;
+  TRY ((aggregate_launch<W> (ctx)));
   {
     const int ipt = F > 10 ? 1 << (F - 10) : 1; // bins per thread of the single planning CTA
 #define PLAN_CASE(I) case I: LAUNCH (K_PLAN, 10 << F, (plan_kernel<I><<<1, PLAN_THREADS, 0, st>>> (ctx->d_bin_hist, F, ctx->bucket_shift, cap, ctx->d_bkt_start, ctx->d_lut, ctx->d_cursor, d_meta, max_buckets))); break;
@@ -500,6 +529,10 @@ static bool sample_overflowed (tjb_ctx *ctx)
 {
   const ResultBlock *hr = ctx->h_res;
   const unsigned long long n_ovf = hr->counters[CTR_OVERFLOW], n_ent = hr->counters[CTR_ENTRIES];
+  if (hr->counters[CTR_RECORDS] > ctx->rec_capacity) { // the record array was too small: the rest of the pipeline saw a part of the sample
+    ctx->want_records = (size_t) hr->counters[CTR_RECORDS] + 1024;
+    return true;
+  }
   if (n_ovf > ctx->ovf_capacity || n_ent > ctx->tab_slots / 2 || n_ent + n_ovf > ctx->list_cap) {
     // the table or the overflow list was too small for this sample: everything after the scan worked on a part of it
     ctx->want_entries = (size_t) (n_ent + n_ovf) * 2 + 4096;
@@ -618,7 +651,8 @@ static int finalise_t (tjb_ctx *ctx, tjb_counter_out *out, int qc_mode)
   const u32 n_keep = hr->meta[META_NKEEP], n_idx = hr->meta[META_NIDX];
   out->n_distinct = hr->meta[META_NDIST];
   // algorithmic bytes of the launches above, now that the counts are known
-  ctx->stats[K_SCAN].bytes_algorithmic += (int64_t) (8 * W + 16) * out->n_raw; // key compared + count word updated per observation
+  ctx->stats[K_SCAN].bytes_algorithmic += (int64_t) 8 * W * out->n_raw;          // the scan writes one record per observation
+  ctx->stats[K_AGGREGATE].bytes_algorithmic += (int64_t) (16 * W + 16) * out->n_raw; // record read, key compared, count word updated
   ctx->stats[K_PARTITION].bytes_algorithmic += (int64_t) (16 * W + 16) * (int64_t) ctx->last_entries;
   ctx->stats[K_BUCKET].bytes_algorithmic += (int64_t) (8 * W + 8) * (int64_t) ctx->last_entries + (int64_t) (8 * W + 4) * n_keep + 8 * (int64_t) n_idx;
   ctx->stats[K_TOTALS].bytes_algorithmic += (int64_t) 24 * n_buckets;
@@ -911,7 +945,7 @@ void tjb_ctx_destroy (tjb_ctx *ctx)
     if (ctx->h_exc_val[i]) cudaFreeHost (ctx->h_exc_val[i]);
   }
   DevBuf *bufs[] = {&ctx->d_pk[0], &ctx->d_pk[1], &ctx->d_exc_pos[0], &ctx->d_exc_pos[1], &ctx->d_exc_val[0], &ctx->d_exc_val[1],
-                    &ctx->d_chunk[0], &ctx->d_chunk[1], &ctx->tab, &ctx->ovf, &ctx->wkey, &ctx->wcnt, &ctx->okey,
+                    &ctx->d_chunk[0], &ctx->d_chunk[1], &ctx->tab, &ctx->recs, &ctx->ovf, &ctx->wkey, &ctx->wcnt, &ctx->okey,
                     &ctx->hist, &ctx->ptmp, &ctx->heads, &ctx->pos, &ctx->seg, &ctx->drec, &ctx->dcount, &ctx->keep, &ctx->kpos, &ctx->krec,
                     &ctx->cw, &ctx->csum, &ctx->gkeep, &ctx->gkpos, &ctx->out40, &ctx->idx_i, &ctx->idx_f, &ctx->qrows, &ctx->out_cnt, &ctx->out_ii,
                     &ctx->out_if, &ctx->cov_tab, &ctx->uni_a, &ctx->uni_b, &ctx->b_bkt_start, &ctx->b_cursor, &ctx->b_koff, &ctx->b_ioff, &ctx->b_bstat};
@@ -1054,7 +1088,7 @@ int tjb_count_sample_host (tjb_ctx *ctx, const uint8_t *seqs, size_t n_bytes, co
   int rc = 0;
   CU (cudaSetDevice (ctx->device));
   const bool packed = packed_transfer_enabled (ctx, n_bytes);
-  static const int mix_env = getenv ("TJB_PLAIN_EVERY") ? atoi (getenv ("TJB_PLAIN_EVERY")) : 3; // 0: every chunk packed
+  static const int mix_env = getenv ("TJB_PLAIN_EVERY") ? atoi (getenv ("TJB_PLAIN_EVERY")) : 0; // n > 1: every n-th chunk unpacked (measured: no gain, off)
   const int plain_every = packed && mix_env > 1 && host_range_is_pinned (seqs) ? mix_env : 0;
   PackerSession session (packed);
   for (int attempt = 0; attempt < TJB_MAX_ATTEMPTS; attempt++) {
@@ -1249,6 +1283,7 @@ int tjb_sample_export (tjb_ctx *ctx, void *d_rows, int64_t max_rows, int64_t *n_
   const int W = ctx->rec_words;
   if (row_words) *row_words = W + 1;
   if (ctx->exported_rows < 0) { // table -> rows, once per sample (kept in the context until the sample ends)
+    if (W == 2) TRY ((aggregate_launch<2> (ctx))); else TRY ((aggregate_launch<3> (ctx)));
     const size_t cap_rows = ctx->list_cap;
     TRY (ensure (ctx, ctx->uni_a, cap_rows * (W + 1) * 8 + 16));
     unsigned long long *d_n = (unsigned long long*) ((char*) ctx->uni_a.p + cap_rows * (W + 1) * 8);
@@ -1261,7 +1296,8 @@ int tjb_sample_export (tjb_ctx *ctx, void *d_rows, int64_t max_rows, int64_t *n_
     CU (cudaMemcpyAsync (&h_n, d_n, 8, cudaMemcpyDeviceToHost, ctx->stream));
     CU (cudaMemcpyAsync (ctx->h_res, ctx->d_res, sizeof (ResultBlock), cudaMemcpyDeviceToHost, ctx->stream));
     CU (cudaStreamSynchronize (ctx->stream));
-    if (h_n > cap_rows || ctx->h_res->counters[CTR_OVERFLOW] > ctx->ovf_capacity) {
+    if (ctx->h_res->counters[CTR_RECORDS] > ctx->rec_capacity) ctx->want_records = (size_t) ctx->h_res->counters[CTR_RECORDS] + 1024;
+    if (h_n > cap_rows || ctx->h_res->counters[CTR_OVERFLOW] > ctx->ovf_capacity || ctx->h_res->counters[CTR_RECORDS] > ctx->rec_capacity) {
       ctx->want_entries = (size_t) h_n * 2 + 4096; // the caller starts the sample again (tjb_sample_begin sizes from this)
       ctx->err = "aggregation table too small for this chunk: begin the sample again";
       return TJB_ERR_TOO_LARGE;

@@ -30,8 +30,7 @@
 // Windows own the code runs that START inside their owned bytes.
 #pragma once
 #include "tjb_common.cuh"
-#include "tjb_table.cuh"
-#include "tjb_bucket.cuh" // rec_bin(): the scan also accumulates the bin histogram the partition plan is made from
+
 
 #define SCAN_WARPS 8
 #define SCAN_THREADS (SCAN_WARPS * 32)
@@ -50,9 +49,6 @@
 #define SW_G1 (SW_G0 + SW_TILE / 16)
 #ifndef SW_CHUNK
 #define SW_CHUNK (SW_ROWS >= 8 ? 2 : 4) // consecutive windows per ticket (power of two, >= 2)
-#endif
-#ifndef SCAN_DIRECT
-#define SCAN_DIRECT 1                 // 1: batches are drawn straight from the candidate bit masks; 0: shared-memory queue
 #endif
 #ifndef SW_QCAP
 #define SW_QCAP 512                   // candidate queue (linear; moved to the front when the next round may not fit)
@@ -152,9 +148,9 @@ __device__ __forceinline__ u32 prmt (u32 a, u32 b, u32 sel)
 
 template <int W>
 __global__ void __launch_bounds__ (SCAN_THREADS, SCAN_CTAS_PER_SM)
-tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_len, AggTable tab, u64 *__restrict__ out,
+tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_len, u64 *__restrict__ out,
                  unsigned long long capacity, unsigned long long *__restrict__ counters, long long n_tiles,
-                 u32 *__restrict__ bin_hist, int bin_bits, u32 *__restrict__ tile_ctr)
+                 u32 *__restrict__ tile_ctr)
 {
   extern __shared__ __align__ (16) unsigned char scan_smem[];
   ScanWarpSmem<W> *S = reinterpret_cast<ScanWarpSmem<W>*> (scan_smem) + (threadIdx.x >> 5);
@@ -181,8 +177,6 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
 
   u32 nrec = 0, nskip = 0, parity = 0;
   u32 head = 0, tail = 0, n_old = 0; // candidate FIFO; n_old = entries that belong to the previous window
-  u32 n_pend = 0; int pend = -1;     // SCAN_DIRECT: candidates waiting for a full batch, one per lane (lanes < n_pend)
-  (void) head; (void) tail; (void) n_pend; (void) pend;
 
   // a window is "interior" when [g0, g0 + SW_WIN) lies inside the buffer: one bulk copy stages it.  g0 >= 0 from
   // window 1 on; the last interior window is the largest t with t * SW_TILE - SW_HALO_L + SW_WIN <= n
@@ -207,39 +201,22 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
       }
     }
   };
-  // one observation into the aggregation table (tjb_table.cuh); a new entry is binned for the partition plan
-  auto add_obs = [&] (const Rec<W> &r) -> int {
-    Rec<W> key = r;
-    key.w[0] &= ~3ULL;
-    const int res = table_add<W> (tab, key, flag_weight (r.w[0]));
-    if (res == TAB_NEW) atomicAdd (&bin_hist[rec_bin<W> (key, k, bin_bits)], 1u);
-    return res;
-  };
-  auto flush = [&] () { // staged observations -> aggregation table; the few that cannot be placed -> overflow list
-    u32 n_new = 0;
-    for (u32 i0 = 0; i0 < nrec; i0 += 32) {
-      const u32 i = i0 + lane;
-      int res = TAB_ADDED;
-      Rec<W> r;
-      if (i < nrec) {
-#pragma unroll
-        for (int j = 0; j < W; j++) r.w[j] = S->rec[i * W + j];
-        res = add_obs (r);
-      }
-      n_new += __popc (__ballot_sync (0xffffffffu, res == TAB_NEW));
-      const u32 dm = __ballot_sync (0xffffffffu, res == TAB_DEFER);
-      if (dm) {
-        unsigned long long base = 0;
-        if (lane == 0) base = atomicAdd (&counters[CTR_OVERFLOW], (unsigned long long) __popc (dm));
-        base = __shfl_sync (0xffffffffu, base, 0);
-        if (res == TAB_DEFER) {
-          const unsigned long long pos = base + __popc (dm & ((1u << lane) - 1));
-          if (pos < capacity) store_rec<W> (out, pos, r);
-          atomicAdd (&bin_hist[rec_bin<W> (r, k, bin_bits)], 1u);
-        }
+  auto flush = [&] () { // staged records -> global array, one atomicAdd
+    unsigned long long base = 0;
+    if (lane == 0) base = atomicAdd (&counters[CTR_RECORDS], (unsigned long long) nrec);
+    base = __shfl_sync (0xffffffffu, base, 0);
+    if (W == 2 && base + nrec <= capacity) { // one record = one 16-byte store
+      const ulonglong2 *src = reinterpret_cast<const ulonglong2*> (S->rec);
+      ulonglong2 *dst = reinterpret_cast<ulonglong2*> (out) + base;
+      static_assert (SW_RCAP (2) <= 64, "two stores per lane cover the staging area");
+      if ((u32) lane < nrec) dst[lane] = src[lane];
+      if ((u32) lane + 32 < nrec) dst[lane + 32] = src[lane + 32];
+    } else {
+      for (u32 i = lane; i < nrec * W; i += 32) {
+        const unsigned long long r = base + i / W;
+        if (r < capacity) out[r * W + (i % W)] = S->rec[i];
       }
     }
-    if (lane == 0 && n_new) atomicAdd (&counters[CTR_ENTRIES], (unsigned long long) n_new);
     nrec = 0;
     __syncwarp ();
   };
@@ -313,15 +290,10 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
         }
         return ok;
       };
-      auto emit_slow = [&] (u64 ctx0, u64 ctx1, int code, long long len) { // rare path: one lane on its own
+      auto emit_slow = [&] (u64 ctx0, u64 ctx1, int code, long long len) { // rare path: straight to global
         const Rec<W> q = pack_rec<W> (ctx0, ctx1, code < 2 ? code : 3 - code, sext_field (len, 10), code < 2 ? 1 : 2, k);
-        const int res = add_obs (q);
-        if (res == TAB_NEW) atomicAdd (&counters[CTR_ENTRIES], 1ULL);
-        else if (res == TAB_DEFER) {
-          const unsigned long long pos = atomicAdd (&counters[CTR_OVERFLOW], 1ULL);
-          if (pos < capacity) store_rec<W> (out, pos, q);
-          atomicAdd (&bin_hist[rec_bin<W> (q, k, bin_bits)], 1u);
-        }
+        const unsigned long long pos = atomicAdd (&counters[CTR_RECORDS], 1ULL);
+        if (pos < capacity) store_rec<W> (out, pos, q);
       };
       long long ps = g0 + s;
       while (ps < n) {
@@ -457,52 +429,6 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
       if (row == SW_ROWS - 1 && lane >= SW_G1 - 32 * (SW_ROWS - 1)) cs = 0;
       cb[row >> 1] |= cs << (row & 1);
     }
-#if SCAN_DIRECT
-    // ---- candidates of this window, 32 at a time, straight from the bit masks: candidate i (lane-major order) is
-    // found by a binary search over the lanes' running counts and a select inside the owner lane's four words (no
-    // queue in shared memory, no serial pop loop).  Up to 31 candidates wait in one register per lane (pend) for the
-    // next window to fill their batch.
-    {
-      static_assert (SW_ROWS == 8, "four candidate words per lane");
-      const int cnt = __popc (cb[0]) + __popc (cb[1]) + __popc (cb[2]) + __popc (cb[3]);
-      int inc = cnt; // inclusive prefix sum over the lanes
-#pragma unroll
-      for (int d = 1; d < 32; d <<= 1) { const int t = __shfl_up_sync (0xffffffffu, inc, d); if (lane >= d) inc += t; }
-      const int total = __shfl_sync (0xffffffffu, inc, 31);
-      int consumed = 0;
-      auto fetch = [&] (int i) -> int { // queue-entry code of candidate i of this window; every lane calls it
-        i = i < 0 ? 0 : (i >= total ? total - 1 : i);
-        int sl = 0; // lanes whose running count is <= i = the lane that owns candidate i
-#pragma unroll
-        for (int step = 16; step; step >>= 1) { const int v = __shfl_sync (0xffffffffu, inc, sl + step - 1); if (v <= i) sl += step; }
-        int r = i - (__shfl_sync (0xffffffffu, inc, sl) - __shfl_sync (0xffffffffu, cnt, sl));
-        const u32 w0 = __shfl_sync (0xffffffffu, cb[0], sl), w1 = __shfl_sync (0xffffffffu, cb[1], sl);
-        const u32 w2 = __shfl_sync (0xffffffffu, cb[2], sl), w3 = __shfl_sync (0xffffffffu, cb[3], sl);
-        u32 m = w0, j = 0;
-        int c0 = __popc (w0);
-        if (r >= c0) { r -= c0; m = w1; j = 1; c0 = __popc (w1); if (r >= c0) { r -= c0; m = w2; j = 2; c0 = __popc (w2); if (r >= c0) { r -= c0; m = w3; j = 3; } } }
-        for (; r > 0; r--) m &= m - 1;
-        return (int) (((u32) st << 15) | (j << 10) | ((u32) sl << 5) | (u32) (__ffs (m) - 1));
-      };
-      if (total) {
-        while ((int) n_pend + (total - consumed) >= 32) {
-          const int code = fetch (consumed + lane - (int) n_pend);
-          process_batch (lane < (int) n_pend ? pend : code, st, g0, old_g0);
-          consumed += 32 - (int) n_pend;
-          n_pend = 0; n_old = 0;
-        }
-        const int rem = total - consumed; // < 32 - n_pend
-        if (rem) {
-          const int code = fetch (consumed + lane - (int) n_pend);
-          if (lane >= (int) n_pend && lane < (int) n_pend + rem) pend = code;
-          n_pend += (u32) rem;
-        }
-      }
-      // candidates of the previous window must go before its derived arrays are overwritten by the next window
-      if (n_old) { process_batch (lane < (int) n_pend ? pend : -1, st, g0, old_g0); n_pend = 0; }
-      n_old = n_pend; // what is left (< 32 candidates) waits for the next window
-    }
-#else
     // ---- compaction into the queue (at most SW_QUOTA per lane and round); full batches of 32 go to phase B ------
     for (;;) {
       if (tail + 32 * SW_QUOTA > SW_QCAP) queue_to_front ();
@@ -553,19 +479,14 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
       if (!more) break;
     }
     n_old = tail - head; // what is left (< 32 candidates) waits for the next window
-#endif
     old_g0 = g0;
     t_cur = t_nxt;
     if ((t_nxt & (SW_CHUNK - 1)) != SW_CHUNK - 1) t_nxt++;
     else { t_nxt = __shfl_sync (0xffffffffu, t_fut, 0) * SW_CHUNK; want_ticket = true; }
     g0 = (long long) t_cur * SW_TILE - SW_HALO_L;
   }
-#if SCAN_DIRECT
-  if (n_pend) process_batch (lane < (int) n_pend ? pend : -1, st ^ 1, old_g0, 0); // they belong to the last window
-#else
   if (tail != head) // what is left belongs to the last window, whose bytes are still staged
     process_batch (lane < (int) (tail - head) ? (int) S->cand[head + lane] : -1, st ^ 1, old_g0, 0);
-#endif
   if (nrec) flush ();
 #pragma unroll
   for (int d = 16; d; d >>= 1) nskip += __shfl_xor_sync (0xffffffffu, nskip, d);
