@@ -181,6 +181,35 @@ int tjb_merge_tracts (int32_t n_samples, const int32_t *n_hist, const int32_t *l
                       const int32_t *mode_len, const char *names, int32_t name_stride, int32_t levenshtein_distance,
                       int32_t *out_sample, int32_t *out_index, int32_t *out_tract_id);
 
+/* ---- per-sample context histograms after the mapper (reference src/context_histogram.c:224-305, 364-421): what
+ * new_genomic_context_list() builds from a hopo_counter once finalise_hopo_counter() has returned.  Input: the mapped
+ * elements hc->elem[hc->ref_start .. hc->n_elem) in the order the location sort left them in (hopo_counter.c:562),
+ * reference layout (40-byte hopo_element with the mapper's fields filled in).  Output: the genomic_context_list's
+ * histograms as flat malloc()ed arrays (release with tjb_context_table_free): one row per context_histogram_t with the
+ * fields of src/context_histogram.h:17-43, the context pairs and the (tract length, reads) bins of its empfreq, most
+ * frequent first.  The reference's quirks are kept (the last histogram of a sample is dropped, :379-382; the context
+ * union of :411-418).  GFF3 features (:331-351) are not looked up here.  Sequential host code; returns n_hist. */
+typedef struct {
+  int32_t kmer_size;              /* -k */
+  int32_t min_tract_size;         /* -m: also the largest location difference inside one histogram (:262) */
+  int32_t max_distance_per_flank; /* -d */
+  int32_t levenshtein_distance;   /* -l (after the defaulting of src/main.c:192) */
+} tjb_hist_opts;
+
+typedef struct {
+  int32_t n_hist, name_stride;    /* name_stride = 2 k + 4 bytes per name ("LEFT.B.RIGHT", NUL padded) */
+  int32_t *location, *loc2d /* 3 per row */, *base, *neg_strand, *mismatches, *multi, *indel, *integral, *n_context,
+          *mode_context_count, *mode_context_length, *mode_context_id, *h_min, *h_max;
+  char *names;
+  int32_t *ctx_first;             /* n_hist + 1: contexts of row i = contexts[2 * ctx_first[i] .. 2 * ctx_first[i + 1]) */
+  uint64_t *contexts;
+  int32_t *h_first;               /* n_hist + 1: bins of row i = h_length / h_freq [h_first[i] .. h_first[i + 1]) */
+  int32_t *h_length, *h_freq;
+} tjb_context_table;
+
+int tjb_context_histograms (const tjb_hist_opts *opt, const void *elem, int32_t n_elem, tjb_context_table *out);
+void tjb_context_table_free (tjb_context_table *t);
+
 /* host FASTQ/FASTA(.gz) decoder on its own (kseq semantics): appends "SEQ\n" per record to dst (capacity cap);
  * returns bytes written (0 = end of file), <0 on error.  Exposed for tests and for callers that feed
  * tjb_count_sample_host themselves. */

@@ -272,3 +272,31 @@ def reference_merge_tracts(tables, levenshtein_distance=2):
                               C.c_int(levenshtein_distance), p(out[0]), p(out[1]), p(out[2]))
     assert rc == total
     return tuple(out)
+
+
+# ---- per-sample context histograms (rows 11-13): the unmodified reference end to end with the stand-in mapper ---------
+PIPELINE_SO = os.path.join(HERE, "_ref", "libref_pipeline.so")
+
+
+def reference_pipeline(buf, fasta, gff, k=25, m=4, min_coverage=5, remove_biased=True, max_distance_per_flank=1,
+                       levenshtein_distance=2):
+    """reads -> new_genomic_context_list() of the compiled reference (oracle/shim/ref_pipeline.c).  Returns
+    (mapped elements in location order as a HOPO_DTYPE array, dict of the histogram table) or (None, None) when the
+    reference excludes the sample"""
+    from tatajuba_b200._lib import TjbContextTable  # layout of the table only
+
+    class _Dump(C.Structure):
+        _fields_ = [("n_mapped", C.c_int), ("elem", C.c_void_p), ("hist", TjbContextTable)]
+    lib = C.CDLL(PIPELINE_SO)
+    buf = np.frombuffer(buf, dtype=np.uint8) if not isinstance(buf, np.ndarray) else buf
+    d = _Dump()
+    rc = lib.ref_pipeline_run(C.c_void_p(buf.ctypes.data), C.c_size_t(buf.size), os.fsencode(fasta), os.fsencode(gff), k, m,
+                              min_coverage, int(remove_biased), max_distance_per_flank, levenshtein_distance, C.byref(d))
+    if rc < 0:
+        return None, None
+    elem = np.zeros(d.n_mapped, dtype=HOPO_DTYPE)
+    if d.n_mapped:
+        C.memmove(elem.ctypes.data, d.elem, 40 * d.n_mapped)
+    table = d.hist.to_numpy()
+    lib.ref_pipeline_free(C.byref(d))
+    return elem, table

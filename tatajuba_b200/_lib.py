@@ -18,7 +18,7 @@ EXPORTS = [
     "tjb_count_sample_files", "tjb_count_sample_host", "tjb_count_sample_device", "tjb_count_sample",
     "tjb_counter_out_free", "tjb_ctx_set_result_mode", "tjb_device_count", "tjb_sample_begin", "tjb_sample_scan_device",
     "tjb_ctx_table_capacity", "tjb_ctx_reserve_entries",
-    "tjb_sample_export", "tjb_sample_import", "tjb_sample_finalise", "tjb_query_rows_device", "tjb_query_rows", "tjb_union_queries_device", "tjb_merge_tracts", "tjb_reader_open", "tjb_reader_fill", "tjb_reader_close",
+    "tjb_sample_export", "tjb_sample_import", "tjb_sample_finalise", "tjb_query_rows_device", "tjb_query_rows", "tjb_union_queries_device", "tjb_merge_tracts", "tjb_context_histograms", "tjb_context_table_free", "tjb_reader_open", "tjb_reader_fill", "tjb_reader_close",
 ]
 
 
@@ -33,6 +33,38 @@ class TjbCounterOut(C.Structure):
                 ("name", C.c_char_p), ("n_reads", C.c_int64), ("n_bases", C.c_int64), ("n_raw", C.c_int64),
                 ("n_distinct", C.c_int64), ("n_skipped_nonacgt", C.c_int64), ("ms_decode", C.c_double),
                 ("ms_device", C.c_double), ("arena", C.c_int32), ("reserved", C.c_int32)]
+
+
+class TjbHistOpts(C.Structure):
+    _fields_ = [("kmer_size", C.c_int32), ("min_tract_size", C.c_int32), ("max_distance_per_flank", C.c_int32),
+                ("levenshtein_distance", C.c_int32)]
+
+
+_I32P, _U64P = C.POINTER(C.c_int32), C.POINTER(C.c_uint64)
+
+
+class TjbContextTable(C.Structure):
+    INT_ARRAYS = ["location", "loc2d", "base", "neg_strand", "mismatches", "multi", "indel", "integral", "n_context",
+                  "mode_context_count", "mode_context_length", "mode_context_id", "h_min", "h_max"]
+    _fields_ = ([("n_hist", C.c_int32), ("name_stride", C.c_int32)] + [(n, _I32P) for n in INT_ARRAYS] +
+                [("names", C.POINTER(C.c_char)), ("ctx_first", _I32P), ("contexts", _U64P), ("h_first", _I32P),
+                 ("h_length", _I32P), ("h_freq", _I32P)])
+
+    def to_numpy(self):
+        """copies of the arrays as a dict (names as an (n, stride) uint8 array)"""
+        import numpy as np
+        n = max(self.n_hist, 0)
+        out = {"n_hist": self.n_hist}
+        if n == 0:
+            return out
+        arr = lambda p, cnt, dt: np.ctypeslib.as_array(p, shape=(cnt,)).astype(dt).copy() if cnt else np.zeros(0, dt)  # noqa: E731
+        for name in self.INT_ARRAYS:
+            out[name] = arr(getattr(self, name), 3 * n if name == "loc2d" else n, np.int32)
+        out["names"] = np.ctypeslib.as_array(C.cast(self.names, C.POINTER(C.c_uint8)), shape=(n * self.name_stride,)).reshape(n, self.name_stride).copy()
+        out["ctx_first"], out["h_first"] = arr(self.ctx_first, n + 1, np.int32), arr(self.h_first, n + 1, np.int32)
+        out["contexts"] = arr(self.contexts, 2 * int(out["ctx_first"][-1]), np.uint64)
+        out["h_length"], out["h_freq"] = arr(self.h_length, int(out["h_first"][-1]), np.int32), arr(self.h_freq, int(out["h_first"][-1]), np.int32)
+        return out
 
 
 class TjbKernelStat(C.Structure):
@@ -96,6 +128,9 @@ def load():
     lib.tjb_query_rows.argtypes = [pout, vp]
     lib.tjb_union_queries_device.argtypes = [vp, vp, i64, i32, vp, C.POINTER(i64), vp]
     lib.tjb_merge_tracts.argtypes = [i32, vp, vp, vp, vp, vp, i32, i32, vp, vp, vp]
+    lib.tjb_context_histograms.argtypes = [C.POINTER(TjbHistOpts), vp, i32, C.POINTER(TjbContextTable)]
+    lib.tjb_context_table_free.argtypes = [C.POINTER(TjbContextTable)]
+    lib.tjb_context_table_free.restype = None
     lib.tjb_reader_open.restype = vp
     lib.tjb_reader_open.argtypes = [cp]
     lib.tjb_reader_fill.restype = i64

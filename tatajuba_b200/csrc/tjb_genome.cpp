@@ -8,6 +8,8 @@
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
+#include <string>
+#include <utility>
 #include <vector>
 
 #include "tjb_gpu.h"
@@ -109,4 +111,278 @@ extern "C" int tjb_merge_tracts (int32_t n_samples, const int32_t *n_hist, const
     out_tract_id[i] = id;
   }
   return n_acc;
+}
+
+// ---------------------------------------------------------------------------------------------------------
+// Per-sample context histograms after the mapper: rows 11-13 of the hot-path table.
+//
+// Restates, on the flat arrays of the C ABI, what new_genomic_context_list() does with a hopo_counter once
+// finalise_hopo_counter() has returned (reference src/context_histogram.c:237-271): the mapped elements are walked in
+// location order and each one either joins the LAST histogram (same base, location within -m, flanks within -d
+// substitutions, or names within -l edits) or starts a new one (:245-268, distance :25-48, Hamming per flank
+// src/hopo_counter.c:61-68); then finalise_genomic_context_hist() (:274-305): the weighted tract-length histogram of
+// every context (empirical_frequency.c:202-277: bins by length, most frequent first, ties by length descending) and
+// genomic_context_merge_histograms_at_same_location() (:364-421), including its two quirks: the list is cut to j
+// entries where j is the INDEX of the last one (:379-382: the last histogram of every sample is dropped), and the
+// context lists are united by "append unless equal to the first differing one" (:411-418).  The GFF3 feature of a
+// context (:331-351) is a table look-up by position that stays with the reference's annotation code.
+// A sequential chain (every element is compared with the histogram the previous one went to): host code, like the
+// mapper it follows.
+namespace {
+
+inline int32_t sext_bits (uint64_t v, int lo, int width)
+{
+  const int64_t m = 1LL << (width - 1);
+  const int64_t x = (int64_t) ((v >> lo) & ((1ULL << width) - 1));
+  return (int32_t) ((x ^ m) - m);
+}
+
+struct Elem { // the fields of a mapped hopo_element (src/hopo_counter.h:34-49)
+  uint64_t ctx[2];
+  int32_t base, length, count, mismatches, multi, neg_strand, location, loc2d[3];
+};
+
+Elem read_elem (const uint8_t *p)
+{
+  Elem e;
+  uint64_t bits;
+  int32_t tail[4];
+  memcpy (e.ctx, p, 16); memcpy (&bits, p + 16, 8); memcpy (tail, p + 24, 16);
+  e.base = sext_bits (bits, 0, 2); e.length = sext_bits (bits, 2, 10); e.count = sext_bits (bits, 12, 20);
+  e.mismatches = sext_bits (bits, 32, 12); e.multi = sext_bits (bits, 44, 3); e.neg_strand = sext_bits (bits, 47, 2);
+  e.location = tail[0]; e.loc2d[0] = tail[1]; e.loc2d[1] = tail[2]; e.loc2d[2] = tail[3];
+  return e;
+}
+
+struct Hist {
+  std::vector<uint64_t> ctx;                 // pairs
+  int32_t base, multi, indel, neg_strand, mismatches;
+  std::string name;
+  int32_t integral, location, loc2d[3], mode_count, mode_length, mode_id;
+  std::vector<std::pair<int32_t, int32_t>> bins; // (tract length, reads): raw while elements arrive, then the histogram
+  int32_t hmin = 0, hmax = 0;
+};
+
+const char kBase[4] = {'A', 'C', 'G', 'T'};
+
+// "LEFT.B.RIGHT" of a context, reverse complemented for a hit on the negative strand (src/hopo_counter.c:471-493)
+std::string context_name (const uint64_t *ctx, int32_t base, int k, bool neg)
+{
+  std::string s ((size_t) 2 * k + 3, '.');
+  if (!neg) {
+    for (int i = 0; i < k; i++) s[i] = kBase[(ctx[0] >> (2 * i)) & 3];
+    s[k + 1] = kBase[base & 3];
+    for (int i = 0; i < k; i++) s[k + 3 + i] = kBase[(ctx[1] >> (2 * i)) & 3];
+  } else {
+    const int n = 2 * k + 3;
+    for (int i = 0; i < k; i++) s[n - 1 - i] = kBase[(~(ctx[0] >> (2 * i))) & 3];
+    s[n - 1 - (k + 1)] = kBase[(~base) & 3];
+    for (int i = 0; i < k; i++) s[n - 1 - (k + 3) - i] = kBase[(~(ctx[1] >> (2 * i))) & 3];
+  }
+  return s;
+}
+
+// differing bases of two flanks, counted up to max_dist (src/hopo_counter.c:61-68)
+int flank_distance (uint64_t a, uint64_t b, int max_dist)
+{
+  uint64_t d = a ^ b;
+  int dist = 0;
+  while (d && dist < max_dist) { if (d & 3) dist++; d >>= 2; }
+  return dist;
+}
+
+const int kMaxDist = 0xffff; // CH_MAX_DIST
+
+// src/context_histogram.c:25-48
+int hist_elem_distance (const Hist &h, const Elem &e, int max_distance, int location_difference, int *idx_match)
+{
+  *idx_match = -1;
+  if (h.base != e.base) return kMaxDist;
+  if (std::abs (e.location - h.location) > location_difference) return kMaxDist;
+  int this_max = 0;
+  for (size_t c = 0; c < h.ctx.size () / 2; c++) {
+    int distance = flank_distance (h.ctx[2 * c], e.ctx[0], 2 * max_distance);
+    if (distance >= 2 * max_distance) return distance;
+    distance += flank_distance (h.ctx[2 * c + 1], e.ctx[1], 2 * max_distance - distance);
+    if (distance >= 2 * max_distance) return distance;
+    if (distance > this_max) this_max = distance;
+    if (distance == 0) { *idx_match = (int) c; return 0; }
+  }
+  return this_max;
+}
+
+Hist new_hist (const Elem &e, std::string &&name) // :133-167
+{
+  Hist h;
+  h.ctx = {e.ctx[0], e.ctx[1]};
+  h.base = e.base; h.multi = e.multi; h.indel = 0;
+  h.neg_strand = e.neg_strand ? 1 : 0; h.mismatches = e.mismatches;
+  h.name = std::move (name);
+  h.integral = e.count; h.location = e.location;
+  for (int i = 0; i < 3; i++) h.loc2d[i] = e.loc2d[i];
+  h.mode_count = e.count; h.mode_length = e.length; h.mode_id = 0;
+  h.bins.push_back ({e.length, e.count});
+  return h;
+}
+
+void add_elem (Hist &h, const Elem &e, std::string &&name, int idx_match) // :182-222
+{
+  if (idx_match < 0) { idx_match = (int) (h.ctx.size () / 2); h.ctx.push_back (e.ctx[0]); h.ctx.push_back (e.ctx[1]); }
+  if (h.mode_count < e.count) {
+    h.mode_count = e.count; h.mode_length = e.length; h.mode_id = idx_match;
+    h.location = e.location;
+    for (int i = 0; i < 3; i++) h.loc2d[i] = e.loc2d[i];
+    h.mismatches = e.mismatches; h.neg_strand = e.neg_strand ? 1 : 0;
+    h.name = std::move (name);
+  }
+  if ((h.multi ^ e.multi) == 1) h.multi = 2;
+  h.integral += e.count;
+  h.bins.push_back ({e.length, e.count});
+}
+
+// (value, weight) pairs -> bins by value with summed weights, most frequent first, ties by value descending
+// (empirical_frequency.c:254-277 after the sort of :219 / :245)
+void make_histogram (std::vector<std::pair<int32_t, int32_t>> &v, int32_t *vmin, int32_t *vmax)
+{
+  std::sort (v.begin (), v.end ());
+  std::vector<std::pair<int32_t, int32_t>> out;
+  for (const auto &p : v) {
+    if (!out.empty () && out.back ().first == p.first) out.back ().second += p.second;
+    else out.push_back (p);
+  }
+  *vmin = out.front ().first; *vmax = out.back ().first;
+  std::sort (out.begin (), out.end (), [] (const std::pair<int32_t, int32_t> &a, const std::pair<int32_t, int32_t> &b) {
+    return a.second != b.second ? a.second > b.second : a.first > b.first; });
+  v.swap (out);
+}
+
+bool hists_overlap (const Hist &c1, const Hist &c2, int lev, std::vector<uint32_t> &tab) // :87-110
+{
+  const int32_t apart = std::abs (c1.location - c2.location);
+  if (!apart) return true;
+  const int32_t tract = std::min (c1.mode_length, c2.mode_length);
+  if (apart > tract - 1 || c1.base != c2.base) return false;
+  const uint32_t n = (uint32_t) c1.name.size ();
+  std::string other = c2.name;
+  other.resize (n, '\0'); // the reference reads the second name over the first one's length
+  return border_free_levenshtein (c1.name.data (), n, other.data (), n, tab) <= (uint32_t) lev;
+}
+
+void accumulate (Hist &to, Hist &from) // :387-421
+{
+  std::vector<std::pair<int32_t, int32_t>> both = to.bins;
+  both.insert (both.end (), from.bins.begin (), from.bins.end ());
+  make_histogram (both, &to.hmin, &to.hmax);
+  to.bins.swap (both);
+  if (to.mode_count < from.mode_count) {
+    to.location = from.location; to.mode_count = from.mode_count; to.mode_length = from.mode_length;
+    to.mode_id = from.mode_id; to.mismatches = from.mismatches;
+    for (int i = 0; i < 3; i++) to.loc2d[i] = from.loc2d[i];
+    to.ctx.swap (from.ctx);
+    to.name.swap (from.name);
+  }
+  to.integral += from.integral;
+  const size_t n1 = to.ctx.size () / 2;
+  for (size_t i = 0; i < from.ctx.size () / 2; i++)
+    for (size_t j = 0; j < n1; j++)
+      if (to.ctx[2 * j] != from.ctx[2 * i] || to.ctx[2 * j + 1] != from.ctx[2 * i + 1]) { // :411-418, as written
+        to.ctx.push_back (from.ctx[2 * i]); to.ctx.push_back (from.ctx[2 * i + 1]);
+        break;
+      }
+}
+
+template <typename T> T *alloc_array (size_t n) { return (T*) malloc ((n ? n : 1) * sizeof (T)); }
+
+} // namespace
+
+extern "C" void tjb_context_table_free (tjb_context_table *t)
+{
+  if (!t) return;
+  void *p[] = {t->location, t->loc2d, t->base, t->neg_strand, t->mismatches, t->multi, t->indel, t->integral, t->n_context,
+               t->mode_context_count, t->mode_context_length, t->mode_context_id, t->h_min, t->h_max, t->names, t->ctx_first,
+               t->contexts, t->h_first, t->h_length, t->h_freq};
+  for (void *q : p) free (q);
+  memset (t, 0, sizeof (*t));
+}
+
+extern "C" int tjb_context_histograms (const tjb_hist_opts *opt, const void *elem, int32_t n_elem, tjb_context_table *out)
+{
+  if (!opt || !out || n_elem < 0 || (n_elem && !elem) || opt->kmer_size < 2 || opt->kmer_size > 32) return TJB_ERR_ARG;
+  memset (out, 0, sizeof (*out));
+  const int k = opt->kmer_size;
+  out->name_stride = 2 * k + 4;
+  if (!n_elem) return 0;
+  const uint8_t *p = (const uint8_t*) elem;
+  std::vector<Hist> hist;
+  std::vector<uint32_t> tab;
+  // 1. elements in location order against the last histogram (:237-268)
+  for (int32_t i = 0; i < n_elem; i++) {
+    const Elem e = read_elem (p + (size_t) 40 * i);
+    std::string name = context_name (e.ctx, e.base, k, e.neg_strand != 0);
+    if (hist.empty ()) { hist.push_back (new_hist (e, std::move (name))); continue; }
+    Hist &last = hist.back ();
+    int idx_match;
+    int distance = hist_elem_distance (last, e, opt->max_distance_per_flank, opt->min_tract_size, &idx_match);
+    if (distance < opt->max_distance_per_flank) add_elem (last, e, std::move (name), idx_match);
+    else {
+      if (distance < kMaxDist) { // same base, close by: try again, now allowing indels between the names
+        const uint32_t n = (uint32_t) last.name.size ();
+        distance = (int) border_free_levenshtein (last.name.data (), n, name.data (), n, tab);
+      }
+      if (distance < opt->levenshtein_distance) { add_elem (last, e, std::move (name), idx_match); last.indel = 1; }
+      else hist.push_back (new_hist (e, std::move (name)));
+    }
+  }
+  // 2. tract-length histogram of every context (:279-286); elements of weight 0 do not take part
+  for (Hist &h : hist) {
+    std::vector<std::pair<int32_t, int32_t>> v;
+    for (const auto &b : h.bins) if (b.second) v.push_back (b);
+    if (v.empty ()) return TJB_ERR_ARG; // the reference stops with "vector of empirical frequencies with all freqs=0"
+    make_histogram (v, &h.hmin, &h.hmax);
+    h.bins.swap (v);
+  }
+  // 3. neighbours that overlap are merged (:364-385); the list then keeps j entries, j being the index of the last one
+  std::vector<Hist> merged;
+  merged.push_back (std::move (hist[0]));
+  for (size_t i = 1; i < hist.size (); i++) {
+    if (hists_overlap (merged.back (), hist[i], opt->levenshtein_distance, tab)) accumulate (merged.back (), hist[i]);
+    else merged.push_back (std::move (hist[i]));
+  }
+  const size_t n_out = merged.size () - 1; // :379-382: n_hist = j
+  // 4. flat arrays
+  size_t n_ctx = 0, n_bins = 0;
+  for (size_t i = 0; i < n_out; i++) { n_ctx += merged[i].ctx.size () / 2; n_bins += merged[i].bins.size (); }
+  out->n_hist = (int32_t) n_out;
+  out->location = alloc_array<int32_t> (n_out); out->loc2d = alloc_array<int32_t> (3 * n_out); out->base = alloc_array<int32_t> (n_out);
+  out->neg_strand = alloc_array<int32_t> (n_out); out->mismatches = alloc_array<int32_t> (n_out); out->multi = alloc_array<int32_t> (n_out);
+  out->indel = alloc_array<int32_t> (n_out); out->integral = alloc_array<int32_t> (n_out); out->n_context = alloc_array<int32_t> (n_out);
+  out->mode_context_count = alloc_array<int32_t> (n_out); out->mode_context_length = alloc_array<int32_t> (n_out);
+  out->mode_context_id = alloc_array<int32_t> (n_out); out->h_min = alloc_array<int32_t> (n_out); out->h_max = alloc_array<int32_t> (n_out);
+  out->names = alloc_array<char> (n_out * (size_t) out->name_stride);
+  out->ctx_first = alloc_array<int32_t> (n_out + 1); out->contexts = alloc_array<uint64_t> (2 * n_ctx);
+  out->h_first = alloc_array<int32_t> (n_out + 1); out->h_length = alloc_array<int32_t> (n_bins); out->h_freq = alloc_array<int32_t> (n_bins);
+  if (!out->location || !out->loc2d || !out->base || !out->neg_strand || !out->mismatches || !out->multi || !out->indel || !out->integral ||
+      !out->n_context || !out->mode_context_count || !out->mode_context_length || !out->mode_context_id || !out->h_min || !out->h_max ||
+      !out->names || !out->ctx_first || !out->contexts || !out->h_first || !out->h_length || !out->h_freq) {
+    tjb_context_table_free (out);
+    return TJB_ERR_NOMEM;
+  }
+  memset (out->names, 0, n_out * (size_t) out->name_stride);
+  size_t c = 0, b = 0;
+  for (size_t i = 0; i < n_out; i++) {
+    const Hist &h = merged[i];
+    out->location[i] = h.location; out->base[i] = h.base; out->neg_strand[i] = h.neg_strand; out->mismatches[i] = h.mismatches;
+    for (int j = 0; j < 3; j++) out->loc2d[3 * i + j] = h.loc2d[j];
+    out->multi[i] = h.multi; out->indel[i] = h.indel; out->integral[i] = h.integral; out->n_context[i] = (int32_t) (h.ctx.size () / 2);
+    out->mode_context_count[i] = h.mode_count; out->mode_context_length[i] = h.mode_length; out->mode_context_id[i] = h.mode_id;
+    out->h_min[i] = h.hmin; out->h_max[i] = h.hmax;
+    memcpy (out->names + i * (size_t) out->name_stride, h.name.data (), std::min (h.name.size (), (size_t) out->name_stride - 1));
+    out->ctx_first[i] = (int32_t) c;
+    memcpy (out->contexts + 2 * c, h.ctx.data (), h.ctx.size () * sizeof (uint64_t));
+    c += h.ctx.size () / 2;
+    out->h_first[i] = (int32_t) b;
+    for (const auto &bin : h.bins) { out->h_length[b] = bin.first; out->h_freq[b] = bin.second; b++; }
+  }
+  out->ctx_first[n_out] = (int32_t) c; out->h_first[n_out] = (int32_t) b;
+  return (int) n_out;
 }

@@ -536,6 +536,7 @@ static bool sample_overflowed (tjb_ctx *ctx)
   if (n_ovf > ctx->ovf_capacity || n_ent > ctx->tab_slots / 2 || n_ent + n_ovf > ctx->list_cap) {
     // the table or the overflow list was too small for this sample: everything after the scan worked on a part of it
     ctx->want_entries = (size_t) (n_ent + n_ovf) * 2 + 4096;
+    if (ctx->want_entries < (size_t) n_ovf * 8 + 4096) ctx->want_entries = (size_t) n_ovf * 8 + 4096; // the overflow list is an eighth of it
     return true;
   }
   ctx->last_entries = (size_t) (n_ent + n_ovf);

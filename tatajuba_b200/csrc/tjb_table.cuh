@@ -11,8 +11,8 @@
 // length field is biased by 512):
 //   key == mine                   add my weight to the slot's count word (one load + one RED: the common case)
 //   key == 0                      empty, or claimed a moment ago: CAS count 0 -> my weight claims the slot, the claimer
-//                                 then stores the key.  A thread that loses the CAS reads the key once more: mine ->
-//                                 add; still 0 -> the observation is DEFERRED to the overflow list; else probe on
+//                                 then stores the key.  A thread that loses the CAS reads the key a few more times:
+//                                 mine -> add; still 0 -> the observation is DEFERRED to the overflow list; else probe on
 //   otherwise                     another key: probe on (linear)
 // After TAB_MAXPROBE probes the observation is deferred as well.  Deferred observations keep their raw form (one record
 // each, flag bits set); the partition kernel turns them into weighted records of weight 1, so a key may reach the
@@ -25,6 +25,7 @@
 #ifndef TAB_MAXPROBE
 #define TAB_MAXPROBE 48
 #endif
+#define TAB_RELOOK 32 // looks at a slot whose claim was lost before the observation is deferred
 
 struct AggTable {
   unsigned long long *cnt;   // [slots] forward count | reverse count << 32
@@ -102,7 +103,10 @@ template <int W> __device__ __noinline__ int table_add (AggTable t, Rec<W> key, 
         }
         return TAB_NEW;
       }
-      seen = table_probe<W> (t, slot, key); // claimed by somebody else a moment ago: its key may be there by now
+      // claimed by somebody else a moment ago: its key is on its way (the claimer stores it right after its CAS).  Look
+      // again a few times (bounded: nobody is waited for indefinitely) before giving the observation to the overflow list;
+      // when a kernel adds all records of a sample at once, the ~depth copies of a new key arrive together
+      for (int again = 0; again < TAB_RELOOK && seen == 0; again++) { __nanosleep (64); seen = table_probe<W> (t, slot, key); }
       if (seen == 0) return TAB_DEFER;
     }
     if (seen == 1) { red_add_global (t.cnt + slot, weight); return TAB_ADDED; }

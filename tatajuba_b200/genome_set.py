@@ -265,6 +265,23 @@ def count_samples(contexts, n_samples, count_one, on_done=None):
     return results
 
 
+def context_histograms(elem40, kmer_size=25, min_tract_size=4, max_distance_per_flank=1, levenshtein_distance=2):
+    """new_genomic_context_list() after finalise_hopo_counter() (src/context_histogram.c:237-305, 364-421): the mapped
+    elements of one sample (HOPO_DTYPE array, hc.elem[ref_start:] in the order the location sort left them in) ->
+    dict of flat arrays, one row per context histogram (tjb_context_histograms)"""
+    lib = _lib.load()
+    e = np.ascontiguousarray(elem40)
+    assert e.dtype.itemsize == 40
+    opt = _lib.TjbHistOpts(int(kmer_size), int(min_tract_size), int(max_distance_per_flank), int(levenshtein_distance))
+    t = _lib.TjbContextTable()
+    rc = lib.tjb_context_histograms(C.byref(opt), C.c_void_p(e.ctypes.data if len(e) else 0), len(e), C.byref(t))
+    if rc < 0:
+        raise RuntimeError(f"tjb_context_histograms: {rc}")
+    out = t.to_numpy()
+    lib.tjb_context_table_free(C.byref(t))
+    return out
+
+
 def surviving_samples(alive):
     """remove_empty_genomes + index labelling (src/genome_set.c:97-100, 132-142): samples without any mapped HT are
     dropped BEFORE sample ids are assigned, so ids depend on which samples survive.  alive: one flag per sample.
