@@ -10,8 +10,9 @@ A step = one full pass of the replaced span (scan + aggregate + sort + QC + grou
 over that sample.  Every timed number is gated on parity: before any timing the unmodified reference (oracle/_ref)
 counts the SAME full sample and its state at the mapper call must equal ours, device-resident and from host memory.
 
-  value   reads resident in HBM when the timed region starts; the steps are dealt to two contexts of the GPU (the
-          reference's own loop over samples is a parallel one, src/genome_set.c:66-68), results in the pinned arena
+  value   reads resident in HBM when the timed region starts, one context (one sample at a time), results in the pinned
+          arena; `config.two_contexts` adds the throughput with the steps dealt to two contexts of the GPU (the
+          reference's own loop over samples is a parallel one, src/genome_set.c:66-68)
   e2e     the same through the reference-facing C ABI call with the decoded reads in pinned HOST memory: host -> device
           copies inside, results in malloc()ed host memory as the binding needs them
   extra legs (rank 0, in the same JSON line): the sample with 0.1 % and 1 % substitution errors, BASELINE configs[4]
@@ -231,7 +232,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--legs", default=",".join(ALL_LEGS), help="extra legs to run (comma separated; 'none' for the headline only)")
-    ap.add_argument("--contexts", type=int, default=2, help="contexts per GPU the steps are dealt to")
+    ap.add_argument("--contexts", type=int, default=1, help="contexts per GPU the steps of the headline are dealt to (the C4 leg always uses 2)")
     ap.add_argument("--no-cpu-baseline", action="store_true", help="skip the parity gate / CPU baseline (kernel experiments only)")
     args = ap.parse_args()
     args.legs = [x for x in args.legs.split(",") if x and x != "none"]
@@ -348,7 +349,18 @@ def main():
                 scan_ms += s["ms_total"]; scan_launches += s["launches"]; scan_bytes += s["bytes_algorithmic"]
         launches += c.launch_count()
         c.set_profiling(0)
-    ms_single, _ = timed(lambda: [ctx.count_device(d_buf.data_ptr(), n_bytes, opt) for _ in range(args.steps)])
+    ms_single = ms
+    two = None
+    if len(ctxs) == 1:  # the same steps dealt to two contexts (sample i's reduce and copy-out under sample i+1's scan)
+        pair = [ctx, Context(local_rank)]
+        pair[1].set_result_mode(True)
+        for _ in range(args.warmup):
+            pair[1].count_device(d_buf.data_ptr(), n_bytes, opt)
+        ms2, _ = timed(lambda: count_steps(args.steps, lambda c, s: c.count_device(d_buf.data_ptr(), n_bytes, opt), pair))
+        two = {"ms_per_step": ms2 / args.steps, "value": world * n_bases * args.steps / (ms2 * 1e-3), "unit": "bases/s"}
+        pair[1].close()
+    else:
+        ms_single, _ = timed(lambda: [ctx.count_device(d_buf.data_ptr(), n_bytes, opt) for _ in range(args.steps)])
     kernels = kernel_table(ctx, lambda: ctx.count_device(d_buf.data_ptr(), n_bytes, opt))
 
     # ---- e2e: pinned host buffer -> C ABI -> malloc()ed host results --------------------------------------------------
@@ -436,7 +448,7 @@ def main():
         "scaling": "weak", "vs_baseline": None, "dtype": "u8/u64", "data": "synthetic",
         "config": {"workload": WORKLOAD, "bases_per_gpu": n_bases, "reads_per_gpu": n_reads, "input_bytes": n_bytes,
                    "l2": "input (503 MB) larger than L2 (126 MB); no flush needed", "parity": parity,
-                   "contexts_per_gpu": len(ctxs), "one_context_ms_per_step": ms_single / args.steps, **stats0},
+                   "contexts_per_gpu": len(ctxs), "one_context_ms_per_step": ms_single / args.steps, "two_contexts": two, **stats0},
         "e2e": {"value": world * n_bases * args.steps / (ms_e2e * 1e-3), "unit": "bases/s", "ms_per_step": ms_e2e / args.steps,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "results": "malloc()ed host arrays (reference layout)",
                 "transfer": transfer},
@@ -499,8 +511,10 @@ def c4_leg(ctxs, rank, world, timed, all_ranks_ok, args):
     computes the union of the mapper queries; rank 0 runs the cross-sample merge (tjb_merge_tracts) on a stand-in
     post-mapper table.  Everything between the first sample and the merged tract ids is inside the timed region."""
     import torch
-    from tatajuba_b200 import TatajubaOptions, genome_set
+    from tatajuba_b200 import Context, TatajubaOptions, genome_set
     opt = TatajubaOptions(K, M, MIN_COV, True, paired_end=True)
+    if len(ctxs) < 2:  # two contexts per GPU: sample i's reduce, copy-out and host work under sample i+1's copy-in and scan
+        ctxs = list(ctxs) + [Context(ctxs[0].device)]
     mine = genome_set.samples_of_rank(C4_SAMPLES, rank, world)
     cores = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)
     threads = max(1, cores // max(1, int(os.environ.get("LOCAL_WORLD_SIZE", world))))
@@ -527,13 +541,17 @@ def c4_leg(ctxs, rank, world, timed, all_ranks_ok, args):
         c.set_result_mode(True)
     ctx = ctxs[0]
 
-    def job():
+    resident = [p.cuda() for p in pinned]  # 8.2 GB at one GPU
+    torch.cuda.synchronize()
+
+    def job(from_host=True):
         rows = {}
 
         def done(c, i, hc):  # on the context's thread, before it counts its next sample
             rows[mine[i]] = genome_set.query_rows_device(c, hc).clone()
             return hc.n_idx
-        genome_set.count_samples(ctxs, len(bufs), lambda c, i: c.count_host(pinned[i], opt), on_done=done)
+        one = (lambda c, i: c.count_host(pinned[i], opt)) if from_host else (lambda c, i: c.count_device(resident[i].data_ptr(), resident[i].numel(), opt))
+        genome_set.count_samples(ctxs, len(bufs), one, on_done=done)
         all_rows, sizes = genome_set.allgather_tables_device(rows, C4_SAMPLES)
         uni, idx = genome_set.union_queries_device(ctx, all_rows, K)
         n_concat = 0
@@ -546,15 +564,21 @@ def c4_leg(ctxs, rank, world, timed, all_ranks_ok, args):
                                "name": np.zeros((n, 1), np.uint8)})
             n_concat = len(genome_set.merge_tracts(tables, 2)[0])
         return int(uni.shape[0]), int(sum(sizes)), n_concat
-    job()
-    best, out = None, None
-    for _ in range(3):
-        ms, out = timed(job)
-        best = ms if best is None else min(best, ms)
+    best_by_mode = {}
+    for from_host in (False, True):
+        job(from_host)
+        best, out = None, None
+        for _ in range(3):
+            ms, out = timed(lambda: job(from_host))
+            best = ms if best is None else min(best, ms)
+        best_by_mode[from_host] = best
+    best = best_by_mode[False]
     return {"workload": f"configs[3]: {C4_SAMPLES} samples x {C4_GENOME / 1e6:.1f} Mbp x {C4_COVERAGE}x PE, tract polymorphism on {C4_FRACTION:.0%} of the tracts",
             "scaling": "strong (the 96 samples are dealt to the ranks)", "ms": best, "value": bases_total / (best * 1e-3), "unit": "bases/s",
             "samples_per_rank": len(mine), "contexts_per_gpu": len(ctxs), "bases_total": bases_total, "parity": parity,
-            "inside": "H2D of every sample, count, query rows on the device, allgather, union of mapper queries, merge of tract ids (rank 0)",
+            "inside": "count of every sample (reads resident in HBM), query rows on the device, allgather, union of mapper queries, merge of tract ids (rank 0)",
+            "from_host": {"ms": best_by_mode[True], "value": bases_total / (best_by_mode[True] * 1e-3), "unit": "bases/s",
+                          "note": "the same with the reads of every sample in pinned host memory: H2D inside"},
             "n_union": out[0], "rows": out[1], "merged_rows": out[2]}
 
 

@@ -1058,7 +1058,9 @@ static bool packed_transfer_enabled (tjb_ctx *ctx, size_t n_bytes)
 {
   if (n_bytes < TJB_PACK_MIN_BYTES) return false;
   tjb_packer *pool = host_pool ();
-  if (!pool || tjb_packer_threads (pool) < 2) return false; // PCIe beats one core
+  // a packer thread turns ~6 GB/s of reads into 2-bit codes; the copy engine moves ~55 GB/s of plain bytes: below ~10
+  // threads (ranks that share a host split its cores) the bytes are sent as they are
+  if (!pool || tjb_packer_threads (pool) < 9) return false;
   for (int i = 0; i < 2; i++) {
     if (!ctx->h_pk[i] && cudaMallocHost ((void**) &ctx->h_pk[i], TJB_HOST_CHUNK_BYTES / 4 + 64) != cudaSuccess) return false;
     if (!ctx->h_exc_pos[i] && cudaMallocHost ((void**) &ctx->h_exc_pos[i], (size_t) TJB_PACK_EXC_CAP * 4) != cudaSuccess) return false;

@@ -45,7 +45,7 @@ class Context:
     def __init__(self, device=0):
         self.lib = _lib.load()
         # the host pool (2-bit packing of host buffers, copy-out of the results) spins while a sample is processed, so
-        # ranks that share one host (torchrun: LOCAL_WORLD_SIZE) split the cores between them; with fewer than 4
+        # ranks that share one host (torchrun: LOCAL_WORLD_SIZE) split the cores between them; with fewer than 9
         # threads the library sends host buffers as they are and uses the pool for the copy-out only
         if "TJB_HOST_PACK" not in os.environ and int(os.environ.get("LOCAL_WORLD_SIZE", "1")) > 1:
             cpus = len(os.sched_getaffinity(0)) if hasattr(os, "sched_getaffinity") else (os.cpu_count() or 1)

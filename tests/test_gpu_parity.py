@@ -103,17 +103,43 @@ def test_gpu_drop_paths(ctx, restatement):
         assert want.status == status
 
 
+SW_TILE, SW_HALO_L, SW_HALO_R = 4000, 32, 64  # scan window geometry (csrc/tjb_scan.cuh): owned bytes, staged halos
+
+
 def test_gpu_tile_boundaries(ctx, restatement):
-    """tracts, flanks and long runs straddling the 8192-byte scan tiles and the staged halo"""
+    """tracts whose start sits on the last / first owned byte of a scan window (t * 4000 - 1, t * 4000, t * 4000 + 3999),
+    with runs of 31 (fast path) and 32 bases (slow path) at k = 32, which needs the whole 31 + 32 + 1 = 64-byte right
+    halo; flanks reaching into the left halo; an odd byte inside a flank at the first and the last interior window"""
     rng = np.random.default_rng(4)
-    fl = (b"GATC" * 8)
-    for pad in list(range(8100, 8260, 7)) + [16300, 16384, 16385]:
-        pre = bytes(rng.choice(np.frombuffer(b"ACGT", np.uint8), size=pad - 40).tobytes())
-        buf = pre + b"\n" + fl + b"A" * 9 + fl + b"\n" + fl + b"T" * 300 + fl + b"\n" + fl + b"C" * 5 + fl
-        check(ctx, restatement, buf, 25, 4, 1, False, f"pad {pad}", device_too=False)
-        check(ctx, restatement, buf, 32, 2, 1, False, f"pad {pad} k32", device_too=False)
+
+    def rnd(n):  # random bases without runs of 2+ (so that only the planted tracts are found near the boundaries)
+        out = bytearray()
+        while len(out) < n:
+            c = b"ACGT"[rng.integers(0, 4)]
+            if not out or out[-1] != c:
+                out.append(c)
+        return bytes(out)
+    n_windows = 5
+    for k, m in [(32, 2), (25, 4)]:
+        for t in (1, 2, n_windows - 1):
+            for start in (t * SW_TILE - 1, t * SW_TILE, t * SW_TILE + SW_TILE - 1):
+                for run, base in [(31, b"A"), (32, b"T"), (5, b"C"), (31, b"G")]:
+                    for odd_at in (None, start - 3, start + run + k - 2):
+                        body = bytearray(rnd(n_windows * SW_TILE + 300))
+                        prev = bytes([body[start - 1]])
+                        base_ = base if base != prev and base != bytes([body[start + run]]) else (b"C" if prev != b"C" and body[start + run] != ord("C") else b"G")
+                        body[start:start + run] = base_ * run
+                        if odd_at is not None:
+                            body[odd_at] = ord("n")
+                        buf = bytes(body) + b"\n"
+                        check(ctx, restatement, buf, k, m, 1, False, f"k={k} window {t} start {start} run {run} odd {odd_at}", device_too=False)
+    fl = b"GATC" * 8
     long_run = fl + b"G" * 20000 + fl + b"\n"
     check(ctx, restatement, long_run * 2, 25, 4, 1, False, "20k run")
+    # reads that end / begin exactly at a window boundary
+    for cut in (SW_TILE - 1, SW_TILE, SW_TILE + 1, 2 * SW_TILE - SW_HALO_L, 2 * SW_TILE + SW_HALO_R):
+        a, b = rnd(cut - 40) + fl + b"AAAAA" + fl[:3], fl + b"TTTTTT" + fl + rnd(500)
+        check(ctx, restatement, a + b"\n" + b + b"\n", 25, 4, 1, False, f"read boundary at {len(a)}", device_too=False)
 
 
 def test_gpu_files_path_matches_oracle(ctx, restatement, tmp_path):
