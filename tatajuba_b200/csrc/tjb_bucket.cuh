@@ -16,7 +16,7 @@
 //   wbucket_reduce_kernel grid      per bucket: smem sort + merge + QC + groups; compact output at the bucket start
 //   totals_kernel         1 CTA     exclusive scans of the per-bucket kept / group counts
 //   pack_kernel           grid      reference-layout 40-byte hopo_element rows + idx arrays + coverage hash inserts
-//   cov_max_kernel        grid      coverage = max over the hash table
+//   cov_max_kernel        grid      coverage = max over the hash table (only when a count wrapped; pack_kernel keeps the max otherwise)
 //
 // Buckets with more than BK_CAP records (one bin holding > BK_CAP/2 distinct observations: pathological samples) are
 // flagged and reduced by the multi-pass global path in tjb_sort.cuh / tjb_reduce.cuh instead.
@@ -47,7 +47,9 @@
 #define BK_CURSOR_STRIDE 32 // one partition cursor per 128-byte line: L2 atomics serialise per sector, not per address
 
 // meta[] slots (device u32)
-enum { META_NBUCKETS = 0, META_NOVERSIZE = 1, META_TICKET = 2, META_N = 3, META_NDIST = 4, META_NKEEP = 5, META_NIDX = 6, META_WORDS = 8 };
+enum { META_NBUCKETS = 0, META_NOVERSIZE = 1, META_TICKET = 2, META_N = 3, META_NDIST = 4, META_NKEEP = 5, META_NIDX = 6,
+       META_COVSCAN = 7, // a kept record has a count <= 0 (its 20-bit field wrapped): the coverage needs the table scan
+       META_WORDS = 8 };
 
 struct DigitList { int n; unsigned char word[28], shift[28], nbits[28]; };
 
@@ -261,20 +263,32 @@ aggregate_kernel (const u64 *__restrict__ recs, unsigned long long *__restrict__
   const int lane = threadIdx.x & 31;
   u32 n_new = 0;
   for (size_t i0 = (size_t) blockIdx.x * 256 + threadIdx.x; i0 < n; i0 += AGG_UNROLL * stride) {
+    // the kernel lives on L2 latency (a random 16-byte read per record): the records of AGG_UNROLL rounds are loaded
+    // together, then their home slots are read together, and only what did not hit its key there takes the probe loop
     Rec<W> r[AGG_UNROLL];
+    u32 slot[AGG_UNROLL];
+    int seen[AGG_UNROLL];
 #pragma unroll
     for (int u = 0; u < AGG_UNROLL; u++) { const size_t i = i0 + u * stride; if (i < n) r[u] = load_rec<W> (recs, i); }
 #pragma unroll
     for (int u = 0; u < AGG_UNROLL; u++) {
       const size_t i = i0 + u * stride;
-      int res = TAB_ADDED;
-      Rec<W> key;
+      seen[u] = -1;
       if (i < n) {
-        key = r[u];
+        Rec<W> key = r[u];
         key.w[0] &= ~3ULL;
-        res = table_add<W> (tab, key, flag_weight (r[u].w[0]));
-        if (res != TAB_ADDED) atomicAdd (&bin_hist[rec_bin<W> (key, k, F)], 1u); // a new entry, or a record of the overflow list
+        slot[u] = key_hash<W> (key) & tab.mask;
+        seen[u] = table_probe<W> (tab, slot[u], key);
       }
+    }
+#pragma unroll
+    for (int u = 0; u < AGG_UNROLL; u++) {
+      if (seen[u] < 0) continue;
+      if (seen[u] == 1) { red_add_global (tab.cnt + slot[u], flag_weight (r[u].w[0])); continue; } // the common case at depth
+      Rec<W> key = r[u];
+      key.w[0] &= ~3ULL;
+      const int res = table_add<W> (tab, key, flag_weight (r[u].w[0]));
+      if (res != TAB_ADDED) atomicAdd (&bin_hist[rec_bin<W> (key, k, F)], 1u); // a new entry, or a record of the overflow list
       n_new += res == TAB_NEW;
       if (res == TAB_DEFER) {
         const unsigned long long pos = atomicAdd (&counters[CTR_OVERFLOW], 1ULL);
@@ -619,8 +633,9 @@ totals_kernel (const uint4 *__restrict__ bstat, u32 *__restrict__ meta, u32 *__r
 }
 
 // ------------------------------------------------------------------------------- coverage hash + pack ----
-// coverage table: slot key = (flank & 0x7fffffff) + 1, 0 = empty (one memset clears keys and sums)
-__device__ __forceinline__ void cov_insert (u32 *__restrict__ keys, u32 *__restrict__ vals, u32 mask, u32 key, u32 w)
+// coverage table: slot key = (flank & 0x7fffffff) + 1, 0 = empty (one memset clears keys and sums).  Returns the key's
+// sum after this weight: with positive weights the largest value any insert returns is the largest final sum.
+__device__ __forceinline__ int cov_insert (u32 *__restrict__ keys, u32 *__restrict__ vals, u32 mask, u32 key, u32 w)
 {
   u32 slot = (key * 0x9E3779B1u) >> 7;
   key += 1;
@@ -632,8 +647,7 @@ __device__ __forceinline__ void cov_insert (u32 *__restrict__ keys, u32 *__restr
       prev = atomicCAS (&keys[slot], 0u, key);
       if (prev != 0 && prev != key) { slot++; continue; }
     }
-    atomicAdd (&vals[slot], w);
-    return;
+    return (int) (atomicAdd (&vals[slot], w) + w);
   }
 }
 
@@ -655,8 +669,14 @@ __global__ void __launch_bounds__ (256)
 pack_kernel (const u64 *__restrict__ out_rec, const u32 *__restrict__ out_cnt, const u32 *__restrict__ out_idx_i, const u32 *__restrict__ out_idx_f,
              const u32 *__restrict__ bkt_start, const uint4 *__restrict__ bstat, const u32 *__restrict__ koff, const u32 *__restrict__ ioff,
              const u32 *__restrict__ meta, int k, u64 *__restrict__ out40, int *__restrict__ idx_initial, int *__restrict__ idx_final,
-             u32 *__restrict__ cov_keys, u32 *__restrict__ cov_vals, u32 cov_mask, u32 max_keep, u32 max_idx, unsigned long long capacity)
+             u32 *__restrict__ cov_keys, u32 *__restrict__ cov_vals, u32 cov_mask, u32 max_keep, u32 max_idx, unsigned long long capacity,
+             int *__restrict__ cov, u32 *__restrict__ meta_out)
 {
+  // coverage (hopo_counter.c:434: the largest summed weight of any 31-bit flank key): every insert returns its key's
+  // running sum and the largest one seen is kept; exact as long as every weight is positive, which the QC filter
+  // guarantees unless a count wrapped its signed 20-bit field (then META_COVSCAN asks the host for cov_max_kernel)
+  int best = INT_MIN;
+  bool nonpositive = false;
   // The host launches this kernel before it knows the counts, into arrays sized from the previous sample (max_keep,
   // max_idx; the coverage table holds 2 max_keep keys at load <= 0.5): nothing is written beyond them, and the host
   // repeats the launch with exact sizes when the counts turn out larger (or the sample had to be redone).
@@ -682,8 +702,10 @@ pack_kernel (const u64 *__restrict__ out_rec, const u32 *__restrict__ out_cnt, c
         bits = ((u64) rec_base<W> (r, k) & 3) | (((u64) rec_len_field<W> (r) & 0x3ff) << 2) | (((u64) cnt & 0xfffff) << 12) |
                (0xffeULL << 32) | (((u64) rec_flag<W> (r) & 7) << 49);
         c0 = rec_ctx0<W> (r, k); c1 = rec_ctx1<W> (r, k);
-        cov_insert (cov_keys, cov_vals, cov_mask, (u32) (c0 & 0x7fffffffULL), (u32) cnt);
-        cov_insert (cov_keys, cov_vals, cov_mask, (u32) (c1 & 0x7fffffffULL), (u32) cnt);
+        const int s0 = cov_insert (cov_keys, cov_vals, cov_mask, (u32) (c0 & 0x7fffffffULL), (u32) cnt);
+        const int s1 = cov_insert (cov_keys, cov_vals, cov_mask, (u32) (c1 & 0x7fffffffULL), (u32) cnt);
+        best = max (best, max (s0, s1));
+        nonpositive = nonpositive || cnt <= 0;
       }
       stage[5 * lane] = c0; stage[5 * lane + 1] = c1; stage[5 * lane + 2] = bits;
       stage[5 * lane + 3] = ~0ULL; // read_offset = -1 (hopo_counter.c:511), loc_ref_id = -1 (:297)
@@ -695,6 +717,9 @@ pack_kernel (const u64 *__restrict__ out_rec, const u32 *__restrict__ out_cnt, c
     for (int t = 0; t < 5; t++) { const u32 w = t * 32 + lane; if (w < 5 * rows) o[w] = stage[w]; }
     __syncwarp ();
   }
+  best = __reduce_max_sync (0xffffffffu, best);
+  if (lane == 0 && best != INT_MIN) atomicMax (cov, best);
+  if (__any_sync (0xffffffffu, nonpositive) && lane == 0) meta_out[META_COVSCAN] = 1;
   for (u32 t = blockIdx.x * 256 + threadIdx.x; t < n_idx; t += stride) {
     const u32 b = bucket_of (ioff, nb, t);
     const u32 start = bkt_start[b], ko = koff[b], u = t - ioff[b];
@@ -705,7 +730,8 @@ pack_kernel (const u64 *__restrict__ out_rec, const u32 *__restrict__ out_cnt, c
   }
 }
 
-// coverage = largest summed weight of any key (empirical_frequency.c:254-277 sorted by frequency, hopo_counter.c:434)
+// coverage = largest summed weight of any key (empirical_frequency.c:254-277 sorted by frequency, hopo_counter.c:434):
+// the scan of the whole table, only needed when a weight was not positive (META_COVSCAN)
 __global__ void __launch_bounds__ (256)
 cov_max_kernel (const u32 *__restrict__ keys, const u32 *__restrict__ vals, u32 n_slots, int *__restrict__ cov)
 {

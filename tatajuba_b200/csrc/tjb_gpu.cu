@@ -99,6 +99,7 @@ struct tjb_ctx {
   // results: pinned, device-mapped arena {elem[keep_cap] (40 B), idx_initial[idx_cap], idx_final[idx_cap]}
   char *h_arena = nullptr, *d_arena = nullptr;
   size_t arena_keep_cap = 0, arena_idx_cap = 0;
+  u32 cov_slots = 0;                        // slots of the coverage table of the last pack launch
   DevBuf out_cnt, out_ii, out_if, cov_tab, out40, idx_i, idx_f, qrows;
   DevBuf hist, ptmp, heads, pos, seg, drec, dcount, keep, kpos, krec, cw, csum, gkeep, gkpos;
   DevBuf uni_a, uni_b;                      // union of query rows
@@ -592,8 +593,8 @@ static int finalise_t (tjb_ctx *ctx, tjb_counter_out *out, int qc_mode)
     CU (cudaMemsetAsync (cov_keys, 0, (size_t) slots * 8, st)); // keys and sums
     if (again) CU (cudaMemcpyAsync (&ctx->d_res->cov, &cov_init, 4, cudaMemcpyHostToDevice, st)); // (the prologue set it for the first launch)
     LAUNCH (K_PACK, (8 * W + 4 + 40) * (size_t) ctx->last_keep + 16 * (size_t) ctx->last_idx,
-            (pack_kernel<W><<<grid * 4, 256, 0, st>>> ((const u64*) ctx->okey.p, (u32*) ctx->out_cnt.p, (u32*) ctx->out_ii.p, (u32*) ctx->out_if.p, ctx->d_bkt_start, ctx->d_bstat, ctx->d_koff, ctx->d_ioff, d_meta, k, o40, oi, of, cov_keys, cov_vals, slots - 1, max_keep, max_idx, cap)));
-    LAUNCH (K_COVMAX, 8 * (size_t) slots, (cov_max_kernel<<<nblk (slots, 256 * 8), 256, 0, st>>> (cov_keys, cov_vals, slots, &ctx->d_res->cov)));
+            (pack_kernel<W><<<grid * 4, 256, 0, st>>> ((const u64*) ctx->okey.p, (u32*) ctx->out_cnt.p, (u32*) ctx->out_ii.p, (u32*) ctx->out_if.p, ctx->d_bkt_start, ctx->d_bstat, ctx->d_koff, ctx->d_ioff, d_meta, k, o40, oi, of, cov_keys, cov_vals, slots - 1, max_keep, max_idx, cap, &ctx->d_res->cov, d_meta)));
+    ctx->cov_slots = slots;
     CU (cudaGetLastError ());
     if (ctx->result_dma) { // one copy of what the previous sample needed (+ 12 %); the rest follows after the counts if it was more
       const size_t sk = ctx->last_keep ? ctx->last_keep + ctx->last_keep / 8 + 256 : 0, si = ctx->last_idx ? ctx->last_idx + ctx->last_idx / 8 + 256 : 0;
@@ -671,6 +672,14 @@ static int finalise_t (tjb_ctx *ctx, tjb_counter_out *out, int qc_mode)
     CU (cudaMemcpyAsync (ctx->h_arena, ctx->out40.p, (size_t) n_keep * 40, cudaMemcpyDeviceToHost, st));
     CU (cudaMemcpyAsync (ctx->h_arena + mk * 40, ctx->idx_i.p, (size_t) n_idx * 4, cudaMemcpyDeviceToHost, st));
     CU (cudaMemcpyAsync (ctx->h_arena + mk * 40 + mi * 4, ctx->idx_f.p, (size_t) n_idx * 4, cudaMemcpyDeviceToHost, st));
+    CU (cudaStreamSynchronize (st));
+  }
+  if (hr->meta[META_COVSCAN]) { // a count wrapped its 20-bit field: the running maximum is not the answer, scan the table
+    const int cov_init2 = INT_MIN;
+    u32 *cov_keys = (u32*) ctx->cov_tab.p, *cov_vals = cov_keys + ctx->cov_slots;
+    CU (cudaMemcpyAsync (&ctx->d_res->cov, &cov_init2, 4, cudaMemcpyHostToDevice, st));
+    LAUNCH (K_COVMAX, 8 * (size_t) ctx->cov_slots, (cov_max_kernel<<<nblk (ctx->cov_slots, 256 * 8), 256, 0, st>>> (cov_keys, cov_vals, ctx->cov_slots, &ctx->d_res->cov)));
+    CU (cudaMemcpyAsync (ctx->h_res, ctx->d_res, sizeof (ResultBlock), cudaMemcpyDeviceToHost, st));
     CU (cudaStreamSynchronize (st));
   }
   tr.mark ("pack");

@@ -473,3 +473,18 @@ def test_gpu_many_samples_two_contexts(ctx, restatement):
         other.close()
     for s, hc in enumerate(res):
         pyoracle.assert_same_boundary(as_boundary(hc), restatement.run_buffer(bufs[s], 25, 4, 5, True), f"sample {s}")
+
+
+def test_gpu_count_field_wraps(ctx, restatement):
+    """more than 2^19 copies of one (context, length): the reference's signed 20-bit count field wraps (hopo_counter.h:40),
+    the wrapped value goes through the QC filter, the group sums and the coverage (the coverage then needs the scan of
+    the whole table instead of the running maximum the pack kernel keeps)"""
+    fwd, rev = b"CGAAAATC", b"GATTTTCG"
+    other = b"TCAAAAAGT"
+    buf = (fwd + b"\n") * 300_100 + (rev + b"\n") * 300_000 + (other + b"\n") * 7 + (bytes(synth.revcomp(np.frombuffer(other, np.uint8)).tobytes()) + b"\n") * 5
+    for rb in (True, False):
+        want = check(ctx, restatement, buf, 2, 4, 1, rb, f"count wrap rb={rb}")
+        cnt = pyoracle.unpack_bits(want.elem["bits"])["count"]
+        assert want.n_raw == 600_112 and (cnt.min() < 0) == rb  # "-b" keeps count > 1 only: the wrapped one is dropped
+    if pyoracle.Reference.available():
+        pyoracle.assert_same_boundary(restatement.run_buffer(buf, 2, 4, 1, True), pyoracle.Reference().run_buffer(buf, 2, 4, 1, True), "count wrap vs reference")
