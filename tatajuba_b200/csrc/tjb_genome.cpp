@@ -76,33 +76,64 @@ extern "C" int tjb_merge_tracts (int32_t n_samples, const int32_t *n_hist, const
   if (!total) return 0;
   if (!location || !base || !mode_len || !names || !out_sample || !out_index || !out_tract_id) return TJB_ERR_ARG;
 
-  // 1. percolate the samples into one vector ordered by location.  Samples are merged one after the other into the
-  //    accumulated vector; on equal locations the NEW sample's row goes first, then ONE accumulated row
-  //    (genome_set.c:274-281), which is not what a stable sort by (location, sample) would give.
+  // 1. percolate the samples into one vector ordered by location.  The reference merges the samples one after the
+  //    other into the accumulated vector; on equal locations the NEW sample's row goes first, then ONE accumulated row
+  //    (genome_set.c:274-281), which is not what a stable sort by (location, sample) would give — and costs
+  //    n_samples x total row moves (0.15 s for 96 samples of 20 K rows).  The rule only ever reorders rows of EQUAL
+  //    location, and what it does to such a group does not depend on the rest: so the rows are first merged by location
+  //    alone (a balanced tree of stable two-way merges, rows of equal location in (sample, index) order), and then
+  //    every group of equal location gets the order the sequential merges would have left it in — the reverse of the
+  //    sample order when every sample has at most one row there (the usual case), the literal interleaving otherwise.
   std::vector<int32_t> acc (total), next (total);
-  int32_t n_acc = n_hist[0];
-  for (int32_t j = 0; j < n_acc; j++) acc[j] = j;
-  for (int32_t s = 1; s < n_samples; s++) {
-    int32_t a = 0, b = first[s], o = 0;
-    const int32_t b_end = first[s + 1];
-    while (a < n_acc && b < b_end) {
-      const int32_t la = location[acc[a]], lb = location[b];
-      if (la > lb) next[o++] = b++;
-      else if (la < lb) next[o++] = acc[a++];
-      else { next[o++] = b++; next[o++] = acc[a++]; }
+  for (int32_t j = 0; j < total; j++) acc[j] = j;
+  {
+    std::vector<int32_t> bound (first.begin (), first.end ()); // run boundaries: one run per sample to start with
+    auto by_location = [&] (int32_t x, int32_t y) { return location[x] < location[y]; };
+    while (bound.size () > 2) {
+      std::vector<int32_t> nb;
+      nb.push_back (0);
+      for (size_t r = 0; r + 1 < bound.size (); r += 2) {
+        const int32_t lo = bound[r], mid = bound[r + 1], hi = r + 2 < bound.size () ? bound[r + 2] : mid;
+        std::merge (acc.begin () + lo, acc.begin () + mid, acc.begin () + mid, acc.begin () + hi, next.begin () + lo, by_location);
+        nb.push_back (hi);
+      }
+      acc.swap (next);
+      bound.swap (nb);
     }
-    while (b < b_end) next[o++] = b++;
-    while (a < n_acc) next[o++] = acc[a++];
-    acc.swap (next);
-    n_acc = o;
   }
+  std::vector<int32_t> sample_of (total);
+  for (int32_t s = 0; s < n_samples; s++) for (int32_t j = first[s]; j < first[s + 1]; j++) sample_of[j] = s;
+  std::vector<int32_t> grp, merged;
+  for (int32_t g0 = 0; g0 < total; ) {
+    int32_t g1 = g0 + 1;
+    bool twice = false; // some sample has two rows at this location
+    while (g1 < total && location[acc[g1]] == location[acc[g0]]) { twice = twice || sample_of[acc[g1]] == sample_of[acc[g1 - 1]]; g1++; }
+    if (!twice) std::reverse (acc.begin () + g0, acc.begin () + g1);
+    else { // the sequential merges, on this group alone: new sample's row, then one accumulated row, while both have some
+      grp.clear ();
+      int32_t i = g0;
+      while (i < g1) {
+        int32_t e = i + 1;
+        while (e < g1 && sample_of[acc[e]] == sample_of[acc[i]]) e++;
+        merged.clear ();
+        int32_t a = 0, b = i;
+        const int32_t na = (int32_t) grp.size ();
+        while (a < na && b < e) { merged.push_back (acc[b++]); merged.push_back (grp[a++]); }
+        while (b < e) merged.push_back (acc[b++]);
+        while (a < na) merged.push_back (grp[a++]);
+        grp.swap (merged);
+        i = e;
+      }
+      std::copy (grp.begin (), grp.end (), acc.begin () + g0);
+    }
+    g0 = g1;
+  }
+  const int32_t n_acc = total;
 
   // 2. tract ids: every row is compared with the FIRST row of the current tract (genome_set.c:208-222)
   const Tables t = {location, base, mode_len, names, name_stride, levenshtein_distance};
   std::vector<uint32_t> tab;
   std::vector<char> yname;
-  std::vector<int32_t> sample_of (total);
-  for (int32_t s = 0; s < n_samples; s++) for (int32_t j = first[s]; j < first[s + 1]; j++) sample_of[j] = s;
   int32_t prev = 0, id = 0;
   for (int32_t i = 0; i < n_acc; i++) {
     if (i && !rows_overlap (t, acc[i], acc[prev], tab, yname)) { id++; prev = i; }

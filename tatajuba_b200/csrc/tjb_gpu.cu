@@ -283,7 +283,8 @@ static int begin_sample (tjb_ctx *ctx, const tjb_opts *opt, size_t n_bytes_hint)
   size_t est = ctx->want_entries ? ctx->want_entries
              : (ctx->last_entries ? ctx->last_entries + ctx->last_entries / 4 + 1024 : estimate_entries (n_bytes_hint, opt->min_tract_size));
   ctx->want_entries = 0;
-  size_t slots = pow2_at_least (3 * est);
+  static const int tab_factor = getenv ("TJB_TABLE_FACTOR") ? atoi (getenv ("TJB_TABLE_FACTOR")) : 3; // slots per expected entry (experiments)
+  size_t slots = pow2_at_least ((size_t) (tab_factor >= 2 && tab_factor <= 64 ? tab_factor : 3) * est);
   if (slots < ((size_t) 1 << 16)) slots = (size_t) 1 << 16;
   if (slots > TJB_MAX_TABLE_SLOTS) slots = TJB_MAX_TABLE_SLOTS;
   ctx->tab_slots = slots;

@@ -50,3 +50,25 @@ def test_surviving_samples():
     assert genome_set.surviving_samples([True, False, True, True]) == {0: 0, 2: 1, 3: 2}
     with pytest.raises(RuntimeError):
         genome_set.surviving_samples([False, False])
+
+
+@pytest.mark.parametrize("seed", range(40, 46))
+def test_merge_many_ties_matches_compiled_reference(reference, seed):
+    """few distinct locations, many samples, several rows of one sample at the same location: the order the sequential
+    two-way merges leave equal locations in (genome_set.c:274-281) is reproduced group by group"""
+    rng = np.random.default_rng(seed)
+    n_samples, k = int(rng.integers(2, 40)), 6
+    tables = []
+    for _ in range(n_samples):
+        n = int(rng.integers(0, 60))
+        loc = np.sort(rng.integers(0, 25, size=n)).astype(np.int32)  # duplicates inside a sample are likely
+        name = np.frombuffer(b"ACGTAC.A.GTCAGT\0", np.uint8)
+        tables.append({"location": loc, "base": rng.integers(0, 2, size=n).astype(np.int32),
+                       "mode_context_length": rng.integers(2, 9, size=n).astype(np.int32), "name": np.tile(name, (n, 1))})
+    if not any(len(t["location"]) for t in tables):
+        tables[0] = {"location": np.array([3], np.int32), "base": np.zeros(1, np.int32), "mode_context_length": np.full(1, 4, np.int32),
+                     "name": np.tile(np.frombuffer(b"ACGTAC.A.GTCAGT\0", np.uint8), (1, 1))}
+    got = genome_set.merge_tracts(tables, 2)
+    want = pyoracle.reference_merge_tracts(tables, 2)
+    for a, b in zip(got, want):
+        assert np.array_equal(a, b)

@@ -1,37 +1,46 @@
 #!/usr/bin/env python
-"""Per-CUDA-source-line instruction counts and stall samples of one kernel from an .ncu-rep (needs -lineinfo and
---import-source on).  usage: python tools/ncu_lines.py REPORT.ncu-rep KERNEL_REGEX [top_n]"""
+"""instructions executed per CUDA source line of a kernel in an .ncu-rep captured with --import-source on
+(ncu -i <rep> --page source --csv --print-source cuda,sass): top lines and sums per line range"""
 import csv
-import io
 import subprocess
 import sys
+from collections import defaultdict
 
-rep, pat = sys.argv[1], sys.argv[2]
-top = int(sys.argv[3]) if len(sys.argv) > 3 else 40
-txt = subprocess.run(["ncu", "-i", rep, "--page", "source", "--print-source", "cuda,sass", "--csv", "--kernel-name",
-                      f"regex:{pat}"], capture_output=True, text=True).stdout
-rows, fname, first_fn, launches = [], "", None, 0
-for r in csv.reader(io.StringIO(txt)):
-    if not r:
-        continue
-    if r[0] == "File Path":
-        fname = r[1].split("/")[-1]
-        continue
-    if r[0] == "Function Name":
-        continue
-    if r[0] == "Kernel Name":
-        launches += 1
-        if launches > 1:
-            break  # first matching launch only
-        continue
-    if r[0] == "Line No" or not r[0].isdigit():
-        continue
-    try:
-        rows.append((fname, int(r[0]), r[1].strip(), int(r[7]), int(r[4])))
-    except (ValueError, IndexError):
-        pass
-tot_i = sum(x[3] for x in rows) or 1
-tot_s = sum(x[4] for x in rows) or 1
-print(f"# {rep} {pat}: {tot_i} warp instructions, {tot_s} stall samples attributed to source lines")
-for f, ln, src, ins, smp in sorted(rows, key=lambda x: -x[3])[:top]:
-    print(f"{100 * ins / tot_i:5.1f}% inst {100 * smp / tot_s:5.1f}% smp  {f}:{ln:<4d} {src[:110]}")
+
+def main():
+    rep = sys.argv[1]
+    top = int(sys.argv[2]) if len(sys.argv) > 2 else 40
+    out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass"], capture_output=True, text=True).stdout
+    rows = list(csv.reader(out.splitlines()))
+    per = defaultdict(lambda: [0, 0, ""])  # (file, line) -> [instructions, samples, text]
+    fname, hdr = None, None
+    for r in rows:
+        if len(r) >= 2 and r[0] == "File Name":
+            fname = r[1].split("/")[-1]
+            continue
+        if len(r) > 7 and r[0] == "Line No":
+            hdr = r
+            ie, ns = hdr.index("Instructions Executed"), hdr.index("# Samples")
+            continue
+        if hdr and len(r) == len(hdr):
+            try:
+                line = int(r[0])
+            except ValueError:
+                continue
+            key = (fname, line)
+            if r[1].strip():
+                per[key][2] = r[1].strip()
+            try:
+                per[key][0] += int(r[ie] or 0)
+                per[key][1] += int(r[ns] or 0)
+            except ValueError:
+                pass
+    total = sum(v[0] for v in per.values())
+    tsamp = sum(v[1] for v in per.values())
+    print(f"total instructions {total}  samples {tsamp}")
+    for (f, l), v in sorted(per.items(), key=lambda kv: -kv[1][0])[:top]:
+        print(f"{100 * v[0] / total:5.1f}% inst {100 * v[1] / max(tsamp, 1):5.1f}% smp  {f}:{l:<4d} {v[2][:110]}")
+
+
+if __name__ == "__main__":
+    main()
