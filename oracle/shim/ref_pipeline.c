@@ -9,6 +9,53 @@
 #include "context_histogram.h"
 #include "tjb_gpu.h" /* only for the layout of tjb_context_table, so that both sides fill the same struct */
 
+/* The reference's read_gff3_from_file() (biomcmc-lib gff3_format.c:197-279) deletes its seq_region vector a second time:
+ * gff3_finalise() takes the pointer BY VALUE, reorder_seqid_charvector_from_pragma() (:531-535, :560-563) deletes the
+ * vector and replaces the callee's copy, and :273 then deletes the caller's stale pointer (--ref_counter on freed memory).
+ * The command line does that once at start-up; a test process that builds many samples does it per call and
+ * eventually decrements a live object that reused the chunk.  The features of the GFF3 are not what this shim pins, so
+ * the file is read with the reference's own building blocks (same calls, same order as :213-271) minus that last delete.
+ * Only what synth.write_reference() writes is handled: pragmas, feature lines, no ##FASTA section. */
+gff3_t new_gff3_t (const char *filename);
+gff3_fields gff3_fields_from_char_line (char *line);
+void add_fields_to_gff3_t (gff3_t g3, gff3_fields gfield);
+void gff3_finalise (gff3_t g3, char_vector seq_region);
+void gff3_generate_seq_vectors (gff3_t g3, hashtable hgs);
+
+static gff3_t shim_read_gff3 (const char *path)
+{
+  FILE *f = fopen (path, "r");
+  if (!f) biomcmc_error ("shim: cannot open %s", path);
+  gff3_t g3 = new_gff3_t (path);
+  char_vector seq_region = new_char_vector (1);
+  int *reg_size = NULL, n_reg = 0;
+  char *line = NULL, name[1024]; size_t cap = 0; ssize_t n;
+  while ((n = getline (&line, &cap, f)) != -1) {
+    while (n > 0 && (line[n - 1] == '\n' || line[n - 1] == '\r')) line[--n] = '\0';
+    if (!n) continue;
+    if (line[0] == '#') {
+      int i1, i2;
+      if (sscanf (line, "##sequence-region %1023s %d %d", name, &i1, &i2) == 3) {
+        char_vector_add_string (seq_region, name);
+        reg_size = (int*) realloc (reg_size, (size_t) (n_reg + 1) * sizeof (int));
+        reg_size[n_reg++] = i2 - 1;
+      }
+      continue;
+    }
+    gff3_fields gf = gff3_fields_from_char_line (line);
+    if (gff3_fields_is_valid (gf)) add_fields_to_gff3_t (g3, gf);
+  }
+  free (line); fclose (f);
+  char_vector_finalise_big (g3->sequence);
+  hashtable hgs = new_hashtable (n_reg);
+  for (int i = 0; i < n_reg; i++) insert_hashtable (hgs, seq_region->string[i], reg_size[i]);
+  gff3_finalise (g3, seq_region); /* releases seq_region (see above) */
+  gff3_generate_seq_vectors (g3, hgs);
+  del_hashtable (hgs);
+  free (reg_size);
+  return g3;
+}
+
 typedef struct {
   int n_mapped;            /* hc->n_elem - hc->ref_start */
   void *elem;              /* malloc'ed copy, 40 bytes each */
@@ -22,10 +69,8 @@ ref_pipeline_run (const char *buf, size_t n_bytes, const char *fasta, const char
   tatajuba_options_t opt;
   memset (&opt, 0, sizeof (opt));
   memset (out, 0, sizeof (*out));
-  opt.gff = read_gff3_from_file (gff);
-  alignment aln = read_fasta_alignment_from_file ((char*) fasta, false);
-  add_fasta_to_gff3 (opt.gff, aln->taxlabel, aln->character);
-  del_alignment (aln);
+  opt.gff = shim_read_gff3 (gff);
+  /* (main.c:133-137 also attaches the fasta's DNA to the GFF3; nothing on this path reads it) */
   opt.reference_fasta_filename = (char*) fasta;
   opt.outdir = (char*) ".";
   opt.paired_end = false; opt.remove_biased = remove_biased; opt.save_vcf = false;

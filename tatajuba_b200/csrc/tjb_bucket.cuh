@@ -284,10 +284,11 @@ aggregate_kernel (const u64 *__restrict__ recs, unsigned long long *__restrict__
 #pragma unroll
     for (int u = 0; u < AGG_UNROLL; u++) {
       if (seen[u] < 0) continue;
-      if (seen[u] == 1) { red_add_global (tab.cnt + slot[u], flag_weight (r[u].w[0])); continue; } // the common case at depth
+      if (seen[u] == 1) { table_count_one (tab, slot[u], r[u].w[0]); continue; } // the common case at depth
       Rec<W> key = r[u];
       key.w[0] &= ~3ULL;
-      const int res = table_add<W> (tab, key, flag_weight (r[u].w[0]));
+      const int res = seen[u] == 2 ? table_add_from<W> (tab, key, flag_weight (r[u].w[0]), (slot[u] + 1) & tab.mask, -1)
+                                   : table_add_from<W> (tab, key, flag_weight (r[u].w[0]), slot[u], 0);
       if (res != TAB_ADDED) atomicAdd (&bin_hist[rec_bin<W> (key, k, F)], 1u); // a new entry, or a record of the overflow list
       n_new += res == TAB_NEW;
       if (res == TAB_DEFER) {

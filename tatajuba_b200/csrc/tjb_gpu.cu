@@ -283,8 +283,12 @@ static int begin_sample (tjb_ctx *ctx, const tjb_opts *opt, size_t n_bytes_hint)
   size_t est = ctx->want_entries ? ctx->want_entries
              : (ctx->last_entries ? ctx->last_entries + ctx->last_entries / 4 + 1024 : estimate_entries (n_bytes_hint, opt->min_tract_size));
   ctx->want_entries = 0;
-  static const int tab_factor = getenv ("TJB_TABLE_FACTOR") ? atoi (getenv ("TJB_TABLE_FACTOR")) : 3; // slots per expected entry (experiments)
-  size_t slots = pow2_at_least ((size_t) (tab_factor >= 2 && tab_factor <= 64 ? tab_factor : 3) * est);
+  // slots per expected entry: collisions make the lanes of a warp probe in turns, so a table that stays L2 resident is
+  // kept sparse (measured at 58 K entries: 3x: aggregate 79 us + partition 12; 8x: 60 + 19; 16x: 57 + 22); a large one
+  // is not: its memset and the partition's walk grow with the slots
+  static const int tab_factor = getenv ("TJB_TABLE_FACTOR") ? atoi (getenv ("TJB_TABLE_FACTOR")) : 0; // experiments
+  const size_t factor = tab_factor >= 2 && tab_factor <= 64 ? (size_t) tab_factor : (est <= ((size_t) 1 << 18) ? 8 : 3);
+  size_t slots = pow2_at_least (factor * est);
   if (slots < ((size_t) 1 << 16)) slots = (size_t) 1 << 16;
   if (slots > TJB_MAX_TABLE_SLOTS) slots = TJB_MAX_TABLE_SLOTS;
   ctx->tab_slots = slots;

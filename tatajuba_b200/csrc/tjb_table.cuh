@@ -48,14 +48,19 @@ __device__ __forceinline__ unsigned long long cas_global (unsigned long long *p,
 }
 
 // weight of one raw observation: flag 1 = seen on the forward strand, 2 = reverse complement (hopo_counter.c:237, 245)
-__device__ __forceinline__ unsigned long long flag_weight (u64 w0) { return (w0 & 1) ? 1ULL : (1ULL << 32); }
+__device__ __forceinline__ unsigned long long flag_weight (u64 w0) { return 1ULL << (((u32) w0 & 2u) << 4); }
+__device__ __forceinline__ void red_add_global32 (u32 *p, u32 v)
+{ asm volatile ("red.global.add.u32 [%0], %1;" :: "l"(p), "r"(v) : "memory"); }
+// one observation onto a slot that holds its key: +1 on the strand's half of the count word
+__device__ __forceinline__ void table_count_one (const AggTable &t, u32 slot, u64 w0)
+{ red_add_global32 (reinterpret_cast<u32*> (t.cnt + slot) + (((u32) w0 >> 1) & 1u), 1u); }
 
 template <int W> __device__ __forceinline__ u32 key_hash (const Rec<W> &r) // flag bits do not take part
 {
-  u32 h = (u32) (r.w[0] >> 2) * 0x9E3779B1u ^ (u32) (r.w[0] >> 34) * 0x85EBCA6Bu ^ (u32) r.w[1] * 0xC2B2AE35u ^ (u32) (r.w[1] >> 32) * 0x27D4EB2Fu;
-  if (W == 3) h ^= (u32) r.w[W - 1] * 0x165667B1u ^ (u32) (r.w[W - 1] >> 32) * 0x9E3779B1u;
-  h ^= h >> 15; h *= 0x2C1B3C6Du; h ^= h >> 13;
-  return h;
+  const u64 a = (r.w[0] >> 2) * 0x9E3779B97F4A7C15ULL, b = r.w[1] * 0xC2B2AE3D27D4EB4FULL;
+  u32 h = (u32) (a >> 32) ^ (u32) (b >> 32) ^ (u32) b;
+  if (W == 3) { const u64 c = r.w[W - 1] * 0x165667B19E3779F9ULL; h ^= (u32) (c >> 32) ^ (u32) c; }
+  return h ^ (h >> 15);
 }
 
 // what a slot's key reads as: 0 = nothing there (yet), 1 = `key`, 2 = something else (another key, or a key half written)
@@ -88,12 +93,12 @@ enum { TAB_ADDED = 0, TAB_NEW = 1, TAB_DEFER = 2 };
 // key: record words with the flag bits cleared.  Returns TAB_NEW when this call created the entry (the caller counts
 // entries and bins them), TAB_DEFER when the observation has to go to the overflow list.  One copy of the code per
 // kernel (it is called from several places of the scan, and the probe loop must not be unrolled into each of them).
-template <int W> __device__ __noinline__ int table_add (AggTable t, Rec<W> key, unsigned long long weight)
+template <int W> __device__ __noinline__ int table_add_from (AggTable t, Rec<W> key, unsigned long long weight, u32 slot, int seen)
 {
-  u32 slot = key_hash<W> (key) & t.mask;
+  // slot / seen: where the caller's own look at the home slot left off (seen < 0: nothing looked at yet)
 #pragma unroll 1
   for (int p = 0; p < TAB_MAXPROBE; p++, slot = (slot + 1) & t.mask) {
-    int seen = table_probe<W> (t, slot, key);
+    if (seen < 0) seen = table_probe<W> (t, slot, key);
     if (seen == 0) {
       if (cas_global (t.cnt + slot, 0ULL, weight) == 0ULL) {
         if (W == 2) __stcg (reinterpret_cast<ulonglong2*> (t.keys) + slot, make_ulonglong2 (key.w[0], key.w[1]));
@@ -106,10 +111,14 @@ template <int W> __device__ __noinline__ int table_add (AggTable t, Rec<W> key, 
       // claimed by somebody else a moment ago: its key is on its way (the claimer stores it right after its CAS).  Look
       // again a few times (bounded: nobody is waited for indefinitely) before giving the observation to the overflow list;
       // when a kernel adds all records of a sample at once, the ~depth copies of a new key arrive together
+      seen = table_probe<W> (t, slot, key);
       for (int again = 0; again < TAB_RELOOK && seen == 0; again++) { __nanosleep (64); seen = table_probe<W> (t, slot, key); }
       if (seen == 0) return TAB_DEFER;
     }
     if (seen == 1) { red_add_global (t.cnt + slot, weight); return TAB_ADDED; }
+    seen = -1;
   }
   return TAB_DEFER;
 }
+template <int W> __device__ __forceinline__ int table_add (const AggTable &t, const Rec<W> &key, unsigned long long weight)
+{ return table_add_from<W> (t, key, weight, key_hash<W> (key) & t.mask, -1); }

@@ -158,22 +158,29 @@ def nrun_reads(k=25, seed=17, n_reads=400, p_run=0.03, lead_tract=True):
     return reads
 
 
-def write_reference(fasta_path, gff_path, genome, contig="chr1", gene_every=1200, gene_len=900):
+def write_reference(fasta_path, gff_path, genome, contig="chr1", gene_every=1200, gene_len=900, extra_contig=3000):
     """reference genome as FASTA (60 columns) and a GFF3 with one gene + CDS every `gene_every` bases (SURVEY.md §8(d)
-    config C1; reader rules: biomcmc-lib gff3_format.c:197-279)"""
+    config C1; reader rules: biomcmc-lib gff3_format.c:197-279), followed by a second, short contig of random bases
+    (more than one reference sequence, like a draft assembly)."""
     g = genome.tobytes() if hasattr(genome, "tobytes") else bytes(genome)
+    contigs = [(contig, g)]
+    if extra_contig:
+        contigs.append((contig + "_b", random_genome(extra_contig, seed=len(g) % 9973 + 17).tobytes()))
     with open(fasta_path, "wb") as f:
-        f.write(b">" + contig.encode() + b"\n")
-        for i in range(0, len(g), 60):
-            f.write(g[i:i + 60] + b"\n")
+        for name, seq in contigs:
+            f.write(b">" + name.encode() + b"\n")
+            for i in range(0, len(seq), 60):
+                f.write(seq[i:i + 60] + b"\n")
     with open(gff_path, "w") as f:
         f.write("##gff-version 3\n")
-        f.write(f"##sequence-region {contig} 1 {len(g)}\n")
-        f.write(f"{contig}\tsynth\tregion\t1\t{len(g)}\t.\t+\t.\tID={contig}:1..{len(g)};Name={contig}\n")
+        for name, seq in contigs:
+            f.write(f"##sequence-region {name} 1 {len(seq)}\n")
         n = 0
-        for start in range(101, len(g) - gene_len, gene_every):
-            n += 1
-            strand = "+" if n % 2 else "-"
-            f.write(f"{contig}\tsynth\tgene\t{start}\t{start + gene_len - 1}\t.\t{strand}\t.\tID=gene-{n:05d};Name=g{n}\n")
-            f.write(f"{contig}\tsynth\tCDS\t{start}\t{start + gene_len - 1}\t.\t{strand}\t0\tID=cds-{n:05d};Parent=gene-{n:05d};"
-                    f"product=hypothetical protein {n}\n")
+        for name, seq in contigs:
+            f.write(f"{name}\tsynth\tregion\t1\t{len(seq)}\t.\t+\t.\tID={name}:1..{len(seq)};Name={name}\n")
+            for start in range(101, len(seq) - gene_len, gene_every):
+                n += 1
+                strand = "+" if n % 2 else "-"
+                f.write(f"{name}\tsynth\tgene\t{start}\t{start + gene_len - 1}\t.\t{strand}\t.\tID=gene-{n:05d};Name=g{n}\n")
+                f.write(f"{name}\tsynth\tCDS\t{start}\t{start + gene_len - 1}\t.\t{strand}\t0\tID=cds-{n:05d};Parent=gene-{n:05d};"
+                        f"product=hypothetical protein {n}\n")
