@@ -249,9 +249,11 @@ plan_big_kernel (const u32 *__restrict__ bin_hist, int F, int bshift, unsigned l
 // --------------------------------------------------------------------------------------- aggregate -------
 // The scan's records (one per observed tract) are added to the aggregation table (tjb_table.cuh): the run-length count
 // of hopo_counter.c:352-365 without a sort.  One record per thread and round, AGG_UNROLL rounds in flight; a thread
-// that creates an entry also counts it for the partition plan.
+// that creates an entry also counts it for the partition plan.  (Measured, config 2 / config 5 (k=32, 39 M records on
+// 234 K keys): 1 round in flight 57 / 623 us, 2: 55 / 628, 4: 62 / 1023 — more probes in flight only add reductions
+// queueing on the same count words.)
 #ifndef AGG_UNROLL
-#define AGG_UNROLL 4
+#define AGG_UNROLL 2
 #endif
 template <int W>
 __global__ void __launch_bounds__ (256)
