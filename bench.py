@@ -544,16 +544,24 @@ def c4_leg(ctxs, rank, world, timed, all_ranks_ok, args):
     resident = [p.cuda() for p in pinned]  # 8.2 GB at one GPU
     torch.cuda.synchronize()
 
+    stages = {}
+
     def job(from_host=True):
         rows = {}
+        t0 = time.perf_counter()
 
         def done(c, i, hc):  # on the context's thread, before it counts its next sample
             rows[mine[i]] = genome_set.query_rows_device(c, hc).clone()
             return hc.n_idx
         one = (lambda c, i: c.count_host(pinned[i], opt)) if from_host else (lambda c, i: c.count_device(resident[i].data_ptr(), resident[i].numel(), opt))
         genome_set.count_samples(ctxs, len(bufs), one, on_done=done)
+        torch.cuda.synchronize()
+        t1 = time.perf_counter()
         all_rows, sizes = genome_set.allgather_tables_device(rows, C4_SAMPLES)
+        torch.cuda.synchronize()
+        t2 = time.perf_counter()
         uni, idx = genome_set.union_queries_device(ctx, all_rows, K)
+        t3 = time.perf_counter()
         n_concat = 0
         if rank == 0:  # stand-in post-mapper tables: one histogram per union row a sample has, at the row's rank as location
             tables, off, idx_h = [], 0, idx.cpu().numpy()
@@ -563,6 +571,9 @@ def c4_leg(ctxs, rank, world, timed, all_ranks_ok, args):
                 tables.append({"location": loc, "base": np.zeros(n, np.int32), "mode_context_length": np.full(n, 4, np.int32),
                                "name": np.zeros((n, 1), np.uint8)})
             n_concat = len(genome_set.merge_tracts(tables, 2)[0])
+        t4 = time.perf_counter()
+        stages[from_host] = {"count_samples": (t1 - t0) * 1e3, "allgather": (t2 - t1) * 1e3, "union": (t3 - t2) * 1e3,
+                             "merge_tracts_rank0": (t4 - t3) * 1e3}
         return int(uni.shape[0]), int(sum(sizes)), n_concat
     best_by_mode = {}
     for from_host in (False, True):
@@ -577,7 +588,8 @@ def c4_leg(ctxs, rank, world, timed, all_ranks_ok, args):
             "scaling": "strong (the 96 samples are dealt to the ranks)", "ms": best, "value": bases_total / (best * 1e-3), "unit": "bases/s",
             "samples_per_rank": len(mine), "contexts_per_gpu": len(ctxs), "bases_total": bases_total, "parity": parity,
             "inside": "count of every sample (reads resident in HBM), query rows on the device, allgather, union of mapper queries, merge of tract ids (rank 0)",
-            "from_host": {"ms": best_by_mode[True], "value": bases_total / (best_by_mode[True] * 1e-3), "unit": "bases/s",
+            "stages_ms": {k: round(v, 2) for k, v in stages[False].items()},
+            "from_host": {"ms": best_by_mode[True], "stages_ms": {k: round(v, 2) for k, v in stages[True].items()}, "value": bases_total / (best_by_mode[True] * 1e-3), "unit": "bases/s",
                           "note": "the same with the reads of every sample in pinned host memory: H2D inside"},
             "n_union": out[0], "rows": out[1], "merged_rows": out[2]}
 

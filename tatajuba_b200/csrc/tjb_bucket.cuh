@@ -426,6 +426,7 @@ wbucket_reduce_kernel (const u64 *__restrict__ wkey, const unsigned long long *_
 #pragma unroll
         for (int j = 0; j < W; j++) { s_w[j * BK_CAP + i] = r.w[j]; d[j] |= r.w[j] ^ f.w[j]; }
         s_perm0[i] = (unsigned short) i;
+        s_val[i] = 0; // rank counters of the comparison sort (free until the QC step)
       }
 #pragma unroll
       for (int j = 0; j < W; j++) {
@@ -437,20 +438,35 @@ wbucket_reduce_kernel (const u64 *__restrict__ wkey, const unsigned long long *_
     // ---- sort the records, ascending in `cur` (equal keys end up next to each other) ---------------------------
     unsigned short *cur = s_perm0, *nxt = s_perm1;
     if (n <= BK_RANKSORT_MAX) {
-      // few records (the usual case at high depth): rank by comparison, one record per thread, broadcast reads; equal
-      // keys are ranked by their index
+      // few records (the usual case at high depth): rank by comparison, one record per thread, broadcast reads.  The
+      // comparison is a 128-bit subtraction whose final borrow says "y < x" (W = 2: the flag bits of a weighted key are
+      // zero, so (w1, w0) as one number is the reference's order); equal keys (a key that arrived in two records) get
+      // consecutive ranks from a counter at their common rank, in any order: their weights are added below
       if ((u32) tid < n) {
-        Rec<W> x;
-#pragma unroll
-        for (int j = 0; j < W; j++) x.w[j] = s_w[j * BK_CAP + tid];
         u32 less = 0;
-        for (u32 o = 0; o < n; o++) {
-          Rec<W> y;
+        if (W == 2) {
+          const u64 x0 = s_w[tid], x1 = s_w[BK_CAP + tid];
+          const u32 x0l = (u32) x0, x0h = (u32) (x0 >> 32), x1l = (u32) x1, x1h = (u32) (x1 >> 32);
+#pragma unroll 4
+          for (u32 o = 0; o < n; o++) {
+            const u64 y0 = s_w[o], y1 = s_w[BK_CAP + o];
+            u32 borrow;
+            asm ("{\n .reg .u32 t;\n sub.cc.u32 t, %1, %5;\n subc.cc.u32 t, %2, %6;\n subc.cc.u32 t, %3, %7;\n subc.cc.u32 t, %4, %8;\n subc.u32 %0, 0, 0;\n}"
+                 : "=r"(borrow) : "r"((u32) y0), "r"((u32) (y0 >> 32)), "r"((u32) y1), "r"((u32) (y1 >> 32)), "r"(x0l), "r"(x0h), "r"(x1l), "r"(x1h));
+            less -= borrow; // 0xffffffff when y < x
+          }
+        } else {
+          Rec<W> x;
 #pragma unroll
-          for (int j = 0; j < W; j++) y.w[j] = s_w[j * BK_CAP + o];
-          less += rec_greater<W> (x, y) || (o < (u32) tid && same_tract<W> (x, y));
+          for (int j = 0; j < W; j++) x.w[j] = s_w[j * BK_CAP + tid];
+          for (u32 o = 0; o < n; o++) {
+            Rec<W> y;
+#pragma unroll
+            for (int j = 0; j < W; j++) y.w[j] = s_w[j * BK_CAP + o];
+            less += rec_greater<W> (x, y);
+          }
         }
-        nxt[less] = (unsigned short) tid;
+        nxt[less + atomicAdd (&s_val[less], 1u)] = (unsigned short) tid; // s_val[0 .. n) was zeroed while the bucket was loaded
       }
       __syncthreads ();
       unsigned short *t = cur; cur = nxt; nxt = t;

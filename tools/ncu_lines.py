@@ -12,9 +12,15 @@ def main():
     top = int(sys.argv[2]) if len(sys.argv) > 2 else 40
     out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv", "--print-source", "cuda,sass"], capture_output=True, text=True).stdout
     rows = list(csv.reader(out.splitlines()))
+    only = sys.argv[3] if len(sys.argv) > 3 else None  # substring of the kernel name
     per = defaultdict(lambda: [0, 0, ""])  # (file, line) -> [instructions, samples, text]
-    fname, hdr = None, None
+    fname, hdr, kernel = None, None, ""
     for r in rows:
+        if len(r) >= 2 and r[0] in ("Kernel Name", "Function Name"):
+            kernel = r[1]
+            continue
+        if only and only not in kernel:
+            continue
         if len(r) >= 2 and r[0] == "File Name":
             fname = r[1].split("/")[-1]
             continue

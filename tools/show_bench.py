@@ -3,7 +3,7 @@
 import json
 import sys
 
-d = json.load(open(sys.argv[1]))
+d = json.loads([l for l in open(sys.argv[1]) if l.startswith("{")][-1])
 kern = lambda k: " ".join(f"{n.replace('_kernel', '')}={v['us']}" for n, v in k.items())  # noqa: E731
 print(f"step {d['ms_per_step']:.3f} ms  value {d['value'] / 1e9:.0f} G  two ctx {d['config'].get('two_contexts')}")
 print(f"e2e {d['e2e']['ms_per_step']:.2f} ms {d['e2e']['value'] / 1e9:.1f} G  plain {d['e2e']['transfer']['plain']['ms_per_step']:.2f}  h2d {d['e2e']['h2d_bytes_per_step']}")
