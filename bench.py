@@ -563,10 +563,10 @@ def c4_leg(ctxs, rank, world, timed, all_ranks_ok, args):
         uni, idx = genome_set.union_queries_device(ctx, all_rows, K)
         t3 = time.perf_counter()
         n_concat = 0
-        if rank == 0:  # stand-in post-mapper tables: one histogram per union row a sample has, at the row's rank as location
+        if rank == 0:  # stand-in post-mapper tables: one histogram per union row a sample has, located by the row's rank
             tables, off, idx_h = [], 0, idx.cpu().numpy()
             for n in sizes:
-                loc = np.sort(idx_h[off:off + n]).astype(np.int32)
+                loc = (np.sort(idx_h[off:off + n]) * 8).astype(np.int32)  # tracts 8 bp apart: neighbours are different tracts
                 off += n
                 tables.append({"location": loc, "base": np.zeros(n, np.int32), "mode_context_length": np.full(n, 4, np.int32),
                                "name": np.zeros((n, 1), np.uint8)})

@@ -8,6 +8,7 @@
 #include <algorithm>
 #include <cstdlib>
 #include <cstring>
+#include <memory>
 #include <string>
 #include <utility>
 #include <vector>
@@ -81,40 +82,68 @@ extern "C" int tjb_merge_tracts (int32_t n_samples, const int32_t *n_hist, const
   //    (genome_set.c:274-281), which is not what a stable sort by (location, sample) would give — and costs
   //    n_samples x total row moves (0.15 s for 96 samples of 20 K rows).  The rule only ever reorders rows of EQUAL
   //    location, and what it does to such a group does not depend on the rest: so the rows are first merged by location
-  //    alone (a balanced tree of stable two-way merges, rows of equal location in (sample, index) order), and then
+  //    alone (a stable radix sort: rows of equal location stay in (sample, index) order), and then
   //    every group of equal location gets the order the sequential merges would have left it in — the reverse of the
   //    sample order when every sample has at most one row there (the usual case), the literal interleaving otherwise.
-  std::vector<int32_t> acc (total), next (total);
-  for (int32_t j = 0; j < total; j++) acc[j] = j;
+  //    Rows carry their location and sample along, so that nothing after the sort reads the input tables at random.
+  struct Row { uint32_t loc; int32_t sample, row, pad; };
+  std::unique_ptr<Row[]> acc (new Row[total]), other (new Row[total]);
   {
-    std::vector<int32_t> bound (first.begin (), first.end ()); // run boundaries: one run per sample to start with
-    auto by_location = [&] (int32_t x, int32_t y) { return location[x] < location[y]; };
-    while (bound.size () > 2) {
-      std::vector<int32_t> nb;
-      nb.push_back (0);
-      for (size_t r = 0; r + 1 < bound.size (); r += 2) {
-        const int32_t lo = bound[r], mid = bound[r + 1], hi = r + 2 < bound.size () ? bound[r + 2] : mid;
-        std::merge (acc.begin () + lo, acc.begin () + mid, acc.begin () + mid, acc.begin () + hi, next.begin () + lo, by_location);
-        nb.push_back (hi);
+    uint32_t differ = 0; // locations may be negative (nothing forbids it): biased to unsigned for the sort
+    const uint32_t loc0 = (uint32_t) location[0] ^ 0x80000000u;
+    uint32_t lo = loc0, hi = loc0;
+    bool ascending = true; // within every sample, as the reference's merge expects (genome_set.c:274)
+    for (int32_t s = 0; s < n_samples; s++) for (int32_t j = first[s]; j < first[s + 1]; j++) {
+      acc[j].loc = (uint32_t) location[j] ^ 0x80000000u; acc[j].sample = s; acc[j].row = j; acc[j].pad = 0;
+      differ |= acc[j].loc ^ loc0;
+      lo = std::min (lo, acc[j].loc); hi = std::max (hi, acc[j].loc);
+      if (j > first[s] && acc[j].loc < acc[j - 1].loc) ascending = false;
+    }
+    if (ascending && (uint64_t) (hi - lo) <= 8ull * (uint64_t) total + 1024) {
+      // locations dense enough (many samples of one genome): one counting sort by location, done block of locations by
+      // block of locations with one cursor per sample, so that the part of the output being written (~128 KB) stays in
+      // cache (sample after sample over the whole range would touch every line of the output once per sample)
+      std::vector<uint32_t> start ((size_t) (hi - lo) + 2, 0u);
+      for (int32_t j = 0; j < total; j++) start[acc[j].loc - lo + 1]++;
+      for (size_t c = 1; c < start.size (); c++) start[c] += start[c - 1];
+      std::vector<int32_t> cursor (first.begin (), first.end () - 1);
+      const uint64_t range = (uint64_t) (hi - lo) + 1;
+      const uint64_t block = std::max<uint64_t> (1, range * 8192 / (uint64_t) total);
+      for (uint64_t b0 = 0; b0 < range; b0 += block) {
+        const uint64_t limit = (uint64_t) lo + std::min (range, b0 + block); // exclusive
+        for (int32_t s = 0; s < n_samples; s++) {
+          int32_t j = cursor[s];
+          for (; j < first[s + 1] && (uint64_t) acc[j].loc < limit; j++) other[start[acc[j].loc - lo]++] = acc[j];
+          cursor[s] = j;
+        }
       }
-      acc.swap (next);
-      bound.swap (nb);
+      acc.swap (other);
+    } else {
+      const int DIGIT = 8;
+      const uint32_t digit_mask = (1u << DIGIT) - 1;
+      std::vector<uint32_t> start ((size_t) 1 << DIGIT);
+      for (int shift = 0; shift < 32 && (differ >> shift); shift += DIGIT) { // digits above the highest differing bit are equal
+        std::fill (start.begin (), start.end (), 0u);
+        for (int32_t j = 0; j < total; j++) start[(acc[j].loc >> shift) & digit_mask]++;
+        uint32_t run = 0;
+        for (auto &c : start) { const uint32_t n = c; c = run; run += n; }
+        for (int32_t j = 0; j < total; j++) other[start[(acc[j].loc >> shift) & digit_mask]++] = acc[j];
+        acc.swap (other);
+      }
     }
   }
-  std::vector<int32_t> sample_of (total);
-  for (int32_t s = 0; s < n_samples; s++) for (int32_t j = first[s]; j < first[s + 1]; j++) sample_of[j] = s;
-  std::vector<int32_t> grp, merged;
+  std::vector<Row> grp, merged;
   for (int32_t g0 = 0; g0 < total; ) {
     int32_t g1 = g0 + 1;
     bool twice = false; // some sample has two rows at this location
-    while (g1 < total && location[acc[g1]] == location[acc[g0]]) { twice = twice || sample_of[acc[g1]] == sample_of[acc[g1 - 1]]; g1++; }
-    if (!twice) std::reverse (acc.begin () + g0, acc.begin () + g1);
+    while (g1 < total && acc[g1].loc == acc[g0].loc) { twice = twice || acc[g1].sample == acc[g1 - 1].sample; g1++; }
+    if (!twice) std::reverse (acc.get () + g0, acc.get () + g1);
     else { // the sequential merges, on this group alone: new sample's row, then one accumulated row, while both have some
       grp.clear ();
       int32_t i = g0;
       while (i < g1) {
         int32_t e = i + 1;
-        while (e < g1 && sample_of[acc[e]] == sample_of[acc[i]]) e++;
+        while (e < g1 && acc[e].sample == acc[i].sample) e++;
         merged.clear ();
         int32_t a = 0, b = i;
         const int32_t na = (int32_t) grp.size ();
@@ -124,24 +153,23 @@ extern "C" int tjb_merge_tracts (int32_t n_samples, const int32_t *n_hist, const
         grp.swap (merged);
         i = e;
       }
-      std::copy (grp.begin (), grp.end (), acc.begin () + g0);
+      std::copy (grp.begin (), grp.end (), acc.get () + g0);
     }
     g0 = g1;
   }
-  const int32_t n_acc = total;
 
   // 2. tract ids: every row is compared with the FIRST row of the current tract (genome_set.c:208-222)
   const Tables t = {location, base, mode_len, names, name_stride, levenshtein_distance};
   std::vector<uint32_t> tab;
   std::vector<char> yname;
   int32_t prev = 0, id = 0;
-  for (int32_t i = 0; i < n_acc; i++) {
-    if (i && !rows_overlap (t, acc[i], acc[prev], tab, yname)) { id++; prev = i; }
-    out_sample[i] = sample_of[acc[i]];
-    out_index[i] = acc[i] - first[sample_of[acc[i]]];
+  for (int32_t i = 0; i < total; i++) {
+    if (i && acc[i].loc != acc[prev].loc && !rows_overlap (t, acc[i].row, acc[prev].row, tab, yname)) { id++; prev = i; }
+    out_sample[i] = acc[i].sample;
+    out_index[i] = acc[i].row - first[acc[i].sample];
     out_tract_id[i] = id;
   }
-  return n_acc;
+  return total;
 }
 
 // ---------------------------------------------------------------------------------------------------------

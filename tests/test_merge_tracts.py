@@ -72,3 +72,20 @@ def test_merge_many_ties_matches_compiled_reference(reference, seed):
     want = pyoracle.reference_merge_tracts(tables, 2)
     for a, b in zip(got, want):
         assert np.array_equal(a, b)
+
+
+@pytest.mark.parametrize("seed", range(40, 44))
+def test_merge_sparse_locations_matches_compiled_reference(reference, seed):
+    """locations spread over far more positions than there are rows (few samples of a large genome): the library sorts
+    them by radix passes instead of one counting sort; same result as the reference's sequential merges"""
+    rng = np.random.default_rng(seed)
+    tables = make_tables(seed, int(rng.integers(2, 7)), int(rng.integers(50, 300)))
+    for t in tables:
+        t["location"] = (t["location"].astype(np.int64) * 4001 % (1 << 30)).astype(np.int32)
+        order = np.argsort(t["location"], kind="stable")
+        for key in t:
+            t[key] = np.ascontiguousarray(t[key][order])
+    got = genome_set.merge_tracts(tables, 2)
+    want = pyoracle.reference_merge_tracts(tables, 2)
+    for a, b in zip(got, want):
+        assert np.array_equal(a, b)
