@@ -218,6 +218,16 @@ tjb_reader *tjb_reader_open (const char *path);
 int64_t tjb_reader_fill (tjb_reader *r, uint8_t *dst, size_t cap, int64_t *n_reads, int64_t *n_bases);
 void tjb_reader_close (tjb_reader *r);
 
+/* the gzip stream under tjb_reader for regular .gz files (replaces gzopen / gzread of the reference's reader,
+ * src/hopo_counter.c:141-153): our own inflate on a producer thread.  tjb_gz_open() returns NULL for anything that is
+ * not a regular file starting with a gzip member (the reader then uses zlib, which also reads plain text);
+ * tjb_gz_next() hands out the next decoded piece (valid until the following call): bytes, 0 at the end of the file,
+ * TJB_ERR_IO for corrupt or truncated data or a CRC-32 / length mismatch, after everything decodable was delivered. */
+typedef struct tjb_gzstream tjb_gzstream;
+tjb_gzstream *tjb_gz_open (const char *path);
+int64_t tjb_gz_next (tjb_gzstream *g, const uint8_t **data);
+void tjb_gz_close (tjb_gzstream *g);
+
 #ifdef __cplusplus
 }
 #endif
