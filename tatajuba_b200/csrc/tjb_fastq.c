@@ -10,7 +10,9 @@
  *     (the parser returns -2 and the reference's loop stops on any negative value).
  * Instead of handing one read at a time to a scalar scan, reads are packed as "SEQ\n" into large chunks
  * (pinned, double buffered by the caller) so that the device scans them with '\n' as the read separator.
- * This is our own implementation (block-wise memchr over a 1 MiB inflate buffer), not the klib macros.
+ * This is our own implementation (block-wise memchr over the decoded pieces), not the klib macros.  Regular .gz files
+ * are inflated by tjb_inflate.c (own decoder on a producer thread); everything else (plain text, pipes) is read through
+ * zlib's gzread() like the reference does.  TJB_ZLIB=1 in the environment sends .gz files through zlib as well.
  */
 #include <stdlib.h>
 #include <string.h>
@@ -20,8 +22,10 @@
 #define TJB_IOBUF (1u << 20)
 
 struct tjb_reader {
-  gzFile fp;
-  uint8_t *io;           /* inflate buffer */
+  gzFile fp;             /* zlib path ... */
+  tjb_gzstream *gz;      /* ... or our own inflate: io then points at the stream's current piece */
+  uint8_t *io_own;       /* buffer of the zlib path */
+  const uint8_t *io;     /* decoded bytes being parsed */
   size_t io_pos, io_end;
   int io_eof;
   int pending_header;    /* a header char ('>' / '@') was consumed while reading sequence lines */
@@ -36,7 +40,16 @@ struct tjb_reader {
 static int refill (tjb_reader *r)
 {
   if (r->io_eof) return 0;
-  int got = gzread (r->fp, r->io, TJB_IOBUF);
+  if (r->gz) {
+    const int64_t n = tjb_gz_next (r->gz, &r->io);
+    r->io_pos = 0;
+    /* corrupt or truncated data: what could be decoded has been delivered, the file ends here (gzread() < 0) */
+    if (n <= 0) { r->io_end = 0; r->io_eof = 1; return 0; }
+    r->io_end = (size_t) n;
+    return 1;
+  }
+  int got = gzread (r->fp, r->io_own, TJB_IOBUF);
+  r->io = r->io_own;
   r->io_pos = 0;
   if (got <= 0) { r->io_end = 0; r->io_eof = 1; return 0; }
   r->io_end = (size_t) got;
@@ -67,9 +80,9 @@ static int take_line (tjb_reader *r, uint8_t **buf, size_t *len, size_t *cap)
 {
   for (;;) {
     if (r->io_pos >= r->io_end && !refill (r)) break;
-    uint8_t *p = r->io + r->io_pos;
+    const uint8_t *p = r->io + r->io_pos;
     size_t avail = r->io_end - r->io_pos;
-    uint8_t *nl = (uint8_t*) memchr (p, '\n', avail);
+    const uint8_t *nl = (const uint8_t*) memchr (p, '\n', avail);
     size_t n = nl ? (size_t) (nl - p) : avail;
     if (buf) {
       if (!buf_reserve (buf, *len, cap, n + 1)) return -1;
@@ -84,14 +97,16 @@ static int take_line (tjb_reader *r, uint8_t **buf, size_t *len, size_t *cap)
 
 tjb_reader *tjb_reader_open (const char *path)
 {
-  gzFile fp = gzopen (path, "rb");
-  if (!fp) return NULL;
-  gzbuffer (fp, 1u << 20);
   tjb_reader *r = (tjb_reader*) calloc (1, sizeof (tjb_reader));
-  if (!r) { gzclose (fp); return NULL; }
-  r->fp = fp;
-  r->io = (uint8_t*) malloc (TJB_IOBUF);
-  if (!r->io) { gzclose (fp); free (r); return NULL; }
+  if (!r) return NULL;
+  const char *force_zlib = getenv ("TJB_ZLIB");
+  if (!(force_zlib && force_zlib[0] == '1')) r->gz = tjb_gz_open (path); /* NULL unless a regular gzip file */
+  if (r->gz) return r;
+  r->fp = gzopen (path, "rb");
+  if (!r->fp) { free (r); return NULL; }
+  gzbuffer (r->fp, 1u << 20);
+  r->io_own = (uint8_t*) malloc (TJB_IOBUF);
+  if (!r->io_own) { gzclose (r->fp); free (r); return NULL; }
   return r;
 }
 
@@ -99,7 +114,8 @@ void tjb_reader_close (tjb_reader *r)
 {
   if (!r) return;
   if (r->fp) gzclose (r->fp);
-  free (r->io); free (r->seq); free (r->qual); free (r);
+  tjb_gz_close (r->gz);
+  free (r->io_own); free (r->seq); free (r->qual); free (r);
 }
 
 /* parse one record into seq[]; returns 1 = record ready, 0 = no more records, -1 = out of memory */
@@ -143,10 +159,47 @@ static int next_record (tjb_reader *r)
   return 1;
 }
 
+/* The common case without the per-line machinery: a four-line FASTQ record that lies completely in the decoded piece
+ * (header, one sequence line, '+' line, one quality line of the same length, no '\r').  Copies the sequence straight to
+ * dst and returns its length + 1; 0 = not that shape (next_record() decides), -1 = does not fit into dst any more. */
+static inline int64_t fast_record (tjb_reader *r, uint8_t *dst, size_t room)
+{
+  const uint8_t *p = r->io + r->io_pos, *const end = r->io + r->io_end;
+  if (p >= end || *p != '@') return 0;
+  const uint8_t *nl = (const uint8_t*) memchr (p, '\n', (size_t) (end - p));
+  if (!nl) return 0;
+  const uint8_t *seq = nl + 1;
+  nl = (const uint8_t*) memchr (seq, '\n', (size_t) (end - seq));
+  if (!nl) return 0;
+  const size_t len = (size_t) (nl - seq);
+  if (!len || seq[len - 1] == '\r' || seq[0] == '>' || seq[0] == '@' || seq[0] == '+') return 0;
+  if (end - nl < 3 || nl[1] != '+') return 0;
+  nl = (const uint8_t*) memchr (nl + 1, '\n', (size_t) (end - nl - 1));
+  if (!nl) return 0;
+  const uint8_t *qual = nl + 1;
+  if ((size_t) (end - qual) < len + 1 || qual[len] != '\n' || memchr (qual, '\n', len)) return 0;
+  if (len > 1 && qual[len - 1] == '\r') return 0;
+  if (len + 1 > room) return -1;
+  memcpy (dst, seq, len);
+  dst[len] = '\n';
+  r->io_pos = (size_t) (qual + len + 1 - r->io);
+  return (int64_t) len + 1;
+}
+
 int64_t tjb_reader_fill (tjb_reader *r, uint8_t *dst, size_t cap, int64_t *n_reads, int64_t *n_bases)
 {
   size_t w = 0;
   for (;;) {
+    if (!r->seq_ready && !r->pending_header && !r->finished) {
+      const int64_t got = fast_record (r, dst + w, cap - w);
+      if (got > 0) {
+        w += (size_t) got;
+        if (n_reads) (*n_reads)++;
+        if (n_bases) (*n_bases) += got - 1;
+        continue;
+      }
+      if (got < 0 && w) break; /* chunk full: the record is parsed again by the next call */
+    }
     if (!r->seq_ready) {
       int rc = next_record (r);
       if (rc < 0) return TJB_ERR_NOMEM;

@@ -27,7 +27,10 @@
 #define LIT_TABLE ((1 << LIT_BITS) + 1024)
 #define DIST_TABLE ((1 << DIST_BITS) + 512)
 #define WINDOW 32768u
-#define GZ_PAYLOAD (4u << 20)       /* decoded bytes per buffer */
+#ifndef GZ_PAYLOAD_LOG
+#define GZ_PAYLOAD_LOG 22
+#endif
+#define GZ_PAYLOAD (1u << GZ_PAYLOAD_LOG) /* decoded bytes per buffer */
 #define GZ_SLACK 320u               /* one loop iteration never writes more than this past the soft end */
 #define GZ_NBUF 3
 #define TAIL_BYTES 32
