@@ -570,10 +570,13 @@ def c4_leg(ctxs, rank, world, timed, all_ranks_ok, args):
                 off += n
                 tables.append({"location": loc, "base": np.zeros(n, np.int32), "mode_context_length": np.full(n, 4, np.int32),
                                "name": np.zeros((n, 1), np.uint8)})
+            t_prep = time.perf_counter()
             n_concat = len(genome_set.merge_tracts(tables, 2)[0])
         t4 = time.perf_counter()
         stages[from_host] = {"count_samples": (t1 - t0) * 1e3, "allgather": (t2 - t1) * 1e3, "union": (t3 - t2) * 1e3,
                              "merge_tracts_rank0": (t4 - t3) * 1e3}
+        if rank == 0:  # of which: building the stand-in tables in Python (96 sorts), the rest is genome_set.merge_tracts
+            stages[from_host]["merge_tracts_rank0_standin_tables"] = (t_prep - t3) * 1e3
         return int(uni.shape[0]), int(sum(sizes)), n_concat
     best_by_mode = {}
     for from_host in (False, True):

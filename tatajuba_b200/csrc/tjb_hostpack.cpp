@@ -367,3 +367,25 @@ extern "C" long tjb_hostpack_selftest (const uint8_t *src, size_t n, int threads
   return !same ? -4 : r == r2 ? r : -3;
 }
 extern "C" void tjb_hostpack_expand_hook (void *dst, const void *src, size_t n_rows) { tjb_expand_rows (dst, src, n_rows); }
+
+// measurement hook (tools/pack_bench.py): seconds of the best of `reps` passes over src[0, n) in chunks of `chunk` bytes
+// through a pool of `threads` workers, like tjb_count_sample_host() drives it (without the copies)
+#include <chrono>
+extern "C" double tjb_hostpack_bench (const uint8_t *src, size_t n, int threads, int reps, size_t chunk)
+{
+  tjb_packer *p = tjb_packer_create (threads);
+  std::vector<uint8_t> packed (chunk / 4 + 64), val (chunk / 16);
+  std::vector<uint32_t> pos (chunk / 16);
+  double best = 1e30;
+  tjb_packer_begin (p);
+  for (int r = 0; r < reps; r++) {
+    const auto t0 = std::chrono::steady_clock::now ();
+    for (size_t off = 0; off < n; off += chunk)
+      tjb_packer_run (p, src + off, n - off < chunk ? n - off : chunk, packed.data (), pos.data (), val.data (), pos.size ());
+    const double s = std::chrono::duration<double> (std::chrono::steady_clock::now () - t0).count ();
+    if (s < best) best = s;
+  }
+  tjb_packer_end (p);
+  tjb_packer_destroy (p);
+  return best;
+}
