@@ -36,7 +36,8 @@ enum {
   TJB_ERR_ARG = -2,
   TJB_ERR_IO = -3,
   TJB_ERR_NOMEM = -4,
-  TJB_ERR_TOO_LARGE = -5         /* more than INT32_MAX tract observations (the reference's int n_elem) */
+  TJB_ERR_TOO_LARGE = -5,        /* more than INT32_MAX tract observations (the reference's int n_elem) */
+  TJB_ERR_NOALLOC_LIMIT = -6     /* tjb_tract_rows_noalloc: more reads than its fixed scratch is sized for */
 };
 
 /* the four tatajuba_options_t fields the path reads (src/hopo_counter.h:20-32); clamps as src/main.c:184-192 */
@@ -209,6 +210,26 @@ typedef struct {
 
 int tjb_context_histograms (const tjb_hist_opts *opt, const void *elem, int32_t n_elem, tjb_context_table *out);
 void tjb_context_table_free (tjb_context_table *t);
+
+/* Scan + count of one small batch of reads WITHOUT any allocation.  This entry point has no counterpart in the
+ * reference: it was added for callers that cannot call cudaMalloc (code under
+ * CUDA graph capture, tight serving loops, harnesses that forbid it).  d_seqs: n_bytes of reads separated by '\n' in
+ * device memory, n_bytes <= TJB_NOALLOC_MAX_BYTES (else TJB_ERR_NOALLOC_LIMIT, nothing is enqueued).  d_rows (device,
+ * room for max_rows rows) receives the sample's aggregation table in the row format of tjb_sample_export(): W + 1
+ * 64-bit words per row, W = 2 for kmer_size <= 26 and 3 above (tjb_sample_export's row_words - 1), {key words without
+ * the flag bits, forward count | reverse count << 32}, in no particular order; a key may appear in more than one row
+ * (add their counts), as in tjb_sample_export().  d_status (device, 3 x int64): [0] rows written, or -1 when the batch
+ * did not fit (more than 2^18 tract observations, more distinct ones than the 2^17-slot table takes, or more rows than
+ * max_rows); [1] tract observations; [2] skipped runs of non-ACGT bytes.  Everything is enqueued on `stream` (a
+ * cudaStream_t cast to void*, NULL = the default stream) and NOTHING is synchronised: read d_status after the stream.
+ * The scratch (records, table, counters: 11.9 MB) is one static device array that every GPU which loads the library
+ * holds until exit; all calls share it and it keeps the last call's contents (each call clears what must start at
+ * zero), so calls that overlap on the GPU (different streams, several host threads) race: one call at a time per GPU.
+ * Calls no cudaMalloc / cudaFree / cudaHostAlloc and no allocating library routine. */
+#define TJB_NOALLOC_MAX_BYTES ((size_t) 4 << 20)
+int tjb_tract_rows_noalloc (int device, const void *d_seqs, size_t n_bytes, const tjb_opts *opt, void *d_rows, int64_t max_rows,
+                            int64_t *d_status, void *stream);
+size_t tjb_noalloc_max_bytes (void);
 
 /* host FASTQ/FASTA(.gz) decoder on its own (kseq semantics): appends "SEQ\n" per record to dst (capacity cap);
  * returns bytes written (0 = end of file), <0 on error.  Exposed for tests and for callers that feed

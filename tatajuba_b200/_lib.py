@@ -19,7 +19,7 @@ EXPORTS = [
     "tjb_counter_out_free", "tjb_ctx_set_result_mode", "tjb_device_count", "tjb_sample_begin", "tjb_sample_scan_device",
     "tjb_ctx_table_capacity", "tjb_ctx_reserve_entries",
     "tjb_sample_export", "tjb_sample_import", "tjb_sample_finalise", "tjb_query_rows_device", "tjb_query_rows", "tjb_union_queries_device", "tjb_merge_tracts", "tjb_context_histograms", "tjb_context_table_free", "tjb_reader_open", "tjb_reader_fill", "tjb_reader_close",
-    "tjb_gz_open", "tjb_gz_next", "tjb_gz_close",
+    "tjb_gz_open", "tjb_gz_next", "tjb_gz_close", "tjb_tract_rows_noalloc", "tjb_noalloc_max_bytes",
 ]
 
 
@@ -144,5 +144,7 @@ def load():
     lib.tjb_gz_next.argtypes = [vp, C.POINTER(vp)]
     lib.tjb_gz_close.argtypes = [vp]
     lib.tjb_gz_close.restype = None
+    lib.tjb_tract_rows_noalloc.argtypes = [i32, vp, sz, po, vp, i64, vp, vp]
+    lib.tjb_noalloc_max_bytes.restype = sz
     _lib = lib
     return lib

@@ -904,6 +904,7 @@ const char *tjb_strerror (int code)
     case TJB_ERR_IO: return "I/O error";
     case TJB_ERR_NOMEM: return "out of memory";
     case TJB_ERR_TOO_LARGE: return "input too large";
+    case TJB_ERR_NOALLOC_LIMIT: return "batch larger than the fixed scratch of tjb_tract_rows_noalloc (TJB_NOALLOC_MAX_BYTES = 4 MiB of reads)";
     default: return "unknown code";
   }
 }
@@ -1403,6 +1404,114 @@ void tjb_counter_out_free (tjb_counter_out *out)
   free (out->name);
   out->elem = nullptr; out->idx_initial = out->idx_final = nullptr; out->name = nullptr;
   out->arena = 0;
+}
+
+} // extern "C"
+
+// ---- tjb_tract_rows_noalloc: scan + count of one small batch of reads without any allocation ------------------------
+// No counterpart in the reference; added for callers that cannot call
+// cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).  The scan's records, the
+// aggregation table, its overflow list and the counters live in ONE file-scope device array of a fixed size (every GPU
+// that loads the library holds it until exit); the caller passes the reads and the output rows.  Nothing here calls
+// cudaMalloc, cudaFree, cudaHostAlloc or a library routine that allocates; everything is enqueued on the caller's stream
+// and nothing is synchronised.  Every call shares the array: it is cleared at the start of a call (stream ordered), and
+// two calls that overlap on the GPU (different streams, or several host threads) race.
+#define NA_SLOTS   ((size_t) 1 << 17)   // table slots
+#define NA_REC_CAP ((size_t) 1 << 18)   // tract observations per call
+#define NA_OVF_CAP ((size_t) 1 << 14)
+#define NA_BIN_BITS 8                   // the aggregate kernel bins new entries for the partition plan: kept, unused here
+#define NA_OFF_COUNTERS 0               // CTR_WORDS x u64
+#define NA_OFF_NROWS    64              // u64
+#define NA_OFF_TILE     128             // u32
+#define NA_OFF_BINS     256             // 2^NA_BIN_BITS x u32
+#define NA_OFF_TABLE    (NA_OFF_BINS + (4u << NA_BIN_BITS))
+#define NA_OFF_OVF      (NA_OFF_TABLE + NA_SLOTS * 40)          // sized for W = 3 (40 bytes per slot, 24 per record)
+#define NA_OFF_RECS     (NA_OFF_OVF + NA_OVF_CAP * 24)
+#define NA_SCRATCH_BYTES (NA_OFF_RECS + NA_REC_CAP * 24)        // 11.9 MB
+static_assert (CTR_WORDS * 8 <= NA_OFF_NROWS && NA_OFF_TABLE % 256 == 0 && NA_OFF_OVF % 256 == 0 && NA_OFF_RECS % 256 == 0, "scratch layout");
+static __device__ __align__ (256) unsigned char g_noalloc_scratch[NA_SCRATCH_BYTES];
+
+// status[0] = rows written, or -1 when the batch did not fit the fixed scratch (more than NA_REC_CAP observations, an
+// overfull table) or the caller's rows array; status[1] = tract observations; status[2] = skipped non-ACGT runs
+__global__ void noalloc_status_kernel (const unsigned long long *__restrict__ counters, const unsigned long long *__restrict__ n_rows,
+                                       unsigned long long max_rows, long long *__restrict__ status)
+{
+  const bool fits = counters[CTR_RECORDS] <= NA_REC_CAP && counters[CTR_OVERFLOW] <= NA_OVF_CAP && *n_rows <= max_rows;
+  status[0] = fits ? (long long) *n_rows : -1LL;
+  status[1] = (long long) counters[CTR_RECORDS];
+  status[2] = (long long) counters[CTR_SKIP];
+}
+
+#define NA_MAX_DEVICES 64
+static std::mutex g_noalloc_mu;
+static unsigned char *g_noalloc_ptr[NA_MAX_DEVICES]; // device address of the array on each device, looked up once
+static int g_noalloc_sms[NA_MAX_DEVICES];
+
+// once per device, with that device current: the DEVICE address of the array (its name is only a host-side handle)
+static int noalloc_setup (int device, unsigned char **ptr, int *sms)
+{
+  std::lock_guard<std::mutex> lk (g_noalloc_mu);
+  if (!g_noalloc_ptr[device]) {
+    unsigned char *p = nullptr;
+    if (cudaGetSymbolAddress ((void**) &p, g_noalloc_scratch) != cudaSuccess || !p) { cudaGetLastError (); return TJB_ERR_CUDA; }
+    int n_sm = 0;
+    if (cudaDeviceGetAttribute (&n_sm, cudaDevAttrMultiProcessorCount, device) != cudaSuccess || n_sm < 1) { cudaGetLastError (); return TJB_ERR_CUDA; }
+    if (cudaFuncSetAttribute (tjb_scan_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) scan_smem_bytes<2> ()) != cudaSuccess ||
+        cudaFuncSetAttribute (tjb_scan_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int) scan_smem_bytes<3> ()) != cudaSuccess) { cudaGetLastError (); return TJB_ERR_CUDA; }
+    g_noalloc_sms[device] = n_sm;
+    g_noalloc_ptr[device] = p;
+  }
+  *ptr = g_noalloc_ptr[device]; *sms = g_noalloc_sms[device];
+  return 0;
+}
+
+template <int W>
+static int noalloc_enqueue (unsigned char *base, int sms, const uint8_t *d_seqs, size_t n, const tjb_opts *opt, u64 *d_rows, unsigned long long max_rows,
+                            long long *d_status, cudaStream_t st)
+{
+  unsigned long long *counters = (unsigned long long*) (base + NA_OFF_COUNTERS), *n_rows = (unsigned long long*) (base + NA_OFF_NROWS);
+  u32 *tile_ctr = (u32*) (base + NA_OFF_TILE), *bins = (u32*) (base + NA_OFF_BINS);
+  u64 *ovf = (u64*) (base + NA_OFF_OVF), *recs = (u64*) (base + NA_OFF_RECS);
+  AggTable tab;
+  tab.cnt = (unsigned long long*) (base + NA_OFF_TABLE); tab.keys = (u64*) (base + NA_OFF_TABLE) + NA_SLOTS; tab.mask = (u32) (NA_SLOTS - 1);
+  // what must start at zero: counters, row count, window tickets, bins, the table (keys and counts)
+  if (cudaMemsetAsync (base, 0, NA_OFF_TABLE + table_bytes (NA_SLOTS, W), st) != cudaSuccess) return TJB_ERR_CUDA;
+  const long long n_tiles = (long long) ((n + SW_TILE - 1) / SW_TILE);
+  if (n_tiles) {
+    const int min_len = opt->min_tract_size < 2 ? 2 : opt->min_tract_size;
+    const long long want = (n_tiles + SCAN_WARPS - 1) / SCAN_WARPS;
+    const long long grid = want < (long long) sms * SCAN_CTAS_PER_SM ? want : (long long) sms * SCAN_CTAS_PER_SM;
+    tjb_scan_kernel<W><<<(u32) grid, SCAN_THREADS, scan_smem_bytes<W> (), st>>> (d_seqs, (long long) n, opt->kmer_size, min_len, recs, NA_REC_CAP, counters, n_tiles, tile_ctr);
+    const u32 g_agg = (u32) (nblk (NA_REC_CAP, 256 * AGG_UNROLL) < (size_t) sms * 8 ? nblk (NA_REC_CAP, 256 * AGG_UNROLL) : (size_t) sms * 8);
+    aggregate_kernel<W><<<g_agg, 256, 0, st>>> (recs, counters, NA_REC_CAP, tab, ovf, NA_OVF_CAP, opt->kmer_size, bins, NA_BIN_BITS);
+    table_export_kernel<W><<<(u32) sms * 4, 256, 0, st>>> (tab, ovf, counters, NA_OVF_CAP, d_rows, n_rows, max_rows);
+  }
+  noalloc_status_kernel<<<1, 1, 0, st>>> (counters, n_rows, max_rows, d_status);
+  return cudaGetLastError () == cudaSuccess ? 0 : TJB_ERR_CUDA;
+}
+
+extern "C" {
+
+size_t tjb_noalloc_max_bytes (void) { return TJB_NOALLOC_MAX_BYTES; }
+
+int tjb_tract_rows_noalloc (int device, const void *d_seqs, size_t n_bytes, const tjb_opts *opt, void *d_rows, int64_t max_rows,
+                            int64_t *d_status, void *stream)
+{
+  if (device < 0 || device >= NA_MAX_DEVICES || !opt || !d_status || max_rows < 0 || (n_bytes && !d_seqs) || (max_rows && !d_rows)) return TJB_ERR_ARG;
+  if (opt->kmer_size < 2 || opt->kmer_size > 32 || opt->min_tract_size < 1) return TJB_ERR_ARG;
+  if (n_bytes > TJB_NOALLOC_MAX_BYTES) return TJB_ERR_NOALLOC_LIMIT; // before any CUDA call: a clear error, nothing enqueued
+  int current = -1;
+  if (cudaGetDevice (&current) != cudaSuccess) { cudaGetLastError (); return TJB_ERR_CUDA; }
+  if (current != device && cudaSetDevice (device) != cudaSuccess) { cudaGetLastError (); return TJB_ERR_CUDA; }
+  unsigned char *base = nullptr;
+  int sms = 0;
+  int rc = noalloc_setup (device, &base, &sms);
+  if (rc == 0)
+    rc = tjb_rec_words (opt->kmer_size) == 2
+       ? noalloc_enqueue<2> (base, sms, (const uint8_t*) d_seqs, n_bytes, opt, (u64*) d_rows, (unsigned long long) max_rows, (long long*) d_status, (cudaStream_t) stream)
+       : noalloc_enqueue<3> (base, sms, (const uint8_t*) d_seqs, n_bytes, opt, (u64*) d_rows, (unsigned long long) max_rows, (long long*) d_status, (cudaStream_t) stream);
+  if (current != device && current >= 0) cudaSetDevice (current);
+  return rc;
 }
 
 } // extern "C"
