@@ -276,7 +276,9 @@ def main():
     ctx = ctxs[0]
     e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
 
-    def timed(fn):
+    by_rank = {}
+
+    def timed(fn, tag=None):
         """device time of fn() between two events on an otherwise idle stream, bracketed by barriers; max over ranks"""
         barrier()
         e0.record()
@@ -284,7 +286,15 @@ def main():
         torch.cuda.synchronize()
         e1.record()
         barrier()
-        return max_over_ranks(e0.elapsed_time(e1)), out
+        mine = e0.elapsed_time(e1)
+        if tag and world > 1:  # every rank's own time, for the record (the reported one is the maximum)
+            t = torch.tensor([mine], dtype=torch.float64, device="cuda")
+            allr = [torch.zeros_like(t) for _ in range(world)]
+            dist.all_gather(allr, t)
+            by_rank[tag] = [round(float(x.item()), 4) for x in allr]
+        elif tag:
+            by_rank[tag] = [round(mine, 4)]
+        return max_over_ranks(mine), out
 
     def count_steps(steps, count_one, contexts):
         return genome_set.count_samples(contexts, steps, count_one)
@@ -327,6 +337,7 @@ def main():
                               "parallelises over samples only); the same run is the parity gate"}
 
     # ---- value: device-resident, steps dealt to the contexts of this GPU, results in the arena -----------------------
+    barrier()  # ranks leave the parity gate at different times: wait for them BEFORE the warm-up, not with idle GPUs after it
     for c in ctxs:
         c.set_result_mode(True)
         for _ in range(args.warmup):
@@ -339,7 +350,17 @@ def main():
     sampler = ClockSampler(local_rank)
     if rank == 0 and not os.environ.get("BENCH_NO_SAMPLER"):
         sampler.start()
-    ms, _ = timed(lambda: count_steps(args.steps, lambda c, s: c.count_device(d_buf.data_ptr(), n_bytes, opt), ctxs))
+    step_wall = []
+
+    def one_step(c, s):
+        t0 = time.perf_counter()
+        r = c.count_device(d_buf.data_ptr(), n_bytes, opt)
+        step_wall.append(time.perf_counter() - t0)
+        return r
+    ms, _ = timed(lambda: count_steps(args.steps, one_step, ctxs), tag="value_ms_by_rank")
+    if os.environ.get("BENCH_DEBUG"):
+        sys.stderr.write(f"[bench] rank {rank}: {ms:.3f} ms for {args.steps} steps; host wall per step (us): "
+                         + " ".join(f"{x * 1e6:.0f}" for x in step_wall) + "\n")
     clocks = sampler.summary() if rank == 0 else None
     scan_ms = scan_launches = scan_bytes = 0
     launches = 0
@@ -448,7 +469,8 @@ def main():
         "scaling": "weak", "vs_baseline": None, "dtype": "u8/u64", "data": "synthetic",
         "config": {"workload": WORKLOAD, "bases_per_gpu": n_bases, "reads_per_gpu": n_reads, "input_bytes": n_bytes,
                    "l2": "input (503 MB) larger than L2 (126 MB); no flush needed", "parity": parity,
-                   "contexts_per_gpu": len(ctxs), "one_context_ms_per_step": ms_single / args.steps, "two_contexts": two, **stats0},
+                   "contexts_per_gpu": len(ctxs), "one_context_ms_per_step": ms_single / args.steps, "two_contexts": two,
+                   "value_ms_by_rank": by_rank.get("value_ms_by_rank"), **stats0},
         "e2e": {"value": world * n_bases * args.steps / (ms_e2e * 1e-3), "unit": "bases/s", "ms_per_step": ms_e2e / args.steps,
                 "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h, "results": "malloc()ed host arrays (reference layout)",
                 "transfer": transfer},

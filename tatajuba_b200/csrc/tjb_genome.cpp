@@ -10,8 +10,12 @@
 #include <cstring>
 #include <memory>
 #include <string>
+#include <thread>
 #include <utility>
 #include <vector>
+#if defined(__linux__)
+#include <sched.h>
+#endif
 
 #include "tjb_gpu.h"
 
@@ -86,89 +90,175 @@ extern "C" int tjb_merge_tracts (int32_t n_samples, const int32_t *n_hist, const
   //    every group of equal location gets the order the sequential merges would have left it in — the reverse of the
   //    sample order when every sample has at most one row there (the usual case), the literal interleaving otherwise.
   //    Rows carry their location and sample along, so that nothing after the sort reads the input tables at random.
+  //    Many samples of one genome (dense locations) are handled in SLICES of the location range by a few threads: the
+  //    sort and the tie rule never look across a location boundary, and the tract-id chain (step 2) can be cut wherever
+  //    two neighbouring rows are at least max (mode_len) apart: such a row cannot overlap the first row of any earlier
+  //    tract (rows_overlap() needs a distance below the shorter of the two mode lengths), so it starts a tract whatever
+  //    came before.
   struct Row { uint32_t loc; int32_t sample, row, pad; };
-  std::unique_ptr<Row[]> acc (new Row[total]), other (new Row[total]);
-  {
-    uint32_t differ = 0; // locations may be negative (nothing forbids it): biased to unsigned for the sort
-    const uint32_t loc0 = (uint32_t) location[0] ^ 0x80000000u;
-    uint32_t lo = loc0, hi = loc0;
-    bool ascending = true; // within every sample, as the reference's merge expects (genome_set.c:274)
-    for (int32_t s = 0; s < n_samples; s++) for (int32_t j = first[s]; j < first[s + 1]; j++) {
+  int workers = (int) std::thread::hardware_concurrency ();
+#if defined(__linux__)
+  cpu_set_t set;
+  if (sched_getaffinity (0, sizeof (set), &set) == 0 && CPU_COUNT (&set) > 0) workers = std::min (workers > 0 ? workers : 1 << 20, CPU_COUNT (&set));
+#endif
+  if (const char *e = getenv ("TJB_MERGE_THREADS")) workers = atoi (e);
+  workers = std::max (1, std::min (std::min (workers, 32), total / 4096));
+  auto parallel_for = [] (int n, auto &&fn) { // fn (0 .. n-1), 0 on this thread
+    std::vector<std::thread> th;
+    for (int r = 1; r < n; r++) th.emplace_back ([&fn, r] { fn (r); });
+    fn (0);
+    for (auto &t : th) t.join ();
+  };
+  Row *acc = (Row*) malloc (sizeof (Row) * (size_t) total), *other = (Row*) malloc (sizeof (Row) * (size_t) total);
+  struct Free { Row *&a, *&b; ~Free () { free (a); free (b); } } free_rows = {acc, other};
+  if (!acc || !other) return TJB_ERR_NOMEM;
+  // rows with their (biased: locations may be negative, nothing forbids it) location; every worker takes a share of
+  // the rows (and is the first to touch that part of both arrays)
+  struct Seen { uint32_t differ = 0, lo = 0xffffffffu, hi = 0; int32_t max_mode_len = 0; bool ascending = true; };
+  std::vector<Seen> seen (workers);
+  const uint32_t loc0 = (uint32_t) location[0] ^ 0x80000000u;
+  parallel_for (workers, [&] (int w) {
+    const int32_t j0 = (int32_t) ((int64_t) total * w / workers), j1 = (int32_t) ((int64_t) total * (w + 1) / workers);
+    int32_t s = (int32_t) (std::upper_bound (first.begin (), first.end (), j0) - first.begin ()) - 1;
+    Seen v;
+    for (int32_t j = j0; j < j1; j++) {
+      while (j >= first[s + 1]) s++;
       acc[j].loc = (uint32_t) location[j] ^ 0x80000000u; acc[j].sample = s; acc[j].row = j; acc[j].pad = 0;
-      differ |= acc[j].loc ^ loc0;
-      lo = std::min (lo, acc[j].loc); hi = std::max (hi, acc[j].loc);
-      if (j > first[s] && acc[j].loc < acc[j - 1].loc) ascending = false;
+      v.differ |= acc[j].loc ^ loc0;
+      v.lo = std::min (v.lo, acc[j].loc); v.hi = std::max (v.hi, acc[j].loc);
+      v.max_mode_len = std::max (v.max_mode_len, mode_len[j]);
+      if (j > first[s] && location[j] < location[j - 1]) v.ascending = false;
+      other[j].loc = 0; // first touch
     }
-    if (ascending && (uint64_t) (hi - lo) <= 8ull * (uint64_t) total + 1024) {
-      // locations dense enough (many samples of one genome): one counting sort by location, done block of locations by
-      // block of locations with one cursor per sample, so that the part of the output being written (~128 KB) stays in
-      // cache (sample after sample over the whole range would touch every line of the output once per sample)
-      std::vector<uint32_t> start ((size_t) (hi - lo) + 2, 0u);
-      for (int32_t j = 0; j < total; j++) start[acc[j].loc - lo + 1]++;
-      for (size_t c = 1; c < start.size (); c++) start[c] += start[c - 1];
-      std::vector<int32_t> cursor (first.begin (), first.end () - 1);
-      const uint64_t range = (uint64_t) (hi - lo) + 1;
-      const uint64_t block = std::max<uint64_t> (1, range * 8192 / (uint64_t) total);
-      for (uint64_t b0 = 0; b0 < range; b0 += block) {
-        const uint64_t limit = (uint64_t) lo + std::min (range, b0 + block); // exclusive
-        for (int32_t s = 0; s < n_samples; s++) {
-          int32_t j = cursor[s];
-          for (; j < first[s + 1] && (uint64_t) acc[j].loc < limit; j++) other[start[acc[j].loc - lo]++] = acc[j];
-          cursor[s] = j;
-        }
-      }
-      acc.swap (other);
-    } else {
-      const int DIGIT = 8;
-      const uint32_t digit_mask = (1u << DIGIT) - 1;
-      std::vector<uint32_t> start ((size_t) 1 << DIGIT);
-      for (int shift = 0; shift < 32 && (differ >> shift); shift += DIGIT) { // digits above the highest differing bit are equal
-        std::fill (start.begin (), start.end (), 0u);
-        for (int32_t j = 0; j < total; j++) start[(acc[j].loc >> shift) & digit_mask]++;
-        uint32_t run = 0;
-        for (auto &c : start) { const uint32_t n = c; c = run; run += n; }
-        for (int32_t j = 0; j < total; j++) other[start[(acc[j].loc >> shift) & digit_mask]++] = acc[j];
-        acc.swap (other);
-      }
+    seen[w] = v;
+  });
+  uint32_t differ = 0, lo = 0xffffffffu, hi = 0;
+  int32_t max_mode_len = 0;
+  bool ascending = true; // within every sample, as the reference's merge expects (genome_set.c:274)
+  for (const Seen &v : seen) { differ |= v.differ; lo = std::min (lo, v.lo); hi = std::max (hi, v.hi); max_mode_len = std::max (max_mode_len, v.max_mode_len); ascending = ascending && v.ascending; }
+  const bool dense = ascending && (uint64_t) (hi - lo) <= 8ull * (uint64_t) total + 1024;
+
+  // slices: [bound[r], bound[r + 1]) in biased locations, rows [slice_row[r], slice_row[r + 1]) of the sorted vector
+  const int n_slices = dense ? workers : 1;
+  std::vector<uint64_t> bound (n_slices + 1);
+  for (int r = 0; r <= n_slices; r++) bound[r] = (uint64_t) lo + ((uint64_t) (hi - lo) + 1) * (uint64_t) r / (uint64_t) n_slices;
+  std::vector<int32_t> slice_row (n_slices + 1, 0), cut ((size_t) (n_slices + 1) * (size_t) std::max (n_samples, 1));
+  if (dense) for (int r = 0; r <= n_slices; r++) { // where every sample's rows cross the slice boundaries
+    int32_t rows = 0;
+    for (int32_t s = 0; s < n_samples; s++) {
+      const Row *b0 = acc + first[s], *b1 = acc + first[s + 1];
+      const Row *c = std::partition_point (b0, b1, [&] (const Row &x) { return (uint64_t) x.loc < bound[r]; });
+      cut[(size_t) r * n_samples + s] = (int32_t) (c - acc);
+      rows += (int32_t) (c - b0);
     }
-  }
-  std::vector<Row> grp, merged;
-  for (int32_t g0 = 0; g0 < total; ) {
-    int32_t g1 = g0 + 1;
-    bool twice = false; // some sample has two rows at this location
-    while (g1 < total && acc[g1].loc == acc[g0].loc) { twice = twice || acc[g1].sample == acc[g1 - 1].sample; g1++; }
-    if (!twice) std::reverse (acc.get () + g0, acc.get () + g1);
-    else { // the sequential merges, on this group alone: new sample's row, then one accumulated row, while both have some
-      grp.clear ();
-      int32_t i = g0;
-      while (i < g1) {
-        int32_t e = i + 1;
-        while (e < g1 && acc[e].sample == acc[i].sample) e++;
-        merged.clear ();
-        int32_t a = 0, b = i;
-        const int32_t na = (int32_t) grp.size ();
-        while (a < na && b < e) { merged.push_back (acc[b++]); merged.push_back (grp[a++]); }
-        while (b < e) merged.push_back (acc[b++]);
-        while (a < na) merged.push_back (grp[a++]);
-        grp.swap (merged);
-        i = e;
-      }
-      std::copy (grp.begin (), grp.end (), acc.get () + g0);
-    }
-    g0 = g1;
+    slice_row[r] = rows;
   }
 
-  // 2. tract ids: every row is compared with the FIRST row of the current tract (genome_set.c:208-222)
-  const Tables t = {location, base, mode_len, names, name_stride, levenshtein_distance};
-  std::vector<uint32_t> tab;
-  std::vector<char> yname;
-  int32_t prev = 0, id = 0;
-  for (int32_t i = 0; i < total; i++) {
-    if (i && acc[i].loc != acc[prev].loc && !rows_overlap (t, acc[i].row, acc[prev].row, tab, yname)) { id++; prev = i; }
-    out_sample[i] = acc[i].sample;
-    out_index[i] = acc[i].row - first[acc[i].sample];
-    out_tract_id[i] = id;
+  // sort + tie rule of the rows [r0, r1) of the sorted vector (a whole number of location groups)
+  auto tie_rule = [&] (Row *v, int32_t r0, int32_t r1) {
+    std::vector<Row> grp, merged;
+    for (int32_t g0 = r0; g0 < r1; ) {
+      int32_t g1 = g0 + 1;
+      bool twice = false; // some sample has two rows at this location
+      while (g1 < r1 && v[g1].loc == v[g0].loc) { twice = twice || v[g1].sample == v[g1 - 1].sample; g1++; }
+      if (!twice) std::reverse (v + g0, v + g1);
+      else { // the sequential merges, on this group alone: new sample's row, then one accumulated row, while both have some
+        grp.clear ();
+        int32_t i = g0;
+        while (i < g1) {
+          int32_t e = i + 1;
+          while (e < g1 && v[e].sample == v[i].sample) e++;
+          merged.clear ();
+          int32_t a = 0, b = i;
+          const int32_t na = (int32_t) grp.size ();
+          while (a < na && b < e) { merged.push_back (v[b++]); merged.push_back (grp[a++]); }
+          while (b < e) merged.push_back (v[b++]);
+          while (a < na) merged.push_back (grp[a++]);
+          grp.swap (merged);
+          i = e;
+        }
+        std::copy (grp.begin (), grp.end (), v + g0);
+      }
+      g0 = g1;
+    }
+  };
+  // one slice of the dense case: a counting sort by location, done block of locations by block of locations with one
+  // cursor per sample, so that the part of the output being written (~128 KB) stays in cache (sample after sample over
+  // the whole range would touch every line of the output once per sample)
+  auto sort_slice = [&] (int r) {
+    const uint64_t b_lo = bound[r], range = bound[r + 1] - bound[r];
+    const int32_t r0 = slice_row[r], r1 = slice_row[r + 1];
+    if (r1 == r0) return;
+    std::vector<uint32_t> start ((size_t) range + 1, 0u);
+    std::vector<int32_t> cursor (cut.begin () + (size_t) r * n_samples, cut.begin () + (size_t) (r + 1) * n_samples);
+    const int32_t *stop = cut.data () + (size_t) (r + 1) * n_samples;
+    for (int32_t s = 0; s < n_samples; s++) for (int32_t j = cursor[s]; j < stop[s]; j++) start[(uint64_t) acc[j].loc - b_lo + 1]++;
+    start[0] = (uint32_t) r0;
+    for (size_t c = 1; c < start.size (); c++) start[c] += start[c - 1];
+    const uint64_t block = std::max<uint64_t> (1, range * 8192 / (uint64_t) (r1 - r0));
+    for (uint64_t b0 = 0; b0 < range; b0 += block) {
+      const uint64_t limit = b_lo + std::min (range, b0 + block); // exclusive
+      for (int32_t s = 0; s < n_samples; s++) {
+        int32_t j = cursor[s];
+        for (; j < stop[s] && (uint64_t) acc[j].loc < limit; j++) other[start[(uint64_t) acc[j].loc - b_lo]++] = acc[j];
+        cursor[s] = j;
+      }
+    }
+    tie_rule (other, r0, r1);
+  };
+  if (dense) {
+    parallel_for (n_slices, sort_slice);
+    std::swap (acc, other);
+  } else {
+    const int DIGIT = 8;
+    const uint32_t digit_mask = (1u << DIGIT) - 1;
+    std::vector<uint32_t> start ((size_t) 1 << DIGIT);
+    for (int shift = 0; shift < 32 && (differ >> shift); shift += DIGIT) { // digits above the highest differing bit are equal
+      std::fill (start.begin (), start.end (), 0u);
+      for (int32_t j = 0; j < total; j++) start[(acc[j].loc >> shift) & digit_mask]++;
+      uint32_t run = 0;
+      for (auto &c : start) { const uint32_t n = c; c = run; run += n; }
+      for (int32_t j = 0; j < total; j++) other[start[(acc[j].loc >> shift) & digit_mask]++] = acc[j];
+      std::swap (acc, other);
+    }
+    tie_rule (acc, 0, total);
   }
+
+  // 2. tract ids: every row is compared with the FIRST row of the current tract (genome_set.c:208-222).  A slice whose
+  //    first row is max_mode_len or more away from the row before it starts a chain of its own; the others are chained
+  //    on by the thread of the slice before them.
+  const Tables t = {location, base, mode_len, names, name_stride, levenshtein_distance};
+  std::vector<char> own_chain (n_slices, 0);
+  std::vector<int32_t> tracts (n_slices, 0); // tracts started in the chain that begins at slice r
+  for (int r = 0; r < n_slices; r++) {
+    const int32_t r0 = slice_row[r];
+    own_chain[r] = r == 0 || (dense && r0 > 0 && r0 < total && (int64_t) acc[r0].loc - (int64_t) acc[r0 - 1].loc >= (int64_t) std::max (max_mode_len, 1));
+  }
+  if (!dense) slice_row[n_slices] = total;
+  auto chain = [&] (int r) {
+    if (!own_chain[r]) return;
+    int r_end = r + 1;
+    while (r_end < n_slices && !own_chain[r_end]) r_end++;
+    const int32_t i0 = slice_row[r], i1 = slice_row[r_end];
+    std::vector<uint32_t> tab;
+    std::vector<char> yname;
+    int32_t prev = i0, id = 0;
+    for (int32_t i = i0; i < i1; i++) {
+      if (i > i0 && acc[i].loc != acc[prev].loc && !rows_overlap (t, acc[i].row, acc[prev].row, tab, yname)) { id++; prev = i; }
+      out_sample[i] = acc[i].sample;
+      out_index[i] = acc[i].row - first[acc[i].sample];
+      out_tract_id[i] = id;
+    }
+    tracts[r] = i1 > i0 ? id + 1 : 0;
+  };
+  parallel_for (n_slices, chain);
+  std::vector<int32_t> id_offset (n_slices, 0);
+  for (int r = 0, run = 0; r < n_slices; r++) { if (own_chain[r]) { id_offset[r] = run; run += tracts[r]; } else id_offset[r] = id_offset[r - 1]; }
+  auto renumber = [&] (int r) {
+    if (!id_offset[r]) return;
+    for (int32_t i = slice_row[r]; i < slice_row[r + 1]; i++) out_tract_id[i] += id_offset[r];
+  };
+  parallel_for (n_slices, renumber);
   return total;
 }
 

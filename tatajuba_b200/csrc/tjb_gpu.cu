@@ -54,6 +54,7 @@ struct tjb_ctx {
   cudaStream_t stream = nullptr;
   std::string err;
   int profiling = 0; // 0 off, 1 scan kernel only, 2 every kernel
+  bool t1_recorded = false;
   int result_mode = TJB_RESULT_MALLOC;
   bool result_dma = false; // results leave through a device staging array + DMA instead of mapped stores of the pack kernel
   int64_t launches = 0;
@@ -644,6 +645,8 @@ static int finalise_t (tjb_ctx *ctx, tjb_counter_out *out, int qc_mode)
     } else spec.keep = spec.idx = 0;
   }
   tr.mark ("prealloc");
+  ctx->t1_recorded = false;
+  if (ctx->profiling) { CU (cudaEventRecord (ctx->ev_t1, st)); ctx->t1_recorded = true; } // end of the sample's device work: no second round trip for it
   CU (cudaStreamSynchronize (st)); // ---- the synchronisation of the sample
   tr.mark ("sync");
   const ResultBlock *hr = ctx->h_res;
@@ -737,12 +740,13 @@ static int finalise (tjb_ctx *ctx, tjb_counter_out *out)
 
 static void out_reset (tjb_counter_out *out) { memset (out, 0, sizeof (*out)); }
 
-// device time of the call between ev_t0 and now (diagnostics): another round trip, so only when profiling is on
+// device time of the call between ev_t0 and the end of the sample's device work (diagnostics, when profiling is on)
 static int device_time (tjb_ctx *ctx, tjb_counter_out *out)
 {
   if (!ctx->profiling) return 0;
-  CU (cudaEventRecord (ctx->ev_t1, ctx->stream));
+  if (!ctx->t1_recorded) CU (cudaEventRecord (ctx->ev_t1, ctx->stream)); // (paths that do not end in finalise ())
   CU (cudaEventSynchronize (ctx->ev_t1));
+  ctx->t1_recorded = false;
   float ms = 0.f;
   cudaEventElapsedTime (&ms, ctx->ev_t0, ctx->ev_t1);
   out->ms_device = ms;

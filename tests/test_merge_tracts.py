@@ -89,3 +89,24 @@ def test_merge_sparse_locations_matches_compiled_reference(reference, seed):
     want = pyoracle.reference_merge_tracts(tables, 2)
     for a, b in zip(got, want):
         assert np.array_equal(a, b)
+
+
+@pytest.mark.parametrize("seed,threads", [(50, 16), (51, 5), (52, 32)])
+def test_merge_in_slices_matches_compiled_reference(reference, seed, threads, monkeypatch):
+    """tables large enough for the sliced, multi-threaded path (many samples of one genome): same result as the
+    reference's sequential merges and as one thread, whether or not the tract-id chain can be cut at a slice boundary
+    (sites ~40 apart, mode lengths up to 13 / up to 60: chains are cut / carried over)"""
+    rng = np.random.default_rng(seed)
+    tables = make_tables(seed, 30, 4000)
+    if seed == 51:  # long tracts: neighbouring sites overlap, no boundary is a safe cut
+        for t in tables:
+            t["mode_context_length"] = (t["mode_context_length"] + rng.integers(20, 50, len(t["location"]))).astype(np.int32)
+    assert sum(len(t["location"]) for t in tables) > 16 * 4096
+    want = pyoracle.reference_merge_tracts(tables, 2)
+    monkeypatch.setenv("TJB_MERGE_THREADS", str(threads))
+    got = genome_set.merge_tracts(tables, 2)
+    monkeypatch.setenv("TJB_MERGE_THREADS", "1")
+    one = genome_set.merge_tracts(tables, 2)
+    for a, b, c in zip(got, want, one):
+        assert np.array_equal(a, b)
+        assert np.array_equal(c, b)
