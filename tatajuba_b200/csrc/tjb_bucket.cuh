@@ -277,6 +277,7 @@ aggregate_kernel (const u64 *__restrict__ recs, unsigned long long *__restrict__
       const size_t i = i0 + u * stride;
       seen[u] = -1;
       if (i < n) {
+        r[u] = canon_obs<W> (r[u], k); // the scan's fast path leaves the strand canonicalisation to this kernel
         Rec<W> key = r[u];
         key.w[0] &= ~3ULL;
         slot[u] = key_hash<W> (key) & tab.mask;

@@ -92,6 +92,60 @@ template <int W> __device__ __forceinline__ void store_rec (u64 *p, size_t i, co
   }
 }
 
+// ---------------------------------------------------------------------------------------------------------
+// Raw tract observation: what the scan kernel appends for a tract found on its fast path.  Both flanks as the scan
+// has them (k GRAY codes each, A0 C1 T2 G3, base j in bits 2j..2j+1, in read orientation), the tract's gray code and
+// its length; bit 63 of one word says "raw".  Strand canonicalisation (hopo_counter.c:233-246) is left to the kernel
+// that counts the observations (aggregate_kernel has idle issue slots, the scan has none): canon_obs() turns a raw
+// observation into the record above; records the scan's slow path wrote in their final form pass through.
+//   W = 2:  w0 = left flank | gray << 52 | length << 54       w1 = right flank | 1 << 63
+//   W = 3:  w0 = gray | length << 2 | 1 << 63                 w1 = left flank     w2 = right flank
+// ---------------------------------------------------------------------------------------------------------
+#ifndef SCAN_RAW_OBS
+#define SCAN_RAW_OBS 1
+#endif
+#define TJB_OBS_RAW (1ULL << 63)
+
+template <int W> __device__ __forceinline__ Rec<W> pack_obs (u64 left, u64 right, int gray, int len)
+{
+  Rec<W> r;
+  if (W == 2) { r.w[0] = left | ((u64) gray << 52) | ((u64) len << 54); r.w[1] = right | TJB_OBS_RAW; }
+  else { r.w[0] = (u64) gray | ((u64) len << 2) | TJB_OBS_RAW; r.w[1] = left; r.w[W - 1] = right; }
+  return r;
+}
+
+// reverse complement of a k-base word of GRAY codes (A0 C1 T2 G3, base j in bits 2j..2j+1), as BINARY codes
+// (A0 C1 G2 T3).  The bit reversal also swaps the two bits of every base: a base (h, l) arrives as (l, h).  Its
+// binary code is (h, h ^ l), the complement of that (~h, ~(h ^ l)): the high bit from the swapped low bit, the low
+// bit from the XOR of both.
+__device__ __forceinline__ u64 revcomp_gray (u64 g, int k, u64 kmask)
+{
+  const u64 y = __brevll (g) >> (64 - 2 * k); // k >= 2
+  const u64 m5 = 0x5555555555555555ULL;
+  return ~(((y & m5) << 1) | ((y ^ (y >> 1)) & m5)) & kmask;
+}
+
+// flanks in gray codes + tract code -> the canonical record: A / C tracts keep the read's strand (gray -> binary
+// codes, hopo_counter.c:233-238), T / G tracts are reverse-complemented (:239-246)
+template <int W> __device__ __forceinline__ Rec<W> canon_from_gray (u64 gl64, u64 gr64, int gray, int len, int k)
+{
+  const u64 kmask = (k == 32) ? ~0ULL : ((1ULL << (2 * k)) - 1);
+  const u64 m5 = 0x5555555555555555ULL;
+  u64 ctx0, ctx1;
+  if (gray < 2) { ctx0 = gl64 ^ ((gl64 >> 1) & m5); ctx1 = gr64 ^ ((gr64 >> 1) & m5); }
+  else { ctx0 = revcomp_gray (gr64, k, kmask); ctx1 = revcomp_gray (gl64, k, kmask); }
+  return pack_rec<W> (ctx0, ctx1, gray & 1, len, gray < 2 ? 1 : 2, k);
+}
+template <int W> __device__ __forceinline__ Rec<W> canon_obs (const Rec<W> &r, int k)
+{
+  if (W == 2) {
+    if (!(r.w[1] & TJB_OBS_RAW)) return r;
+    return canon_from_gray<W> (r.w[0] & ((1ULL << 52) - 1), r.w[1] & ~TJB_OBS_RAW, (int) (r.w[0] >> 52) & 3, (int) (r.w[0] >> 54), k);
+  }
+  if (!(r.w[0] & TJB_OBS_RAW)) return r;
+  return canon_from_gray<W> (r.w[1], r.w[W - 1], (int) r.w[0] & 3, (int) (r.w[0] >> 2) & 0x3ff, k);
+}
+
 // value of a signed bit-field of `bits` bits holding v (gcc semantics for the reference's int64_t bit-fields)
 __host__ __device__ __forceinline__ int sext_field (long long v, int bits)
 {

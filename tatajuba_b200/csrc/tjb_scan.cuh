@@ -4,41 +4,50 @@
 // 285-307), which walk one read at a time, byte by byte, on one CPU thread.  Here a whole chunk of reads
 // ("SEQ\nSEQ\n...", '\n' = read separator, written by csrc/tjb_fastq.c) is scanned by the full grid.
 //
-// The reads are touched once, at HBM speed, so the kernel is bound by the integer pipe (LOP3/SHF/PRMT issue at half
-// rate on sm_100): the design minimises ALU-pipe instructions per input byte and keeps every WARP autonomous.  A warp
-// owns windows of 2048 staged bytes (1952 owned + 32 left / 64 right halo), fetched by ONE 1-D bulk async copy
-// (cp.async.bulk -> UBLKCP) onto a warp-private mbarrier, double buffered; there is no block barrier after set-up.
+// The reads are touched once, at HBM speed, so the kernel is bound by instruction issue and by the integer pipe
+// (LOP3 / SHF / PRMT / ISETP issue at half rate on sm_100): the design minimises instructions per input byte, moves
+// what it can to the FMA pipe (shifts as multiply-high) and keeps every WARP autonomous.  A warp owns windows of 4096
+// staged bytes (4000 owned + 32 left / 64 right halo), fetched by ONE 1-D bulk async copy (cp.async.bulk -> UBLKCP)
+// onto a warp-private mbarrier; there is no block barrier after set-up.  The bytes are only read in pass 1, so there is
+// ONE byte buffer per warp and the copy of the next window is issued right after pass 1; the derived arrays are what
+// is double buffered.  60 % of the windows are dealt to the warps up front (a contiguous range each), the rest goes by
+// ticket from one global counter, two windows per ticket, requested one window ahead.
 //
 //   pass 1   every lane turns 16 bytes into (a) one 32-bit word of 2-bit "gray" codes (byte >> 1) & 3 = A0 C1 T2 G3
 //            (AND + one multiply per 4 bytes), (b) a 16-bit mask of non-letter bytes (bit 6 clear: the read
-//            separator; sign-replicating PRMT + two DP4A), (c) one "bad group" bit: some byte is neither one of
-//            "ACGT" nor looks like a separator (bytes re-derived from their codes by PRMT look-ups, two words per
-//            look-up, compared with a DP4A sum of squares).  The three derived arrays (codes 512 B, masks 256 B,
-//            bad bits 16 B per window) stay in shared memory, double buffered; everything after pass 1 works on them;
+//            separator; two DP4A per 8 bytes), (c) one "bad group" bit: some byte is neither one of "ACGT" nor the
+//            separator (bytes re-derived from code << 1 | letter by PRMT look-ups, two words per look-up, and
+//            compared with the bytes themselves).  The three derived arrays (codes 1024 B, masks 512 B, bad bits 32 B
+//            per window) stay in shared memory; everything after pass 1 works on them;
 //   pass 2   code-run starts (candidates: min(max(m,2),4) equal codes, previous code differs) by funnel shifts on the
-//            code words; one shuffle prefix sum per window compacts them into a per-warp FIFO that is carried over
+//            code words (one copy of the rows per candidate length); every lane reserves room for its candidates in
+//            the warp's queue with one shared-memory atomic and pops its bits into it; the queue is carried over
 //            window boundaries, so phase B always runs on 32 candidates;
 //   phase B  one candidate per lane, no byte is touched: run end, both flanks (2k bits each) and the read-boundary
 //            test are funnel shifts over the derived arrays.  A separator anywhere in [s-k, e+k] rejects the tract
 //            (the reference's s >= k and e <= L-k-1 rules, hopo_counter.c:229, :232); a bad group in that span (N,
 //            lower case, U, IUPAC, a control byte ...), a run of 32+ codes or a non-letter that is not '\n' sends the
-//            candidate to the byte-exact slow path, which restates the reference loop literally.  Strand
-//            canonicalisation is a 64-bit bit reversal (:239-246).  Records are staged per warp and appended to the
-//            global array with one atomicAdd per ~50 records; the bin histogram of the partition plan
-//            (tjb_bucket.cuh) is accumulated here too.
+//            candidate to the byte-exact slow path, which restates the reference loop literally.  The fast path
+//            emits RAW observations (both flanks in gray codes, read orientation; tjb_common.cuh): the strand
+//            canonicalisation of :233-246 is done by the kernel that counts them (aggregate_kernel waits on L2 and
+//            has the issue slots; here they cost 7 % of the run time).  Records are staged per warp and appended to
+//            the global array with one atomicAdd per ~50 records.
 //
 // Windows own the code runs that START inside their owned bytes.
 #pragma once
+#include <type_traits>
 #include "tjb_common.cuh"
 
 
+#ifndef SCAN_WARPS
 #define SCAN_WARPS 8
+#endif
 #define SCAN_THREADS (SCAN_WARPS * 32)
 #ifndef SCAN_CTAS_PER_SM
 #define SCAN_CTAS_PER_SM 3
 #endif
 #ifndef SW_ROWS
-#define SW_ROWS 8                     // 16-byte groups per lane and window (even, <= 8)
+#define SW_ROWS 8                     // 16-byte groups per lane and window (8: the only geometry the tests cover)
 #endif
 #define SW_WIN (SW_ROWS * 512)        // staged bytes per window = SW_ROWS rows of 32 groups of 16 bytes
 #define SW_HALO_L 32                  // >= k, multiple of 16
@@ -48,13 +57,19 @@
 #define SW_G0 (SW_HALO_L / 16)        // owned groups [SW_G0, SW_G1)
 #define SW_G1 (SW_G0 + SW_TILE / 16)
 #ifndef SW_CHUNK
-#define SW_CHUNK (SW_ROWS >= 8 ? 2 : 4) // consecutive windows per ticket (power of two, >= 2)
+#define SW_CHUNK (SW_ROWS >= 8 ? 2 : 4) // consecutive windows per ticket (power of two)
 #endif
 #ifndef SW_QCAP
 #define SW_QCAP 512                   // candidate queue (linear; moved to the front when the next round may not fit)
 #endif
-#define SW_QUOTA 7                    // new candidates per lane and round: three bit planes of the ballot prefix sum
-#define SW_RCAP(W) ((W) == 2 ? 64 : 48) // staged records per warp (three CTAs of 8 warps must fit in 228 KB); flushed
+#define SW_QUOTA 7                    // new candidates per lane and round
+#ifndef SCAN_STATIC_PCT
+#define SCAN_STATIC_PCT 60            // share of the windows dealt to the warps up front (the rest goes by ticket)
+#endif
+#ifndef SW_RCAP2
+#define SW_RCAP2 64
+#endif
+#define SW_RCAP(W) ((W) == 2 ? SW_RCAP2 : 48) // staged records per warp (three CTAs of 8 warps must fit in 228 KB); flushed
                                       // when more than SW_RCAP - 32 are pending
 #define SCAN_GRAY_MUL 0x00820820u     // ((w & 0x06060606) * this) >> 24 = the four 2-bit codes of w's bytes
 #define SCAN_GRAY_LUT 0x47544341u     // code -> byte: 'A' 'C' 'T' 'G'
@@ -70,6 +85,7 @@ template <int W> struct ScanWarpSmem {
   u32 bad[2][SW_ROWS + 4];            // bit g = group g holds a byte that is neither ACGT nor separator-like
   alignas (16) u64 rec[SW_RCAP (W) * W];
   unsigned long long bar;             // mbarrier of the raw bytes
+  u32 qtail, qpad;                    // end of the candidate queue (the lanes reserve their entries with an atomic)
   unsigned short cand[SW_QCAP];       // candidates: stage << 15 | row pair << 10 | lane << 5 | bit (see pass 2)
 };
 static_assert (sizeof (ScanWarpSmem<2>) % 16 == 0 && sizeof (ScanWarpSmem<3>) % 16 == 0, "warp slices must stay 16-byte aligned");
@@ -129,16 +145,6 @@ __device__ __forceinline__ u64 codes_at (const u32 *codes, int p)
   return ((u64) __funnelshift_r (a1, a2, sh) << 32) | __funnelshift_r (a0, a1, sh);
 }
 
-// reverse complement of a k-base word of GRAY codes (A0 C1 T2 G3, base j in bits 2j..2j+1), as BINARY codes
-// (A0 C1 G2 T3).  The bit reversal also swaps the two bits of every base: a base (h, l) arrives as (l, h).  Its
-// binary code is (h, h ^ l), the complement of that (~h, ~(h ^ l)): the high bit from the swapped low bit, the low
-// bit from the XOR of both.
-__device__ __forceinline__ u64 revcomp_gray (u64 g, int k, u64 kmask)
-{
-  const u64 y = __brevll (g) >> (64 - 2 * k); // k >= 2
-  const u64 m5 = 0x5555555555555555ULL;
-  return ~(((y & m5) << 1) | ((y ^ (y >> 1)) & m5)) & kmask;
-}
 __device__ __forceinline__ u32 prmt (u32 a, u32 b, u32 sel)
 {
   u32 d;
@@ -157,12 +163,13 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
   uint8_t *s_lutf = scan_smem + SCAN_WARPS * sizeof (ScanWarpSmem<W>), *s_lutr = s_lutf + 256;
 
   const int tid = threadIdx.x, lane = tid & 31;
-  {
-    const int f = tjb_code_fwd (tid); // SCAN_THREADS == 256
-    s_lutf[tid] = (uint8_t) f;
-    s_lutr[tid] = (uint8_t) (f < 4 ? 3 - f : f);
+  for (int i = tid; i < 256; i += SCAN_THREADS) {
+    const int f = tjb_code_fwd (i);
+    s_lutf[i] = (uint8_t) f;
+    s_lutr[i] = (uint8_t) (f < 4 ? 3 - f : f);
   }
   if (lane == 0) {
+    S->qtail = 0;
     mbar_init (&S->bar, 1);
     asm volatile ("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -171,7 +178,6 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
   // into integer-pipe shifts / logic
   const u32 kq0 = (u32) ((unsigned long long) n >> 62);
   const u32 kq4 = 16u + kq0, kq16 = (1u << 16) + kq0, kq26 = (1u << 26) + kq0, kq30 = (1u << 30) + kq0, kq31 = (1u << 31) + kq0;
-  const u32 kqm1 = 0xffffffffu + kq0;
   const u64 kmask = (k == 32) ? ~0ULL : ((1ULL << (2 * k)) - 1);
   __syncthreads (); // the only block-wide barrier: LUTs and mbarriers are set up
 
@@ -256,11 +262,11 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
           const u32 m2 = __funnelshift_r (n2, n3, sh) & low_mask (nspan - 64);
           if (!(m0 | m1 | m2)) {
             const u64 gl64 = codes_at (codes, P) & kmask, gr64 = codes_at (codes, s + len) & kmask;
-            const u64 m5 = 0x5555555555555555ULL;
-            u64 ctx0, ctx1;
-            if (gray < 2) { ctx0 = gl64 ^ ((gl64 >> 1) & m5); ctx1 = gr64 ^ ((gr64 >> 1) & m5); } // A / C tract: forward strand, gray -> A0 C1 G2 T3, :233-238
-            else { ctx0 = revcomp_gray (gr64, k, kmask); ctx1 = revcomp_gray (gl64, k, kmask); } // T / G tract: reverse complement, :239-246
-            r = pack_rec<W> (ctx0, ctx1, gray & 1, sext_field (len, 10), gray < 2 ? 1 : 2, k);
+            // two-word records leave the strand canonicalisation to the kernel that counts them (measured: configs[1]
+            // 191 -> 178 us); with three-word records (k >= 27) the same change made the scan slower (configs[4] 1.30 ->
+            // 1.75 ms), so they are written in their final form
+            if (SCAN_RAW_OBS && W == 2) r = pack_obs<W> (gl64, gr64, gray, len); // len < 32: the 10-bit field holds it as it is
+            else r = canon_from_gray<W> (gl64, gr64, gray, len, k);
             emit = true;
           }
         }
@@ -346,19 +352,31 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
   // windows are handed out by a global ticket counter (SMs on the two dies do not run at the same speed, a static
   // deal leaves a tail); the ticket of the window after next is requested one window ahead, its latency is hidden
   // (SW_CHUNK consecutive windows per ticket: one counter served 258 K atomics in 250 us and its latency showed)
-  u32 t_cur = 0, t_nxt = 0, t_fut = 0;
+  // SCAN_STATIC_PCT: that share of the windows is dealt up front, a contiguous range per warp, and only the rest goes by
+  // ticket (a quarter of the atomics on the one counter, and their answers come back sooner)
+  u32 t_cur = 0, t_nxt = 0, t_fut = 0, run_end = 0; // run_end: end of the contiguous windows this warp holds
   bool want_ticket = false;
-  if (lane == 0) t_fut = atomicAdd (tile_ctr, 2u);
-  t_fut = __shfl_sync (0xffffffffu, t_fut, 0);
-  t_cur = t_fut * SW_CHUNK;
-  t_nxt = t_cur + 1;
-  t_fut++; // the second chunk of the first request
+  const u32 n_warps = gridDim.x * SCAN_WARPS;
+  const u32 n_static = (u32) (((unsigned long long) n_tiles * SCAN_STATIC_PCT / 100) / n_warps) & ~(u32) (SW_CHUNK - 1);
+  const u32 t_dyn0 = n_static * n_warps; // tickets count chunks from here on
+  if (n_static) {
+    if (lane == 0) t_fut = atomicAdd (tile_ctr, 1u); // the first chunk after the dealt range: asked for now, needed much later
+    t_cur = (blockIdx.x * SCAN_WARPS + (threadIdx.x >> 5)) * n_static;
+    run_end = t_cur + n_static;
+  } else {
+    if (lane == 0) t_fut = atomicAdd (tile_ctr, 2u);
+    t_fut = __shfl_sync (0xffffffffu, t_fut, 0);
+    t_cur = t_fut * SW_CHUNK;
+    run_end = t_cur + SW_CHUNK;
+    t_fut++; // the second chunk of the first request
+  }
+  if (t_cur + 1 < run_end) t_nxt = t_cur + 1;
+  else { t_nxt = t_dyn0 + __shfl_sync (0xffffffffu, t_fut, 0) * SW_CHUNK; run_end = t_nxt + SW_CHUNK; want_ticket = true; }
   long long g0 = (long long) t_cur * SW_TILE - SW_HALO_L, old_g0 = 0;
   int st = 0;
   bool in_cur = false;
   if (t_cur < n_tiles) { in_cur = interior (t_cur); stage_tile (t_cur); }
   const u32 hdr = (u32) lane << 5;
-  const u32 lt_lanes = (1u << lane) - 1;
   // the queue is linear: what is left moves to the front only when the next round might not fit behind it
   auto queue_to_front = [&] () {
     const u32 cnt = tail - head; // < 32
@@ -366,6 +384,7 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
     __syncwarp ();
     if (lane < (int) cnt) S->cand[lane] = v;
     head = 0; tail = cnt;
+    if (lane == 0) S->qtail = cnt;
     __syncwarp ();
   };
   for (; t_cur < n_tiles; st ^= 1) {
@@ -394,11 +413,11 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
         const u32 z23 = mad_hi (a3, kq30, mad_hi (a2, kq26, m3 * kq4 + m2));
         const u32 xa = prmt (SCAN_LUT_A, SCAN_LUT_B, z01), xb = prmt (SCAN_LUT_A, SCAN_LUT_B, __umulhi (z01, kq16));
         const u32 xc = prmt (SCAN_LUT_A, SCAN_LUT_B, z23), xd = prmt (SCAN_LUT_A, SCAN_LUT_B, __umulhi (z23, kq16));
-        // the bytes their codes stand for, against the bytes themselves (word differences: zero iff equal), then the
-        // sum of the squared bytes of the differences over the group
-        const u32 d0 = prmt (xa, xb, 0x6420) * kqm1 + w0, d1 = prmt (xa, xb, 0x7531) * kqm1 + w1;
-        const u32 d2 = prmt (xc, xd, 0x6420) * kqm1 + w2, d3 = prmt (xc, xd, 0x7531) * kqm1 + w3;
-        const u32 acc = __dp4a (d0, d0, __dp4a (d1, d1, __dp4a (d2, d2, __dp4a (d3, d3, 0u))));
+        // the bytes their codes stand for, against the bytes themselves: (expected ^ byte) | ... over the group (the
+        // compiler makes it four compare-and-or instructions; a multiply-add / DP4A form on the FMA pipe took twice as many)
+        const u32 e01 = (prmt (xa, xb, 0x6420) ^ w0) | (prmt (xa, xb, 0x7531) ^ w1);
+        const u32 e23 = (prmt (xc, xd, 0x6420) ^ w2) | (prmt (xc, xd, 0x7531) ^ w3);
+        const u32 acc = e01 | e23;
         // bit j of the mask = byte j is a non-letter: 64 * (255 - sum of the weights of the letters), bytes are 0x40 / 0
         const int lo8 = dp4a_us (a1, 0x80C0E0F0u, dp4a_us (a0, 0xF8FCFEFFu, 255 * 64));
         const int hi8 = dp4a_us (a3, 0x80C0E0F0u, dp4a_us (a2, 0xF8FCFEFFu, 255 * 64));
@@ -416,19 +435,26 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
     u32 cb[SW_ROWS / 2];
 #pragma unroll
     for (int j = 0; j < SW_ROWS / 2; j++) cb[j] = 0;
+    // one copy of the rows per candidate length (2, 3, 4): no test of cand_len inside them
+    auto pass2 = [&] (auto cl) {
+      constexpr int CL = decltype (cl)::value;
 #pragma unroll
-    for (int row = 0; row < SW_ROWS; row++) {
-      const int grp = row * 32 + lane;
-      const u32 cc = c[row], cn = codes[(grp + 1) & (SW_GROUPS - 1)], cp = codes[(grp - 1) & (SW_GROUPS - 1)];
-      u32 tt = cc ^ __funnelshift_r (cc, cn, 2);
-      if (cand_len >= 3) tt |= cc ^ __funnelshift_r (cc, cn, 4);
-      if (cand_len >= 4) tt |= cc ^ __funnelshift_r (cc, cn, 6);
-      const u32 dp = cc ^ __funnelshift_l (cp, cc, 2);
-      u32 cs = ~(tt | __umulhi (tt, kq31)) & (dp | __umulhi (dp, kq31)) & 0x55555555u; // x >> 1 on the FMA pipe
-      if (row == 0 && lane < SW_G0) cs = 0;                       // halo groups are owned by the neighbouring windows
-      if (row == SW_ROWS - 1 && lane >= SW_G1 - 32 * (SW_ROWS - 1)) cs = 0;
-      cb[row >> 1] |= cs << (row & 1);
-    }
+      for (int row = 0; row < SW_ROWS; row++) {
+        const int grp = row * 32 + lane;
+        const u32 cc = c[row], cn = codes[(grp + 1) & (SW_GROUPS - 1)], cp = codes[(grp - 1) & (SW_GROUPS - 1)];
+        u32 tt = cc ^ __funnelshift_r (cc, cn, 2);
+        if (CL >= 3) tt |= cc ^ __funnelshift_r (cc, cn, 4);
+        if (CL >= 4) tt |= cc ^ __funnelshift_r (cc, cn, 6);
+        const u32 dp = cc ^ __funnelshift_l (cp, cc, 2);
+        u32 cs = ~(tt | __umulhi (tt, kq31)) & (dp | __umulhi (dp, kq31)) & 0x55555555u; // x >> 1 on the FMA pipe
+        if (row == 0 && lane < SW_G0) cs = 0;                       // halo groups are owned by the neighbouring windows
+        if (row == SW_ROWS - 1 && lane >= SW_G1 - 32 * (SW_ROWS - 1)) cs = 0;
+        cb[row >> 1] |= cs << (row & 1);
+      }
+    };
+    if (cand_len >= 4) pass2 (std::integral_constant<int, 4> ());
+    else if (cand_len == 3) pass2 (std::integral_constant<int, 3> ());
+    else pass2 (std::integral_constant<int, 2> ());
     // ---- compaction into the queue (at most SW_QUOTA per lane and round); full batches of 32 go to phase B ------
     for (;;) {
       if (tail + 32 * SW_QUOTA > SW_QCAP) queue_to_front ();
@@ -436,12 +462,14 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
 #pragma unroll
       for (int j = 0; j < SW_ROWS / 2; j++) have += __popc (cb[j]);
       const int mine = have < SW_QUOTA ? have : SW_QUOTA;
-      // prefix sum over the lanes from the ballots of the three bits of the counts
-      const u32 b0 = __ballot_sync (0xffffffffu, mine & 1), b1 = __ballot_sync (0xffffffffu, mine & 2), b2 = __ballot_sync (0xffffffffu, mine & 4);
       const bool capped = __any_sync (0xffffffffu, have > SW_QUOTA); // rare: some lane keeps candidates for another round
-      const int total = __popc (b0) + 2 * __popc (b1) + 4 * __popc (b2);
+      // every lane reserves its entries with one shared-memory atomic on the warp's tail (their order within a round
+      // does not matter); the new tail is read back after the entries are written
+      int total = 1;
+      u32 pos = 0;
+      if (mine) pos = atomicAdd (&S->qtail, (u32) mine);
       if (total) {
-        unsigned short *qp = S->cand + tail + (u32) (__popc (b0 & lt_lanes) + 2 * __popc (b1 & lt_lanes) + 4 * __popc (b2 & lt_lanes));
+        unsigned short *qp = S->cand + pos;
         if (!capped) {
 #pragma unroll
           for (int j = 0; j < SW_ROWS / 2; j++) {
@@ -460,8 +488,8 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
             cb[j] = m;
           }
         }
-        tail += (u32) total;
         __syncwarp ();
+        tail = *reinterpret_cast<volatile u32*> (&S->qtail);
         while (tail - head >= 32) {
           process_batch ((int) S->cand[head + lane], st, g0, old_g0);
           head += 32;
@@ -481,8 +509,8 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
     n_old = tail - head; // what is left (< 32 candidates) waits for the next window
     old_g0 = g0;
     t_cur = t_nxt;
-    if ((t_nxt & (SW_CHUNK - 1)) != SW_CHUNK - 1) t_nxt++;
-    else { t_nxt = __shfl_sync (0xffffffffu, t_fut, 0) * SW_CHUNK; want_ticket = true; }
+    if (t_nxt + 1 < run_end) t_nxt++;
+    else { t_nxt = t_dyn0 + __shfl_sync (0xffffffffu, t_fut, 0) * SW_CHUNK; run_end = t_nxt + SW_CHUNK; want_ticket = true; }
     g0 = (long long) t_cur * SW_TILE - SW_HALO_L;
   }
   if (tail != head) // what is left belongs to the last window, whose bytes are still staged

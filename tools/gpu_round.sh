@@ -36,8 +36,8 @@ PY
   NCU="ncu --set full --clock-control none --import-source on"
   if timeout 300 python /tmp/one_sample.py > gpurun_out/one_sample.log 2>&1; then
     # third sample of the context: sizes settled.  One capture per kernel of the step
-    ( timeout 900 $NCU -k regex:tjb_scan_kernel --launch-skip 2 --launch-count 1 -o gpurun_out/r02_scan -f python /tmp/one_sample.py ) > gpurun_out/ncu_scan.log 2>&1
-    ( timeout 900 $NCU -k regex:"aggregate_kernel|wpartition_kernel|wbucket_reduce_kernel|pack_kernel|plan_kernel|totals_kernel" --launch-skip 12 --launch-count 6 -o gpurun_out/r02_reduce -f python /tmp/one_sample.py ) > gpurun_out/ncu_reduce.log 2>&1
+    ( timeout 900 $NCU -k regex:tjb_scan_kernel --launch-skip 2 --launch-count 1 -o gpurun_out/r02b_scan -f python /tmp/one_sample.py ) > gpurun_out/ncu_scan.log 2>&1
+    ( timeout 900 $NCU -k regex:"aggregate_kernel|wpartition_kernel|wbucket_reduce_kernel|pack_kernel|plan_kernel|totals_kernel" --launch-skip 12 --launch-count 6 -o gpurun_out/r02b_reduce -f python /tmp/one_sample.py ) > gpurun_out/ncu_reduce.log 2>&1
   fi
   ls -la gpurun_out/*.ncu-rep
 fi
