@@ -190,6 +190,7 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
   const u32 t_last_interior = t_int > 0xffffffffLL ? 0xffffffffu : (u32) t_int;
   auto interior = [&] (u32 t) { return t >= 1u && t <= t_last_interior; };
   // the caller has made sure (__syncwarp) that every lane is done reading the previous window's bytes
+  u32 run_end = 0; // end of the contiguous windows this warp holds (see the main loop)
   auto stage_tile = [&] (u32 t) {
     const long long g0 = (long long) t * SW_TILE - SW_HALO_L;
     if (interior (t)) {
@@ -241,9 +242,7 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
       const u64 win = codes_at (codes, s); // codes s .. s+31
       gray = (int) ((u32) win & 3u);
       const u32 pat = (u32) gray * 0x55555555u;
-      u32 x0 = (u32) win ^ pat, x1 = (u32) (win >> 32) ^ pat;
-      x0 = (x0 | (x0 >> 1)) & 0x55555555u;
-      x1 = (x1 | (x1 >> 1)) & 0x55555555u;
+      const u32 x0 = (u32) win ^ pat, x1 = (u32) (win >> 32) ^ pat; // lowest set bit: either bit of the first code that differs
       const int len = x0 ? ((__ffs (x0) - 1) >> 1) : (x1 ? 16 + ((__ffs (x1) - 1) >> 1) : 32);
       if (len >= 32) slow = true; // long run: may leave the window
       else if (len >= min_len) {
@@ -354,7 +353,7 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
   // (SW_CHUNK consecutive windows per ticket: one counter served 258 K atomics in 250 us and its latency showed)
   // SCAN_STATIC_PCT: that share of the windows is dealt up front, a contiguous range per warp, and only the rest goes by
   // ticket (a quarter of the atomics on the one counter, and their answers come back sooner)
-  u32 t_cur = 0, t_nxt = 0, t_fut = 0, run_end = 0; // run_end: end of the contiguous windows this warp holds
+  u32 t_cur = 0, t_nxt = 0, t_fut = 0;
   bool want_ticket = false;
   const u32 n_warps = gridDim.x * SCAN_WARPS;
   const u32 n_static = (u32) (((unsigned long long) n_tiles * SCAN_STATIC_PCT / 100) / n_warps) & ~(u32) (SW_CHUNK - 1);

@@ -8,7 +8,7 @@ for lib in tatajuba_b200/lib/libtjb_gpu.so tatajuba_b200/lib/libtjb_gpu_*.so; do
   [ -f "$lib" ] || continue
   echo "== $lib $*" >> gpurun_out/variants.log
   for rep in 1 2; do
-    ( TJB_LIB=$PWD/$lib timeout 300 python tools/prof_step.py --steps 6 --stats "$@" ) 2>&1 | grep -E "tjb_scan|aggregate|n_raw" >> gpurun_out/variants.log
+    ( TJB_LIB=$PWD/$lib timeout 300 python tools/prof_step.py --steps 6 --stats "$@" ) 2>&1 | grep -E "tjb_scan|aggregate|pack_kernel|n_raw" >> gpurun_out/variants.log
   done
 done
 cat gpurun_out/variants.log
