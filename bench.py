@@ -419,6 +419,8 @@ def main():
                                         kernel_table, k=32, m=3, steps=max(3, args.steps // 2))
         extra["c5"]["workload"] = "configs[4]: k=32 (3-word records), m=3, 300x of a 5 Mbp genome = 1.5 Gbases"
         del c5
+    if "c5" in args.legs and world > 1:
+        extra["c5_sharded"] = c5_sharded_leg(ctx, rank, world, timed, all_ranks_ok)
     if "c4" in args.legs:
         extra["c4"] = c4_leg(ctxs, rank, world, timed, all_ranks_ok, args)
     if "exchange" in args.legs:
@@ -526,12 +528,58 @@ def single_sample_leg(ctxs, opt, buf, args, timed, count_steps, kernel_table, k=
     return leg
 
 
+def c5_sharded_leg(ctx, rank, world, timed, all_ranks_ok):
+    """BASELINE configs[4] (k=32, m=3, 300x of 5 Mbp = 1.5 Gbases) as ONE sample split by read over the ranks (SURVEY.md
+    8e "by read chunk within a sample"): every rank scans its chunk from HBM into its own table, the tables cross NVLink
+    as rows (one NCCL allgather), every rank adds the others' rows and finalises the complete table.  Strong scaling:
+    the sample is the same at every N.  Parity: every rank's result against its own one-GPU count of the whole sample
+    (which the N = 1 `c5` leg compares with the compiled reference)."""
+    import numpy as np
+    import torch
+    from oracle import pyoracle
+    from tatajuba_b200 import TatajubaOptions, genome_set, synth
+    opt5 = TatajubaOptions(32, 3, 5, True, paired_end=True)
+    buf = synth.sample_buffer(GENOME, 300, seed=3)
+    n_bases = n_bases_of(buf)
+    rows = buf.reshape(-1, READ_LEN + 1)
+    lo, hi = rows.shape[0] * rank // world, rows.shape[0] * (rank + 1) // world
+    chunk = torch.from_numpy(np.ascontiguousarray(rows[lo:hi]).reshape(-1)).cuda()
+    whole = torch.from_numpy(buf).cuda()
+    ctx.set_result_mode(True)
+    one = ctx.count_device(whole.data_ptr(), whole.numel(), opt5)
+    want = pyoracle.Boundary(one.status, one.n_raw, one.elem.copy(), one.idx_initial.copy(), one.idx_final.copy(), one.coverage)
+    ms_one = min(timed(lambda: ctx.count_device(whole.data_ptr(), whole.numel(), opt5))[0] for _ in range(3))
+    del whole
+
+    def run():
+        return genome_set.count_sample_sharded(ctx, chunk.data_ptr(), chunk.numel(), opt5, total_bytes_hint=buf.size)
+    got = run()
+    ok = True
+    try:
+        pyoracle.assert_same_boundary(pyoracle.Boundary(got.status, got.n_raw, got.elem, got.idx_initial, got.idx_final, got.coverage),
+                                      want, f"rank {rank}: configs[4] in {world} read chunks against one GPU")
+    except AssertionError as e:
+        ok = False
+        print(f"[bench] {e}", file=sys.stderr)
+    if not all_ranks_ok(ok):
+        raise SystemExit("bench: configs[4] sharded by read chunk differs from the one-GPU result")
+    run()
+    ms = min(timed(run, "c5_sharded" if i == 0 else None)[0] for i in range(3))
+    return {"workload": "configs[4] as ONE sample split by read over the ranks: k=32, m=3, 300x of a 5 Mbp genome = 1.5 Gbases",
+            "scaling": "strong", "ranks": world, "ms_per_sample": ms, "value": n_bases / (ms * 1e-3), "unit": "bases/s",
+            "one_gpu_ms_per_sample": ms_one, "speedup_over_one_gpu": ms_one / ms,
+            "exchange": "table rows, one nccl all_gather_into_tensor, device to device; QC / groups / coverage on the complete table on every rank",
+            "parity": "every rank against its own one-GPU count of the whole sample (that count against the reference: the c5 leg at N = 1)",
+            "n_raw": int(got.n_raw), "n_elem": int(got.n_elem)}
+
+
 def c4_leg(ctxs, rank, world, timed, all_ranks_ok, args):
     """BASELINE configs[3]: 96 samples of a 1.7 Mbp population (5 % of the tracts differ between samples), 50x PE.  Strong
     scaling: the samples are dealt to the ranks, every rank deals ITS samples dynamically to its contexts (reads in
     pinned host memory: H2D inside), then the query rows are exchanged (one allgather, GPU to GPU) and every rank
     computes the union of the mapper queries; rank 0 runs the cross-sample merge (tjb_merge_tracts) on a stand-in
-    post-mapper table.  Everything between the first sample and the merged tract ids is inside the timed region."""
+    post-mapper table.  Two timed parts, added up: first sample -> union, and the merge; building the stand-in tables
+    (in place of the mapper) happens between them and is not timed."""
     import torch
     from tatajuba_b200 import Context, TatajubaOptions, genome_set
     opt = TatajubaOptions(K, M, MIN_COV, True, paired_end=True)
@@ -568,7 +616,8 @@ def c4_leg(ctxs, rank, world, timed, all_ranks_ok, args):
 
     stages = {}
 
-    def job(from_host=True):
+    def front(from_host=True):
+        """count of every sample -> query rows on the device -> allgather -> union of the mapper queries"""
         rows = {}
         t0 = time.perf_counter()
 
@@ -584,35 +633,51 @@ def c4_leg(ctxs, rank, world, timed, all_ranks_ok, args):
         t2 = time.perf_counter()
         uni, idx = genome_set.union_queries_device(ctx, all_rows, K)
         t3 = time.perf_counter()
-        n_concat = 0
-        if rank == 0:  # stand-in post-mapper tables: one histogram per union row a sample has, located by the row's rank
-            tables, off, idx_h = [], 0, idx.cpu().numpy()
-            for n in sizes:
-                loc = (np.sort(idx_h[off:off + n]) * 8).astype(np.int32)  # tracts 8 bp apart: neighbours are different tracts
-                off += n
-                tables.append({"location": loc, "base": np.zeros(n, np.int32), "mode_context_length": np.full(n, 4, np.int32),
-                               "name": np.zeros((n, 1), np.uint8)})
-            t_prep = time.perf_counter()
-            n_concat = len(genome_set.merge_tracts(tables, 2)[0])
-        t4 = time.perf_counter()
-        stages[from_host] = {"count_samples": (t1 - t0) * 1e3, "allgather": (t2 - t1) * 1e3, "union": (t3 - t2) * 1e3,
-                             "merge_tracts_rank0": (t4 - t3) * 1e3}
-        if rank == 0:  # of which: building the stand-in tables in Python (96 sorts), the rest is genome_set.merge_tracts
-            stages[from_host]["merge_tracts_rank0_standin_tables"] = (t_prep - t3) * 1e3
-        return int(uni.shape[0]), int(sum(sizes)), n_concat
-    best_by_mode = {}
+        stages[from_host] = {"count_samples": (t1 - t0) * 1e3, "allgather": (t2 - t1) * 1e3, "union": (t3 - t2) * 1e3}
+        return uni, idx, sizes
+
+    def standin_tables(idx, sizes):
+        """NOT timed (it stands in for the mapper, which is out of scope): post-mapper tables for rank 0's merge, one
+        histogram per union row a sample has, located by the row's rank in the union"""
+        if rank != 0:
+            return None
+        tables, off, idx_h = [], 0, idx.cpu().numpy()
+        for n in sizes:
+            loc = (np.sort(idx_h[off:off + n]) * 8).astype(np.int32)  # tracts 8 bp apart: neighbours are different tracts
+            off += n
+            tables.append({"location": loc, "base": np.zeros(n, np.int32), "mode_context_length": np.full(n, 4, np.int32),
+                           "name": np.zeros((n, 1), np.uint8)})
+        return tables
+
+    def back(tables):
+        """the cross-sample merge of the tract ids (tjb_merge_tracts: host code, rank 0, all host threads)"""
+        return len(genome_set.merge_tracts(tables, 2)[0]) if rank == 0 else 0
+
+    best_by_mode, front_by_mode, back_by_mode = {}, {}, {}
+    out = None
     for from_host in (False, True):
-        job(from_host)
-        best, out = None, None
+        front(from_host)
+        best = None
         for _ in range(3):
-            ms, out = timed(lambda: job(from_host))
-            best = ms if best is None else min(best, ms)
+            ms_f, (uni, idx, sizes) = timed(lambda: front(from_host))
+            tables = standin_tables(idx, sizes)
+            ms_b, n_concat = timed(lambda: back(tables))
+            if best is None or ms_f + ms_b < best:
+                best, front_by_mode[from_host], back_by_mode[from_host] = ms_f + ms_b, ms_f, ms_b
+                stages[from_host]["merge_tracts_rank0"] = ms_b
+                kept = dict(stages[from_host])
+            out = (int(uni.shape[0]), int(sum(sizes)), n_concat)
+        stages[from_host] = kept
         best_by_mode[from_host] = best
     best = best_by_mode[False]
     return {"workload": f"configs[3]: {C4_SAMPLES} samples x {C4_GENOME / 1e6:.1f} Mbp x {C4_COVERAGE}x PE, tract polymorphism on {C4_FRACTION:.0%} of the tracts",
             "scaling": "strong (the 96 samples are dealt to the ranks)", "ms": best, "value": bases_total / (best * 1e-3), "unit": "bases/s",
             "samples_per_rank": len(mine), "contexts_per_gpu": len(ctxs), "bases_total": bases_total, "parity": parity,
-            "inside": "count of every sample (reads resident in HBM), query rows on the device, allgather, union of mapper queries, merge of tract ids (rank 0)",
+            "inside": "count of every sample (reads resident in HBM), query rows on the device, allgather, union of mapper queries, merge of tract ids (rank 0, host code); "
+                      "the stand-in post-mapper tables are built between the two timed parts, outside them",
+            "device_span": {"ms": front_by_mode[False], "value": bases_total / (front_by_mode[False] * 1e-3), "unit": "bases/s",
+                            "what": "count + query rows + allgather + union: the part that runs on the GPUs and shards over them"},
+            "merge_rank0_ms": back_by_mode[False],
             "stages_ms": {k: round(v, 2) for k, v in stages[False].items()},
             "from_host": {"ms": best_by_mode[True], "stages_ms": {k: round(v, 2) for k, v in stages[True].items()}, "value": bases_total / (best_by_mode[True] * 1e-3), "unit": "bases/s",
                           "note": "the same with the reads of every sample in pinned host memory: H2D inside"},

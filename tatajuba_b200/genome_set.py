@@ -147,22 +147,35 @@ def allgather_tables_device(local_tables, n_samples, group=None):
     dist.all_gather_into_tensor(all_counts, counts.to(dev), group=group)
     all_counts = all_counts.cpu().numpy().reshape(world, per_rank)
     pad_rows = max(int(all_counts.sum(axis=1).max()), 1)
-    send = torch.zeros((pad_rows, ROW_WORDS), dtype=torch.int64, device=dev)
-    off = 0
-    for s in mine:
-        n = local_tables[s].shape[0]
-        send[off:off + n] = local_tables[s]
-        off += n
+    send = torch.empty((pad_rows, ROW_WORDS), dtype=torch.int64, device=dev)  # the padding is never read
+    n_mine = int(all_counts[rank].sum())
+    if n_mine:
+        torch.cat([local_tables[s].reshape(-1, ROW_WORDS) for s in mine], out=send[:n_mine])
     recv = torch.empty((world, pad_rows, ROW_WORDS), dtype=torch.int64, device=dev)
     dist.all_gather_into_tensor(recv.view(-1), send.view(-1), group=group)
-    pieces, sizes = [None] * n_samples, [0] * n_samples
+    shift, sizes = gather_plan(all_counts, n_samples, world, pad_rows)
+    total = int(sizes.sum())
+    if total == 0:
+        return torch.empty((0, ROW_WORDS), dtype=torch.int64, device=dev), [0] * n_samples
+    meta = torch.from_numpy(np.stack([shift, sizes])).to(dev)
+    index = torch.repeat_interleave(meta[0], meta[1], output_size=total) + torch.arange(total, dtype=torch.int64, device=dev)
+    return recv.view(-1, ROW_WORDS).index_select(0, index), [int(x) for x in sizes]
+
+
+def gather_plan(all_counts, n_samples, world, pad_rows):
+    """Global sample order out of the rank-major receive buffer of the allgather with ONE gather.  all_counts[r, i] =
+    rows of the i-th sample of rank r; every rank's rows are contiguous from r * pad_rows.  Returns (shift, sizes), one
+    entry per sample in global order: output row p of sample s comes from receive row p + shift[s]."""
+    sizes, starts = np.zeros(n_samples, dtype=np.int64), np.zeros(n_samples, dtype=np.int64)
     for r in range(world):
-        off = 0
-        for i, s in enumerate(samples_of_rank(n_samples, r, world)):
-            n = int(all_counts[r, i])
-            pieces[s], sizes[s] = recv[r, off:off + n], n
-            off += n
-    return torch.cat(pieces), sizes
+        ids = samples_of_rank(n_samples, r, world)
+        if not ids:
+            continue
+        c = np.asarray(all_counts[r, :len(ids)], dtype=np.int64)
+        sizes[ids] = c
+        starts[ids] = r * pad_rows + np.concatenate(([0], np.cumsum(c)[:-1]))
+    out_first = np.concatenate(([0], np.cumsum(sizes)[:-1])) if n_samples else np.zeros(0, dtype=np.int64)
+    return starts - out_first, sizes
 
 
 def union_queries_device(ctx, d_rows, kmer_size):

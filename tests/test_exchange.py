@@ -131,3 +131,28 @@ def test_union_of_counted_samples(built, restatement):
     for a, b in zip(index, want_index):
         assert np.array_equal(a, b)
     ctx.close()
+
+
+@pytest.mark.parametrize("n_samples,world", [(96, 2), (96, 8), (5, 4), (3, 8), (7, 1)])
+def test_gather_plan_restores_the_global_sample_order(n_samples, world):
+    """the index arithmetic of allgather_tables_device (N > 1 ranks), on a simulated receive buffer"""
+    import torch
+    rng = np.random.default_rng(n_samples * 31 + world)
+    tabs = {s: torch.from_numpy(rng.integers(0, 1 << 40, (int(rng.integers(0, 50)), 3))) for s in range(n_samples)}
+    per_rank = (n_samples + world - 1) // world
+    all_counts = np.zeros((world, per_rank), dtype=np.int64)
+    for r in range(world):
+        for i, s in enumerate(genome_set.samples_of_rank(n_samples, r, world)):
+            all_counts[r, i] = tabs[s].shape[0]
+    pad_rows = max(int(all_counts.sum(axis=1).max()), 1)
+    recv = torch.full((world, pad_rows, 3), -1, dtype=torch.int64)
+    for r in range(world):
+        ids = genome_set.samples_of_rank(n_samples, r, world)
+        if ids and all_counts[r].sum():
+            recv[r, :int(all_counts[r].sum())] = torch.cat([tabs[s] for s in ids])
+    shift, sizes = genome_set.gather_plan(all_counts, n_samples, world, pad_rows)
+    total = int(sizes.sum())
+    index = torch.repeat_interleave(torch.from_numpy(shift), torch.from_numpy(sizes), output_size=total) + torch.arange(total)
+    got = recv.view(-1, 3).index_select(0, index)
+    assert torch.equal(got, torch.cat([tabs[s] for s in range(n_samples)]))
+    assert [int(x) for x in sizes] == [tabs[s].shape[0] for s in range(n_samples)]

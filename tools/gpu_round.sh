@@ -1,8 +1,8 @@
 #!/bin/bash
-# One-GPU round check (gpurun -- bash tools/gpu_round.sh [tests] [bench] [launches] [ncu]): the GPU tests, both bench arms,
+# One-GPU round check (gpurun -- bash tools/gpu_round.sh [tests] [bench] [launches] [ncu] [sanitize]): the GPU tests, both bench arms,
 # the ncu launch list of the bench command and one `ncu --set full` capture of every kernel of the step.  Each ncu pass
 # runs only after its own command has exited 0 without ncu; nothing printed under ncu is a bench value.
-what=${*:-tests bench launches ncu}
+what=${*:-tests bench launches ncu sanitize}
 mkdir -p gpurun_out
 has () { case " $what " in *" $1 "*) return 0;; esac; return 1; }
 if has tests; then
@@ -40,4 +40,11 @@ PY
     ( timeout 900 $NCU -k regex:"aggregate_kernel|wpartition_kernel|wbucket_reduce_kernel|pack_kernel|plan_kernel|totals_kernel" --launch-skip 12 --launch-count 6 -o gpurun_out/r02b_reduce -f python /tmp/one_sample.py ) > gpurun_out/ncu_reduce.log 2>&1
   fi
   ls -la gpurun_out/*.ncu-rep
+fi
+if has sanitize; then
+  # memcheck and racecheck over a small sample (every kernel of the step, the warp-private shared-memory protocols of the scan)
+  for tool in memcheck racecheck; do
+    ( timeout 900 compute-sanitizer --tool $tool --print-limit 20 python tools/prof_step.py --genome 300000 --coverage 30 --steps 2 ) > gpurun_out/sanitizer_$tool.log 2>&1
+    grep -E "ERROR SUMMARY|RACECHECK SUMMARY|n_raw" gpurun_out/sanitizer_$tool.log
+  done
 fi
