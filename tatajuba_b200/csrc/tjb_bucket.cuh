@@ -320,12 +320,20 @@ wpartition_kernel (AggTable tab, const u64 *__restrict__ ovf, unsigned long long
     unsigned long long c[PART_UNROLL];
 #pragma unroll
     for (int u = 0; u < PART_UNROLL; u++) { const size_t sl = s0 + u * stride; c[u] = sl < n_slots ? tab.cnt[sl] : 0ULL; }
+    // every step of an entry (key, bucket of its bin, cursor, stores) waits for the one before it: the steps of the
+    // PART_UNROLL entries of a thread are issued together, not entry after entry
+    Rec<W> key[PART_UNROLL];
+    u32 bkt[PART_UNROLL], pos[PART_UNROLL];
+#pragma unroll
+    for (int u = 0; u < PART_UNROLL; u++) if (c[u]) key[u] = table_key_at<W> (tab, (u32) (s0 + u * stride));
+#pragma unroll
+    for (int u = 0; u < PART_UNROLL; u++) if (c[u]) bkt[u] = lut[rec_bin<W> (key[u], k, F)];
+#pragma unroll
+    for (int u = 0; u < PART_UNROLL; u++) if (c[u]) pos[u] = atomicAdd (&cursor[(size_t) bkt[u] * BK_CURSOR_STRIDE], 1u);
 #pragma unroll
     for (int u = 0; u < PART_UNROLL; u++) {
       if (!c[u]) continue;
-      const Rec<W> key = table_key_at<W> (tab, (u32) (s0 + u * stride));
-      const u32 pos = atomicAdd (&cursor[(size_t) lut[rec_bin<W> (key, k, F)] * BK_CURSOR_STRIDE], 1u);
-      if (pos < list_cap) { store_rec<W> (wkey, pos, key); wcnt[pos] = c[u]; }
+      if (pos[u] < list_cap) { store_rec<W> (wkey, pos[u], key[u]); wcnt[pos[u]] = c[u]; }
       n_obs += (u32) c[u] + ((u32) (c[u] >> 32) & 0x7fffffffu);
     }
   }
@@ -338,9 +346,18 @@ wpartition_kernel (AggTable tab, const u64 *__restrict__ ovf, unsigned long long
     if (pos < list_cap) { store_rec<W> (wkey, pos, r); wcnt[pos] = c; }
     n_obs++;
   }
+  // one atomic per CTA on the sample's counter (9 K warps adding to one address took longer than the walk itself)
+  __shared__ unsigned long long s_obs[256 / 32];
 #pragma unroll
   for (int d = 16; d; d >>= 1) n_obs += __shfl_xor_sync (0xffffffffu, n_obs, d);
-  if ((threadIdx.x & 31) == 0 && n_obs) atomicAdd (&counters[CTR_NRAW], n_obs);
+  if ((threadIdx.x & 31) == 0) s_obs[threadIdx.x >> 5] = n_obs;
+  __syncthreads ();
+  if (threadIdx.x == 0) {
+    unsigned long long t = 0;
+#pragma unroll
+    for (int w = 0; w < 256 / 32; w++) t += s_obs[w];
+    if (t) atomicAdd (&counters[CTR_NRAW], t);
+  }
 }
 
 // ---------------------------------------------------------------------------------- bucket reduce --------
