@@ -2,7 +2,7 @@
 # One-GPU round check (gpurun -- bash tools/gpu_round.sh [tests] [bench] [launches] [ncu] [sanitize]): the GPU tests, both bench arms,
 # the ncu launch list of the bench command and one `ncu --set full` capture of every kernel of the step.  Each ncu pass
 # runs only after its own command has exited 0 without ncu; nothing printed under ncu is a bench value.
-what=${*:-tests bench launches ncu sanitize}
+what=${*:-tests bench launches ncu}
 mkdir -p gpurun_out
 has () { case " $what " in *" $1 "*) return 0;; esac; return 1; }
 if has tests; then
@@ -42,6 +42,7 @@ PY
   ls -la gpurun_out/*.ncu-rep
 fi
 if has sanitize; then
+  # (compute-sanitizer is closed on this pool: the step is not part of the default list)
   # memcheck and racecheck over a small sample (every kernel of the step, the warp-private shared-memory protocols of the scan)
   for tool in memcheck racecheck; do
     ( timeout 900 compute-sanitizer --tool $tool --print-limit 20 python tools/prof_step.py --genome 300000 --coverage 30 --steps 2 ) > gpurun_out/sanitizer_$tool.log 2>&1
