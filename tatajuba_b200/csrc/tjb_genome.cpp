@@ -393,6 +393,7 @@ void add_elem (Hist &h, const Elem &e, std::string &&name, int idx_match) // :18
 // (empirical_frequency.c:254-277 after the sort of :219 / :245)
 void make_histogram (std::vector<std::pair<int32_t, int32_t>> &v, int32_t *vmin, int32_t *vmax)
 {
+  if (v.size () == 1) { *vmin = *vmax = v[0].first; return; } // the common case: one tract length seen in this context
   std::sort (v.begin (), v.end ());
   std::vector<std::pair<int32_t, int32_t>> out;
   for (const auto &p : v) {
@@ -463,6 +464,7 @@ extern "C" int tjb_context_histograms (const tjb_hist_opts *opt, const void *ele
   if (!n_elem) return 0;
   const uint8_t *p = (const uint8_t*) elem;
   std::vector<Hist> hist;
+  hist.reserve ((size_t) n_elem); // most elements open a histogram of their own
   std::vector<uint32_t> tab;
   // 1. elements in location order against the last histogram (:237-268)
   for (int32_t i = 0; i < n_elem; i++) {
@@ -484,14 +486,14 @@ extern "C" int tjb_context_histograms (const tjb_hist_opts *opt, const void *ele
   }
   // 2. tract-length histogram of every context (:279-286); elements of weight 0 do not take part
   for (Hist &h : hist) {
-    std::vector<std::pair<int32_t, int32_t>> v;
-    for (const auto &b : h.bins) if (b.second) v.push_back (b);
+    auto &v = h.bins;
+    v.erase (std::remove_if (v.begin (), v.end (), [] (const std::pair<int32_t, int32_t> &b) { return b.second == 0; }), v.end ());
     if (v.empty ()) return TJB_ERR_ARG; // the reference stops with "vector of empirical frequencies with all freqs=0"
     make_histogram (v, &h.hmin, &h.hmax);
-    h.bins.swap (v);
   }
   // 3. neighbours that overlap are merged (:364-385); the list then keeps j entries, j being the index of the last one
   std::vector<Hist> merged;
+  merged.reserve (hist.size ());
   merged.push_back (std::move (hist[0]));
   for (size_t i = 1; i < hist.size (); i++) {
     if (hists_overlap (merged.back (), hist[i], opt->levenshtein_distance, tab)) accumulate (merged.back (), hist[i]);

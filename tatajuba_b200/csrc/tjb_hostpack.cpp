@@ -66,16 +66,6 @@ __attribute__ ((target ("avx2"))) static long pack_avx2 (const uint8_t *src, siz
     memcpy (packed + (i >> 2), &lo, 4);
     memcpy (packed + (i >> 2) + 4, &hi, 4);
     uint32_t bad = ~(uint32_t) _mm256_movemask_epi8 (ok);
-    // Every read ends in an exception (its separator), one per ~5 iterations at 150-base reads: a branch on `bad`
-    // mispredicts about that often.  The first exception of the 32 bytes is therefore written without a branch (a
-    // dummy entry when there is none, not committed); only a second one in the same 32 bytes takes the loop.
-    if (ne < cap) {
-      const int j = __builtin_ctz (bad | 0x80000000u);
-      exc_pos[ne] = pos0 + (uint32_t) (i + j);
-      exc_val[ne] = src[i + j];
-    } else if (bad) return -1;
-    ne += bad != 0;
-    bad &= bad - 1;
     while (bad) {
       const int j = __builtin_ctz (bad);
       bad &= bad - 1;
