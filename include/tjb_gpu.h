@@ -237,6 +237,11 @@ size_t tjb_noalloc_max_bytes (void);
 typedef struct tjb_reader tjb_reader;
 tjb_reader *tjb_reader_open (const char *path);
 int64_t tjb_reader_fill (tjb_reader *r, uint8_t *dst, size_t cap, int64_t *n_reads, int64_t *n_bases);
+/* a read longer than `cap`: tjb_reader_fill() first returns what the chunk holds, then TJB_ERR_TOO_LARGE; this call
+ * hands out the waiting read in the reader's own buffer (no '\n' behind it; valid until the next call on the reader) and
+ * returns its length (0: none waiting).  src/kseq.h:172-212 accepts reads of any length, and so does the file path of
+ * tjb_count_sample_files(): such a read is copied and scanned as a chunk of its own. */
+int64_t tjb_reader_take_long (tjb_reader *r, const uint8_t **seq, int64_t *n_reads, int64_t *n_bases);
 void tjb_reader_close (tjb_reader *r);
 
 /* the gzip stream under tjb_reader for regular .gz files (replaces gzopen / gzread of the reference's reader,

@@ -18,7 +18,7 @@ EXPORTS = [
     "tjb_count_sample_files", "tjb_count_sample_host", "tjb_count_sample_device", "tjb_count_sample",
     "tjb_counter_out_free", "tjb_ctx_set_result_mode", "tjb_device_count", "tjb_sample_begin", "tjb_sample_scan_device",
     "tjb_ctx_table_capacity", "tjb_ctx_reserve_entries",
-    "tjb_sample_export", "tjb_sample_import", "tjb_sample_finalise", "tjb_query_rows_device", "tjb_query_rows", "tjb_union_queries_device", "tjb_merge_tracts", "tjb_context_histograms", "tjb_context_table_free", "tjb_reader_open", "tjb_reader_fill", "tjb_reader_close",
+    "tjb_sample_export", "tjb_sample_import", "tjb_sample_finalise", "tjb_query_rows_device", "tjb_query_rows", "tjb_union_queries_device", "tjb_merge_tracts", "tjb_context_histograms", "tjb_context_table_free", "tjb_reader_open", "tjb_reader_fill", "tjb_reader_take_long", "tjb_reader_close",
     "tjb_gz_open", "tjb_gz_next", "tjb_gz_close", "tjb_tract_rows_noalloc", "tjb_noalloc_max_bytes",
 ]
 
@@ -136,6 +136,8 @@ def load():
     lib.tjb_reader_open.argtypes = [cp]
     lib.tjb_reader_fill.restype = i64
     lib.tjb_reader_fill.argtypes = [vp, vp, sz, C.POINTER(i64), C.POINTER(i64)]
+    lib.tjb_reader_take_long.restype = i64
+    lib.tjb_reader_take_long.argtypes = [vp, C.POINTER(vp), C.POINTER(i64), C.POINTER(i64)]
     lib.tjb_reader_close.argtypes = [vp]
     lib.tjb_reader_close.restype = None
     lib.tjb_gz_open.restype = vp

@@ -206,7 +206,10 @@ int64_t tjb_reader_fill (tjb_reader *r, uint8_t *dst, size_t cap, int64_t *n_rea
       if (rc == 0) break;
       r->seq_ready = 1;
     }
-    if (r->seq_len + 1 > cap) return TJB_ERR_TOO_LARGE; /* a single read larger than a whole chunk */
+    if (r->seq_len + 1 > cap) {                          /* a single read larger than a whole chunk: */
+      if (w) break;                                      /* what the chunk holds goes first, */
+      return TJB_ERR_TOO_LARGE;                          /* then the caller takes it with tjb_reader_take_long() */
+    }
     if (w + r->seq_len + 1 > cap) break;                 /* keep it for the next chunk */
     memcpy (dst + w, r->seq, r->seq_len);
     w += r->seq_len;
@@ -216,4 +219,18 @@ int64_t tjb_reader_fill (tjb_reader *r, uint8_t *dst, size_t cap, int64_t *n_rea
     r->seq_ready = 0;
   }
   return (int64_t) w;
+}
+
+/* After tjb_reader_fill() returned TJB_ERR_TOO_LARGE: the read that does not fit into a chunk, as it stands in the
+ * reader's own buffer (no separator behind it; valid until the next call on this reader).  The reference accepts reads of
+ * any length (src/kseq.h grows its string), e.g. an assembled genome given as a sample.  Returns its length, 0 when no
+ * read is waiting. */
+int64_t tjb_reader_take_long (tjb_reader *r, const uint8_t **seq, int64_t *n_reads, int64_t *n_bases)
+{
+  if (!r || !seq || !r->seq_ready) return 0;
+  *seq = r->seq;
+  r->seq_ready = 0;
+  if (n_reads) (*n_reads)++;
+  if (n_bases) (*n_bases) += (int64_t) r->seq_len;
+  return (int64_t) r->seq_len;
 }

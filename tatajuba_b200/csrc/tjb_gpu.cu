@@ -69,6 +69,7 @@ struct tjb_ctx {
   uint8_t *h_pinned[4] = {nullptr, nullptr, nullptr, nullptr}; // files path: two chunks per decoder thread
   cudaEvent_t h_free[4] = {nullptr, nullptr, nullptr, nullptr}; // pinned chunk i may be overwritten once this has fired
   DevBuf d_chunk[2];
+  DevBuf d_long;                             // a read longer than a chunk: copied and scanned on its own
   // host-buffer path with 2-bit packed transfers (tjb_hostpack.h): pinned and device staging per chunk slot
   uint8_t *h_pk[2] = {nullptr, nullptr}; uint32_t *h_exc_pos[2] = {nullptr, nullptr}; uint8_t *h_exc_val[2] = {nullptr, nullptr};
   DevBuf d_pk[2], d_exc_pos[2], d_exc_val[2];
@@ -847,7 +848,8 @@ table_import_kernel (const u64 *__restrict__ rows, unsigned long long n, int k, 
 }
 
 // ---- file feed: one decoder thread per FASTQ file, two pinned chunks each -----------------
-struct FeedSlot { uint8_t *pin = nullptr; cudaEvent_t free_ev = nullptr; int64_t got = 0; int state = 0; /* 0 empty, 1 full */ };
+struct FeedSlot { uint8_t *pin = nullptr; cudaEvent_t free_ev = nullptr; int64_t got = 0; int state = 0; /* 0 empty, 1 full */
+                  const uint8_t *long_read = nullptr; /* got bytes in the reader's own buffer instead of pin */ };
 struct FileFeed {
   std::mutex mu;
   std::condition_variable cv;
@@ -868,11 +870,21 @@ static void file_feed_worker (FileFeed *f, int p, tjb_reader *rd, int device)
     }
     cudaEventSynchronize (s.free_ev); // the copy engine has drained this pinned chunk (no-op before its first use)
     auto t0 = std::chrono::steady_clock::now ();
-    const int64_t got = tjb_reader_fill (rd, s.pin, TJB_CHUNK_BYTES, &f->n_reads[p], &f->n_bases[p]);
+    int64_t got = tjb_reader_fill (rd, s.pin, TJB_CHUNK_BYTES, &f->n_reads[p], &f->n_bases[p]);
+    const uint8_t *long_read = nullptr;
+    if (got == TJB_ERR_TOO_LARGE) { // a read longer than a chunk: handed over where it lies in the reader
+      const int64_t len = tjb_reader_take_long (rd, &long_read, &f->n_reads[p], &f->n_bases[p]);
+      if (len > 0) got = len; else long_read = nullptr;
+    }
     f->ms_decode[p] += std::chrono::duration<double, std::milli> (std::chrono::steady_clock::now () - t0).count ();
-    { std::lock_guard<std::mutex> lk (f->mu); s.got = got; s.state = 1; }
+    { std::lock_guard<std::mutex> lk (f->mu); s.got = got; s.long_read = long_read; s.state = 1; }
     f->cv.notify_all ();
     if (got <= 0) return;
+    if (long_read) { // the reader's buffer must stay as it is until the consumer has copied it
+      std::unique_lock<std::mutex> lk (f->mu);
+      f->cv.wait (lk, [&] { return s.state == 0 || f->abort; });
+      if (f->abort) return;
+    }
   }
 }
 
@@ -965,7 +977,7 @@ void tjb_ctx_destroy (tjb_ctx *ctx)
     if (ctx->h_exc_val[i]) cudaFreeHost (ctx->h_exc_val[i]);
   }
   DevBuf *bufs[] = {&ctx->d_pk[0], &ctx->d_pk[1], &ctx->d_exc_pos[0], &ctx->d_exc_pos[1], &ctx->d_exc_val[0], &ctx->d_exc_val[1],
-                    &ctx->d_chunk[0], &ctx->d_chunk[1], &ctx->tab, &ctx->recs, &ctx->ovf, &ctx->wkey, &ctx->wcnt, &ctx->okey,
+                    &ctx->d_chunk[0], &ctx->d_chunk[1], &ctx->d_long, &ctx->tab, &ctx->recs, &ctx->ovf, &ctx->wkey, &ctx->wcnt, &ctx->okey,
                     &ctx->hist, &ctx->ptmp, &ctx->heads, &ctx->pos, &ctx->seg, &ctx->drec, &ctx->dcount, &ctx->keep, &ctx->kpos, &ctx->krec,
                     &ctx->cw, &ctx->csum, &ctx->gkeep, &ctx->gkpos, &ctx->out40, &ctx->idx_i, &ctx->idx_f, &ctx->qrows, &ctx->out_cnt, &ctx->out_ii,
                     &ctx->out_if, &ctx->cov_tab, &ctx->uni_a, &ctx->uni_b, &ctx->b_bkt_start, &ctx->b_cursor, &ctx->b_koff, &ctx->b_ioff, &ctx->b_bstat};
@@ -1037,6 +1049,21 @@ int tjb_count_sample_device (tjb_ctx *ctx, const void *d_seqs, size_t n_bytes, c
   TRY (device_time (ctx, out));
   tr.mark ("post");
   return out->status;
+}
+
+// A read longer than a chunk (the reference accepts any length, src/kseq.h:172-212; e.g. an assembly given as a sample)
+// is copied into a device buffer of its own and scanned there; rare, so everything around it is synchronous.
+static int scan_long_read (tjb_ctx *ctx, const uint8_t *h_seq, size_t len)
+{
+  CU (cudaStreamSynchronize (ctx->stream));      // the buffer's previous user, if any, is done
+  CU (cudaStreamSynchronize (ctx->copy_stream));
+  TRY (ensure (ctx, ctx->d_long, len + 32));
+  CU (cudaMemsetAsync ((uint8_t*) ctx->d_long.p + len, '\n', 16, ctx->stream)); // the separator behind it
+  CU (cudaMemcpyAsync (ctx->d_long.p, h_seq, len, cudaMemcpyHostToDevice, ctx->stream));
+  ctx->h2d_bytes += (int64_t) len;
+  TRY (launch_scan (ctx, (const uint8_t*) ctx->d_long.p, len + 1));
+  CU (cudaStreamSynchronize (ctx->stream));      // the host memory may change hands after this call
+  return 0;
 }
 
 // cut [p, p+len) at the last '\n' so that a chunk always holds whole reads
@@ -1125,7 +1152,14 @@ int tjb_count_sample_host (tjb_ctx *ctx, const uint8_t *seqs, size_t n_bytes, co
     bool used[2] = {false, false};
     while (off < n_bytes) {
       size_t len = whole_reads_prefix (seqs + off, max_chunk < n_bytes - off ? max_chunk : n_bytes - off, n_bytes - off);
-      if (!len) { ctx->err = "a single read exceeds the chunk size"; return TJB_ERR_TOO_LARGE; }
+      if (!len) { // one read longer than a chunk: on its own, as it is
+        const size_t rest = n_bytes - off;
+        const void *nl = memchr (seqs + off + max_chunk, '\n', rest - max_chunk);
+        const size_t seq_len = nl ? (size_t) ((const uint8_t*) nl - (seqs + off)) : rest;
+        TRY (scan_long_read (ctx, seqs + off, seq_len));
+        off += nl ? seq_len + 1 : seq_len;
+        continue;
+      }
       long n_exc = -1;
       const bool plain_turn = plain_every && (chunk_no % plain_every) == plain_every - 1;
       if (packed && !plain_turn) {
@@ -1208,6 +1242,14 @@ static int count_files_once (tjb_ctx *ctx, const char *const *files, int n_files
     if (sl.got <= 0) { // end of this file (0) or a decode error (< 0)
       finished[p] = true; alive--;
       if (sl.got < 0) { rc = (int) sl.got; ctx->err = std::string ("decode failed: ") + files[p]; }
+      continue;
+    }
+    if (sl.long_read) {
+      rc = scan_long_read (ctx, sl.long_read, (size_t) sl.got);
+      if (rc >= 0 && cudaEventRecord (sl.free_ev, ctx->copy_stream) != cudaSuccess) rc = TJB_ERR_CUDA; // (the pinned slot was not used)
+      { std::lock_guard<std::mutex> lk (feed.mu); sl.state = 0; sl.long_read = nullptr; }
+      feed.cv.notify_all ();
+      turn[p] ^= 1;
       continue;
     }
     cudaError_t e = cudaSuccess;

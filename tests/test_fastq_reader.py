@@ -76,3 +76,48 @@ def test_record_rules_match_compiled_reference(tmp_path, reference, restatement,
         ref = reference.run_files([p], 25, 4, 1, False)
         ours, _, _ = decode(p)
         assert restatement.run_buffer(ours, 25, 4, 1, False).n_raw == ref.n_raw, i
+
+
+def decode_with_long_reads(path, cap):
+    """like decode(), for files with reads longer than the chunk: tjb_reader_fill() hands out what the chunk holds,
+    then TJB_ERR_TOO_LARGE (-5), and tjb_reader_take_long() the read itself"""
+    lib = _lib.load()
+    r = lib.tjb_reader_open(os.fsencode(path))
+    assert r
+    buf = np.empty(cap, dtype=np.uint8)
+    out, nr, nb, n_long = [], C.c_int64(0), C.c_int64(0), 0
+    while True:
+        got = lib.tjb_reader_fill(r, buf.ctypes.data, cap, C.byref(nr), C.byref(nb))
+        if got == -5:
+            q = C.c_void_p()
+            n = lib.tjb_reader_take_long(r, C.byref(q), C.byref(nr), C.byref(nb))
+            assert n + 1 > cap
+            out.append(C.string_at(q, n) + b"\n")
+            n_long += 1
+            continue
+        assert got >= 0
+        if got == 0:
+            break
+        out.append(buf[:got].tobytes())
+    assert lib.tjb_reader_take_long(r, C.byref(C.c_void_p()), None, None) == 0  # nothing waiting
+    lib.tjb_reader_close(r)
+    return b"".join(out), nr.value, nb.value, n_long
+
+
+@pytest.mark.parametrize("gz", [False, True])
+def test_reads_longer_than_a_chunk(tmp_path, built, gz):
+    """the reference's parser accepts reads of any length (src/kseq.h:172-212); here a read that does not fit into a
+    chunk is handed out on its own, in order, between the chunks of the reads around it"""
+    rng = np.random.default_rng(5)
+    seqs = [bytes(rng.choice(list(b"ACGT"), size=n).astype(np.uint8)) for n in (50, 3000, 80, 999, 1000, 5000, 10, 7)]
+    for fasta in (False, True):
+        p = str(tmp_path / (("a.fasta" if fasta else "a.fastq") + (".gz" if gz else "")))
+        with (gzip.open(p, "wb") if gz else open(p, "wb")) as f:
+            for i, q in enumerate(seqs):
+                if fasta:  # multi-line FASTA: the long reads span many lines
+                    f.write(b">s%d\n" % i + b"\n".join(q[j:j + 60] for j in range(0, len(q), 60)) + b"\n")
+                else:
+                    f.write(b"@s%d\n" % i + q + b"\n+\n" + b"I" * len(q) + b"\n")
+        got, nr, nb, n_long = decode_with_long_reads(p, cap=1000)  # reads of >= 1000 bases do not fit (length + 1 > cap)
+        assert got == b"".join(q + b"\n" for q in seqs)
+        assert nr == len(seqs) and nb == sum(len(q) for q in seqs) and n_long == 3

@@ -153,6 +153,35 @@ def test_gpu_files_path_matches_oracle(ctx, restatement, tmp_path):
     assert hc.name == r1 and hc.n_reads == rows.shape[0] and hc.n_bases == rows.shape[0] * 150
 
 
+def test_gpu_read_longer_than_a_chunk(ctx, restatement, tmp_path):
+    """a 40 Mbp sequence (an assembly given as a sample) between ordinary reads: longer than the 32 MiB chunks of the
+    host-buffer and file paths, which scan it on its own; the reference accepts reads of any length (src/kseq.h:172-212)"""
+    import torch
+    big = synth.inject_tract_polymorphism(synth.random_genome(40_000_000, 21), 0.02, seed=3)
+    rows = synth.paired_reads(synth.random_genome(100_000, 22), 20, seed=4)
+    half = rows.shape[0] // 2
+    nl = np.frombuffer(b"\n", np.uint8)
+    buf = np.concatenate([rows[:half].reshape(-1), big, nl, rows[half:].reshape(-1), big, nl])  # twice: its tracts pass -b
+    opt = TatajubaOptions(25, 4, 2, False)
+    want = restatement.run_buffer(buf.tobytes(), 25, 4, 2, False)
+    assert want.n_raw > 400_000
+    d = torch.from_numpy(buf).cuda()
+    pyoracle.assert_same_boundary(as_boundary(ctx.count_device(d.data_ptr(), d.numel(), opt)), want, "long read, device buffer")
+    pyoracle.assert_same_boundary(as_boundary(ctx.count_host(buf, opt)), want, "long read, host buffer")
+    fa = str(tmp_path / "assembly.fasta")
+    with open(fa, "wb") as f:
+        for r in rows[:half]:
+            f.write(b">r\n" + r.tobytes())
+        f.write(b">contig\n" + b"\n".join(big[j:j + 80].tobytes() for j in range(0, big.size, 80)) + b"\n")
+        for r in rows[half:]:
+            f.write(b">r\n" + r.tobytes())
+        f.write(b">contig_again\n" + big.tobytes() + b"\n")  # one line this time
+    hc = ctx.count_files([fa], TatajubaOptions(25, 4, 2, False, paired_end=False))
+    pyoracle.assert_same_boundary(as_boundary(hc), want, "long read, FASTA file")
+    assert hc.n_reads == rows.shape[0] + 2 and hc.n_bases == rows.shape[0] * 150 + 2 * big.size
+    assert hc.n_elem > 100_000  # the contig's tracts, seen twice
+
+
 def test_gpu_matches_compiled_reference_when_it_travelled(ctx):
     if not pyoracle.Reference.available():
         pytest.skip("oracle/_ref not present")
