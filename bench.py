@@ -636,6 +636,15 @@ def c4_leg(ctxs, rank, world, timed, all_ranks_ok, args):
         stages[from_host] = {"count_samples": (t1 - t0) * 1e3, "allgather": (t2 - t1) * 1e3, "union": (t3 - t2) * 1e3}
         return uni, idx, sizes
 
+    def by_rank(ms):  # outside the timed parts: every rank's own counting time (a rank that is done early waits in the allgather)
+        if world == 1:
+            return [round(ms, 2)]
+        import torch.distributed as dist
+        mine_ms = torch.tensor([ms], dtype=torch.float64, device="cuda")
+        allr = [torch.zeros_like(mine_ms) for _ in range(world)]
+        dist.all_gather(allr, mine_ms)
+        return [round(float(x.item()), 2) for x in allr]
+
     def standin_tables(idx, sizes):
         """NOT timed (it stands in for the mapper, which is out of scope): post-mapper tables for rank 0's merge, one
         histogram per union row a sample has, located by the row's rank in the union"""
@@ -660,6 +669,7 @@ def c4_leg(ctxs, rank, world, timed, all_ranks_ok, args):
         best = None
         for _ in range(3):
             ms_f, (uni, idx, sizes) = timed(lambda: front(from_host))
+            stages[from_host]["count_samples_by_rank"] = by_rank(stages[from_host]["count_samples"])
             tables = standin_tables(idx, sizes)
             ms_b, n_concat = timed(lambda: back(tables))
             if best is None or ms_f + ms_b < best:
@@ -678,8 +688,8 @@ def c4_leg(ctxs, rank, world, timed, all_ranks_ok, args):
             "device_span": {"ms": front_by_mode[False], "value": bases_total / (front_by_mode[False] * 1e-3), "unit": "bases/s",
                             "what": "count + query rows + allgather + union: the part that runs on the GPUs and shards over them"},
             "merge_rank0_ms": back_by_mode[False],
-            "stages_ms": {k: round(v, 2) for k, v in stages[False].items()},
-            "from_host": {"ms": best_by_mode[True], "stages_ms": {k: round(v, 2) for k, v in stages[True].items()}, "value": bases_total / (best_by_mode[True] * 1e-3), "unit": "bases/s",
+            "stages_ms": {k: (round(v, 2) if not isinstance(v, list) else v) for k, v in stages[False].items()},
+            "from_host": {"ms": best_by_mode[True], "stages_ms": {k: (round(v, 2) if not isinstance(v, list) else v) for k, v in stages[True].items()}, "value": bases_total / (best_by_mode[True] * 1e-3), "unit": "bases/s",
                           "note": "the same with the reads of every sample in pinned host memory: H2D inside"},
             "n_union": out[0], "rows": out[1], "merged_rows": out[2]}
 

@@ -65,7 +65,7 @@ typedef struct {
   int64_t n_distinct;        /* distinct (base, contexts, length) before the QC filter                   */
   int64_t n_skipped_nonacgt; /* qualifying runs of a non-ACGTU byte (undefined behaviour in the reference,
                                 hopo_counter.c:233-248): counted and skipped, see DESIGN.md                 */
-  double  ms_decode, ms_device; /* host FASTQ decode wall time; device time (CUDA events) for scan+reduce */
+  double  ms_decode, ms_device; /* host FASTQ decode wall time; device time (CUDA events) for scan+reduce, profiling level 2 */
   int32_t arena;             /* non-zero: elem / idx_initial / idx_final point into the context's result arena
                                 (TJB_RESULT_ARENA): not to be free()d, valid until the context counts its next sample */
   int32_t reserved;
@@ -91,6 +91,8 @@ int  tjb_ctx_create (int device, tjb_ctx **ctx);
 void tjb_ctx_destroy (tjb_ctx *ctx);
 /* the context's stream as a cudaStream_t cast to void* (for callers that time with their own events) */
 void *tjb_ctx_stream (tjb_ctx *ctx);
+/* 0 = off; 1 = the scan kernel's launches are timed (two events per launch, nothing else: cheap enough for a timed
+ * region); 2 = every kernel, and ms_device of tjb_counter_out */
 int  tjb_ctx_set_profiling (tjb_ctx *ctx, int on);
 /* Where the result arrays live.  TJB_RESULT_MALLOC (default): malloc()ed copies owned by the caller, as the reference
  * needs them (it realloc()s and free()s hc->elem, hopo_counter.c:180-183, 562).  TJB_RESULT_ARENA: pointers into the

@@ -647,7 +647,7 @@ static int finalise_t (tjb_ctx *ctx, tjb_counter_out *out, int qc_mode)
   }
   tr.mark ("prealloc");
   ctx->t1_recorded = false;
-  if (ctx->profiling) { CU (cudaEventRecord (ctx->ev_t1, st)); ctx->t1_recorded = true; } // end of the sample's device work: no second round trip for it
+  if (ctx->profiling >= 2) { CU (cudaEventRecord (ctx->ev_t1, st)); ctx->t1_recorded = true; } // end of the sample's device work: no second round trip for it
   CU (cudaStreamSynchronize (st)); // ---- the synchronisation of the sample
   tr.mark ("sync");
   const ResultBlock *hr = ctx->h_res;
@@ -741,10 +741,10 @@ static int finalise (tjb_ctx *ctx, tjb_counter_out *out)
 
 static void out_reset (tjb_counter_out *out) { memset (out, 0, sizeof (*out)); }
 
-// device time of the call between ev_t0 and the end of the sample's device work (diagnostics, when profiling is on)
+// device time of the call between ev_t0 and the end of the sample's device work (diagnostics, profiling level 2)
 static int device_time (tjb_ctx *ctx, tjb_counter_out *out)
 {
-  if (!ctx->profiling) return 0;
+  if (ctx->profiling < 2) return 0; // level 1 times the scan kernel only (bench.py inside its timed region): nothing else is recorded
   if (!ctx->t1_recorded) CU (cudaEventRecord (ctx->ev_t1, ctx->stream)); // (paths that do not end in finalise ())
   CU (cudaEventSynchronize (ctx->ev_t1));
   ctx->t1_recorded = false;
@@ -1037,7 +1037,7 @@ int tjb_count_sample_device (tjb_ctx *ctx, const void *d_seqs, size_t n_bytes, c
   for (int attempt = 0; attempt < TJB_MAX_ATTEMPTS; attempt++) {
     out_reset (out);
     TRY (begin_sample (ctx, opt, n_bytes));
-    if (ctx->profiling) CU (cudaEventRecord (ctx->ev_t0, ctx->stream));
+    if (ctx->profiling >= 2) CU (cudaEventRecord (ctx->ev_t0, ctx->stream));
     TRY (launch_scan (ctx, (const uint8_t*) d_seqs, n_bytes));
     tr.mark ("device:scan_enqueue");
     rc = finalise (ctx, out);
@@ -1143,7 +1143,7 @@ int tjb_count_sample_host (tjb_ctx *ctx, const uint8_t *seqs, size_t n_bytes, co
   for (int attempt = 0; attempt < TJB_MAX_ATTEMPTS; attempt++) {
     out_reset (out);
     TRY (begin_sample (ctx, opt, n_bytes));
-    if (ctx->profiling) CU (cudaEventRecord (ctx->ev_t0, ctx->stream));
+    if (ctx->profiling >= 2) CU (cudaEventRecord (ctx->ev_t0, ctx->stream));
     for (int i = 0; i < 2; i++) TRY (ensure (ctx, ctx->d_chunk[i], (max_chunk < n_bytes ? max_chunk : n_bytes) + 16));
     CU (cudaEventRecord (ctx->ev_ready, ctx->stream));            // workspace set up / previous sample done
     CU (cudaStreamWaitEvent (ctx->copy_stream, ctx->ev_ready, 0));
@@ -1215,7 +1215,7 @@ static int count_files_once (tjb_ctx *ctx, const char *const *files, int n_files
     if (!ctx->h_free[i]) CU (cudaEventCreateWithFlags (&ctx->h_free[i], cudaEventDisableTiming));
   }
   for (int i = 0; i < 2; i++) TRY (ensure (ctx, ctx->d_chunk[i], TJB_CHUNK_BYTES));
-  if (ctx->profiling) CU (cudaEventRecord (ctx->ev_t0, ctx->stream));
+  if (ctx->profiling >= 2) CU (cudaEventRecord (ctx->ev_t0, ctx->stream));
   CU (cudaEventRecord (ctx->ev_ready, ctx->stream));
   CU (cudaStreamWaitEvent (ctx->copy_stream, ctx->ev_ready, 0));
   // One decoder thread per file (R1 and R2 inflate and parse concurrently; the order of the reads does not matter to
@@ -1321,7 +1321,7 @@ int tjb_sample_begin (tjb_ctx *ctx, const tjb_opts *opt, size_t n_bytes_hint)
 {
   if (!ctx) return TJB_ERR_ARG;
   TRY (begin_sample (ctx, opt, n_bytes_hint));
-  if (ctx->profiling) CU (cudaEventRecord (ctx->ev_t0, ctx->stream));
+  if (ctx->profiling >= 2) CU (cudaEventRecord (ctx->ev_t0, ctx->stream));
   return 0;
 }
 
