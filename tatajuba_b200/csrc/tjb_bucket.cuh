@@ -276,7 +276,7 @@ aggregate_kernel (const u64 *__restrict__ recs, unsigned long long *__restrict__
     for (int u = 0; u < AGG_UNROLL; u++) {
       const size_t i = i0 + u * stride;
       seen[u] = -1;
-      if (i < n) {
+      if (i < n && r[u].w[0] != 0) { // (all zero: the unused rest of a warp's block of positions, tjb_scan.cuh)
         r[u] = canon_obs<W> (r[u], k); // the scan's fast path leaves the strand canonicalisation to this kernel
         Rec<W> key = r[u];
         key.w[0] &= ~3ULL;

@@ -341,11 +341,17 @@ static int launch_scan (tjb_ctx *ctx, const uint8_t *d_seqs, size_t n)
   if (ctx->scan_launches++) CU (cudaMemsetAsync (ctx->d_tile_ctr, 0, sizeof (u32), ctx->stream)); // window tickets of this launch (the first: cleared by the prologue)
   long long want = (n_tiles + SCAN_WARPS - 1) / SCAN_WARPS;
   long long grid = want < (long long) ctx->sm_count * SCAN_CTAS_PER_SM ? want : (long long) ctx->sm_count * SCAN_CTAS_PER_SM;
+  // record positions are reserved in blocks once every warp has many windows to scan (what a warp leaves unused of its
+  // last block, at most a block per warp, is small against the record array then: bytes / 16 + 64 Ki positions)
+#ifndef SCAN_REC_BLOCK3
+#define SCAN_REC_BLOCK3 256u
+#endif
+  const u32 rec_block = (ctx->rec_words == 3 && n_tiles >= 16 * grid * SCAN_WARPS) ? SCAN_REC_BLOCK3 : 0u; // (W = 2: exact, see flush ())
   // algorithmic bytes of this launch: every sequence byte read once (+ 8W bytes per emitted record, added at finalise)
   if (ctx->rec_words == 2)
-    LAUNCH (K_SCAN, n, (tjb_scan_kernel<2><<<(u32) grid, SCAN_THREADS, scan_smem_bytes<2> (), ctx->stream>>> (d_seqs, (long long) n, opt->kmer_size, min_len, (u64*) ctx->recs.p, ctx->rec_capacity, ctx->d_res->counters, n_tiles, ctx->d_tile_ctr)));
+    LAUNCH (K_SCAN, n, (tjb_scan_kernel<2><<<(u32) grid, SCAN_THREADS, scan_smem_bytes<2> (), ctx->stream>>> (d_seqs, (long long) n, opt->kmer_size, min_len, (u64*) ctx->recs.p, ctx->rec_capacity, ctx->d_res->counters, n_tiles, ctx->d_tile_ctr, rec_block)));
   else
-    LAUNCH (K_SCAN, n, (tjb_scan_kernel<3><<<(u32) grid, SCAN_THREADS, scan_smem_bytes<3> (), ctx->stream>>> (d_seqs, (long long) n, opt->kmer_size, min_len, (u64*) ctx->recs.p, ctx->rec_capacity, ctx->d_res->counters, n_tiles, ctx->d_tile_ctr)));
+    LAUNCH (K_SCAN, n, (tjb_scan_kernel<3><<<(u32) grid, SCAN_THREADS, scan_smem_bytes<3> (), ctx->stream>>> (d_seqs, (long long) n, opt->kmer_size, min_len, (u64*) ctx->recs.p, ctx->rec_capacity, ctx->d_res->counters, n_tiles, ctx->d_tile_ctr, rec_block)));
   CU (cudaGetLastError ());
   return 0;
 }
@@ -1527,7 +1533,7 @@ static int noalloc_enqueue (unsigned char *base, int sms, const uint8_t *d_seqs,
     const int min_len = opt->min_tract_size < 2 ? 2 : opt->min_tract_size;
     const long long want = (n_tiles + SCAN_WARPS - 1) / SCAN_WARPS;
     const long long grid = want < (long long) sms * SCAN_CTAS_PER_SM ? want : (long long) sms * SCAN_CTAS_PER_SM;
-    tjb_scan_kernel<W><<<(u32) grid, SCAN_THREADS, scan_smem_bytes<W> (), st>>> (d_seqs, (long long) n, opt->kmer_size, min_len, recs, NA_REC_CAP, counters, n_tiles, tile_ctr);
+    tjb_scan_kernel<W><<<(u32) grid, SCAN_THREADS, scan_smem_bytes<W> (), st>>> (d_seqs, (long long) n, opt->kmer_size, min_len, recs, NA_REC_CAP, counters, n_tiles, tile_ctr, 0u);
     const u32 g_agg = (u32) (nblk (NA_REC_CAP, 256 * AGG_UNROLL) < (size_t) sms * 8 ? nblk (NA_REC_CAP, 256 * AGG_UNROLL) : (size_t) sms * 8);
     aggregate_kernel<W><<<g_agg, 256, 0, st>>> (recs, counters, NA_REC_CAP, tab, ovf, NA_OVF_CAP, opt->kmer_size, bins, NA_BIN_BITS);
     table_export_kernel<W><<<(u32) sms * 4, 256, 0, st>>> (tab, ovf, counters, NA_OVF_CAP, d_rows, n_rows, max_rows);

@@ -156,7 +156,7 @@ template <int W>
 __global__ void __launch_bounds__ (SCAN_THREADS, SCAN_CTAS_PER_SM)
 tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_len, u64 *__restrict__ out,
                  unsigned long long capacity, unsigned long long *__restrict__ counters, long long n_tiles,
-                 u32 *__restrict__ tile_ctr)
+                 u32 *__restrict__ tile_ctr, u32 rec_block)
 {
   extern __shared__ __align__ (16) unsigned char scan_smem[];
   ScanWarpSmem<W> *S = reinterpret_cast<ScanWarpSmem<W>*> (scan_smem) + (threadIdx.x >> 5);
@@ -208,20 +208,45 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
       }
     }
   };
-  auto flush = [&] () { // staged records -> global array, one atomicAdd
-    unsigned long long base = 0;
-    if (lane == 0) base = atomicAdd (&counters[CTR_RECORDS], (unsigned long long) nrec);
-    base = __shfl_sync (0xffffffffu, base, 0);
-    if (W == 2 && base + nrec <= capacity) { // one record = one 16-byte store
-      const ulonglong2 *src = reinterpret_cast<const ulonglong2*> (S->rec);
+  // staged records -> global array.  Every warp of the grid takes its positions from ONE counter, and one address
+  // serves about one atomic per nanosecond: with a request per ~40 records a dense sample (configs[4]: 39 M records in
+  // 1.3 ms) ran at exactly that rate, whatever the instruction count.  rec_block > 0: a warp reserves rec_block (>= 64)
+  // positions at a time and fills them flush by flush (a flush may straddle two blocks); what is left of its last block
+  // when the kernel ends is filled with all-zero records, which no real record is (aggregate_kernel skips them).
+  // rec_block == 0: exact reservations, no holes (small inputs, and callers that read CTR_RECORDS as a count).
+  unsigned long long blk_pos = 0, blk_end = 0;
+  auto store_staged = [&] (u32 first, unsigned long long base, u32 cnt) { // records [first, first + cnt) of the staging area
+    if (W == 2 && base + cnt <= capacity) { // one record = one 16-byte store
+      const ulonglong2 *src = reinterpret_cast<const ulonglong2*> (S->rec) + first;
       ulonglong2 *dst = reinterpret_cast<ulonglong2*> (out) + base;
       static_assert (SW_RCAP (2) <= 64, "two stores per lane cover the staging area");
-      if ((u32) lane < nrec) dst[lane] = src[lane];
-      if ((u32) lane + 32 < nrec) dst[lane + 32] = src[lane + 32];
+      if ((u32) lane < cnt) dst[lane] = src[lane];
+      if ((u32) lane + 32 < cnt) dst[lane + 32] = src[lane + 32];
     } else {
-      for (u32 i = lane; i < nrec * W; i += 32) {
+      for (u32 i = lane; i < cnt * W; i += 32) {
         const unsigned long long r = base + i / W;
-        if (r < capacity) out[r * W + (i % W)] = S->rec[i];
+        if (r < capacity) out[r * W + (i % W)] = S->rec[first * W + i];
+      }
+    }
+  };
+  auto flush = [&] () {
+    if (W == 2 || !rec_block) { // (two-word records: measured slower with blocks, 181 -> 190-195 us at configs[1])
+      unsigned long long base = 0;
+      if (lane == 0) base = atomicAdd (&counters[CTR_RECORDS], (unsigned long long) nrec);
+      base = __shfl_sync (0xffffffffu, base, 0);
+      store_staged (0, base, nrec);
+    } else {
+      u32 done = 0;
+      while (done < nrec) { // at most twice: rec_block >= the staging area
+        if (blk_pos == blk_end) {
+          unsigned long long base = 0;
+          if (lane == 0) base = atomicAdd (&counters[CTR_RECORDS], (unsigned long long) rec_block);
+          blk_pos = __shfl_sync (0xffffffffu, base, 0);
+          blk_end = blk_pos + rec_block;
+        }
+        const u32 room = (u32) (blk_end - blk_pos), n1 = nrec - done < room ? nrec - done : room;
+        store_staged (done, blk_pos, n1);
+        blk_pos += n1; done += n1;
       }
     }
     nrec = 0;
@@ -261,10 +286,10 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
           const u32 m2 = __funnelshift_r (n2, n3, sh) & low_mask (nspan - 64);
           if (!(m0 | m1 | m2)) {
             const u64 gl64 = codes_at (codes, P) & kmask, gr64 = codes_at (codes, s + len) & kmask;
-            // two-word records leave the strand canonicalisation to the kernel that counts them (measured: configs[1]
-            // 191 -> 178 us); with three-word records (k >= 27) the same change made the scan slower (configs[4] 1.30 ->
-            // 1.75 ms), so they are written in their final form
-            if (SCAN_RAW_OBS && W == 2) r = pack_obs<W> (gl64, gr64, gray, len); // len < 32: the 10-bit field holds it as it is
+            // the strand canonicalisation is left to the kernel that counts the records (measured: configs[1] 191 -> 178 us;
+            // configs[4] 1.30 -> 1.17 ms once the record positions were reserved in blocks: without them the faster scan
+            // ran into the rate of its one position counter, 1.75 ms)
+            if (SCAN_RAW_OBS) r = pack_obs<W> (gl64, gr64, gray, len); // len < 32: the 10-bit field holds it as it is
             else r = canon_from_gray<W> (gl64, gr64, gray, len, k);
             emit = true;
           }
@@ -515,6 +540,11 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
   if (tail != head) // what is left belongs to the last window, whose bytes are still staged
     process_batch (lane < (int) (tail - head) ? (int) S->cand[head + lane] : -1, st ^ 1, old_g0, 0);
   if (nrec) flush ();
+  if (W != 2) for (unsigned long long r = blk_pos + lane; r < blk_end; r += 32) // the rest of this warp's last block: empty records
+    if (r < capacity) {
+#pragma unroll
+      for (int j = 0; j < W; j++) out[r * W + j] = 0ULL;
+    }
 #pragma unroll
   for (int d = 16; d; d >>= 1) nskip += __shfl_xor_sync (0xffffffffu, nskip, d);
   if (lane == 0 && nskip) atomicAdd (&counters[CTR_SKIP], (unsigned long long) nskip);
