@@ -346,7 +346,7 @@ static int launch_scan (tjb_ctx *ctx, const uint8_t *d_seqs, size_t n)
 #ifndef SCAN_REC_BLOCK3
 #define SCAN_REC_BLOCK3 256u
 #endif
-  const u32 rec_block = (ctx->rec_words == 3 && n_tiles >= 16 * grid * SCAN_WARPS) ? SCAN_REC_BLOCK3 : 0u; // (W = 2: exact, see flush ())
+  const u32 rec_block = ((ctx->rec_words == 3 || SCAN_BLOCKS_W2) && n_tiles >= 16 * grid * SCAN_WARPS) ? (ctx->rec_words == 3 ? SCAN_REC_BLOCK3 : 128u) : 0u; // (W = 2: exact, see flush ())
   // algorithmic bytes of this launch: every sequence byte read once (+ 8W bytes per emitted record, added at finalise)
   if (ctx->rec_words == 2)
     LAUNCH (K_SCAN, n, (tjb_scan_kernel<2><<<(u32) grid, SCAN_THREADS, scan_smem_bytes<2> (), ctx->stream>>> (d_seqs, (long long) n, opt->kmer_size, min_len, (u64*) ctx->recs.p, ctx->rec_capacity, ctx->d_res->counters, n_tiles, ctx->d_tile_ctr, rec_block)));

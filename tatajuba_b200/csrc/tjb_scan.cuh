@@ -63,6 +63,9 @@
 #define SW_QCAP 512                   // candidate queue (linear; moved to the front when the next round may not fit)
 #endif
 #define SW_QUOTA 7                    // new candidates per lane and round
+#ifndef SCAN_BLOCKS_W2
+#define SCAN_BLOCKS_W2 0
+#endif
 #ifndef SCAN_STATIC_PCT
 #define SCAN_STATIC_PCT 60            // share of the windows dealt to the warps up front (the rest goes by ticket)
 #endif
@@ -230,7 +233,7 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
     }
   };
   auto flush = [&] () {
-    if (W == 2 || !rec_block) { // (two-word records: measured slower with blocks, 181 -> 190-195 us at configs[1])
+    if ((W == 2 && !SCAN_BLOCKS_W2) || !rec_block) { // (two-word records: measured slower with blocks, 181 -> 190-195 us at configs[1]; the kernel grows from 6.4 K to 7.6 K instructions)
       unsigned long long base = 0;
       if (lane == 0) base = atomicAdd (&counters[CTR_RECORDS], (unsigned long long) nrec);
       base = __shfl_sync (0xffffffffu, base, 0);
@@ -540,7 +543,7 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
   if (tail != head) // what is left belongs to the last window, whose bytes are still staged
     process_batch (lane < (int) (tail - head) ? (int) S->cand[head + lane] : -1, st ^ 1, old_g0, 0);
   if (nrec) flush ();
-  if (W != 2) for (unsigned long long r = blk_pos + lane; r < blk_end; r += 32) // the rest of this warp's last block: empty records
+  if (W != 2 || SCAN_BLOCKS_W2) for (unsigned long long r = blk_pos + lane; r < blk_end; r += 32) // the rest of this warp's last block: empty records
     if (r < capacity) {
 #pragma unroll
       for (int j = 0; j < W; j++) out[r * W + j] = 0ULL;
