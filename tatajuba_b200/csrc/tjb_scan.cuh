@@ -155,6 +155,88 @@ __device__ __forceinline__ u32 prmt (u32 a, u32 b, u32 sel)
   return d;
 }
 
+// ---- the byte-exact slow path: the reference loop (hopo_counter.c:219-258) restated literally over every byte run of
+// the code run that starts at global position ps0 (gray = its 2-bit code).  Taken by candidates whose span holds a byte
+// that is neither ACGT nor the separator, and by runs of 32+.  Phase B is expanded at several places of the
+// kernel and this code is cold (SCAN_SLOW_INLINE = 0 keeps one copy behind a call).  Returns the number of fenced runs (non-ACGTU run that is the first tract of its read).
+#ifndef SCAN_SLOW_INLINE
+#define SCAN_SLOW_INLINE 1 // 0: one copy behind a call; measured slower (spills around the call: 177 -> 188 us at configs[1])
+#endif
+#if SCAN_SLOW_INLINE
+#define SCAN_SLOW_ATTR __forceinline__
+#else
+#define SCAN_SLOW_ATTR __noinline__
+#endif
+template <int W>
+__device__ SCAN_SLOW_ATTR u32 scan_slow_path (const uint8_t *__restrict__ buf, long long n, int k, int min_len, u64 *__restrict__ out,
+                                            unsigned long long capacity, unsigned long long *__restrict__ counters,
+                                            const uint8_t *s_lutf, const uint8_t *s_lutr, long long ps0, int gray)
+{
+  u32 nskip = 0;
+  auto byte_at = [&] (long long gp) -> int { return (gp >= 0 && gp < n) ? buf[gp] : '\n'; };
+  // contexts of the byte run [rs, re] of a base with forward code `code` (0..3); false when a flank leaves the read
+  auto flanks = [&] (long long rs, long long re, int code, u64 &ctx0, u64 &ctx1) -> bool {
+    bool ok = true;
+    ctx0 = ctx1 = 0;
+    for (int j = 0; j < k; j++) {
+      const int bl = byte_at (code < 2 ? rs - k + j : re + k - j), br = byte_at (code < 2 ? re + 1 + j : rs - 1 - j);
+      const int cl = (code < 2) ? s_lutf[bl] : s_lutr[bl], cr = (code < 2) ? s_lutf[br] : s_lutr[br];
+      ok = ok && (cl != 5) && (cr != 5);
+      ctx0 |= (u64) (cl & 3) << (2 * j);
+      ctx1 |= (u64) (cr & 3) << (2 * j);
+    }
+    return ok;
+  };
+  auto emit_slow = [&] (u64 ctx0, u64 ctx1, int code, long long len) { // rare path: straight to global
+    const Rec<W> q = pack_rec<W> (ctx0, ctx1, code < 2 ? code : 3 - code, sext_field (len, 10), code < 2 ? 1 : 2, k);
+    const unsigned long long pos = atomicAdd (&counters[CTR_RECORDS], 1ULL);
+    if (pos < capacity) store_rec<W> (out, pos, q);
+  };
+  long long ps = ps0;
+  while (ps < n) {
+    const int b0 = byte_at (ps);
+    if (((b0 >> 1) & 3) != gray) break;
+    long long pe = ps;
+    while (pe + 1 < n && byte_at (pe + 1) == b0) pe++;
+    const long long len = pe - ps + 1;
+    const int code = s_lutf[b0];
+    // cheap exits first
+    if (len >= min_len && code != 5 && byte_at (ps - 1) != '\n' && byte_at (pe + 1) != '\n') {
+      u64 ctx0, ctx1;
+      if (flanks (ps, pe, code & 3, ctx0, ctx1)) {
+        if (code < 4) emit_slow (ctx0, ctx1, code, len);
+        else {
+          // Run of a byte that is none of ACGTU (e.g. NNNN).  The reference takes neither strand branch and calls
+          // add_kmer_to_hopo_counter() with whatever context[], hopo_base_int and reverse_forward_flag hold
+          // (hopo_counter.c:233-248): those of the last tract emitted for THIS read, with the length of this run.
+          // Walk back to that tract; when the read has none the reference reads uninitialised stack: fenced,
+          // counted and skipped.  (The right-edge rule holds for every earlier run because it holds for this one;
+          // once a run is closer than k to the read start so is every run before it.)
+          bool found = false;
+          long long q = ps - 1;
+          for (;;) {
+            const int b1 = byte_at (q);
+            if (b1 == '\n') break;
+            long long qs = q;
+            while (byte_at (qs - 1) == b1) qs--;
+            const int c1 = s_lutf[b1];
+            if (q - qs + 1 >= min_len && c1 < 4) {
+              bool okl = true;
+              for (int j = 1; j <= k; j++) okl = okl && byte_at (qs - j) != '\n';
+              if (okl) { flanks (qs, q, c1, ctx0, ctx1); emit_slow (ctx0, ctx1, c1, len); found = true; }
+              break;
+            }
+            q = qs - 1;
+          }
+          if (!found) nskip++;
+        }
+      }
+    }
+    ps = pe + 1;
+  }
+  return nskip;
+}
+
 template <int W>
 __global__ void __launch_bounds__ (SCAN_THREADS, SCAN_CTAS_PER_SM)
 tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_len, u64 *__restrict__ out,
@@ -306,71 +388,8 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
       for (int j = 0; j < W; j++) S->rec[slot * W + j] = r.w[j];
     }
     nrec += __popc (em);
-    if (slow) {
-      // byte-exact restatement of the reference loop over every byte run inside this code run
-      const long long g0 = par == cur_st ? cur_g0 : old_g0;
-      auto byte_at = [&] (long long gp) -> int { return (gp >= 0 && gp < n) ? buf[gp] : '\n'; };
-      // contexts of the byte run [rs, re] of a base with forward code `code` (0..3); false when a flank leaves the read
-      auto flanks = [&] (long long rs, long long re, int code, u64 &ctx0, u64 &ctx1) -> bool {
-        bool ok = true;
-        ctx0 = ctx1 = 0;
-        for (int j = 0; j < k; j++) {
-          const int bl = byte_at (code < 2 ? rs - k + j : re + k - j), br = byte_at (code < 2 ? re + 1 + j : rs - 1 - j);
-          const int cl = (code < 2) ? s_lutf[bl] : s_lutr[bl], cr = (code < 2) ? s_lutf[br] : s_lutr[br];
-          ok = ok && (cl != 5) && (cr != 5);
-          ctx0 |= (u64) (cl & 3) << (2 * j);
-          ctx1 |= (u64) (cr & 3) << (2 * j);
-        }
-        return ok;
-      };
-      auto emit_slow = [&] (u64 ctx0, u64 ctx1, int code, long long len) { // rare path: straight to global
-        const Rec<W> q = pack_rec<W> (ctx0, ctx1, code < 2 ? code : 3 - code, sext_field (len, 10), code < 2 ? 1 : 2, k);
-        const unsigned long long pos = atomicAdd (&counters[CTR_RECORDS], 1ULL);
-        if (pos < capacity) store_rec<W> (out, pos, q);
-      };
-      long long ps = g0 + s;
-      while (ps < n) {
-        const int b0 = byte_at (ps);
-        if (((b0 >> 1) & 3) != gray) break;
-        long long pe = ps;
-        while (pe + 1 < n && byte_at (pe + 1) == b0) pe++;
-        const long long len = pe - ps + 1;
-        const int code = s_lutf[b0];
-        // cheap exits first
-        if (len >= min_len && code != 5 && byte_at (ps - 1) != '\n' && byte_at (pe + 1) != '\n') {
-          u64 ctx0, ctx1;
-          if (flanks (ps, pe, code & 3, ctx0, ctx1)) {
-            if (code < 4) emit_slow (ctx0, ctx1, code, len);
-            else {
-              // Run of a byte that is none of ACGTU (e.g. NNNN).  The reference takes neither strand branch and calls
-              // add_kmer_to_hopo_counter() with whatever context[], hopo_base_int and reverse_forward_flag hold
-              // (hopo_counter.c:233-248): those of the last tract emitted for THIS read, with the length of this run.
-              // Walk back to that tract; when the read has none the reference reads uninitialised stack: fenced,
-              // counted and skipped.  (The right-edge rule holds for every earlier run because it holds for this one;
-              // once a run is closer than k to the read start so is every run before it.)
-              bool found = false;
-              long long q = ps - 1;
-              for (;;) {
-                const int b1 = byte_at (q);
-                if (b1 == '\n') break;
-                long long qs = q;
-                while (byte_at (qs - 1) == b1) qs--;
-                const int c1 = s_lutf[b1];
-                if (q - qs + 1 >= min_len && c1 < 4) {
-                  bool okl = true;
-                  for (int j = 1; j <= k; j++) okl = okl && byte_at (qs - j) != '\n';
-                  if (okl) { flanks (qs, q, c1, ctx0, ctx1); emit_slow (ctx0, ctx1, c1, len); found = true; }
-                  break;
-                }
-                q = qs - 1;
-              }
-              if (!found) nskip++;
-            }
-          }
-        }
-        ps = pe + 1;
-      }
-    }
+    if (slow) // rare
+      nskip += scan_slow_path<W> (buf, n, k, min_len, out, capacity, counters, s_lutf, s_lutr, (par == cur_st ? cur_g0 : old_g0) + s, gray);
     __syncwarp ();
     if (nrec > SW_RCAP (W) - 32) flush ();
   };
