@@ -314,19 +314,49 @@ struct Hist {
 
 const char kBase[4] = {'A', 'C', 'G', 'T'};
 
-// "LEFT.B.RIGHT" of a context, reverse complemented for a hit on the negative strand (src/hopo_counter.c:471-493)
+// "LEFT.B.RIGHT" of a context, reverse complemented for a hit on the negative strand (src/hopo_counter.c:471-493).
+// Four bases per table look-up: kQuad[b] = the four letters of the byte b of 2-bit codes, first base first.
+struct QuadTable {
+  char fwd[256][4], rev[256][4]; // rev: complemented, last base first
+  QuadTable ()
+  {
+    for (int b = 0; b < 256; b++)
+      for (int j = 0; j < 4; j++) {
+        const int code = (b >> (2 * j)) & 3;
+        fwd[b][j] = kBase[code];
+        rev[b][3 - j] = kBase[3 - code];
+      }
+  }
+};
+const QuadTable kQuad;
+
+// k letters of a flank, first base first, into dst
+inline void flank_letters (uint64_t ctx, int k, char *dst)
+{
+  int i = 0;
+  for (; i + 4 <= k; i += 4, ctx >>= 8) memcpy (dst + i, kQuad.fwd[ctx & 0xff], 4);
+  for (; i < k; i++, ctx >>= 2) dst[i] = kBase[ctx & 3];
+}
+// the same flank complemented, last base first, ending at dst_end (exclusive)
+inline void flank_letters_rc (uint64_t ctx, int k, char *dst_end)
+{
+  int i = 0;
+  for (; i + 4 <= k; i += 4, ctx >>= 8) memcpy (dst_end - i - 4, kQuad.rev[ctx & 0xff], 4);
+  for (; i < k; i++, ctx >>= 2) dst_end[-1 - i] = kBase[3 - (ctx & 3)];
+}
+
 std::string context_name (const uint64_t *ctx, int32_t base, int k, bool neg)
 {
   std::string s ((size_t) 2 * k + 3, '.');
   if (!neg) {
-    for (int i = 0; i < k; i++) s[i] = kBase[(ctx[0] >> (2 * i)) & 3];
+    flank_letters (ctx[0], k, &s[0]);
     s[k + 1] = kBase[base & 3];
-    for (int i = 0; i < k; i++) s[k + 3 + i] = kBase[(ctx[1] >> (2 * i)) & 3];
-  } else {
+    flank_letters (ctx[1], k, &s[k + 3]);
+  } else { // position n - 1 - i of the forward name, complemented
     const int n = 2 * k + 3;
-    for (int i = 0; i < k; i++) s[n - 1 - i] = kBase[(~(ctx[0] >> (2 * i))) & 3];
+    flank_letters_rc (ctx[0], k, &s[0] + n);
     s[n - 1 - (k + 1)] = kBase[(~base) & 3];
-    for (int i = 0; i < k; i++) s[n - 1 - (k + 3) - i] = kBase[(~(ctx[1] >> (2 * i))) & 3];
+    flank_letters_rc (ctx[1], k, &s[0] + n - (k + 3));
   }
   return s;
 }
