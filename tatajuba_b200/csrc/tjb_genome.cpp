@@ -109,9 +109,18 @@ extern "C" int tjb_merge_tracts (int32_t n_samples, const int32_t *n_hist, const
     fn (0);
     for (auto &t : th) t.join ();
   };
-  Row *acc = (Row*) malloc (sizeof (Row) * (size_t) total), *other = (Row*) malloc (sizeof (Row) * (size_t) total);
-  struct Free { Row *&a, *&b; ~Free () { free (a); free (b); } } free_rows = {acc, other};
-  if (!acc || !other) return TJB_ERR_NOMEM;
+  // the two row arrays (16 bytes per row each) are kept by the calling thread from one call to the next: on fresh
+  // memory, page faults were 40 % of a merge of 1.9 M rows
+  struct Scratch { void *p = nullptr; size_t cap = 0; ~Scratch () { free (p); } };
+  static thread_local Scratch scratch;
+  const size_t need = 2 * sizeof (Row) * (size_t) total;
+  if (scratch.cap < need) {
+    free (scratch.p);
+    scratch.p = malloc (need + need / 8);
+    scratch.cap = scratch.p ? need + need / 8 : 0;
+    if (!scratch.p) return TJB_ERR_NOMEM;
+  }
+  Row *acc = (Row*) scratch.p, *other = acc + total;
   // rows with their (biased: locations may be negative, nothing forbids it) location; every worker takes a share of
   // the rows (and is the first to touch that part of both arrays)
   struct Seen { uint32_t differ = 0, lo = 0xffffffffu, hi = 0; int32_t max_mode_len = 0; bool ascending = true; };
