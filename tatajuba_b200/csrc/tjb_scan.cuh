@@ -511,10 +511,9 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
       const bool capped = __any_sync (0xffffffffu, have > SW_QUOTA); // rare: some lane keeps candidates for another round
       // every lane reserves its entries with one shared-memory atomic on the warp's tail (their order within a round
       // does not matter); the new tail is read back after the entries are written
-      int total = 1;
       u32 pos = 0;
       if (mine) pos = atomicAdd (&S->qtail, (u32) mine);
-      if (total) {
+      {
         unsigned short *qp = S->cand + pos;
         if (!capped) {
 #pragma unroll
@@ -536,21 +535,18 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
         }
         __syncwarp ();
         tail = *reinterpret_cast<volatile u32*> (&S->qtail);
-        while (tail - head >= 32) {
-          process_batch ((int) S->cand[head + lane], st, g0, old_g0);
-          head += 32;
-          n_old = n_old > 32 ? n_old - 32 : 0;
-        }
       }
-      const bool more = capped; // a capped lane has bits left
-      if (!more && !n_old) break;
-      // candidates of the previous window must go before its derived arrays are overwritten by the next window
-      if (n_old) {
-        process_batch (lane < (int) (tail - head) ? (int) S->cand[head + lane] : -1, st, g0, old_g0);
-        head = tail;
-        n_old = 0;
+      // full batches; then, once, whatever is left when it still holds candidates of the previous window: they must go
+      // before its derived arrays are overwritten by the next window.  (One expansion of phase B for both cases.)
+      for (;;) {
+        const u32 left = tail - head;
+        if (left < 32 && !n_old) break;
+        const u32 take = left < 32 ? left : 32;
+        process_batch ((u32) lane < take ? (int) S->cand[head + lane] : -1, st, g0, old_g0);
+        head += take;
+        n_old = n_old > take ? n_old - take : 0;
       }
-      if (!more) break;
+      if (!capped) break; // (a capped lane has bits left: another round)
     }
     n_old = tail - head; // what is left (< 32 candidates) waits for the next window
     old_g0 = g0;
