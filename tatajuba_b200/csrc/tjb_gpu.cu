@@ -1110,8 +1110,8 @@ static bool packed_transfer_enabled (tjb_ctx *ctx, size_t n_bytes)
 {
   if (n_bytes < TJB_PACK_MIN_BYTES) return false;
   tjb_packer *pool = host_pool ();
-  // a packer thread turns ~6 GB/s of reads into 2-bit codes; the copy engine moves ~55 GB/s of plain bytes: below ~10
-  // threads (ranks that share a host split its cores) the bytes are sent as they are
+  // sixteen packer threads turn 80-100 GB/s of reads into 2-bit codes (tools/pack_bench.py), fewer than ten do not beat
+  // the copy engine's ~55 GB/s of plain bytes (ranks that share a host split its cores): then the bytes are sent as they are
   if (!pool || tjb_packer_threads (pool) < 9) return false;
   for (int i = 0; i < 2; i++) {
     if (!ctx->h_pk[i] && cudaMallocHost ((void**) &ctx->h_pk[i], TJB_HOST_CHUNK_BYTES / 4 + 64) != cudaSuccess) return false;
@@ -1134,8 +1134,9 @@ static bool host_range_is_pinned (const void *p)
 
 // Host buffer: chunks are copied on the context's copy stream while the previous chunk is scanned on the compute
 // stream (two device chunk buffers).  Large inputs cross PCIe 2-bit packed (host threads pack chunk i+1 while chunk i is
-// copied, unpacked and scanned); when the caller's memory is pinned, every third chunk travels as it is instead, so that
-// the copy engine (~55 GB/s of plain bytes) and the packer threads (~70 GB/s) work on different chunks at the same time.
+// copied, unpacked and scanned).  TJB_PLAIN_EVERY=n sends every n-th chunk of a pinned buffer as it is, so that the copy
+// engine and the packer threads work on different chunks at the same time: measured slower (both draw on the host's
+// memory bandwidth), off by default.
 int tjb_count_sample_host (tjb_ctx *ctx, const uint8_t *seqs, size_t n_bytes, const tjb_opts *opt, tjb_counter_out *out)
 {
   if (!ctx || !out || (n_bytes && !seqs)) return TJB_ERR_ARG;
