@@ -433,74 +433,80 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
     if (lane == 0) S->qtail = cnt;
     __syncwarp ();
   };
-  for (; t_cur < n_tiles; st ^= 1) {
-    if (want_ticket) { if (lane == 0) t_fut = atomicAdd (tile_ctr, 1u); want_ticket = false; }
-    if (in_cur) { mbar_wait (&S->bar, parity); parity ^= 1u; }
-    else __syncwarp ();
-    u32 *codes = S->codes[st];
-    u32 c[SW_ROWS];
-    {
-      // ---- pass 1: 16 bytes per lane and row -> gray codes, non-letter mask, bad-group bit -------------------
-      const uint4 *raw128 = reinterpret_cast<const uint4*> (S->raw);
-      unsigned short *nl16 = reinterpret_cast<unsigned short*> (S->nl[st]);
-#pragma unroll
-      for (int row = 0; row < SW_ROWS; row++) {
-        const int grp = row * 32 + lane;
-        const uint4 v = raw128[grp];
-        const u32 w0 = v.x, w1 = v.y, w2 = v.z, w3 = v.w;
-        const u32 m0 = w0 & 0x06060606u, m1 = w1 & 0x06060606u, m2 = w2 & 0x06060606u, m3 = w3 & 0x06060606u;
-        const u32 p0 = m0 * SCAN_GRAY_MUL, p1 = m1 * SCAN_GRAY_MUL, p2 = m2 * SCAN_GRAY_MUL, p3 = m3 * SCAN_GRAY_MUL;
-        c[row] = __byte_perm (__byte_perm (p0, p1, 0x0073), __byte_perm (p2, p3, 0x0073), 0x5410);
-        // letters have bit 6 set.  Look-up selectors: code << 1 | letter, the nibbles of two words interleaved in one
-        // register.  The integer pipe is the bottleneck, so shifts, adds and the word comparison are multiply-adds
-        // with multipliers the compiler cannot see through (kq*): they issue on the FMA pipe.
-        const u32 a0 = w0 & 0x40404040u, a1 = w1 & 0x40404040u, a2 = w2 & 0x40404040u, a3 = w3 & 0x40404040u;
-        const u32 z01 = mad_hi (a1, kq30, mad_hi (a0, kq26, m1 * kq4 + m0)); // m0 | m1 << 4 | a0 >> 6 | a1 >> 2
-        const u32 z23 = mad_hi (a3, kq30, mad_hi (a2, kq26, m3 * kq4 + m2));
-        const u32 xa = prmt (SCAN_LUT_A, SCAN_LUT_B, z01), xb = prmt (SCAN_LUT_A, SCAN_LUT_B, __umulhi (z01, kq16));
-        const u32 xc = prmt (SCAN_LUT_A, SCAN_LUT_B, z23), xd = prmt (SCAN_LUT_A, SCAN_LUT_B, __umulhi (z23, kq16));
-        // the bytes their codes stand for, against the bytes themselves: (expected ^ byte) | ... over the group (the
-        // compiler makes it four compare-and-or instructions; a multiply-add / DP4A form on the FMA pipe took twice as many)
-        const u32 e01 = (prmt (xa, xb, 0x6420) ^ w0) | (prmt (xa, xb, 0x7531) ^ w1);
-        const u32 e23 = (prmt (xc, xd, 0x6420) ^ w2) | (prmt (xc, xd, 0x7531) ^ w3);
-        const u32 acc = e01 | e23;
-        // bit j of the mask = byte j is a non-letter: 64 * (255 - sum of the weights of the letters), bytes are 0x40 / 0
-        const int lo8 = dp4a_us (a1, 0x80C0E0F0u, dp4a_us (a0, 0xF8FCFEFFu, 255 * 64));
-        const int hi8 = dp4a_us (a3, 0x80C0E0F0u, dp4a_us (a2, 0xF8FCFEFFu, 255 * 64));
-        nl16[grp] = (unsigned short) __umulhi ((u32) (hi8 * 256 + lo8), kq26);
-        codes[grp] = c[row];
-        const u32 bb = __ballot_sync (0xffffffffu, acc != 0);
-        if (lane == 0) S->bad[st][row] = bb;
-      }
-    }
-    __syncwarp (); // the derived arrays are complete and nobody reads the bytes any more:
-    in_cur = false;
-    if (t_nxt < n_tiles) { in_cur = interior (t_nxt); stage_tile (t_nxt); } // fetch the next window over them
-    // ---- pass 2: code-run starts of the owned groups.  Rows 2j (even bits) and 2j+1 (odd bits) share cand_bits[j]:
-    // bit b = byte b / 2 of group 64 * j + 32 * (b & 1) + lane
+  // one more pass of the loop after the last window when candidates are left (fewer than 32, of the last window, whose
+  // derived arrays are still there): it runs the rounds below without new candidates, and they drain the queue
+  for (;; st ^= 1) {
+    const bool have_win = t_cur < n_tiles;
+    if (!have_win && !n_old) break;
     u32 cb[SW_ROWS / 2];
 #pragma unroll
     for (int j = 0; j < SW_ROWS / 2; j++) cb[j] = 0;
-    // one copy of the rows per candidate length (2, 3, 4): no test of cand_len inside them
-    auto pass2 = [&] (auto cl) {
-      constexpr int CL = decltype (cl)::value;
+    if (have_win) {
+      if (want_ticket) { if (lane == 0) t_fut = atomicAdd (tile_ctr, 1u); want_ticket = false; }
+      if (in_cur) { mbar_wait (&S->bar, parity); parity ^= 1u; }
+      else __syncwarp ();
+      u32 *codes = S->codes[st];
+      u32 c[SW_ROWS];
+      {
+        // ---- pass 1: 16 bytes per lane and row -> gray codes, non-letter mask, bad-group bit -------------------
+        const uint4 *raw128 = reinterpret_cast<const uint4*> (S->raw);
+        unsigned short *nl16 = reinterpret_cast<unsigned short*> (S->nl[st]);
 #pragma unroll
-      for (int row = 0; row < SW_ROWS; row++) {
-        const int grp = row * 32 + lane;
-        const u32 cc = c[row], cn = codes[(grp + 1) & (SW_GROUPS - 1)], cp = codes[(grp - 1) & (SW_GROUPS - 1)];
-        u32 tt = cc ^ __funnelshift_r (cc, cn, 2);
-        if (CL >= 3) tt |= cc ^ __funnelshift_r (cc, cn, 4);
-        if (CL >= 4) tt |= cc ^ __funnelshift_r (cc, cn, 6);
-        const u32 dp = cc ^ __funnelshift_l (cp, cc, 2);
-        u32 cs = ~(tt | __umulhi (tt, kq31)) & (dp | __umulhi (dp, kq31)) & 0x55555555u; // x >> 1 on the FMA pipe
-        if (row == 0 && lane < SW_G0) cs = 0;                       // halo groups are owned by the neighbouring windows
-        if (row == SW_ROWS - 1 && lane >= SW_G1 - 32 * (SW_ROWS - 1)) cs = 0;
-        cb[row >> 1] |= cs << (row & 1);
+        for (int row = 0; row < SW_ROWS; row++) {
+          const int grp = row * 32 + lane;
+          const uint4 v = raw128[grp];
+          const u32 w0 = v.x, w1 = v.y, w2 = v.z, w3 = v.w;
+          const u32 m0 = w0 & 0x06060606u, m1 = w1 & 0x06060606u, m2 = w2 & 0x06060606u, m3 = w3 & 0x06060606u;
+          const u32 p0 = m0 * SCAN_GRAY_MUL, p1 = m1 * SCAN_GRAY_MUL, p2 = m2 * SCAN_GRAY_MUL, p3 = m3 * SCAN_GRAY_MUL;
+          c[row] = __byte_perm (__byte_perm (p0, p1, 0x0073), __byte_perm (p2, p3, 0x0073), 0x5410);
+          // letters have bit 6 set.  Look-up selectors: code << 1 | letter, the nibbles of two words interleaved in one
+          // register.  The integer pipe is the bottleneck, so shifts, adds and the word comparison are multiply-adds
+          // with multipliers the compiler cannot see through (kq*): they issue on the FMA pipe.
+          const u32 a0 = w0 & 0x40404040u, a1 = w1 & 0x40404040u, a2 = w2 & 0x40404040u, a3 = w3 & 0x40404040u;
+          const u32 z01 = mad_hi (a1, kq30, mad_hi (a0, kq26, m1 * kq4 + m0)); // m0 | m1 << 4 | a0 >> 6 | a1 >> 2
+          const u32 z23 = mad_hi (a3, kq30, mad_hi (a2, kq26, m3 * kq4 + m2));
+          const u32 xa = prmt (SCAN_LUT_A, SCAN_LUT_B, z01), xb = prmt (SCAN_LUT_A, SCAN_LUT_B, __umulhi (z01, kq16));
+          const u32 xc = prmt (SCAN_LUT_A, SCAN_LUT_B, z23), xd = prmt (SCAN_LUT_A, SCAN_LUT_B, __umulhi (z23, kq16));
+          // the bytes their codes stand for, against the bytes themselves: (expected ^ byte) | ... over the group (the
+          // compiler makes it four compare-and-or instructions; a multiply-add / DP4A form on the FMA pipe took twice as many)
+          const u32 e01 = (prmt (xa, xb, 0x6420) ^ w0) | (prmt (xa, xb, 0x7531) ^ w1);
+          const u32 e23 = (prmt (xc, xd, 0x6420) ^ w2) | (prmt (xc, xd, 0x7531) ^ w3);
+          const u32 acc = e01 | e23;
+          // bit j of the mask = byte j is a non-letter: 64 * (255 - sum of the weights of the letters), bytes are 0x40 / 0
+          const int lo8 = dp4a_us (a1, 0x80C0E0F0u, dp4a_us (a0, 0xF8FCFEFFu, 255 * 64));
+          const int hi8 = dp4a_us (a3, 0x80C0E0F0u, dp4a_us (a2, 0xF8FCFEFFu, 255 * 64));
+          nl16[grp] = (unsigned short) __umulhi ((u32) (hi8 * 256 + lo8), kq26);
+          codes[grp] = c[row];
+          const u32 bb = __ballot_sync (0xffffffffu, acc != 0);
+          if (lane == 0) S->bad[st][row] = bb;
+        }
       }
-    };
-    if (cand_len >= 4) pass2 (std::integral_constant<int, 4> ());
-    else if (cand_len == 3) pass2 (std::integral_constant<int, 3> ());
-    else pass2 (std::integral_constant<int, 2> ());
+      __syncwarp (); // the derived arrays are complete and nobody reads the bytes any more:
+      in_cur = false;
+      if (t_nxt < n_tiles) { in_cur = interior (t_nxt); stage_tile (t_nxt); } // fetch the next window over them
+      // ---- pass 2: code-run starts of the owned groups.  Rows 2j (even bits) and 2j+1 (odd bits) share cand_bits[j]:
+      // bit b = byte b / 2 of group 64 * j + 32 * (b & 1) + lane
+      // one copy of the rows per candidate length (2, 3, 4): no test of cand_len inside them
+      auto pass2 = [&] (auto cl) {
+        constexpr int CL = decltype (cl)::value;
+#pragma unroll
+        for (int row = 0; row < SW_ROWS; row++) {
+          const int grp = row * 32 + lane;
+          const u32 cc = c[row], cn = codes[(grp + 1) & (SW_GROUPS - 1)], cp = codes[(grp - 1) & (SW_GROUPS - 1)];
+          u32 tt = cc ^ __funnelshift_r (cc, cn, 2);
+          if (CL >= 3) tt |= cc ^ __funnelshift_r (cc, cn, 4);
+          if (CL >= 4) tt |= cc ^ __funnelshift_r (cc, cn, 6);
+          const u32 dp = cc ^ __funnelshift_l (cp, cc, 2);
+          u32 cs = ~(tt | __umulhi (tt, kq31)) & (dp | __umulhi (dp, kq31)) & 0x55555555u; // x >> 1 on the FMA pipe
+          if (row == 0 && lane < SW_G0) cs = 0;                       // halo groups are owned by the neighbouring windows
+          if (row == SW_ROWS - 1 && lane >= SW_G1 - 32 * (SW_ROWS - 1)) cs = 0;
+          cb[row >> 1] |= cs << (row & 1);
+        }
+      };
+      if (cand_len >= 4) pass2 (std::integral_constant<int, 4> ());
+      else if (cand_len == 3) pass2 (std::integral_constant<int, 3> ());
+      else pass2 (std::integral_constant<int, 2> ());
+    }
     // ---- compaction into the queue (at most SW_QUOTA per lane and round); full batches of 32 go to phase B ------
     for (;;) {
       if (tail + 32 * SW_QUOTA > SW_QCAP) queue_to_front ();
@@ -555,8 +561,6 @@ tjb_scan_kernel (const uint8_t *__restrict__ buf, long long n, int k, int min_le
     else { t_nxt = t_dyn0 + __shfl_sync (0xffffffffu, t_fut, 0) * SW_CHUNK; run_end = t_nxt + SW_CHUNK; want_ticket = true; }
     g0 = (long long) t_cur * SW_TILE - SW_HALO_L;
   }
-  if (tail != head) // what is left belongs to the last window, whose bytes are still staged
-    process_batch (lane < (int) (tail - head) ? (int) S->cand[head + lane] : -1, st ^ 1, old_g0, 0);
   if (nrec) flush ();
   if (W != 2 || SCAN_BLOCKS_W2) for (unsigned long long r = blk_pos + lane; r < blk_end; r += 32) // the rest of this warp's last block: empty records
     if (r < capacity) {
