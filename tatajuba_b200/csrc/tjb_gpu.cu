@@ -341,12 +341,13 @@ static int launch_scan (tjb_ctx *ctx, const uint8_t *d_seqs, size_t n)
   if (ctx->scan_launches++) CU (cudaMemsetAsync (ctx->d_tile_ctr, 0, sizeof (u32), ctx->stream)); // window tickets of this launch (the first: cleared by the prologue)
   long long want = (n_tiles + SCAN_WARPS - 1) / SCAN_WARPS;
   long long grid = want < (long long) ctx->sm_count * SCAN_CTAS_PER_SM ? want : (long long) ctx->sm_count * SCAN_CTAS_PER_SM;
-  // record positions are reserved in blocks once every warp has many windows to scan (what a warp leaves unused of its
-  // last block, at most a block per warp, is small against the record array then: bytes / 16 + 64 Ki positions)
+  // record positions are reserved in blocks once every warp has eight or more windows to scan (from ~110 MB of reads on;
+  // what a warp leaves unused of its last block, at most a block per warp, is small against the record array then:
+  // bytes / 16 + 64 Ki positions)
 #ifndef SCAN_REC_BLOCK3
 #define SCAN_REC_BLOCK3 256u
 #endif
-  const u32 rec_block = ((ctx->rec_words == 3 || SCAN_BLOCKS_W2) && n_tiles >= 16 * grid * SCAN_WARPS) ? (ctx->rec_words == 3 ? SCAN_REC_BLOCK3 : 128u) : 0u; // (W = 2: exact, see flush ())
+  const u32 rec_block = ((ctx->rec_words == 3 || SCAN_BLOCKS_W2) && n_tiles >= 8 * grid * SCAN_WARPS) ? (ctx->rec_words == 3 ? SCAN_REC_BLOCK3 : 128u) : 0u; // (W = 2: exact, see flush ())
   // algorithmic bytes of this launch: every sequence byte read once (+ 8W bytes per emitted record, added at finalise)
   if (ctx->rec_words == 2)
     LAUNCH (K_SCAN, n, (tjb_scan_kernel<2><<<(u32) grid, SCAN_THREADS, scan_smem_bytes<2> (), ctx->stream>>> (d_seqs, (long long) n, opt->kmer_size, min_len, (u64*) ctx->recs.p, ctx->rec_capacity, ctx->d_res->counters, n_tiles, ctx->d_tile_ctr, rec_block)));
