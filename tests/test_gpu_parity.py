@@ -182,6 +182,20 @@ def test_gpu_read_longer_than_a_chunk(ctx, restatement, tmp_path):
     assert hc.n_elem > 100_000  # the contig's tracts, seen twice
 
 
+@pytest.mark.parametrize("coverage,k,m", [(150, 32, 3), (120, 27, 2)])
+def test_gpu_mid_size_three_word_records(ctx, restatement, coverage, k, m):
+    """120-150 MB of reads with k >= 27: eight or more windows per warp, so the scan reserves its record positions in
+    blocks of 256 and fills the unused rest of every warp's last block with empty records (tjb_scan.cuh); m = 2 makes
+    the records many (14 M)"""
+    import torch
+    buf = synth.sample_buffer(1_000_000, coverage, seed=7, error_rate=0.002)
+    opt = TatajubaOptions(k, m, 5, True)
+    want = restatement.run_buffer(buf, k, m, 5, True)
+    d = torch.from_numpy(buf).cuda()
+    for rep in range(2):  # the second sample of the context: sizes from the first
+        pyoracle.assert_same_boundary(as_boundary(ctx.count_device(d.data_ptr(), d.numel(), opt)), want, f"k={k} m={m} sample {rep}")
+
+
 def test_gpu_matches_compiled_reference_when_it_travelled(ctx):
     if not pyoracle.Reference.available():
         pytest.skip("oracle/_ref not present")
