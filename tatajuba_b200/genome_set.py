@@ -318,14 +318,19 @@ def merge_tracts(tables, levenshtein_distance=2):
     total = int(n_hist.sum())
     cat = lambda k, dt: np.ascontiguousarray(np.concatenate([np.asarray(t[k], dt) for t in tables]) if total else np.zeros(0, dt))  # noqa: E731
     loc, base, mlen = cat("location", np.int32), cat("base", np.int32), cat("mode_context_length", np.int32)
-    stride = max([t["name"].shape[1] for t in tables if len(t["location"])] or [1])
-    names = np.zeros((total, stride), np.uint8)
-    off = 0
-    for t in tables:
-        n = len(t["location"])
-        if n:
-            names[off:off + n, : t["name"].shape[1]] = np.asarray(t["name"]).view(np.uint8).reshape(n, -1)
-        off += n
+    widths = {t["name"].shape[1] for t in tables if len(t["location"])}
+    stride = max(widths or [1])
+    if len(widths) == 1:  # the usual case (one kmer size): one concatenation instead of a zeroed array filled piece by piece
+        names = np.ascontiguousarray(np.concatenate([np.asarray(t["name"]).view(np.uint8).reshape(len(t["location"]), -1)
+                                                     for t in tables if len(t["location"])]))
+    else:
+        names = np.zeros((total, stride), np.uint8)
+        off = 0
+        for t in tables:
+            n = len(t["location"])
+            if n:
+                names[off:off + n, : t["name"].shape[1]] = np.asarray(t["name"]).view(np.uint8).reshape(n, -1)
+            off += n
     out = [np.empty(total, np.int32) for _ in range(3)]
     p = lambda a: C.c_void_p(a.ctypes.data)  # noqa: E731
     rc = lib.tjb_merge_tracts(len(tables), p(n_hist), p(loc), p(base), p(mlen), p(names), stride, int(levenshtein_distance),
