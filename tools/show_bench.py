@@ -15,7 +15,9 @@ for e, v in d.get("errors", {}).items():
 if "c5" in d:
     v = d["c5"]
     print(f"c5: {v['ms_per_step']:.3f} ms {v['value'] / 1e9:.0f} G  ref {v.get('reference_bases_per_s', 0) / 1e9:.3f} G  ", kern(v["kernels"]))
-if "c5_sharded" in d:
+if "c5_sharded" in d and "error" in d["c5_sharded"]:
+    print("c5 sharded: FAILED", d["c5_sharded"]["error"])
+elif "c5_sharded" in d:
     v = d["c5_sharded"]
     print(f"c5 sharded over {v['ranks']} ranks: {v['ms_per_sample']:.3f} ms {v['value'] / 1e9:.0f} G  one GPU {v['one_gpu_ms_per_sample']:.3f} ms  speed-up {v['speedup_over_one_gpu']:.2f}")
 if "c4" in d:
